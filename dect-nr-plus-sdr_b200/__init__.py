@@ -1,0 +1,155 @@
+"""dect-nr-plus-sdr_b200 -- B200 (sm_100a) implementation of the DECT NR+ PCC/PDC PHY hot path.
+
+This Python module is only a thin ctypes binding over the C ABI in include/dnrp_c_api.h
+(libdnrp_cuda.so); the product is the CUDA library.  There is no CPU fallback: if the library or a GPU
+is missing, calls raise.  The directory name is not a valid Python identifier, load it with
+
+    import importlib.util, sys
+    spec = importlib.util.spec_from_file_location("dectnrp_b200", ".../dect-nr-plus-sdr_b200/__init__.py")
+
+or use `tests/conftest.py::load_product()`.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libdnrp_cuda.so")
+HEADER_PATH = os.path.join(os.path.dirname(_HERE), "include", "dnrp_c_api.h")
+
+
+class DnrpError(RuntimeError):
+    pass
+
+
+class Psdef(C.Structure):
+    _fields_ = [(n, C.c_uint32) for n in
+                ("u", "b", "PacketLengthType", "PacketLength", "tm_mode_index", "mcs_index", "Z")]
+
+
+class PacketSizes(C.Structure):
+    _fields_ = [("psdef", Psdef)] + [(n, C.c_uint32) for n in (
+        "N_eff_TX", "N_SS", "N_TS", "N_TX", "closed_loop", "N_bps", "N_b_DFT", "N_b_CP", "N_b_OCC",
+        "N_PACKET_symb", "N_DF_symb", "N_PDC_subc", "N_DRS_subc", "G", "N_PDC_bits", "N_TB_bits",
+        "N_TB_byte", "C", "K_plus", "K_minus", "C_plus", "C_minus", "N_samples_STF",
+        "N_samples_STF_CP_only", "N_samples_DF", "N_samples_GI", "N_samples_packet_no_GI",
+        "N_samples_packet")]
+
+    def as_dict(self):
+        d = {n: getattr(self, n) for n, _ in self._fields_ if n != "psdef"}
+        d.update({n: getattr(self.psdef, n) for n, _ in Psdef._fields_})
+        return d
+
+
+class Config(C.Structure):
+    _fields_ = [("psdef", Psdef)] + [(n, C.c_uint32) for n in (
+        "N_RX", "oversampling", "resample_L", "resample_M", "max_batch", "network_id", "plcf_type",
+        "chestim_mode_lr", "chestim_mode_lr_t_stride", "tdec_min_iter", "tdec_max_iter")]
+
+
+def build(verbose=False):
+    """compile libdnrp_cuda.so in-tree for sm_100a (nvcc cross-compiles without a GPU)"""
+    subprocess.check_call(["make", "-C", _HERE, "-j8", "libdnrp_cuda.so"],
+                          stdout=None if verbose else subprocess.DEVNULL)
+    return LIB_PATH
+
+
+_lib = None
+
+
+def lib():
+    global _lib
+    if _lib is None:
+        if not os.path.exists(LIB_PATH):
+            raise DnrpError("libdnrp_cuda.so is not built (run __graft_entry__.build()); no CPU fallback exists")
+        _lib = C.CDLL(LIB_PATH)
+        _lib.dnrp_last_error_string.restype = C.c_char_p
+    return _lib
+
+
+def _check(rc):
+    if rc != 0:
+        raise DnrpError("dnrp error %d: %s" % (rc, lib().dnrp_last_error_string().decode()))
+
+
+def get_packet_sizes(u, b, PacketLengthType, PacketLength, tm_mode_index, mcs_index, Z):
+    """sp3::get_packet_sizes (host only); returns dict or None if the configuration is impossible"""
+    ps = PacketSizes()
+    rc = lib().dnrp_get_packet_sizes(C.byref(Psdef(u, b, PacketLengthType, PacketLength, tm_mode_index, mcs_index, Z)),
+                                     C.byref(ps))
+    return ps.as_dict() if rc == 0 else None
+
+
+def _ptr(a, dtype):
+    if a is None:
+        return None
+    assert a.dtype == dtype and a.flags["C_CONTIGUOUS"], (a.dtype, dtype)
+    return a.ctypes.data_as(C.c_void_p)
+
+
+class Phy:
+    """One context = one GPU + one packet geometry + a maximum batch size."""
+
+    def __init__(self, psdef, max_batch, N_RX=1, network_id=123456789, plcf_type=1, device=0, oversampling=1,
+                 resample=(1, 1), chestim_mode_lr=True, chestim_stride=2, tdec_iters=(2, 10)):
+        self._ctx = C.c_void_p()
+        cfg = Config(Psdef(*psdef), N_RX, oversampling, resample[0], resample[1], max_batch, network_id, plcf_type,
+                     int(chestim_mode_lr), chestim_stride, tdec_iters[0], tdec_iters[1])
+        _check(lib().dnrp_ctx_create(C.byref(cfg), device, C.byref(self._ctx)))
+        ps = PacketSizes()
+        _check(lib().dnrp_ctx_get_packet_sizes(self._ctx, C.byref(ps)))
+        self.ps = ps.as_dict()
+        self.max_batch = max_batch
+        self.plcf_type = plcf_type
+        self.dbits_stride = ((self.ps["G"] + 7) // 8 + 3) & ~3
+
+    def close(self):
+        if self._ctx:
+            lib().dnrp_ctx_destroy(self._ctx)
+            self._ctx = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    # ---- fec_t (reference lib/include/dectnrp/phy/fec/fec.hpp:84-166)
+    def fec_encode(self, plcf, tb, cl_bf_mask=None, rv=None):
+        n = tb.shape[0]
+        plcf = np.ascontiguousarray(plcf, dtype=np.uint8).reshape(n, 10)
+        tb = np.ascontiguousarray(tb, dtype=np.uint8).reshape(n, self.ps["N_TB_byte"])
+        pcc = np.zeros((n, 28), dtype=np.uint8)
+        pdc = np.zeros((n, self.dbits_stride), dtype=np.uint8)
+        mask = None if cl_bf_mask is None else np.ascontiguousarray(cl_bf_mask, dtype=np.uint32)
+        rvv = None if rv is None else np.ascontiguousarray(rv, dtype=np.uint8)
+        _check(lib().dnrp_fec_encode(self._ctx, n, _ptr(plcf, np.uint8), _ptr(mask, np.uint32), _ptr(tb, np.uint8),
+                                     _ptr(rvv, np.uint8), _ptr(pcc, np.uint8), _ptr(pdc, np.uint8)))
+        return pcc, pdc
+
+    def fec_decode_tb(self, llr, harq_slot=None, rv=None, harq_reset=None):
+        n = llr.shape[0]
+        llr = np.ascontiguousarray(llr, dtype=np.int16).reshape(n, self.ps["G"])
+        tb = np.zeros((n, self.ps["N_TB_byte"]), dtype=np.uint8)
+        ok = np.zeros(n, dtype=np.uint8)
+        nit = np.zeros((n, self.ps["C"]), dtype=np.uint8)
+        slot = None if harq_slot is None else np.ascontiguousarray(harq_slot, dtype=np.uint32)
+        rvv = None if rv is None else np.ascontiguousarray(rv, dtype=np.uint8)
+        rst = None if harq_reset is None else np.ascontiguousarray(harq_reset, dtype=np.uint8)
+        _check(lib().dnrp_fec_decode_tb(self._ctx, n, _ptr(llr, np.int16), _ptr(slot, np.uint32), _ptr(rvv, np.uint8),
+                                        _ptr(rst, np.uint8), _ptr(tb, np.uint8), _ptr(ok, np.uint8),
+                                        _ptr(nit, np.uint8)))
+        return ok.astype(bool), tb, nit
+
+    def fec_decode_plcf(self, llr196):
+        n = llr196.shape[0]
+        llr196 = np.ascontiguousarray(llr196, dtype=np.int16).reshape(n, 196)
+        ok = np.zeros((n, 2), dtype=np.uint8)
+        plcf = np.zeros((n, 2, 10), dtype=np.uint8)
+        mask = np.zeros((n, 2), dtype=np.uint32)
+        nit = np.zeros((n, 2), dtype=np.uint8)
+        _check(lib().dnrp_fec_decode_plcf(self._ctx, n, _ptr(llr196, np.int16), _ptr(ok, np.uint8),
+                                          _ptr(plcf, np.uint8), _ptr(mask, np.uint32), _ptr(nit, np.uint8)))
+        return ok.astype(bool), plcf, mask, nit

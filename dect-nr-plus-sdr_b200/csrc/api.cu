@@ -1,0 +1,285 @@
+// api.cu -- the extern "C" boundary of libdnrp_cuda.so (declared in include/dnrp_c_api.h).
+#include <cstring>
+#include <mutex>
+#include "ctx.hpp"
+
+namespace dnrp {
+static thread_local std::string g_last_error;
+void set_last_error(const std::string& s) { g_last_error = s; }
+}  // namespace dnrp
+
+using namespace dnrp;
+
+#define DNRP_REQUIRE(cond, msg)             \
+    do {                                    \
+        if (!(cond)) {                      \
+            dnrp::set_last_error(msg);      \
+            return DNRP_ERR_INVALID;        \
+        }                                   \
+    } while (0)
+
+static void fill_packet_sizes(const spec::packet_sizes_t& q, dnrp_packet_sizes_t* o) {
+    std::memset(o, 0, sizeof(*o));
+    std::memcpy(&o->psdef, &q.psdef, sizeof(o->psdef));
+    o->N_eff_TX = q.tm.N_eff_TX; o->N_SS = q.tm.N_SS; o->N_TS = q.tm.N_TS; o->N_TX = q.tm.N_TX;
+    o->closed_loop = q.tm.cl; o->N_bps = q.mcs.N_bps;
+    o->N_b_DFT = q.N_b_DFT; o->N_b_CP = q.N_b_CP; o->N_b_OCC = q.N_b_OCC;
+    o->N_PACKET_symb = q.N_PACKET_symb; o->N_DF_symb = q.N_DF_symb;
+    o->N_PDC_subc = q.N_PDC_subc; o->N_DRS_subc = q.N_DRS_subc;
+    o->G = q.G; o->N_PDC_bits = q.N_PDC_bits; o->N_TB_bits = q.N_TB_bits; o->N_TB_byte = q.N_TB_byte;
+    o->C = q.C; o->K_plus = q.seg.K1; o->K_minus = q.seg.K2; o->C_plus = q.seg.C1; o->C_minus = q.seg.C2;
+    o->N_samples_STF = q.N_samples_STF; o->N_samples_STF_CP_only = q.N_samples_STF_CP_only;
+    o->N_samples_DF = q.N_samples_DF; o->N_samples_GI = q.N_samples_GI;
+    o->N_samples_packet_no_GI = q.N_samples_packet_no_GI; o->N_samples_packet = q.N_samples_packet;
+}
+
+extern "C" {
+
+const char* dnrp_last_error_string(void) { return g_last_error.c_str(); }
+
+int dnrp_get_packet_sizes(const dnrp_psdef_t* psdef, dnrp_packet_sizes_t* out) {
+    DNRP_REQUIRE(psdef && out, "null argument");
+    spec::psdef_t d;
+    std::memcpy(&d, psdef, sizeof(d));
+    spec::packet_sizes_t q;
+    if (!spec::get_packet_sizes(d, q)) {
+        set_last_error("packet configuration not possible");
+        return DNRP_ERR_INVALID;
+    }
+    fill_packet_sizes(q, out);
+    return DNRP_OK;
+}
+
+int dnrp_ctx_create(const dnrp_config_t* cfg, int device, dnrp_ctx_t** out) {
+    DNRP_REQUIRE(cfg && out, "null argument");
+    DNRP_REQUIRE(cfg->max_batch > 0, "max_batch must be > 0");
+    DNRP_REQUIRE(cfg->plcf_type == 1 || cfg->plcf_type == 2, "plcf_type must be 1 or 2");
+    int ndev = 0;
+    if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
+        set_last_error("no CUDA device (this library has no CPU fallback)");
+        return DNRP_ERR_NO_DEVICE;
+    }
+    DNRP_CUDA(cudaSetDevice(device));
+    dnrp_ctx* c = new dnrp_ctx();
+    c->cfg = *cfg;
+    if (c->cfg.tdec_min_iter == 0) c->cfg.tdec_min_iter = 2;
+    if (c->cfg.tdec_max_iter == 0) c->cfg.tdec_max_iter = 10;
+    if (c->cfg.oversampling == 0) c->cfg.oversampling = 1;
+    if (c->cfg.resample_L == 0 || c->cfg.resample_M == 0) c->cfg.resample_L = c->cfg.resample_M = 1;
+    if (c->cfg.N_RX == 0) c->cfg.N_RX = 1;
+    if (c->cfg.chestim_mode_lr_t_stride == 0) c->cfg.chestim_mode_lr_t_stride = 2;
+    c->device = device;
+    c->B = cfg->max_batch;
+    spec::psdef_t d;
+    std::memcpy(&d, &cfg->psdef, sizeof(d));
+    int rc = DNRP_OK;
+    auto fail = [&](int code, const char* msg) {
+        if (msg) set_last_error(msg);
+        delete c;
+        return code;
+    };
+    if (!spec::get_packet_sizes(d, c->ps)) return fail(DNRP_ERR_INVALID, "packet configuration not possible");
+    if ((rc = build_fec_plan(c->ps, c->fec)) != DNRP_OK) return fail(rc, "FEC plan failed");
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess)
+        return fail(DNRP_ERR_CUDA, "cudaStreamCreate failed");
+
+    const fec_plan_t& f = c->fec;
+    const size_t B = c->B;
+    const uint32_t c_init = cfg->plcf_type == 1 ? (cfg->network_id & 0xff) : (cfg->network_id >> 8);
+    bool ok = true;
+#define UP(x) ok = ok && ((x) == cudaSuccess)
+    UP(c->d_rm_arena.upload(f.rm_arena));
+    UP(c->d_xp_arena.upload(f.xp_arena));
+    UP(c->d_xp_tb.upload(f.xp_tb));
+    UP(c->d_rx_cbs.upload(f.rx_cbs));
+    UP(c->d_tx_cbs.upload(f.tx_cbs));
+    UP(c->d_rx_pcc.upload(std::vector<cb_desc_t>(f.rx_pcc, f.rx_pcc + 2)));
+    UP(c->d_tx_pcc.upload(std::vector<txcb_desc_t>(f.tx_pcc, f.tx_pcc + 2)));
+    UP(c->d_gold_pdc.upload(spec::gold_sequence_packed(c_init, c->ps.G + 64)));
+    UP(c->d_gold_pcc.upload(spec::gold_sequence_packed(spec::PCC_SCRAMBLING_INIT, 256)));
+    UP(c->d_tb_in.alloc(B * f.tb_stride));
+    UP(c->d_plcf_in.alloc(B * 16));
+    UP(c->d_rv.alloc(B));
+    UP(c->d_reset.alloc(B));
+    UP(c->d_plcf_mask.alloc(B));
+    UP(c->d_slot.alloc(B));
+    UP(c->d_pdc_bits.alloc(B * f.dbits_stride));
+    UP(c->d_pcc_bits.alloc(B * 28));
+    UP(c->d_llr.alloc(B * (size_t)c->ps.G));
+    UP(c->d_llr_pcc.alloc(B * 196));
+    UP(c->d_soft.alloc(B * (size_t)f.soft_stride));
+    UP(c->d_soft_pcc.alloc(B * 640));
+    UP(c->d_cb_crc.alloc(B * c->ps.C));
+    UP(c->d_saved.alloc(B * (size_t)f.saved_stride));
+    UP(c->d_tb_out.alloc(B * (size_t)f.tb_stride));
+    UP(c->d_n_iter.alloc(B * c->ps.C));
+    UP(c->d_tb_ok.alloc(B));
+    UP(c->d_pcc_crc.alloc(B * 2));
+    UP(c->d_plcf_out.alloc(B * 32));
+    UP(c->d_pcc_n_iter.alloc(B * 2));
+    UP(c->d_pcc_mask.alloc(B * 2));
+#undef UP
+    if (!ok) return fail(DNRP_ERR_CUDA, "device allocation failed");
+    *out = c;
+    return DNRP_OK;
+}
+
+void dnrp_ctx_destroy(dnrp_ctx_t* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    delete ctx;
+}
+
+int dnrp_ctx_get_packet_sizes(const dnrp_ctx_t* ctx, dnrp_packet_sizes_t* out) {
+    DNRP_REQUIRE(ctx && out, "null argument");
+    fill_packet_sizes(ctx->ps, out);
+    return DNRP_OK;
+}
+
+int dnrp_ctx_synchronize(dnrp_ctx_t* ctx) {
+    DNRP_REQUIRE(ctx, "null argument");
+    DNRP_CUDA(cudaStreamSynchronize(ctx->stream));
+    return DNRP_OK;
+}
+
+}  // extern "C"
+
+// ---- device-side FEC stages on the context's own buffers (used by the full chain as well)
+namespace dnrp {
+
+int run_fec_encode(dnrp_ctx* c, uint32_t n, bool have_mask, bool have_rv) {
+    const fec_plan_t& f = c->fec;
+    DNRP_CUDA(cudaMemsetAsync(c->d_pdc_bits.p, 0, (size_t)n * f.dbits_stride, c->stream));
+    DNRP_CUDA(cudaMemsetAsync(c->d_pcc_bits.p, 0, (size_t)n * 28, c->stream));
+    txfec_params_t p{};
+    p.cbs = c->d_tx_cbs.p; p.C = c->ps.C;
+    p.in = c->d_tb_in.p; p.in_stride = f.tb_stride;
+    p.rv = have_rv ? c->d_rv.p : nullptr;
+    p.plcf_mask = nullptr;
+    p.gold = c->d_gold_pdc.p; p.gold_bit_off = 0;
+    p.out = c->d_pdc_bits.p; p.out_stride = f.dbits_stride;
+    p.rm_arena = c->d_rm_arena.p;
+    DNRP_CUDA(launch_tx_fec(p, n, f.Kmax, c->stream));
+    // PLCF: one launch, the descriptor (type 1 or 2) is the plan's plcf_type
+    txfec_params_t q{};
+    q.cbs = c->d_tx_pcc.p + (c->cfg.plcf_type - 1); q.C = 1;
+    q.in = c->d_plcf_in.p; q.in_stride = 16;
+    q.rv = nullptr;
+    q.plcf_mask = have_mask ? c->d_plcf_mask.p : nullptr;
+    q.gold = c->d_gold_pcc.p; q.gold_bit_off = 0;
+    q.out = c->d_pcc_bits.p; q.out_stride = 28;
+    q.rm_arena = c->d_rm_arena.p;
+    DNRP_CUDA(launch_tx_fec(q, n, 96, c->stream));
+    return DNRP_OK;
+}
+
+int run_fec_decode_tb(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, bool have_reset) {
+    const fec_plan_t& f = c->fec;
+    tdec_params_t p{};
+    p.cbs = c->d_rx_cbs.p; p.C = c->ps.C;
+    p.llr = c->d_llr.p; p.llr_stride = c->ps.G;
+    p.gold = c->d_gold_pdc.p; p.gold_bit_off = 0;
+    p.soft = c->d_soft.p; p.soft_stride = f.soft_stride;
+    p.cb_crc = c->d_cb_crc.p;
+    p.saved = c->d_saved.p; p.saved_stride = f.saved_stride;
+    p.slot = have_slot ? c->d_slot.p : nullptr;
+    p.rv = have_rv ? c->d_rv.p : nullptr;
+    p.reset = have_reset ? c->d_reset.p : nullptr;
+    p.tb_out = c->d_tb_out.p; p.tb_stride = f.tb_stride;
+    p.n_iter = c->d_n_iter.p;
+    p.rm_arena = c->d_rm_arena.p; p.xp_arena = c->d_xp_arena.p;
+    p.min_it = c->cfg.tdec_min_iter; p.max_it = c->cfg.tdec_max_iter;
+    p.crc_mode = 0; p.plcf_mask = nullptr;
+    DNRP_CUDA(launch_turbo_decode(p, n, f.tdec_threads, f.tdec_smem, c->stream));
+    tbfin_params_t t{};
+    t.C = c->ps.C; t.tbs_bits = c->ps.N_TB_bits; t.chunk_bytes = f.tb_chunk_bytes;
+    t.slot = p.slot; t.cb_crc = c->d_cb_crc.p;
+    t.tb_out = c->d_tb_out.p; t.tb_stride = f.tb_stride;
+    t.xp_tb = c->d_xp_tb.p; t.tb_ok = c->d_tb_ok.p;
+    DNRP_CUDA(launch_tb_finalize(t, n, c->stream));
+    return DNRP_OK;
+}
+
+int run_fec_decode_plcf(dnrp_ctx* c, uint32_t n) {
+    const fec_plan_t& f = c->fec;
+    tdec_params_t p{};
+    p.cbs = c->d_rx_pcc.p; p.C = 2;
+    p.llr = c->d_llr_pcc.p; p.llr_stride = 196;
+    p.gold = c->d_gold_pcc.p; p.gold_bit_off = 0;
+    p.soft = c->d_soft_pcc.p; p.soft_stride = 640;
+    p.cb_crc = c->d_pcc_crc.p;
+    p.saved = nullptr; p.saved_stride = 0;
+    p.slot = nullptr; p.rv = nullptr; p.reset = nullptr;
+    p.tb_out = c->d_plcf_out.p; p.tb_stride = 32;
+    p.n_iter = c->d_pcc_n_iter.p;
+    p.rm_arena = c->d_rm_arena.p; p.xp_arena = c->d_xp_arena.p;
+    p.min_it = 1; p.max_it = 5;  // pcc_enc.cpp:39
+    p.crc_mode = 1; p.plcf_mask = c->d_pcc_mask.p;
+    DNRP_CUDA(launch_turbo_decode(p, n, f.tdec_threads, f.tdec_smem, c->stream));
+    return DNRP_OK;
+}
+
+}  // namespace dnrp
+
+extern "C" {
+
+int dnrp_fec_encode(dnrp_ctx_t* c, uint32_t n, const uint8_t* plcf, const uint32_t* cl_bf_mask,
+                    const uint8_t* tb, const uint8_t* rv, uint8_t* pcc_bits, uint8_t* pdc_bits) {
+    DNRP_REQUIRE(c && plcf && tb && pcc_bits && pdc_bits, "null argument");
+    DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    const fec_plan_t& f = c->fec;
+    DNRP_CUDA(cudaMemcpy2DAsync(c->d_tb_in.p, f.tb_stride, tb, c->ps.N_TB_byte, c->ps.N_TB_byte, n,
+                                cudaMemcpyHostToDevice, c->stream));
+    DNRP_CUDA(cudaMemcpy2DAsync(c->d_plcf_in.p, 16, plcf, 10, 10, n, cudaMemcpyHostToDevice, c->stream));
+    if (cl_bf_mask) DNRP_CUDA(cudaMemcpyAsync(c->d_plcf_mask.p, cl_bf_mask, 4 * n, cudaMemcpyHostToDevice, c->stream));
+    if (rv) DNRP_CUDA(cudaMemcpyAsync(c->d_rv.p, rv, n, cudaMemcpyHostToDevice, c->stream));
+    int rc = run_fec_encode(c, n, cl_bf_mask != nullptr, rv != nullptr);
+    if (rc) return rc;
+    DNRP_CUDA(cudaMemcpyAsync(pcc_bits, c->d_pcc_bits.p, (size_t)n * 28, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaMemcpyAsync(pdc_bits, c->d_pdc_bits.p, (size_t)n * f.dbits_stride, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    return DNRP_OK;
+}
+
+int dnrp_fec_decode_tb(dnrp_ctx_t* c, uint32_t n, const int16_t* llr, const uint32_t* harq_slot,
+                       const uint8_t* rv, const uint8_t* harq_reset, uint8_t* tb_out, uint8_t* crc_ok,
+                       uint8_t* n_iter) {
+    DNRP_REQUIRE(c && llr && tb_out && crc_ok, "null argument");
+    DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    const fec_plan_t& f = c->fec;
+    if (harq_slot)
+        for (uint32_t i = 0; i < n; ++i) DNRP_REQUIRE(harq_slot[i] < c->B, "harq slot out of range");
+    DNRP_CUDA(cudaMemcpyAsync(c->d_llr.p, llr, (size_t)n * c->ps.G * 2, cudaMemcpyHostToDevice, c->stream));
+    if (harq_slot) DNRP_CUDA(cudaMemcpyAsync(c->d_slot.p, harq_slot, 4 * n, cudaMemcpyHostToDevice, c->stream));
+    if (rv) DNRP_CUDA(cudaMemcpyAsync(c->d_rv.p, rv, n, cudaMemcpyHostToDevice, c->stream));
+    if (harq_reset) DNRP_CUDA(cudaMemcpyAsync(c->d_reset.p, harq_reset, n, cudaMemcpyHostToDevice, c->stream));
+    int rc = run_fec_decode_tb(c, n, harq_slot != nullptr, rv != nullptr, harq_reset != nullptr);
+    if (rc) return rc;
+    DNRP_CUDA(cudaMemcpy2DAsync(tb_out, c->ps.N_TB_byte, c->d_tb_out.p, f.tb_stride, c->ps.N_TB_byte, n,
+                                cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaMemcpyAsync(crc_ok, c->d_tb_ok.p, n, cudaMemcpyDeviceToHost, c->stream));
+    if (n_iter) DNRP_CUDA(cudaMemcpyAsync(n_iter, c->d_n_iter.p, (size_t)n * c->ps.C, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    return DNRP_OK;
+}
+
+int dnrp_fec_decode_plcf(dnrp_ctx_t* c, uint32_t n, const int16_t* llr196, uint8_t* ok, uint8_t* plcf,
+                         uint32_t* mask, uint8_t* n_iter) {
+    DNRP_REQUIRE(c && llr196 && ok && plcf && mask, "null argument");
+    DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    DNRP_CUDA(cudaMemcpyAsync(c->d_llr_pcc.p, llr196, (size_t)n * 196 * 2, cudaMemcpyHostToDevice, c->stream));
+    int rc = run_fec_decode_plcf(c, n);
+    if (rc) return rc;
+    DNRP_CUDA(cudaMemcpyAsync(ok, c->d_pcc_crc.p, (size_t)n * 2, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaMemcpy2DAsync(plcf, 10, c->d_plcf_out.p, 16, 10, (size_t)n * 2, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaMemcpyAsync(mask, c->d_pcc_mask.p, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
+    if (n_iter) DNRP_CUDA(cudaMemcpyAsync(n_iter, c->d_pcc_n_iter.p, (size_t)n * 2, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    return DNRP_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,97 @@
+// ctx.hpp -- the per-device, per-geometry context behind the C ABI: host-side plan (tables derived
+// from spec*.hpp) + device workspaces.  Host C++ only; kernels are reached through the launch_*
+// functions of the .cuh headers.
+#pragma once
+#include <cuda_runtime.h>
+#include <cstdint>
+#include <string>
+#include <vector>
+#include "../../include/dnrp_c_api.h"
+#include "fec_rx.cuh"
+#include "fec_tx.cuh"
+#include "spec.hpp"
+#include "spec_fec.hpp"
+#include "spec_re.hpp"
+
+namespace dnrp {
+
+void set_last_error(const std::string& s);
+
+#define DNRP_CUDA(expr)                                                                       \
+    do {                                                                                      \
+        cudaError_t e__ = (expr);                                                             \
+        if (e__ != cudaSuccess) {                                                             \
+            ::dnrp::set_last_error(std::string(#expr) + ": " + cudaGetErrorString(e__));      \
+            return DNRP_ERR_CUDA;                                                             \
+        }                                                                                     \
+    } while (0)
+
+// RAII device allocation
+template <typename T>
+struct dbuf {
+    T* p = nullptr;
+    size_t n = 0;
+    dbuf() = default;
+    dbuf(const dbuf&) = delete;
+    dbuf& operator=(const dbuf&) = delete;
+    ~dbuf() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t count) {
+        if (p) cudaFree(p);
+        p = nullptr;
+        n = count;
+        if (count == 0) return cudaSuccess;
+        cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T));
+        if (e == cudaSuccess) e = cudaMemset(p, 0, count * sizeof(T));
+        return e;
+    }
+    cudaError_t upload(const std::vector<T>& v) {
+        cudaError_t e = alloc(v.size());
+        if (e != cudaSuccess || v.empty()) return e;
+        return cudaMemcpy(p, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice);
+    }
+};
+
+uint32_t tdec_window(uint32_t K);
+uint32_t gf2_xpow_host(uint32_t n, uint32_t poly, uint32_t order);
+
+struct fec_plan_t {
+    // rate matching / CRC-combination tables shared by all code block sizes of the plan
+    std::vector<uint16_t> rm_arena;   // per K: src[N] then pos[N]
+    std::vector<uint32_t> xp_arena;
+    std::vector<cb_desc_t> rx_cbs;    // PDC decode descriptors [C]
+    std::vector<txcb_desc_t> tx_cbs;  // PDC encode descriptors [C]
+    cb_desc_t rx_pcc[2];              // PLCF type 1 / type 2
+    txcb_desc_t tx_pcc[2];
+    std::vector<uint32_t> xp_tb;      // TB CRC chunk multipliers
+    uint32_t tb_chunk_bytes = 64;
+    uint32_t soft_stride = 0, saved_stride = 0, tb_stride = 0, dbits_stride = 0;
+    uint32_t Kmax = 0, tdec_threads = 0;
+    size_t tdec_smem = 0;
+};
+
+int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f);
+
+}  // namespace dnrp
+
+struct dnrp_ctx {
+    dnrp_config_t cfg;
+    dnrp::spec::packet_sizes_t ps;
+    int device = 0;
+    cudaStream_t stream = nullptr;
+    uint32_t B = 0;  // max batch
+
+    dnrp::fec_plan_t fec;
+    // device tables
+    dnrp::dbuf<uint16_t> d_rm_arena;
+    dnrp::dbuf<uint32_t> d_xp_arena, d_xp_tb;
+    dnrp::dbuf<dnrp::cb_desc_t> d_rx_cbs, d_rx_pcc;
+    dnrp::dbuf<dnrp::txcb_desc_t> d_tx_cbs, d_tx_pcc;
+    dnrp::dbuf<uint8_t> d_gold_pdc, d_gold_pcc;
+    // device workspaces, [B] leading dimension
+    dnrp::dbuf<uint8_t> d_tb_in, d_plcf_in, d_rv, d_reset, d_pdc_bits, d_pcc_bits;
+    dnrp::dbuf<uint32_t> d_plcf_mask, d_slot;
+    dnrp::dbuf<int16_t> d_llr, d_llr_pcc, d_soft, d_soft_pcc;
+    dnrp::dbuf<uint8_t> d_cb_crc, d_saved, d_tb_out, d_n_iter, d_tb_ok;
+    dnrp::dbuf<uint8_t> d_pcc_crc, d_plcf_out, d_pcc_n_iter;
+    dnrp::dbuf<uint32_t> d_pcc_mask;
+};

@@ -1,0 +1,389 @@
+// fec_rx.cu -- RX side of the FEC chain on the GPU: descramble + de-rate-match + HARQ combine + turbo
+// decode + CRC in ONE kernel per batch (grid = code blocks x packets), then a small per-packet kernel
+// for the transport-block level CRC logic.  Reference: lib/src/phy/fec/pdc_enc.cpp:291-492,
+// lib/src/phy/fec/pcc_enc.cpp:215-364 (file:line relative to /root/reference).
+#include "fec_rx.cuh"
+#include "turbo_dec.cuh"
+
+namespace dnrp {
+using namespace tdec;
+
+__device__ __forceinline__ int clampi(int v, int lim) { return max(-lim, min(lim, v)); }
+
+// a*b mod g over GF(2), operands < 2^order
+__device__ __forceinline__ uint32_t gf2_mulmod(uint32_t a, uint32_t b, uint32_t poly, uint32_t order) {
+    uint32_t r = 0;
+    const uint32_t top = 1u << order;
+    for (uint32_t i = 0; i < order; ++i) {
+        r <<= 1;
+        if (r & top) r ^= poly;
+        if ((b >> (order - 1 - i)) & 1) r ^= a;
+    }
+    return r;
+}
+
+__global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
+    extern __shared__ uint32_t smem[];
+    const cb_desc_t cb = p.cbs[blockIdx.x];
+    const uint32_t pkt = blockIdx.y;
+    const uint32_t slot = p.slot ? p.slot[pkt] : pkt;
+    const uint32_t tid = threadIdx.x, nthr = blockDim.x;
+    const uint32_t K = cb.K, L = cb.L, T = cb.P / 2, KH = K / 2, D = K + 4, N = 3 * D;
+    const uint32_t nck = (L + S_CK - 1) / S_CK;
+    const bool reset = p.reset ? p.reset[pkt] != 0 : true;
+    const uint32_t rv = p.rv ? p.rv[pkt] : 0;
+
+    uint8_t* cb_crc = p.cb_crc + (size_t)slot * p.C + blockIdx.x;
+    uint8_t* saved = p.saved ? p.saved + (size_t)slot * p.saved_stride + cb.saved_off : nullptr;
+    uint8_t* tb_out = p.tb_out + (size_t)pkt * p.tb_stride + cb.out_byte;
+    uint8_t* n_iter_out = p.n_iter + (size_t)pkt * p.C + blockIdx.x;
+
+    // ---- code block already decoded in an earlier transmission: copy the saved bytes
+    // (reference pdc_enc.cpp:404-406)
+    if (!reset && *cb_crc) {
+        for (uint32_t i = tid; i < cb.rlen_byte; i += nthr) tb_out[i] = saved[i];
+        if (tid == 0) *n_iter_out = 0;
+        return;
+    }
+
+    uint32_t* SYS = smem;
+    uint32_t* EXT = SYS + KH;
+    uint32_t* XIN = EXT + KH;
+    uint32_t* PAR = XIN + KH;
+    uint32_t* CK = PAR + KH;                 // [nck][7][T]
+    uint32_t* AE = CK + nck * 7 * T;         // [2][7][T]
+    uint32_t* BS = AE + 2 * 7 * T;           // [2][7][T]
+    uint8_t* HARD = (uint8_t*)(BS + 2 * 7 * T);  // [KH]
+    __shared__ uint32_t s_crc;
+
+    int16_t* soft = p.soft + (size_t)slot * p.soft_stride + cb.soft_off;
+    const int16_t* llr = p.llr + (size_t)pkt * p.llr_stride + cb.rp;
+    const uint16_t* rm_pos = p.rm_arena + cb.rm_off;
+    const uint32_t rm_start = cb.rm_start[rv];
+
+    // ---- prologue: soft[n] (+)= sum of the descrambled LLRs that rate matching mapped onto n
+    // (srsran_scrambling_s_offset + srsran_rm_turbo_rx_lut_, pdc_enc.cpp:339-363); plain int16 wrap
+    for (uint32_t n = tid; n < N; n += nthr) {
+        int acc = reset ? 0 : soft[n];
+        uint32_t e = rm_pos[n] + N - rm_start;
+        if (e >= N) e -= N;
+        for (; e < cb.n_e; e += N) {
+            const uint32_t g = cb.rp + e + p.gold_bit_off;
+            const int v = llr[e];
+            acc += ((p.gold[g >> 3] >> (7 - (g & 7))) & 1) ? -v : v;
+        }
+        const int16_t v16 = (int16_t)acc;
+        soft[n] = v16;
+        if (n < K) {
+            const uint32_t pw = n >= KH ? n - KH : n;
+            ((int16_t*)SYS)[2 * ((pw % L) * T + pw / L) + (n >= KH)] = (int16_t)clampi(v16, 1023);
+        }
+    }
+    for (uint32_t i = tid; i < KH; i += nthr) EXT[i] = 0;
+    for (uint32_t i = tid; i < 4 * 7 * T; i += nthr) AE[i] = 0;  // AE and BS are contiguous
+    __syncthreads();
+
+    const bool active = tid < T;
+    const uint32_t t = tid;
+    const uint32_t wl = t, wh = t + T, P = cb.P;
+    uint32_t n_iter = 0;
+    bool crc_ok = false;
+    uint32_t plcf_mask = 0;
+
+    for (uint32_t it = 0; it < p.max_it && !crc_ok; ++it) {
+        for (uint32_t dec = 0; dec < 2; ++dec) {
+            // ---- parity of this constituent decoder -> shared, window-transposed
+            const int16_t* par = soft + (1 + dec) * D;
+            for (uint32_t i = tid; i < K; i += nthr) {
+                const uint32_t pw = i >= KH ? i - KH : i;
+                ((int16_t*)PAR)[2 * ((pw % L) * T + pw / L) + (i >= KH)] = (int16_t)clampi(par[i], 1023);
+            }
+            // ---- decoder input x = systematic + a-priori, in decoder order
+            if (dec == 0) {
+                for (uint32_t i = tid; i < KH; i += nthr) XIN[i] = vadd(SYS[i], EXT[i]);
+            } else if (active) {
+                const uint32_t j0 = t * L;
+                uint32_t pi = (uint32_t)(((uint64_t)cb.f1 * j0 + (uint64_t)cb.f2 * j0 * j0) % K);
+                uint32_t g = (uint32_t)((cb.f1 + (uint64_t)cb.f2 * (2 * j0 + 1)) % K);
+                const uint32_t g2 = (2 * cb.f2) % K;
+                for (uint32_t k = 0; k < L; ++k) {
+                    const bool up = pi >= KH;
+                    const uint32_t pw = up ? pi - KH : pi;
+                    const uint32_t a = (pw % L) * T + pw / L;
+                    uint32_t w = vadd(SYS[a], EXT[a]);
+                    if (up) w = swap16(w);
+                    XIN[k * T + t] = w;
+                    pi += g; if (pi >= K) pi -= K;
+                    g += g2; if (g >= K) g -= K;
+                }
+            }
+            __syncthreads();
+
+            uint32_t ae_new[8], bs_new[8];
+            if (active) {
+                // ---- termination metrics of this decoder (three tail steps back from state 0)
+                int tail[8];
+                {
+                    const int16_t* d0 = soft; const int16_t* d1 = soft + D; const int16_t* d2 = soft + 2 * D;
+                    int xt[3], zt[3];
+                    if (dec == 0) {
+                        xt[0] = d0[K]; zt[0] = d1[K]; xt[1] = d2[K]; zt[1] = d0[K + 1]; xt[2] = d1[K + 1]; zt[2] = d2[K + 1];
+                    } else {
+                        xt[0] = d0[K + 2]; zt[0] = d1[K + 2]; xt[1] = d2[K + 2]; zt[1] = d0[K + 3]; xt[2] = d1[K + 3]; zt[2] = d2[K + 3];
+                    }
+                    int b[8], nb[8];
+#pragma unroll
+                    for (int s = 0; s < 8; ++s) b[s] = s == 0 ? 0 : -8192;
+#pragma unroll
+                    for (int tt = 2; tt >= 0; --tt) {
+                        const int x = clampi(xt[tt], 1023), z = clampi(zt[tt], 1023);
+                        // allowed transition: u = s1^s2 (a = 0), parity z = s0^s2, next = (0, s0, s1)
+                        nb[0] = b[0];          nb[1] = b[0] + x + z;  nb[2] = b[1] + x;      nb[3] = b[1] + z;
+                        nb[4] = b[2] + z;      nb[5] = b[2] + x;      nb[6] = b[3] + x + z;  nb[7] = b[3];
+#pragma unroll
+                        for (int s = 0; s < 8; ++s) b[s] = nb[s] - nb[0];
+                    }
+#pragma unroll
+                    for (int s = 0; s < 8; ++s) tail[s] = b[s];
+                }
+                const uint32_t* BSd = BS + dec * 7 * T;
+                const uint32_t* AEd = AE + dec * 7 * T;
+                auto fetch = [&](const uint32_t* arr, int s, uint32_t v) -> int {
+                    if (s == 0) return 0;
+                    const uint32_t w = arr[(s - 1) * T + (v % T)];
+                    return (int)(int16_t)(v >= T ? (w >> 16) : (w & 0xffff));
+                };
+
+                // ---- beta: training over window w+1 (both halves), then the real backward pass
+                uint32_t b[8];
+#pragma unroll
+                for (int s = 0; s < 8; ++s) {
+                    const int lo = (wl + 2 >= P) ? tail[s] : fetch(BSd, s, wl + 2);
+                    const int hi = (wh + 2 >= P) ? tail[s] : fetch(BSd, s, wh + 2);
+                    b[s] = pack(lo, hi);
+                }
+                {
+                    const uint32_t tn = (t + 1 == T) ? 0 : t + 1;
+                    const bool wrap = (t + 1 == T);
+                    for (int k = (int)L - 1; k >= 0; --k) {
+                        uint32_t x = XIN[k * T + tn], y = PAR[k * T + tn];
+                        if (wrap) { x >>= 16; y >>= 16; }
+                        beta_step(b, x, y);
+                    }
+                    if (wh == P - 1) {
+#pragma unroll
+                        for (int s = 0; s < 8; ++s) b[s] = (b[s] & 0xffffu) | ((uint32_t)tail[s] << 16);
+                    }
+                }
+                for (int k = (int)L - 1; k >= 0; --k) {
+                    if (((k + 1) % S_CK) == 0 || k + 1 == (int)L) {
+                        const int c = k / S_CK;
+#pragma unroll
+                        for (int s = 1; s < 8; ++s) CK[(c * 7 + s - 1) * T + t] = b[s];
+                    }
+                    beta_step(b, XIN[k * T + t], PAR[k * T + t]);
+                }
+#pragma unroll
+                for (int s = 0; s < 8; ++s) bs_new[s] = b[s];
+
+                // ---- alpha: training over window w-1, then forward pass with LLR output
+                uint32_t a[8];
+#pragma unroll
+                for (int s = 0; s < 8; ++s) {
+                    const int ex = s == 0 ? 0 : -8192;
+                    const int lo = (wl <= 1) ? ex : fetch(AEd, s, wl - 2);
+                    const int hi = (wh <= 1) ? ex : fetch(AEd, s, wh - 2);
+                    a[s] = pack(lo, hi);
+                }
+                {
+                    const uint32_t tp = (t == 0) ? T - 1 : t - 1;
+                    const bool wrap = (t == 0);
+                    for (uint32_t k = 0; k < L; ++k) {
+                        uint32_t x = XIN[k * T + tp], y = PAR[k * T + tp];
+                        if (wrap) { x <<= 16; y <<= 16; }
+                        alpha_step(a, x, y);
+                    }
+                    if (wl == 0) {
+#pragma unroll
+                        for (int s = 0; s < 8; ++s) a[s] = (a[s] & 0xffff0000u) | (s == 0 ? 0u : 0xE000u);
+                    }
+                }
+                // QPP position of the first step of this thread (decoder 2 scatters to natural order)
+                const uint32_t j0 = t * L;
+                uint32_t pi = (uint32_t)(((uint64_t)cb.f1 * j0 + (uint64_t)cb.f2 * j0 * j0) % K);
+                uint32_t g = (uint32_t)((cb.f1 + (uint64_t)cb.f2 * (2 * j0 + 1)) % K);
+                const uint32_t g2 = (2 * cb.f2) % K;
+                for (uint32_t c = 0; c < nck; ++c) {
+                    const int k0 = c * S_CK;
+                    const int n = min((int)S_CK, (int)L - k0);
+                    uint32_t bb[S_CK][8];
+#pragma unroll
+                    for (int i = 0; i < S_CK; ++i) bb[i][0] = 0;
+                    // beta at time k0+n from the checkpoint, then recompute down to k0+1
+#pragma unroll
+                    for (int i = S_CK - 1; i >= 0; --i) {
+                        if (i == n - 1) {
+#pragma unroll
+                            for (int s = 1; s < 8; ++s) bb[i][s] = CK[(c * 7 + s - 1) * T + t];
+                        } else if (i < n - 1) {
+#pragma unroll
+                            for (int s = 0; s < 8; ++s) bb[i][s] = bb[i + 1][s];
+                            beta_step(bb[i], XIN[(k0 + i + 1) * T + t], PAR[(k0 + i + 1) * T + t]);
+                        }
+                    }
+#pragma unroll
+                    for (int i = 0; i < S_CK; ++i) {
+                        if (i < n) {
+                            const uint32_t k = k0 + i;
+                            const uint32_t x = XIN[k * T + t], y = PAR[k * T + t];
+                            const uint32_t l = llr_step(a, bb[i], x, y);
+                            const uint32_t e = vclamp(vadd(l, vneg(x)), 2047);
+                            if (dec == 0) {
+                                EXT[k * T + t] = e;
+                            } else {
+                                const bool up = pi >= KH;
+                                const uint32_t pw = up ? pi - KH : pi;
+                                const uint32_t ad = (pw % L) * T + pw / L;
+                                const uint32_t hb = ((int16_t)(l & 0xffff) > 0 ? 1u : 0u) | ((int16_t)(l >> 16) > 0 ? 2u : 0u);
+                                EXT[ad] = up ? swap16(e) : e;
+                                HARD[ad] = (uint8_t)(up ? ((hb >> 1) | ((hb & 1) << 1)) : hb);
+                                pi += g; if (pi >= K) pi -= K;
+                                g += g2; if (g >= K) g -= K;
+                            }
+                            alpha_step(a, x, y);
+                        }
+                    }
+                }
+#pragma unroll
+                for (int s = 0; s < 8; ++s) ae_new[s] = a[s];
+            }
+            if (tid == 0) s_crc = 0;
+            __syncthreads();
+            if (active) {
+#pragma unroll
+                for (int s = 1; s < 8; ++s) {
+                    AE[(dec * 7 + s - 1) * T + t] = ae_new[s];
+                    BS[(dec * 7 + s - 1) * T + t] = bs_new[s];
+                }
+            }
+        }
+        // ---- CRC of the hard decisions (natural order), remainder of the whole block mod g
+        ++n_iter;
+        {
+            uint32_t r = 0;
+            if (active) {
+                uint32_t r_lo = 0, r_hi = 0;
+                const uint32_t top = 1u << cb.crc_order;
+                for (uint32_t k = 0; k < L; ++k) {
+                    const uint32_t hb = HARD[k * T + t];
+                    r_lo = (r_lo << 1) | (hb & 1);
+                    if (r_lo & top) r_lo ^= cb.crc_poly;
+                    r_hi = (r_hi << 1) | (hb >> 1);
+                    if (r_hi & top) r_hi ^= cb.crc_poly;
+                }
+                const uint32_t* xp = p.xp_arena + cb.xp_off;
+                r = gf2_mulmod(r_lo, xp[wl], cb.crc_poly, cb.crc_order) ^
+                    gf2_mulmod(r_hi, xp[wh], cb.crc_poly, cb.crc_order);
+            }
+            for (int o = 16; o > 0; o >>= 1) r ^= __shfl_xor_sync(0xffffffffu, r, o);
+            if ((tid & 31) == 0 && r) atomicXor(&s_crc, r);
+        }
+        __syncthreads();
+        const uint32_t rem = s_crc;
+        if (p.crc_mode == 0) {
+            crc_ok = (rem == 0) && n_iter >= p.min_it;
+        } else {  // PLCF: remainder equals the CL/BF mask (pcc_enc.cpp:326-346)
+            crc_ok = (rem == 0x0000 || rem == 0x5555 || rem == 0xAAAA || rem == 0xFFFF);
+            plcf_mask = rem;
+        }
+        __syncthreads();
+    }
+
+    // ---- outputs: packed bytes (MSB first), flags
+    for (uint32_t bi = tid; bi < K / 8; bi += nthr) {
+        uint32_t v = 0;
+#pragma unroll
+        for (uint32_t q = 0; q < 8; ++q) {
+            const uint32_t pos = bi * 8 + q;
+            const uint32_t pw = pos >= KH ? pos - KH : pos;
+            const uint32_t hb = HARD[(pw % L) * T + pw / L];
+            v = (v << 1) | (pos >= KH ? (hb >> 1) : (hb & 1));
+        }
+        if (bi < cb.rlen_byte) {
+            tb_out[bi] = (uint8_t)v;
+            if (saved && crc_ok) saved[bi] = (uint8_t)v;
+        }
+    }
+    if (tid == 0) {
+        *n_iter_out = (uint8_t)n_iter;
+        *cb_crc = crc_ok ? 1 : 0;
+        if (p.plcf_mask) p.plcf_mask[(size_t)pkt * p.C + blockIdx.x] = crc_ok ? plcf_mask : 0xffffffffu;
+    }
+}
+
+// ---- transport-block level logic, one block per packet (reference pdc_enc.cpp:415-489):
+// all CB CRCs ok -> (C > 1: check CRC24A over the whole TB, failure resets the CB flags)
+__global__ void __launch_bounds__(256) k_tb_finalize(const tbfin_params_t p) {
+    const uint32_t pkt = blockIdx.x, tid = threadIdx.x;
+    const uint32_t slot = p.slot ? p.slot[pkt] : pkt;
+    uint8_t* cb_crc = p.cb_crc + (size_t)slot * p.C;
+    __shared__ uint32_t s_all, s_crc;
+    if (tid == 0) { s_all = 1; s_crc = 0; }
+    __syncthreads();
+    for (uint32_t c = tid; c < p.C; c += blockDim.x)
+        if (!cb_crc[c]) s_all = 0;
+    __syncthreads();
+    bool ok = s_all != 0;
+    if (ok && p.C > 1) {
+        // CRC24A over tbs + 24 bits, chunked: chunk i covers bytes [i*CH, (i+1)*CH)
+        const uint8_t* tb = p.tb_out + (size_t)pkt * p.tb_stride;
+        const uint32_t nbytes = p.tbs_bits / 8 + 3;
+        const uint32_t nchunk = (nbytes + p.chunk_bytes - 1) / p.chunk_bytes;
+        uint32_t r = 0;
+        for (uint32_t i = tid; i < nchunk; i += blockDim.x) {
+            uint32_t c = 0;
+            const uint32_t b0 = i * p.chunk_bytes, b1 = min(nbytes, b0 + p.chunk_bytes);
+            for (uint32_t b = b0; b < b1; ++b) {
+                const uint32_t v = tb[b];
+#pragma unroll
+                for (int q = 7; q >= 0; --q) {
+                    c = (c << 1) | ((v >> q) & 1);
+                    if (c & 0x1000000u) c ^= 0x1864CFBu;
+                }
+            }
+            // multiply by x^(8 * bytes after this chunk)
+            r ^= gf2_mulmod(c, p.xp_tb[i], 0x1864CFBu, 24);
+        }
+        for (int o = 16; o > 0; o >>= 1) r ^= __shfl_xor_sync(0xffffffffu, r, o);
+        if ((tid & 31) == 0) atomicXor(&s_crc, r);
+        __syncthreads();
+        ok = s_crc == 0;
+        if (!ok)
+            for (uint32_t c = tid; c < p.C; c += blockDim.x) cb_crc[c] = 0;
+    }
+    if (tid == 0) p.tb_ok[pkt] = ok ? 1 : 0;
+}
+
+size_t tdec_smem_bytes(uint32_t K, uint32_t L) {
+    const uint32_t T = K / L / 2, nck = (L + tdec::S_CK - 1) / tdec::S_CK;
+    return (size_t)4 * (4 * (K / 2) + nck * 7 * T + 4 * 7 * T) + K / 2 + 16;
+}
+
+cudaError_t launch_turbo_decode(const tdec_params_t& p, uint32_t n_packets, uint32_t threads, size_t smem,
+                                cudaStream_t st) {
+    static size_t configured = 0;
+    if (smem > configured) {
+        cudaError_t e = cudaFuncSetAttribute(k_turbo_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured = smem;
+    }
+    k_turbo_decode<<<dim3(p.C, n_packets), threads, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_tb_finalize(const tbfin_params_t& p, uint32_t n_packets, cudaStream_t st) {
+    k_tb_finalize<<<n_packets, 256, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace dnrp

@@ -1,0 +1,100 @@
+/* dnrp_c_api.h -- C ABI of libdnrp_cuda.so, the B200 (sm_100a) implementation of the DECT NR+ PCC/PDC
+ * physical-layer hot path.  Plain pointers and sizes only; every function returns 0 on success or a
+ * negative dnrp_status_t; no exceptions cross this boundary; there is NO CPU fallback behind it (a
+ * missing GPU or kernel image is an error).
+ *
+ * The reference (maxpenner/DECT-NR-Plus-SDR) has no FFI layer: firmware is compiled in (reference
+ * README.md:217).  Each entry point below therefore names the reference C++ interface it replaces
+ * (file:line relative to /root/reference); INTEGRATION.md shows the binding a maintainer would add.
+ *
+ * Batching model: one context = one device + one packet geometry ("plan": psdef, antennas, resampling)
+ * + a maximum batch size.  A call processes n <= max_batch packets of that geometry.  Buffers passed in
+ * are HOST pointers unless the name ends in _dev.
+ */
+#ifndef DNRP_C_API_H
+#define DNRP_C_API_H
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef enum {
+    DNRP_OK = 0,
+    DNRP_ERR_INVALID = -1,   /* invalid argument / impossible packet configuration */
+    DNRP_ERR_CUDA = -2,      /* CUDA runtime error, see dnrp_last_error_string() */
+    DNRP_ERR_NO_DEVICE = -3, /* no usable sm_100 device */
+    DNRP_ERR_STATE = -4      /* call order violated (e.g. PDC before PCC) */
+} dnrp_status_t;
+
+typedef struct dnrp_ctx dnrp_ctx_t;
+typedef struct { float re, im; } dnrp_cf32_t;
+
+/* sp3::packet_sizes_def_t, lib/include/dectnrp/sections_part3/derivative/packet_sizes_def.hpp */
+typedef struct {
+    uint32_t u, b, PacketLengthType, PacketLength, tm_mode_index, mcs_index, Z;
+} dnrp_psdef_t;
+
+/* subset of sp3::packet_sizes_t, lib/include/dectnrp/sections_part3/derivative/packet_sizes.hpp */
+typedef struct {
+    dnrp_psdef_t psdef;
+    uint32_t N_eff_TX, N_SS, N_TS, N_TX, closed_loop, N_bps;
+    uint32_t N_b_DFT, N_b_CP, N_b_OCC;
+    uint32_t N_PACKET_symb, N_DF_symb, N_PDC_subc, N_DRS_subc;
+    uint32_t G, N_PDC_bits, N_TB_bits, N_TB_byte, C, K_plus, K_minus, C_plus, C_minus;
+    uint32_t N_samples_STF, N_samples_STF_CP_only, N_samples_DF, N_samples_GI;
+    uint32_t N_samples_packet_no_GI, N_samples_packet;
+} dnrp_packet_sizes_t;
+
+/* replaces worker_pool_config_t (lib/include/dectnrp/phy/pool/worker_pool_config.hpp:35-143) for the
+ * parts the hot path needs */
+typedef struct {
+    dnrp_psdef_t psdef;
+    uint32_t N_RX;             /* receive antennas */
+    uint32_t oversampling;     /* os_min: 1, 2, 4 ... (N_b_DFT_os = oversampling * N_b_DFT) */
+    uint32_t resample_L, resample_M; /* TX: DECT rate * L / M = hardware rate (1/1 = no resampling) */
+    uint32_t max_batch;
+    uint32_t network_id;       /* worker_pool_t::add_network_id, worker_pool.cpp:109-114 */
+    uint32_t plcf_type;        /* 1 or 2: PLCF type transmitted / PDC scrambling variant */
+    uint32_t chestim_mode_lr;  /* phy.json chestim_mode_lr_default */
+    uint32_t chestim_mode_lr_t_stride; /* phy.json chestim_mode_lr_t_stride_default */
+    uint32_t tdec_min_iter, tdec_max_iter; /* 0 = reference defaults 2 / 10 (pdc_enc.cpp:35-36) */
+} dnrp_config_t;
+
+/* sp3::get_packet_sizes, lib/src/sections_part3/derivative/packet_sizes.cpp:97-227.
+ * DNRP_ERR_INVALID where the reference returns std::nullopt. Host only. */
+int dnrp_get_packet_sizes(const dnrp_psdef_t* psdef, dnrp_packet_sizes_t* out);
+
+/* tx_rx_t / worker_tx_rx_t construction (lib/src/phy/tx_rx.cpp:38-129, pool/worker_tx_rx.cpp:43-67):
+ * builds all LUTs and device workspaces for one geometry */
+int dnrp_ctx_create(const dnrp_config_t* cfg, int device, dnrp_ctx_t** out);
+void dnrp_ctx_destroy(dnrp_ctx_t* ctx);
+const char* dnrp_last_error_string(void);
+int dnrp_ctx_get_packet_sizes(const dnrp_ctx_t* ctx, dnrp_packet_sizes_t* out);
+int dnrp_ctx_synchronize(dnrp_ctx_t* ctx);
+
+/* ---- FEC only (fec_t, lib/include/dectnrp/phy/fec/fec.hpp:84-166) --------------------------------
+ * encode_plcf + encode_tb for n packets: plcf [n][10] bytes (type 1 uses the first 5), cl_bf_mask [n]
+ * CRC masks (0, 0x5555, 0xAAAA, 0xFFFF; NULL = 0), tb [n][N_TB_byte], rv [n] (NULL = 0).
+ * Outputs: pcc_bits [n][28] (196 bits used), pdc_bits [n][ceil(G/8) rounded up to 4]. */
+int dnrp_fec_encode(dnrp_ctx_t* ctx, uint32_t n, const uint8_t* plcf, const uint32_t* cl_bf_mask,
+                    const uint8_t* tb, const uint8_t* rv, uint8_t* pcc_bits, uint8_t* pdc_bits);
+
+/* decode_tb for n packets from int16 LLRs [n][G] (LLR > 0 <=> bit 1, reference tb2pdc.cpp:173-176).
+ * harq_slot [n] (NULL: slot = packet index), rv [n] (NULL = 0), harq_reset [n] (NULL = 1: first
+ * transmission).  Outputs: tb_out [n][N_TB_byte], crc_ok [n], n_iter [n][C] (may be NULL). */
+int dnrp_fec_decode_tb(dnrp_ctx_t* ctx, uint32_t n, const int16_t* llr, const uint32_t* harq_slot,
+                       const uint8_t* rv, const uint8_t* harq_reset, uint8_t* tb_out, uint8_t* crc_ok,
+                       uint8_t* n_iter);
+
+/* decode_plcf_test for both PLCF types from 196 LLRs per packet (pcc_enc.cpp:215-364).
+ * Outputs per packet and type t = 0 (type 1), 1 (type 2): ok [n][2], plcf [n][2][10],
+ * mask [n][2] (matched CRC mask), n_iter [n][2] (may be NULL). */
+int dnrp_fec_decode_plcf(dnrp_ctx_t* ctx, uint32_t n, const int16_t* llr196, uint8_t* ok, uint8_t* plcf,
+                         uint32_t* mask, uint8_t* n_iter);
+
+#ifdef __cplusplus
+}
+#endif
+#endif
