@@ -49,6 +49,12 @@ class Config(C.Structure):
         "chestim_mode_lr", "chestim_mode_lr_t_stride", "tdec_min_iter", "tdec_max_iter")]
 
 
+class TxDesc(C.Structure):
+    _fields_ = [("codebook_index", C.c_uint32), ("optimal_scaling_DAC", C.c_uint32), ("DAC_scale", C.c_float),
+                ("iq_phase_rad", C.c_float), ("iq_phase_increment_s2s_post_resampling_rad", C.c_float),
+                ("GI_percentage", C.c_uint32), ("rv", C.c_uint32)]
+
+
 def build(verbose=False):
     """compile libdnrp_cuda.so in-tree for sm_100a (nvcc cross-compiles without a GPU)"""
     subprocess.check_call(["make", "-C", _HERE, "-j8", "libdnrp_cuda.so"],
@@ -153,3 +159,35 @@ class Phy:
         _check(lib().dnrp_fec_decode_plcf(self._ctx, n, _ptr(llr196, np.int16), _ptr(ok, np.uint8),
                                           _ptr(plcf, np.uint8), _ptr(mask, np.uint32), _ptr(nit, np.uint8)))
         return ok.astype(bool), plcf, mask, nit
+
+    # ---- tx_t::generate_tx_packet (reference lib/src/phy/tx/tx.cpp:165-314)
+    def tx(self, plcf, tb, codebook_index=0, DAC_scale=1.0, iq_phase_rad=0.0, iq_phase_increment=0.0,
+           GI_percentage=5, rv=0, optimal_scaling_DAC=False, fetch=True):
+        n = tb.shape[0]
+        plcf = np.ascontiguousarray(plcf, dtype=np.uint8).reshape(n, 10)
+        tb = np.ascontiguousarray(tb, dtype=np.uint8).reshape(n, self.ps["N_TB_byte"])
+
+        def per(v):
+            return np.broadcast_to(np.asarray(v), (n,))
+
+        descs = (TxDesc * n)()
+        cb, ds, ph, inc, gi, rvv = per(codebook_index), per(DAC_scale), per(iq_phase_rad), per(iq_phase_increment), \
+            per(GI_percentage), per(rv)
+        for i in range(n):
+            descs[i] = TxDesc(int(cb[i]), int(optimal_scaling_DAC), float(ds[i]), float(ph[i]), float(inc[i]),
+                              int(gi[i]), int(rvv[i]))
+        lib().dnrp_tx_stride.restype = C.c_uint32
+        stride = lib().dnrp_tx_stride(self._ctx)
+        iq = np.zeros((n, self.ps["N_TX"], stride), dtype=np.complex64) if fetch else None
+        ns = np.zeros(n, dtype=np.uint32)
+        _check(lib().dnrp_tx_batch(self._ctx, n, descs, _ptr(plcf, np.uint8), _ptr(tb, np.uint8),
+                                   _ptr(iq, np.complex64), _ptr(ns, np.uint32)))
+        return iq, ns
+
+    def time_stage(self, stage, n, reps=10):
+        ms = C.c_float()
+        _check(lib().dnrp_time_stage(self._ctx, stage, n, reps, C.byref(ms)))
+        return ms.value
+
+
+STAGE_FEC_DECODE_TB, STAGE_FEC_ENCODE, STAGE_FEC_DECODE_PLCF = 1, 2, 3

@@ -120,6 +120,7 @@ int dnrp_ctx_create(const dnrp_config_t* cfg, int device, dnrp_ctx_t** out) {
     UP(c->d_pcc_mask.alloc(B * 2));
 #undef UP
     if (!ok) return fail(DNRP_ERR_CUDA, "device allocation failed");
+    if ((rc = build_phy_plan(c)) != DNRP_OK) return fail(rc, nullptr);
     *out = c;
     return DNRP_OK;
 }
@@ -278,6 +279,97 @@ int dnrp_fec_decode_plcf(dnrp_ctx_t* c, uint32_t n, const int16_t* llr196, uint8
     DNRP_CUDA(cudaMemcpy2DAsync(plcf, 10, c->d_plcf_out.p, 16, 10, (size_t)n * 2, cudaMemcpyDeviceToHost, c->stream));
     DNRP_CUDA(cudaMemcpyAsync(mask, c->d_pcc_mask.p, (size_t)n * 8, cudaMemcpyDeviceToHost, c->stream));
     if (n_iter) DNRP_CUDA(cudaMemcpyAsync(n_iter, c->d_pcc_n_iter.p, (size_t)n * 2, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    return DNRP_OK;
+}
+
+}  // extern "C"
+
+extern "C" int dnrp_time_stage(dnrp_ctx_t* c, int stage, uint32_t n, uint32_t reps, float* ms_per_rep) {
+    DNRP_REQUIRE(c && ms_per_rep && reps > 0, "invalid argument");
+    DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    cudaEvent_t e0, e1;
+    DNRP_CUDA(cudaEventCreate(&e0));
+    DNRP_CUDA(cudaEventCreate(&e1));
+    int rc = DNRP_OK;
+    DNRP_CUDA(cudaEventRecord(e0, c->stream));
+    for (uint32_t r = 0; r < reps && rc == DNRP_OK; ++r) {
+        switch (stage) {
+            case DNRP_STAGE_FEC_DECODE_TB: rc = run_fec_decode_tb(c, n, false, false, false); break;
+            case DNRP_STAGE_FEC_ENCODE: rc = run_fec_encode(c, n, false, false); break;
+            case DNRP_STAGE_FEC_DECODE_PLCF: rc = run_fec_decode_plcf(c, n); break;
+            default: set_last_error("unknown stage"); rc = DNRP_ERR_INVALID;
+        }
+    }
+    if (rc != DNRP_OK) return rc;
+    DNRP_CUDA(cudaEventRecord(e1, c->stream));
+    DNRP_CUDA(cudaEventSynchronize(e1));
+    float ms = 0;
+    DNRP_CUDA(cudaEventElapsedTime(&ms, e0, e1));
+    cudaEventDestroy(e0);
+    cudaEventDestroy(e1);
+    *ms_per_rep = ms / reps;
+    return DNRP_OK;
+}
+
+// ---- transmitter ---------------------------------------------------------------------------------
+namespace dnrp {
+int run_tx_ofdm(dnrp_ctx* c, uint32_t n) {
+    const phy_dims_t& d = c->dims;
+    DNRP_CUDA(cudaMemsetAsync(c->d_iq_tx.p, 0, (size_t)n * d.N_TX * c->tx_stride * sizeof(float2), c->stream));
+    txofdm_params_t p{};
+    p.d = d;
+    p.pcc_bits = c->d_pcc_bits.p; p.pcc_stride = 28;
+    p.pdc_bits = c->d_pdc_bits.p; p.pdc_stride = c->fec.dbits_stride;
+    p.meta = c->d_tx_meta.p;
+    p.iq = c->d_iq_tx.p; p.iq_stride = c->tx_stride;
+    DNRP_CUDA(launch_tx_ofdm(p, n, c->stream));
+    return DNRP_OK;
+}
+}  // namespace dnrp
+
+extern "C" {
+
+uint32_t dnrp_tx_stride(const dnrp_ctx_t* c) { return c ? c->tx_stride : 0; }
+
+int dnrp_tx_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_tx_desc_t* descs, const uint8_t* plcf, const uint8_t* tb,
+                  dnrp_cf32_t* iq_out, uint32_t* n_samples_out) {
+    DNRP_REQUIRE(c && descs && plcf && tb, "null argument");
+    DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
+    DNRP_REQUIRE(c->cfg.resample_L == c->cfg.resample_M, "resampling TX path not built into this context");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    const fec_plan_t& f = c->fec;
+    const phy_dims_t& d = c->dims;
+    std::vector<tx_meta_dev_t> meta(n);
+    std::vector<uint32_t> mask(n);
+    std::vector<uint8_t> rv(n);
+    for (uint32_t i = 0; i < n; ++i) {
+        // the reference asserts these (tx.cpp:560-579); here they are argument errors
+        DNRP_REQUIRE(descs[i].codebook_index < d.n_cb_idx, "codebook index out of bound");
+        DNRP_REQUIRE(descs[i].GI_percentage <= 100, "GI percentage too large");
+        DNRP_REQUIRE(descs[i].rv < 4, "rv out of range");
+        meta[i] = {descs[i].codebook_index, descs[i].optimal_scaling_DAC, descs[i].DAC_scale, descs[i].iq_phase_rad,
+                   descs[i].iq_phase_increment_s2s_post_resampling_rad, descs[i].GI_percentage};
+        const bool cl = c->ps.tm.cl != 0, bf = descs[i].codebook_index > 0;  // tx.cpp:179-181, pcc_enc.cpp:168-178
+        mask[i] = (!cl && !bf) ? 0x0000u : (cl && !bf) ? 0x5555u : (!cl && bf) ? 0xAAAAu : 0xFFFFu;
+        rv[i] = (uint8_t)descs[i].rv;
+        if (n_samples_out)
+            n_samples_out[i] = d.n_no_gi_os + (d.n_packet_os - d.n_no_gi_os) * descs[i].GI_percentage / 100;
+    }
+    DNRP_CUDA(cudaMemcpy2DAsync(c->d_tb_in.p, f.tb_stride, tb, c->ps.N_TB_byte, c->ps.N_TB_byte, n,
+                                cudaMemcpyHostToDevice, c->stream));
+    DNRP_CUDA(cudaMemcpy2DAsync(c->d_plcf_in.p, 16, plcf, 10, 10, n, cudaMemcpyHostToDevice, c->stream));
+    DNRP_CUDA(cudaMemcpyAsync(c->d_plcf_mask.p, mask.data(), 4 * n, cudaMemcpyHostToDevice, c->stream));
+    DNRP_CUDA(cudaMemcpyAsync(c->d_rv.p, rv.data(), n, cudaMemcpyHostToDevice, c->stream));
+    DNRP_CUDA(cudaMemcpyAsync(c->d_tx_meta.p, meta.data(), n * sizeof(tx_meta_dev_t), cudaMemcpyHostToDevice, c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));  // the staging vectors above are pageable and local
+    int rc = run_fec_encode(c, n, true, true);
+    if (rc) return rc;
+    if ((rc = run_tx_ofdm(c, n)) != DNRP_OK) return rc;
+    if (iq_out)
+        DNRP_CUDA(cudaMemcpyAsync(iq_out, c->d_iq_tx.p, (size_t)n * d.N_TX * c->tx_stride * sizeof(float2),
+                                  cudaMemcpyDeviceToHost, c->stream));
     DNRP_CUDA(cudaStreamSynchronize(c->stream));
     return DNRP_OK;
 }

@@ -9,6 +9,7 @@
 #include "../../include/dnrp_c_api.h"
 #include "fec_rx.cuh"
 #include "fec_tx.cuh"
+#include "phy.cuh"
 #include "spec.hpp"
 #include "spec_fec.hpp"
 #include "spec_re.hpp"
@@ -94,4 +95,23 @@ struct dnrp_ctx {
     dnrp::dbuf<uint8_t> d_cb_crc, d_saved, d_tb_out, d_n_iter, d_tb_ok;
     dnrp::dbuf<uint8_t> d_pcc_crc, d_plcf_out, d_pcc_n_iter;
     dnrp::dbuf<uint32_t> d_pcc_mask;
+
+    // OFDM / receiver plan
+    dnrp::phy_dims_t dims;
+    dnrp::spec::re_map_t re_map;
+    dnrp::dbuf<uint32_t> d_cell, d_pcc_lk, d_pdc_lk;
+    dnrp::dbuf<int8_t> d_stf_sign, d_W;
+    dnrp::dbuf<float> d_W_scale, d_W_scale_opt;
+    dnrp::dbuf<float2> d_twiddle;
+    uint32_t tx_stride = 0;  // samples per antenna in d_iq_tx
+    dnrp::dbuf<float2> d_iq_tx;
+    dnrp::dbuf<dnrp::tx_meta_dev_t> d_tx_meta;
 };
+
+namespace dnrp {
+int build_phy_plan(dnrp_ctx* c);
+int run_fec_encode(dnrp_ctx* c, uint32_t n, bool have_mask, bool have_rv);
+int run_fec_decode_tb(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, bool have_reset);
+int run_fec_decode_plcf(dnrp_ctx* c, uint32_t n);
+int run_tx_ofdm(dnrp_ctx* c, uint32_t n);
+}  // namespace dnrp

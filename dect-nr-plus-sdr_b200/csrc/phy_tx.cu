@@ -1,0 +1,163 @@
+// phy_tx.cu -- transmitter OFDM stage, one thread block per (OFDM symbol, TX antenna, packet):
+// bits -> QAM symbols -> transmit-diversity precoding -> resource mapping (STF / PCC / DRS / PDC) ->
+// codebook beamforming -> scaling -> IFFT -> cyclic prefix (+ STF cover sequence, + mixer), all in one
+// pass through shared memory.  Replaces the per-symbol loop of reference
+// lib/src/phy/tx/tx.cpp:216-279 (run_stf, run_pcc, run_drs, run_pdc, run_beamforming,
+// run_ifft_cp_scale, stf_t::apply_cover_sequence, mixer) for L = M = 1.
+#include "fft.cuh"
+#include "phy.cuh"
+
+namespace dnrp {
+
+// LTE Gray mapping, TS 36.211 7.1 (srsRAN lte_tables.c; reference fix/mod.cpp:137-174), bits MSB first
+__device__ __forceinline__ float2 qam_symbol(const uint8_t* __restrict__ bits, uint32_t off, uint32_t N_bps) {
+    uint32_t v = 0;
+    for (uint32_t i = 0; i < N_bps; ++i) {
+        const uint32_t g = off + i;
+        v = (v << 1) | ((bits[g >> 3] >> (7 - (g & 7))) & 1u);
+    }
+    if (N_bps == 1) {
+        const float a = v ? -0.70710678118654752f : 0.70710678118654752f;
+        return make_float2(a, a);
+    }
+    const uint32_t half = N_bps >> 1;
+    float re = 0.f, im = 0.f;
+    // axis amplitude (1-2b0)(2^(h-1) - (1-2b2)(2^(h-2) - ...)), I from even bit positions, Q from odd
+    for (int i = (int)half - 1; i >= 1; --i) {
+        const float bi = ((v >> (N_bps - 1 - 2 * i)) & 1u) ? -1.f : 1.f;
+        const float bq = ((v >> (N_bps - 2 - 2 * i)) & 1u) ? -1.f : 1.f;
+        const float c = (float)(1u << (half - 1 - i));
+        re = bi * (c - re);
+        im = bq * (c - im);
+    }
+    const float c0 = (float)(1u << (half - 1));
+    re = (((v >> (N_bps - 1)) & 1u) ? -1.f : 1.f) * (c0 - re);
+    im = (((v >> (N_bps - 2)) & 1u) ? -1.f : 1.f) * (c0 - im);
+    const float norm = half == 1 ? 0.70710678118654752f
+                                 : (half == 2 ? 0.31622776601683794f : (half == 3 ? 0.15430334996209191f : 0.07669649888473704f));
+    return make_float2(re * norm, im * norm);
+}
+
+__device__ __forceinline__ void txdiv_pair_dev(uint32_t N_TS, uint32_t i_mod, uint32_t& A, uint32_t& B) {
+    // Y_i index table, reference transmit_diversity_precoding.cpp:45-72
+    if (N_TS == 2) { A = 0; B = 1; return; }
+    if (N_TS == 4) {
+        const uint8_t a4[6] = {0, 2, 0, 1, 0, 1}, b4[6] = {1, 3, 2, 3, 3, 2};
+        A = a4[i_mod]; B = b4[i_mod];
+        return;
+    }
+    const uint8_t a8[12] = {0, 2, 4, 6, 0, 1, 2, 3, 0, 1, 4, 5}, b8[12] = {1, 3, 5, 7, 4, 5, 6, 7, 2, 3, 6, 7};
+    A = a8[i_mod]; B = b8[i_mod];
+}
+
+__device__ __forceinline__ float2 apply_w(int8_t w, float2 v) {
+    switch (w) {
+        case 1: return v;
+        case -1: return make_float2(-v.x, -v.y);
+        case 2: return make_float2(-v.y, v.x);    // * j
+        case -2: return make_float2(v.y, -v.x);   // * -j
+        default: return make_float2(0.f, 0.f);
+    }
+}
+
+__global__ void __launch_bounds__(256) k_tx_ofdm(const txofdm_params_t p) {
+    extern __shared__ float2 sm[];
+    const phy_dims_t& d = p.d;
+    const uint32_t l = blockIdx.x, ant = blockIdx.y, pkt = blockIdx.z;
+    const uint32_t tid = threadIdx.x, nthr = blockDim.x;
+    float2* X = sm;
+    float2* Y = sm + d.N_os;
+    const tx_meta_dev_t meta = p.meta[pkt];
+    const uint8_t* pcc_bits = p.pcc_bits + (size_t)pkt * p.pcc_stride;
+    const uint8_t* pdc_bits = p.pdc_bits + (size_t)pkt * p.pdc_stride;
+    const int8_t* W = d.W + (size_t)meta.codebook_index * d.N_TX * d.N_TS + ant * d.N_TS;
+    const float wscale = meta.DAC_scale * (meta.optimal_scaling_DAC ? d.W_scale_opt[meta.codebook_index]
+                                                                    : d.W_scale[meta.codebook_index]);
+    const float scale = (l == 0 ? rsqrtf((float)(d.N_OCC / 4)) : rsqrtf((float)d.N_OCC)) * wscale;
+
+    for (uint32_t i = tid; i < d.N_os; i += nthr) X[i] = make_float2(0.f, 0.f);
+    __syncthreads();
+
+    // ---- frequency domain of this antenna
+    for (uint32_t k = tid; k < d.Nk; k += nthr) {
+        float2 acc = make_float2(0.f, 0.f);
+        if (l == 0) {
+            const int s = d.stf_sign[k];
+            if (s != 0) {  // only transmit stream 0 carries the STF (run_beamforming(1))
+                const float a = 0.70710678118654752f * (float)s;
+                acc = apply_w(W[0], make_float2(a, a));
+            }
+        } else {
+            const uint32_t cw = d.cell[l * d.Nk + k];
+            const uint32_t type = cw >> 30, idx = cw & 0x03ffffffu;
+            if (type == 1) {  // DRS of transmit stream ts
+                const uint32_t ts = (cw >> 27) & 7u;
+                acc = apply_w(W[ts], make_float2((cw >> 26) & 1u ? -1.f : 1.f, 0.f));
+            } else if (type == 2 || type == 3) {
+                const uint8_t* bits = type == 2 ? pcc_bits : pdc_bits;
+                const uint32_t nbps = type == 2 ? 2u : d.N_bps;
+                if (d.N_TS == 1) {
+                    acc = apply_w(W[0], qam_symbol(bits, idx * nbps, nbps));
+                } else if (type == 2 || d.txdiv) {
+                    // Alamouti pair (q even, q odd): stream A carries s[q], stream B the flipped partner
+                    uint32_t A, B;
+                    txdiv_pair_dev(d.N_TS, (idx >> 1) % d.txdiv_modulo, A, B);
+                    if (W[A] != 0) acc = apply_w(W[A], qam_symbol(bits, idx * nbps, nbps));
+                    if (W[B] != 0) {
+                        const float2 o = qam_symbol(bits, (idx ^ 1u) * nbps, nbps);
+                        const float2 f = (idx & 1u) ? make_float2(o.x, -o.y) : make_float2(-o.x, o.y);
+                        acc = cadd(acc, apply_w(W[B], f));
+                    }
+                } else {
+                    // spatial multiplexing: symbol idx*N_SS + s on stream s (tx.cpp:1054-1060)
+                    for (uint32_t s = 0; s < d.N_SS; ++s)
+                        if (W[s] != 0) acc = cadd(acc, apply_w(W[s], qam_symbol(bits, (idx * d.N_SS + s) * nbps, nbps)));
+                }
+            }
+        }
+        // FFT bin: DC and the upper half from bin 0, the lower half at the top (tx_rx.cpp:197-240)
+        const uint32_t bin = k >= d.N_OCC / 2 ? k - d.N_OCC / 2 : d.N_os - d.N_OCC / 2 + k;
+        X[bin] = make_float2(acc.x * scale, acc.y * scale);
+    }
+
+    const float2* x = block_fft<true>(X, Y, d.N_os, d.twiddle);
+
+    // ---- cyclic prefix, STF cover sequence, mixer
+    const uint32_t cp = l == 0 ? d.stf_cp_os : d.cp_os;
+    const uint32_t len = cp + d.N_os;
+    const uint32_t start = l == 0 ? 0 : d.stf_len_os + (l - 1) * d.sym_len_os;
+    float2* out = p.iq + ((size_t)pkt * d.N_TX + ant) * p.iq_stride + start;
+    const bool mix = meta.iq_phase_rad != 0.f || meta.iq_phase_increment != 0.f;
+    for (uint32_t n = tid; n < len; n += nthr) {
+        uint32_t src = (n + d.N_os - (cp % d.N_os)) % d.N_os;
+        float2 v = x[src];
+        if (l == 0) {
+            const float c[9] = {1.f, -1.f, 1.f, 1.f, -1.f, -1.f, -1.f, -1.f, -1.f};  // stf.hpp:146-151
+            const float cs = c[n / d.pat_len_os];
+            v.x *= cs; v.y *= cs;
+        }
+        if (mix) {
+            // closed-form phase (the reference's VOLK rotator is recursive; tolerance item in DESIGN.md)
+            double ph = (double)meta.iq_phase_rad + (double)meta.iq_phase_increment * (double)(start + n);
+            ph -= 6.283185307179586476925 * rint(ph * 0.15915494309189533577);
+            float s, c;
+            sincosf((float)ph, &s, &c);
+            v = cmul(v, make_float2(c, s));
+        }
+        out[n] = v;
+    }
+}
+
+cudaError_t launch_tx_ofdm(const txofdm_params_t& p, uint32_t n_packets, cudaStream_t st) {
+    const size_t smem = 2 * sizeof(float2) * p.d.N_os;
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+        cudaError_t e = cudaFuncSetAttribute(k_tx_ofdm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured = smem;
+    }
+    k_tx_ofdm<<<dim3(p.d.N_DF + 1, p.d.N_TX, n_packets), 256, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace dnrp

@@ -154,5 +154,14 @@ inline float codebook_scale(const int8_t* W, uint32_t n) {
     return 1.0f / std::sqrt((float)nz);
 }
 
+// "optimal DAC" scaling (reference beamforming_and_antenna_port_mapping.cpp:155-190)
+inline float codebook_scale_optimal_dac(uint32_t N_TS, uint32_t N_TX, uint32_t idx) {
+    const float r2 = 1.0f / std::sqrt(2.0f);
+    if (N_TS == 2 && N_TX == 2) return idx == 0 ? 1.0f : r2;
+    if (N_TS == 2 && N_TX == 4) return idx < 14 ? 1.0f : r2;
+    if (N_TS == 4 && N_TX == 4) return idx == 0 ? 1.0f : (idx <= 2 ? r2 : 0.5f);
+    return 1.0f;
+}
+
 }  // namespace spec
 }  // namespace dnrp

@@ -94,6 +94,39 @@ int dnrp_fec_decode_tb(dnrp_ctx_t* ctx, uint32_t n, const int16_t* llr, const ui
 int dnrp_fec_decode_plcf(dnrp_ctx_t* ctx, uint32_t n, const int16_t* llr196, uint8_t* ok, uint8_t* plcf,
                          uint32_t* mask, uint8_t* n_iter);
 
+/* ---- transmitter ------------------------------------------------------------------------------
+ * dnrp_tx_desc_t = tx_descriptor_t{codebook_index, tx_meta_t} + the HARQ redundancy version
+ * (lib/include/dectnrp/phy/tx/tx_descriptor.hpp:43-78, tx_meta.hpp:32-58, harq/process_tx.hpp). */
+typedef struct {
+    uint32_t codebook_index;
+    uint32_t optimal_scaling_DAC;
+    float DAC_scale;
+    float iq_phase_rad;
+    float iq_phase_increment_s2s_post_resampling_rad;
+    uint32_t GI_percentage;
+    uint32_t rv;
+} dnrp_tx_desc_t;
+
+/* samples per antenna reserved for one packet in iq_out (packet incl. full guard interval, padded) */
+uint32_t dnrp_tx_stride(const dnrp_ctx_t* ctx);
+
+/* tx_t::generate_tx_packet (lib/src/phy/tx/tx.cpp:165-314) for n packets.
+ * plcf [n][10], tb [n][N_TB_byte]; iq_out [n][N_TX][dnrp_tx_stride()] (zero padded; may be NULL to keep
+ * the IQ on the device for dnrp_channel_batch); n_samples_out [n] = N_samples_transmit (may be NULL). */
+int dnrp_tx_batch(dnrp_ctx_t* ctx, uint32_t n, const dnrp_tx_desc_t* descs, const uint8_t* plcf,
+                  const uint8_t* tb, dnrp_cf32_t* iq_out, uint32_t* n_samples_out);
+
+/* ---- measurement hook ------------------------------------------------------------------------
+ * Re-runs one device stage `reps` times on the data already resident in the context (left there by
+ * the previous host-facing call) and returns the average CUDA-event time per repetition in ms,
+ * measured on the context's stream.  stage: see dnrp_stage_t. */
+typedef enum {
+    DNRP_STAGE_FEC_DECODE_TB = 1,
+    DNRP_STAGE_FEC_ENCODE = 2,
+    DNRP_STAGE_FEC_DECODE_PLCF = 3
+} dnrp_stage_t;
+int dnrp_time_stage(dnrp_ctx_t* ctx, int stage, uint32_t n, uint32_t reps, float* ms_per_rep);
+
 #ifdef __cplusplus
 }
 #endif
