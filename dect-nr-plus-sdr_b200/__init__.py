@@ -55,6 +55,24 @@ class TxDesc(C.Structure):
                 ("GI_percentage", C.c_uint32), ("rv", C.c_uint32)]
 
 
+class SyncReport(C.Structure):
+    _fields_ = [("fine_peak_time_local", C.c_uint32), ("cfo_fractional_rad", C.c_float),
+                ("cfo_integer_rad", C.c_float), ("rms", C.c_float * 8)]
+
+
+class PccReport(C.Structure):
+    _fields_ = [("plcf_ok", C.c_uint8 * 2), ("plcf", (C.c_uint8 * 10) * 2), ("crc_mask", C.c_uint32 * 2),
+                ("snr_dB", C.c_float), ("cfo_residual_rad", C.c_float), ("sto_fractional", C.c_float),
+                ("rms", C.c_float * 8)]
+
+
+class PdcReport(C.Structure):
+    _fields_ = [("crc_ok", C.c_uint32), ("snr_dB", C.c_float)]
+
+
+TAP_Y, TAP_DRS_ZF, TAP_STF_ZF, TAP_LLR_PCC, TAP_LLR_PDC, TAP_WIENER_CLASS = 1, 2, 3, 4, 5, 6
+
+
 def build(verbose=False):
     """compile libdnrp_cuda.so in-tree for sm_100a (nvcc cross-compiles without a GPU)"""
     subprocess.check_call(["make", "-C", _HERE, "-j8", "libdnrp_cuda.so"],
@@ -183,6 +201,58 @@ class Phy:
         _check(lib().dnrp_tx_batch(self._ctx, n, descs, _ptr(plcf, np.uint8), _ptr(tb, np.uint8),
                                    _ptr(iq, np.complex64), _ptr(ns, np.uint32)))
         return iq, ns
+
+    # ---- rx_synced_t::demoddecod_rx_pcc / demoddecod_rx_pdc (reference rx_synced.cpp:186-436)
+    def rx_stride(self):
+        lib().dnrp_rx_stride.restype = C.c_uint32
+        return lib().dnrp_rx_stride(self._ctx)
+
+    def rx_pcc(self, iq, t0=0, cfo_fractional_rad=0.0, cfo_integer_rad=0.0, rms=None, n=None):
+        """iq [n][N_RX][rx_stride] complex64 host windows, or None to use the device-resident windows
+        (after loopback_tx_to_rx); returns the list of PccReport"""
+        if iq is not None:
+            n = iq.shape[0]
+            iq = np.ascontiguousarray(iq, dtype=np.complex64)
+            assert iq.shape[-1] == self.rx_stride(), (iq.shape, self.rx_stride())
+        t0v, cf, ci = (np.broadcast_to(np.asarray(v), (n,)) for v in (t0, cfo_fractional_rad, cfo_integer_rad))
+        sync = (SyncReport * n)()
+        for i in range(n):
+            sync[i].fine_peak_time_local = int(t0v[i])
+            sync[i].cfo_fractional_rad = float(cf[i])
+            sync[i].cfo_integer_rad = float(ci[i])
+            if rms is not None:
+                for a, v in enumerate(np.atleast_1d(rms[i])):
+                    sync[i].rms[a] = float(v)
+        out = (PccReport * n)()
+        _check(lib().dnrp_rx_pcc_batch(self._ctx, n, _ptr(iq, np.complex64), sync, out))
+        return out
+
+    def rx_pdc(self, n, harq_slot=None, rv=None, harq_reset=None):
+        tb = np.zeros((n, self.ps["N_TB_byte"]), dtype=np.uint8)
+        nit = np.zeros((n, self.ps["C"]), dtype=np.uint8)
+        slot = None if harq_slot is None else np.ascontiguousarray(harq_slot, dtype=np.uint32)
+        rvv = None if rv is None else np.ascontiguousarray(rv, dtype=np.uint8)
+        rst = None if harq_reset is None else np.ascontiguousarray(harq_reset, dtype=np.uint8)
+        out = (PdcReport * n)()
+        _check(lib().dnrp_rx_pdc_batch(self._ctx, n, _ptr(slot, np.uint32), _ptr(rvv, np.uint8), _ptr(rst, np.uint8),
+                                       _ptr(tb, np.uint8), out, _ptr(nit, np.uint8)))
+        ok = np.array([o.crc_ok for o in out], dtype=bool)
+        snr = np.array([o.snr_dB for o in out], dtype=np.float32)
+        return ok, tb, snr, nit
+
+    def tap(self, which, n):
+        lib().dnrp_tap_bytes.restype = C.c_size_t
+        nbytes = lib().dnrp_tap_bytes(self._ctx, which, n)
+        buf = np.zeros(nbytes, dtype=np.uint8)
+        _check(lib().dnrp_tap_read(self._ctx, which, n, _ptr(buf, np.uint8), C.c_size_t(nbytes)))
+        if which in (TAP_Y, TAP_DRS_ZF, TAP_STF_ZF):
+            return buf.view(np.complex64).reshape(n, -1)
+        if which in (TAP_LLR_PCC, TAP_LLR_PDC):
+            return buf.view(np.int16).reshape(n, -1)
+        return buf.reshape(n, -1)
+
+    def loopback_tx_to_rx(self, n, t0=0):
+        _check(lib().dnrp_loopback_tx_to_rx(self._ctx, n, t0))
 
     def time_stage(self, stage, n, reps=10):
         ms = C.c_float()

@@ -1,0 +1,183 @@
+// api_rx.cu -- receiver side of the C ABI: batched rx_synced_t::demoddecod_rx_pcc / _pdc
+// (reference lib/src/phy/rx/rx_synced/rx_synced.cpp:186-436) on the context's device buffers.
+#include <cstring>
+#include "ctx.hpp"
+
+using namespace dnrp;
+
+#define DNRP_REQUIRE(cond, msg)             \
+    do {                                    \
+        if (!(cond)) {                      \
+            dnrp::set_last_error(msg);      \
+            return DNRP_ERR_INVALID;        \
+        }                                   \
+    } while (0)
+
+namespace dnrp {
+
+rx_params_t make_rx_params(dnrp_ctx* c) {
+    rx_params_t p{};
+    p.d = c->dims;
+    p.iq = c->d_iq_rx.p; p.iq_stride = c->rx_stride;
+    p.state = c->d_rx_state.p;
+    p.Y = c->d_Y.p; p.hzf = c->d_hzf.p; p.hstf = c->d_hstf.p; p.snr_part = c->d_snr_part.p;
+    p.cls = c->d_cls.p; p.cls_stride = c->cls_stride;
+    p.llr_pcc = c->d_llr_pcc.p;
+    p.llr = c->d_llr.p; p.llr_stride = c->ps.G;
+    return p;
+}
+
+// The reference interleaves FFTs, estimation and decoding symbol by symbol for latency; for a batch
+// the whole front end of all packets runs first (every later stage only reads its results).
+int run_rx_front(dnrp_ctx* c, uint32_t n) {
+    const rx_params_t p = make_rx_params(c);
+    DNRP_CUDA(launch_rx_stf(p, n, c->stream));
+    DNRP_CUDA(launch_rx_fft(p, n, c->stream));
+    DNRP_CUDA(launch_rx_snr_class(p, n, c->stream));
+    return DNRP_OK;
+}
+
+int run_rx_pcc(dnrp_ctx* c, uint32_t n) {
+    const rx_params_t p = make_rx_params(c);
+    DNRP_CUDA(launch_rx_demap(p, n, true, c->stream));
+    return run_fec_decode_plcf(c, n);
+}
+
+int run_rx_pdc(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, bool have_reset) {
+    const rx_params_t p = make_rx_params(c);
+    DNRP_CUDA(launch_rx_demap(p, n, false, c->stream));
+    return run_fec_decode_tb(c, n, have_slot, have_rv, have_reset);
+}
+
+}  // namespace dnrp
+
+extern "C" {
+
+uint32_t dnrp_rx_stride(const dnrp_ctx_t* c) { return c ? c->rx_stride : 0; }
+
+int dnrp_rx_pcc_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, const dnrp_sync_report_t* sync,
+                      dnrp_pcc_report_t* out) {
+    DNRP_REQUIRE(c && sync && out, "null argument");
+    DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    const phy_dims_t& d = c->dims;
+    for (uint32_t i = 0; i < n; ++i) {
+        DNRP_REQUIRE(sync[i].fine_peak_time_local + d.n_no_gi_os <= c->rx_stride, "packet exceeds the IQ window");
+        rx_state_t& s = c->h_rx_state[i];
+        std::memset(&s, 0, sizeof(s));
+        s.t0 = (int32_t)sync[i].fine_peak_time_local;
+        s.inc0 = sync[i].cfo_fractional_rad + sync[i].cfo_integer_rad;  // rx_synced.cpp:240
+        for (uint32_t a = 0; a < 8; ++a) s.rms[a] = sync[i].rms[a];
+    }
+    DNRP_CUDA(cudaMemcpyAsync(c->d_rx_state.p, c->h_rx_state.data(), n * sizeof(rx_state_t),
+                              cudaMemcpyHostToDevice, c->stream));
+    if (iq_in)
+        DNRP_CUDA(cudaMemcpyAsync(c->d_iq_rx.p, iq_in, (size_t)n * d.N_RX * c->rx_stride * sizeof(float2),
+                                  cudaMemcpyHostToDevice, c->stream));
+    int rc = run_rx_front(c, n);
+    if (rc) return rc;
+    if ((rc = run_rx_pcc(c, n)) != DNRP_OK) return rc;
+    std::vector<uint8_t> ok(2 * n), plcf(32 * n);
+    std::vector<uint32_t> mask(2 * n);
+    DNRP_CUDA(cudaMemcpyAsync(c->h_rx_state.data(), c->d_rx_state.p, n * sizeof(rx_state_t),
+                              cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaMemcpyAsync(ok.data(), c->d_pcc_crc.p, 2 * n, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaMemcpyAsync(plcf.data(), c->d_plcf_out.p, 32 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaMemcpyAsync(mask.data(), c->d_pcc_mask.p, 8 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    for (uint32_t i = 0; i < n; ++i) {
+        const rx_state_t& s = c->h_rx_state[i];
+        dnrp_pcc_report_t& r = out[i];
+        std::memset(&r, 0, sizeof(r));
+        for (uint32_t t = 0; t < 2; ++t) {
+            r.plcf_ok[t] = ok[2 * i + t];
+            std::memcpy(r.plcf[t], &plcf[32 * i + 16 * t], 10);
+            r.crc_mask[t] = mask[2 * i + t];
+        }
+        r.snr_dB = s.snr_db_pcc;
+        r.cfo_residual_rad = s.cfo_left;
+        r.sto_fractional = s.sto_fractional;
+        for (uint32_t a = 0; a < 8; ++a) r.rms[a] = s.rms[a];
+    }
+    return DNRP_OK;
+}
+
+int dnrp_rx_pdc_batch(dnrp_ctx_t* c, uint32_t n, const uint32_t* harq_slot, const uint8_t* rv,
+                      const uint8_t* harq_reset, uint8_t* tb_out, dnrp_pdc_report_t* out, uint8_t* n_iter) {
+    DNRP_REQUIRE(c && tb_out && out, "null argument");
+    DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    const fec_plan_t& f = c->fec;
+    if (harq_slot)
+        for (uint32_t i = 0; i < n; ++i) DNRP_REQUIRE(harq_slot[i] < c->B, "harq slot out of range");
+    if (harq_slot) DNRP_CUDA(cudaMemcpyAsync(c->d_slot.p, harq_slot, 4 * n, cudaMemcpyHostToDevice, c->stream));
+    if (rv) DNRP_CUDA(cudaMemcpyAsync(c->d_rv.p, rv, n, cudaMemcpyHostToDevice, c->stream));
+    if (harq_reset) DNRP_CUDA(cudaMemcpyAsync(c->d_reset.p, harq_reset, n, cudaMemcpyHostToDevice, c->stream));
+    int rc = run_rx_pdc(c, n, harq_slot != nullptr, rv != nullptr, harq_reset != nullptr);
+    if (rc) return rc;
+    std::vector<uint8_t> ok(n);
+    DNRP_CUDA(cudaMemcpy2DAsync(tb_out, c->ps.N_TB_byte, c->d_tb_out.p, f.tb_stride, c->ps.N_TB_byte, n,
+                                cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaMemcpyAsync(ok.data(), c->d_tb_ok.p, n, cudaMemcpyDeviceToHost, c->stream));
+    if (n_iter) DNRP_CUDA(cudaMemcpyAsync(n_iter, c->d_n_iter.p, (size_t)n * c->ps.C, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    for (uint32_t i = 0; i < n; ++i) {
+        out[i].crc_ok = ok[i];
+        out[i].snr_dB = c->h_rx_state[i].snr_db_pdc;  // read back by the PCC call (whole packet is known)
+    }
+    return DNRP_OK;
+}
+
+static bool tap_desc(const dnrp_ctx_t* c, int tap, uint32_t n, const void*& src, size_t& bytes) {
+    const phy_dims_t& d = c->dims;
+    switch (tap) {
+        case DNRP_TAP_Y: src = c->d_Y.p; bytes = (size_t)n * d.N_RX * d.N_DF * d.Nk * sizeof(float2); return true;
+        case DNRP_TAP_DRS_ZF:
+            src = c->d_hzf.p; bytes = (size_t)n * d.N_RX * d.N_eff_TX * d.n_drs * d.NP * sizeof(float2); return true;
+        case DNRP_TAP_STF_ZF: src = c->d_hstf.p; bytes = (size_t)n * d.N_RX * d.NP * sizeof(float2); return true;
+        case DNRP_TAP_LLR_PCC: src = c->d_llr_pcc.p; bytes = (size_t)n * 196 * 2; return true;
+        case DNRP_TAP_LLR_PDC: src = c->d_llr.p; bytes = (size_t)n * c->ps.G * 2; return true;
+        case DNRP_TAP_WIENER_CLASS: src = c->d_cls.p; bytes = (size_t)n * c->cls_stride; return true;
+        default: return false;
+    }
+}
+
+size_t dnrp_tap_bytes(const dnrp_ctx_t* c, int tap, uint32_t n) {
+    const void* src;
+    size_t bytes = 0;
+    if (!c || !tap_desc(c, tap, n, src, bytes)) return 0;
+    return bytes;
+}
+
+int dnrp_tap_read(dnrp_ctx_t* c, int tap, uint32_t n, void* dst, size_t dst_bytes) {
+    DNRP_REQUIRE(c && dst, "null argument");
+    DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
+    const void* src;
+    size_t bytes = 0;
+    DNRP_REQUIRE(tap_desc(c, tap, n, src, bytes), "unknown tap");
+    DNRP_REQUIRE(dst_bytes >= bytes, "destination too small");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    DNRP_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    return DNRP_OK;
+}
+
+int dnrp_loopback_tx_to_rx(dnrp_ctx_t* c, uint32_t n, uint32_t t0) {
+    DNRP_REQUIRE(c, "null argument");
+    DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
+    const phy_dims_t& d = c->dims;
+    DNRP_REQUIRE(t0 + d.n_packet_os <= c->rx_stride, "offset exceeds the IQ window");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    DNRP_CUDA(cudaMemsetAsync(c->d_iq_rx.p, 0, (size_t)n * d.N_RX * c->rx_stride * sizeof(float2), c->stream));
+    for (uint32_t a = 0; a < d.N_RX; ++a) {
+        // one strided copy per RX antenna: rows = packets
+        const float2* src = c->d_iq_tx.p + (size_t)(a % d.N_TX) * c->tx_stride;
+        float2* dst = c->d_iq_rx.p + (size_t)a * c->rx_stride + t0;
+        DNRP_CUDA(cudaMemcpy2DAsync(dst, (size_t)d.N_RX * c->rx_stride * sizeof(float2), src,
+                                    (size_t)d.N_TX * c->tx_stride * sizeof(float2),
+                                    (size_t)d.n_packet_os * sizeof(float2), n, cudaMemcpyDeviceToDevice, c->stream));
+    }
+    return DNRP_OK;
+}
+
+}  // extern "C"

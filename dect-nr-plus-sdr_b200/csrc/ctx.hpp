@@ -106,6 +106,18 @@ struct dnrp_ctx {
     uint32_t tx_stride = 0;  // samples per antenna in d_iq_tx
     dnrp::dbuf<float2> d_iq_tx;
     dnrp::dbuf<dnrp::tx_meta_dev_t> d_tx_meta;
+
+    // receiver: Wiener LUTs (mode l / lr, three SNR classes) and workspaces
+    struct wiener_bufs_t {
+        dnrp::dbuf<uint16_t> idx_pilot, idx_weight;
+        dnrp::dbuf<float> weights;
+    } d_wiener_l[3], d_wiener_lr[3];
+    uint32_t rx_stride = 0;  // samples per antenna in d_iq_rx
+    uint32_t cls_stride = 0;
+    dnrp::dbuf<float2> d_iq_rx, d_Y, d_hzf, d_hstf, d_snr_part;
+    dnrp::dbuf<dnrp::rx_state_t> d_rx_state;
+    dnrp::dbuf<uint8_t> d_cls;
+    std::vector<dnrp::rx_state_t> h_rx_state;
 };
 
 namespace dnrp {
@@ -114,4 +126,8 @@ int run_fec_encode(dnrp_ctx* c, uint32_t n, bool have_mask, bool have_rv);
 int run_fec_decode_tb(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, bool have_reset);
 int run_fec_decode_plcf(dnrp_ctx* c, uint32_t n);
 int run_tx_ofdm(dnrp_ctx* c, uint32_t n);
+dnrp::rx_params_t make_rx_params(dnrp_ctx* c);
+int run_rx_front(dnrp_ctx* c, uint32_t n);             // STF stage, FFTs, DRS zero forcing, SNR classes
+int run_rx_pcc(dnrp_ctx* c, uint32_t n);               // PCC demap + blind PLCF decode
+int run_rx_pdc(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, bool have_reset);
 }  // namespace dnrp

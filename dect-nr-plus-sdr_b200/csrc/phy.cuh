@@ -28,7 +28,53 @@ struct phy_dims_t {
     const float* W_scale;      // [n_cb_idx]
     const float* W_scale_opt;  // [n_cb_idx] "optimal DAC" variant
     const float2* twiddle;     // [N_os]
+    // receiver
+    uint32_t chestim_lr, chestim_stride;    // phy.json chestim_mode_lr_default / _t_stride_default
+    uint32_t n_full_ps;                     // full processing stages in lr mode (rx_synced.cpp:1031-1032)
+    uint32_t pcc_l_max;                     // last OFDM symbol carrying PCC cells
+    struct wiener_dev_t {
+        const uint16_t* idx_pilot;          // [n_t][4][Nk]
+        const uint16_t* idx_weight;         // [n_t][4][Nk]
+        const float* weights;               // [n_vec][n_interp]
+        uint32_t n_interp, n_t;
+    } wiener_l[3], wiener_lr[3];            // per SNR class {-5, 15, 35} dB (rx_synced_param.hpp:216-232)
 };
+
+// per-packet receiver state, produced by the STF stage and consumed by every later stage
+// (the mutable part of sync_report_t + estimator_sto/snr state, reference rx_synced.cpp:503-619)
+struct rx_state_t {
+    int32_t t0;              // first STF sample inside the packet's RX window (fine peak)
+    float inc0;              // mixer phase increment for the STF (cfo_fractional + cfo_integer), rad/sample
+    float inc1;              // increment after the STF based residual correction
+    float cfo_left;          // residual estimated on the STF (added to sync_report.cfo_fractional_rad)
+    float sto_inc;           // estimator_sto phase_increment_rad (per subcarrier)
+    float sto_fractional;    // in samples
+    float rms[8];
+    float SpN_sum, N_sum;    // estimator_snr accumulators after the STF (boost removed)
+    uint32_t SpN_cnt, N_cnt;
+    float snr_db_pcc, snr_db_pdc;
+};
+
+struct rx_params_t {
+    phy_dims_t d;
+    const float2* iq;        // [packet][N_RX][iq_stride]
+    size_t iq_stride;
+    rx_state_t* state;       // [packet]
+    float2* Y;               // [packet][N_RX][N_DF][Nk] equalised-domain OFDM symbols 1..N_DF
+    float2* hzf;             // [packet][N_RX][N_eff_TX][n_drs][NP] zero-forced DRS pilots
+    float2* hstf;            // [packet][N_RX][NP] zero-forced STF cells (after STO derotation)
+    float2* snr_part;        // [packet][N_DF][N_RX] (S+N sum, N sum) of the DRS cells in that symbol
+    uint8_t* cls;            // [packet][cls_stride] Wiener class valid after the j-th OFDM symbol with DRS cells
+    uint32_t cls_stride;
+    int16_t* llr_pcc;        // [packet][196]
+    int16_t* llr;            // [packet][llr_stride]
+    size_t llr_stride;
+};
+
+cudaError_t launch_rx_stf(const rx_params_t& p, uint32_t n_packets, cudaStream_t st);
+cudaError_t launch_rx_fft(const rx_params_t& p, uint32_t n_packets, cudaStream_t st);
+cudaError_t launch_rx_snr_class(const rx_params_t& p, uint32_t n_packets, cudaStream_t st);
+cudaError_t launch_rx_demap(const rx_params_t& p, uint32_t n_packets, bool pcc, cudaStream_t st);
 
 // per-packet transmit parameters: tx_descriptor_t::codebook_index + tx_meta_t
 // (reference lib/include/dectnrp/phy/tx/tx_descriptor.hpp:43-78, tx_meta.hpp:32-58)

@@ -1,0 +1,449 @@
+// phy_rx.cu -- synchronised receiver front end on the GPU (reference lib/src/phy/rx/rx_synced/
+// rx_synced.cpp): STF stage (CFO derotation, cover sequence, residual CFO, FFT, zero-forcing at the STF
+// cells, fractional STO, SNR), data field FFTs with DRS zero-forcing, Wiener class selection, and the
+// fused channel interpolation + MRC/Alamouti combining + soft demapping kernel.
+#include "fft.cuh"
+#include "phy.cuh"
+
+namespace dnrp {
+
+__device__ __forceinline__ float2 rot(double ph) {  // exp(j*ph), argument reduced in double
+    ph -= 6.283185307179586476925 * rint(ph * 0.15915494309189533577);
+    float s, c;
+    sincosf((float)ph, &s, &c);
+    return make_float2(c, s);
+}
+
+// block-wide sum of a float2 (all threads call; result valid in every thread)
+__device__ float2 block_sum2(float2 v, float2* s_red) {
+    for (int o = 16; o > 0; o >>= 1) {
+        v.x += __shfl_xor_sync(0xffffffffu, v.x, o);
+        v.y += __shfl_xor_sync(0xffffffffu, v.y, o);
+    }
+    const uint32_t w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) s_red[w] = v;
+    __syncthreads();
+    float2 t = make_float2(0.f, 0.f);
+    for (uint32_t i = 0; i < nw; ++i) { t.x += s_red[i].x; t.y += s_red[i].y; }
+    return t;
+}
+
+// subcarrier index of STF cell i (every 4th occupied subcarrier, centre gap of 8; stf.cpp:219-231)
+__device__ __forceinline__ uint32_t stf_cell_k(uint32_t i, uint32_t N_OCC) {
+    const uint32_t NS = N_OCC / 4;
+    return i < NS / 2 ? 4 * i : N_OCC / 2 + 4 + 4 * (i - NS / 2);
+}
+
+// FFT bin of subcarrier k (0 .. N_OCC, DC at N_OCC/2), inverse of the TX mapping
+__device__ __forceinline__ uint32_t bin_of_k(uint32_t k, const phy_dims_t& d) {
+    return k >= d.N_OCC / 2 ? k - d.N_OCC / 2 : d.N_os - d.N_OCC / 2 + k;
+}
+
+// ---- STF stage, one block per packet (rx_synced.cpp:503-709, estimator_sto.cpp:47-173,
+// estimator_snr.cpp:48-145)
+__global__ void __launch_bounds__(256) k_rx_stf(const rx_params_t p) {
+    extern __shared__ float2 sm[];
+    const phy_dims_t& d = p.d;
+    const uint32_t pkt = blockIdx.x, tid = threadIdx.x, nthr = blockDim.x;
+    rx_state_t& st = p.state[pkt];
+    const uint32_t NS = d.N_OCC / 4;
+    float2* S = sm;                      // [stf_len_os] derotated STF with the cover sequence undone
+    float2* X = S + d.stf_len_os;        // [N_os]
+    float2* Yb = X + d.N_os;             // [N_os]
+    float2* H = Yb + d.N_os;             // [N_RX][NS] zero-forced STF cells
+    __shared__ float2 s_red[8];
+    __shared__ float s_ang[8];
+
+    const int32_t t0 = st.t0;
+    const float inc0 = st.inc0;
+    const float c[9] = {1.f, -1.f, 1.f, 1.f, -1.f, -1.f, -1.f, -1.f, -1.f};
+    const float fscale = sqrtf((float)d.N_OCC) / (float)d.N_os;  // rx_synced.cpp:761
+    float2 corr = make_float2(0.f, 0.f);
+
+    for (uint32_t a = 0; a < d.N_RX; ++a) {
+        const float2* x = p.iq + ((size_t)pkt * d.N_RX + a) * p.iq_stride + t0;
+        float2 pw = make_float2(0.f, 0.f);
+        for (uint32_t n = tid; n < d.stf_len_os; n += nthr) {
+            float2 v = cmul(x[n], rot((double)inc0 * (double)n));
+            pw.x += v.x * v.x + v.y * v.y;
+            const float cs = c[n / d.pat_len_os];
+            S[n] = make_float2(v.x * cs, v.y * cs);
+        }
+        pw = block_sum2(pw, s_red);
+        if (tid == 0 && !(st.rms[a] > 0.f)) st.rms[a] = sqrtf(pw.x / (float)d.stf_len_os);
+        // residual CFO: sum over pattern pairs of <pattern j, conj(pattern j+1)> (rx_synced.cpp:536-550)
+        float2 cr = make_float2(0.f, 0.f);
+        const uint32_t npair = (d.n_pat - 1) * d.pat_len_os;
+        for (uint32_t n = tid; n < npair; n += nthr) cr = cadd(cr, cmulc(S[n], S[n + d.pat_len_os]));
+        cr = block_sum2(cr, s_red);
+        corr = cadd(corr, cr);
+        // FFT of the last N_os samples, un-mirror, scale, zero-forcing at the STF cells
+        for (uint32_t n = tid; n < d.N_os; n += nthr) X[n] = S[d.stf_cp_os + n];
+        const float2* F = block_fft<false>(X, Yb, d.N_os, d.twiddle);
+        for (uint32_t i = tid; i < NS; i += nthr) {
+            const uint32_t k = stf_cell_k(i, d.N_OCC);
+            const float2 y = F[bin_of_k(k, d)];
+            const float sg = 0.70710678118654752f * (float)d.stf_sign[k];
+            // y / (sg + j*sg) = y * conj(ref) / |ref|^2, |ref|^2 = 1
+            H[a * NS + i] = cmulc(make_float2(y.x * fscale, y.y * fscale), make_float2(sg, sg));
+        }
+        __syncthreads();
+    }
+
+    // ---- fractional STO from the phase gradient over the STF cells, angles averaged over antennas
+    for (uint32_t a = 0; a < d.N_RX; ++a) {
+        float2 acc = make_float2(0.f, 0.f);
+        for (uint32_t i = tid; i + 1 < NS; i += nthr) {
+            float2 pr = cmulc(H[a * NS + i], H[a * NS + i + 1]);
+            if (i == NS / 2 - 1) {  // centre pair spans 8 subcarriers: rotate back by half its angle
+                const float ang = atan2f(pr.y, pr.x);
+                float s_, c_;
+                sincosf(-ang * 0.5f, &s_, &c_);
+                pr = cmul(pr, make_float2(c_, s_));
+            }
+            acc = cadd(acc, pr);
+        }
+        acc = block_sum2(acc, s_red);
+        if (tid == 0) s_ang[a] = atan2f(acc.y, acc.x) / 4.0f;
+    }
+    __syncthreads();
+    float sto_inc = 0.f;
+    for (uint32_t a = 0; a < d.N_RX; ++a) sto_inc += s_ang[a];
+    sto_inc /= (float)d.N_RX;
+
+    // ---- derotate the STF cells (zero rotation at DC), then SNR on the derotated cells
+    float2 sn = make_float2(0.f, 0.f);  // (S+N sum, N sum)
+    for (uint32_t a = 0; a < d.N_RX; ++a) {
+        for (uint32_t i = tid; i < NS; i += nthr) {
+            const int k = (int)stf_cell_k(i, d.N_OCC) - (int)(d.N_OCC / 2);
+            H[a * NS + i] = cmul(H[a * NS + i], rot((double)sto_inc * (double)k));
+        }
+        __syncthreads();
+        for (uint32_t i = tid; i < NS; i += nthr) {
+            const float2 h = H[a * NS + i];
+            sn.x += h.x * h.x + h.y * h.y;
+            if (i + 1 < NS) {
+                const float2 dlt = csub(h, H[a * NS + i + 1]);
+                sn.y += 0.5f * (dlt.x * dlt.x + dlt.y * dlt.y);
+            }
+            p.hstf[((size_t)pkt * d.N_RX + a) * NS + i] = h;
+        }
+    }
+    sn = block_sum2(sn, s_red);
+    if (tid == 0) {
+        const float cfo_left = atan2f(corr.y, corr.x) / (float)d.pat_len_os;
+        st.cfo_left = cfo_left;
+        st.inc1 = inc0 + cfo_left;
+        st.sto_inc = sto_inc;
+        st.sto_fractional = sto_inc / 6.283185307179586f * (float)d.N_os;
+        // STF cells are boosted by 6 dB: keep the noise, divide the signal part by 4
+        const float S_ = sn.x - sn.y;
+        st.SpN_sum = S_ * 0.25f + sn.y;
+        st.N_sum = sn.y;
+        st.SpN_cnt = d.N_RX * NS;
+        st.N_cnt = d.N_RX * (NS - 1);
+    }
+}
+
+// sign of the DRS cell at (symbol l, subcarrier k): the transmitter's own resource element table
+// (spec_re.hpp cell words, bit 26 = negative pilot; clause 5.2.3, reference drs.cpp:60-101)
+__device__ __forceinline__ float drs_sign_dev(const phy_dims_t& d, uint32_t l, uint32_t k) {
+    return ((d.cell[(size_t)l * d.Nk + k] >> 26) & 1u) ? -1.f : 1.f;
+}
+
+// ---- data field: one block per (symbol l = 1..N_DF, RX antenna, packet): CFO derotation, CP removal,
+// FFT, un-mirroring, amplitude scaling, STO derotation (rx_synced.cpp:711-771); DRS symbols also
+// deliver the zero-forced pilots and their SNR sums (rx_synced.cpp:773-861, estimator_snr.cpp:76-86)
+__global__ void __launch_bounds__(256) k_rx_fft(const rx_params_t p) {
+    extern __shared__ float2 sm[];
+    const phy_dims_t& d = p.d;
+    const uint32_t l = blockIdx.x + 1, a = blockIdx.y, pkt = blockIdx.z;
+    const uint32_t tid = threadIdx.x, nthr = blockDim.x;
+    const rx_state_t& st = p.state[pkt];
+    float2* X = sm;
+    float2* Yb = sm + d.N_os;
+    __shared__ float2 s_red[8];
+
+    const uint32_t n0 = d.stf_len_os + (l - 1) * d.sym_len_os + d.cp_os;  // relative to the first STF sample
+    const float2* x = p.iq + ((size_t)pkt * d.N_RX + a) * p.iq_stride + st.t0 + n0;
+    // mixer phase is continuous: inc0 over the STF, inc1 afterwards (rx_synced.cpp:239-245, 552-555)
+    const double ph0 = (double)st.inc0 * (double)d.stf_len_os + (double)st.inc1 * (double)(n0 - d.stf_len_os);
+    for (uint32_t n = tid; n < d.N_os; n += nthr) X[n] = cmul(x[n], rot(ph0 + (double)st.inc1 * (double)n));
+    const float2* F = block_fft<false>(X, Yb, d.N_os, d.twiddle);
+
+    const float fscale = sqrtf((float)d.N_OCC) / (float)d.N_os;
+    float2* Yout = p.Y + (((size_t)pkt * d.N_RX + a) * d.N_DF + (l - 1)) * d.Nk;
+    float2* Ys = (float2*)(F == X ? Yb : X);  // keep the output symbol in shared for the pilot stage
+    for (uint32_t k = tid; k < d.Nk; k += nthr) {
+        const float2 y = F[bin_of_k(k, d)];
+        const float2 v = cmul(make_float2(y.x * fscale, y.y * fscale),
+                              rot((double)st.sto_inc * (double)((int)k - (int)(d.N_OCC / 2))));
+        Yout[k] = v;
+        Ys[k] = v;
+    }
+    __syncthreads();
+
+    // ---- DRS of this symbol (if any): stream group g0..g1 at occurrence n
+    float2 sn = make_float2(0.f, 0.f);
+    bool any = false;
+    for (uint32_t ts = 0; ts < d.N_eff_TX; ++ts) {
+        const uint32_t lt = l - 1 - ts / 4;  // symbols since the first DRS symbol of this stream
+        if (l < 1 + ts / 4 || lt % d.N_step != 0) continue;
+        const uint32_t n = lt / d.N_step;
+        if (n >= d.n_drs) continue;
+        any = true;
+        const uint32_t pc = ((ts & 3) + 2 * (n & 1)) & 3;
+        float2* hz = p.hzf + ((((size_t)pkt * d.N_RX + a) * d.N_eff_TX + ts) * d.n_drs + n) * d.NP;
+        for (uint32_t i = tid; i < d.NP; i += nthr) {
+            const uint32_t q = 4 * i + pc;
+            const uint32_t k = q < d.N_OCC / 2 ? q : q + 1;
+            const float sg = drs_sign_dev(d, l, k);
+            const float2 h = make_float2(Ys[k].x * sg, Ys[k].y * sg);  // division by +-1
+            hz[i] = h;
+            sn.x += h.x * h.x + h.y * h.y;
+            if (i + 1 < d.NP) {
+                const uint32_t q2 = q + 4, k2 = q2 < d.N_OCC / 2 ? q2 : q2 + 1;
+                const float sg2 = drs_sign_dev(d, l, k2);
+                const float2 dlt = csub(h, make_float2(Ys[k2].x * sg2, Ys[k2].y * sg2));
+                sn.y += 0.5f * (dlt.x * dlt.x + dlt.y * dlt.y);
+            }
+        }
+    }
+    sn = block_sum2(sn, s_red);
+    if (tid == 0) p.snr_part[((size_t)pkt * d.N_DF + (l - 1)) * d.N_RX + a] = any ? sn : make_float2(0.f, 0.f);
+}
+
+// ---- Wiener class per DRS symbol, one thread per packet: replays estimator_snr_t in symbol order and
+// picks the nearest of {-5, 15, 35} dB, later index winning ties (rx_synced.cpp:863-891)
+__global__ void k_rx_snr_class(const rx_params_t p, uint32_t n_packets) {
+    const uint32_t pkt = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pkt >= n_packets) return;
+    const phy_dims_t& d = p.d;
+    rx_state_t& st = p.state[pkt];
+    float SpN = st.SpN_sum, Ns = st.N_sum;
+    uint32_t c1 = st.SpN_cnt, c2 = st.N_cnt;
+    uint32_t j = 0;
+    const uint32_t ts_per_sym = d.N_eff_TX < 4 ? d.N_eff_TX : 4;
+    float snr_db = 0.f;
+    st.snr_db_pcc = 0.f;
+    for (uint32_t l = 1; l <= d.N_DF; ++l) {
+        bool is_drs = (l - 1) % d.N_step == 0 && (l - 1) / d.N_step < d.n_drs;
+        if (d.N_eff_TX == 8 && l >= 2 && (l - 2) % d.N_step == 0 && (l - 2) / d.N_step < d.n_drs) is_drs = true;
+        if (is_drs) {
+            for (uint32_t a = 0; a < d.N_RX; ++a) {
+                const float2 v = p.snr_part[((size_t)pkt * d.N_DF + (l - 1)) * d.N_RX + a];
+                SpN += v.x;
+                Ns += v.y;
+            }
+            c1 += d.N_RX * ts_per_sym * d.NP;
+            c2 += d.N_RX * ts_per_sym * (d.NP - 1);
+            if (SpN <= 0.f || Ns <= 0.f) snr_db = 0.f;
+            else snr_db = 10.0f * log10f(((SpN - Ns) / (float)c1) / (Ns / (float)c2));
+            const float ref[3] = {-5.f, 15.f, 35.f};
+            uint32_t idx = 0;
+            float best = fabsf(snr_db - ref[0]);
+            for (uint32_t i = 1; i < 3; ++i) {
+                const float s = fabsf(snr_db - ref[i]);
+                if (s <= best) { best = s; idx = i; }
+            }
+            p.cls[(size_t)pkt * p.cls_stride + j] = (uint8_t)idx;
+            ++j;
+        }
+        if (l == d.pcc_l_max) st.snr_db_pcc = snr_db;
+    }
+    st.snr_db_pdc = snr_db;
+}
+
+// ---- channel estimate of transmit stream ts at (symbol l, subcarrier k) seen by RX antenna a: the value
+// rx_synced_t::run_drs_ch_interpolation (rx_synced.cpp:893-960) holds in chestim[ts][k] at the moment
+// the reference collects the cells of symbol l.  Closed form of the processing stage bookkeeping of
+// rx_synced.cpp:1027-1152, see DESIGN.md "Receiver: which interpolation serves which symbol".
+__device__ float2 chan_est(const rx_params_t& p, uint32_t pkt, uint32_t a, uint32_t ts, uint32_t l, uint32_t k,
+                           bool pcc_stage) {
+    const phy_dims_t& d = p.d;
+    const uint8_t* cls = p.cls + (size_t)pkt * p.cls_stride;
+    const float2* hz_ts = p.hzf + (((size_t)pkt * d.N_RX + a) * d.N_eff_TX + ts) * d.n_drs * d.NP;
+    float2 h = make_float2(0.f, 0.f);
+    if (pcc_stage || !d.chestim_lr || d.n_full_ps == 0) {
+        // mode "l": DRS occurrence n at or before symbol l, non-interlaced pilots, LUT slot 0
+        uint32_t n = (l - 1) / d.N_step;
+        if (n >= d.n_drs) n = d.n_drs - 1;
+        const uint32_t j = d.N_eff_TX == 8 ? 2 * n + (ts >= 4 ? 1 : 0) : n;
+        const phy_dims_t::wiener_dev_t& W = d.wiener_l[cls[j]];
+        const uint32_t pc = ((ts & 3) + 2 * (n & 1)) & 3;
+        const size_t o = (size_t)pc * d.Nk + k;
+        const float* w = W.weights + (size_t)W.idx_weight[o] * W.n_interp;
+        const float2* hz = hz_ts + (size_t)n * d.NP + W.idx_pilot[o];
+        for (uint32_t i = 0; i < W.n_interp; ++i) {
+            h.x += w[i] * hz[i].x;
+            h.y += w[i] * hz[i].y;
+        }
+    } else {
+        // mode "lr": processing stage ps between DRS occurrences ps (left) and ps + 1 (right)
+        uint32_t ps = 0, r = 0;
+        if (l > 1) {
+            ps = (l - 2) / d.N_step;
+            if (ps > d.n_full_ps - 1) ps = d.n_full_ps - 1;
+            r = l - 1 - ps * d.N_step;
+        }
+        const uint32_t rs = ps == 0 ? 0 : 1;
+        const uint32_t re = r < d.N_step ? r : d.N_step;
+        const uint32_t rstar = rs + ((re - rs) / d.chestim_stride) * d.chestim_stride;
+        const uint32_t j = d.N_eff_TX == 8 ? 2 * (ps + 1) + 1 : ps + 1;
+        const phy_dims_t::wiener_dev_t& W = d.wiener_lr[cls[j]];
+        const uint32_t pc = ((ts & 3) + 2 * (ps & 1)) & 3;
+        const size_t o = ((size_t)rstar * 4 + pc) * d.Nk + k;
+        const float* w = W.weights + (size_t)W.idx_weight[o] * W.n_interp;
+        const uint32_t m0 = W.idx_pilot[o];
+        const uint32_t flip = pc >= 2 ? 1 : 0;
+        for (uint32_t i = 0; i < W.n_interp; ++i) {
+            const uint32_t m = m0 + i;
+            const uint32_t side = (m & 1) ^ flip;
+            const float2 v = hz_ts[(size_t)(ps + side) * d.NP + (m >> 1)];
+            h.x += w[i] * v.x;
+            h.y += w[i] * v.y;
+        }
+    }
+    return h;
+}
+
+// transmit stream pair of Alamouti pair index i_mod (Table 6.3.3.2, reference
+// transmit_diversity_precoding.cpp:45-72); same table as the transmitter
+__device__ __forceinline__ void txdiv_pair_rx(uint32_t N_TS, uint32_t i_mod, uint32_t& A, uint32_t& B) {
+    if (N_TS == 2) { A = 0; B = 1; return; }
+    if (N_TS == 4) {
+        A = (0x101020u >> (4 * i_mod)) & 0xfu;   // 0 2 0 1 0 1
+        B = (0x233231u >> (4 * i_mod)) & 0xfu;   // 1 3 2 3 3 2
+        return;
+    }
+    A = (uint32_t)((0x541032106420ull >> (4 * i_mod)) & 0xfull);  // 0 2 4 6 0 1 2 3 0 1 4 5
+    B = (uint32_t)((0x763276547531ull >> (4 * i_mod)) & 0xfull);  // 1 3 5 7 4 5 6 7 2 3 6 7
+}
+
+// float -> int16 like a C cast (toward zero), saturating
+__device__ __forceinline__ float to_short(float v) {
+    v = truncf(v);
+    return fminf(fmaxf(v, -32768.f), 32767.f);
+}
+
+// soft demapper to int16 LLRs, LLR > 0 <=> bit 1 (srsRAN demod_soft_demodulate_s restated, DESIGN.md
+// "Demapper"; called by rx_synced.cpp:997, 1287, 1297, 1322)
+__device__ void demap_cell(float2 z, uint32_t N_bps, int16_t* out) {
+    if (N_bps == 1) {
+        out[0] = (int16_t)to_short(-(100.f * (z.x + z.y) * 0.70710678118654752f));
+        return;
+    }
+    if (N_bps == 2) {
+        out[0] = (int16_t)to_short(z.x * (-100.f * 1.41421356237309505f));
+        out[1] = (int16_t)to_short(z.y * (-100.f * 1.41421356237309505f));
+        return;
+    }
+    const float S = N_bps == 4 ? 400.f : (N_bps == 6 ? 700.f : 1000.f);
+    const float nrm = N_bps == 4 ? 0.31622776601683794f : (N_bps == 6 ? 0.15430334996209191f : 0.07669649888473704f);
+    const float yre = to_short(S * z.x), yim = to_short(S * z.y);
+    out[0] = (int16_t)(-yre);  // -(-32768) saturates below
+    out[1] = (int16_t)(-yim);
+    if (yre == -32768.f) out[0] = 32767;
+    if (yim == -32768.f) out[1] = 32767;
+    float th = (float)(N_bps == 4 ? 2 : (N_bps == 6 ? 4 : 8)) * S * nrm;
+    float a0 = to_short(fabsf(yre) - th), a1 = to_short(fabsf(yim) - th);
+    out[2] = (int16_t)a0;
+    out[3] = (int16_t)a1;
+    for (uint32_t b = 4; b < N_bps; b += 2) {
+        th *= 0.5f;
+        a0 = to_short(fabsf(a0) - th);
+        a1 = to_short(fabsf(a1) - th);
+        out[b] = (int16_t)a0;
+        out[b + 1] = (int16_t)a1;
+    }
+}
+
+// ---- fused channel interpolation + MRC / Alamouti combining + demapping, one thread per cell (single
+// stream) or per cell pair (transmit diversity).  grid (ceil(units / 128), packets)
+__global__ void __launch_bounds__(128) k_rx_demap(const rx_params_t p, uint32_t pcc) {
+    const phy_dims_t& d = p.d;
+    const uint32_t pkt = blockIdx.y;
+    const uint32_t n_cells = pcc ? 98u : d.N_PDC_subc;
+    const uint32_t N_bps = pcc ? 2u : d.N_bps;
+    const uint32_t* lk = pcc ? d.pcc_lk : d.pdc_lk;
+    int16_t* out = pcc ? p.llr_pcc + (size_t)pkt * 196 : p.llr + (size_t)pkt * p.llr_stride;
+    const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
+    int16_t tmp[16];
+    if (d.N_eff_TX == 1) {
+        if (u >= n_cells) return;
+        const uint32_t l = lk[u] >> 16, k = lk[u] & 0xffffu;
+        float2 num = make_float2(0.f, 0.f);
+        float den = 0.f;
+        for (uint32_t a = 0; a < d.N_RX; ++a) {
+            const float2 y = p.Y[(((size_t)pkt * d.N_RX + a) * d.N_DF + (l - 1)) * d.Nk + k];
+            const float2 h = chan_est(p, pkt, a, 0, l, k, pcc);
+            num = cadd(num, cmulc(y, h));
+            den += h.x * h.x + h.y * h.y;
+        }
+        demap_cell(make_float2(num.x / den, num.y / den), N_bps, tmp);
+        for (uint32_t b = 0; b < N_bps; ++b) out[(size_t)u * N_bps + b] = tmp[b];
+    } else {
+        if (2 * u >= n_cells) return;
+        const uint32_t q = 2 * u;
+        const uint32_t l = lk[q] >> 16, k0 = lk[q] & 0xffffu, k1 = lk[q + 1] & 0xffffu;
+        const uint32_t im = u % d.txdiv_modulo;
+        uint32_t tsA, tsB;
+        txdiv_pair_rx(d.N_eff_TX, im, tsA, tsB);
+        float2 n0 = make_float2(0.f, 0.f), n1 = n0;
+        float den = 0.f;
+        for (uint32_t a = 0; a < d.N_RX; ++a) {
+            const float2* Y = p.Y + (((size_t)pkt * d.N_RX + a) * d.N_DF + (l - 1)) * d.Nk;
+            const float2 r0 = Y[k0], r1 = Y[k1];
+            const float2 hA0 = chan_est(p, pkt, a, tsA, l, k0, pcc), hA1 = chan_est(p, pkt, a, tsA, l, k1, pcc);
+            const float2 hB0 = chan_est(p, pkt, a, tsB, l, k0, pcc), hB1 = chan_est(p, pkt, a, tsB, l, k1, pcc);
+            const float2 h0 = make_float2(0.5f * (hA0.x + hA1.x), 0.5f * (hA0.y + hA1.y));
+            const float2 h1 = make_float2(0.5f * (hB0.x + hB1.x), 0.5f * (hB0.y + hB1.y));
+            // conj(h0) r0 + h1 conj(r1)   and   -h1 conj(r0) + conj(h0) r1   (rx_synced.cpp:1372-1373)
+            n0 = cadd(n0, cadd(cmulc(r0, h0), cmulc(h1, r1)));
+            n1 = cadd(n1, csub(cmulc(r1, h0), cmulc(h1, r0)));
+            den += h0.x * h0.x + h0.y * h0.y + h1.x * h1.x + h1.y * h1.y;
+        }
+        demap_cell(make_float2(n0.x / den, n0.y / den), N_bps, tmp);
+        demap_cell(make_float2(n1.x / den, n1.y / den), N_bps, tmp + N_bps);
+        for (uint32_t b = 0; b < 2 * N_bps; ++b) out[(size_t)q * N_bps + b] = tmp[b];
+    }
+}
+
+cudaError_t launch_rx_demap(const rx_params_t& p, uint32_t n_packets, bool pcc, cudaStream_t st) {
+    const uint32_t n_cells = pcc ? 98u : p.d.N_PDC_subc;
+    const uint32_t units = p.d.N_eff_TX == 1 ? n_cells : n_cells / 2;
+    k_rx_demap<<<dim3((units + 127) / 128, n_packets), 128, 0, st>>>(p, pcc ? 1u : 0u);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_rx_snr_class(const rx_params_t& p, uint32_t n_packets, cudaStream_t st) {
+    k_rx_snr_class<<<(n_packets + 127) / 128, 128, 0, st>>>(p, n_packets);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_rx_fft(const rx_params_t& p, uint32_t n_packets, cudaStream_t st) {
+    const size_t smem = sizeof(float2) * 2 * p.d.N_os;
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+        cudaError_t e = cudaFuncSetAttribute(k_rx_fft, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured = smem;
+    }
+    k_rx_fft<<<dim3(p.d.N_DF, p.d.N_RX, n_packets), 256, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
+cudaError_t launch_rx_stf(const rx_params_t& p, uint32_t n_packets, cudaStream_t st) {
+    const size_t smem = sizeof(float2) * ((size_t)p.d.stf_len_os + 2 * p.d.N_os + (size_t)p.d.N_RX * (p.d.N_OCC / 4));
+    static size_t configured = 0;
+    if (smem > 48 * 1024 && smem > configured) {
+        cudaError_t e = cudaFuncSetAttribute(k_rx_stf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e != cudaSuccess) return e;
+        configured = smem;
+    }
+    k_rx_stf<<<n_packets, 256, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
+}  // namespace dnrp

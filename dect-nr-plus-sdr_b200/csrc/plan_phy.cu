@@ -1,7 +1,10 @@
 // plan_phy.cu -- host-side construction of the OFDM / receiver plan of one packet geometry: flat
 // resource-element tables, STF signs, codebooks, FFT twiddles, Wiener look-up tables; uploaded once.
+#include <algorithm>
 #include <cmath>
+#include <cstring>
 #include "ctx.hpp"
+#include "spec_wiener.hpp"
 
 namespace dnrp {
 
@@ -73,6 +76,51 @@ int build_phy_plan(dnrp_ctx* c) {
     c->tx_stride = (d.n_packet_os + 3) & ~3u;
     UP(c->d_iq_tx.alloc((size_t)c->B * d.N_TX * c->tx_stride));
     UP(c->d_tx_meta.alloc(c->B));
+
+    // ---- receiver
+    d.chestim_lr = c->cfg.chestim_mode_lr ? 1 : 0;
+    d.chestim_stride = c->cfg.chestim_mode_lr_t_stride ? c->cfg.chestim_mode_lr_t_stride : 1;
+    {
+        // rx_synced.cpp:1027-1032: stage length 6 / 11 / 12 symbols for N_step 5 / 10 / 10 (N_eff_TX 8)
+        const uint32_t ps_len = d.N_eff_TX <= 2 ? 6 : (d.N_eff_TX == 4 ? 11 : 12);
+        d.n_full_ps = d.N_DF >= ps_len - d.N_step ? (d.N_DF - (ps_len - d.N_step)) / d.N_step : 0;
+        if (d.n_full_ps + 1 > d.n_drs) d.n_full_ps = d.n_drs > 0 ? d.n_drs - 1 : 0;
+        d.pcc_l_max = 0;
+        for (uint32_t v : m.pcc_lk) d.pcc_l_max = std::max(d.pcc_l_max, v >> 16);
+    }
+    static const double nu_max[3] = {100.0, 100.0, 500.0}, tau_rms[3] = {0.1e-6, 0.1e-6, 1.0e-6},
+                        snr_db[3] = {-5.0, 15.0, 35.0};
+    static const uint32_t n_lr[3] = {14, 8, 3}, n_l[3] = {7, 4, 2};
+    for (uint32_t i = 0; i < 3 && ok; ++i) {
+        spec::wiener_lut_t Ll, Llr;
+        if (!spec::build_wiener_lut(d.b, d.u, 0, nu_max[i], tau_rms[i], snr_db[i], n_l[i], Ll) ||
+            !spec::build_wiener_lut(d.b, d.u, d.N_step, nu_max[i], tau_rms[i], snr_db[i], n_lr[i], Llr)) {
+            set_last_error("Wiener LUT construction failed");
+            return DNRP_ERR_INVALID;
+        }
+        UP(c->d_wiener_l[i].idx_pilot.upload(Ll.idx_pilot));
+        UP(c->d_wiener_l[i].idx_weight.upload(Ll.idx_weight));
+        UP(c->d_wiener_l[i].weights.upload(Ll.weights));
+        UP(c->d_wiener_lr[i].idx_pilot.upload(Llr.idx_pilot));
+        UP(c->d_wiener_lr[i].idx_weight.upload(Llr.idx_weight));
+        UP(c->d_wiener_lr[i].weights.upload(Llr.weights));
+        d.wiener_l[i] = {c->d_wiener_l[i].idx_pilot.p, c->d_wiener_l[i].idx_weight.p, c->d_wiener_l[i].weights.p,
+                         Ll.n_interp, Ll.n_t};
+        d.wiener_lr[i] = {c->d_wiener_lr[i].idx_pilot.p, c->d_wiener_lr[i].idx_weight.p,
+                          c->d_wiener_lr[i].weights.p, Llr.n_interp, Llr.n_t};
+    }
+    // RX window: the packet plus room for the synchronisation offset t0 (at most one STF) in front
+    c->rx_stride = (d.n_packet_os + d.stf_len_os + 3) & ~3u;
+    c->cls_stride = (d.N_eff_TX == 8 ? 2 : 1) * d.n_drs + 2;
+    const size_t B = c->B;
+    UP(c->d_iq_rx.alloc(B * d.N_RX * c->rx_stride));
+    UP(c->d_Y.alloc(B * d.N_RX * d.N_DF * d.Nk));
+    UP(c->d_hzf.alloc(B * d.N_RX * d.N_eff_TX * d.n_drs * d.NP));
+    UP(c->d_hstf.alloc(B * d.N_RX * d.NP));
+    UP(c->d_snr_part.alloc(B * d.N_DF * d.N_RX));
+    UP(c->d_rx_state.alloc(B));
+    UP(c->d_cls.alloc(B * c->cls_stride));
+    c->h_rx_state.resize(B);
 #undef UP
     if (!ok) {
         set_last_error("device allocation failed (phy plan)");

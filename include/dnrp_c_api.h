@@ -116,6 +116,72 @@ uint32_t dnrp_tx_stride(const dnrp_ctx_t* ctx);
 int dnrp_tx_batch(dnrp_ctx_t* ctx, uint32_t n, const dnrp_tx_desc_t* descs, const uint8_t* plcf,
                   const uint8_t* tb, dnrp_cf32_t* iq_out, uint32_t* n_samples_out);
 
+/* ---- synchronised receiver ----------------------------------------------------------------------
+ * dnrp_sync_report_t = the fields of sync_report_t the synchronised receiver consumes
+ * (lib/include/dectnrp/phy/rx/sync/sync_report.hpp:41-111).  fine_peak_time_local is the index of the
+ * first STF sample inside this packet's IQ window (the reference's fine_peak_time_64 relative to the
+ * buffer position the window starts at); the cfo values are CORRECTION phase increments in rad per
+ * sample at the oversampled rate, as sync_t hands them over; rms[a] = 0 lets the STF stage estimate it. */
+typedef struct {
+    uint32_t fine_peak_time_local;
+    float cfo_fractional_rad;
+    float cfo_integer_rad;
+    float rms[8];
+} dnrp_sync_report_t;
+
+/* pcc_report_t (lib/include/dectnrp/phy/rx/rx_synced/pcc_report.hpp:33-52) + the sync_report_t fields
+ * the PCC stage updates (rx_synced.cpp:258-262): index 0 = PLCF type 1, 1 = type 2 */
+typedef struct {
+    uint8_t plcf_ok[2];
+    uint8_t plcf[2][10];
+    uint32_t crc_mask[2];       /* matched mask: 0 none, 0x5555 closed loop, 0xAAAA beamforming, 0xFFFF both */
+    float snr_dB;
+    float cfo_residual_rad;     /* STF based residual, added to cfo_fractional_rad from then on */
+    float sto_fractional;       /* in samples */
+    float rms[8];
+} dnrp_pcc_report_t;
+
+/* pdc_report_t (lib/include/dectnrp/phy/rx/rx_synced/pdc_report.hpp:33-56) */
+typedef struct {
+    uint32_t crc_ok;
+    float snr_dB;
+} dnrp_pdc_report_t;
+
+/* samples per antenna reserved for one packet's IQ window in iq_in */
+uint32_t dnrp_rx_stride(const dnrp_ctx_t* ctx);
+
+/* rx_synced_t::demoddecod_rx_pcc (lib/src/phy/rx/rx_synced/rx_synced.cpp:115-274) for n packets.
+ * iq_in [n][N_RX][dnrp_rx_stride()] host IQ windows (NULL: the windows already resident on the device,
+ * e.g. written by dnrp_channel_batch); sync [n]; out [n].  Runs the whole front end of the packet (STF
+ * stage, all data field FFTs, DRS zero forcing, SNR classes) and the blind PLCF decoding. */
+int dnrp_rx_pcc_batch(dnrp_ctx_t* ctx, uint32_t n, const dnrp_cf32_t* iq_in, const dnrp_sync_report_t* sync,
+                      dnrp_pcc_report_t* out);
+
+/* rx_synced_t::demoddecod_rx_pdc (rx_synced.cpp:276-361) for the n packets of the preceding
+ * dnrp_rx_pcc_batch call: channel interpolation, MRC / Alamouti combining, demapping, decode_tb.
+ * harq_slot / rv / harq_reset as in dnrp_fec_decode_tb; tb_out [n][N_TB_byte]; n_iter [n][C] or NULL. */
+int dnrp_rx_pdc_batch(dnrp_ctx_t* ctx, uint32_t n, const uint32_t* harq_slot, const uint8_t* rv,
+                      const uint8_t* harq_reset, uint8_t* tb_out, dnrp_pdc_report_t* out, uint8_t* n_iter);
+
+/* test / scope taps (the reference exposes the same data through its JSON export and TCP scope,
+ * rx_synced.cpp:363-443): copies an intermediate device buffer of the last call to the host.
+ * Returns DNRP_ERR_INVALID if dst_bytes is smaller than the buffer for n packets. */
+typedef enum {
+    DNRP_TAP_Y = 1,        /* cf32 [n][N_RX][N_DF][N_b_OCC+1] OFDM symbols 1..N_DF after FFT/scale/STO */
+    DNRP_TAP_DRS_ZF = 2,   /* cf32 [n][N_RX][N_eff_TX][n_drs][N_b_OCC/4] */
+    DNRP_TAP_STF_ZF = 3,   /* cf32 [n][N_RX][N_b_OCC/4] */
+    DNRP_TAP_LLR_PCC = 4,  /* int16 [n][196] */
+    DNRP_TAP_LLR_PDC = 5,  /* int16 [n][G] */
+    DNRP_TAP_WIENER_CLASS = 6 /* uint8 [n][dnrp_tap_bytes/n] class after each DRS symbol */
+} dnrp_tap_t;
+size_t dnrp_tap_bytes(const dnrp_ctx_t* ctx, int tap, uint32_t n);
+int dnrp_tap_read(dnrp_ctx_t* ctx, int tap, uint32_t n, void* dst, size_t dst_bytes);
+
+/* device-resident loop back: copies the n packets produced by the last dnrp_tx_batch into the
+ * receiver's IQ windows (TX antenna t -> RX antenna t % N_TX, offset `t0` samples), the "hardware
+ * simulator with an ideal channel" of the reference's loopback firmware. */
+int dnrp_loopback_tx_to_rx(dnrp_ctx_t* ctx, uint32_t n, uint32_t t0);
+
 /* ---- measurement hook ------------------------------------------------------------------------
  * Re-runs one device stage `reps` times on the data already resident in the context (left there by
  * the previous host-facing call) and returns the average CUDA-event time per repetition in ms,
