@@ -70,7 +70,26 @@ class PdcReport(C.Structure):
     _fields_ = [("crc_ok", C.c_uint32), ("snr_dB", C.c_float)]
 
 
-TAP_Y, TAP_DRS_ZF, TAP_STF_ZF, TAP_LLR_PCC, TAP_LLR_PDC, TAP_WIENER_CLASS = 1, 2, 3, 4, 5, 6
+# numpy views of the same C structs (batched calls fill / read them without a Python loop)
+SYNC_DTYPE = np.dtype([("fine_peak_time_local", "u4"), ("cfo_fractional_rad", "f4"), ("cfo_integer_rad", "f4"),
+                       ("rms", "f4", (8,))], align=True)
+PCC_DTYPE = np.dtype([("plcf_ok", "u1", (2,)), ("plcf", "u1", (2, 10)), ("crc_mask", "u4", (2,)), ("snr_dB", "f4"),
+                      ("cfo_residual_rad", "f4"), ("sto_fractional", "f4"), ("rms", "f4", (8,))], align=True)
+PDC_DTYPE = np.dtype([("crc_ok", "u4"), ("snr_dB", "f4")], align=True)
+assert SYNC_DTYPE.itemsize == C.sizeof(SyncReport) and PCC_DTYPE.itemsize == C.sizeof(PccReport)
+assert PDC_DTYPE.itemsize == C.sizeof(PdcReport)
+
+
+class ChannelDesc(C.Structure):
+    _fields_ = [("snr_dB", C.c_float), ("net_bandwidth_norm", C.c_float), ("t0", C.c_uint32), ("mode", C.c_uint32),
+                ("seed", C.c_uint64)]
+
+
+CHANNEL_DTYPE = np.dtype([("snr_dB", "f4"), ("net_bandwidth_norm", "f4"), ("t0", "u4"), ("mode", "u4"),
+                          ("seed", "u8")], align=True)
+assert CHANNEL_DTYPE.itemsize == C.sizeof(ChannelDesc)
+TAP_Y, TAP_DRS_ZF, TAP_STF_ZF, TAP_LLR_PCC, TAP_LLR_PDC, TAP_WIENER_CLASS, TAP_TB_OK = 1, 2, 3, 4, 5, 6, 7
+KERNEL_TURBO_DECODE_PDC, KERNEL_RX_FFT, KERNEL_RX_DEMAP_PDC, KERNEL_RX_STF = 0, 1, 2, 3
 
 
 def build(verbose=False):
@@ -127,6 +146,8 @@ class Phy:
         self.ps = ps.as_dict()
         self.max_batch = max_batch
         self.plcf_type = plcf_type
+        self.N_RX = N_RX
+        self.oversampling = oversampling
         self.dbits_stride = ((self.ps["G"] + 7) // 8 + 3) & ~3
 
     def close(self):
@@ -207,38 +228,41 @@ class Phy:
         lib().dnrp_rx_stride.restype = C.c_uint32
         return lib().dnrp_rx_stride(self._ctx)
 
-    def rx_pcc(self, iq, t0=0, cfo_fractional_rad=0.0, cfo_integer_rad=0.0, rms=None, n=None):
+    def make_sync(self, n, t0=0, cfo_fractional_rad=0.0, cfo_integer_rad=0.0, rms=None):
+        """[n] dnrp_sync_report_t as a numpy structured array (same memory layout as SyncReport)"""
+        sync = np.zeros(n, dtype=SYNC_DTYPE)
+        sync["fine_peak_time_local"] = t0
+        sync["cfo_fractional_rad"] = cfo_fractional_rad
+        sync["cfo_integer_rad"] = cfo_integer_rad
+        if rms is not None:
+            r = np.asarray(rms, dtype=np.float32).reshape(n, -1)
+            sync["rms"][:, :r.shape[1]] = r
+        return sync
+
+    def rx_pcc(self, iq, t0=0, cfo_fractional_rad=0.0, cfo_integer_rad=0.0, rms=None, n=None, sync=None):
         """iq [n][N_RX][rx_stride] complex64 host windows, or None to use the device-resident windows
-        (after loopback_tx_to_rx); returns the list of PccReport"""
+        (after channel / loopback_tx_to_rx); returns [n] PccReport records (numpy structured array)"""
         if iq is not None:
             n = iq.shape[0]
             iq = np.ascontiguousarray(iq, dtype=np.complex64)
             assert iq.shape[-1] == self.rx_stride(), (iq.shape, self.rx_stride())
-        t0v, cf, ci = (np.broadcast_to(np.asarray(v), (n,)) for v in (t0, cfo_fractional_rad, cfo_integer_rad))
-        sync = (SyncReport * n)()
-        for i in range(n):
-            sync[i].fine_peak_time_local = int(t0v[i])
-            sync[i].cfo_fractional_rad = float(cf[i])
-            sync[i].cfo_integer_rad = float(ci[i])
-            if rms is not None:
-                for a, v in enumerate(np.atleast_1d(rms[i])):
-                    sync[i].rms[a] = float(v)
-        out = (PccReport * n)()
-        _check(lib().dnrp_rx_pcc_batch(self._ctx, n, _ptr(iq, np.complex64), sync, out))
+        if sync is None:
+            sync = self.make_sync(n, t0, cfo_fractional_rad, cfo_integer_rad, rms)
+        out = np.zeros(n, dtype=PCC_DTYPE).view(np.recarray)
+        _check(lib().dnrp_rx_pcc_batch(self._ctx, n, _ptr(iq, np.complex64), sync.ctypes.data_as(C.c_void_p),
+                                       out.ctypes.data_as(C.c_void_p)))
         return out
 
-    def rx_pdc(self, n, harq_slot=None, rv=None, harq_reset=None):
-        tb = np.zeros((n, self.ps["N_TB_byte"]), dtype=np.uint8)
+    def rx_pdc(self, n, harq_slot=None, rv=None, harq_reset=None, tb_out=None):
+        tb = np.zeros((n, self.ps["N_TB_byte"]), dtype=np.uint8) if tb_out is None else tb_out
         nit = np.zeros((n, self.ps["C"]), dtype=np.uint8)
         slot = None if harq_slot is None else np.ascontiguousarray(harq_slot, dtype=np.uint32)
         rvv = None if rv is None else np.ascontiguousarray(rv, dtype=np.uint8)
         rst = None if harq_reset is None else np.ascontiguousarray(harq_reset, dtype=np.uint8)
-        out = (PdcReport * n)()
+        out = np.zeros(n, dtype=PDC_DTYPE)
         _check(lib().dnrp_rx_pdc_batch(self._ctx, n, _ptr(slot, np.uint32), _ptr(rvv, np.uint8), _ptr(rst, np.uint8),
-                                       _ptr(tb, np.uint8), out, _ptr(nit, np.uint8)))
-        ok = np.array([o.crc_ok for o in out], dtype=bool)
-        snr = np.array([o.snr_dB for o in out], dtype=np.float32)
-        return ok, tb, snr, nit
+                                       _ptr(tb, np.uint8), out.ctypes.data_as(C.c_void_p), _ptr(nit, np.uint8)))
+        return out["crc_ok"].astype(bool), tb, out["snr_dB"].copy(), nit
 
     def tap(self, which, n):
         lib().dnrp_tap_bytes.restype = C.c_size_t
@@ -254,6 +278,30 @@ class Phy:
     def loopback_tx_to_rx(self, n, t0=0):
         _check(lib().dnrp_loopback_tx_to_rx(self._ctx, n, t0))
 
+    # ---- simulation channel (reference simulation/vspace.cpp:437-512, wireless/channel_{awgn,flat}.cpp)
+    def channel(self, n, snr_dB=100.0, t0=0, mode=0, seed=1, net_bandwidth_norm=None, fetch=False):
+        if net_bandwidth_norm is None:
+            net_bandwidth_norm = 1.0 / self.oversampling
+        descs = np.zeros(n, dtype=CHANNEL_DTYPE)
+        descs["snr_dB"], descs["net_bandwidth_norm"], descs["t0"], descs["mode"] = snr_dB, net_bandwidth_norm, t0, mode
+        descs["seed"] = seed
+        out = np.zeros((n, self.N_RX, self.rx_stride()), dtype=np.complex64) if fetch else None
+        _check(lib().dnrp_channel_batch(self._ctx, n, descs.ctypes.data_as(C.c_void_p), _ptr(out, np.complex64)))
+        return out
+
+    # ---- measurement
+    def kernel_time_enable(self, on=True):
+        _check(lib().dnrp_kernel_time_enable(self._ctx, int(on)))
+
+    def kernel_time_read(self, kernel):
+        ms, cnt = C.c_float(), C.c_uint32()
+        _check(lib().dnrp_kernel_time_read(self._ctx, kernel, C.byref(ms), C.byref(cnt)))
+        return ms.value, cnt.value
+
+    def launch_count(self):
+        lib().dnrp_launch_count.restype = C.c_uint64
+        return lib().dnrp_launch_count(self._ctx)
+
     def time_stage(self, stage, n, reps=10):
         ms = C.c_float()
         _check(lib().dnrp_time_stage(self._ctx, stage, n, reps, C.byref(ms)))
@@ -261,3 +309,4 @@ class Phy:
 
 
 STAGE_FEC_DECODE_TB, STAGE_FEC_ENCODE, STAGE_FEC_DECODE_PLCF = 1, 2, 3
+STAGE_RX_CHAIN, STAGE_TX_CHAIN, STAGE_CHANNEL = 4, 5, 6

@@ -129,6 +129,8 @@ void dnrp_ctx_destroy(dnrp_ctx_t* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    for (auto& t : ctx->ktimer)
+        for (cudaEvent_t e : t.ev) cudaEventDestroy(e);
     delete ctx;
 }
 
@@ -161,7 +163,7 @@ int run_fec_encode(dnrp_ctx* c, uint32_t n, bool have_mask, bool have_rv) {
     p.gold = c->d_gold_pdc.p; p.gold_bit_off = 0;
     p.out = c->d_pdc_bits.p; p.out_stride = f.dbits_stride;
     p.rm_arena = c->d_rm_arena.p;
-    DNRP_CUDA(launch_tx_fec(p, n, f.Kmax, c->stream));
+    DNRP_LAUNCH(c, -1, launch_tx_fec(p, n, f.Kmax, c->stream));
     // PLCF: one launch, the descriptor (type 1 or 2) is the plan's plcf_type
     txfec_params_t q{};
     q.cbs = c->d_tx_pcc.p + (c->cfg.plcf_type - 1); q.C = 1;
@@ -171,7 +173,7 @@ int run_fec_encode(dnrp_ctx* c, uint32_t n, bool have_mask, bool have_rv) {
     q.gold = c->d_gold_pcc.p; q.gold_bit_off = 0;
     q.out = c->d_pcc_bits.p; q.out_stride = 28;
     q.rm_arena = c->d_rm_arena.p;
-    DNRP_CUDA(launch_tx_fec(q, n, 96, c->stream));
+    DNRP_LAUNCH(c, -1, launch_tx_fec(q, n, 96, c->stream));
     return DNRP_OK;
 }
 
@@ -192,13 +194,13 @@ int run_fec_decode_tb(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, boo
     p.rm_arena = c->d_rm_arena.p; p.xp_arena = c->d_xp_arena.p;
     p.min_it = c->cfg.tdec_min_iter; p.max_it = c->cfg.tdec_max_iter;
     p.crc_mode = 0; p.plcf_mask = nullptr;
-    DNRP_CUDA(launch_turbo_decode(p, n, f.tdec_threads, f.tdec_smem, c->stream));
+    DNRP_LAUNCH(c, DNRP_KERNEL_TURBO_DECODE_PDC, launch_turbo_decode(p, n, f.tdec_threads, f.tdec_smem, c->stream));
     tbfin_params_t t{};
     t.C = c->ps.C; t.tbs_bits = c->ps.N_TB_bits; t.chunk_bytes = f.tb_chunk_bytes;
     t.slot = p.slot; t.cb_crc = c->d_cb_crc.p;
     t.tb_out = c->d_tb_out.p; t.tb_stride = f.tb_stride;
     t.xp_tb = c->d_xp_tb.p; t.tb_ok = c->d_tb_ok.p;
-    DNRP_CUDA(launch_tb_finalize(t, n, c->stream));
+    DNRP_LAUNCH(c, -1, launch_tb_finalize(t, n, c->stream));
     return DNRP_OK;
 }
 
@@ -217,7 +219,7 @@ int run_fec_decode_plcf(dnrp_ctx* c, uint32_t n) {
     p.rm_arena = c->d_rm_arena.p; p.xp_arena = c->d_xp_arena.p;
     p.min_it = 1; p.max_it = 5;  // pcc_enc.cpp:39
     p.crc_mode = 1; p.plcf_mask = c->d_pcc_mask.p;
-    DNRP_CUDA(launch_turbo_decode(p, n, f.tdec_threads, f.tdec_smem, c->stream));
+    DNRP_LAUNCH(c, -1, launch_turbo_decode(p, n, f.tdec_threads, f.tdec_smem, c->stream));
     return DNRP_OK;
 }
 
@@ -299,6 +301,16 @@ extern "C" int dnrp_time_stage(dnrp_ctx_t* c, int stage, uint32_t n, uint32_t re
             case DNRP_STAGE_FEC_DECODE_TB: rc = run_fec_decode_tb(c, n, false, false, false); break;
             case DNRP_STAGE_FEC_ENCODE: rc = run_fec_encode(c, n, false, false); break;
             case DNRP_STAGE_FEC_DECODE_PLCF: rc = run_fec_decode_plcf(c, n); break;
+            case DNRP_STAGE_RX_CHAIN:
+                rc = run_rx_front(c, n);
+                if (rc == DNRP_OK) rc = run_rx_pcc(c, n);
+                if (rc == DNRP_OK) rc = run_rx_pdc(c, n, false, false, false);
+                break;
+            case DNRP_STAGE_TX_CHAIN:
+                rc = run_fec_encode(c, n, true, true);
+                if (rc == DNRP_OK) rc = run_tx_ofdm(c, n);
+                break;
+            case DNRP_STAGE_CHANNEL: rc = run_channel(c, n); break;
             default: set_last_error("unknown stage"); rc = DNRP_ERR_INVALID;
         }
     }
@@ -324,7 +336,7 @@ int run_tx_ofdm(dnrp_ctx* c, uint32_t n) {
     p.pdc_bits = c->d_pdc_bits.p; p.pdc_stride = c->fec.dbits_stride;
     p.meta = c->d_tx_meta.p;
     p.iq = c->d_iq_tx.p; p.iq_stride = c->tx_stride;
-    DNRP_CUDA(launch_tx_ofdm(p, n, c->stream));
+    DNRP_LAUNCH(c, -1, launch_tx_ofdm(p, n, c->stream));
     return DNRP_OK;
 }
 }  // namespace dnrp

@@ -31,22 +31,34 @@ rx_params_t make_rx_params(dnrp_ctx* c) {
 // the whole front end of all packets runs first (every later stage only reads its results).
 int run_rx_front(dnrp_ctx* c, uint32_t n) {
     const rx_params_t p = make_rx_params(c);
-    DNRP_CUDA(launch_rx_stf(p, n, c->stream));
-    DNRP_CUDA(launch_rx_fft(p, n, c->stream));
-    DNRP_CUDA(launch_rx_snr_class(p, n, c->stream));
+    DNRP_LAUNCH(c, DNRP_KERNEL_RX_STF, launch_rx_stf(p, n, c->stream));
+    DNRP_LAUNCH(c, DNRP_KERNEL_RX_FFT, launch_rx_fft(p, n, c->stream));
+    DNRP_LAUNCH(c, -1, launch_rx_snr_class(p, n, c->stream));
     return DNRP_OK;
 }
 
 int run_rx_pcc(dnrp_ctx* c, uint32_t n) {
     const rx_params_t p = make_rx_params(c);
-    DNRP_CUDA(launch_rx_demap(p, n, true, c->stream));
+    DNRP_LAUNCH(c, -1, launch_rx_demap(p, n, true, c->stream));
     return run_fec_decode_plcf(c, n);
 }
 
 int run_rx_pdc(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, bool have_reset) {
     const rx_params_t p = make_rx_params(c);
-    DNRP_CUDA(launch_rx_demap(p, n, false, c->stream));
+    DNRP_LAUNCH(c, DNRP_KERNEL_RX_DEMAP_PDC, launch_rx_demap(p, n, false, c->stream));
     return run_fec_decode_tb(c, n, have_slot, have_rv, have_reset);
+}
+
+int run_channel(dnrp_ctx* c, uint32_t n) {
+    const phy_dims_t& d = c->dims;
+    channel_params_t p{};
+    p.N_TX = d.N_TX; p.N_RX = d.N_RX;
+    p.tx = c->d_iq_tx.p; p.tx_stride = c->tx_stride;
+    p.rx = c->d_iq_rx.p; p.rx_stride = c->rx_stride;
+    p.n_samples = d.n_packet_os;
+    p.meta = c->d_chan_meta.p;
+    DNRP_LAUNCH(c, -1, launch_channel(p, n, c->stream));
+    return DNRP_OK;
 }
 
 }  // namespace dnrp
@@ -138,6 +150,7 @@ static bool tap_desc(const dnrp_ctx_t* c, int tap, uint32_t n, const void*& src,
         case DNRP_TAP_LLR_PCC: src = c->d_llr_pcc.p; bytes = (size_t)n * 196 * 2; return true;
         case DNRP_TAP_LLR_PDC: src = c->d_llr.p; bytes = (size_t)n * c->ps.G * 2; return true;
         case DNRP_TAP_WIENER_CLASS: src = c->d_cls.p; bytes = (size_t)n * c->cls_stride; return true;
+        case DNRP_TAP_TB_OK: src = c->d_tb_ok.p; bytes = n; return true;
         default: return false;
     }
 }
@@ -161,6 +174,61 @@ int dnrp_tap_read(dnrp_ctx_t* c, int tap, uint32_t n, void* dst, size_t dst_byte
     DNRP_CUDA(cudaStreamSynchronize(c->stream));
     return DNRP_OK;
 }
+
+int dnrp_channel_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_channel_desc_t* descs, dnrp_cf32_t* iq_rx_out) {
+    DNRP_REQUIRE(c && descs, "null argument");
+    DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    const phy_dims_t& d = c->dims;
+    std::vector<chan_meta_dev_t> meta(n);
+    for (uint32_t i = 0; i < n; ++i) {
+        DNRP_REQUIRE(descs[i].t0 + d.n_packet_os <= c->rx_stride, "offset exceeds the IQ window");
+        DNRP_REQUIRE(descs[i].mode <= 1, "unknown channel mode");
+        DNRP_REQUIRE(descs[i].net_bandwidth_norm > 0.f, "net_bandwidth_norm must be > 0");
+        const float n0_dBFS = -10.0f * log10f(descs[i].net_bandwidth_norm) - descs[i].snr_dB;  // noise.cpp:37-38
+        meta[i] = {descs[i].t0, descs[i].mode, powf(10.0f, n0_dBFS / 20.0f), (uint32_t)descs[i].seed,
+                   (uint32_t)(descs[i].seed >> 32)};
+    }
+    DNRP_CUDA(cudaMemcpyAsync(c->d_chan_meta.p, meta.data(), n * sizeof(chan_meta_dev_t), cudaMemcpyHostToDevice,
+                              c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));  // meta is a local pageable vector
+    int rc = run_channel(c, n);
+    if (rc) return rc;
+    if (iq_rx_out)
+        DNRP_CUDA(cudaMemcpyAsync(iq_rx_out, c->d_iq_rx.p, (size_t)n * d.N_RX * c->rx_stride * sizeof(float2),
+                                  cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    return DNRP_OK;
+}
+
+int dnrp_kernel_time_enable(dnrp_ctx_t* c, int enable) {
+    DNRP_REQUIRE(c, "null argument");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    c->ktime_on = enable != 0;
+    for (auto& t : c->ktimer) { t.used = 0; t.acc_ms = 0.f; t.count = 0; }
+    return DNRP_OK;
+}
+
+int dnrp_kernel_time_read(dnrp_ctx_t* c, int kernel, float* ms_total, uint32_t* launches) {
+    DNRP_REQUIRE(c && ms_total && launches, "null argument");
+    DNRP_REQUIRE(kernel >= 0 && kernel < DNRP_KERNEL_COUNT, "unknown kernel");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    auto& t = c->ktimer[kernel];
+    for (size_t i = 0; i + 1 < t.used; i += 2) {
+        float ms = 0.f;
+        DNRP_CUDA(cudaEventElapsedTime(&ms, t.ev[i], t.ev[i + 1]));
+        t.acc_ms += ms;
+        ++t.count;
+    }
+    t.used = 0;
+    *ms_total = t.acc_ms;
+    *launches = t.count;
+    return DNRP_OK;
+}
+
+uint64_t dnrp_launch_count(const dnrp_ctx_t* c) { return c ? c->launches : 0; }
 
 int dnrp_loopback_tx_to_rx(dnrp_ctx_t* c, uint32_t n, uint32_t t0) {
     DNRP_REQUIRE(c, "null argument");

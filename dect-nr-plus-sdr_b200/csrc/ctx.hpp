@@ -74,6 +74,13 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f);
 
 }  // namespace dnrp
 
+// one kernel launch: counted, and timed with events when dnrp_kernel_time_enable is on (k < 0: untimed)
+#define DNRP_LAUNCH(c, k, expr)          \
+    do {                                 \
+        ::dnrp::kscope ks__((c), (k));   \
+        DNRP_CUDA(expr);                 \
+    } while (0)
+
 struct dnrp_ctx {
     dnrp_config_t cfg;
     dnrp::spec::packet_sizes_t ps;
@@ -118,7 +125,44 @@ struct dnrp_ctx {
     dnrp::dbuf<dnrp::rx_state_t> d_rx_state;
     dnrp::dbuf<uint8_t> d_cls;
     std::vector<dnrp::rx_state_t> h_rx_state;
+    dnrp::dbuf<dnrp::chan_meta_dev_t> d_chan_meta;
+
+    // measurement: launch counter and optional per-kernel event timers (dnrp_kernel_time_*)
+    uint64_t launches = 0;
+    bool ktime_on = false;
+    struct ktimer_t {
+        std::vector<cudaEvent_t> ev;  // start/stop pairs
+        size_t used = 0;
+        float acc_ms = 0.f;
+        uint32_t count = 0;
+    } ktimer[DNRP_KERNEL_COUNT];
 };
+
+namespace dnrp {
+// brackets one kernel launch with events when timing is enabled; always counts the launch
+struct kscope {
+    dnrp_ctx* c;
+    int k;
+    cudaEvent_t stop = nullptr;
+    kscope(dnrp_ctx* c_, int k_) : c(c_), k(k_) {
+        ++c->launches;
+        if (!c->ktime_on || k < 0) return;
+        auto& t = c->ktimer[k];
+        if (t.used + 2 > t.ev.size()) {
+            cudaEvent_t a, b;
+            if (cudaEventCreate(&a) != cudaSuccess || cudaEventCreate(&b) != cudaSuccess) return;
+            t.ev.push_back(a);
+            t.ev.push_back(b);
+        }
+        cudaEventRecord(t.ev[t.used], c->stream);
+        stop = t.ev[t.used + 1];
+        t.used += 2;
+    }
+    ~kscope() {
+        if (stop) cudaEventRecord(stop, c->stream);
+    }
+};
+}  // namespace dnrp
 
 namespace dnrp {
 int build_phy_plan(dnrp_ctx* c);
@@ -130,4 +174,5 @@ dnrp::rx_params_t make_rx_params(dnrp_ctx* c);
 int run_rx_front(dnrp_ctx* c, uint32_t n);             // STF stage, FFTs, DRS zero forcing, SNR classes
 int run_rx_pcc(dnrp_ctx* c, uint32_t n);               // PCC demap + blind PLCF decode
 int run_rx_pdc(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, bool have_reset);
+int run_channel(dnrp_ctx* c, uint32_t n);
 }  // namespace dnrp

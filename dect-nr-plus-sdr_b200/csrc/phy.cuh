@@ -98,4 +98,20 @@ struct txofdm_params_t {
 
 cudaError_t launch_tx_ofdm(const txofdm_params_t& p, uint32_t n_packets, cudaStream_t st);
 
+// simulation channel (phy_channel.cu)
+struct chan_meta_dev_t {
+    uint32_t t0;        // first sample of the packet inside the RX window
+    uint32_t mode;      // 0 = awgn (unit links), 1 = flat (one CN(0,1) coefficient per link and packet)
+    float sigma;        // standard deviation of the complex noise sample, sqrt(10^(n0_dBFS / 10))
+    uint32_t seed_lo, seed_hi;
+};
+struct channel_params_t {
+    uint32_t N_TX, N_RX;
+    const float2* tx;  size_t tx_stride;   // [packet][N_TX][tx_stride]
+    float2* rx;        size_t rx_stride;   // [packet][N_RX][rx_stride]
+    uint32_t n_samples;                    // TX samples superimposed (rest of the window is noise only)
+    const chan_meta_dev_t* meta;           // [packet]
+};
+cudaError_t launch_channel(const channel_params_t& p, uint32_t n_packets, cudaStream_t st);
+
 }  // namespace dnrp

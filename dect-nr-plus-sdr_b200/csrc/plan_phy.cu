@@ -120,6 +120,7 @@ int build_phy_plan(dnrp_ctx* c) {
     UP(c->d_snr_part.alloc(B * d.N_DF * d.N_RX));
     UP(c->d_rx_state.alloc(B));
     UP(c->d_cls.alloc(B * c->cls_stride));
+    UP(c->d_chan_meta.alloc(B));
     c->h_rx_state.resize(B);
 #undef UP
     if (!ok) {

@@ -172,7 +172,8 @@ typedef enum {
     DNRP_TAP_STF_ZF = 3,   /* cf32 [n][N_RX][N_b_OCC/4] */
     DNRP_TAP_LLR_PCC = 4,  /* int16 [n][196] */
     DNRP_TAP_LLR_PDC = 5,  /* int16 [n][G] */
-    DNRP_TAP_WIENER_CLASS = 6 /* uint8 [n][dnrp_tap_bytes/n] class after each DRS symbol */
+    DNRP_TAP_WIENER_CLASS = 6, /* uint8 [n][dnrp_tap_bytes/n] class after each DRS symbol */
+    DNRP_TAP_TB_OK = 7         /* uint8 [n] transport block CRC flags of the last PDC decode */
 } dnrp_tap_t;
 size_t dnrp_tap_bytes(const dnrp_ctx_t* ctx, int tap, uint32_t n);
 int dnrp_tap_read(dnrp_ctx_t* ctx, int tap, uint32_t n, void* dst, size_t dst_bytes);
@@ -182,6 +183,27 @@ int dnrp_tap_read(dnrp_ctx_t* ctx, int tap, uint32_t n, void* dst, size_t dst_by
  * simulator with an ideal channel" of the reference's loopback firmware. */
 int dnrp_loopback_tx_to_rx(dnrp_ctx_t* ctx, uint32_t n, uint32_t t0);
 
+/* ---- simulation channel ------------------------------------------------------------------------
+ * One packet's wireless channel + receiver noise, the per-packet equivalent of
+ * vspace_t::wchannel_get_samples (lib/src/simulation/vspace.cpp:437-512) for one TX and one RX node:
+ * every TX antenna is superimposed on every RX antenna (mode 0 "awgn": unit links,
+ * channel_awgn.cpp:39-64; mode 1 "flat": one CN(0,1) coefficient per link, redrawn per packet,
+ * channel_flat.cpp:47-88), delayed by t0 samples into the RX window, then white noise of absolute level
+ * n0_dBFS = -10 log10(net_bandwidth_norm) - snr_dB is added over the whole window (noise.cpp:31-41).
+ * Noise and coefficients come from Philox4x32-10 keyed by `seed` (the reference uses srsRAN's
+ * generator: realisations differ, statistics do not). */
+typedef struct {
+    float snr_dB;
+    float net_bandwidth_norm;   /* 1 / oversampling in the reference's simulator */
+    uint32_t t0;
+    uint32_t mode;              /* 0 awgn, 1 flat */
+    uint64_t seed;
+} dnrp_channel_desc_t;
+
+/* reads the n packets left on the device by dnrp_tx_batch, writes the receiver's IQ windows (device);
+ * iq_rx_out [n][N_RX][dnrp_rx_stride()] receives a host copy unless NULL */
+int dnrp_channel_batch(dnrp_ctx_t* ctx, uint32_t n, const dnrp_channel_desc_t* descs, dnrp_cf32_t* iq_rx_out);
+
 /* ---- measurement hook ------------------------------------------------------------------------
  * Re-runs one device stage `reps` times on the data already resident in the context (left there by
  * the previous host-facing call) and returns the average CUDA-event time per repetition in ms,
@@ -189,9 +211,27 @@ int dnrp_loopback_tx_to_rx(dnrp_ctx_t* ctx, uint32_t n, uint32_t t0);
 typedef enum {
     DNRP_STAGE_FEC_DECODE_TB = 1,
     DNRP_STAGE_FEC_ENCODE = 2,
-    DNRP_STAGE_FEC_DECODE_PLCF = 3
+    DNRP_STAGE_FEC_DECODE_PLCF = 3,
+    DNRP_STAGE_RX_CHAIN = 4,   /* rx front end + PCC + PDC on the resident IQ windows and sync reports */
+    DNRP_STAGE_TX_CHAIN = 5,   /* FEC encode + OFDM on the resident TB / PLCF / descriptors */
+    DNRP_STAGE_CHANNEL = 6     /* channel on the resident TX IQ and descriptors */
 } dnrp_stage_t;
 int dnrp_time_stage(dnrp_ctx_t* ctx, int stage, uint32_t n, uint32_t reps, float* ms_per_rep);
+
+/* Per-kernel device time inside the stages above: while enabled, every launch of the named kernel is
+ * bracketed by CUDA events on the context's stream; dnrp_kernel_time_read synchronises and returns the
+ * accumulated milliseconds and the launch count since the last reset. */
+typedef enum {
+    DNRP_KERNEL_TURBO_DECODE_PDC = 0,
+    DNRP_KERNEL_RX_FFT = 1,
+    DNRP_KERNEL_RX_DEMAP_PDC = 2,
+    DNRP_KERNEL_RX_STF = 3,
+    DNRP_KERNEL_COUNT = 4
+} dnrp_kernel_t;
+int dnrp_kernel_time_enable(dnrp_ctx_t* ctx, int enable);
+int dnrp_kernel_time_read(dnrp_ctx_t* ctx, int kernel, float* ms_total, uint32_t* launches);
+/* number of kernel launches issued on the context's stream since creation (all kernels of this library) */
+uint64_t dnrp_launch_count(const dnrp_ctx_t* ctx);
 
 #ifdef __cplusplus
 }

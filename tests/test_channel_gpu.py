@@ -1,0 +1,58 @@
+"""GPU parity of the simulation channel (dnrp_channel_batch) against oracle/channel.c, plus the statistics
+the reference's channel guarantees (noise power = 10^(n0_dBFS/10), unit-power flat coefficients).
+Tolerance: same Philox stream on both sides, so samples agree to fp32 rounding of logf/sincos:
+max |diff| <= 2e-5 * (sigma + max|x|)."""
+import numpy as np
+import pytest
+
+from oracle import channel as ochan, spec
+from conftest import CONFIGS
+
+pytestmark = pytest.mark.gpu
+NET = 123456789
+
+
+@pytest.mark.parametrize("name,N_RX,mode,snr", [("C1_loopback", 1, 0, 20.0), ("txdiv2_b4_mcs3", 2, 1, 7.0),
+                                                 ("C3_b16_txdiv4_mcs7", 4, 1, 25.0)])
+def test_channel_matches_oracle(product, name, N_RX, mode, snr):
+    cfg = CONFIGS[name]
+    ps = spec.get_packet_sizes(*cfg)
+    n = 3
+    phy = product.Phy(cfg, max_batch=n, N_RX=N_RX, network_id=NET)
+    rng = np.random.default_rng(3)
+    tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
+    plcf = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    iq_tx, ns = phy.tx(plcf, tb)
+    t0 = np.array([0, 7, 33])
+    seed = 0x1234567811223344
+    rx = phy.channel(n, snr_dB=snr, t0=t0, mode=mode, seed=seed, fetch=True)
+    sigma = 10 ** (-snr / 20)
+    for i in range(n):
+        ref = ochan.channel(iq_tx[i], phy.rx_stride(), N_RX, t0=int(t0[i]), mode=mode, snr_dB=snr, seed=seed, pkt=i,
+                            n_samples=ps["N_samples_packet"])
+        tol = 2e-5 * (sigma + np.abs(iq_tx[i]).max() * ps["N_TX"])
+        assert np.abs(rx[i] - ref).max() <= tol, (name, i, float(np.abs(rx[i] - ref).max()), tol)
+    phy.close()
+
+
+def test_channel_statistics(product):
+    """noise only windows: E|n|^2 = 10^(-snr/10) / net_bandwidth_norm; flat coefficients: E|g|^2 = 1"""
+    cfg = CONFIGS["C1_loopback"]
+    ps = spec.get_packet_sizes(*cfg)
+    n = 512
+    phy = product.Phy(cfg, max_batch=n, N_RX=2, network_id=NET, oversampling=2)
+    tb = np.zeros((n, ps["N_TB_byte"]), dtype=np.uint8)
+    plcf = np.zeros((n, 10), dtype=np.uint8)
+    iq_tx, ns = phy.tx(plcf, tb, fetch=True)
+    rx = phy.channel(n, snr_dB=10.0, t0=0, mode=1, seed=99, fetch=True)
+    tail = rx[:, :, ps["N_samples_packet"] * 2 + 8:]          # behind the packet: noise only
+    p_noise = float(np.mean(np.abs(tail) ** 2))
+    assert abs(p_noise / (10 ** -1.0 * 2) - 1.0) < 0.01, p_noise
+    assert abs(float(np.mean(tail.real * tail.imag))) < 2e-3 * p_noise * 50
+    # link coefficients from the noise free part: y = g x + n  ->  g ~ <y, x> / <x, x>
+    L = ps["N_samples_packet_no_GI"] * 2
+    x = iq_tx[:, 0, :L]
+    g = np.einsum("pal,pl->pa", rx[:, :, :L], np.conj(x)) / np.einsum("pl,pl->p", x, np.conj(x))[:, None]
+    assert abs(float(np.mean(np.abs(g) ** 2)) - 1.0) < 0.12
+    assert abs(np.mean(g)) < 0.12
+    phy.close()
