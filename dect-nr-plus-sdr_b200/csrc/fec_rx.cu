@@ -63,24 +63,51 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
 
     // ---- prologue: soft[n] (+)= sum of the descrambled LLRs that rate matching mapped onto n
     // (srsran_scrambling_s_offset + srsran_rm_turbo_rx_lut_, pdc_enc.cpp:339-363); plain int16 wrap
-    for (uint32_t n = tid; n < N; n += nthr) {
-        int acc = reset ? 0 : soft[n];
-        uint32_t e = rm_pos[n] + N - rm_start;
-        if (e >= N) e -= N;
-        for (; e < cb.n_e; e += N) {
-            const uint32_t g = cb.rp + e + p.gold_bit_off;
-            const int v = llr[e];
-            acc += ((p.gold[g >> 3] >> (7 - (g & 7))) & 1) ? -v : v;
+    // Four independent elements per thread and trip so that the dependent global loads (table -> LLR /
+    // scrambling bit) of different elements overlap; the block only has a few warps to hide them.
+    for (uint32_t n0 = tid; n0 < N; n0 += 4 * nthr) {
+        uint32_t e[4];
+        int acc[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t n = n0 + u * nthr;
+            e[u] = 0xffffffffu;
+            acc[u] = 0;
+            if (n < N) {
+                uint32_t v = rm_pos[n] + N - rm_start;
+                e[u] = v >= N ? v - N : v;
+                if (!reset) acc[u] = soft[n];
+            }
         }
-        const int16_t v16 = (int16_t)acc;
-        soft[n] = v16;
-        if (n < K) {
-            const uint32_t pw = n >= KH ? n - KH : n;
-            ((int16_t*)SYS)[2 * ((pw % L) * T + pw / L) + (n >= KH)] = (int16_t)clampi(v16, 1023);
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            for (uint32_t ee = e[u]; ee < cb.n_e; ee += N) {
+                const uint32_t g = cb.rp + ee + p.gold_bit_off;
+                const int v = llr[ee];
+                acc[u] += ((p.gold[g >> 3] >> (7 - (g & 7))) & 1) ? -v : v;
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t n = n0 + u * nthr;
+            if (n < N) soft[n] = (int16_t)acc[u];
         }
     }
     for (uint32_t i = tid; i < KH; i += nthr) EXT[i] = 0;
     for (uint32_t i = tid; i < 4 * 7 * T; i += nthr) AE[i] = 0;  // AE and BS are contiguous
+    __syncthreads();  // soft[] of this code block is complete (block-wide visibility of the global stores)
+
+    // stage one K-long stream (systematic or a parity) into a window-transposed packed shared array:
+    // word (k, t) = (element t*L + k, element KH + t*L + k), both clamped to the channel range
+    auto stage = [&](uint32_t* dst, const int16_t* src) {
+#pragma unroll 4
+        for (uint32_t i = tid; i < KH; i += nthr) {
+            const int lo = clampi(src[i], 1023), hi = clampi(src[i + KH], 1023);
+            const uint32_t q = __umulhi(i, cb.Linv), r = i - q * L;
+            dst[r * T + q] = pack(lo, hi);
+        }
+    };
+    stage(SYS, soft);
     __syncthreads();
 
     const bool active = tid < T;
@@ -93,11 +120,7 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
     for (uint32_t it = 0; it < p.max_it && !crc_ok; ++it) {
         for (uint32_t dec = 0; dec < 2; ++dec) {
             // ---- parity of this constituent decoder -> shared, window-transposed
-            const int16_t* par = soft + (1 + dec) * D;
-            for (uint32_t i = tid; i < K; i += nthr) {
-                const uint32_t pw = i >= KH ? i - KH : i;
-                ((int16_t*)PAR)[2 * ((pw % L) * T + pw / L) + (i >= KH)] = (int16_t)clampi(par[i], 1023);
-            }
+            stage(PAR, soft + (1 + dec) * D);
             // ---- decoder input x = systematic + a-priori, in decoder order
             if (dec == 0) {
                 for (uint32_t i = tid; i < KH; i += nthr) XIN[i] = vadd(SYS[i], EXT[i]);
@@ -109,7 +132,8 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
                 for (uint32_t k = 0; k < L; ++k) {
                     const bool up = pi >= KH;
                     const uint32_t pw = up ? pi - KH : pi;
-                    const uint32_t a = (pw % L) * T + pw / L;
+                    const uint32_t q = __umulhi(pw, cb.Linv);
+                    const uint32_t a = (pw - q * L) * T + q;
                     uint32_t w = vadd(SYS[a], EXT[a]);
                     if (up) w = swap16(w);
                     XIN[k * T + t] = w;
@@ -154,60 +178,64 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
                     return (int)(int16_t)(v >= T ? (w >> 16) : (w & 0xffff));
                 };
 
-                // ---- beta: training over window w+1 (both halves), then the real backward pass
-                uint32_t b[8];
+                // ---- training passes: beta over window w+1 and alpha over window w-1 are independent
+                // recursions, run in one loop (two dependency chains in flight) with the next step's
+                // shared-memory words prefetched one iteration ahead
+                uint32_t b[8], a[8];
 #pragma unroll
                 for (int s = 0; s < 8; ++s) {
                     const int lo = (wl + 2 >= P) ? tail[s] : fetch(BSd, s, wl + 2);
                     const int hi = (wh + 2 >= P) ? tail[s] : fetch(BSd, s, wh + 2);
                     b[s] = pack(lo, hi);
+                    const int ex = s == 0 ? 0 : -8192;
+                    const int alo = (wl <= 1) ? ex : fetch(AEd, s, wl - 2);
+                    const int ahi = (wh <= 1) ? ex : fetch(AEd, s, wh - 2);
+                    a[s] = pack(alo, ahi);
                 }
                 {
-                    const uint32_t tn = (t + 1 == T) ? 0 : t + 1;
-                    const bool wrap = (t + 1 == T);
-                    for (int k = (int)L - 1; k >= 0; --k) {
-                        uint32_t x = XIN[k * T + tn], y = PAR[k * T + tn];
-                        if (wrap) { x >>= 16; y >>= 16; }
-                        beta_step(b, x, y);
+                    const bool wrapn = (t + 1 == T), wrapp = (t == 0);
+                    const uint32_t* Xn = XIN + (wrapn ? 0 : t + 1);
+                    const uint32_t* Yn = PAR + (wrapn ? 0 : t + 1);
+                    const uint32_t* Xp = XIN + (wrapp ? T - 1 : t - 1);
+                    const uint32_t* Yp = PAR + (wrapp ? T - 1 : t - 1);
+                    const uint32_t shn = wrapn ? 16 : 0, shp = wrapp ? 16 : 0;
+                    uint32_t xb = Xn[(L - 1) * T], yb = Yn[(L - 1) * T], xa = Xp[0], ya = Yp[0];
+                    for (uint32_t i = 0; i < L; ++i) {
+                        const uint32_t in = i + 1 < L ? i + 1 : i;  // last iteration: harmless reload
+                        const uint32_t xb_n = Xn[(L - 1 - in) * T], yb_n = Yn[(L - 1 - in) * T];
+                        const uint32_t xa_n = Xp[in * T], ya_n = Yp[in * T];
+                        beta_step(b, xb >> shn, yb >> shn);
+                        alpha_step(a, xa << shp, ya << shp);
+                        xb = xb_n; yb = yb_n; xa = xa_n; ya = ya_n;
                     }
                     if (wh == P - 1) {
 #pragma unroll
                         for (int s = 0; s < 8; ++s) b[s] = (b[s] & 0xffffu) | ((uint32_t)tail[s] << 16);
-                    }
-                }
-                for (int k = (int)L - 1; k >= 0; --k) {
-                    if (((k + 1) % S_CK) == 0 || k + 1 == (int)L) {
-                        const int c = k / S_CK;
-#pragma unroll
-                        for (int s = 1; s < 8; ++s) CK[(c * 7 + s - 1) * T + t] = b[s];
-                    }
-                    beta_step(b, XIN[k * T + t], PAR[k * T + t]);
-                }
-#pragma unroll
-                for (int s = 0; s < 8; ++s) bs_new[s] = b[s];
-
-                // ---- alpha: training over window w-1, then forward pass with LLR output
-                uint32_t a[8];
-#pragma unroll
-                for (int s = 0; s < 8; ++s) {
-                    const int ex = s == 0 ? 0 : -8192;
-                    const int lo = (wl <= 1) ? ex : fetch(AEd, s, wl - 2);
-                    const int hi = (wh <= 1) ? ex : fetch(AEd, s, wh - 2);
-                    a[s] = pack(lo, hi);
-                }
-                {
-                    const uint32_t tp = (t == 0) ? T - 1 : t - 1;
-                    const bool wrap = (t == 0);
-                    for (uint32_t k = 0; k < L; ++k) {
-                        uint32_t x = XIN[k * T + tp], y = PAR[k * T + tp];
-                        if (wrap) { x <<= 16; y <<= 16; }
-                        alpha_step(a, x, y);
                     }
                     if (wl == 0) {
 #pragma unroll
                         for (int s = 0; s < 8; ++s) a[s] = (a[s] & 0xffff0000u) | (s == 0 ? 0u : 0xE000u);
                     }
                 }
+                // ---- backward pass over the own windows, checkpoint every S_CK steps
+                {
+                    const uint32_t* X = XIN + t;
+                    const uint32_t* Y = PAR + t;
+                    uint32_t x = X[(L - 1) * T], y = Y[(L - 1) * T];
+                    for (int k = (int)L - 1; k >= 0; --k) {
+                        const int kn = k > 0 ? k - 1 : 0;
+                        const uint32_t x_n = X[kn * T], y_n = Y[kn * T];
+                        if (((k + 1) % S_CK) == 0 || k + 1 == (int)L) {
+                            const int c = k / S_CK;
+#pragma unroll
+                            for (int s = 1; s < 8; ++s) CK[(c * 7 + s - 1) * T + t] = b[s];
+                        }
+                        beta_step(b, x, y);
+                        x = x_n; y = y_n;
+                    }
+                }
+#pragma unroll
+                for (int s = 0; s < 8; ++s) bs_new[s] = b[s];
                 // QPP position of the first step of this thread (decoder 2 scatters to natural order)
                 const uint32_t j0 = t * L;
                 uint32_t pi = (uint32_t)(((uint64_t)cb.f1 * j0 + (uint64_t)cb.f2 * j0 * j0) % K);
@@ -216,9 +244,14 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
                 for (uint32_t c = 0; c < nck; ++c) {
                     const int k0 = c * S_CK;
                     const int n = min((int)S_CK, (int)L - k0);
-                    uint32_t bb[S_CK][8];
+                    uint32_t bb[S_CK][8], xs[S_CK], ys[S_CK];
 #pragma unroll
-                    for (int i = 0; i < S_CK; ++i) bb[i][0] = 0;
+                    for (int i = 0; i < S_CK; ++i) {
+                        bb[i][0] = 0;
+                        const int ki = k0 + (i < n ? i : 0);  // the chunk's inputs, loaded once
+                        xs[i] = XIN[ki * T + t];
+                        ys[i] = PAR[ki * T + t];
+                    }
                     // beta at time k0+n from the checkpoint, then recompute down to k0+1
 #pragma unroll
                     for (int i = S_CK - 1; i >= 0; --i) {
@@ -228,14 +261,15 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
                         } else if (i < n - 1) {
 #pragma unroll
                             for (int s = 0; s < 8; ++s) bb[i][s] = bb[i + 1][s];
-                            beta_step(bb[i], XIN[(k0 + i + 1) * T + t], PAR[(k0 + i + 1) * T + t]);
+                            constexpr int S1 = S_CK - 1;
+                            beta_step(bb[i], xs[i < S1 ? i + 1 : S1], ys[i < S1 ? i + 1 : S1]);
                         }
                     }
 #pragma unroll
                     for (int i = 0; i < S_CK; ++i) {
                         if (i < n) {
                             const uint32_t k = k0 + i;
-                            const uint32_t x = XIN[k * T + t], y = PAR[k * T + t];
+                            const uint32_t x = xs[i], y = ys[i];
                             const uint32_t l = llr_step(a, bb[i], x, y);
                             const uint32_t e = vclamp(vadd(l, vneg(x)), 2047);
                             if (dec == 0) {
@@ -243,7 +277,8 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
                             } else {
                                 const bool up = pi >= KH;
                                 const uint32_t pw = up ? pi - KH : pi;
-                                const uint32_t ad = (pw % L) * T + pw / L;
+                                const uint32_t q = __umulhi(pw, cb.Linv);
+                                const uint32_t ad = (pw - q * L) * T + q;
                                 const uint32_t hb = ((int16_t)(l & 0xffff) > 0 ? 1u : 0u) | ((int16_t)(l >> 16) > 0 ? 2u : 0u);
                                 EXT[ad] = up ? swap16(e) : e;
                                 HARD[ad] = (uint8_t)(up ? ((hb >> 1) | ((hb & 1) << 1)) : hb);
@@ -306,7 +341,8 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
         for (uint32_t q = 0; q < 8; ++q) {
             const uint32_t pos = bi * 8 + q;
             const uint32_t pw = pos >= KH ? pos - KH : pos;
-            const uint32_t hb = HARD[(pw % L) * T + pw / L];
+            const uint32_t qq = __umulhi(pw, cb.Linv);
+            const uint32_t hb = HARD[(pw - qq * L) * T + qq];
             v = (v << 1) | (pos >= KH ? (hb >> 1) : (hb & 1));
         }
         if (bi < cb.rlen_byte) {

@@ -107,6 +107,7 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         // decoder (pdc_enc.cpp:322-337)
         cb_desc_t r{};
         r.K = K; r.L = L; r.P = K / L; r.f1 = f1; r.f2 = f2;
+        r.Linv = (uint32_t)(((1ull << 32) + L - 1) / L);
         const uint32_t n_e = Qm * (Gp / s.C);
         r.rp = cb * n_e;
         r.n_e = n_e;
@@ -164,6 +165,7 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         f.tx_pcc[ty] = t;
         cb_desc_t r{};
         r.K = K; r.L = L; r.P = K / L; r.f1 = f1; r.f2 = f2;
+        r.Linv = (uint32_t)(((1ull << 32) + L - 1) / L);
         r.rp = 0; r.n_e = spec::PCC_BITS;
         r.out_byte = ty * 16;      // plcf_out [packet][2][16]
         r.rlen_byte = nb / 8;

@@ -34,6 +34,7 @@ struct cb_desc_t {
     uint32_t crc_poly, crc_order;  // check polynomial of this CB (24B, 24A when C == 1, 16 for PLCF)
     uint32_t xp_off;           // offset of the per-window x^n mod g table in the table arena
     uint32_t saved_off;        // byte offset inside the packet's saved-bytes area
+    uint32_t Linv;             // ceil(2^32 / L): i / L == __umulhi(i, Linv) for every i < 2^32 / L
 };
 
 namespace tdec {
@@ -42,7 +43,8 @@ static constexpr int S_CK = 8;             // checkpoint distance
 static constexpr uint32_t NEG2 = 0xE000E000u;  // (-8192, -8192)
 
 __device__ __forceinline__ uint32_t vadd(uint32_t a, uint32_t b) { return __vadd2(a, b); }
-__device__ __forceinline__ uint32_t vneg(uint32_t a) { return __vadd2(~a, 0x00010001u); }
+__device__ __forceinline__ uint32_t vsub(uint32_t a, uint32_t b) { return __vsub2(a, b); }
+__device__ __forceinline__ uint32_t vneg(uint32_t a) { return __vsub2(0u, a); }
 __device__ __forceinline__ uint32_t vmax(uint32_t a, uint32_t b) { return __vmaxs2(a, b); }
 __device__ __forceinline__ uint32_t vmin(uint32_t a, uint32_t b) { return __vmins2(a, b); }
 __device__ __forceinline__ uint32_t vaddmax(uint32_t a, uint32_t b, uint32_t c) { return __viaddmax_s16x2(a, b, c); }
@@ -66,10 +68,9 @@ __device__ __forceinline__ void beta_step(uint32_t (&b)[8], uint32_t x, uint32_t
     n[5] = vaddmax(b[6], y, vadd(b[2], x));      // u0->S6 (y) | u1->S2 (x)
     n[6] = vaddmax(b[3], xy, b[7]);              // u0->S7 (0) | u1->S3 (x+y)
     n[7] = vaddmax(b[7], xy, b[3]);              // u0->S3 (0) | u1->S7 (x+y)
-    const uint32_t m = vneg(n[0]);
     b[0] = 0;
 #pragma unroll
-    for (int s = 1; s < 8; ++s) b[s] = vadd(n[s], m);
+    for (int s = 1; s < 8; ++s) b[s] = vsub(n[s], n[0]);
 }
 
 // one forward step: a[] <- alpha at the next trellis time, normalised to state 0
@@ -84,10 +85,9 @@ __device__ __forceinline__ void alpha_step(uint32_t (&a)[8], uint32_t x, uint32_
     n[6] = vaddmax(a[5], y, vadd(a[4], x));
     n[7] = vaddmax(a[7], xy, a[6]);
     n[3] = vaddmax(a[6], xy, a[7]);
-    const uint32_t m = vneg(n[0]);
     a[0] = 0;
 #pragma unroll
-    for (int s = 1; s < 8; ++s) a[s] = vadd(n[s], m);
+    for (int s = 1; s < 8; ++s) a[s] = vsub(n[s], n[0]);
 }
 
 // a-posteriori LLR of the step with alpha a[] (before), beta bn[] (after)
