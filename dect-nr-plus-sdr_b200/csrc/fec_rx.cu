@@ -46,8 +46,9 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
         return;
     }
 
-    uint32_t* SYS = smem;
-    uint32_t* EXT = SYS + KH;
+    // the systematic stream stays in the (L2 resident) soft buffer and is re-read once per half
+    // iteration: one K/2-word array less per block = one more resident block per SM
+    uint32_t* EXT = smem;
     uint32_t* XIN = EXT + KH;
     uint32_t* PAR = XIN + KH;
     uint32_t* CK = PAR + KH;                 // [nck][7][T]
@@ -99,16 +100,17 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
 
     // stage one K-long stream (systematic or a parity) into a window-transposed packed shared array:
     // word (k, t) = (element t*L + k, element KH + t*L + k), both clamped to the channel range
-    auto stage = [&](uint32_t* dst, const int16_t* src) {
+    // (add_ext: decoder 1's input, systematic + a-priori, which shares the natural order)
+    auto stage = [&](uint32_t* dst, const int16_t* src, bool add_ext) {
 #pragma unroll 4
         for (uint32_t i = tid; i < KH; i += nthr) {
             const int lo = clampi(src[i], 1023), hi = clampi(src[i + KH], 1023);
-            const uint32_t q = __umulhi(i, cb.Linv), r = i - q * L;
-            dst[r * T + q] = pack(lo, hi);
+            const uint32_t q = __umulhi(i, cb.Linv), a = (i - q * L) * T + q;
+            uint32_t w = pack(lo, hi);
+            if (add_ext) w = vadd(w, EXT[a]);
+            dst[a] = w;
         }
     };
-    stage(SYS, soft);
-    __syncthreads();
 
     const bool active = tid < T;
     const uint32_t t = tid;
@@ -120,21 +122,22 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
     for (uint32_t it = 0; it < p.max_it && !crc_ok; ++it) {
         for (uint32_t dec = 0; dec < 2; ++dec) {
             // ---- parity of this constituent decoder -> shared, window-transposed
-            stage(PAR, soft + (1 + dec) * D);
+            stage(PAR, soft + (1 + dec) * D, false);
             // ---- decoder input x = systematic + a-priori, in decoder order
             if (dec == 0) {
-                for (uint32_t i = tid; i < KH; i += nthr) XIN[i] = vadd(SYS[i], EXT[i]);
+                stage(XIN, soft, true);
             } else if (active) {
                 const uint32_t j0 = t * L;
                 uint32_t pi = (uint32_t)(((uint64_t)cb.f1 * j0 + (uint64_t)cb.f2 * j0 * j0) % K);
                 uint32_t g = (uint32_t)((cb.f1 + (uint64_t)cb.f2 * (2 * j0 + 1)) % K);
                 const uint32_t g2 = (2 * cb.f2) % K;
+#pragma unroll 4
                 for (uint32_t k = 0; k < L; ++k) {
                     const bool up = pi >= KH;
                     const uint32_t pw = up ? pi - KH : pi;
                     const uint32_t q = __umulhi(pw, cb.Linv);
                     const uint32_t a = (pw - q * L) * T + q;
-                    uint32_t w = vadd(SYS[a], EXT[a]);
+                    uint32_t w = vadd(pack(clampi(soft[pw], 1023), clampi(soft[pw + KH], 1023)), EXT[a]);
                     if (up) w = swap16(w);
                     XIN[k * T + t] = w;
                     pi += g; if (pi >= K) pi -= K;
@@ -402,7 +405,7 @@ __global__ void __launch_bounds__(256) k_tb_finalize(const tbfin_params_t p) {
 
 size_t tdec_smem_bytes(uint32_t K, uint32_t L) {
     const uint32_t T = K / L / 2, nck = (L + tdec::S_CK - 1) / tdec::S_CK;
-    return (size_t)4 * (4 * (K / 2) + nck * 7 * T + 4 * 7 * T) + K / 2 + 16;
+    return (size_t)4 * (3 * (K / 2) + nck * 7 * T + 4 * 7 * T) + K / 2 + 16;
 }
 
 cudaError_t launch_turbo_decode(const tdec_params_t& p, uint32_t n_packets, uint32_t threads, size_t smem,
