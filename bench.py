@@ -222,7 +222,8 @@ def run_b200(args):
     k_ms, k_cnt = phy.kernel_time_read(product.KERNEL_TURBO_DECODE_PDC)
     others = {name: phy.kernel_time_read(k) for name, k in (("k_rx_fft", product.KERNEL_RX_FFT),
                                                             ("k_rx_demap_pdc", product.KERNEL_RX_DEMAP_PDC),
-                                                            ("k_rx_stf", product.KERNEL_RX_STF))}
+                                                            ("k_rx_stf", product.KERNEL_RX_STF),
+                                                            ("k_derm_pdc", product.KERNEL_DERM_PDC))}
     phy.kernel_time_enable(False)
     ok_res = phy.tap(product.TAP_TB_OK, P).reshape(-1).astype(bool)
     n_ok_res = int(ok_res.sum())

@@ -89,7 +89,7 @@ CHANNEL_DTYPE = np.dtype([("snr_dB", "f4"), ("net_bandwidth_norm", "f4"), ("t0",
                           ("seed", "u8")], align=True)
 assert CHANNEL_DTYPE.itemsize == C.sizeof(ChannelDesc)
 TAP_Y, TAP_DRS_ZF, TAP_STF_ZF, TAP_LLR_PCC, TAP_LLR_PDC, TAP_WIENER_CLASS, TAP_TB_OK = 1, 2, 3, 4, 5, 6, 7
-KERNEL_TURBO_DECODE_PDC, KERNEL_RX_FFT, KERNEL_RX_DEMAP_PDC, KERNEL_RX_STF = 0, 1, 2, 3
+KERNEL_TURBO_DECODE_PDC, KERNEL_RX_FFT, KERNEL_RX_DEMAP_PDC, KERNEL_RX_STF, KERNEL_DERM_PDC = 0, 1, 2, 3, 4
 
 
 def build(verbose=False):

@@ -194,6 +194,9 @@ int run_fec_decode_tb(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, boo
     p.rm_arena = c->d_rm_arena.p; p.xp_arena = c->d_xp_arena.p;
     p.min_it = c->cfg.tdec_min_iter; p.max_it = c->cfg.tdec_max_iter;
     p.crc_mode = 0; p.plcf_mask = nullptr;
+    uint32_t max_n_e = 0;
+    for (const cb_desc_t& d : f.rx_cbs) max_n_e = std::max(max_n_e, d.n_e);
+    DNRP_LAUNCH(c, DNRP_KERNEL_DERM_PDC, launch_derm(p, n, max_n_e, c->stream));
     DNRP_LAUNCH(c, DNRP_KERNEL_TURBO_DECODE_PDC, launch_turbo_decode(p, n, f.tdec_threads, f.tdec_smem, c->stream));
     tbfin_params_t t{};
     t.C = c->ps.C; t.tbs_bits = c->ps.N_TB_bits; t.chunk_bytes = f.tb_chunk_bytes;
@@ -219,6 +222,7 @@ int run_fec_decode_plcf(dnrp_ctx* c, uint32_t n) {
     p.rm_arena = c->d_rm_arena.p; p.xp_arena = c->d_xp_arena.p;
     p.min_it = 1; p.max_it = 5;  // pcc_enc.cpp:39
     p.crc_mode = 1; p.plcf_mask = c->d_pcc_mask.p;
+    DNRP_LAUNCH(c, -1, launch_derm(p, n, spec::PCC_BITS, c->stream));
     DNRP_LAUNCH(c, -1, launch_turbo_decode(p, n, f.tdec_threads, f.tdec_smem, c->stream));
     return DNRP_OK;
 }

@@ -22,16 +22,89 @@ __device__ __forceinline__ uint32_t gf2_mulmod(uint32_t a, uint32_t b, uint32_t 
     return r;
 }
 
+// ---- descrambling + de-rate-matching + HARQ soft combining, one block per (code block, packet):
+// soft[n] (+)= sum of the descrambled LLRs that rate matching mapped onto circular buffer position n
+// (srsran_scrambling_s_offset + srsran_rm_turbo_rx_lut_, reference pdc_enc.cpp:339-363); plain int16
+// wrap-around adds.  A streaming kernel of its own so that it runs at full occupancy: inside the decoder
+// (three warps per block) its dependent loads were the largest stall source (profiles/).
+// The code block's LLRs are first descrambled into shared memory with coalesced loads; the table driven
+// gather then reads shared memory.  cap = int16 capacity of the dynamic shared buffer.
+__global__ void __launch_bounds__(256) k_derm(const tdec_params_t p, uint32_t cap) {
+    extern __shared__ uint32_t smem[];
+    const cb_desc_t cb = p.cbs[blockIdx.x];
+    const uint32_t pkt = blockIdx.y;
+    const uint32_t slot = p.slot ? p.slot[pkt] : pkt;
+    const uint32_t tid = threadIdx.x, nthr = blockDim.x;
+    const uint32_t N = 3 * (cb.K + 4);
+    const bool reset = p.reset ? p.reset[pkt] != 0 : true;
+    const uint32_t rv = p.rv ? p.rv[pkt] : 0;
+    // code block already decoded in an earlier transmission: nothing to combine (pdc_enc.cpp:404-406)
+    if (!reset && p.cb_crc[(size_t)slot * p.C + blockIdx.x]) return;
+
+    int16_t* soft = p.soft + (size_t)slot * p.soft_stride + cb.soft_off;
+    const int16_t* llr = p.llr + (size_t)pkt * p.llr_stride + cb.rp;
+    const uint16_t* rm_pos = p.rm_arena + cb.rm_off;
+    const uint32_t rm_start = cb.rm_start[rv];
+    int16_t* DSC = (int16_t*)smem;
+    const bool staged = cb.n_e <= cap;
+    if (staged) {
+        for (uint32_t e = tid; e < cb.n_e; e += nthr) {
+            const uint32_t g = cb.rp + e + p.gold_bit_off;
+            const int v = llr[e];
+            DSC[e] = (int16_t)(((p.gold[g >> 3] >> (7 - (g & 7))) & 1) ? -v : v);
+        }
+        __syncthreads();
+    }
+    for (uint32_t n0 = tid; n0 < N; n0 += 4 * nthr) {
+        uint32_t e[4];
+        int acc[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t n = n0 + u * nthr;
+            e[u] = 0xffffffffu;
+            acc[u] = 0;
+            if (n < N) {
+                uint32_t v = rm_pos[n] + N - rm_start;
+                e[u] = v >= N ? v - N : v;
+                if (!reset) acc[u] = soft[n];
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            if (staged) {
+                for (uint32_t ee = e[u]; ee < cb.n_e; ee += N) acc[u] += DSC[ee];
+            } else {
+                for (uint32_t ee = e[u]; ee < cb.n_e; ee += N) {
+                    const uint32_t g = cb.rp + ee + p.gold_bit_off;
+                    const int v = llr[ee];
+                    acc[u] += ((p.gold[g >> 3] >> (7 - (g & 7))) & 1) ? -v : v;
+                }
+            }
+        }
+#pragma unroll
+        for (int u = 0; u < 4; ++u) {
+            const uint32_t n = n0 + u * nthr;
+            if (n < N) soft[n] = (int16_t)acc[u];
+        }
+    }
+}
+
+cudaError_t launch_derm(const tdec_params_t& p, uint32_t n_packets, uint32_t max_n_e, cudaStream_t st) {
+    // shared buffer for the largest code block's LLRs, at most 48 KB (no opt-in); larger ones gather from global
+    const uint32_t cap = max_n_e < 24576u ? ((max_n_e + 7u) & ~7u) : 24576u;
+    k_derm<<<dim3(p.C, n_packets), 256, (size_t)cap * 2, st>>>(p, cap);
+    return cudaGetLastError();
+}
+
 __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
     extern __shared__ uint32_t smem[];
     const cb_desc_t cb = p.cbs[blockIdx.x];
     const uint32_t pkt = blockIdx.y;
     const uint32_t slot = p.slot ? p.slot[pkt] : pkt;
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
-    const uint32_t K = cb.K, L = cb.L, T = cb.P / 2, KH = K / 2, D = K + 4, N = 3 * D;
+    const uint32_t K = cb.K, L = cb.L, T = cb.P / 2, KH = K / 2, D = K + 4;
     const uint32_t nck = (L + S_CK - 1) / S_CK;
     const bool reset = p.reset ? p.reset[pkt] != 0 : true;
-    const uint32_t rv = p.rv ? p.rv[pkt] : 0;
 
     uint8_t* cb_crc = p.cb_crc + (size_t)slot * p.C + blockIdx.x;
     uint8_t* saved = p.saved ? p.saved + (size_t)slot * p.saved_stride + cb.saved_off : nullptr;
@@ -57,58 +130,33 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
     uint8_t* HARD = (uint8_t*)(BS + 2 * 7 * T);  // [KH]
     __shared__ uint32_t s_crc;
 
-    int16_t* soft = p.soft + (size_t)slot * p.soft_stride + cb.soft_off;
-    const int16_t* llr = p.llr + (size_t)pkt * p.llr_stride + cb.rp;
-    const uint16_t* rm_pos = p.rm_arena + cb.rm_off;
-    const uint32_t rm_start = cb.rm_start[rv];
-
-    // ---- prologue: soft[n] (+)= sum of the descrambled LLRs that rate matching mapped onto n
-    // (srsran_scrambling_s_offset + srsran_rm_turbo_rx_lut_, pdc_enc.cpp:339-363); plain int16 wrap
-    // Four independent elements per thread and trip so that the dependent global loads (table -> LLR /
-    // scrambling bit) of different elements overlap; the block only has a few warps to hide them.
-    for (uint32_t n0 = tid; n0 < N; n0 += 4 * nthr) {
-        uint32_t e[4];
-        int acc[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const uint32_t n = n0 + u * nthr;
-            e[u] = 0xffffffffu;
-            acc[u] = 0;
-            if (n < N) {
-                uint32_t v = rm_pos[n] + N - rm_start;
-                e[u] = v >= N ? v - N : v;
-                if (!reset) acc[u] = soft[n];
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            for (uint32_t ee = e[u]; ee < cb.n_e; ee += N) {
-                const uint32_t g = cb.rp + ee + p.gold_bit_off;
-                const int v = llr[ee];
-                acc[u] += ((p.gold[g >> 3] >> (7 - (g & 7))) & 1) ? -v : v;
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const uint32_t n = n0 + u * nthr;
-            if (n < N) soft[n] = (int16_t)acc[u];
-        }
-    }
+    // soft buffer of this code block, written by k_derm: d0 | d1 | d2, each D = K + 4 int16
+    const int16_t* soft = p.soft + (size_t)slot * p.soft_stride + cb.soft_off;
     for (uint32_t i = tid; i < KH; i += nthr) EXT[i] = 0;
     for (uint32_t i = tid; i < 4 * 7 * T; i += nthr) AE[i] = 0;  // AE and BS are contiguous
-    __syncthreads();  // soft[] of this code block is complete (block-wide visibility of the global stores)
+    __syncthreads();
 
     // stage one K-long stream (systematic or a parity) into a window-transposed packed shared array:
     // word (k, t) = (element t*L + k, element KH + t*L + k), both clamped to the channel range
-    // (add_ext: decoder 1's input, systematic + a-priori, which shares the natural order)
+    // (add_ext: input of the first constituent decoder, systematic + a-priori, natural order).
+    // 8-byte loads (K/2 and every stream offset are multiples of 4 elements), several in flight per
+    // thread: a block has only three warps to cover the L2 / HBM latency.
     auto stage = [&](uint32_t* dst, const int16_t* src, bool add_ext) {
+        const uint2* lo4 = reinterpret_cast<const uint2*>(src);
+        const uint2* hi4 = reinterpret_cast<const uint2*>(src + KH);
 #pragma unroll 4
-        for (uint32_t i = tid; i < KH; i += nthr) {
-            const int lo = clampi(src[i], 1023), hi = clampi(src[i + KH], 1023);
-            const uint32_t q = __umulhi(i, cb.Linv), a = (i - q * L) * T + q;
-            uint32_t w = pack(lo, hi);
-            if (add_ext) w = vadd(w, EXT[a]);
-            dst[a] = w;
+        for (uint32_t i4 = tid; i4 < KH / 4; i4 += nthr) {
+            const uint2 lo = lo4[i4], hi = hi4[i4];
+            const uint32_t lw[2] = {lo.x, lo.y}, hw[2] = {hi.x, hi.y};
+#pragma unroll
+            for (int u = 0; u < 4; ++u) {
+                const uint32_t i = 4 * i4 + u;
+                const uint32_t q = __umulhi(i, cb.Linv), a = (i - q * L) * T + q;
+                // (low half: element i, high half: element i + K/2), clamped as a pair
+                uint32_t w = vclamp(__byte_perm(lw[u >> 1], hw[u >> 1], (u & 1) ? 0x7632 : 0x5410), 1023);
+                if (add_ext) w = vadd(w, EXT[a]);
+                dst[a] = w;
+            }
         }
     };
 
@@ -177,7 +225,7 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
                 const uint32_t* AEd = AE + dec * 7 * T;
                 auto fetch = [&](const uint32_t* arr, int s, uint32_t v) -> int {
                     if (s == 0) return 0;
-                    const uint32_t w = arr[(s - 1) * T + (v % T)];
+                    const uint32_t w = arr[(s - 1) * T + (v >= T ? v - T : v)];  // v < 2T
                     return (int)(int16_t)(v >= T ? (w >> 16) : (w & 0xffff));
                 };
 

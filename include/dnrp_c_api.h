@@ -226,7 +226,8 @@ typedef enum {
     DNRP_KERNEL_RX_FFT = 1,
     DNRP_KERNEL_RX_DEMAP_PDC = 2,
     DNRP_KERNEL_RX_STF = 3,
-    DNRP_KERNEL_COUNT = 4
+    DNRP_KERNEL_DERM_PDC = 4,
+    DNRP_KERNEL_COUNT = 5
 } dnrp_kernel_t;
 int dnrp_kernel_time_enable(dnrp_ctx_t* ctx, int enable);
 int dnrp_kernel_time_read(dnrp_ctx_t* ctx, int kernel, float* ms_total, uint32_t* launches);
