@@ -197,7 +197,8 @@ int run_fec_decode_tb(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, boo
     uint32_t max_n_e = 0;
     for (const cb_desc_t& d : f.rx_cbs) max_n_e = std::max(max_n_e, d.n_e);
     DNRP_LAUNCH(c, DNRP_KERNEL_DERM_PDC, launch_derm(p, n, max_n_e, c->stream));
-    DNRP_LAUNCH(c, DNRP_KERNEL_TURBO_DECODE_PDC, launch_turbo_decode(p, n, f.tdec_threads, f.tdec_smem, c->stream));
+    const tdec_geom_t geom = tdec_geometry(f.rx_cbs.data(), (uint32_t)f.rx_cbs.size());
+    DNRP_LAUNCH(c, DNRP_KERNEL_TURBO_DECODE_PDC, launch_turbo_decode(p, n, geom, c->stream));
     tbfin_params_t t{};
     t.C = c->ps.C; t.tbs_bits = c->ps.N_TB_bits; t.chunk_bytes = f.tb_chunk_bytes;
     t.slot = p.slot; t.cb_crc = c->d_cb_crc.p;
@@ -223,7 +224,7 @@ int run_fec_decode_plcf(dnrp_ctx* c, uint32_t n) {
     p.min_it = 1; p.max_it = 5;  // pcc_enc.cpp:39
     p.crc_mode = 1; p.plcf_mask = c->d_pcc_mask.p;
     DNRP_LAUNCH(c, -1, launch_derm(p, n, spec::PCC_BITS, c->stream));
-    DNRP_LAUNCH(c, -1, launch_turbo_decode(p, n, f.tdec_threads, f.tdec_smem, c->stream));
+    DNRP_LAUNCH(c, -1, launch_turbo_decode(p, n, tdec_geometry(f.rx_pcc, 2), c->stream));
     return DNRP_OK;
 }
 

@@ -96,28 +96,43 @@ cudaError_t launch_derm(const tdec_params_t& p, uint32_t n_packets, uint32_t max
     return cudaGetLastError();
 }
 
-__global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
-    extern __shared__ uint32_t smem[];
-    const cb_desc_t cb = p.cbs[blockIdx.x];
-    const uint32_t pkt = blockIdx.y;
+// One thread GROUP of tg threads decodes one item = (code block, packet); a block holds
+// blockDim.x / tg groups.  Large code blocks: one group per block (tg = blockDim.x, a multiple of 32).
+// Small ones (PLCF, K < ~2000: fewer than 32 window pairs): tg is a power of two <= 32 and many items
+// share a block, all groups moving through the same barriers in lockstep.
+template <bool GROUPED>
+__global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p, uint32_t tg, uint32_t smem_item_words,
+                                                      uint32_t n_items) {
+    extern __shared__ uint32_t smem_all[];
+    __shared__ uint32_t s_crc_all[128];
+    const uint32_t grp = GROUPED ? threadIdx.x / tg : 0;
+    const uint32_t tid = GROUPED ? threadIdx.x % tg : threadIdx.x, nthr = GROUPED ? tg : blockDim.x;
+    const uint32_t item = GROUPED ? blockIdx.x * (blockDim.x / tg) + grp : blockIdx.x;
+    const bool valid = item < n_items;
+    const uint32_t cbi = valid ? item % p.C : 0, pkt = valid ? item / p.C : 0;
+    const cb_desc_t cb = p.cbs[cbi];
+    uint32_t* smem = smem_all + (size_t)grp * smem_item_words;
+    uint32_t& s_crc = s_crc_all[grp];
     const uint32_t slot = p.slot ? p.slot[pkt] : pkt;
-    const uint32_t tid = threadIdx.x, nthr = blockDim.x;
     const uint32_t K = cb.K, L = cb.L, T = cb.P / 2, KH = K / 2, D = K + 4;
     const uint32_t nck = (L + S_CK - 1) / S_CK;
     const bool reset = p.reset ? p.reset[pkt] != 0 : true;
 
-    uint8_t* cb_crc = p.cb_crc + (size_t)slot * p.C + blockIdx.x;
+    uint8_t* cb_crc = p.cb_crc + (size_t)slot * p.C + cbi;
     uint8_t* saved = p.saved ? p.saved + (size_t)slot * p.saved_stride + cb.saved_off : nullptr;
     uint8_t* tb_out = p.tb_out + (size_t)pkt * p.tb_stride + cb.out_byte;
-    uint8_t* n_iter_out = p.n_iter + (size_t)pkt * p.C + blockIdx.x;
+    uint8_t* n_iter_out = p.n_iter + (size_t)pkt * p.C + cbi;
 
     // ---- code block already decoded in an earlier transmission: copy the saved bytes
-    // (reference pdc_enc.cpp:404-406)
-    if (!reset && *cb_crc) {
+    // (reference pdc_enc.cpp:404-406); the group then idles through the barriers below
+    bool done = !valid;
+    if (valid && !reset && *cb_crc) {
         for (uint32_t i = tid; i < cb.rlen_byte; i += nthr) tb_out[i] = saved[i];
         if (tid == 0) *n_iter_out = 0;
-        return;
+        done = true;
     }
+    const bool skipped = done;
+    if (!GROUPED && done) return;  // single item per block: nothing left to do
 
     // the systematic stream stays in the (L2 resident) soft buffer and is re-read once per half
     // iteration: one K/2-word array less per block = one more resident block per SM
@@ -128,7 +143,6 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
     uint32_t* AE = CK + nck * 7 * T;         // [2][7][T]
     uint32_t* BS = AE + 2 * 7 * T;           // [2][7][T]
     uint8_t* HARD = (uint8_t*)(BS + 2 * 7 * T);  // [KH]
-    __shared__ uint32_t s_crc;
 
     // soft buffer of this code block, written by k_derm: d0 | d1 | d2, each D = K + 4 int16
     const int16_t* soft = p.soft + (size_t)slot * p.soft_stride + cb.soft_off;
@@ -160,20 +174,26 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
         }
     };
 
-    const bool active = tid < T;
     const uint32_t t = tid;
     const uint32_t wl = t, wh = t + T, P = cb.P;
     uint32_t n_iter = 0;
     bool crc_ok = false;
     uint32_t plcf_mask = 0;
 
-    for (uint32_t it = 0; it < p.max_it && !crc_ok; ++it) {
+    for (uint32_t it = 0; it < p.max_it; ++it) {
+        if (GROUPED) {
+            if (!__syncthreads_or(!done)) break;  // every group of the block has finished
+        } else if (done) {
+            break;
+        }
+        const bool work = GROUPED ? !done : true;  // uniform within a group
+        const bool active = work && tid < T;
         for (uint32_t dec = 0; dec < 2; ++dec) {
             // ---- parity of this constituent decoder -> shared, window-transposed
-            stage(PAR, soft + (1 + dec) * D, false);
+            if (work) stage(PAR, soft + (1 + dec) * D, false);
             // ---- decoder input x = systematic + a-priori, in decoder order
             if (dec == 0) {
-                stage(XIN, soft, true);
+                if (work) stage(XIN, soft, true);
             } else if (active) {
                 const uint32_t j0 = t * L;
                 uint32_t pi = (uint32_t)(((uint64_t)cb.f1 * j0 + (uint64_t)cb.f2 * j0 * j0) % K);
@@ -354,7 +374,7 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
             }
         }
         // ---- CRC of the hard decisions (natural order), remainder of the whole block mod g
-        ++n_iter;
+        if (work) ++n_iter;
         {
             uint32_t r = 0;
             if (active) {
@@ -371,19 +391,25 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
                 r = gf2_mulmod(r_lo, xp[wl], cb.crc_poly, cb.crc_order) ^
                     gf2_mulmod(r_hi, xp[wh], cb.crc_poly, cb.crc_order);
             }
-            for (int o = 16; o > 0; o >>= 1) r ^= __shfl_xor_sync(0xffffffffu, r, o);
-            if ((tid & 31) == 0 && r) atomicXor(&s_crc, r);
+            // xor over the group: whole warps, or an aligned power-of-two slice of one warp
+            const uint32_t width = GROUPED ? (tg >= 32 ? 32u : tg) : 32u;
+            for (int o = (int)width / 2; o > 0; o >>= 1) r ^= __shfl_xor_sync(0xffffffffu, r, o);
+            if ((tid & (width - 1)) == 0 && r) atomicXor(&s_crc, r);
         }
         __syncthreads();
-        const uint32_t rem = s_crc;
-        if (p.crc_mode == 0) {
-            crc_ok = (rem == 0) && n_iter >= p.min_it;
-        } else {  // PLCF: remainder equals the CL/BF mask (pcc_enc.cpp:326-346)
-            crc_ok = (rem == 0x0000 || rem == 0x5555 || rem == 0xAAAA || rem == 0xFFFF);
-            plcf_mask = rem;
+        if (work) {
+            const uint32_t rem = s_crc;
+            if (p.crc_mode == 0) {
+                crc_ok = (rem == 0) && n_iter >= p.min_it;
+            } else {  // PLCF: remainder equals the CL/BF mask (pcc_enc.cpp:326-346)
+                crc_ok = (rem == 0x0000 || rem == 0x5555 || rem == 0xAAAA || rem == 0xFFFF);
+                plcf_mask = rem;
+            }
+            done = crc_ok;
         }
         __syncthreads();
     }
+    if (skipped) return;  // no barrier below
 
     // ---- outputs: packed bytes (MSB first), flags
     for (uint32_t bi = tid; bi < K / 8; bi += nthr) {
@@ -404,7 +430,7 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p) {
     if (tid == 0) {
         *n_iter_out = (uint8_t)n_iter;
         *cb_crc = crc_ok ? 1 : 0;
-        if (p.plcf_mask) p.plcf_mask[(size_t)pkt * p.C + blockIdx.x] = crc_ok ? plcf_mask : 0xffffffffu;
+        if (p.plcf_mask) p.plcf_mask[(size_t)pkt * p.C + cbi] = crc_ok ? plcf_mask : 0xffffffffu;
     }
 }
 
@@ -456,15 +482,41 @@ size_t tdec_smem_bytes(uint32_t K, uint32_t L) {
     return (size_t)4 * (3 * (K / 2) + nck * 7 * T + 4 * 7 * T) + K / 2 + 16;
 }
 
-cudaError_t launch_turbo_decode(const tdec_params_t& p, uint32_t n_packets, uint32_t threads, size_t smem,
-                                cudaStream_t st) {
+tdec_geom_t tdec_geometry(const cb_desc_t* cbs, uint32_t n) {
+    tdec_geom_t g{32, 32, 0};
+    uint32_t Tmax = 1;
+    for (uint32_t i = 0; i < n; ++i) {
+        Tmax = std::max(Tmax, cbs[i].P / 2);
+        g.smem_item = std::max(g.smem_item, tdec_smem_bytes(cbs[i].K, cbs[i].L));
+    }
+    g.smem_item = (g.smem_item + 15) & ~(size_t)15;
+    if (Tmax >= 32) {  // one item per block
+        g.threads = g.tg = ((Tmax + 31) / 32) * 32;
+    } else {           // many small items per block: power-of-two groups inside 128 threads
+        g.tg = 1;
+        while (g.tg < Tmax) g.tg *= 2;
+        g.threads = 128;
+        while (g.threads > g.tg && (size_t)(g.threads / g.tg) * g.smem_item > 96 * 1024) g.threads /= 2;
+    }
+    return g;
+}
+
+cudaError_t launch_turbo_decode(const tdec_params_t& p, uint32_t n_packets, const tdec_geom_t& g, cudaStream_t st) {
+    const uint32_t per_block = g.threads / g.tg, n_items = n_packets * p.C;
+    const size_t smem = per_block * g.smem_item;
     static size_t configured = 0;
     if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_turbo_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaError_t e = cudaFuncSetAttribute(k_turbo_decode<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(k_turbo_decode<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         if (e != cudaSuccess) return e;
         configured = smem;
     }
-    k_turbo_decode<<<dim3(p.C, n_packets), threads, smem, st>>>(p);
+    const dim3 grid((n_items + per_block - 1) / per_block);
+    if (per_block == 1)
+        k_turbo_decode<false><<<grid, g.threads, smem, st>>>(p, g.tg, (uint32_t)(g.smem_item / 4), n_items);
+    else
+        k_turbo_decode<true><<<grid, g.threads, smem, st>>>(p, g.tg, (uint32_t)(g.smem_item / 4), n_items);
     return cudaGetLastError();
 }
 

@@ -46,8 +46,13 @@ size_t tdec_smem_bytes(uint32_t K, uint32_t L);
 // descramble + de-rate-match + HARQ combine into the soft buffers; must precede launch_turbo_decode.
 // max_n_e = largest LLR count of a code block in p.cbs (sizes the shared staging buffer)
 cudaError_t launch_derm(const tdec_params_t& p, uint32_t n_packets, uint32_t max_n_e, cudaStream_t st);
-cudaError_t launch_turbo_decode(const tdec_params_t& p, uint32_t n_packets, uint32_t threads, size_t smem,
-                                cudaStream_t st);
+// thread/shared-memory geometry of a decoder launch over the n descriptors cbs (host copies)
+struct tdec_geom_t {
+    uint32_t threads, tg;  // block size, threads per (code block, packet) item
+    size_t smem_item;      // dynamic shared bytes per item
+};
+tdec_geom_t tdec_geometry(const cb_desc_t* cbs, uint32_t n);
+cudaError_t launch_turbo_decode(const tdec_params_t& p, uint32_t n_packets, const tdec_geom_t& g, cudaStream_t st);
 cudaError_t launch_tb_finalize(const tbfin_params_t& p, uint32_t n_packets, cudaStream_t st);
 
 }  // namespace dnrp
