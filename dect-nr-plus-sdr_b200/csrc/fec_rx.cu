@@ -188,6 +188,7 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p, uin
         }
         const bool work = GROUPED ? !done : true;  // uniform within a group
         const bool active = work && tid < T;
+#pragma unroll 1  // one copy of the half-iteration body: the kernel is instruction-cache bound otherwise
         for (uint32_t dec = 0; dec < 2; ++dec) {
             // ---- parity of this constituent decoder -> shared, window-transposed
             if (work) stage(PAR, soft + (1 + dec) * D, false);
@@ -243,24 +244,29 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p, uin
                 }
                 const uint32_t* BSd = BS + dec * 7 * T;
                 const uint32_t* AEd = AE + dec * 7 * T;
-                auto fetch = [&](const uint32_t* arr, int s, uint32_t v) -> int {
-                    if (s == 0) return 0;
-                    const uint32_t w = arr[(s - 1) * T + (v >= T ? v - T : v)];  // v < 2T
-                    return (int)(int16_t)(v >= T ? (w >> 16) : (w & 0xffff));
-                };
+                // boundary metric of window v as int16: word v (low half) for v < T, word v - T (high half)
+                // otherwise; row s - 1 of the [7][T] word array
+                auto hidx = [&](uint32_t v) -> uint32_t { return v < T ? 2 * v : 2 * (v - T) + 1; };
+                const bool b_lo_end = wl + 2 >= P, b_hi_end = wh + 2 >= P, a_lo_beg = wl <= 1, a_hi_beg = wh <= 1;
+                const int16_t* pb_lo = (const int16_t*)BSd + hidx(b_lo_end ? wl : wl + 2);
+                const int16_t* pb_hi = (const int16_t*)BSd + hidx(b_hi_end ? wh : wh + 2);
+                const int16_t* pa_lo = (const int16_t*)AEd + hidx(a_lo_beg ? wl : wl - 2);
+                const int16_t* pa_hi = (const int16_t*)AEd + hidx(a_hi_beg ? wh : wh - 2);
 
                 // ---- training passes: beta over window w+1 and alpha over window w-1 are independent
                 // recursions, run in one loop (two dependency chains in flight) with the next step's
                 // shared-memory words prefetched one iteration ahead
                 uint32_t b[8], a[8];
+                b[0] = pack(b_lo_end ? tail[0] : 0, b_hi_end ? tail[0] : 0);
+                a[0] = 0;
 #pragma unroll
-                for (int s = 0; s < 8; ++s) {
-                    const int lo = (wl + 2 >= P) ? tail[s] : fetch(BSd, s, wl + 2);
-                    const int hi = (wh + 2 >= P) ? tail[s] : fetch(BSd, s, wh + 2);
+                for (int s = 1; s < 8; ++s) {
+                    const uint32_t row = (s - 1) * 2 * T;
+                    const int lo = b_lo_end ? tail[s] : (int)pb_lo[row];
+                    const int hi = b_hi_end ? tail[s] : (int)pb_hi[row];
                     b[s] = pack(lo, hi);
-                    const int ex = s == 0 ? 0 : -8192;
-                    const int alo = (wl <= 1) ? ex : fetch(AEd, s, wl - 2);
-                    const int ahi = (wh <= 1) ? ex : fetch(AEd, s, wh - 2);
+                    const int alo = a_lo_beg ? -8192 : (int)pa_lo[row];
+                    const int ahi = a_hi_beg ? -8192 : (int)pa_hi[row];
                     a[s] = pack(alo, ahi);
                 }
                 {
@@ -270,11 +276,14 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p, uin
                     const uint32_t* Xp = XIN + (wrapp ? T - 1 : t - 1);
                     const uint32_t* Yp = PAR + (wrapp ? T - 1 : t - 1);
                     const uint32_t shn = wrapn ? 16 : 0, shp = wrapp ? 16 : 0;
-                    uint32_t xb = Xn[(L - 1) * T], yb = Yn[(L - 1) * T], xa = Xp[0], ya = Yp[0];
+                    // running pointers; the prefetch of the last iteration reads one row outside XIN / PAR,
+                    // which is still inside this item's shared arrays (EXT | XIN | PAR | CK) and unused
+                    const uint32_t* pxb = Xn + (size_t)(L - 1) * T;
+                    const uint32_t* pyb = Yn + (size_t)(L - 1) * T;
+                    uint32_t xb = *pxb, yb = *pyb, xa = *Xp, ya = *Yp;
                     for (uint32_t i = 0; i < L; ++i) {
-                        const uint32_t in = i + 1 < L ? i + 1 : i;  // last iteration: harmless reload
-                        const uint32_t xb_n = Xn[(L - 1 - in) * T], yb_n = Yn[(L - 1 - in) * T];
-                        const uint32_t xa_n = Xp[in * T], ya_n = Yp[in * T];
+                        pxb -= T; pyb -= T; Xp += T; Yp += T;
+                        const uint32_t xb_n = *pxb, yb_n = *pyb, xa_n = *Xp, ya_n = *Yp;
                         beta_step(b, xb >> shn, yb >> shn);
                         alpha_step(a, xa << shp, ya << shp);
                         xb = xb_n; yb = yb_n; xa = xa_n; ya = ya_n;
@@ -290,12 +299,12 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p, uin
                 }
                 // ---- backward pass over the own windows, checkpoint every S_CK steps
                 {
-                    const uint32_t* X = XIN + t;
-                    const uint32_t* Y = PAR + t;
-                    uint32_t x = X[(L - 1) * T], y = Y[(L - 1) * T];
+                    const uint32_t* X = XIN + t + (size_t)(L - 1) * T;
+                    const uint32_t* Y = PAR + t + (size_t)(L - 1) * T;
+                    uint32_t x = *X, y = *Y;
                     for (int k = (int)L - 1; k >= 0; --k) {
-                        const int kn = k > 0 ? k - 1 : 0;
-                        const uint32_t x_n = X[kn * T], y_n = Y[kn * T];
+                        X -= T; Y -= T;  // last prefetch: one row below, inside EXT / XIN, unused
+                        const uint32_t x_n = *X, y_n = *Y;
                         if (((k + 1) % S_CK) == 0 || k + 1 == (int)L) {
                             const int c = k / S_CK;
 #pragma unroll
@@ -502,7 +511,11 @@ tdec_geom_t tdec_geometry(const cb_desc_t* cbs, uint32_t n) {
 }
 
 cudaError_t launch_turbo_decode(const tdec_params_t& p, uint32_t n_packets, const tdec_geom_t& g, cudaStream_t st) {
-    const uint32_t per_block = g.threads / g.tg, n_items = n_packets * p.C;
+    const uint32_t n_items = n_packets * p.C;
+    uint32_t threads = g.threads;
+    // grouped launch: prefer at least two blocks per SM over full 128-thread blocks
+    while (threads > 32 && threads > g.tg && n_items / (threads / g.tg) < 2 * 148) threads /= 2;
+    const uint32_t per_block = threads / g.tg;
     const size_t smem = per_block * g.smem_item;
     static size_t configured = 0;
     if (smem > configured) {
@@ -514,9 +527,9 @@ cudaError_t launch_turbo_decode(const tdec_params_t& p, uint32_t n_packets, cons
     }
     const dim3 grid((n_items + per_block - 1) / per_block);
     if (per_block == 1)
-        k_turbo_decode<false><<<grid, g.threads, smem, st>>>(p, g.tg, (uint32_t)(g.smem_item / 4), n_items);
+        k_turbo_decode<false><<<grid, threads, smem, st>>>(p, g.tg, (uint32_t)(g.smem_item / 4), n_items);
     else
-        k_turbo_decode<true><<<grid, g.threads, smem, st>>>(p, g.tg, (uint32_t)(g.smem_item / 4), n_items);
+        k_turbo_decode<true><<<grid, threads, smem, st>>>(p, g.tg, (uint32_t)(g.smem_item / 4), n_items);
     return cudaGetLastError();
 }
 
