@@ -89,7 +89,15 @@ CHANNEL_DTYPE = np.dtype([("snr_dB", "f4"), ("net_bandwidth_norm", "f4"), ("t0",
                           ("seed", "u8")], align=True)
 assert CHANNEL_DTYPE.itemsize == C.sizeof(ChannelDesc)
 TAP_Y, TAP_DRS_ZF, TAP_STF_ZF, TAP_LLR_PCC, TAP_LLR_PDC, TAP_WIENER_CLASS, TAP_TB_OK = 1, 2, 3, 4, 5, 6, 7
-KERNEL_TURBO_DECODE_PDC, KERNEL_RX_FFT, KERNEL_RX_DEMAP_PDC, KERNEL_RX_STF, KERNEL_DERM_PDC = 0, 1, 2, 3, 4
+KERNEL_TURBO_DECODE_PDC, KERNEL_RX_FFT, KERNEL_RX_DEMAP_PDC, KERNEL_RX_STF, KERNEL_DERM_PDC, KERNEL_SYNC = range(6)
+# dnrp_sync_result_t
+SYNC_RESULT_DTYPE = np.dtype([("detected", "u4"), ("detection_time_local", "u4"), ("detection_ant_idx", "u4"),
+                              ("detection_metric", "f4"), ("detection_rms", "f4"), ("coarse_peak_time_local", "u4"),
+                              ("coarse_peak_array", "f4", (8,)), ("rms_array", "f4", (8,)),
+                              ("cfo_fractional_rad", "f4"), ("cfo_integer_rad", "f4"), ("N_eff_TX", "u4"),
+                              ("fine_peak_time_local", "u4"), ("n_detections", "u4"), ("strongest_ant", "u4")],
+                             align=True)
+assert SYNC_RESULT_DTYPE.itemsize == 112
 
 
 def build(verbose=False):
@@ -248,9 +256,23 @@ class Phy:
             assert iq.shape[-1] == self.rx_stride(), (iq.shape, self.rx_stride())
         if sync is None:
             sync = self.make_sync(n, t0, cfo_fractional_rad, cfo_integer_rad, rms)
+        # sync="device": continue on the results the preceding sync() left on the device
+        sync_p = None if isinstance(sync, str) else sync.ctypes.data_as(C.c_void_p)
         out = np.zeros(n, dtype=PCC_DTYPE).view(np.recarray)
-        _check(lib().dnrp_rx_pcc_batch(self._ctx, n, _ptr(iq, np.complex64), sync.ctypes.data_as(C.c_void_p),
-                                       out.ctypes.data_as(C.c_void_p)))
+        _check(lib().dnrp_rx_pcc_batch(self._ctx, n, _ptr(iq, np.complex64), sync_p, out.ctypes.data_as(C.c_void_p)))
+        return out
+
+    # ---- sync_chunk_t::search (reference lib/src/phy/rx/sync/sync_chunk.cpp:120-215), one search per window
+    def sync(self, iq=None, n=None, search_length=0, fetch=True):
+        """iq [n][N_RX][rx_stride] complex64 host windows or None (device-resident windows); returns [n]
+        dnrp_sync_result_t records"""
+        if iq is not None:
+            n = iq.shape[0]
+            iq = np.ascontiguousarray(iq, dtype=np.complex64)
+            assert iq.shape[1:] == (self.N_RX, self.rx_stride()), (iq.shape, self.rx_stride())
+        out = np.zeros(n, dtype=SYNC_RESULT_DTYPE).view(np.recarray) if fetch else None
+        _check(lib().dnrp_sync_batch(self._ctx, n, _ptr(iq, np.complex64), int(search_length),
+                                     None if out is None else out.ctypes.data_as(C.c_void_p)))
         return out
 
     def rx_pdc(self, n, harq_slot=None, rv=None, harq_reset=None, tb_out=None):

@@ -61,28 +61,69 @@ int run_channel(dnrp_ctx* c, uint32_t n) {
     return DNRP_OK;
 }
 
+int run_sync(dnrp_ctx* c, uint32_t n, uint32_t search_length, bool hand_over) {
+    const phy_dims_t& d = c->dims;
+    sync_params_t p{};
+    p.d = d;
+    p.iq = c->d_iq_rx.p; p.iq_stride = c->rx_stride;
+    p.n_ant = d.N_RX;  // RX_SYNC_PARAM_AUTOCORRELATOR_ANTENNA_LIMIT = 8 >= N_RX
+    p.step = c->sync_step; p.n_steps = c->sync_n_steps;
+    p.search_length = search_length ? search_length : c->rx_stride - d.stf_len_os - d.pat_len_os;
+    // autocorrelator_detection.cpp:60-62: minimum rms scaled with the sample rate relative to 30.72 MS/s
+    p.rms_min = 0.005f * (float)std::sqrt((double)d.u * d.b * c->cfg.oversampling * 1.728e6 / 30.72e6);
+    p.c_steps = c->d_sync_c.p; p.p_steps = c->d_sync_p.p;
+    p.templates = c->d_sync_tpl.p; p.n_tpl = c->sync_n_tpl;
+    p.xc = c->d_sync_xc.p;
+    p.result = c->d_sync_result.p;
+    p.rx_state = hand_over ? c->d_rx_state.p : nullptr;
+    c->launches += 3;  // launch_sync issues four kernels
+    DNRP_LAUNCH(c, DNRP_KERNEL_SYNC, launch_sync(p, n, c->stream));
+    return DNRP_OK;
+}
+
 }  // namespace dnrp
 
 extern "C" {
+
+int dnrp_sync_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, uint32_t search_length,
+                    dnrp_sync_result_t* out) {
+    static_assert(sizeof(dnrp_sync_result_t) == sizeof(sync_result_dev_t), "sync result layouts differ");
+    DNRP_REQUIRE(c, "null argument");
+    DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
+    DNRP_REQUIRE(search_length <= c->rx_stride, "search_length exceeds the IQ window");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    if (iq_in)
+        DNRP_CUDA(cudaMemcpyAsync(c->d_iq_rx.p, iq_in, (size_t)n * c->dims.N_RX * c->rx_stride * sizeof(float2),
+                                  cudaMemcpyHostToDevice, c->stream));
+    const int rc = run_sync(c, n, search_length, true);
+    if (rc) return rc;
+    if (out)
+        DNRP_CUDA(cudaMemcpyAsync(out, c->d_sync_result.p, n * sizeof(dnrp_sync_result_t), cudaMemcpyDeviceToHost,
+                                  c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    return DNRP_OK;
+}
 
 uint32_t dnrp_rx_stride(const dnrp_ctx_t* c) { return c ? c->rx_stride : 0; }
 
 int dnrp_rx_pcc_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, const dnrp_sync_report_t* sync,
                       dnrp_pcc_report_t* out) {
-    DNRP_REQUIRE(c && sync && out, "null argument");
+    DNRP_REQUIRE(c && out, "null argument");
     DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
     DNRP_CUDA(cudaSetDevice(c->device));
     const phy_dims_t& d = c->dims;
-    for (uint32_t i = 0; i < n; ++i) {
-        DNRP_REQUIRE(sync[i].fine_peak_time_local + d.n_no_gi_os <= c->rx_stride, "packet exceeds the IQ window");
-        rx_state_t& s = c->h_rx_state[i];
-        std::memset(&s, 0, sizeof(s));
-        s.t0 = (int32_t)sync[i].fine_peak_time_local;
-        s.inc0 = sync[i].cfo_fractional_rad + sync[i].cfo_integer_rad;  // rx_synced.cpp:240
-        for (uint32_t a = 0; a < 8; ++a) s.rms[a] = sync[i].rms[a];
-    }
-    DNRP_CUDA(cudaMemcpyAsync(c->d_rx_state.p, c->h_rx_state.data(), n * sizeof(rx_state_t),
-                              cudaMemcpyHostToDevice, c->stream));
+    if (sync) {
+        for (uint32_t i = 0; i < n; ++i) {
+            DNRP_REQUIRE(sync[i].fine_peak_time_local + d.n_no_gi_os <= c->rx_stride, "packet exceeds the IQ window");
+            rx_state_t& s = c->h_rx_state[i];
+            std::memset(&s, 0, sizeof(s));
+            s.t0 = (int32_t)sync[i].fine_peak_time_local;
+            s.inc0 = sync[i].cfo_fractional_rad + sync[i].cfo_integer_rad;  // rx_synced.cpp:240
+            for (uint32_t a = 0; a < 8; ++a) s.rms[a] = sync[i].rms[a];
+        }
+        DNRP_CUDA(cudaMemcpyAsync(c->d_rx_state.p, c->h_rx_state.data(), n * sizeof(rx_state_t),
+                                  cudaMemcpyHostToDevice, c->stream));
+    }  // else: d_rx_state was written by the preceding dnrp_sync_batch (k_sync_final)
     if (iq_in)
         DNRP_CUDA(cudaMemcpyAsync(c->d_iq_rx.p, iq_in, (size_t)n * d.N_RX * c->rx_stride * sizeof(float2),
                                   cudaMemcpyHostToDevice, c->stream));

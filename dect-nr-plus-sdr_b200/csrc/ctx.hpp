@@ -127,6 +127,12 @@ struct dnrp_ctx {
     std::vector<dnrp::rx_state_t> h_rx_state;
     dnrp::dbuf<dnrp::chan_meta_dev_t> d_chan_meta;
 
+    // packet synchronisation: STF templates for N_eff_TX = 1, 2, 4, 8 (up to the context's), step sums, results
+    uint32_t sync_n_tpl = 0, sync_step = 0, sync_n_steps = 0;
+    dnrp::dbuf<float2> d_sync_tpl, d_sync_c, d_sync_xc;
+    dnrp::dbuf<float> d_sync_p;
+    dnrp::dbuf<dnrp::sync_result_dev_t> d_sync_result;
+
     // measurement: launch counter and optional per-kernel event timers (dnrp_kernel_time_*)
     uint64_t launches = 0;
     bool ktime_on = false;
@@ -175,4 +181,5 @@ int run_rx_front(dnrp_ctx* c, uint32_t n);             // STF stage, FFTs, DRS z
 int run_rx_pcc(dnrp_ctx* c, uint32_t n);               // PCC demap + blind PLCF decode
 int run_rx_pdc(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, bool have_reset);
 int run_channel(dnrp_ctx* c, uint32_t n);
+int run_sync(dnrp_ctx* c, uint32_t n, uint32_t search_length, bool hand_over);
 }  // namespace dnrp

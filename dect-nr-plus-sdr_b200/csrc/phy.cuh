@@ -98,6 +98,35 @@ struct txofdm_params_t {
 
 cudaError_t launch_tx_ofdm(const txofdm_params_t& p, uint32_t n_packets, cudaStream_t st);
 
+// packet synchronisation (phy_sync.cu): detection, coarse peak, fine peak of the first packet in each window
+struct sync_result_dev_t {
+    uint32_t detected;
+    uint32_t detection_time_local, detection_ant_idx;
+    float detection_metric, detection_rms;
+    uint32_t coarse_peak_time_local;
+    float coarse_peak_array[8];
+    float rms_array[8];
+    float cfo_fractional_rad, cfo_integer_rad;
+    uint32_t N_eff_TX, fine_peak_time_local;
+    uint32_t n_detections, strongest_ant;
+};
+struct sync_params_t {
+    phy_dims_t d;
+    const float2* iq;  size_t iq_stride;  // [packet][N_RX][iq_stride]
+    uint32_t n_ant;                        // antennas used (RX_SYNC_PARAM_AUTOCORRELATOR_ANTENNA_LIMIT = 8)
+    uint32_t step, n_steps;                // detection step (pattern / 4) and number of steps in the window
+    uint32_t search_length;                // samples the detection may consume
+    float rms_min;
+    float2* c_steps;                       // [packet][n_ant][n_steps]
+    float* p_steps;                        // [packet][n_ant][n_steps]
+    const float2* templates;               // [n_tpl][stf_len_os]
+    uint32_t n_tpl;
+    float2* xc;                            // [packet][n_tpl] (max abs(xcorr), lag)
+    sync_result_dev_t* result;             // [packet]
+    rx_state_t* rx_state;                  // [packet] optional: receives t0 / CFO / rms for the synced receiver
+};
+cudaError_t launch_sync(const sync_params_t& p, uint32_t n_packets, cudaStream_t st);
+
 // simulation channel (phy_channel.cu)
 struct chan_meta_dev_t {
     uint32_t t0;        // first sample of the packet inside the RX window

@@ -1,0 +1,433 @@
+// phy_sync.cu -- packet synchronisation on the GPU for a batch of IQ windows (one search per window):
+//   k_sync_steps   per-step autocorrelation and power sums          (autocorrelator_detection.cpp:152-196)
+//   k_sync_peak    detection gates, per-sample coarse peak search, validity, fractional CFO, rms
+//                  (autocorrelator_detection.cpp:197-250, autocorrelator_peak.cpp:145-384)
+//   k_sync_xcorr   CFO pre-corrected cross-correlation with every N_eff_TX template (crosscorrelator.cpp:89-249)
+//   k_sync_final   N_eff_TX decision and fine peak, hand-over to the synchronised receiver
+// The reference streams samples through moving sums that pop and push; here every candidate position is
+// evaluated directly from prefix sums (same sums, different association order).  Constants:
+// lib/include/dectnrp/phy/rx/sync/sync_param.hpp as shipped (cover sequence active).
+#include "fft.cuh"
+#include "phy.cuh"
+
+namespace dnrp {
+
+namespace {
+__device__ __constant__ float c_cover[9] = {1.f, -1.f, 1.f, 1.f, -1.f, -1.f, -1.f, -1.f, -1.f};
+
+__device__ __forceinline__ float warp_sum(float v) {
+    for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+    return v;
+}
+
+// inclusive block-wide prefix sum of a double array in shared memory, in place (n arbitrary)
+__device__ void block_scan(double* a, uint32_t n, double* s_part) {
+    const uint32_t tid = threadIdx.x, nthr = blockDim.x;
+    const uint32_t per = (n + nthr - 1) / nthr, lo = min(tid * per, n), hi = min(lo + per, n);
+    double s = 0.0;
+    for (uint32_t i = lo; i < hi; ++i) { s += a[i]; a[i] = s; }
+    s_part[tid] = s;
+    __syncthreads();
+    if (tid == 0) {
+        double acc = 0.0;
+        for (uint32_t t = 0; t < nthr; ++t) { const double v = s_part[t]; s_part[t] = acc; acc += v; }
+    }
+    __syncthreads();
+    const double off = s_part[tid];
+    for (uint32_t i = lo; i < hi; ++i) a[i] += off;
+    __syncthreads();
+}
+}  // namespace
+
+// block-wide sum of three floats (result in every thread)
+__device__ float3 block_sum3(float3 v, float3* s_red) {
+    v.x = warp_sum(v.x); v.y = warp_sum(v.y); v.z = warp_sum(v.z);
+    const uint32_t w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) s_red[w] = v;
+    __syncthreads();
+    float3 t = make_float3(0.f, 0.f, 0.f);
+    for (uint32_t i = 0; i < nw; ++i) { t.x += s_red[i].x; t.y += s_red[i].y; t.z += s_red[i].z; }
+    return t;
+}
+
+// ---- one block per packet: detection -> coarse peak -> validity -> fractional CFO and rms
+__global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32_t len) {
+    extern __shared__ double smem_d[];
+    __shared__ double s_part[384];  // also used as float [3][256]
+    __shared__ float3 s_red[8];
+    __shared__ uint32_t s_min;
+    __shared__ unsigned long long s_best;
+    const phy_dims_t& d = p.d;
+    const uint32_t pkt = blockIdx.x, tid = threadIdx.x, nthr = blockDim.x;
+    const uint32_t n_pat = d.n_pat, pat = d.pat_len_os, stf_len = d.stf_len_os, step = p.step;
+    const uint32_t W = 4 * n_pat, Wc = 4 * (n_pat - 1);
+    const float prefactor = (float)n_pat / (float)(n_pat - 1);
+    const uint32_t bos = pat / 16;  // b * os
+    sync_result_dev_t& res = p.result[pkt];
+    float uw[8];
+    for (uint32_t i = 0; i + 1 < n_pat; ++i) uw[i] = c_cover[i] * c_cover[i + 1];
+
+    uint32_t j_from = (stf_len + pat + step - 1) / step - 1;  // first step whose end reaches ignore_before_index
+    uint32_t n_det_total = 0;
+    for (uint32_t attempt = 0; attempt < 8; ++attempt) {
+        // ---- detection: first (step, antenna) passing the gates
+        uint32_t best_j = 0xffffffffu, best_a = 0;
+        float best_metric = 0.f, best_rms = 0.f;
+        for (uint32_t a = 0; a < p.n_ant; ++a) {
+            double* Pp = smem_d;                    // [n_steps + 1]
+            double* Pr = Pp + p.n_steps + 1;
+            double* Pi = Pr + p.n_steps + 1;
+            const size_t o = ((size_t)pkt * p.n_ant + a) * p.n_steps;
+            for (uint32_t j = tid; j < p.n_steps; j += nthr) {
+                Pp[j + 1] = p.p_steps[o + j];
+                Pr[j + 1] = p.c_steps[o + j].x;
+                Pi[j + 1] = p.c_steps[o + j].y;
+            }
+            if (tid == 0) { Pp[0] = Pr[0] = Pi[0] = 0.0; s_min = 0xffffffffu; }
+            __syncthreads();
+            block_scan(Pp + 1, p.n_steps, s_part);
+            block_scan(Pr + 1, p.n_steps, s_part);
+            block_scan(Pi + 1, p.n_steps, s_part);
+            for (uint32_t j = j_from + tid; j < p.n_steps; j += nthr) {
+                const uint32_t n = (j + 1) * step;
+                if (n - step >= p.search_length || n > len || j + 1 < W) continue;
+                const float power = (float)(Pp[j + 1] - Pp[j + 1 - W]);
+                const float rms = sqrtf(power / (float)stf_len);
+                if (rms < p.rms_min || 2.0f < rms) continue;
+                // movsum_t::get_sum_back(2) / get_sum_front(2) as implemented by the reference (movsum.hpp:55-70):
+                // "front" = oldest + newest step, "back" = the two steps after the oldest
+                const float front = (float)(Pp[j + 2 - W] - Pp[j + 1 - W]) + (float)(Pp[j + 1] - Pp[j]);
+                const float back = (float)(Pp[j + 4 - W] - Pp[j + 2 - W]);
+                if (sqrtf(back) * 0.5 >= sqrtf(front)) continue;
+                float cr = 0.f, ci = 0.f;
+                for (uint32_t i = 0; i + 1 < n_pat; ++i) {
+                    const uint32_t lo = j + 1 - Wc + 4 * i;
+                    cr += uw[i] * (float)(Pr[lo + 4] - Pr[lo]);
+                    ci += uw[i] * (float)(Pi[lo + 4] - Pi[lo]);
+                }
+                const float t = prefactor * hypotf(cr, ci) / power;
+                const float metric = t * t;
+                if (metric < 0.18f || 1.50f < metric || !(0.18f < metric)) continue;
+                atomicMin(&s_min, j);
+            }
+            __syncthreads();
+            const uint32_t ja = s_min;
+            if (ja < best_j) {
+                best_j = ja; best_a = a;
+                const float power = (float)(Pp[ja + 1] - Pp[ja + 1 - W]);
+                float cr = 0.f, ci = 0.f;
+                for (uint32_t i = 0; i + 1 < n_pat; ++i) {
+                    const uint32_t lo = ja + 1 - Wc + 4 * i;
+                    cr += uw[i] * (float)(Pr[lo + 4] - Pr[lo]);
+                    ci += uw[i] * (float)(Pi[lo + 4] - Pi[lo]);
+                }
+                const float t = prefactor * hypotf(cr, ci) / power;
+                best_metric = t * t;
+                best_rms = sqrtf(power / (float)stf_len);
+            }
+            __syncthreads();
+        }
+        if (best_j == 0xffffffffu) break;  // nothing (more) in this window
+        ++n_det_total;
+        const uint32_t n_det = (best_j + 1) * step, r0 = n_det - pat;
+        if (r0 + stf_len > len) break;
+
+        // ---- coarse peak: per-sample metric over one STF after (detection - 1 pattern), smoothed, arg max
+        const uint32_t A0 = r0 - stf_len, S2 = 2 * stf_len;
+        float* Qr = reinterpret_cast<float*>(smem_d);   // prefix of q[m] = r[m - pat] conj(r[m]), [S2 + 1]
+        float* Qi = Qr + S2 + 1;
+        float* PW = Qi + S2 + 1;                        // prefix of abs(r[m])^2
+        float* M = PW + S2 + 1;                         // metric [stf_len]
+        float peak_metric[8];
+        uint32_t peak_index[8];
+        const uint32_t sm_right = bos, sm_len = 2 * bos + 1;
+        for (uint32_t a = 0; a < p.n_ant; ++a) {
+            const float2* x = p.iq + ((size_t)pkt * d.N_RX + a) * p.iq_stride + A0;
+            // serial prefix per thread chunk + chunk offsets (three arrays at once)
+            const uint32_t per = (S2 + nthr - 1) / nthr, lo = min(tid * per, S2), hi = min(lo + per, S2);
+            float sr = 0.f, si = 0.f, sp = 0.f;
+            for (uint32_t i = lo; i < hi; ++i) {
+                const float2 b = x[i];
+                sp += b.x * b.x + b.y * b.y;
+                if (i >= pat) {
+                    const float2 e = x[i - pat];
+                    sr += e.x * b.x + e.y * b.y;
+                    si += e.y * b.x - e.x * b.y;
+                }
+                Qr[i + 1] = sr; Qi[i + 1] = si; PW[i + 1] = sp;
+            }
+            float* part = reinterpret_cast<float*>(s_part);  // [3][nthr]
+            part[tid] = sr; part[nthr + tid] = si; part[2 * nthr + tid] = sp;
+            __syncthreads();
+            if (tid < 3) {
+                float acc = 0.f;
+                for (uint32_t t = 0; t < nthr; ++t) { const float v = part[tid * nthr + t]; part[tid * nthr + t] = acc; acc += v; }
+            }
+            if (tid == 0) { Qr[0] = Qi[0] = PW[0] = 0.f; }
+            __syncthreads();
+            const float o_r = part[tid], o_i = part[nthr + tid], o_p = part[2 * nthr + tid];
+            for (uint32_t i = lo; i < hi; ++i) { Qr[i + 1] += o_r; Qi[i + 1] += o_i; PW[i + 1] += o_p; }
+            __syncthreads();
+            for (uint32_t k = tid; k < stf_len; k += nthr) {
+                const uint32_t e = stf_len + k + 1;  // prefix index just after sample n = r0 + k
+                const float power = PW[e] - PW[e - stf_len];
+                float cr = 0.f, ci = 0.f;
+                for (uint32_t i = 0; i + 1 < n_pat; ++i) {
+                    const uint32_t hi2 = e - (n_pat - 2 - i) * pat, lo2 = hi2 - pat;
+                    cr += uw[i] * (Qr[hi2] - Qr[lo2]);
+                    ci += uw[i] * (Qi[hi2] - Qi[lo2]);
+                }
+                const float t = prefactor * hypotf(cr, ci) / power;
+                M[k] = t * t;
+            }
+            if (tid == 0) s_best = 0ull;
+            __syncthreads();
+            unsigned long long mine = 0ull;
+            for (uint32_t k = tid; k < stf_len; k += nthr) {
+                float s = 0.f;
+                const uint32_t k0 = k + 1 >= sm_len ? k + 1 - sm_len : 0;
+                for (uint32_t q = k0; q <= k; ++q) s += M[q];
+                const float mean = s / (float)sm_len;
+                // larger mean wins, first position on ties: key = (float bits, inverted position)
+                const unsigned long long key = ((unsigned long long)__float_as_uint(mean) << 32) | (0xffffffffu - k);
+                if (mean > 0.f && key > mine) mine = key;
+            }
+            atomicMax(&s_best, mine);
+            __syncthreads();
+            const unsigned long long bk = s_best;
+            peak_metric[a] = __uint_as_float((uint32_t)(bk >> 32));
+            peak_index[a] = bk ? r0 + (0xffffffffu - (uint32_t)bk) - sm_right : 0u;
+            __syncthreads();
+        }
+        // ---- validity (autocorrelator_peak.cpp:286-326)
+        float widx = 0.f, msum = 0.f, cpa[8];
+        uint32_t valid = 0;
+        for (uint32_t a = 0; a < 8; ++a) cpa[a] = 0.f;
+        for (uint32_t a = 0; a < p.n_ant; ++a) {
+            if (best_metric + (-0.25f) >= peak_metric[a]) continue;
+            if ((long long)n_det + (long long)(-0.3 * (double)stf_len) >= (long long)peak_index[a]) continue;
+            cpa[a] = peak_metric[a];
+            widx += peak_metric[a] * (float)peak_index[a];
+            msum += peak_metric[a];
+            ++valid;
+        }
+        if (!valid) { j_from = best_j + 1; continue; }
+        const uint32_t coarse = (uint32_t)roundf(widx / msum) - (stf_len - 1);
+        // ---- rms and fractional CFO over the STF at the coarse peak (autocorrelator_peak.cpp:328-360)
+        float wcfo = 0.f, ms2 = 0.f, rms_arr[8];
+        uint32_t strongest = 0;
+        for (uint32_t a = 0; a < 8; ++a) rms_arr[a] = 0.f;
+        for (uint32_t a = 0; a < p.n_ant; ++a) {
+            if (cpa[a] <= 0.f) continue;
+            if (cpa[a] > cpa[strongest]) strongest = a;
+            const float2* x = p.iq + ((size_t)pkt * d.N_RX + a) * p.iq_stride + coarse;
+            float3 acc = make_float3(0.f, 0.f, 0.f);
+            for (uint32_t i = tid; i < stf_len; i += nthr) {
+                const float2 b = x[i];
+                acc.z += b.x * b.x + b.y * b.y;
+                if (i + pat < stf_len) {
+                    const float2 e = x[i + pat];
+                    const float w = uw[i / pat];
+                    acc.x += w * (b.x * e.x + b.y * e.y);
+                    acc.y += w * (b.y * e.x - b.x * e.y);
+                }
+            }
+            acc = block_sum3(acc, s_red);
+            rms_arr[a] = sqrtf(acc.z / (float)stf_len);
+            wcfo += peak_metric[a] * atan2f(acc.y, acc.x) / (float)pat;
+            ms2 += peak_metric[a];
+        }
+        if (tid == 0) {
+            res.detected = 1;
+            res.detection_time_local = n_det; res.detection_ant_idx = best_a;
+            res.detection_metric = best_metric; res.detection_rms = best_rms;
+            res.coarse_peak_time_local = coarse;
+            for (uint32_t a = 0; a < 8; ++a) { res.coarse_peak_array[a] = cpa[a]; res.rms_array[a] = rms_arr[a]; }
+            res.cfo_fractional_rad = wcfo / ms2;
+            res.cfo_integer_rad = 0.f;  // coarse_peak_f_domain.cpp:94-201: not implemented in the reference
+            res.N_eff_TX = 0; res.fine_peak_time_local = 0;
+            res.n_detections = n_det_total; res.strongest_ant = strongest;
+        }
+        return;
+    }
+    if (tid == 0) {
+        res.detected = 0;
+        res.n_detections = n_det_total;
+        res.N_eff_TX = 0; res.fine_peak_time_local = 0; res.coarse_peak_time_local = 0;
+        res.cfo_fractional_rad = 0.f; res.cfo_integer_rad = 0.f; res.strongest_ant = 0;
+        for (uint32_t a = 0; a < 8; ++a) { res.coarse_peak_array[a] = 0.f; res.rms_array[a] = 0.f; }
+    }
+}
+
+// ---- one warp per detection step: c_j = sum r[m - pat] conj(r[m]), p_j = sum abs(r[m])^2 over the step
+__global__ void __launch_bounds__(256) k_sync_steps(const sync_params_t p) {
+    const uint32_t j = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const uint32_t a = blockIdx.y, pkt = blockIdx.z;
+    if (j >= p.n_steps) return;
+    const float2* x = p.iq + ((size_t)pkt * p.d.N_RX + a) * p.iq_stride;
+    const uint32_t pat = p.d.pat_len_os, m0 = j * p.step;
+    float cr = 0.f, ci = 0.f, pw = 0.f;
+    for (uint32_t i = lane; i < p.step; i += 32) {
+        const float2 b = x[m0 + i];
+        pw += b.x * b.x + b.y * b.y;
+        if (m0 >= pat) {
+            const float2 e = x[m0 + i - pat];
+            cr += e.x * b.x + e.y * b.y;
+            ci += e.y * b.x - e.x * b.y;
+        }
+    }
+    cr = warp_sum(cr); ci = warp_sum(ci); pw = warp_sum(pw);
+    if (lane == 0) {
+        const size_t o = ((size_t)pkt * p.n_ant + a) * p.n_steps + j;
+        p.c_steps[o] = make_float2(cr, ci);
+        p.p_steps[o] = pw;
+    }
+}
+
+// ---- fine peak: cross-correlation of the CFO pre-corrected window on the strongest antenna with one STF template.
+// grid (template, packet).  A thread owns XC_LAGS consecutive lags and a slice of the template; the window
+// slides through registers, so eight complex MACs cost two shared loads.  The window is stored with one pad
+// element per eight (threads of a warp start eight elements apart).
+constexpr uint32_t XC_LAGS = 8, XC_THREADS = 512;
+__device__ __forceinline__ uint32_t xc_pos(uint32_t e) { return e + (e >> 3); }
+
+__global__ void __launch_bounds__(XC_THREADS) k_sync_xcorr(const sync_params_t p, uint32_t len, uint32_t IC) {
+    extern __shared__ float2 smem_x[];
+    __shared__ unsigned long long s_best;
+    const phy_dims_t& d = p.d;
+    const uint32_t tpl = blockIdx.x, pkt = blockIdx.y, tid = threadIdx.x;
+    const uint32_t S = d.stf_len_os, sl = d.pat_len_os, n_lag = 2 * sl + 1;  // 16 b os samples to either side
+    const uint32_t LT = (n_lag + XC_LAGS - 1) / XC_LAGS, n_lag_pad = LT * XC_LAGS;
+    const sync_result_dev_t& res = p.result[pkt];
+    float2* out = p.xc + (size_t)pkt * p.n_tpl + tpl;
+    const long long w0 = (long long)res.coarse_peak_time_local - sl;
+    if (!res.detected || w0 < 0 || w0 + n_lag + S - 1 > len) {
+        if (tid == 0) *out = make_float2(-1.f, 0.f);
+        return;
+    }
+    float2* mix = smem_x;                              // [xc_pos(n_lag_pad + S)]
+    float2* tp = mix + xc_pos(n_lag_pad + S) + 1;      // [S]
+    float2* part = tp + S;                             // [IC][n_lag_pad]
+    const float2* x = p.iq + ((size_t)pkt * d.N_RX + res.strongest_ant) * p.iq_stride + w0;
+    const double inc = (double)(res.cfo_fractional_rad + res.cfo_integer_rad);
+    const uint32_t n_mix = n_lag + S - 1;
+    for (uint32_t i = tid; i < n_lag_pad + S; i += XC_THREADS) {
+        float2 r = make_float2(0.f, 0.f);
+        if (i < n_mix) {
+            const float2 v = x[i];
+            double sd, cd;
+            sincos(inc * (double)i, &sd, &cd);
+            const float cs = (float)cd, sn = (float)sd;
+            r = make_float2(v.x * cs - v.y * sn, v.x * sn + v.y * cs);
+        }
+        mix[xc_pos(i)] = r;
+    }
+    const float2* T = p.templates + (size_t)tpl * S;
+    for (uint32_t i = tid; i < S; i += XC_THREADS) tp[i] = T[i];
+    if (tid == 0) s_best = 0ull;
+    __syncthreads();
+    if (tid < LT * IC) {
+        const uint32_t lt = tid % LT, ic = tid / LT, j0 = lt * XC_LAGS;
+        uint32_t chunk = ((S + IC - 1) / IC + 7) & ~7u;
+        const uint32_t i0 = min(ic * chunk, S), i1 = min(i0 + chunk, S);
+        float ar[XC_LAGS], ai[XC_LAGS];
+        float2 w[XC_LAGS];
+#pragma unroll
+        for (uint32_t k = 0; k < XC_LAGS; ++k) { ar[k] = ai[k] = 0.f; }
+#pragma unroll
+        for (uint32_t k = 0; k + 1 < XC_LAGS; ++k) w[k] = mix[xc_pos(j0 + i0 + k)];
+        for (uint32_t i = i0; i < i1; i += 8) {
+#pragma unroll
+            for (uint32_t u = 0; u < 8; ++u) {
+                w[(u + 7) & 7] = mix[xc_pos(j0 + i + u + 7)];
+                const float2 t = tp[i + u];
+#pragma unroll
+                for (uint32_t k = 0; k < XC_LAGS; ++k) {
+                    const float2 m = w[(u + k) & 7];
+                    ar[k] = fmaf(m.x, t.x, fmaf(m.y, t.y, ar[k]));
+                    ai[k] = fmaf(m.y, t.x, fmaf(-m.x, t.y, ai[k]));
+                }
+            }
+        }
+#pragma unroll
+        for (uint32_t k = 0; k < XC_LAGS; ++k) part[ic * n_lag_pad + j0 + k] = make_float2(ar[k], ai[k]);
+    }
+    __syncthreads();
+    unsigned long long mine = 0ull;
+    for (uint32_t j = tid; j < n_lag; j += XC_THREADS) {
+        float re = 0.f, im = 0.f;
+        for (uint32_t ic = 0; ic < IC; ++ic) { re += part[ic * n_lag_pad + j].x; im += part[ic * n_lag_pad + j].y; }
+        const float m2 = re * re + im * im;
+        const unsigned long long key = ((unsigned long long)__float_as_uint(m2) << 32) | (0xffffffffu - j);
+        if (key > mine) mine = key;
+    }
+    atomicMax(&s_best, mine);
+    __syncthreads();
+    if (tid == 0) {
+        const unsigned long long bk = s_best;
+        *out = make_float2(sqrtf(__uint_as_float((uint32_t)(bk >> 32))), (float)(0xffffffffu - (uint32_t)bk));
+    }
+}
+
+// ---- N_eff_TX decision, fine peak, hand-over to the synchronised receiver (crosscorrelator.cpp:205-249)
+__global__ void k_sync_final(const sync_params_t p, uint32_t n, uint32_t len) {
+    const uint32_t pkt = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pkt >= n) return;
+    sync_result_dev_t& res = p.result[pkt];
+    const uint32_t sl = p.d.pat_len_os;
+    if (res.detected) {
+        float best = 0.f;
+        uint32_t best_tpl = 0, best_idx = 0;
+        bool ok = true;
+        for (uint32_t t = 0; t < p.n_tpl; ++t) {
+            const float2 v = p.xc[(size_t)pkt * p.n_tpl + t];
+            if (v.x < 0.f) ok = false;  // window left the buffer
+            if (best < v.x) { best = v.x; best_tpl = t; best_idx = (uint32_t)v.y; }
+        }
+        if (ok) {
+            res.N_eff_TX = 1u << best_tpl;
+            res.fine_peak_time_local = res.coarse_peak_time_local - sl + best_idx;
+        } else {
+            res.detected = 0;
+        }
+    }
+    if (p.rx_state) {
+        rx_state_t s = {};
+        if (res.detected && (size_t)res.fine_peak_time_local + p.d.n_no_gi_os <= p.iq_stride) {
+            s.t0 = (int32_t)res.fine_peak_time_local;
+            s.inc0 = res.cfo_fractional_rad + res.cfo_integer_rad;
+            for (uint32_t a = 0; a < 8; ++a) s.rms[a] = res.rms_array[a];
+        } else {
+            s.t0 = 0;  // nothing found: the receiver runs on the window start and fails its CRCs
+            for (uint32_t a = 0; a < 8; ++a) s.rms[a] = 1.f;
+        }
+        p.rx_state[pkt] = s;
+    }
+}
+
+cudaError_t launch_sync(const sync_params_t& p, uint32_t n, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    const phy_dims_t& d = p.d;
+    const uint32_t len = (uint32_t)p.iq_stride;
+    k_sync_steps<<<dim3((p.n_steps + 7) / 8, p.n_ant, n), 256, 0, st>>>(p);
+    const size_t sm_det = 3 * (size_t)(p.n_steps + 1) * sizeof(double);
+    const size_t sm_peak = (3 * (size_t)(2 * d.stf_len_os + 1) + d.stf_len_os) * sizeof(float);
+    const size_t sm2 = sm_det > sm_peak ? sm_det : sm_peak;
+    cudaError_t e = cudaFuncSetAttribute(k_sync_peak, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
+    if (e != cudaSuccess) return e;
+    k_sync_peak<<<n, 256, sm2, st>>>(p, len);
+    const uint32_t n_lag = 2 * d.pat_len_os + 1, LT = (n_lag + XC_LAGS - 1) / XC_LAGS, n_lag_pad = LT * XC_LAGS;
+    uint32_t IC = XC_THREADS / LT;
+    const uint32_t ic_max = d.stf_len_os / 32 ? d.stf_len_os / 32 : 1;
+    if (IC > ic_max) IC = ic_max;
+    if (IC == 0) return cudaErrorInvalidConfiguration;  // more than XC_THREADS * XC_LAGS lags
+    const size_t sm3 = ((size_t)(n_lag_pad + d.stf_len_os) * 9 / 8 + 2 + d.stf_len_os + (size_t)IC * n_lag_pad) * sizeof(float2);
+    e = cudaFuncSetAttribute(k_sync_xcorr, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm3);
+    if (e != cudaSuccess) return e;
+    k_sync_xcorr<<<dim3(p.n_tpl, n), XC_THREADS, sm3, st>>>(p, len, IC);
+    k_sync_final<<<(n + 127) / 128, 128, 0, st>>>(p, n, len);
+    return cudaGetLastError();
+}
+
+}  // namespace dnrp

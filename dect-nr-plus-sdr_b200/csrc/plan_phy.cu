@@ -109,8 +109,46 @@ int build_phy_plan(dnrp_ctx* c) {
         d.wiener_lr[i] = {c->d_wiener_lr[i].idx_pilot.p, c->d_wiener_lr[i].idx_weight.p,
                           c->d_wiener_lr[i].weights.p, Llr.n_interp, Llr.n_t};
     }
-    // RX window: the packet plus room for the synchronisation offset t0 (at most one STF) in front
-    c->rx_stride = (d.n_packet_os + d.stf_len_os + 3) & ~3u;
+    // RX window: the packet plus room for two STFs (the detection ignores the first STF + 1 pattern of a window
+    // and the fine search looks one pattern to either side of the coarse peak)
+    c->rx_stride = (d.n_packet_os + 2 * d.stf_len_os + 3) & ~3u;
+    // packet synchronisation: time-domain STF of a single stream for every N_eff_TX the receiver has to
+    // tell apart (stf_template.cpp:81-204 for L = M = 1): scale 1/sqrt(N_OCC/4), unnormalised inverse DFT,
+    // long CP, cover sequence.  Only every 4th subcarrier is occupied, so a direct sparse IDFT is cheap.
+    {
+        std::vector<float2> tpl;
+        c->sync_n_tpl = 0;
+        const double scale = 1.0 / std::sqrt((double)(d.N_OCC / 4)), pi = 3.14159265358979323846;
+        for (uint32_t ntx = 1; ntx <= d.N_eff_TX; ntx <<= 1, ++c->sync_n_tpl) {
+            const std::vector<int8_t> sgn = spec::build_stf_sign(d.b, ntx);
+            std::vector<double> xr(d.N_os, 0.0), xi(d.N_os, 0.0);
+            for (uint32_t k = 0; k < d.Nk; ++k) {
+                if (!sgn[k]) continue;
+                const int bin = (int)k - (int)(d.N_OCC / 2);
+                const double yr = sgn[k] * scale * std::sqrt(0.5), yi = yr;  // +-exp(j pi/4) * scale
+                for (uint32_t n = 0; n < d.N_os; ++n) {
+                    const long long m = ((long long)bin * n) % (long long)d.N_os;
+                    const double ph = 2.0 * pi * (double)m / (double)d.N_os;
+                    const double cs = std::cos(ph), sn = std::sin(ph);
+                    xr[n] += yr * cs - yi * sn;
+                    xi[n] += yr * sn + yi * cs;
+                }
+            }
+            for (uint32_t n = 0; n < d.stf_len_os; ++n) {
+                const uint32_t src = (n + d.N_os - d.stf_cp_os % d.N_os) % d.N_os;
+                const float cv = spec::stf_cover(n / d.pat_len_os);
+                tpl.push_back(make_float2((float)xr[src] * cv, (float)xi[src] * cv));
+            }
+        }
+        UP(c->d_sync_tpl.upload(tpl));
+        c->sync_step = d.pat_len_os / 4;
+        c->sync_n_steps = c->rx_stride / c->sync_step;
+        const size_t nb = (size_t)c->B * d.N_RX * c->sync_n_steps;
+        UP(c->d_sync_c.alloc(nb));
+        UP(c->d_sync_p.alloc(nb));
+        UP(c->d_sync_xc.alloc((size_t)c->B * c->sync_n_tpl));
+        UP(c->d_sync_result.alloc(c->B));
+    }
     c->cls_stride = (d.N_eff_TX == 8 ? 2 : 1) * d.n_drs + 2;
     const size_t B = c->B;
     UP(c->d_iq_rx.alloc(B * d.N_RX * c->rx_stride));

@@ -150,9 +150,39 @@ typedef struct {
 /* samples per antenna reserved for one packet's IQ window in iq_in */
 uint32_t dnrp_rx_stride(const dnrp_ctx_t* ctx);
 
+/* ---- packet synchronisation -------------------------------------------------------------------
+ * sync_report_t as sync_chunk_t::search fills it (lib/src/phy/rx/sync/sync_chunk.cpp:120-215,
+ * lib/include/dectnrp/phy/rx/sync/sync_report.hpp:41-111), times relative to the window start. */
+typedef struct {
+    uint32_t detected;                 /* 0: no packet in this window, the other fields are zero */
+    uint32_t detection_time_local;
+    uint32_t detection_ant_idx;
+    float detection_metric;
+    float detection_rms;
+    uint32_t coarse_peak_time_local;
+    float coarse_peak_array[8];        /* 0 for antennas whose coarse peak was not valid */
+    float rms_array[8];
+    float cfo_fractional_rad;
+    float cfo_integer_rad;
+    uint32_t N_eff_TX;
+    uint32_t fine_peak_time_local;
+    uint32_t n_detections;             /* detections in this window incl. the ones dropped as invalid */
+    uint32_t strongest_ant;            /* antenna the cross-correlation ran on */
+} dnrp_sync_result_t;
+
+/* sync_chunk_t::search for n IQ windows, first packet of each window: autocorrelator_detection_t,
+ * autocorrelator_peak_t (coarse peak, fractional CFO, rms), crosscorrelator_t (N_eff_TX, fine peak); constants of
+ * sync_param.hpp as shipped.  iq_in [n][N_RX][dnrp_rx_stride()] host windows or NULL (windows already on the
+ * device).  search_length = samples the detection may consume (0: window minus one STF and one pattern).
+ * out [n] may be NULL.  The results also stay on the device: a following dnrp_rx_pcc_batch with sync = NULL
+ * runs on them (packets not detected are processed at offset 0 and fail their CRCs). */
+int dnrp_sync_batch(dnrp_ctx_t* ctx, uint32_t n, const dnrp_cf32_t* iq_in, uint32_t search_length,
+                    dnrp_sync_result_t* out);
+
 /* rx_synced_t::demoddecod_rx_pcc (lib/src/phy/rx/rx_synced/rx_synced.cpp:115-274) for n packets.
  * iq_in [n][N_RX][dnrp_rx_stride()] host IQ windows (NULL: the windows already resident on the device,
- * e.g. written by dnrp_channel_batch); sync [n]; out [n].  Runs the whole front end of the packet (STF
+ * e.g. written by dnrp_channel_batch); sync [n] or NULL (use the results of the preceding dnrp_sync_batch,
+ * which stay on the device); out [n].  Runs the whole front end of the packet (STF
  * stage, all data field FFTs, DRS zero forcing, SNR classes) and the blind PLCF decoding. */
 int dnrp_rx_pcc_batch(dnrp_ctx_t* ctx, uint32_t n, const dnrp_cf32_t* iq_in, const dnrp_sync_report_t* sync,
                       dnrp_pcc_report_t* out);
@@ -227,7 +257,8 @@ typedef enum {
     DNRP_KERNEL_RX_DEMAP_PDC = 2,
     DNRP_KERNEL_RX_STF = 3,
     DNRP_KERNEL_DERM_PDC = 4,
-    DNRP_KERNEL_COUNT = 5
+    DNRP_KERNEL_SYNC = 5,            /* the four synchronisation kernels together */
+    DNRP_KERNEL_COUNT = 6
 } dnrp_kernel_t;
 int dnrp_kernel_time_enable(dnrp_ctx_t* ctx, int enable);
 int dnrp_kernel_time_read(dnrp_ctx_t* ctx, int kernel, float* ms_total, uint32_t* launches);

@@ -1,0 +1,64 @@
+"""ORACLE (test infrastructure, not product code) -- Python front of oracle/sync.c (packet synchronisation:
+reference lib/src/phy/rx/sync/{sync_chunk,autocorrelator_detection,autocorrelator_peak,crosscorrelator,
+stf_template}.cpp).  Parity unpinned (see sync.c header)."""
+import ctypes as C
+
+import numpy as np
+
+from . import lib, spec
+
+
+class Report(C.Structure):
+    _fields_ = [("detected", C.c_int32), ("detection_ant_idx", C.c_int32), ("detection_time_local", C.c_int32),
+                ("detection_time_with_jump_back_local", C.c_int32), ("detection_rms", C.c_float),
+                ("detection_metric", C.c_float), ("coarse_peak_time_local", C.c_int32),
+                ("coarse_peak_array", C.c_float * 8), ("rms_array", C.c_float * 8), ("cfo_fractional_rad", C.c_float),
+                ("cfo_integer_rad", C.c_float), ("N_eff_TX", C.c_int32), ("fine_peak_time_local", C.c_int32),
+                ("n_detections", C.c_int32)]
+
+
+def stf_template(u, b, N_eff_TX, os=1):
+    """stf_template_t::generate_stf_time_domain (stf_template.cpp:81-204) for L = M = 1: the transmitter's STF of a
+    single stream, scale 1/sqrt(N_OCC/4), unnormalised IFFT, long CP, cover sequence"""
+    N_OCC, N_os = 56 * b, 64 * b * os
+    cp = (N_os // 4) * (3 if u == 1 else 5)
+    y = spec.stf_filled(b, N_eff_TX) * np.float32(1.0 / np.sqrt(np.float32(N_OCC // 4)))
+    X = np.zeros(N_os, dtype=np.complex128)
+    X[:N_OCC // 2 + 1] = y[N_OCC // 2:]
+    X[N_os - N_OCC // 2:] = y[:N_OCC // 2]
+    x = (np.fft.ifft(X) * N_os).astype(np.complex64)
+    t = x[(np.arange(cp + N_os) - cp) % N_os].copy()
+    npat = 7 if u == 1 else 9
+    plen = t.size // npat
+    for p in range(npat):
+        t[p * plen:(p + 1) * plen] *= np.float32(spec.STF_COVER[p])
+    return t
+
+
+def templates(u, b, N_eff_TX_max, os=1):
+    n = [1, 2, 4, 8]
+    return np.stack([stf_template(u, b, v, os) for v in n if v <= N_eff_TX_max])
+
+
+def search(iq, u, b, os=1, N_eff_TX_max=1, search_length=None):
+    """iq [n_ant][len] complex64 -> Report (first packet found in the window)"""
+    L = lib()
+    iq = np.ascontiguousarray(iq, dtype=np.complex64)
+    n_ant, n = iq.shape
+    tpl = np.ascontiguousarray(templates(u, b, N_eff_TX_max, os))
+    stf_len = tpl.shape[1]
+    if search_length is None:
+        search_length = n - stf_len - stf_len // (7 if u == 1 else 9)
+    rep = Report()
+    L.orc_sync_search.restype = C.c_int
+    L.orc_sync_search.argtypes = [C.c_void_p, C.c_long, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int,
+                                  C.c_int, C.c_double, C.c_void_p]
+    rc = L.orc_sync_search(iq.ctypes.data, n, n, n_ant, u, b, os, tpl.ctypes.data, tpl.shape[0], int(search_length),
+                           float(u * b * os * 1.728e6), C.addressof(rep))
+    if rc == -2:
+        # the fine search window leaves the buffer (cannot happen in the reference's ring buffer): the product
+        # reports such a window as "not detected", and so does this front
+        rep.detected = 0
+    elif rc != 0:
+        raise RuntimeError("oracle sync failed (rc=%d)" % rc)
+    return rep
