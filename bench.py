@@ -1,9 +1,9 @@
 #!/usr/bin/env python
 """bench.py -- decoded PDC throughput of the DECT NR+ receive hot path on B200.
 
-One "step" = one pass of the synchronised receiver (STF stage, FFTs, DRS zero forcing, Wiener
-interpolation, equalisation, demapping, blind PLCF decode, de-rate-matching/HARQ, turbo decode, CRC) over one
-batch of synthetic packets of BASELINE.json configs[1] (mu=1 beta=16 N_TX=1 64-QAM, AWGN 25 dB).
+One "step" = one pass of the receiver from raw IQ windows to transport blocks (packet synchronisation, STF stage,
+FFTs, DRS zero forcing, Wiener interpolation, equalisation, demapping, blind PLCF decode, de-rate-matching/HARQ,
+turbo decode, CRC) over one batch of synthetic packets of BASELINE.json configs[1] (mu=1 beta=16 N_TX=1 64-QAM, AWGN 25 dB).
 
   value   decoded PDC Mbit/s (N_TB_bits of CRC-passing packets / device time), IQ windows resident in HBM
   e2e     same metric through the C ABI with HOST buffers (pinned IQ in, transport blocks + reports out)
@@ -94,10 +94,13 @@ def cpu_windows(ps, N_RX, snr_db, mode, n_distinct, seed):
         g = np.ones((N_RX, N_TX), dtype=np.complex64)
         if mode == 1:
             g = ((rng.standard_normal((N_RX, N_TX)) + 1j * rng.standard_normal((N_RX, N_TX))) / np.sqrt(2))
-        y = (g @ iq).astype(np.complex64)
+        stf_len = ps["N_samples_STF"]
+        t0 = int(rng.integers(stf_len // 2, 2 * stf_len - 4))
+        y = np.zeros((N_RX, L + 2 * stf_len), dtype=np.complex64)
+        y[:, t0:t0 + L] = g @ iq
         sigma = 10 ** (-snr_db / 20)
         y = y + (sigma / np.sqrt(2)) * (rng.standard_normal(y.shape) + 1j * rng.standard_normal(y.shape))
-        wins.append(np.ascontiguousarray(np.pad(y, ((0, 0), (0, 64))), dtype=np.complex64))
+        wins.append(np.ascontiguousarray(y, dtype=np.complex64))
         tbs.append(tb)
     return wins, tbs
 
@@ -105,7 +108,7 @@ def cpu_windows(ps, N_RX, snr_db, mode, n_distinct, seed):
 def cpu_rx_rate(workload, n_packets, threads):
     """decoded PDC Mbit/s of the oracle receiver (rx_synced restatement + PLCF blind decode + PDC decode)"""
     from concurrent.futures import ThreadPoolExecutor
-    from oracle import fec, rx, spec
+    from oracle import fec, rx, spec, sync as osync
     psdef, N_RX, snr_db, mode = WORKLOADS[workload]
     ps = spec.get_packet_sizes(*psdef)
     wins, tbs = cpu_windows(ps, N_RX, snr_db, mode, 8, seed=7)
@@ -113,7 +116,13 @@ def cpu_rx_rate(workload, n_packets, threads):
     gold = fec.pdc_gold(NETWORK_ID, 1, ps["G"])
 
     def one(i):
-        r = cfg.rx_packet(wins[i % len(wins)], want_Y=False)
+        w = wins[i % len(wins)]
+        s = osync.search(w, psdef[0], psdef[1], N_eff_TX_max=ps["N_eff_TX"])
+        if not s.detected:
+            return False
+        r = cfg.rx_packet(w, t0=s.fine_peak_time_local, cfo_fractional_rad=s.cfo_fractional_rad,
+                          cfo_integer_rad=s.cfo_integer_rad, rms=np.array(s.rms_array[:], dtype=np.float32),
+                          want_Y=False)
         fec.pcc_decode(r["llr_pcc"], 1)
         fec.pcc_decode(r["llr_pcc"], 2)
         ok, out, _ = fec.pdc_decode(r["llr_pdc"], ps, 0, gold)
@@ -135,7 +144,10 @@ def run_reference(args):
     import oracle
     oracle.build()
     threads = os.cpu_count() or 1
-    per_step = args.cpu_packets or threads * 24
+    per_step = args.cpu_packets
+    if not per_step:  # about 10 s of CPU work per step
+        _, pps0, _, _, _ = cpu_rx_rate(args.workload, threads * 4, threads)
+        per_step = int(min(max(pps0 * 10.0, threads * 8), 100000))
     for _ in range(min(args.warmup, 1)):
         cpu_rx_rate(args.workload, threads, threads)
     rates, pkts, t_all = [], [], 0.0
@@ -183,7 +195,8 @@ def run_b200(args):
     rng = np.random.default_rng(1000 + rank)
     tb = rng.integers(0, 256, (P, ps["N_TB_byte"]), dtype=np.uint8)
     plcf = rng.integers(0, 256, (P, 10), dtype=np.uint8)
-    t0 = rng.integers(0, 64, P).astype(np.uint32)
+    stf_len, pat = ps["N_samples_STF"], 16 * psdef[1]
+    t0 = rng.integers(2 * pat, 2 * stf_len - 4, P).astype(np.uint32)   # unknown to the receiver: found by sync
     phy.tx(plcf, tb, fetch=False)
     host_iq = torch.empty((P, N_RX, stride), dtype=torch.complex64, pin_memory=True)
     win = host_iq.numpy()
@@ -191,13 +204,15 @@ def run_b200(args):
     tb_pinned = torch.empty((P, ps["N_TB_byte"]), dtype=torch.uint8, pin_memory=True)
 
     def e2e_step():
-        pcc = phy.rx_pcc(win, t0=t0)
+        sres = phy.sync(iq=win)
+        pcc = phy.rx_pcc(None, n=P, sync="device")
         ok, tb_out, snr, nit = phy.rx_pdc(P, tb_out=tb_pinned.numpy())
-        return pcc, ok, tb_out
+        return pcc, ok, tb_out, sres
 
     # correctness gate before any timing: every CRC-passing TB must equal what was sent
-    pcc, ok, tb_out = e2e_step()
+    pcc, ok, tb_out, sres = e2e_step()
     n_ok = int(ok.sum())
+    n_sync_ok = int(((sres.detected == 1) & (sres.fine_peak_time_local == t0)).sum())
     if not np.array_equal(tb_out[ok], tb[ok]):
         raise SystemExit("bench.py: decoded transport blocks differ from the transmitted ones")
     n_plcf_ok = int(pcc.plcf_ok[:, 0].sum())
@@ -209,13 +224,13 @@ def run_b200(args):
 
     # ---- resident steps: IQ windows + sync reports already in HBM (left there by e2e_step)
     for _ in range(args.warmup):
-        phy.time_stage(product.STAGE_RX_CHAIN, P, reps=1)
+        phy.time_stage(product.STAGE_SYNC_RX_CHAIN, P, reps=1)
     phy.kernel_time_enable(True)
     clocks = ClockSampler(local)
     barrier()
     clocks.start()
     l0 = phy.launch_count()
-    ms_step = phy.time_stage(product.STAGE_RX_CHAIN, P, reps=args.steps)   # CUDA events on the kernels' stream
+    ms_step = phy.time_stage(product.STAGE_SYNC_RX_CHAIN, P, reps=args.steps)   # CUDA events on the kernels' stream
     launches = phy.launch_count() - l0
     barrier()
     clk = clocks.stop()
@@ -223,7 +238,8 @@ def run_b200(args):
     others = {name: phy.kernel_time_read(k) for name, k in (("k_rx_fft", product.KERNEL_RX_FFT),
                                                             ("k_rx_demap_pdc", product.KERNEL_RX_DEMAP_PDC),
                                                             ("k_rx_stf", product.KERNEL_RX_STF),
-                                                            ("k_derm_pdc", product.KERNEL_DERM_PDC))}
+                                                            ("k_derm_pdc", product.KERNEL_DERM_PDC),
+                                                            ("k_sync_x4", product.KERNEL_SYNC))}
     phy.kernel_time_enable(False)
     ok_res = phy.tap(product.TAP_TB_OK, P).reshape(-1).astype(bool)
     n_ok_res = int(ok_res.sum())
@@ -240,12 +256,13 @@ def run_b200(args):
 
     # ---- reduce over ranks: max of the times, sum of the counters (the one collective of this path)
     times = torch.tensor([ms_step, e2e_s * 1e3], dtype=torch.float64, device="cuda")
-    counters = torch.tensor([P, n_ok_res, n_ok_res * ps["N_TB_bits"], n_ok, n_plcf_ok], dtype=torch.int64, device="cuda")
+    counters = torch.tensor([P, n_ok_res, n_ok_res * ps["N_TB_bits"], n_ok, n_plcf_ok, n_sync_ok], dtype=torch.int64,
+                            device="cuda")
     if world > 1:
         dist.all_reduce(times, op=dist.ReduceOp.MAX)
         dist.all_reduce(counters, op=dist.ReduceOp.SUM)
     ms_step_max, e2e_ms_max = [float(v) for v in times.cpu()]
-    tot_P, tot_ok, tot_bits, tot_ok_e2e, tot_plcf = [int(v) for v in counters.cpu()]
+    tot_P, tot_ok, tot_bits, tot_ok_e2e, tot_plcf, tot_sync = [int(v) for v in counters.cpu()]
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
@@ -274,21 +291,26 @@ def run_b200(args):
         import oracle
         oracle.build()
         threads = os.cpu_count() or 1
-        n_cpu = args.cpu_packets or threads * 48
+        n_cpu = args.cpu_packets
+        if not n_cpu:  # calibrate on a short run, then size the sample to about 15 s of CPU work
+            _, pps0, _, _, _ = cpu_rx_rate(args.workload, threads * 4, threads)
+            n_cpu = int(min(max(pps0 * 15.0, threads * 8), 200000))
         mbps, pps, n_ok_cpu, dt, _ = cpu_rx_rate(args.workload, n_cpu, threads)
         cpu = {"value": mbps, "unit": "Mbit/s", "cores": threads, "kind": "port",
                "sample": "%d packets of %s (%.1f s, %d CRC ok), scalar C oracle" % (n_cpu, args.workload, dt, n_ok_cpu)}
 
-    h2d = P * N_RX * stride * 8 + P * 48
-    d2h = P * ps["N_TB_byte"] + P * (ps["C"] + 8 + 76)
+    h2d = P * N_RX * stride * 8
+    d2h = P * ps["N_TB_byte"] + P * (ps["C"] + 8 + 76 + 112)
     out = {
         "metric": "decoded_pdc_throughput", "value": value, "unit": "Mbit/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_step_max, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "int16+f32", "data": "synthetic",
         "config": {"workload": args.workload, "packets_per_step_per_gpu": P, "packets_per_s": tot_P / (ms_step_max * 1e-3),
-                   "crc_ok": tot_ok, "packets": tot_P, "plcf_ok": tot_plcf, "N_TB_bits": ps["N_TB_bits"],
-                   "stages": "rx_synced chain: STF stage, FFT+DRS ZF, SNR class, PCC demap+PLCF decode, PDC "
-                             "demap, de-rate-match+HARQ+turbo decode+CRC (sync search not in the step)",
+                   "crc_ok": tot_ok, "packets": tot_P, "plcf_ok": tot_plcf, "sync_exact": tot_sync,
+                   "N_TB_bits": ps["N_TB_bits"],
+                   "stages": "raw IQ windows -> TBs: sync (detection, coarse peak, CFO, xcorr fine peak), STF stage, "
+                             "FFT+DRS ZF, SNR class, PCC demap+PLCF decode, PDC demap, de-rate-match+HARQ, turbo "
+                             "decode+CRC",
                    "l2": "inputs larger than L2 (%.0f MB of IQ per step)" % (P * N_RX * stride * 8 / 1e6)},
         "clocks": clk,
         "e2e": {"value": e2e_value, "unit": "Mbit/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,

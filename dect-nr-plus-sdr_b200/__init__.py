@@ -331,4 +331,4 @@ class Phy:
 
 
 STAGE_FEC_DECODE_TB, STAGE_FEC_ENCODE, STAGE_FEC_DECODE_PLCF = 1, 2, 3
-STAGE_RX_CHAIN, STAGE_TX_CHAIN, STAGE_CHANNEL = 4, 5, 6
+STAGE_RX_CHAIN, STAGE_TX_CHAIN, STAGE_CHANNEL, STAGE_SYNC, STAGE_SYNC_RX_CHAIN = 4, 5, 6, 7, 8

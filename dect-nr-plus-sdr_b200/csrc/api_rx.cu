@@ -1,5 +1,6 @@
 // api_rx.cu -- receiver side of the C ABI: batched rx_synced_t::demoddecod_rx_pcc / _pdc
 // (reference lib/src/phy/rx/rx_synced/rx_synced.cpp:186-436) on the context's device buffers.
+#include <cmath>
 #include <cstring>
 #include "ctx.hpp"
 

@@ -244,7 +244,9 @@ typedef enum {
     DNRP_STAGE_FEC_DECODE_PLCF = 3,
     DNRP_STAGE_RX_CHAIN = 4,   /* rx front end + PCC + PDC on the resident IQ windows and sync reports */
     DNRP_STAGE_TX_CHAIN = 5,   /* FEC encode + OFDM on the resident TB / PLCF / descriptors */
-    DNRP_STAGE_CHANNEL = 6     /* channel on the resident TX IQ and descriptors */
+    DNRP_STAGE_CHANNEL = 6,    /* channel on the resident TX IQ and descriptors */
+    DNRP_STAGE_SYNC = 7,       /* packet synchronisation on the resident IQ windows, hand-over to the receiver */
+    DNRP_STAGE_SYNC_RX_CHAIN = 8 /* 7 followed by 4: raw IQ windows -> transport blocks */
 } dnrp_stage_t;
 int dnrp_time_stage(dnrp_ctx_t* ctx, int stage, uint32_t n, uint32_t reps, float* ms_per_rep);
 

@@ -2,6 +2,7 @@
 reference lib/src/phy/rx/sync/{sync_chunk,autocorrelator_detection,autocorrelator_peak,crosscorrelator,
 stf_template}.cpp).  Parity unpinned (see sync.c header)."""
 import ctypes as C
+import functools
 
 import numpy as np
 
@@ -35,6 +36,7 @@ def stf_template(u, b, N_eff_TX, os=1):
     return t
 
 
+@functools.lru_cache(maxsize=None)
 def templates(u, b, N_eff_TX_max, os=1):
     n = [1, 2, 4, 8]
     return np.stack([stf_template(u, b, v, os) for v in n if v <= N_eff_TX_max])
