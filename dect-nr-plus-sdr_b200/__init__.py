@@ -89,15 +89,16 @@ CHANNEL_DTYPE = np.dtype([("snr_dB", "f4"), ("net_bandwidth_norm", "f4"), ("t0",
                           ("seed", "u8")], align=True)
 assert CHANNEL_DTYPE.itemsize == C.sizeof(ChannelDesc)
 TAP_Y, TAP_DRS_ZF, TAP_STF_ZF, TAP_LLR_PCC, TAP_LLR_PDC, TAP_WIENER_CLASS, TAP_TB_OK = 1, 2, 3, 4, 5, 6, 7
-KERNEL_TURBO_DECODE_PDC, KERNEL_RX_FFT, KERNEL_RX_DEMAP_PDC, KERNEL_RX_STF, KERNEL_DERM_PDC, KERNEL_SYNC = range(6)
+KERNEL_TURBO_DECODE_PDC, KERNEL_RX_FFT, KERNEL_RX_DEMAP_PDC, KERNEL_RX_STF, KERNEL_DERM_PDC, KERNEL_SYNC, \
+    KERNEL_RESAMPLE = range(7)
 # dnrp_sync_result_t
 SYNC_RESULT_DTYPE = np.dtype([("detected", "u4"), ("detection_time_local", "u4"), ("detection_ant_idx", "u4"),
                               ("detection_metric", "f4"), ("detection_rms", "f4"), ("coarse_peak_time_local", "u4"),
                               ("coarse_peak_array", "f4", (8,)), ("rms_array", "f4", (8,)),
                               ("cfo_fractional_rad", "f4"), ("cfo_integer_rad", "f4"), ("N_eff_TX", "u4"),
-                              ("fine_peak_time_local", "u4"), ("n_detections", "u4"), ("strongest_ant", "u4")],
-                             align=True)
-assert SYNC_RESULT_DTYPE.itemsize == 112
+                              ("fine_peak_time_local", "u4"), ("n_detections", "u4"), ("strongest_ant", "u4"),
+                              ("coarse_peak_time_hw", "u4")], align=True)
+assert SYNC_RESULT_DTYPE.itemsize == 116
 
 
 def build(verbose=False):
@@ -156,6 +157,7 @@ class Phy:
         self.plcf_type = plcf_type
         self.N_RX = N_RX
         self.oversampling = oversampling
+        self.resample = tuple(resample)
         self.dbits_stride = ((self.ps["G"] + 7) // 8 + 3) & ~3
 
     def close(self):
@@ -303,7 +305,7 @@ class Phy:
     # ---- simulation channel (reference simulation/vspace.cpp:437-512, wireless/channel_{awgn,flat}.cpp)
     def channel(self, n, snr_dB=100.0, t0=0, mode=0, seed=1, net_bandwidth_norm=None, fetch=False):
         if net_bandwidth_norm is None:
-            net_bandwidth_norm = 1.0 / self.oversampling
+            net_bandwidth_norm = self.resample[1] / (self.resample[0] * self.oversampling)
         descs = np.zeros(n, dtype=CHANNEL_DTYPE)
         descs["snr_dB"], descs["net_bandwidth_norm"], descs["t0"], descs["mode"] = snr_dB, net_bandwidth_norm, t0, mode
         descs["seed"] = seed

@@ -50,6 +50,25 @@ int dnrp_get_packet_sizes(const dnrp_psdef_t* psdef, dnrp_packet_sizes_t* out) {
     return DNRP_OK;
 }
 
+int dnrp_resampler_design(uint32_t L, uint32_t M, uint32_t oversampling, float* taps_out, uint32_t taps_cap,
+                          uint32_t* info4) {
+    DNRP_REQUIRE(info4 && L > 0 && M > 0, "invalid argument");
+    spec::resampler_design_t r;
+    DNRP_REQUIRE(spec::design_resampler(L, M, oversampling, r), "no filter definition for this oversampling");
+    info4[0] = r.filter_length; info4[1] = r.subfilter_length; info4[2] = r.delay; info4[3] = (uint32_t)r.taps.size();
+    if (taps_out) {
+        DNRP_REQUIRE(taps_cap >= r.taps.size(), "taps_out too small");
+        std::memcpy(taps_out, r.taps.data(), r.taps.size() * sizeof(float));
+    }
+    return DNRP_OK;
+}
+
+uint32_t dnrp_resampler_n_after(uint32_t L, uint32_t M, uint32_t oversampling, uint32_t n_in) {
+    spec::resampler_design_t r;
+    if (!spec::design_resampler(L, M, oversampling, r)) return 0;
+    return r.n_after(n_in);
+}
+
 int dnrp_ctx_create(const dnrp_config_t* cfg, int device, dnrp_ctx_t** out) {
     DNRP_REQUIRE(cfg && out, "null argument");
     DNRP_REQUIRE(cfg->max_batch > 0, "max_batch must be > 0");
@@ -347,8 +366,23 @@ int run_tx_ofdm(dnrp_ctx* c, uint32_t n) {
     p.pcc_bits = c->d_pcc_bits.p; p.pcc_stride = 28;
     p.pdc_bits = c->d_pdc_bits.p; p.pdc_stride = c->fec.dbits_stride;
     p.meta = c->d_tx_meta.p;
-    p.iq = c->d_iq_tx.p; p.iq_stride = c->tx_stride;
+    if (!c->resampling) {
+        p.iq = c->d_iq_tx.p; p.iq_stride = c->tx_stride;
+        DNRP_LAUNCH(c, -1, launch_tx_ofdm(p, n, c->stream));
+        return DNRP_OK;
+    }
+    // tx.cpp:913-934 + 679-704: IFFT output -> polyphase resampler -> mixer at the hardware rate; the guard interval
+    // stays zero (memset above)
+    p.iq = c->d_iq_tx_os.p; p.iq_stride = c->tx_os_stride; p.no_mix = 1;
     DNRP_LAUNCH(c, -1, launch_tx_ofdm(p, n, c->stream));
+    resample_params_t r{};
+    r.L = c->rs_tx.L; r.M = c->rs_tx.M; r.SL = c->rs_tx.subfilter_length; r.delay = c->rs_tx.delay;
+    r.taps = c->d_rs_tx_taps.p;
+    r.in = c->d_iq_tx_os.p; r.in_stride = c->tx_os_stride; r.n_in = d.n_no_gi_os;
+    r.out = c->d_iq_tx.p; r.out_stride = c->tx_stride; r.n_out = c->n_no_gi_rs; r.n_fill = 0;
+    r.n_ant = d.N_TX;
+    r.meta = c->d_tx_meta.p;
+    DNRP_LAUNCH(c, DNRP_KERNEL_RESAMPLE, launch_resample(r, n, c->stream));
     return DNRP_OK;
 }
 }  // namespace dnrp
@@ -361,7 +395,6 @@ int dnrp_tx_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_tx_desc_t* descs, const 
                   dnrp_cf32_t* iq_out, uint32_t* n_samples_out) {
     DNRP_REQUIRE(c && descs && plcf && tb, "null argument");
     DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
-    DNRP_REQUIRE(c->cfg.resample_L == c->cfg.resample_M, "resampling TX path not built into this context");
     DNRP_CUDA(cudaSetDevice(c->device));
     const fec_plan_t& f = c->fec;
     const phy_dims_t& d = c->dims;
@@ -379,7 +412,7 @@ int dnrp_tx_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_tx_desc_t* descs, const 
         mask[i] = (!cl && !bf) ? 0x0000u : (cl && !bf) ? 0x5555u : (!cl && bf) ? 0xAAAAu : 0xFFFFu;
         rv[i] = (uint8_t)descs[i].rv;
         if (n_samples_out)
-            n_samples_out[i] = d.n_no_gi_os + (d.n_packet_os - d.n_no_gi_os) * descs[i].GI_percentage / 100;
+            n_samples_out[i] = c->n_no_gi_rs + (c->n_packet_rs - c->n_no_gi_rs) * descs[i].GI_percentage / 100;  // tx.cpp:556
     }
     DNRP_CUDA(cudaMemcpy2DAsync(c->d_tb_in.p, f.tb_stride, tb, c->ps.N_TB_byte, c->ps.N_TB_byte, n,
                                 cudaMemcpyHostToDevice, c->stream));

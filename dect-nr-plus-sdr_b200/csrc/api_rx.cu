@@ -19,7 +19,11 @@ namespace dnrp {
 rx_params_t make_rx_params(dnrp_ctx* c) {
     rx_params_t p{};
     p.d = c->dims;
-    p.iq = c->d_iq_rx.p; p.iq_stride = c->rx_stride;
+    if (c->resampling) {
+        p.iq = c->d_iq_rs.p; p.iq_stride = c->rs_stride; p.t0_zero = 1;
+    } else {
+        p.iq = c->d_iq_rx.p; p.iq_stride = c->rx_stride; p.t0_zero = 0;
+    }
     p.state = c->d_rx_state.p;
     p.Y = c->d_Y.p; p.hzf = c->d_hzf.p; p.hstf = c->d_hstf.p; p.snr_part = c->d_snr_part.p;
     p.cls = c->d_cls.p; p.cls_stride = c->cls_stride;
@@ -31,6 +35,8 @@ rx_params_t make_rx_params(dnrp_ctx* c) {
 // The reference interleaves FFTs, estimation and decoding symbol by symbol for latency; for a batch
 // the whole front end of all packets runs first (every later stage only reads its results).
 int run_rx_front(dnrp_ctx* c, uint32_t n) {
+    const int rc = run_rx_resample(c, n);
+    if (rc) return rc;
     const rx_params_t p = make_rx_params(c);
     DNRP_LAUNCH(c, DNRP_KERNEL_RX_STF, launch_rx_stf(p, n, c->stream));
     DNRP_LAUNCH(c, DNRP_KERNEL_RX_FFT, launch_rx_fft(p, n, c->stream));
@@ -56,7 +62,7 @@ int run_channel(dnrp_ctx* c, uint32_t n) {
     p.N_TX = d.N_TX; p.N_RX = d.N_RX;
     p.tx = c->d_iq_tx.p; p.tx_stride = c->tx_stride;
     p.rx = c->d_iq_rx.p; p.rx_stride = c->rx_stride;
-    p.n_samples = d.n_packet_os;
+    p.n_samples = c->n_packet_rs;
     p.meta = c->d_chan_meta.p;
     DNRP_LAUNCH(c, -1, launch_channel(p, n, c->stream));
     return DNRP_OK;
@@ -66,10 +72,27 @@ int run_sync(dnrp_ctx* c, uint32_t n, uint32_t search_length, bool hand_over) {
     const phy_dims_t& d = c->dims;
     sync_params_t p{};
     p.d = d;
-    p.iq = c->d_iq_rx.p; p.iq_stride = c->rx_stride;
+    p.iq_x = c->d_iq_rx.p; p.x_stride = c->rx_stride; p.x_len = c->rx_stride;
+    p.rs_L = c->cfg.resample_L; p.rs_M = c->cfg.resample_M;
+    p.xc_S = c->stf_len_rs;
+    p.xc_sl = (uint32_t)((uint64_t)d.pat_len_os * p.rs_L / p.rs_M);  // crosscorrelator.cpp:52-56
+    p.n_no_gi_hw = c->n_no_gi_rs;
+    if (c->resampling) {
+        // rx_pacer_t::resample_single_unit on the whole window: hardware rate -> DECT rate, zero history at the start
+        resample_params_t r{};
+        r.L = c->rs_rx.L; r.M = c->rs_rx.M; r.SL = c->rs_rx.subfilter_length; r.delay = c->rs_rx.delay;
+        r.taps = c->d_rs_rx_taps.p;
+        r.in = c->d_iq_rx.p; r.in_stride = c->rx_stride; r.n_in = c->rx_stride;
+        r.out = c->d_iq_sync.p; r.out_stride = c->sync_stride; r.n_out = c->sync_len; r.n_fill = c->sync_stride;
+        r.n_ant = d.N_RX;
+        DNRP_LAUNCH(c, DNRP_KERNEL_RESAMPLE, launch_resample(r, n, c->stream));
+        p.iq = c->d_iq_sync.p; p.iq_stride = c->sync_stride; p.len = c->sync_len;
+    } else {
+        p.iq = c->d_iq_rx.p; p.iq_stride = c->rx_stride; p.len = c->rx_stride;
+    }
     p.n_ant = d.N_RX;  // RX_SYNC_PARAM_AUTOCORRELATOR_ANTENNA_LIMIT = 8 >= N_RX
     p.step = c->sync_step; p.n_steps = c->sync_n_steps;
-    p.search_length = search_length ? search_length : c->rx_stride - d.stf_len_os - d.pat_len_os;
+    p.search_length = search_length ? search_length : p.len - d.stf_len_os - d.pat_len_os;
     // autocorrelator_detection.cpp:60-62: minimum rms scaled with the sample rate relative to 30.72 MS/s
     p.rms_min = 0.005f * (float)std::sqrt((double)d.u * d.b * c->cfg.oversampling * 1.728e6 / 30.72e6);
     p.c_steps = c->d_sync_c.p; p.p_steps = c->d_sync_p.p;
@@ -82,6 +105,21 @@ int run_sync(dnrp_ctx* c, uint32_t n, uint32_t search_length, bool hand_over) {
     return DNRP_OK;
 }
 
+// rx_synced.cpp:214-220 + rx_pacer.cpp: the resampler restarts with empty history at the fine peak
+int run_rx_resample(dnrp_ctx* c, uint32_t n) {
+    if (!c->resampling) return DNRP_OK;
+    const phy_dims_t& d = c->dims;
+    resample_params_t r{};
+    r.L = c->rs_rx.L; r.M = c->rs_rx.M; r.SL = c->rs_rx.subfilter_length; r.delay = c->rs_rx.delay;
+    r.taps = c->d_rs_rx_taps.p;
+    r.in = c->d_iq_rx.p; r.in_stride = c->rx_stride; r.n_in = c->rx_stride;
+    r.start = &c->d_rx_state.p->t0; r.start_stride_words = sizeof(rx_state_t) / 4;
+    r.out = c->d_iq_rs.p; r.out_stride = c->rs_stride; r.n_out = d.n_no_gi_os; r.n_fill = c->rs_stride;
+    r.n_ant = d.N_RX;
+    DNRP_LAUNCH(c, DNRP_KERNEL_RESAMPLE, launch_resample(r, n, c->stream));
+    return DNRP_OK;
+}
+
 }  // namespace dnrp
 
 extern "C" {
@@ -91,7 +129,7 @@ int dnrp_sync_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, uint32_
     static_assert(sizeof(dnrp_sync_result_t) == sizeof(sync_result_dev_t), "sync result layouts differ");
     DNRP_REQUIRE(c, "null argument");
     DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
-    DNRP_REQUIRE(search_length <= c->rx_stride, "search_length exceeds the IQ window");
+    DNRP_REQUIRE(search_length <= c->sync_len, "search_length exceeds the (resampled) IQ window");
     DNRP_CUDA(cudaSetDevice(c->device));
     if (iq_in)
         DNRP_CUDA(cudaMemcpyAsync(c->d_iq_rx.p, iq_in, (size_t)n * c->dims.N_RX * c->rx_stride * sizeof(float2),
@@ -115,7 +153,7 @@ int dnrp_rx_pcc_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, const
     const phy_dims_t& d = c->dims;
     if (sync) {
         for (uint32_t i = 0; i < n; ++i) {
-            DNRP_REQUIRE(sync[i].fine_peak_time_local + d.n_no_gi_os <= c->rx_stride, "packet exceeds the IQ window");
+            DNRP_REQUIRE(sync[i].fine_peak_time_local + c->n_no_gi_rs <= c->rx_stride, "packet exceeds the IQ window");
             rx_state_t& s = c->h_rx_state[i];
             std::memset(&s, 0, sizeof(s));
             s.t0 = (int32_t)sync[i].fine_peak_time_local;
@@ -224,7 +262,7 @@ int dnrp_channel_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_channel_desc_t* des
     const phy_dims_t& d = c->dims;
     std::vector<chan_meta_dev_t> meta(n);
     for (uint32_t i = 0; i < n; ++i) {
-        DNRP_REQUIRE(descs[i].t0 + d.n_packet_os <= c->rx_stride, "offset exceeds the IQ window");
+        DNRP_REQUIRE(descs[i].t0 + c->n_packet_rs <= c->rx_stride, "offset exceeds the IQ window");
         DNRP_REQUIRE(descs[i].mode <= 1, "unknown channel mode");
         DNRP_REQUIRE(descs[i].net_bandwidth_norm > 0.f, "net_bandwidth_norm must be > 0");
         const float n0_dBFS = -10.0f * log10f(descs[i].net_bandwidth_norm) - descs[i].snr_dB;  // noise.cpp:37-38
@@ -276,7 +314,7 @@ int dnrp_loopback_tx_to_rx(dnrp_ctx_t* c, uint32_t n, uint32_t t0) {
     DNRP_REQUIRE(c, "null argument");
     DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
     const phy_dims_t& d = c->dims;
-    DNRP_REQUIRE(t0 + d.n_packet_os <= c->rx_stride, "offset exceeds the IQ window");
+    DNRP_REQUIRE(t0 + c->n_packet_rs <= c->rx_stride, "offset exceeds the IQ window");
     DNRP_CUDA(cudaSetDevice(c->device));
     DNRP_CUDA(cudaMemsetAsync(c->d_iq_rx.p, 0, (size_t)n * d.N_RX * c->rx_stride * sizeof(float2), c->stream));
     for (uint32_t a = 0; a < d.N_RX; ++a) {
@@ -285,7 +323,7 @@ int dnrp_loopback_tx_to_rx(dnrp_ctx_t* c, uint32_t n, uint32_t t0) {
         float2* dst = c->d_iq_rx.p + (size_t)a * c->rx_stride + t0;
         DNRP_CUDA(cudaMemcpy2DAsync(dst, (size_t)d.N_RX * c->rx_stride * sizeof(float2), src,
                                     (size_t)d.N_TX * c->tx_stride * sizeof(float2),
-                                    (size_t)d.n_packet_os * sizeof(float2), n, cudaMemcpyDeviceToDevice, c->stream));
+                                    (size_t)c->n_packet_rs * sizeof(float2), n, cudaMemcpyDeviceToDevice, c->stream));
     }
     return DNRP_OK;
 }

@@ -13,6 +13,7 @@
 #include "spec.hpp"
 #include "spec_fec.hpp"
 #include "spec_re.hpp"
+#include "spec_resample.hpp"
 
 namespace dnrp {
 
@@ -127,6 +128,18 @@ struct dnrp_ctx {
     std::vector<dnrp::rx_state_t> h_rx_state;
     dnrp::dbuf<dnrp::chan_meta_dev_t> d_chan_meta;
 
+    // resampling between the DECT rate (x oversampling) and the hardware rate: hw = dect * L / M (TX direction);
+    // the receive direction uses M / L.  All IQ crossing the C ABI is at the hardware rate.
+    bool resampling = false;
+    dnrp::spec::resampler_design_t rs_tx, rs_rx;
+    dnrp::dbuf<float> d_rs_tx_taps, d_rs_rx_taps;
+    uint32_t n_no_gi_rs = 0, n_packet_rs = 0;   // packet without / with full guard interval at the hardware rate
+    uint32_t stf_len_rs = 0;                    // STF template length at the hardware rate
+    uint32_t tx_os_stride = 0, sync_stride = 0, sync_len = 0, rs_stride = 0;
+    dnrp::dbuf<float2> d_iq_tx_os;              // [B][N_TX][tx_os_stride] TX IQ before resampling
+    dnrp::dbuf<float2> d_iq_sync;               // [B][N_RX][sync_stride] window resampled for detection / coarse peak
+    dnrp::dbuf<float2> d_iq_rs;                 // [B][N_RX][rs_stride] packet resampled from the fine peak
+
     // packet synchronisation: STF templates for N_eff_TX = 1, 2, 4, 8 (up to the context's), step sums, results
     uint32_t sync_n_tpl = 0, sync_step = 0, sync_n_steps = 0;
     dnrp::dbuf<float2> d_sync_tpl, d_sync_c, d_sync_xc;
@@ -182,4 +195,5 @@ int run_rx_pcc(dnrp_ctx* c, uint32_t n);               // PCC demap + blind PLCF
 int run_rx_pdc(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, bool have_reset);
 int run_channel(dnrp_ctx* c, uint32_t n);
 int run_sync(dnrp_ctx* c, uint32_t n, uint32_t search_length, bool hand_over);
+int run_rx_resample(dnrp_ctx* c, uint32_t n);          // hardware rate -> DECT rate from each packet's fine peak
 }  // namespace dnrp

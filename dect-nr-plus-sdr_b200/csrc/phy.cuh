@@ -59,6 +59,7 @@ struct rx_params_t {
     phy_dims_t d;
     const float2* iq;        // [packet][N_RX][iq_stride]
     size_t iq_stride;
+    uint32_t t0_zero;        // 1: iq holds the packet resampled from its fine peak (rx_state_t::t0 is a hardware-rate index)
     rx_state_t* state;       // [packet]
     float2* Y;               // [packet][N_RX][N_DF][Nk] equalised-domain OFDM symbols 1..N_DF
     float2* hzf;             // [packet][N_RX][N_eff_TX][n_drs][NP] zero-forced DRS pilots
@@ -94,9 +95,26 @@ struct txofdm_params_t {
     const tx_meta_dev_t* meta;                     // [packet]
     float2* iq;                                    // [packet][N_TX][iq_stride]
     size_t iq_stride;
+    uint32_t no_mix;                               // 1: the mixer runs after the resampler instead
 };
 
 cudaError_t launch_tx_ofdm(const txofdm_params_t& p, uint32_t n_packets, cudaStream_t st);
+
+// rational resampler (phy_resample.cu): y[m] = sum_j taps[j*L + l] x[i0 - j], p = delay + m*M, l = p % L, i0 = p / L,
+// x = 0 outside [0, n_in) -- the closed form of resampler_t's streaming state machine incl. its final flush
+struct resample_params_t {
+    uint32_t L, M, SL, delay;
+    const float* taps;                       // [SL][L]
+    const float2* in;  size_t in_stride;     // [packet][n_ant][in_stride]
+    const int32_t* start; uint32_t start_stride_words;  // optional per-packet first input sample (else 0)
+    uint32_t n_in;                           // input samples per stream (clipped to in_stride - start)
+    float2* out;  size_t out_stride;         // [packet][n_ant][out_stride]
+    uint32_t n_out;                          // filtered output samples
+    uint32_t n_fill;                         // outputs [n_out, n_fill) are zeroed (guard interval / padding)
+    uint32_t n_ant;
+    const tx_meta_dev_t* meta;               // optional: mixer after resampling (tx.cpp:913-934)
+};
+cudaError_t launch_resample(const resample_params_t& p, uint32_t n_packets, cudaStream_t st);
 
 // packet synchronisation (phy_sync.cu): detection, coarse peak, fine peak of the first packet in each window
 struct sync_result_dev_t {
@@ -109,17 +127,24 @@ struct sync_result_dev_t {
     float cfo_fractional_rad, cfo_integer_rad;
     uint32_t N_eff_TX, fine_peak_time_local;
     uint32_t n_detections, strongest_ant;
+    uint32_t coarse_peak_time_hw;
 };
 struct sync_params_t {
     phy_dims_t d;
-    const float2* iq;  size_t iq_stride;  // [packet][N_RX][iq_stride]
+    const float2* iq;  size_t iq_stride;  // [packet][N_RX][iq_stride] windows at the DECT rate (x oversampling)
+    uint32_t len;                          // usable samples per window in iq
+    const float2* iq_x;  size_t x_stride;  // [packet][N_RX][x_stride] the same windows at the hardware rate (= iq if L = M)
+    uint32_t x_len;
+    uint32_t rs_L, rs_M;                   // hardware rate = DECT rate * L / M
+    uint32_t xc_S, xc_sl;                  // template length and one-sided search range at the hardware rate
+    uint32_t n_no_gi_hw;                   // packet length the receiver needs behind the fine peak (hardware rate)
     uint32_t n_ant;                        // antennas used (RX_SYNC_PARAM_AUTOCORRELATOR_ANTENNA_LIMIT = 8)
     uint32_t step, n_steps;                // detection step (pattern / 4) and number of steps in the window
     uint32_t search_length;                // samples the detection may consume
     float rms_min;
     float2* c_steps;                       // [packet][n_ant][n_steps]
     float* p_steps;                        // [packet][n_ant][n_steps]
-    const float2* templates;               // [n_tpl][stf_len_os]
+    const float2* templates;               // [n_tpl][xc_S]
     uint32_t n_tpl;
     float2* xc;                            // [packet][n_tpl] (max abs(xcorr), lag)
     sync_result_dev_t* result;             // [packet]

@@ -1,0 +1,82 @@
+// phy_resample.cu -- rational resampler L/M with a polyphase Kaiser low pass for a batch of antenna streams
+// (reference lib/src/phy/resample/resampler.cpp; callers tx.cpp:913-934 + 679-704, rx_pacer.cpp:106-143,
+// rx_synced.cpp:711-746, stf_template.cpp:169-186).
+// The reference streams symbol by symbol through a history buffer; its output is the plain convolution of the
+// zero-extended stream with the up-sampled filter, decimated by M and advanced by the filter delay, so every output
+// sample is independent:  y[m] = sum_j taps[j*L + l] x[i0 - j],  p = delay + m*M,  l = p % L,  i0 = p / L.
+// One block = RS_TILE consecutive outputs of one stream: the input span (about RS_TILE*M/L + SL samples) is staged in
+// shared memory with coalesced loads and zero extension, taps are read as [j][l] rows (at most L distinct banks per
+// warp), outputs are written coalesced.  HBM traffic = input once + output once.
+#include "phy.cuh"
+
+namespace dnrp {
+
+constexpr uint32_t RS_TILE = 1024, RS_THREADS = 256;
+
+__global__ void __launch_bounds__(RS_THREADS) k_resample(const resample_params_t p, uint32_t span_max) {
+    extern __shared__ float2 s_x[];
+    float* s_t = reinterpret_cast<float*>(s_x + span_max);
+    const uint32_t tile0 = blockIdx.x * RS_TILE, a = blockIdx.y, pkt = blockIdx.z, tid = threadIdx.x;
+    const int32_t start = p.start ? p.start[(size_t)pkt * p.start_stride_words] : 0;
+    const long long avail = (long long)p.in_stride - start;
+    const uint32_t n_in = avail <= 0 ? 0u : (avail < (long long)p.n_in ? (uint32_t)avail : p.n_in);
+    const float2* x = p.in + ((size_t)pkt * p.n_ant + a) * p.in_stride + start;
+    float2* y = p.out + ((size_t)pkt * p.n_ant + a) * p.out_stride;
+    const uint32_t m_end = min(tile0 + RS_TILE, p.n_out);
+    if (tile0 < p.n_out) {
+        const uint32_t p_lo = p.delay + tile0 * p.M, p_hi = p.delay + (m_end - 1) * p.M;
+        const int32_t i_lo = (int32_t)(p_lo / p.L) - (int32_t)(p.SL - 1);
+        const uint32_t span = (uint32_t)((int32_t)(p_hi / p.L) - i_lo + 1);
+        for (uint32_t i = tid; i < span; i += RS_THREADS) {
+            const int32_t idx = i_lo + (int32_t)i;
+            s_x[i] = (idx >= 0 && (uint32_t)idx < n_in) ? x[idx] : make_float2(0.f, 0.f);
+        }
+        for (uint32_t i = tid; i < p.SL * p.L; i += RS_THREADS) s_t[i] = p.taps[i];
+        __syncthreads();
+        float ph0 = 0.f, inc = 0.f;
+        bool mix = false;
+        if (p.meta) {
+            ph0 = p.meta[pkt].iq_phase_rad; inc = p.meta[pkt].iq_phase_increment;
+            mix = ph0 != 0.f || inc != 0.f;
+        }
+        for (uint32_t m = tile0 + tid; m < m_end; m += RS_THREADS) {
+            const uint32_t pp = p.delay + m * p.M, l = pp % p.L;
+            const float2* v = s_x + ((int32_t)(pp / p.L) - i_lo);
+            const float* t = s_t + l;
+            float re = 0.f, im = 0.f;
+            for (uint32_t j = 0; j < p.SL; ++j) {
+                const float c = t[j * p.L];
+                const float2 s = v[-(int32_t)j];
+                re = fmaf(c, s.x, re);
+                im = fmaf(c, s.y, im);
+            }
+            if (mix) {
+                double ph = (double)ph0 + (double)inc * (double)m;
+                ph -= 6.283185307179586476925 * rint(ph * 0.15915494309189533577);
+                float sn, cs;
+                sincosf((float)ph, &sn, &cs);
+                const float r2 = re * cs - im * sn;
+                im = re * sn + im * cs;
+                re = r2;
+            }
+            y[m] = make_float2(re, im);
+        }
+    }
+    const uint32_t z0 = max(tile0, p.n_out), z1 = min(tile0 + RS_TILE, p.n_fill);
+    for (uint32_t m = z0 + tid; m < z1; m += RS_THREADS) y[m] = make_float2(0.f, 0.f);
+}
+
+cudaError_t launch_resample(const resample_params_t& p, uint32_t n_packets, cudaStream_t st) {
+    if (n_packets == 0) return cudaSuccess;
+    const uint32_t n_total = p.n_out > p.n_fill ? p.n_out : p.n_fill;
+    if (n_total == 0) return cudaSuccess;
+    if ((uint64_t)p.delay + (uint64_t)p.n_out * p.M >= (1ull << 31)) return cudaErrorInvalidValue;
+    const uint32_t span_max = (RS_TILE * p.M) / p.L + p.SL + 2;
+    const size_t smem = (size_t)span_max * sizeof(float2) + (size_t)p.SL * p.L * sizeof(float);
+    cudaError_t e = cudaFuncSetAttribute(k_resample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_resample<<<dim3((n_total + RS_TILE - 1) / RS_TILE, p.n_ant, n_packets), RS_THREADS, smem, st>>>(p, span_max);
+    return cudaGetLastError();
+}
+
+}  // namespace dnrp

@@ -55,7 +55,7 @@ __global__ void __launch_bounds__(256) k_rx_stf(const rx_params_t p) {
     __shared__ float2 s_red[8];
     __shared__ float s_ang[8];
 
-    const int32_t t0 = st.t0;
+    const int32_t t0 = p.t0_zero ? 0 : st.t0;
     const float inc0 = st.inc0;
     const float c[9] = {1.f, -1.f, 1.f, 1.f, -1.f, -1.f, -1.f, -1.f, -1.f};
     const float fscale = sqrtf((float)d.N_OCC) / (float)d.N_os;  // rx_synced.cpp:761
@@ -166,7 +166,7 @@ __global__ void __launch_bounds__(256) k_rx_fft(const rx_params_t p) {
     __shared__ float2 s_red[8];
 
     const uint32_t n0 = d.stf_len_os + (l - 1) * d.sym_len_os + d.cp_os;  // relative to the first STF sample
-    const float2* x = p.iq + ((size_t)pkt * d.N_RX + a) * p.iq_stride + st.t0 + n0;
+    const float2* x = p.iq + ((size_t)pkt * d.N_RX + a) * p.iq_stride + (p.t0_zero ? 0 : st.t0) + n0;
     // mixer phase is continuous: inc0 over the STF, inc1 afterwards (rx_synced.cpp:239-245, 552-555)
     const double ph0 = (double)st.inc0 * (double)d.stf_len_os + (double)st.inc1 * (double)(n0 - d.stf_len_os);
     for (uint32_t n = tid; n < d.N_os; n += nthr) X[n] = cmul(x[n], rot(ph0 + (double)st.inc1 * (double)n));

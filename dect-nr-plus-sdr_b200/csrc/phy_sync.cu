@@ -243,6 +243,8 @@ __global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32
             res.detection_time_local = n_det; res.detection_ant_idx = best_a;
             res.detection_metric = best_metric; res.detection_rms = best_rms;
             res.coarse_peak_time_local = coarse;
+            // rx_pacer_t::convert_length_resampled_to_global (rx_pacer.cpp:311-318)
+            res.coarse_peak_time_hw = (uint32_t)round((double)coarse * (double)p.rs_L / (double)p.rs_M);
             for (uint32_t a = 0; a < 8; ++a) { res.coarse_peak_array[a] = cpa[a]; res.rms_array[a] = rms_arr[a]; }
             res.cfo_fractional_rad = wcfo / ms2;
             res.cfo_integer_rad = 0.f;  // coarse_peak_f_domain.cpp:94-201: not implemented in the reference
@@ -254,7 +256,7 @@ __global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32
     if (tid == 0) {
         res.detected = 0;
         res.n_detections = n_det_total;
-        res.N_eff_TX = 0; res.fine_peak_time_local = 0; res.coarse_peak_time_local = 0;
+        res.N_eff_TX = 0; res.fine_peak_time_local = 0; res.coarse_peak_time_local = 0; res.coarse_peak_time_hw = 0;
         res.cfo_fractional_rad = 0.f; res.cfo_integer_rad = 0.f; res.strongest_ant = 0;
         for (uint32_t a = 0; a < 8; ++a) { res.coarse_peak_array[a] = 0.f; res.rms_array[a] = 0.f; }
     }
@@ -297,22 +299,24 @@ __global__ void __launch_bounds__(XC_THREADS) k_sync_xcorr(const sync_params_t p
     __shared__ unsigned long long s_best;
     const phy_dims_t& d = p.d;
     const uint32_t tpl = blockIdx.x, pkt = blockIdx.y, tid = threadIdx.x;
-    const uint32_t S = d.stf_len_os, sl = d.pat_len_os, n_lag = 2 * sl + 1;  // 16 b os samples to either side
+    const uint32_t S = p.xc_S, sl = p.xc_sl, n_lag = 2 * sl + 1;  // 16 b os L/M samples to either side
     const uint32_t LT = (n_lag + XC_LAGS - 1) / XC_LAGS, n_lag_pad = LT * XC_LAGS;
     const sync_result_dev_t& res = p.result[pkt];
     float2* out = p.xc + (size_t)pkt * p.n_tpl + tpl;
-    const long long w0 = (long long)res.coarse_peak_time_local - sl;
+    const long long w0 = (long long)res.coarse_peak_time_hw - sl;
     if (!res.detected || w0 < 0 || w0 + n_lag + S - 1 > len) {
         if (tid == 0) *out = make_float2(-1.f, 0.f);
         return;
     }
-    float2* mix = smem_x;                              // [xc_pos(n_lag_pad + S)]
-    float2* tp = mix + xc_pos(n_lag_pad + S) + 1;      // [S]
-    float2* part = tp + S;                             // [IC][n_lag_pad]
-    const float2* x = p.iq + ((size_t)pkt * d.N_RX + res.strongest_ant) * p.iq_stride + w0;
-    const double inc = (double)(res.cfo_fractional_rad + res.cfo_integer_rad);
+    const uint32_t S_pad = (S + 7) & ~7u;              // the MAC loop is unrolled by 8: template zero padded
+    float2* mix = smem_x;                              // [xc_pos(n_lag_pad + S_pad)]
+    float2* tp = mix + xc_pos(n_lag_pad + S_pad) + 1;  // [S_pad]
+    float2* part = tp + S_pad;                         // [IC][n_lag_pad]
+    const float2* x = p.iq_x + ((size_t)pkt * d.N_RX + res.strongest_ant) * p.x_stride + w0;
+    // the CFO was measured at the DECT rate; per hardware sample it is smaller by M / L (crosscorrelator.cpp:97-105)
+    const double inc = (double)((res.cfo_fractional_rad + res.cfo_integer_rad) * (float)p.rs_M / (float)p.rs_L);
     const uint32_t n_mix = n_lag + S - 1;
-    for (uint32_t i = tid; i < n_lag_pad + S; i += XC_THREADS) {
+    for (uint32_t i = tid; i < n_lag_pad + S_pad; i += XC_THREADS) {
         float2 r = make_float2(0.f, 0.f);
         if (i < n_mix) {
             const float2 v = x[i];
@@ -324,13 +328,13 @@ __global__ void __launch_bounds__(XC_THREADS) k_sync_xcorr(const sync_params_t p
         mix[xc_pos(i)] = r;
     }
     const float2* T = p.templates + (size_t)tpl * S;
-    for (uint32_t i = tid; i < S; i += XC_THREADS) tp[i] = T[i];
+    for (uint32_t i = tid; i < S_pad; i += XC_THREADS) tp[i] = i < S ? T[i] : make_float2(0.f, 0.f);
     if (tid == 0) s_best = 0ull;
     __syncthreads();
     if (tid < LT * IC) {
         const uint32_t lt = tid % LT, ic = tid / LT, j0 = lt * XC_LAGS;
-        uint32_t chunk = ((S + IC - 1) / IC + 7) & ~7u;
-        const uint32_t i0 = min(ic * chunk, S), i1 = min(i0 + chunk, S);
+        const uint32_t chunk = ((S_pad + IC - 1) / IC + 7) & ~7u;
+        const uint32_t i0 = min(ic * chunk, S_pad), i1 = min(i0 + chunk, S_pad);
         float ar[XC_LAGS], ai[XC_LAGS];
         float2 w[XC_LAGS];
 #pragma unroll
@@ -375,7 +379,7 @@ __global__ void k_sync_final(const sync_params_t p, uint32_t n, uint32_t len) {
     const uint32_t pkt = blockIdx.x * blockDim.x + threadIdx.x;
     if (pkt >= n) return;
     sync_result_dev_t& res = p.result[pkt];
-    const uint32_t sl = p.d.pat_len_os;
+    const uint32_t sl = p.xc_sl;
     if (res.detected) {
         float best = 0.f;
         uint32_t best_tpl = 0, best_idx = 0;
@@ -387,14 +391,14 @@ __global__ void k_sync_final(const sync_params_t p, uint32_t n, uint32_t len) {
         }
         if (ok) {
             res.N_eff_TX = 1u << best_tpl;
-            res.fine_peak_time_local = res.coarse_peak_time_local - sl + best_idx;
+            res.fine_peak_time_local = res.coarse_peak_time_hw - sl + best_idx;
         } else {
             res.detected = 0;
         }
     }
     if (p.rx_state) {
         rx_state_t s = {};
-        if (res.detected && (size_t)res.fine_peak_time_local + p.d.n_no_gi_os <= p.iq_stride) {
+        if (res.detected && (size_t)res.fine_peak_time_local + p.n_no_gi_hw <= p.x_stride) {
             s.t0 = (int32_t)res.fine_peak_time_local;
             s.inc0 = res.cfo_fractional_rad + res.cfo_integer_rad;
             for (uint32_t a = 0; a < 8; ++a) s.rms[a] = res.rms_array[a];
@@ -409,7 +413,7 @@ __global__ void k_sync_final(const sync_params_t p, uint32_t n, uint32_t len) {
 cudaError_t launch_sync(const sync_params_t& p, uint32_t n, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
     const phy_dims_t& d = p.d;
-    const uint32_t len = (uint32_t)p.iq_stride;
+    const uint32_t len = p.len;
     k_sync_steps<<<dim3((p.n_steps + 7) / 8, p.n_ant, n), 256, 0, st>>>(p);
     const size_t sm_det = 3 * (size_t)(p.n_steps + 1) * sizeof(double);
     const size_t sm_peak = (3 * (size_t)(2 * d.stf_len_os + 1) + d.stf_len_os) * sizeof(float);
@@ -417,15 +421,16 @@ cudaError_t launch_sync(const sync_params_t& p, uint32_t n, cudaStream_t st) {
     cudaError_t e = cudaFuncSetAttribute(k_sync_peak, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
     if (e != cudaSuccess) return e;
     k_sync_peak<<<n, 256, sm2, st>>>(p, len);
-    const uint32_t n_lag = 2 * d.pat_len_os + 1, LT = (n_lag + XC_LAGS - 1) / XC_LAGS, n_lag_pad = LT * XC_LAGS;
+    const uint32_t n_lag = 2 * p.xc_sl + 1, LT = (n_lag + XC_LAGS - 1) / XC_LAGS, n_lag_pad = LT * XC_LAGS;
     uint32_t IC = XC_THREADS / LT;
-    const uint32_t ic_max = d.stf_len_os / 32 ? d.stf_len_os / 32 : 1;
+    const uint32_t ic_max = p.xc_S / 32 ? p.xc_S / 32 : 1;
     if (IC > ic_max) IC = ic_max;
     if (IC == 0) return cudaErrorInvalidConfiguration;  // more than XC_THREADS * XC_LAGS lags
-    const size_t sm3 = ((size_t)(n_lag_pad + d.stf_len_os) * 9 / 8 + 2 + d.stf_len_os + (size_t)IC * n_lag_pad) * sizeof(float2);
+    const uint32_t S_pad = (p.xc_S + 7) & ~7u;
+    const size_t sm3 = ((size_t)(n_lag_pad + S_pad) * 9 / 8 + 2 + S_pad + (size_t)IC * n_lag_pad) * sizeof(float2);
     e = cudaFuncSetAttribute(k_sync_xcorr, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm3);
     if (e != cudaSuccess) return e;
-    k_sync_xcorr<<<dim3(p.n_tpl, n), XC_THREADS, sm3, st>>>(p, len, IC);
+    k_sync_xcorr<<<dim3(p.n_tpl, n), XC_THREADS, sm3, st>>>(p, p.x_len, IC);
     k_sync_final<<<(n + 127) / 128, 128, 0, st>>>(p, n, len);
     return cudaGetLastError();
 }

@@ -127,7 +127,7 @@ __global__ void __launch_bounds__(256) k_tx_ofdm(const txofdm_params_t p) {
     const uint32_t len = cp + d.N_os;
     const uint32_t start = l == 0 ? 0 : d.stf_len_os + (l - 1) * d.sym_len_os;
     float2* out = p.iq + ((size_t)pkt * d.N_TX + ant) * p.iq_stride + start;
-    const bool mix = meta.iq_phase_rad != 0.f || meta.iq_phase_increment != 0.f;
+    const bool mix = !p.no_mix && (meta.iq_phase_rad != 0.f || meta.iq_phase_increment != 0.f);
     for (uint32_t n = tid; n < len; n += nthr) {
         uint32_t src = (n + d.N_os - (cp % d.N_os)) % d.N_os;
         float2 v = x[src];

@@ -73,7 +73,39 @@ int build_phy_plan(dnrp_ctx* c) {
     UP(c->d_W_scale.upload(Ws));
     UP(c->d_W_scale_opt.upload(Wso));
     UP(c->d_twiddle.upload(tw));
-    c->tx_stride = (d.n_packet_os + 3) & ~3u;
+    // ---- resampling to the hardware rate (tx.cpp:519-560 sample counts; resampler.cpp design)
+    {
+        const uint32_t L = c->cfg.resample_L, M = c->cfg.resample_M;
+        c->resampling = L != M;
+        if (!spec::design_resampler(L, M, os, c->rs_tx) || !spec::design_resampler(M, L, os, c->rs_rx)) {
+            set_last_error("no resampler filter definition for this oversampling (resampler_param.hpp:71-86)");
+            return DNRP_ERR_INVALID;
+        }
+        if (c->resampling) {
+            if (L < M) {
+                set_last_error("the hardware rate must not be below the DECT rate (resample_L >= resample_M)");
+                return DNRP_ERR_INVALID;
+            }
+            if (d.n_packet_os % M != 0) {
+                set_last_error("oversampled packet length with GI not a multiple of M (tx.cpp:537)");
+                return DNRP_ERR_INVALID;
+            }
+            c->n_no_gi_rs = (uint32_t)(((uint64_t)d.n_no_gi_os * L + M - 1) / M);
+            c->n_packet_rs = d.n_packet_os / M * L;
+            c->stf_len_rs = (uint32_t)((uint64_t)d.stf_len_os * L / M);
+            if (c->n_no_gi_rs > c->rs_tx.n_after(d.n_no_gi_os) || c->n_no_gi_rs >= c->n_packet_rs) {
+                set_last_error("resampler creates fewer samples than the packet needs (tx.cpp:530-545)");
+                return DNRP_ERR_INVALID;
+            }
+            c->tx_os_stride = (d.n_no_gi_os + 3) & ~3u;
+            UP(c->d_iq_tx_os.alloc((size_t)c->B * d.N_TX * c->tx_os_stride));
+            UP(c->d_rs_tx_taps.upload(c->rs_tx.taps));
+            UP(c->d_rs_rx_taps.upload(c->rs_rx.taps));
+        } else {
+            c->n_no_gi_rs = d.n_no_gi_os; c->n_packet_rs = d.n_packet_os; c->stf_len_rs = d.stf_len_os;
+        }
+    }
+    c->tx_stride = (c->n_packet_rs + 3) & ~3u;
     UP(c->d_iq_tx.alloc((size_t)c->B * d.N_TX * c->tx_stride));
     UP(c->d_tx_meta.alloc(c->B));
 
@@ -111,7 +143,19 @@ int build_phy_plan(dnrp_ctx* c) {
     }
     // RX window: the packet plus room for two STFs (the detection ignores the first STF + 1 pattern of a window
     // and the fine search looks one pattern to either side of the coarse peak)
-    c->rx_stride = (d.n_packet_os + 2 * d.stf_len_os + 3) & ~3u;
+    c->rx_stride = (c->n_packet_rs + 2 * c->stf_len_rs + 3) & ~3u;   // hardware rate
+    if (c->resampling) {
+        // detection / coarse peak run on the window resampled to the DECT rate (no flush: only outputs whose newest
+        // input sample lies inside the window), the synchronised receiver on the packet resampled from its fine peak
+        const spec::resampler_design_t& r = c->rs_rx;
+        c->sync_len = (uint32_t)(((uint64_t)c->rx_stride * r.L - 1 - r.delay) / r.M + 1);
+        c->sync_stride = (c->sync_len + 3) & ~3u;
+        c->rs_stride = (d.n_no_gi_os + 3) & ~3u;
+        UP(c->d_iq_sync.alloc((size_t)c->B * d.N_RX * c->sync_stride));
+        UP(c->d_iq_rs.alloc((size_t)c->B * d.N_RX * c->rs_stride));
+    } else {
+        c->sync_len = c->sync_stride = c->rx_stride;
+    }
     // packet synchronisation: time-domain STF of a single stream for every N_eff_TX the receiver has to
     // tell apart (stf_template.cpp:81-204 for L = M = 1): scale 1/sqrt(N_OCC/4), unnormalised inverse DFT,
     // long CP, cover sequence.  Only every 4th subcarrier is occupied, so a direct sparse IDFT is cheap.
@@ -134,15 +178,35 @@ int build_phy_plan(dnrp_ctx* c) {
                     xi[n] += yr * sn + yi * cs;
                 }
             }
+            std::vector<float2> t(d.stf_len_os);
             for (uint32_t n = 0; n < d.stf_len_os; ++n) {
                 const uint32_t src = (n + d.N_os - d.stf_cp_os % d.N_os) % d.N_os;
                 const float cv = spec::stf_cover(n / d.pat_len_os);
-                tpl.push_back(make_float2((float)xr[src] * cv, (float)xi[src] * cv));
+                t[n] = make_float2((float)xr[src] * cv, (float)xi[src] * cv);
+            }
+            if (!c->resampling) {
+                tpl.insert(tpl.end(), t.begin(), t.end());
+            } else {
+                // through the TX resampler, truncated to stf_len * L / M (stf_template.cpp:169-194)
+                const spec::resampler_design_t& r = c->rs_tx;
+                for (uint32_t mo = 0; mo < c->stf_len_rs; ++mo) {
+                    const uint64_t pp = (uint64_t)r.delay + (uint64_t)mo * r.M;
+                    const uint32_t l = (uint32_t)(pp % r.L);
+                    const int64_t i0 = (int64_t)(pp / r.L);
+                    float re = 0.f, im = 0.f;
+                    for (uint32_t j = 0; j < r.subfilter_length; ++j) {
+                        const int64_t i = i0 - j;
+                        if (i < 0 || i >= (int64_t)d.stf_len_os) continue;
+                        re += r.taps[j * r.L + l] * t[i].x;
+                        im += r.taps[j * r.L + l] * t[i].y;
+                    }
+                    tpl.push_back(make_float2(re, im));
+                }
             }
         }
         UP(c->d_sync_tpl.upload(tpl));
         c->sync_step = d.pat_len_os / 4;
-        c->sync_n_steps = c->rx_stride / c->sync_step;
+        c->sync_n_steps = c->sync_len / c->sync_step;
         const size_t nb = (size_t)c->B * d.N_RX * c->sync_n_steps;
         UP(c->d_sync_c.alloc(nb));
         UP(c->d_sync_p.alloc(nb));

@@ -53,7 +53,9 @@ typedef struct {
     dnrp_psdef_t psdef;
     uint32_t N_RX;             /* receive antennas */
     uint32_t oversampling;     /* os_min: 1, 2, 4 ... (N_b_DFT_os = oversampling * N_b_DFT) */
-    uint32_t resample_L, resample_M; /* TX: DECT rate * L / M = hardware rate (1/1 = no resampling) */
+    uint32_t resample_L, resample_M; /* DECT rate * oversampling * L / M = hardware rate (1/1 = no resampling); with
+                                      * L != M every IQ buffer crossing this ABI is at the hardware rate: TX resamples
+                                      * up (tx.cpp:913-934), sync and the receiver resample down (rx_pacer.cpp) */
     uint32_t max_batch;
     uint32_t network_id;       /* worker_pool_t::add_network_id, worker_pool.cpp:109-114 */
     uint32_t plcf_type;        /* 1 or 2: PLCF type transmitted / PDC scrambling variant */
@@ -65,6 +67,14 @@ typedef struct {
 /* sp3::get_packet_sizes, lib/src/sections_part3/derivative/packet_sizes.cpp:97-227.
  * DNRP_ERR_INVALID where the reference returns std::nullopt. Host only. */
 int dnrp_get_packet_sizes(const dnrp_psdef_t* psdef, dnrp_packet_sizes_t* out);
+
+/* resampler_t's filter design (lib/src/phy/resample/resampler.cpp:55-140, filter/kaiser.cpp:37-118,
+ * resampler_param.hpp:61-86) for L/M at the given oversampling.  Host only.  taps_out [subfilter_length][L] =
+ * L * h[l + j L], zero padded (may be NULL); info4 = {filter_length, subfilter_length, delay, taps written}.
+ * dnrp_resampler_n_after = resampler_t::get_N_samples_after_resampling (resampler.cpp:310-328). */
+int dnrp_resampler_design(uint32_t L, uint32_t M, uint32_t oversampling, float* taps_out, uint32_t taps_cap,
+                          uint32_t* info4);
+uint32_t dnrp_resampler_n_after(uint32_t L, uint32_t M, uint32_t oversampling, uint32_t n_in);
 
 /* tx_rx_t / worker_tx_rx_t construction (lib/src/phy/tx_rx.cpp:38-129, pool/worker_tx_rx.cpp:43-67):
  * builds all LUTs and device workspaces for one geometry */
@@ -168,6 +178,7 @@ typedef struct {
     uint32_t fine_peak_time_local;
     uint32_t n_detections;             /* detections in this window incl. the ones dropped as invalid */
     uint32_t strongest_ant;            /* antenna the cross-correlation ran on */
+    uint32_t coarse_peak_time_hw;      /* coarse peak converted to the hardware rate (= local without resampling) */
 } dnrp_sync_result_t;
 
 /* sync_chunk_t::search for n IQ windows, first packet of each window: autocorrelator_detection_t,
@@ -260,7 +271,8 @@ typedef enum {
     DNRP_KERNEL_RX_STF = 3,
     DNRP_KERNEL_DERM_PDC = 4,
     DNRP_KERNEL_SYNC = 5,            /* the four synchronisation kernels together */
-    DNRP_KERNEL_COUNT = 6
+    DNRP_KERNEL_RESAMPLE = 6,        /* every k_resample launch (TX, sync window, RX packet) */
+    DNRP_KERNEL_COUNT = 7
 } dnrp_kernel_t;
 int dnrp_kernel_time_enable(dnrp_ctx_t* ctx, int enable);
 int dnrp_kernel_time_read(dnrp_ctx_t* ctx, int kernel, float* ms_total, uint32_t* launches);

@@ -27,6 +27,7 @@ typedef struct {
     float cfo_fractional_rad, cfo_integer_rad;
     int32_t N_eff_TX, fine_peak_time_local;   /* fine peak relative to the window start */
     int32_t n_detections;
+    int32_t coarse_peak_time_hw;              /* coarse peak at the hardware rate (sync_chunk.cpp:204-205) */
 } orc_sync_report_t;
 
 /* ---- movsum_t<float> / movsum_uw_t (movsum.hpp:33-104, movsum_uw.cpp:28-97) */
@@ -81,10 +82,14 @@ static cf_t conj_dot(const cf_t* a, const cf_t* b, int n);
 
 static const float COVER[9] = {1, -1, 1, 1, -1, -1, -1, -1, -1};  /* stf.hpp:146-148 */
 
-/* One window.  iq [n_ant][stride]; len = usable samples; templates [n_tpl][stf_len] (N_eff_TX = 1, 2, 4, 8 ...).
- * search_length = number of samples the detection may consume (A + B of sync_chunk.hpp:108-124). */
-int orc_sync_search(const cf_t* iq, long stride, int len, int n_ant, int u, int b, int os, const cf_t* templates,
-                    int n_tpl, int search_length, double samp_rate, orc_sync_report_t* rep) {
+/* One window.  iq [n_ant][stride] at the DECT rate (x os); len = usable samples; search_length = number of samples
+ * the detection may consume (A + B of sync_chunk.hpp:108-124).  The cross-correlation runs on the hardware-rate
+ * samples iq_hw [n_ant][stride_hw] (NULL: = iq, L = M = 1) against templates [n_tpl][tpl_len] that went through the
+ * TX resampler (tpl_len = stf_len * L / M), hardware rate = DECT rate * L / M. */
+int orc_sync_search2(const cf_t* iq, long stride, int len, int n_ant, int u, int b, int os, const cf_t* templates,
+                     int n_tpl, int search_length, double samp_rate, const cf_t* iq_hw, long stride_hw, int len_hw,
+                     int L, int M, int tpl_len, orc_sync_report_t* rep) {
+    if (!iq_hw) { iq_hw = iq; stride_hw = stride; len_hw = len; L = M = 1; }
     const int bos = b * os;
     const int n_pat = u == 1 ? 7 : 9;
     const int stf_len = (u == 1 ? 112 : 144) * bos, pat = stf_len / n_pat;
@@ -188,14 +193,17 @@ int orc_sync_search(const cf_t* iq, long stride, int len, int n_ant, int u, int 
         rep->cfo_integer_rad = 0.0f;   /* coarse_peak_f_domain.cpp:94-201: not implemented in the reference */
 
         /* ---- crosscorrelator_t on the strongest antenna (ALL_ANTENNAS switch is off, sync_param.hpp:286) */
-        const int sl = 16 * bos, sr = 16 * bos, n_lag = sl + 1 + sr;
-        const int w0 = rep->coarse_peak_time_local - sl;
-        if (w0 < 0 || w0 + n_lag + stf_len - 1 > len) { ret = -2; break; }
+        /* sync_chunk.cpp:204-205 -> rx_pacer.cpp:311-318: local (resampled) time -> hardware-rate time */
+        rep->coarse_peak_time_hw = (int)round((double)rep->coarse_peak_time_local * (double)L / (double)M);
+        const int sl = 16 * b * os * L / M, sr = sl, n_lag = sl + 1 + sr;   /* crosscorrelator.cpp:52-56 */
+        const int w0 = rep->coarse_peak_time_hw - sl;
+        if (w0 < 0 || w0 + n_lag + tpl_len - 1 > len_hw) { ret = -2; break; }
         int amax = 0; for (int a = 1; a < n_ant; ++a) if (rep->coarse_peak_array[a] > rep->coarse_peak_array[amax]) amax = a;
-        cf_t* mix = (cf_t*)malloc(sizeof(cf_t) * (n_lag + stf_len));
-        const float inc = rep->cfo_fractional_rad + rep->cfo_integer_rad;
-        for (int i = 0; i < n_lag + stf_len - 1; ++i) {
-            const cf_t v = iq[amax * stride + w0 + i];
+        cf_t* mix = (cf_t*)malloc(sizeof(cf_t) * (n_lag + tpl_len));
+        /* crosscorrelator.cpp:97-105: CFO per hardware sample */
+        const float inc = (rep->cfo_fractional_rad + rep->cfo_integer_rad) * (float)M / (float)L;
+        for (int i = 0; i < n_lag + tpl_len - 1; ++i) {
+            const cf_t v = iq_hw[amax * stride_hw + w0 + i];
             const double ph = (double)inc * i; const float c = (float)cos(ph), s = (float)sin(ph);
             mix[i].re = v.re * c - v.im * s; mix[i].im = v.re * s + v.im * c;
         }
@@ -203,7 +211,7 @@ int orc_sync_search(const cf_t* iq, long stride, int len, int n_ant, int u, int 
         for (int tpl = 0; tpl < n_tpl; ++tpl) {
             float mmax = -1.0f; int imax = 0;
             for (int j = 0; j < n_lag; ++j) {
-                const cf_t v = conj_dot(mix + j, templates + (long)tpl * stf_len, stf_len);
+                const cf_t v = conj_dot(mix + j, templates + (long)tpl * tpl_len, tpl_len);
                 const float m2 = v.re * v.re + v.im * v.im;
                 if (m2 > mmax) { mmax = m2; imax = j; }
             }
@@ -218,6 +226,13 @@ int orc_sync_search(const cf_t* iq, long stride, int len, int n_ant, int u, int 
     }
     for (int a = 0; a < n_ant; ++a) { free(mc[a].reg); free(mp[a].reg); }
     return ret;
+}
+
+int orc_sync_search(const cf_t* iq, long stride, int len, int n_ant, int u, int b, int os, const cf_t* templates,
+                    int n_tpl, int search_length, double samp_rate, orc_sync_report_t* rep) {
+    const int stf_len = (u == 1 ? 112 : 144) * b * os;
+    return orc_sync_search2(iq, stride, len, n_ant, u, b, os, templates, n_tpl, search_length, samp_rate, NULL, 0, 0,
+                            1, 1, stf_len, rep);
 }
 
 static cf_t conj_dot(const cf_t* a, const cf_t* b, int n) {  /* sum a * conj(b) */

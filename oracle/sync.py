@@ -15,7 +15,7 @@ class Report(C.Structure):
                 ("detection_metric", C.c_float), ("coarse_peak_time_local", C.c_int32),
                 ("coarse_peak_array", C.c_float * 8), ("rms_array", C.c_float * 8), ("cfo_fractional_rad", C.c_float),
                 ("cfo_integer_rad", C.c_float), ("N_eff_TX", C.c_int32), ("fine_peak_time_local", C.c_int32),
-                ("n_detections", C.c_int32)]
+                ("n_detections", C.c_int32), ("coarse_peak_time_hw", C.c_int32)]
 
 
 def stf_template(u, b, N_eff_TX, os=1):
@@ -37,26 +37,41 @@ def stf_template(u, b, N_eff_TX, os=1):
 
 
 @functools.lru_cache(maxsize=None)
-def templates(u, b, N_eff_TX_max, os=1):
+def templates(u, b, N_eff_TX_max, os=1, L=1, M=1):
+    """stf_template_t for every N_eff_TX; with L != M each template goes through the TX resampler (reset, resample,
+    flush) and is truncated to stf_len * L / M samples (stf_template.cpp:169-194)"""
     n = [1, 2, 4, 8]
-    return np.stack([stf_template(u, b, v, os) for v in n if v <= N_eff_TX_max])
+    t = [stf_template(u, b, v, os) for v in n if v <= N_eff_TX_max]
+    if L != M:
+        from . import resample as rs
+        t = [rs.stream(x, L, M, os)[:x.size * L // M] for x in t]
+    return np.stack(t)
 
 
-def search(iq, u, b, os=1, N_eff_TX_max=1, search_length=None):
-    """iq [n_ant][len] complex64 -> Report (first packet found in the window)"""
-    L = lib()
+def search(iq, u, b, os=1, N_eff_TX_max=1, search_length=None, resample=(1, 1)):
+    """iq [n_ant][len] complex64 at the hardware rate -> Report (first packet found in the window).
+    resample = (L, M) of the TX direction: the window is resampled with M/L for detection and coarse peak (rx_pacer,
+    zero history at the window start, no flush); the cross-correlation runs on the hardware-rate samples."""
+    lb = lib()
     iq = np.ascontiguousarray(iq, dtype=np.complex64)
+    L_, M_ = resample
+    iq_hw = iq
+    if L_ != M_:
+        from . import resample as rs
+        iq = np.ascontiguousarray(np.stack([rs.stream(x, M_, L_, os, flush=False) for x in iq_hw]))
     n_ant, n = iq.shape
-    tpl = np.ascontiguousarray(templates(u, b, N_eff_TX_max, os))
-    stf_len = tpl.shape[1]
+    tpl = np.ascontiguousarray(templates(u, b, N_eff_TX_max, os, L_, M_))
+    stf_len = (112 if u == 1 else 144) * b * os
     if search_length is None:
         search_length = n - stf_len - stf_len // (7 if u == 1 else 9)
     rep = Report()
-    L.orc_sync_search.restype = C.c_int
-    L.orc_sync_search.argtypes = [C.c_void_p, C.c_long, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p, C.c_int,
-                                  C.c_int, C.c_double, C.c_void_p]
-    rc = L.orc_sync_search(iq.ctypes.data, n, n, n_ant, u, b, os, tpl.ctypes.data, tpl.shape[0], int(search_length),
-                           float(u * b * os * 1.728e6), C.addressof(rep))
+    lb.orc_sync_search2.restype = C.c_int
+    lb.orc_sync_search2.argtypes = [C.c_void_p, C.c_long, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                    C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_long, C.c_int, C.c_int, C.c_int,
+                                    C.c_int, C.c_void_p]
+    rc = lb.orc_sync_search2(iq.ctypes.data, n, n, n_ant, u, b, os, tpl.ctypes.data, tpl.shape[0], int(search_length),
+                             float(u * b * os * 1.728e6), iq_hw.ctypes.data, iq_hw.shape[1], iq_hw.shape[1], L_, M_,
+                             tpl.shape[1], C.addressof(rep))
     if rc == -2:
         # the fine search window leaves the buffer (cannot happen in the reference's ring buffer): the product
         # reports such a window as "not detected", and so does this front

@@ -78,8 +78,11 @@ def codebook(N_TS, N_TX, idx):
 
 
 def tx_packet(ps, plcf_bytes, tb_bytes, network_id=123456789, plcf_type=1, rv=0, codebook_index=0, os=1,
-              DAC_scale=1.0, iq_phase_rad=0.0, iq_phase_increment=0.0, GI_percentage=5, debug=None):
-    """returns complex64 [N_TX][N_samples_transmit] (tx.cpp:165-314 with L = M = 1)."""
+              DAC_scale=1.0, iq_phase_rad=0.0, iq_phase_increment=0.0, GI_percentage=5, debug=None,
+              resample=(1, 1)):
+    """returns complex64 [N_TX][N_samples_transmit] (tx.cpp:165-314).  resample = (L, M): every OFDM symbol goes
+    through the streaming resampler (tx.cpp:913-934), the history is flushed at the end (:679-704), the mixer runs at
+    the hardware rate."""
     u, b = ps["u"], ps["b"]
     N_TS, N_TX, N_SS, N_eff_TX = ps["N_TS"], ps["N_TX"], ps["N_SS"], ps["N_eff_TX"]
     N_OCC = ps["N_b_OCC"]
@@ -181,7 +184,20 @@ def tx_packet(ps, plcf_bytes, tb_bytes, network_id=123456789, plcf_type=1, rv=0,
         if debug is not None:
             debug["X"].append(X)
     assert pos == n_no_gi
-    # mixer (tx.cpp:913-934 with the resampler bypassed), phase continuous from the first sample
+    L, M = resample
+    if L != M:
+        from . import resample as rs
+        blocks = [stf_cp_os + N_os] + [cp_os + N_os] * ps["N_DF_symb"]
+        n_no_gi_rs = -(-n_no_gi * L // M)                       # tx.cpp:527-528
+        n_packet_rs = ps["N_samples_packet"] * os // M * L      # tx.cpp:541-542
+        n_tx = n_no_gi_rs + (n_packet_rs - n_no_gi_rs) * GI_percentage // 100
+        res = np.zeros((N_TX, n_tx), dtype=np.complex64)
+        for a in range(N_TX):
+            y = rs.stream(out[a, :n_no_gi], L, M, os, blocks=blocks)
+            assert y.size >= n_no_gi_rs
+            res[a, :n_no_gi_rs] = y[:n_no_gi_rs]
+        out = res
+    # mixer (tx.cpp:913-934), phase continuous from the first sample at the output rate
     if iq_phase_rad != 0.0 or iq_phase_increment != 0.0:
         n = np.arange(n_tx, dtype=np.float64)
         out = (out * np.exp(1j * (iq_phase_rad + iq_phase_increment * n))).astype(np.complex64)
