@@ -82,11 +82,13 @@ assert PDC_DTYPE.itemsize == C.sizeof(PdcReport)
 
 class ChannelDesc(C.Structure):
     _fields_ = [("snr_dB", C.c_float), ("net_bandwidth_norm", C.c_float), ("t0", C.c_uint32), ("mode", C.c_uint32),
-                ("seed", C.c_uint64)]
+                ("seed", C.c_uint64), ("pdp_idx", C.c_uint32), ("tau_rms_ns", C.c_float), ("fD_Hz", C.c_float),
+                ("time_64", C.c_int64)]
 
 
 CHANNEL_DTYPE = np.dtype([("snr_dB", "f4"), ("net_bandwidth_norm", "f4"), ("t0", "u4"), ("mode", "u4"),
-                          ("seed", "u8")], align=True)
+                          ("seed", "u8"), ("pdp_idx", "u4"), ("tau_rms_ns", "f4"), ("fD_Hz", "f4"), ("time_64", "i8")],
+                         align=True)
 assert CHANNEL_DTYPE.itemsize == C.sizeof(ChannelDesc)
 TAP_Y, TAP_DRS_ZF, TAP_STF_ZF, TAP_LLR_PCC, TAP_LLR_PDC, TAP_WIENER_CLASS, TAP_TB_OK = 1, 2, 3, 4, 5, 6, 7
 KERNEL_TURBO_DECODE_PDC, KERNEL_RX_FFT, KERNEL_RX_DEMAP_PDC, KERNEL_RX_STF, KERNEL_DERM_PDC, KERNEL_SYNC, \
@@ -303,12 +305,14 @@ class Phy:
         _check(lib().dnrp_loopback_tx_to_rx(self._ctx, n, t0))
 
     # ---- simulation channel (reference simulation/vspace.cpp:437-512, wireless/channel_{awgn,flat}.cpp)
-    def channel(self, n, snr_dB=100.0, t0=0, mode=0, seed=1, net_bandwidth_norm=None, fetch=False):
+    def channel(self, n, snr_dB=100.0, t0=0, mode=0, seed=1, net_bandwidth_norm=None, fetch=False, pdp_idx=0,
+                tau_rms_ns=0.0, fD_Hz=0.0, time_64=0):
         if net_bandwidth_norm is None:
             net_bandwidth_norm = self.resample[1] / (self.resample[0] * self.oversampling)
         descs = np.zeros(n, dtype=CHANNEL_DTYPE)
         descs["snr_dB"], descs["net_bandwidth_norm"], descs["t0"], descs["mode"] = snr_dB, net_bandwidth_norm, t0, mode
         descs["seed"] = seed
+        descs["pdp_idx"], descs["tau_rms_ns"], descs["fD_Hz"], descs["time_64"] = pdp_idx, tau_rms_ns, fD_Hz, time_64
         out = np.zeros((n, self.N_RX, self.rx_stride()), dtype=np.complex64) if fetch else None
         _check(lib().dnrp_channel_batch(self._ctx, n, descs.ctypes.data_as(C.c_void_p), _ptr(out, np.complex64)))
         return out

@@ -3,6 +3,7 @@
 #include <cmath>
 #include <cstring>
 #include "ctx.hpp"
+#include "spec_channel.hpp"
 
 using namespace dnrp;
 
@@ -64,7 +65,12 @@ int run_channel(dnrp_ctx* c, uint32_t n) {
     p.rx = c->d_iq_rx.p; p.rx_stride = c->rx_stride;
     p.n_samples = c->n_packet_rs;
     p.meta = c->d_chan_meta.p;
+    p.sin_tab = c->d_chan_sin.p;
     DNRP_LAUNCH(c, -1, launch_channel(p, n, c->stream));
+    if (c->chan_any_tdl) {
+        ++c->launches;  // setup + main kernel
+        DNRP_LAUNCH(c, -1, launch_channel_tdl(p, n, c->stream));
+    }
     return DNRP_OK;
 }
 
@@ -261,14 +267,38 @@ int dnrp_channel_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_channel_desc_t* des
     DNRP_CUDA(cudaSetDevice(c->device));
     const phy_dims_t& d = c->dims;
     std::vector<chan_meta_dev_t> meta(n);
+    bool any_tdl = false;
+    const double samp_rate_hw = (double)d.u * d.b * c->cfg.oversampling * 1.728e6 * c->cfg.resample_L / c->cfg.resample_M;
     for (uint32_t i = 0; i < n; ++i) {
         DNRP_REQUIRE(descs[i].t0 + c->n_packet_rs <= c->rx_stride, "offset exceeds the IQ window");
-        DNRP_REQUIRE(descs[i].mode <= 1, "unknown channel mode");
+        DNRP_REQUIRE(descs[i].mode <= 2, "unknown channel mode");
         DNRP_REQUIRE(descs[i].net_bandwidth_norm > 0.f, "net_bandwidth_norm must be > 0");
         const float n0_dBFS = -10.0f * log10f(descs[i].net_bandwidth_norm) - descs[i].snr_dB;  // noise.cpp:37-38
-        meta[i] = {descs[i].t0, descs[i].mode, powf(10.0f, n0_dBFS / 20.0f), (uint32_t)descs[i].seed,
-                   (uint32_t)(descs[i].seed >> 32)};
+        chan_meta_dev_t& m = meta[i];
+        std::memset(&m, 0, sizeof(m));
+        m.t0 = descs[i].t0; m.mode = descs[i].mode; m.sigma = powf(10.0f, n0_dBFS / 20.0f);
+        m.seed_lo = (uint32_t)descs[i].seed; m.seed_hi = (uint32_t)(descs[i].seed >> 32);
+        if (descs[i].mode == 2) {
+            // link.cpp:44-46 asserts these bounds
+            DNRP_REQUIRE(descs[i].pdp_idx < spec::TDL_PROFILES, "pdp_idx out of bound");
+            DNRP_REQUIRE(descs[i].tau_rms_ns >= 0.f && descs[i].tau_rms_ns <= 2000.f, "tau_rms_ns out of bound");
+            DNRP_REQUIRE(descs[i].fD_Hz >= 0.f && descs[i].fD_Hz <= 2000.f, "fD_Hz out of bound");
+            DNRP_REQUIRE(descs[i].time_64 >= 0, "time_64 must not be negative");
+            double pw[spec::TDL_MAX_TAPS];
+            m.samp_rate = samp_rate_hw;
+            m.n_taps = spec::tdl_taps(samp_rate_hw, descs[i].pdp_idx, descs[i].tau_rms_ns, m.tap_delay, pw);
+            for (uint32_t k = 0; k < m.n_taps; ++k) {
+                float sc = 1.0f / sqrtf(40.0f);   // link.cpp:268-274
+                sc *= sqrt(pw[k]);
+                m.tap_scale[k] = sc;
+            }
+            m.fD_Hz = descs[i].fD_Hz; m.time_64 = descs[i].time_64;
+            any_tdl = true;
+        }
     }
+    c->chan_any_tdl = any_tdl;
+    if (any_tdl && c->d_chan_sin.n == 0)
+        DNRP_CUDA(c->d_chan_sin.alloc((size_t)c->B * d.N_RX * d.N_TX * 9 * 40));
     DNRP_CUDA(cudaMemcpyAsync(c->d_chan_meta.p, meta.data(), n * sizeof(chan_meta_dev_t), cudaMemcpyHostToDevice,
                               c->stream));
     DNRP_CUDA(cudaStreamSynchronize(c->stream));  // meta is a local pageable vector

@@ -127,6 +127,8 @@ struct dnrp_ctx {
     dnrp::dbuf<uint8_t> d_cls;
     std::vector<dnrp::rx_state_t> h_rx_state;
     dnrp::dbuf<dnrp::chan_meta_dev_t> d_chan_meta;
+    dnrp::dbuf<dnrp::tdl_sin_t> d_chan_sin;   // allocated by the first doubly selective channel call
+    bool chan_any_tdl = false;
 
     // resampling between the DECT rate (x oversampling) and the hardware rate: hw = dect * L / M (TX direction);
     // the receive direction uses M / L.  All IQ crossing the C ABI is at the hardware rate.

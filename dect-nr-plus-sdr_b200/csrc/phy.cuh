@@ -155,9 +155,23 @@ cudaError_t launch_sync(const sync_params_t& p, uint32_t n_packets, cudaStream_t
 // simulation channel (phy_channel.cu)
 struct chan_meta_dev_t {
     uint32_t t0;        // first sample of the packet inside the RX window
-    uint32_t mode;      // 0 = awgn (unit links), 1 = flat (one CN(0,1) coefficient per link and packet)
+    uint32_t mode;      // 0 = awgn (unit links), 1 = flat (one CN(0,1) coefficient per link and packet),
+                        // 2 = doubly selective (tapped delay line, 40 sinusoids per tap and link)
     float sigma;        // standard deviation of the complex noise sample, sqrt(10^(n0_dBFS / 10))
     uint32_t seed_lo, seed_hi;
+    // mode 2: link_t::set_pdp result (host), Doppler, absolute time of the window's first sample
+    uint32_t n_taps;
+    uint32_t tap_delay[9];
+    float tap_scale[9];  // sqrt(tap power) / sqrt(40)
+    float fD_Hz;
+    double samp_rate;
+    long long time_64;
+};
+// one sinusoid of one tap of one link (link.cpp:165-215): period in samples (sign = sense of rotation), start phase
+struct tdl_sin_t {
+    long long period;
+    float phase0;
+    float s2s;          // (float)(2 pi / period)
 };
 struct channel_params_t {
     uint32_t N_TX, N_RX;
@@ -165,7 +179,9 @@ struct channel_params_t {
     float2* rx;        size_t rx_stride;   // [packet][N_RX][rx_stride]
     uint32_t n_samples;                    // TX samples superimposed (rest of the window is noise only)
     const chan_meta_dev_t* meta;           // [packet]
+    tdl_sin_t* sin_tab;                    // [packet][N_RX][N_TX][9][40], mode 2 only
 };
 cudaError_t launch_channel(const channel_params_t& p, uint32_t n_packets, cudaStream_t st);
+cudaError_t launch_channel_tdl(const channel_params_t& p, uint32_t n_packets, cudaStream_t st);
 
 }  // namespace dnrp

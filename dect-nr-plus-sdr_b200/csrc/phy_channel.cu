@@ -36,6 +36,7 @@ __device__ __forceinline__ float2 cn01(uint32_t a, uint32_t b) {
 __global__ void __launch_bounds__(256) k_channel(const channel_params_t p) {
     const uint32_t a = blockIdx.y, pkt = blockIdx.z;
     const chan_meta_dev_t m = p.meta[pkt];
+    if (m.mode == 2) return;   // k_channel_tdl
     __shared__ float2 g[8];
     if (threadIdx.x < p.N_TX) {
         float2 v = make_float2(1.f, 0.f);
@@ -73,6 +74,115 @@ __global__ void __launch_bounds__(256) k_channel(const channel_params_t p) {
 cudaError_t launch_channel(const channel_params_t& p, uint32_t n_packets, cudaStream_t st) {
     const uint32_t pairs = (p.rx_stride + 1) / 2;
     k_channel<<<dim3((pairs + 255) / 256, p.N_RX, n_packets), 256, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
+// ---- doubly selective channel (channel_doubly.cpp:59-87, link.cpp:165-282): per link a tapped delay line whose tap
+// coefficients are sums of 40 unit sinusoids with Doppler fD cos(angle).  The reference rotates chunk by chunk with a
+// recursive rotator restarted from time_64 % |period|; here a block evaluates that closed form once per sinusoid at
+// its first sample and every thread advances it with fixed rotations (by its lane offset, then by the block width).
+constexpr uint32_t TDL_R = 8, TDL_THREADS = 256, TDL_SIN = 40, TDL_TAPS = 9;
+
+__device__ __forceinline__ float rand_m1p1(uint32_t r) {
+    return ((float)(r >> 8) + 0.5f) * (1.0f / 8388608.0f) - 1.0f;
+}
+
+// grid (packet), one thread per (rx, tx, tap, sinusoid): draw angle of arrival and start phase
+__global__ void __launch_bounds__(256) k_channel_tdl_setup(const channel_params_t p) {
+    const uint32_t pkt = blockIdx.x;
+    const chan_meta_dev_t& m = p.meta[pkt];
+    if (m.mode != 2) return;
+    const uint32_t per_ant = p.N_TX * TDL_TAPS * TDL_SIN, total = p.N_RX * per_ant;
+    for (uint32_t e = threadIdx.x; e < total; e += blockDim.x) {
+        const uint32_t a = e / per_ant, rem = e % per_ant;
+        const uint32_t t = rem / (TDL_TAPS * TDL_SIN), i = (rem / TDL_SIN) % TDL_TAPS, j = rem % TDL_SIN;
+        tdl_sin_t s;
+        s.period = 0x7fffffffffffffffLL; s.phase0 = 0.f; s.s2s = 0.f;
+        if (i < m.n_taps) {
+            const uint4 r = philox4x32_10(make_uint4(j | (i << 8) | (t << 16), a, pkt, 2u),
+                                          make_uint2(m.seed_lo, m.seed_hi));
+            const double ang = (double)rand_m1p1(r.x) * 2.0 * 3.14159265358979323846;
+            const double fd = (double)m.fD_Hz * cos(ang);
+            if (!(-0.01f < fd && fd < 0.01f)) s.period = (long long)(m.samp_rate / fd);   // else: dead band
+            s.phase0 = rand_m1p1(r.y) * 2.0f * 3.14159265358979323846f;
+            s.s2s = (float)((double)(2.0f * 3.14159265358979323846f) / (double)s.period);
+        }
+        p.sin_tab[(size_t)pkt * total + e] = s;
+    }
+}
+
+// grid (ceil(rx_stride / (TDL_THREADS * TDL_R)), N_RX, packet); thread = samples base + tid + 256 r
+__global__ void __launch_bounds__(TDL_THREADS) k_channel_tdl(const channel_params_t p) {
+    extern __shared__ float4 s_rot[];   // per (tx, tap, sinusoid): phasor at the block's first sample, rotation by 256
+    const uint32_t a = blockIdx.y, pkt = blockIdx.z, tid = threadIdx.x;
+    const chan_meta_dev_t& m = p.meta[pkt];
+    if (m.mode != 2) return;
+    float* s_s2s = reinterpret_cast<float*>(s_rot + p.N_TX * TDL_TAPS * TDL_SIN);
+    const uint32_t base = blockIdx.x * TDL_THREADS * TDL_R;
+    const uint32_t per_ant = p.N_TX * TDL_TAPS * TDL_SIN;
+    const tdl_sin_t* tab = p.sin_tab + ((size_t)pkt * p.N_RX + a) * per_ant;
+    for (uint32_t e = tid; e < per_ant; e += TDL_THREADS) {
+        const tdl_sin_t s = tab[e];
+        const long long ap = s.period < 0 ? -s.period : s.period;
+        const double s2s = (double)(2.0f * 3.14159265358979323846f) / (double)s.period;
+        const float ph = (float)(s2s * (double)((m.time_64 + (long long)base) % ap)) + s.phase0;
+        float sn, cs, sn2, cs2;
+        sincosf(ph, &sn, &cs);
+        sincosf(s.s2s * (float)TDL_THREADS, &sn2, &cs2);
+        s_rot[e] = make_float4(cs, sn, cs2, sn2);
+        s_s2s[e] = s.s2s;
+    }
+    __syncthreads();
+    float2 y[TDL_R];
+#pragma unroll
+    for (uint32_t r = 0; r < TDL_R; ++r) y[r] = make_float2(0.f, 0.f);
+    for (uint32_t t = 0; t < p.N_TX; ++t) {
+        const float2* x = p.tx + ((size_t)pkt * p.N_TX + t) * p.tx_stride;
+        for (uint32_t i = 0; i < m.n_taps; ++i) {
+            float2 acc[TDL_R];
+#pragma unroll
+            for (uint32_t r = 0; r < TDL_R; ++r) acc[r] = make_float2(0.f, 0.f);
+            const uint32_t e0 = (t * TDL_TAPS + i) * TDL_SIN;
+            for (uint32_t j = 0; j < TDL_SIN; ++j) {
+                const float4 rt = s_rot[e0 + j];
+                float sn, cs;
+                sincosf(s_s2s[e0 + j] * (float)tid, &sn, &cs);
+                float2 ph = cmul(make_float2(rt.x, rt.y), make_float2(cs, sn));
+                const float2 step = make_float2(rt.z, rt.w);
+#pragma unroll
+                for (uint32_t r = 0; r < TDL_R; ++r) {
+                    acc[r] = cadd(acc[r], ph);
+                    ph = cmul(ph, step);
+                }
+            }
+            const float sc = m.tap_scale[i];
+            const long long off = (long long)m.t0 + m.tap_delay[i];
+#pragma unroll
+            for (uint32_t r = 0; r < TDL_R; ++r) {
+                const long long k = (long long)(base + tid + r * TDL_THREADS) - off;
+                if (k >= 0 && k < (long long)p.n_samples)
+                    y[r] = cadd(y[r], cmul(make_float2(acc[r].x * sc, acc[r].y * sc), x[k]));
+            }
+        }
+    }
+    float2* out = p.rx + ((size_t)pkt * p.N_RX + a) * p.rx_stride;
+#pragma unroll
+    for (uint32_t r = 0; r < TDL_R; ++r) {
+        const uint32_t n = base + tid + r * TDL_THREADS;
+        if (n >= p.rx_stride) continue;
+        const uint4 q = philox4x32_10(make_uint4(n >> 1, a, pkt, 0u), make_uint2(m.seed_lo, m.seed_hi));
+        const float2 w = (n & 1u) ? cn01(q.z, q.w) : cn01(q.x, q.y);
+        out[n] = make_float2(y[r].x + w.x * m.sigma, y[r].y + w.y * m.sigma);
+    }
+}
+
+cudaError_t launch_channel_tdl(const channel_params_t& p, uint32_t n_packets, cudaStream_t st) {
+    k_channel_tdl_setup<<<n_packets, 256, 0, st>>>(p);
+    const size_t smem = (size_t)p.N_TX * TDL_TAPS * TDL_SIN * (sizeof(float4) + sizeof(float));
+    cudaError_t e = cudaFuncSetAttribute(k_channel_tdl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    const uint32_t per_block = TDL_THREADS * TDL_R;
+    k_channel_tdl<<<dim3((p.rx_stride + per_block - 1) / per_block, p.N_RX, n_packets), TDL_THREADS, smem, st>>>(p);
     return cudaGetLastError();
 }
 

@@ -237,8 +237,15 @@ typedef struct {
     float snr_dB;
     float net_bandwidth_norm;   /* 1 / oversampling in the reference's simulator */
     uint32_t t0;
-    uint32_t mode;              /* 0 awgn, 1 flat */
+    uint32_t mode;              /* 0 awgn, 1 flat, 2 doubly selective (tapped delay line, below) */
     uint64_t seed;
+    /* mode 2 only: channel_doubly_t "doubly_<pdp_idx>_<tau_rms_ns>_<fD_Hz>" (channel_doubly.cpp:95-135, link.cpp):
+     * generic power delay profile 0..2 stretched to tau_rms_ns (0..2000), 40 sinusoids per tap with maximum Doppler
+     * fD_Hz (0..2000), evaluated at absolute sample time time_64 + n of the hardware rate */
+    uint32_t pdp_idx;
+    float tau_rms_ns;
+    float fD_Hz;
+    int64_t time_64;
 } dnrp_channel_desc_t;
 
 /* reads the n packets left on the device by dnrp_tx_batch, writes the receiver's IQ windows (device);

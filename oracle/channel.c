@@ -9,6 +9,7 @@
  */
 #include <math.h>
 #include <stdint.h>
+#include <stdlib.h>
 
 typedef struct { float re, im; } cf_t;
 
@@ -63,5 +64,103 @@ void orc_channel(const cf_t* tx, long tx_stride, int N_TX, int n_samples, cf_t* 
                 rx[(long)a * rx_stride + n] = y[i];
             }
         }
+    }
+}
+
+/* ---- doubly selective channel: tapped delay line with a sum of 40 sinusoids per tap
+ * (lib/src/simulation/wireless/channel_doubly.cpp:59-87, link.cpp:72-146 set_pdp, :165-215 randomize, :217-282
+ * pass_through_link; profiles link.hpp:96-109).  The reference draws angles / phases from a time seeded generator
+ * and rotates chunk by chunk (spp_size) with a recursive VOLK rotator restarted from time_64 % |period| at every
+ * chunk; here every sample's phase is that closed form, phase = 2 pi / P * ((time_64 + n) % |P|) + phase0, and the
+ * draws come from Philox (counter = (sinusoid | tap << 8 | tx << 16, rx antenna, packet, 2)).  Pathloss = 1. */
+static const double TDL_DELAY_NS[3][9] = {{0, 30, 70, 90, 110, 190, 410, NAN, NAN},
+                                          {0, 30, 150, 310, 370, 710, 1090, 1730, 2510},
+                                          {0, 50, 120, 200, 230, 500, 1600, 2300, 5000}};
+static const double TDL_POWER_DB[3][9] = {{+0.0f, -1.0f, -2.0f, -3.0f, -8.0f, -17.2f, -20.8f, NAN, NAN},
+                                          {+0.0f, -1.5f, -1.4f, -3.6f, -0.6f, -9.1f, -7.0f, -12.0f, -16.9f},
+                                          {-1.0f, -1.0f, -1.0f, +0.0f, +0.0f, +0.0f, -3.0f, -5.0f, -7.0f}};
+
+/* link_t::get_tau_rms_ns (link.cpp:290-322) of a generic profile; the reference quotes 43.13 / 356.65 / 990.93 ns
+ * (link.hpp:84-88) */
+double orc_tdl_tau_rms_ns(int pdp_idx) {
+    int nfin = 0;
+    for (int i = 0; i < 9; ++i) { if (isfinite(TDL_DELAY_NS[pdp_idx][i])) ++nfin; else break; }
+    double pl[9], sum = 0, mean = 0, var = 0;
+    for (int i = 0; i < nfin; ++i) { pl[i] = pow(10.0, TDL_POWER_DB[pdp_idx][i] / 10.0); sum += pl[i]; }
+    for (int i = 0; i < nfin; ++i) mean += TDL_DELAY_NS[pdp_idx][i] * (pl[i] / sum);
+    for (int i = 0; i < nfin; ++i) { const double A = TDL_DELAY_NS[pdp_idx][i] - mean; var += A * A * (pl[i] / sum); }
+    return sqrt(var);
+}
+
+/* link_t::set_pdp: returns the number of merged taps; delays in samples, powers normalised to sum 1 */
+int orc_tdl_pdp(double samp_rate, int pdp_idx, float tau_rms_ns, uint32_t* delay_smpl, double* power_lin) {
+    int nfin = 0;
+    for (int i = 0; i < 9; ++i) { if (isfinite(TDL_DELAY_NS[pdp_idx][i])) ++nfin; else break; }
+    double pl[9], sum = 0, mean = 0, var = 0;
+    for (int i = 0; i < nfin; ++i) { pl[i] = pow(10.0, TDL_POWER_DB[pdp_idx][i] / 10.0); sum += pl[i]; }
+    for (int i = 0; i < nfin; ++i) mean += TDL_DELAY_NS[pdp_idx][i] * (pl[i] / sum);
+    for (int i = 0; i < nfin; ++i) { const double A = TDL_DELAY_NS[pdp_idx][i] - mean; var += A * A * (pl[i] / sum); }
+    const double scale = (double)tau_rms_ns / sqrt(var), Ts = 1.0 / samp_rate;
+    int n = 0;
+    for (int i = 0; i < nfin; ++i) {
+        const uint32_t A = (uint32_t)floor(TDL_DELAY_NS[pdp_idx][i] * 1.0e-9 * scale / Ts);
+        int idx = -1;
+        for (int j = 0; j < n; ++j) if (delay_smpl[j] == A) { idx = j; break; }
+        if (idx < 0) { delay_smpl[n] = A; power_lin[n] = pl[i]; ++n; } else power_lin[idx] += pl[i];
+    }
+    double s2 = 0;
+    for (int i = 0; i < n; ++i) s2 += power_lin[i];
+    for (int i = 0; i < n; ++i) power_lin[i] /= s2;
+    return n;
+}
+
+static float m1p1(uint32_t r) { return ((float)(r >> 8) + 0.5f) * (1.0f / 8388608.0f) - 1.0f; }
+
+void orc_channel_doubly(const cf_t* tx, long tx_stride, int N_TX, int n_samples, cf_t* rx, long rx_stride, int N_RX,
+                        int t0, float snr_dB, float net_bandwidth_norm, uint64_t seed, uint32_t pkt,
+                        double samp_rate, int pdp_idx, float tau_rms_ns, float fD_Hz, int64_t time_64) {
+    const float n0_dBFS = -10.0f * log10f(net_bandwidth_norm) - snr_dB;
+    const float sigma = powf(10.0f, n0_dBFS / 20.0f);
+    const uint32_t k0 = (uint32_t)seed, k1 = (uint32_t)(seed >> 32);
+    uint32_t delay[9]; double power[9];
+    const int n_taps = orc_tdl_pdp(samp_rate, pdp_idx, tau_rms_ns, delay, power);
+    for (int a = 0; a < N_RX; ++a) {
+        /* noise, same stream as orc_channel */
+        for (long pair = 0; 2 * pair < rx_stride; ++pair) {
+            uint32_t c[4] = {(uint32_t)pair, (uint32_t)a, pkt, 0u};
+            philox4x32_10(c, k0, k1);
+            const cf_t y[2] = {cn01(c[0], c[1]), cn01(c[2], c[3])};
+            for (int i = 0; i < 2 && 2 * pair + i < rx_stride; ++i) {
+                rx[(long)a * rx_stride + 2 * pair + i].re = y[i].re * sigma;
+                rx[(long)a * rx_stride + 2 * pair + i].im = y[i].im * sigma;
+            }
+        }
+        for (int t = 0; t < N_TX; ++t)
+            for (int i = 0; i < n_taps; ++i) {
+                int64_t P[40]; float ph0[40];
+                for (int j = 0; j < 40; ++j) {
+                    uint32_t c[4] = {(uint32_t)j | ((uint32_t)i << 8) | ((uint32_t)t << 16), (uint32_t)a, pkt, 2u};
+                    philox4x32_10(c, k0, k1);
+                    const double ang = (double)m1p1(c[0]) * 2.0 * M_PI;
+                    const double fd = (double)fD_Hz * cos(ang);
+                    P[j] = (-0.01f < fd && fd < 0.01f) ? INT64_MAX : (int64_t)(samp_rate / fd);
+                    ph0[j] = m1p1(c[1]) * 2.0f * (float)M_PI;
+                }
+                float scale = 1.0f / sqrtf(40.0f);
+                scale *= sqrt(power[i]);
+                for (long n = t0 + delay[i]; n < rx_stride && n - t0 - (long)delay[i] < n_samples; ++n) {
+                    const cf_t x = tx[(long)t * tx_stride + (n - t0 - delay[i])];
+                    float sr = 0.f, si = 0.f;
+                    for (int j = 0; j < 40; ++j) {
+                        const double s2s = 2.0f * (float)M_PI / (double)P[j];
+                        const double off = (double)((time_64 + n) % llabs(P[j]));
+                        const float ph = (float)(s2s * off) + ph0[j];
+                        sr += cosf(ph); si += sinf(ph);
+                    }
+                    sr *= scale; si *= scale;
+                    rx[(long)a * rx_stride + n].re += sr * x.re - si * x.im;
+                    rx[(long)a * rx_stride + n].im += sr * x.im + si * x.re;
+                }
+            }
     }
 }

@@ -21,3 +21,30 @@ def channel(tx_iq, rx_stride, N_RX, t0=0, mode=0, snr_dB=100.0, net_bandwidth_no
     L.orc_channel(tx_iq.ctypes.data, tx_stride, N_TX, n_samples, rx.ctypes.data, rx_stride, N_RX, t0, mode,
                   snr_dB, net_bandwidth_norm, seed, pkt)
     return rx
+
+
+def tdl_pdp(samp_rate, pdp_idx, tau_rms_ns):
+    """link_t::set_pdp (link.cpp:72-146): merged tap delays in samples and normalised linear powers"""
+    L = lib()
+    d = np.zeros(9, dtype=np.uint32)
+    p = np.zeros(9, dtype=np.float64)
+    L.orc_tdl_pdp.argtypes = [C.c_double, C.c_int, C.c_float, C.c_void_p, C.c_void_p]
+    n = L.orc_tdl_pdp(float(samp_rate), pdp_idx, tau_rms_ns, d.ctypes.data, p.ctypes.data)
+    return d[:n].copy(), p[:n].copy()
+
+
+def channel_doubly(tx_iq, rx_stride, N_RX, samp_rate, t0=0, snr_dB=100.0, net_bandwidth_norm=1.0, seed=1, pkt=0,
+                   n_samples=None, pdp_idx=0, tau_rms_ns=100.0, fD_Hz=50.0, time_64=0):
+    """channel_doubly_t (tapped delay line, 40 sinusoids per tap): tx_iq [N_TX][tx_stride] -> rx [N_RX][rx_stride]"""
+    L = lib()
+    tx_iq = np.ascontiguousarray(tx_iq, dtype=np.complex64)
+    N_TX, tx_stride = tx_iq.shape
+    n_samples = tx_stride if n_samples is None else n_samples
+    rx = np.zeros((N_RX, rx_stride), dtype=np.complex64)
+    L.orc_channel_doubly.argtypes = [C.c_void_p, C.c_long, C.c_int, C.c_int, C.c_void_p, C.c_long, C.c_int, C.c_int,
+                                     C.c_float, C.c_float, C.c_uint64, C.c_uint32, C.c_double, C.c_int, C.c_float,
+                                     C.c_float, C.c_int64]
+    L.orc_channel_doubly.restype = None
+    L.orc_channel_doubly(tx_iq.ctypes.data, tx_stride, N_TX, n_samples, rx.ctypes.data, rx_stride, N_RX, t0, snr_dB,
+                         net_bandwidth_norm, seed, pkt, float(samp_rate), pdp_idx, tau_rms_ns, fD_Hz, time_64)
+    return rx

@@ -56,3 +56,62 @@ def test_channel_statistics(product):
     assert abs(float(np.mean(np.abs(g) ** 2)) - 1.0) < 0.12
     assert abs(np.mean(g)) < 0.12
     phy.close()
+
+
+@pytest.mark.parametrize("name,N_RX,pdp,tau,fD,os", [("C1_loopback", 1, 0, 43.13, 0.0, 1),
+                                                      ("txdiv2_b4_mcs3", 2, 1, 300.0, 200.0, 1),
+                                                      ("C3_b16_txdiv4_mcs7", 2, 2, 500.0, 2000.0, 1),
+                                                      ("C1_loopback", 2, 1, 2000.0, 50.0, 2)])
+def test_channel_doubly_matches_oracle(product, name, N_RX, pdp, tau, fD, os):
+    """doubly selective channel (tapped delay line x 40 sinusoids): same Philox draws on both sides; the device
+    advances phasors by fixed rotations inside a block, the oracle evaluates every sample's phase in closed form:
+    tolerance 1e-4 of the signal peak"""
+    cfg = CONFIGS[name]
+    ps = spec.get_packet_sizes(*cfg)
+    n = 2
+    phy = product.Phy(cfg, max_batch=n, N_RX=N_RX, network_id=NET, oversampling=os)
+    rng = np.random.default_rng(4)
+    tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
+    plcf = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    iq_tx, ns = phy.tx(plcf, tb)
+    t0 = np.array([5, 77])
+    seed, time_64 = 0xABCDEF0123456789, 987654321012
+    snr = 30.0
+    rx = phy.channel(n, snr_dB=snr, t0=t0, mode=2, seed=seed, fetch=True, pdp_idx=pdp, tau_rms_ns=tau, fD_Hz=fD,
+                     time_64=time_64)
+    fs = cfg[0] * cfg[1] * os * 1.728e6
+    for i in range(n):
+        ref = ochan.channel_doubly(iq_tx[i], phy.rx_stride(), N_RX, fs, t0=int(t0[i]), snr_dB=snr,
+                                   net_bandwidth_norm=1.0 / os, seed=seed, pkt=i, n_samples=ps["N_samples_packet"] * os,
+                                   pdp_idx=pdp, tau_rms_ns=tau, fD_Hz=fD, time_64=time_64)
+        tol = 1e-4 * np.abs(ref).max()
+        assert np.abs(rx[i] - ref).max() <= tol, (name, i, float(np.abs(rx[i] - ref).max()), tol)
+    # mixed batch: packet 0 awgn, packet 1 doubly selective
+    mode = np.array([0, 2])
+    rx2 = phy.channel(n, snr_dB=snr, t0=t0, mode=mode, seed=seed, fetch=True, pdp_idx=pdp, tau_rms_ns=tau, fD_Hz=fD,
+                      time_64=time_64)
+    ref0 = ochan.channel(iq_tx[0], phy.rx_stride(), N_RX, t0=int(t0[0]), mode=0, snr_dB=snr, seed=seed, pkt=0,
+                         net_bandwidth_norm=1.0 / os, n_samples=ps["N_samples_packet"] * os)
+    assert np.abs(rx2[0] - ref0).max() <= 2e-5 * (np.abs(ref0).max() + 1)
+    assert np.array_equal(rx2[1], rx[1])
+    phy.close()
+
+
+def test_channel_doubly_decodes(product):
+    """a mildly dispersive, slowly fading link: sync + receiver still decode most packets"""
+    cfg = CONFIGS["C1_loopback"]
+    ps = spec.get_packet_sizes(*cfg)
+    n = 64
+    phy = product.Phy(cfg, max_batch=n, N_RX=2, network_id=NET)
+    rng = np.random.default_rng(6)
+    tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
+    plcf = np.zeros((n, 10), dtype=np.uint8)
+    phy.tx(plcf, tb, fetch=False)
+    t0 = rng.integers(40, 200, n)
+    phy.channel(n, snr_dB=25.0, t0=t0, mode=2, seed=11, pdp_idx=0, tau_rms_ns=100.0, fD_Hz=20.0, time_64=5000)
+    res = phy.sync(n=n)
+    phy.rx_pcc(None, n=n, sync="device")
+    ok, tb_out, _, _ = phy.rx_pdc(n)
+    assert res.detected.sum() >= n * 3 // 4
+    assert ok.sum() >= n // 2 and (tb_out[ok] == tb[ok]).all()
+    phy.close()

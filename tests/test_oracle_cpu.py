@@ -175,3 +175,21 @@ def test_c_abi_exports_every_declared_symbol(product):
     exported = set(l.split()[-1] for l in out.splitlines() if " T " in l)
     missing = declared - exported
     assert not missing, missing
+
+
+def test_tdl_profiles_rms_delay_spread():
+    """link.hpp:84-88 quotes the measured rms delay spreads of the three generic profiles"""
+    import ctypes as C
+    import oracle
+    from oracle import channel as ochan
+    L = C.CDLL(oracle.build())
+    L.orc_tdl_tau_rms_ns.restype = C.c_double
+    for idx, quoted in enumerate((43.13, 356.65, 990.93)):
+        assert abs(L.orc_tdl_tau_rms_ns(idx) - quoted) < 0.011
+    # with the profile's own spread the delays are the generic ones floored to samples, powers sum to one
+    d, p = ochan.tdl_pdp(1.0e9, 1, L.orc_tdl_tau_rms_ns(1))
+    assert len(d) == 9 and all(abs(int(a) - b) <= 1 for a, b in zip(d, [0, 30, 150, 310, 370, 710, 1090, 1730, 2510]))
+    assert abs(p.sum() - 1.0) < 1e-12
+    # equal sample delays are merged (link.cpp:103-121)
+    d2, p2 = ochan.tdl_pdp(1.728e6, 0, 43.13)
+    assert len(d2) < 7 and len(set(d2.tolist())) == len(d2) and abs(p2.sum() - 1.0) < 1e-12
