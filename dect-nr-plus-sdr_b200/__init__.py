@@ -67,7 +67,9 @@ class PccReport(C.Structure):
 
 
 class PdcReport(C.Structure):
-    _fields_ = [("crc_ok", C.c_uint32), ("snr_dB", C.c_float)]
+    _fields_ = [("crc_ok", C.c_uint32), ("snr_dB", C.c_float), ("mimo_N_RX", C.c_uint32),
+                ("mimo_N_TS_other", C.c_uint32), ("tm_3_7_beamforming_idx", C.c_uint32),
+                ("tm_3_7_beamforming_reciprocal_idx", C.c_uint32)]
 
 
 # numpy views of the same C structs (batched calls fill / read them without a Python loop)
@@ -75,7 +77,8 @@ SYNC_DTYPE = np.dtype([("fine_peak_time_local", "u4"), ("cfo_fractional_rad", "f
                        ("rms", "f4", (8,))], align=True)
 PCC_DTYPE = np.dtype([("plcf_ok", "u1", (2,)), ("plcf", "u1", (2, 10)), ("crc_mask", "u4", (2,)), ("snr_dB", "f4"),
                       ("cfo_residual_rad", "f4"), ("sto_fractional", "f4"), ("rms", "f4", (8,))], align=True)
-PDC_DTYPE = np.dtype([("crc_ok", "u4"), ("snr_dB", "f4")], align=True)
+PDC_DTYPE = np.dtype([("crc_ok", "u4"), ("snr_dB", "f4"), ("mimo_N_RX", "u4"), ("mimo_N_TS_other", "u4"),
+                      ("tm_3_7_beamforming_idx", "u4"), ("tm_3_7_beamforming_reciprocal_idx", "u4")], align=True)
 assert SYNC_DTYPE.itemsize == C.sizeof(SyncReport) and PCC_DTYPE.itemsize == C.sizeof(PccReport)
 assert PDC_DTYPE.itemsize == C.sizeof(PdcReport)
 
@@ -288,6 +291,7 @@ class Phy:
         out = np.zeros(n, dtype=PDC_DTYPE)
         _check(lib().dnrp_rx_pdc_batch(self._ctx, n, _ptr(slot, np.uint32), _ptr(rvv, np.uint8), _ptr(rst, np.uint8),
                                        _ptr(tb, np.uint8), out.ctypes.data_as(C.c_void_p), _ptr(nit, np.uint8)))
+        self.last_pdc_report = out.view(np.recarray)   # incl. the MIMO report fields
         return out["crc_ok"].astype(bool), tb, out["snr_dB"].copy(), nit
 
     def tap(self, which, n):

@@ -54,6 +54,13 @@ int run_rx_pcc(dnrp_ctx* c, uint32_t n) {
 int run_rx_pdc(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, bool have_reset) {
     const rx_params_t p = make_rx_params(c);
     DNRP_LAUNCH(c, DNRP_KERNEL_RX_DEMAP_PDC, launch_rx_demap(p, n, false, c->stream));
+    mimo_params_t mp{};
+    mp.d = c->dims; mp.hzf = c->d_hzf.p; mp.out = c->d_mimo.p;
+    for (int s = 0; s < 2; ++s) {
+        mp.W[s] = c->d_mimo_W[s].p; mp.W_scale[s] = c->d_mimo_scale[s].p;
+        mp.n[s] = c->mimo_n[s]; mp.first[s] = c->mimo_first[s];
+    }
+    DNRP_LAUNCH(c, -1, launch_rx_mimo(mp, n, c->stream));
     return run_fec_decode_tb(c, n, have_slot, have_rv, have_reset);
 }
 
@@ -214,6 +221,8 @@ int dnrp_rx_pdc_batch(dnrp_ctx_t* c, uint32_t n, const uint32_t* harq_slot, cons
     int rc = run_rx_pdc(c, n, harq_slot != nullptr, rv != nullptr, harq_reset != nullptr);
     if (rc) return rc;
     std::vector<uint8_t> ok(n);
+    std::vector<mimo_report_dev_t> mimo(n);
+    DNRP_CUDA(cudaMemcpyAsync(mimo.data(), c->d_mimo.p, n * sizeof(mimo_report_dev_t), cudaMemcpyDeviceToHost, c->stream));
     DNRP_CUDA(cudaMemcpy2DAsync(tb_out, c->ps.N_TB_byte, c->d_tb_out.p, f.tb_stride, c->ps.N_TB_byte, n,
                                 cudaMemcpyDeviceToHost, c->stream));
     DNRP_CUDA(cudaMemcpyAsync(ok.data(), c->d_tb_ok.p, n, cudaMemcpyDeviceToHost, c->stream));
@@ -222,6 +231,9 @@ int dnrp_rx_pdc_batch(dnrp_ctx_t* c, uint32_t n, const uint32_t* harq_slot, cons
     for (uint32_t i = 0; i < n; ++i) {
         out[i].crc_ok = ok[i];
         out[i].snr_dB = c->h_rx_state[i].snr_db_pdc;  // read back by the PCC call (whole packet is known)
+        out[i].mimo_N_RX = mimo[i].N_RX; out[i].mimo_N_TS_other = mimo[i].N_TS_other;
+        out[i].tm_3_7_beamforming_idx = mimo[i].tm_3_7_beamforming_idx;
+        out[i].tm_3_7_beamforming_reciprocal_idx = mimo[i].tm_3_7_beamforming_reciprocal_idx;
     }
     return DNRP_OK;
 }

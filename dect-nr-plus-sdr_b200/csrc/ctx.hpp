@@ -127,6 +127,11 @@ struct dnrp_ctx {
     dnrp::dbuf<uint8_t> d_cls;
     std::vector<dnrp::rx_state_t> h_rx_state;
     dnrp::dbuf<dnrp::chan_meta_dev_t> d_chan_meta;
+    // MIMO report: single-stream codebooks W(1, N_eff_TX) and W(1, N_RX)
+    dnrp::dbuf<int8_t> d_mimo_W[2];
+    dnrp::dbuf<float> d_mimo_scale[2];
+    uint32_t mimo_n[2] = {0, 0}, mimo_first[2] = {0, 0};
+    dnrp::dbuf<dnrp::mimo_report_dev_t> d_mimo;
     dnrp::dbuf<dnrp::tdl_sin_t> d_chan_sin;   // allocated by the first doubly selective channel call
     bool chan_any_tdl = false;
 

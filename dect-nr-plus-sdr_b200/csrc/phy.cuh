@@ -72,6 +72,22 @@ struct rx_params_t {
     size_t llr_stride;
 };
 
+// mimo_report_t (lib/include/dectnrp/phy/rx/rx_synced/mimo/mimo_report.hpp:27-59)
+struct mimo_report_dev_t {
+    uint32_t N_RX, N_TS_other, tm_3_7_beamforming_idx, tm_3_7_beamforming_reciprocal_idx;
+};
+// single-stream codebooks W(1, N) for the codebook search of estimator_mimo_t: side 0 = N = N_eff_TX (matrix for the
+// other side), side 1 = N = N_RX (reciprocal); n = 0 where no beamforming exists (N = 1 or 8)
+struct mimo_params_t {
+    phy_dims_t d;
+    const float2* hzf;               // [packet][N_RX][N_eff_TX][n_drs][NP]
+    const int8_t* W[2];              // [n][N] codes 0, +-1, +-2
+    const float* W_scale[2];         // [n]
+    uint32_t n[2], first[2];         // number of matrices, first matrix without zero entries
+    mimo_report_dev_t* out;          // [packet]
+};
+cudaError_t launch_rx_mimo(const mimo_params_t& p, uint32_t n_packets, cudaStream_t st);
+
 cudaError_t launch_rx_stf(const rx_params_t& p, uint32_t n_packets, cudaStream_t st);
 cudaError_t launch_rx_fft(const rx_params_t& p, uint32_t n_packets, cudaStream_t st);
 cudaError_t launch_rx_snr_class(const rx_params_t& p, uint32_t n_packets, cudaStream_t st);

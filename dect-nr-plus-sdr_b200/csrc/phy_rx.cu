@@ -417,6 +417,65 @@ cudaError_t launch_rx_demap(const rx_params_t& p, uint32_t n_packets, bool pcc, 
     return cudaGetLastError();
 }
 
+// ---- MIMO report: codebook search for single-stream beamforming (modes 3 and 7) on the last zero-forced DRS cells
+// of the packet (estimator_mimo.cpp:80-272, rx_synced.cpp:416-431).  Four wideband cells (rx_synced_param.hpp:271),
+// metric "highest minimum RX power" (:286), matrices without zero entries only (:277).  One thread per packet.
+__device__ uint32_t mimo_search(const float2 (*h)[8][4], uint32_t n_tx, uint32_t n_rx, bool transpose, const int8_t* W,
+                                const float* scale, uint32_t n, uint32_t first) {
+    float best = -1.0e6f;
+    uint32_t ret = 0;
+    for (uint32_t wm = first; wm < n; ++wm) {
+        float inner = 1.0e6f;
+        for (uint32_t rx = 0; rx < n_rx; ++rx) {
+            float2 sum = make_float2(0.f, 0.f);
+            for (uint32_t tx = 0; tx < n_tx; ++tx) {
+                const int8_t w = W[wm * n_tx + tx];
+                float2 part = make_float2(0.f, 0.f);
+                for (uint32_t c = 0; c < 4; ++c) {
+                    const float2 v = transpose ? h[tx][rx][c] : h[rx][tx][c];
+                    float2 q = make_float2(0.f, 0.f);
+                    if (w == 1) q = v;
+                    else if (w == -1) q = make_float2(-v.x, -v.y);
+                    else if (w == 2) q = make_float2(-v.y, v.x);
+                    else if (w == -2) q = make_float2(v.y, -v.x);
+                    part.x += q.x; part.y += q.y;
+                }
+                sum.x += part.x; sum.y += part.y;
+            }
+            const float mag = hypotf(sum.x, sum.y);
+            if (mag < inner) inner = mag;
+        }
+        inner *= scale[wm];
+        if (best < inner) { best = inner; ret = wm; }
+    }
+    return ret;
+}
+
+__global__ void k_rx_mimo(const mimo_params_t p, uint32_t n) {
+    const uint32_t pkt = blockIdx.x * blockDim.x + threadIdx.x;
+    if (pkt >= n) return;
+    const phy_dims_t& d = p.d;
+    const uint32_t step = d.NP / 4, off = step / 2;   // estimator_mimo.cpp:117-122
+    float2 h[8][8][4];
+    for (uint32_t rx = 0; rx < d.N_RX; ++rx)
+        for (uint32_t ts = 0; ts < d.N_eff_TX; ++ts) {
+            const float2* src = p.hzf + ((((size_t)pkt * d.N_RX + rx) * d.N_eff_TX + ts) * d.n_drs + (d.n_drs - 1)) * d.NP;
+            for (uint32_t c = 0; c < 4; ++c) h[rx][ts][c] = src[off + c * step];
+        }
+    mimo_report_dev_t r;
+    r.N_RX = d.N_RX; r.N_TS_other = d.N_eff_TX;
+    r.tm_3_7_beamforming_idx = (d.N_eff_TX == 1 || p.n[0] == 0) ? 0u
+        : mimo_search(h, d.N_eff_TX, d.N_RX, false, p.W[0], p.W_scale[0], p.n[0], p.first[0]);
+    r.tm_3_7_beamforming_reciprocal_idx = (d.N_RX == 1 || p.n[1] == 0) ? 0u
+        : mimo_search(h, d.N_RX, d.N_eff_TX, true, p.W[1], p.W_scale[1], p.n[1], p.first[1]);
+    p.out[pkt] = r;
+}
+
+cudaError_t launch_rx_mimo(const mimo_params_t& p, uint32_t n_packets, cudaStream_t st) {
+    k_rx_mimo<<<(n_packets + 63) / 64, 64, 0, st>>>(p, n_packets);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_rx_snr_class(const rx_params_t& p, uint32_t n_packets, cudaStream_t st) {
     k_rx_snr_class<<<(n_packets + 127) / 128, 128, 0, st>>>(p, n_packets);
     return cudaGetLastError();

@@ -223,6 +223,27 @@ int build_phy_plan(dnrp_ctx* c) {
     UP(c->d_rx_state.alloc(B));
     UP(c->d_cls.alloc(B * c->cls_stride));
     UP(c->d_chan_meta.alloc(B));
+    // MIMO report: W(1, N) for N = N_eff_TX and N = N_RX; the search starts at the first matrix without zero entries
+    // (beamforming_and_antenna_port_mapping.hpp:110-119: index 2 for N = 2, 12 for N = 4)
+    for (uint32_t side = 0; side < 2; ++side) {
+        const uint32_t N = side == 0 ? d.N_eff_TX : d.N_RX;
+        c->mimo_n[side] = 0;
+        if (N != 2 && N != 4) continue;
+        uint32_t cnt = 0;
+        spec::codebook(1, N, 0, &cnt);
+        std::vector<int8_t> Wm;
+        std::vector<float> sc;
+        for (uint32_t i = 0; i < cnt; ++i) {
+            const int8_t* w = spec::codebook(1, N, i, nullptr);
+            Wm.insert(Wm.end(), w, w + N);
+            sc.push_back(spec::codebook_scale(w, N));
+        }
+        c->mimo_n[side] = cnt;
+        c->mimo_first[side] = N == 2 ? 2 : 12;
+        UP(c->d_mimo_W[side].upload(Wm));
+        UP(c->d_mimo_scale[side].upload(sc));
+    }
+    UP(c->d_mimo.alloc(B));
     c->h_rx_state.resize(B);
 #undef UP
     if (!ok) {

@@ -155,6 +155,11 @@ typedef struct {
 typedef struct {
     uint32_t crc_ok;
     float snr_dB;
+    /* mimo_report_t (rx_synced/mimo/mimo_report.hpp:27-59, estimator_mimo.cpp:80-272): codebook indices recommended
+     * for single-stream beamforming (modes 3 / 7), searched on the last DRS cells of the packet; 0 where no
+     * beamforming codebook exists.  The reference fills it for CRC-passing packets only; here always. */
+    uint32_t mimo_N_RX, mimo_N_TS_other;
+    uint32_t tm_3_7_beamforming_idx, tm_3_7_beamforming_reciprocal_idx;
 } dnrp_pdc_report_t;
 
 /* samples per antenna reserved for one packet's IQ window in iq_in */

@@ -157,3 +157,42 @@ def fft(x):
     L.orc_fft.argtypes = [C.c_void_p, C.c_void_p, C.c_int]
     L.orc_fft(x.ctypes.data, out.ctypes.data, x.size)
     return out
+
+
+def mimo_report(hzf_last, literal=True):
+    """estimator_mimo_t::process_drs (estimator_mimo.cpp:80-272) on the zero-forced DRS cells of the packet's last DRS
+    occurrence, hzf_last [N_RX][N_TS][NP] complex64.  Returns (tm_3_7_beamforming_idx, reciprocal_idx).
+    Constants as shipped (rx_synced_param.hpp:271-286): 4 wideband cells, only matrices without zero entries
+    (first index 2 for N = 2, 12 for N = 4), metric = highest minimum RX magnitude times the matrix scale."""
+    from . import tx as otx
+    h = np.asarray(hzf_last, dtype=np.complex64)
+    N_RX, N_TS, NP = h.shape
+    step = NP // 4
+    cells = h[:, :, step // 2 + step * np.arange(4)]              # [rx][ts][4]
+
+    def search(stage, n_tx, n_rx):                                 # stage [rx_virt][tx_virt][4]
+        if n_tx not in (2, 4):
+            return 0
+        first = 2 if n_tx == 2 else 12
+        n = len(otx.W_TABLES[(1, n_tx)])
+        best, ret = np.float32(-1.0e6), -1
+        for wm in range(first, n):
+            W, scale = otx.codebook(1, n_tx, wm)
+            w = W.reshape(n_tx)
+            inner = np.float32(1.0e6)
+            for rx in range(n_rx):
+                s = np.complex64(0)
+                for tx in range(n_tx):
+                    part = np.complex64(0)
+                    for c in range(4):
+                        part = np.complex64(part + stage[rx, tx, c] * w[tx])
+                    s = np.complex64(s + part)
+                inner = min(inner, np.float32(abs(s)))
+            inner = np.float32(inner * scale)
+            if best < inner:
+                best, ret = inner, wm
+        return ret
+
+    idx = 0 if N_TS == 1 else search(cells, N_TS, N_RX)
+    rec = 0 if N_RX == 1 else search(np.transpose(cells, (1, 0, 2)), N_RX, N_TS)
+    return idx, rec

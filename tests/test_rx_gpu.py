@@ -135,3 +135,35 @@ def test_rx_device_loopback(product):
     assert all(p.plcf_ok[0] and bytes(p.plcf[0])[:5] == bytes(plcf[i][:5]) for i, p in enumerate(pcc))
     assert (snr > 40).all()
     phy.close()
+
+
+@pytest.mark.parametrize("cfg,N_RX", [(CONFIGS["txdiv2_b4_mcs3"], 2), (CONFIGS["C3_b16_txdiv4_mcs7"], 4),
+                                      (CONFIGS["C3_b16_txdiv4_mcs7"], 2), (CONFIGS["C1_loopback"], 4),
+                                      ((8, 2, 1, 2, 10, 1, 2048), 2)])
+def test_mimo_report(product, cfg, N_RX):
+    """mimo_report_t of the PDC report against the oracle's codebook search (estimator_mimo.cpp) run on the same
+    zero-forced DRS cells (the device's DRS tap, itself covered by test_rx_matches_oracle)"""
+    ps = spec.get_packet_sizes(*cfg)
+    n = 16
+    phy = product.Phy(cfg, max_batch=n, N_RX=N_RX, network_id=NET)
+    rng = np.random.default_rng(21)
+    tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
+    plcf = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    phy.tx(plcf, tb, fetch=False)
+    phy.channel(n, snr_dB=25.0, t0=7, mode=1, seed=31)
+    phy.rx_pcc(None, t0=7, n=n)
+    phy.rx_pdc(n)
+    rep = phy.last_pdc_report
+    N_TS = ps["N_eff_TX"]
+    hzf = phy.tap(product.TAP_DRS_ZF, n).reshape(n, N_RX, N_TS, -1, ps["N_b_OCC"] // 4)
+    assert (rep.mimo_N_RX == N_RX).all() and (rep.mimo_N_TS_other == N_TS).all()
+    seen = set()
+    for i in range(n):
+        idx, rec = rx.mimo_report(hzf[i, :, :, -1, :])
+        assert (int(rep.tm_3_7_beamforming_idx[i]), int(rep.tm_3_7_beamforming_reciprocal_idx[i])) == (idx, rec), i
+        seen.add((idx, rec))
+    if N_TS in (2, 4) and N_RX in (2, 4):
+        assert len(seen) > 1          # flat fading draws: the recommendation depends on the channel
+    if N_TS == 1:
+        assert (rep.tm_3_7_beamforming_idx == 0).all()
+    phy.close()
