@@ -1,0 +1,505 @@
+// dnrp_host.hpp -- C++ host side above the C ABI (dnrp_c_api.h): the reference's PHY-to-MAC surface for the PCC/PDC
+// path with the same type names, members and call order, so that firmware written against the reference's
+// tpoint_t::work_pcc / work_pdc callbacks runs on batches processed by libdnrp_cuda.so.  Header only, C++17.
+//
+// Mirrored reference interfaces (paths under /root/reference/lib/include/dectnrp):
+//   phy/tx/tx_meta.hpp:32-58, phy/tx/tx_descriptor.hpp:43-78, radio/buffer_tx_meta.hpp:32-50
+//   phy/harq/{process,process_tx,process_rx,process_pool,finalize}.hpp
+//   phy/rx/sync/sync_report.hpp:31-98, phy/rx/rx_synced/{pcc_report,pdc_report}.hpp, mimo/mimo_report.hpp
+//   phy/interfaces/{phy_maclow,maclow_phy,maclow_phy_handle,phy_machigh,machigh_phy}.hpp
+//   upper/tpoint.hpp:128-170 (work_pcc, work_pdc, work_pdc_error)
+//   phy/pool/worker_tx_rx.cpp:117-240 (order of calls: work_pcc FIFO by job order, PDC only if continue_with_pdc,
+//   hp_rx->finalize(crc_status) after the callback, TX descriptors generated afterwards)
+// Not mirrored (out of scope, MAC layer): sp4::plcf_decoder_t / mac_pdu_decoder_t field codecs -- the reports carry
+// the raw PLCF / transport block bytes the reference's decoders would be fed with.
+// There is no CPU fallback: construction throws if libdnrp_cuda.so cannot create its context.
+#pragma once
+#include <array>
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <memory>
+#include <optional>
+#include <stdexcept>
+#include <string>
+#include <vector>
+
+extern "C" {
+#include "dnrp_c_api.h"
+}
+
+namespace dectnrp_b200 {
+
+using cf_t = dnrp_cf32_t;
+
+namespace sp3 {
+using packet_sizes_def_t = dnrp_psdef_t;
+using packet_sizes_t = dnrp_packet_sizes_t;
+}  // namespace sp3
+
+namespace common {
+/// common::ant_t = std::array<float, 8> + number of antennas
+struct ant_t {
+    std::array<float, 8> ary{};
+    uint32_t nof_antennas{0};
+    float at(uint32_t i) const { return ary.at(i); }
+    float& at(uint32_t i) { return ary.at(i); }
+    uint32_t get_nof_antennas() const { return nof_antennas; }
+    bool has_any_larger(float v) const {
+        for (uint32_t i = 0; i < nof_antennas; ++i) if (ary[i] > v) return true;
+        return false;
+    }
+    uint32_t get_index_of_max() const {
+        uint32_t m = 0;
+        for (uint32_t i = 1; i < nof_antennas; ++i) if (ary[i] > ary[m]) m = i;
+        return m;
+    }
+};
+}  // namespace common
+
+namespace radio {
+struct buffer_tx_meta_t {
+    int64_t tx_order_id{0};
+    int64_t tx_order_id_expect_next{0};
+    int64_t tx_time_64{0};
+    uint32_t busy_wait_us{0};
+};
+}  // namespace radio
+
+namespace phy {
+
+namespace harq {
+
+enum class finalize_tx_t { reset_and_terminate, increase_rv_and_keep_running, keep_rv_and_keep_running };
+enum class finalize_rx_t { reset_and_terminate, keep_running, keep_running_or_reset_and_terminate_if_crc_correct };
+
+class process_pool_t;
+
+class process_t {
+    public:
+        explicit process_t(uint32_t id_) : id(id_) {}
+        virtual ~process_t() = default;
+        uint32_t get_id() const { return id; }
+        uint32_t get_PLCF_type() const { return PLCF_type; }
+        uint32_t get_network_id() const { return network_id; }
+        const sp3::packet_sizes_def_t& get_psdef() const { return psdef; }
+        uint32_t get_rv() const { return rv; }
+        bool is_running() const { return running; }
+
+    protected:
+        friend class process_pool_t;
+        const uint32_t id;
+        uint32_t PLCF_type{0}, network_id{0}, rv{0};
+        sp3::packet_sizes_def_t psdef{};
+        bool running{false};
+        void reset() { PLCF_type = 0; network_id = 0; rv = 0; running = false; }
+};
+
+class process_tx_t final : public process_t {
+    public:
+        process_tx_t(uint32_t id_, uint32_t N_TB_byte_max) : process_t(id_), a_tb(N_TB_byte_max, 0) {}
+        uint8_t* get_a_plcf() { return a_plcf.data(); }
+        uint8_t* get_a_tb() { return a_tb.data(); }
+        /// process_tx.cpp:43-62
+        void finalize() {
+            switch (finalize_tx) {
+                case finalize_tx_t::reset_and_terminate: reset_and_terminate_func(); break;
+                case finalize_tx_t::increase_rv_and_keep_running: set_next_rv(); break;
+                case finalize_tx_t::keep_rv_and_keep_running: break;
+            }
+        }
+
+    private:
+        friend class process_pool_t;
+        std::array<uint8_t, 10> a_plcf{};
+        std::vector<uint8_t> a_tb;
+        uint32_t rv_unwrapped{0};
+        finalize_tx_t finalize_tx{finalize_tx_t::reset_and_terminate};
+        /// process_tx.cpp:64-88: 0 -> 2 -> 3 -> 1 -> 0
+        void set_next_rv() {
+            static const uint32_t next[4] = {2, 0, 3, 1};
+            rv = next[rv & 3];
+            ++rv_unwrapped;
+        }
+        void reset_and_terminate_func() {
+            rv_unwrapped = 0;
+            finalize_tx = finalize_tx_t::reset_and_terminate;
+            reset();
+        }
+};
+
+class process_rx_t final : public process_t {
+    public:
+        process_rx_t(uint32_t id_, uint32_t N_TB_byte_max) : process_t(id_), a_tb(N_TB_byte_max, 0) {}
+        /// decoded transport block (reference: get_hb_tb()->get_a())
+        uint8_t* get_a_tb() { return a_tb.data(); }
+        const uint8_t* get_a_tb() const { return a_tb.data(); }
+        /// true until the first PDC of this process was decoded: the soft buffer slot has to be cleared
+        bool is_first_transmission() const { return nof_rx == 0; }
+        /// process_rx.cpp:45-66
+        void finalize(bool crc_status) {
+            ++nof_rx;
+            switch (finalize_rx) {
+                case finalize_rx_t::reset_and_terminate: reset_and_terminate_func(); break;
+                case finalize_rx_t::keep_running: break;
+                case finalize_rx_t::keep_running_or_reset_and_terminate_if_crc_correct:
+                    if (crc_status) reset_and_terminate_func();
+                    break;
+            }
+        }
+
+    private:
+        friend class process_pool_t;
+        std::vector<uint8_t> a_tb;
+        uint32_t nof_rx{0};
+        finalize_rx_t finalize_rx{finalize_rx_t::reset_and_terminate};
+        void reset_and_terminate_func() {
+            nof_rx = 0;
+            finalize_rx = finalize_rx_t::reset_and_terminate;
+            reset();
+        }
+};
+
+/// process_pool.hpp:36-70.  A receive process id doubles as the soft buffer slot on the device.
+class process_pool_t {
+    public:
+        process_pool_t(const sp3::packet_sizes_t& maximum_packet_sizes, uint32_t nof_process_tx, uint32_t nof_process_rx) {
+            for (uint32_t i = 0; i < nof_process_tx; ++i)
+                hp_tx_vec.push_back(std::make_unique<process_tx_t>(i, maximum_packet_sizes.N_TB_byte));
+            for (uint32_t i = 0; i < nof_process_rx; ++i)
+                hp_rx_vec.push_back(std::make_unique<process_rx_t>(i, maximum_packet_sizes.N_TB_byte));
+        }
+        /// nullptr if every process is running (the reference returns nullptr as well, process_pool.cpp:60-70)
+        process_tx_t* get_process_tx(uint32_t PLCF_type, uint32_t network_id, const sp3::packet_sizes_def_t psdef,
+                                     finalize_tx_t ftx) const {
+            for (auto& p : hp_tx_vec)
+                if (!p->running) {
+                    p->running = true; p->PLCF_type = PLCF_type; p->network_id = network_id; p->psdef = psdef;
+                    p->rv = 0; p->finalize_tx = ftx;
+                    return p.get();
+                }
+            return nullptr;
+        }
+        process_rx_t* get_process_rx(uint32_t PLCF_type, uint32_t network_id, const sp3::packet_sizes_def_t psdef,
+                                     uint32_t rv, finalize_rx_t frx) const {
+            for (auto& p : hp_rx_vec)
+                if (!p->running) {
+                    p->running = true; p->PLCF_type = PLCF_type; p->network_id = network_id; p->psdef = psdef;
+                    p->rv = rv; p->finalize_rx = frx; p->nof_rx = 0;
+                    return p.get();
+                }
+            return nullptr;
+        }
+        process_tx_t* get_process_tx_running(uint32_t id, finalize_tx_t ftx) const {
+            if (id >= hp_tx_vec.size() || !hp_tx_vec[id]->running) return nullptr;
+            hp_tx_vec[id]->finalize_tx = ftx;
+            return hp_tx_vec[id].get();
+        }
+        process_rx_t* get_process_rx_running(uint32_t id, uint32_t rv, finalize_rx_t frx) const {
+            if (id >= hp_rx_vec.size() || !hp_rx_vec[id]->running) return nullptr;
+            hp_rx_vec[id]->rv = rv; hp_rx_vec[id]->finalize_rx = frx;
+            return hp_rx_vec[id].get();
+        }
+
+    private:
+        std::vector<std::unique_ptr<process_tx_t>> hp_tx_vec;
+        std::vector<std::unique_ptr<process_rx_t>> hp_rx_vec;
+};
+
+}  // namespace harq
+
+/// tx_meta.hpp:32-58
+struct tx_meta_t {
+    bool optimal_scaling_DAC{false};
+    float DAC_scale{1.0f};
+    float iq_phase_rad{0.0f};
+    float iq_phase_increment_s2s_post_resampling_rad{0.0f};
+    uint32_t GI_percentage{5};
+};
+
+/// tx_descriptor.hpp:43-78
+class tx_descriptor_t {
+    public:
+        tx_descriptor_t(harq::process_tx_t& hp_tx_, uint32_t codebook_index_, tx_meta_t tx_meta_,
+                        radio::buffer_tx_meta_t buffer_tx_meta_, int32_t hw_id_ = -1)
+            : hp_tx(hp_tx_), codebook_index(codebook_index_), tx_meta(tx_meta_), buffer_tx_meta(buffer_tx_meta_),
+              hw_id(hw_id_) {}
+        harq::process_tx_t& hp_tx;
+        uint32_t codebook_index;
+        tx_meta_t tx_meta;
+        radio::buffer_tx_meta_t buffer_tx_meta;
+        int32_t hw_id;
+};
+
+/// sync_report.hpp:31-98
+struct sync_report_t {
+    explicit sync_report_t(uint32_t nof_antennas = 0) {
+        coarse_peak_array.nof_antennas = nof_antennas;
+        rms_array.nof_antennas = nof_antennas;
+    }
+    uint32_t detection_ant_idx{0};
+    float detection_rms{0.f}, detection_metric{0.f};
+    uint32_t detection_time_local{0};
+    uint32_t u{0}, b{0};
+    common::ant_t coarse_peak_array{};
+    uint32_t coarse_peak_time_local{0};
+    int64_t coarse_peak_time_64{0};
+    common::ant_t rms_array{};
+    float cfo_fractional_rad{0.f}, cfo_integer_rad{0.f};
+    uint32_t N_eff_TX{0};
+    uint32_t fine_peak_time_local{0};
+    int64_t fine_peak_time_64{0};
+    float sto_fractional{0.f};
+    int64_t fine_peak_time_corrected_by_sto_fractional_64{0};
+};
+
+/// mimo/mimo_report.hpp:27-59
+struct mimo_report_t {
+    uint32_t N_RX{0}, N_TS_other{0};
+    uint32_t tm_3_7_beamforming_idx{0}, tm_3_7_beamforming_reciprocal_idx{0};
+    uint32_t RI{0}, CQI{0}, PMI{0};
+};
+
+/// pcc_report.hpp:29-43 -- plcf_decoder_t replaced by the raw PLCF bytes per type (index 0 = type 1, 1 = type 2)
+struct pcc_report_t {
+    bool plcf_ok[2]{false, false};
+    std::array<uint8_t, 10> plcf[2]{};
+    uint32_t crc_mask[2]{0, 0};      // 0 none, 0x5555 closed loop, 0xAAAA beamforming, 0xFFFF both
+    float snr_dB{0.f};
+    bool has_any_plcf() const { return plcf_ok[0] || plcf_ok[1]; }
+    /// nullptr if that type did not pass its CRC (plcf_decoder_t::get_plcf_base semantics)
+    const uint8_t* get_plcf_bytes(uint32_t PLCF_type) const {
+        return (PLCF_type == 1 || PLCF_type == 2) && plcf_ok[PLCF_type - 1] ? plcf[PLCF_type - 1].data() : nullptr;
+    }
+};
+
+/// pdc_report.hpp:28-62 -- mac_pdu_decoder_t replaced by the decoded transport block bytes
+struct pdc_report_t {
+    bool crc_status{false};
+    const uint8_t* a_tb{nullptr};
+    uint32_t N_TB_byte{0};
+    float snr_dB{0.f};
+    mimo_report_t mimo_report{};
+};
+
+/// maclow_phy_handle.hpp:28-48
+enum class handle_pcc2pdc_t : uint32_t { th10 = 0, th20, th21, CARDINALITY };
+struct maclow_phy_handle_t {
+    maclow_phy_handle_t() = default;
+    maclow_phy_handle_t(handle_pcc2pdc_t h, uint32_t lrdid_) : handle_pcc2pdc(h), lrdid(lrdid_) {}
+    handle_pcc2pdc_t handle_pcc2pdc{handle_pcc2pdc_t::CARDINALITY};
+    uint32_t lrdid{0};
+};
+
+/// phy_maclow.hpp:28-36
+struct phy_maclow_t {
+    const sync_report_t& sync_report;
+    const pcc_report_t& pcc_report;
+};
+
+/// maclow_phy.hpp:29-85
+struct maclow_phy_t {
+    maclow_phy_t() = default;
+    explicit maclow_phy_t(harq::process_rx_t* hp_rx_) : continue_with_pdc(true), hp_rx(hp_rx_) {}
+    maclow_phy_t(harq::process_rx_t* hp_rx_, maclow_phy_handle_t h) : continue_with_pdc(true), hp_rx(hp_rx_), maclow_phy_handle(h) {}
+    bool continue_with_pdc{false};
+    harq::process_rx_t* hp_rx{nullptr};
+    maclow_phy_handle_t maclow_phy_handle{};
+    handle_pcc2pdc_t get_handle_pcc2pdc() const { return maclow_phy_handle.handle_pcc2pdc; }
+    uint32_t get_handle_lrdid() const { return maclow_phy_handle.lrdid; }
+};
+
+/// phy_machigh.hpp:29-41
+struct phy_machigh_t {
+    const phy_maclow_t& phy_maclow;
+    const maclow_phy_t& maclow_phy;
+    const pdc_report_t& pdc_report;
+};
+
+/// machigh_phy.hpp:33-61 (irregular reports and channel scans are not part of this path)
+struct machigh_phy_t {
+    typedef std::vector<tx_descriptor_t> tx_descriptor_vec_t;
+    tx_descriptor_vec_t tx_descriptor_vec{};
+};
+
+}  // namespace phy
+
+namespace upper {
+/// upper/tpoint.hpp:128-170: the three callbacks of the PCC/PDC path
+class tpoint_t {
+    public:
+        virtual ~tpoint_t() = default;
+        [[nodiscard]] virtual phy::maclow_phy_t work_pcc(const phy::phy_maclow_t& phy_maclow) = 0;
+        [[nodiscard]] virtual phy::machigh_phy_t work_pdc(const phy::phy_machigh_t& phy_machigh) = 0;
+        [[nodiscard]] virtual phy::machigh_phy_t work_pdc_error(const phy::phy_machigh_t& phy_machigh) = 0;
+};
+}  // namespace upper
+
+namespace phy {
+
+/// What worker_pool_t + worker_tx_rx_t + tx_t + rx_synced_t + sync_chunk_t are to the reference for this path, for a
+/// BATCH of packets of one geometry on one GPU.
+class batch_phy_t {
+    public:
+        struct stats_t {
+            uint64_t windows{0}, detections{0}, pcc_ok{0}, pdc_requested{0}, pdc_crc_ok{0}, tx_packets{0};
+        };
+
+        /// cfg.max_batch = windows per process_windows call; nof_process_rx_ = receive HARQ processes of the firmware's
+        /// process_pool_t (their ids address the first soft buffer slots of the context)
+        batch_phy_t(const dnrp_config_t& cfg, int device, uint32_t nof_process_rx_) : config(cfg), max_windows(cfg.max_batch),
+                                                                                     nof_process_rx(nof_process_rx_) {
+            config.max_batch = max_windows + nof_process_rx;
+            if (dnrp_ctx_create(&config, device, &ctx) != DNRP_OK)
+                throw std::runtime_error(std::string("dnrp_ctx_create: ") + dnrp_last_error_string());
+            dnrp_ctx_get_packet_sizes(ctx, &packet_sizes);
+            tx_stride = dnrp_tx_stride(ctx);
+            rx_stride = dnrp_rx_stride(ctx);
+        }
+        ~batch_phy_t() { dnrp_ctx_destroy(ctx); }
+        batch_phy_t(const batch_phy_t&) = delete;
+        batch_phy_t& operator=(const batch_phy_t&) = delete;
+
+        const sp3::packet_sizes_t& get_packet_sizes() const { return packet_sizes; }
+        uint32_t get_tx_stride() const { return tx_stride; }
+        uint32_t get_rx_stride() const { return rx_stride; }
+        uint32_t get_N_RX() const { return config.N_RX ? config.N_RX : 1; }
+        const stats_t& get_stats() const { return stats; }
+        dnrp_ctx_t* get_ctx() { return ctx; }
+
+        /// tx_t::generate_tx_packet for every descriptor (worker_tx_rx.cpp:300-335): IQ [n][N_TX][tx_stride] into iq_out
+        /// (nullptr: stays on the device for channel()), then hp_tx.finalize().  All descriptors must share the context's
+        /// geometry (the reference asserts psdef against maximum_packet_sizes, tx.cpp:430-482).
+        void generate_tx_packets(std::vector<tx_descriptor_t>& descs, cf_t* iq_out, std::vector<uint32_t>* n_samples = nullptr) {
+            const uint32_t n = (uint32_t)descs.size();
+            if (n == 0) return;
+            std::vector<dnrp_tx_desc_t> d(n);
+            std::vector<uint8_t> plcf(10 * (size_t)n), tb((size_t)n * packet_sizes.N_TB_byte);
+            for (uint32_t i = 0; i < n; ++i) {
+                const tx_meta_t& m = descs[i].tx_meta;
+                if (std::memcmp(&descs[i].hp_tx.get_psdef(), &config.psdef, sizeof(dnrp_psdef_t)) != 0)
+                    throw std::invalid_argument("tx_descriptor_t: packet geometry differs from the context's");
+                d[i] = {descs[i].codebook_index, m.optimal_scaling_DAC ? 1u : 0u, m.DAC_scale, m.iq_phase_rad,
+                        m.iq_phase_increment_s2s_post_resampling_rad, m.GI_percentage, descs[i].hp_tx.get_rv()};
+                std::memcpy(&plcf[10 * (size_t)i], descs[i].hp_tx.get_a_plcf(), 10);
+                std::memcpy(&tb[(size_t)i * packet_sizes.N_TB_byte], descs[i].hp_tx.get_a_tb(), packet_sizes.N_TB_byte);
+            }
+            std::vector<uint32_t> ns(n);
+            check(dnrp_tx_batch(ctx, n, d.data(), plcf.data(), tb.data(), iq_out, ns.data()), "dnrp_tx_batch");
+            for (uint32_t i = 0; i < n; ++i) descs[i].hp_tx.finalize();
+            if (n_samples) *n_samples = ns;
+            stats.tx_packets += n;
+        }
+
+        /// simulation only: the packets of the last generate_tx_packets call through the channel into the RX windows
+        void channel(const std::vector<dnrp_channel_desc_t>& descs, cf_t* iq_rx_out = nullptr) {
+            check(dnrp_channel_batch(ctx, (uint32_t)descs.size(), descs.data(), iq_rx_out), "dnrp_channel_batch");
+        }
+
+        /// One scheduling quantum of the receive path for n IQ windows [n][N_RX][rx_stride] at the hardware rate
+        /// (nullptr: the windows left on the device by channel()); window_start_64[i] = global time of window i's first
+        /// sample.  sync_chunk_t::search -> rx_synced_t::demoddecod_rx_pcc -> work_pcc (FIFO) -> demoddecod_rx_pdc ->
+        /// work_pdc / work_pdc_error -> hp_rx->finalize.  Returns the TX descriptors the firmware handed back.
+        machigh_phy_t::tx_descriptor_vec_t process_windows(uint32_t n, const cf_t* windows, const int64_t* window_start_64,
+                                                           upper::tpoint_t& tpoint) {
+            machigh_phy_t::tx_descriptor_vec_t tx_out;
+            if (n == 0) return tx_out;
+            if (n > max_windows) throw std::invalid_argument("more windows than the context was created for");
+            std::vector<dnrp_sync_result_t> sres(n);
+            check(dnrp_sync_batch(ctx, n, windows, 0, sres.data()), "dnrp_sync_batch");
+            std::vector<dnrp_pcc_report_t> pcc(n);
+            check(dnrp_rx_pcc_batch(ctx, n, nullptr, nullptr, pcc.data()), "dnrp_rx_pcc_batch");
+            stats.windows += n;
+
+            std::vector<sync_report_t> sync_reports;
+            std::vector<pcc_report_t> pcc_reports(n);
+            std::vector<maclow_phy_t> maclow(n);
+            std::vector<uint32_t> slot(n), job(n, 0);
+            std::vector<uint8_t> rv(n, 0), reset(n, 1), keep(n, 0);
+            sync_reports.reserve(n);
+            const uint32_t N_RX = get_N_RX();
+            for (uint32_t i = 0; i < n; ++i) {               // FIFO: job order = window order (worker_tx_rx.cpp:165-170)
+                sync_reports.emplace_back(N_RX);
+                sync_report_t& s = sync_reports.back();
+                const dnrp_sync_result_t& r = sres[i];
+                if (!r.detected) continue;
+                ++stats.detections;
+                const int64_t t0 = window_start_64 ? window_start_64[i] : 0;
+                s.detection_ant_idx = r.detection_ant_idx; s.detection_rms = r.detection_rms;
+                s.detection_metric = r.detection_metric; s.detection_time_local = r.detection_time_local;
+                s.u = config.psdef.u; s.b = config.psdef.b; s.N_eff_TX = r.N_eff_TX;
+                for (uint32_t a = 0; a < N_RX; ++a) { s.coarse_peak_array.at(a) = r.coarse_peak_array[a]; s.rms_array.at(a) = pcc[i].rms[a]; }
+                s.coarse_peak_time_local = r.coarse_peak_time_local;
+                s.coarse_peak_time_64 = t0 + r.coarse_peak_time_hw;
+                s.cfo_fractional_rad = r.cfo_fractional_rad + pcc[i].cfo_residual_rad;   // rx_synced.cpp:552
+                s.cfo_integer_rad = r.cfo_integer_rad;
+                s.fine_peak_time_local = r.fine_peak_time_local;
+                s.fine_peak_time_64 = t0 + r.fine_peak_time_local;
+                s.sto_fractional = pcc[i].sto_fractional;                                   // rx_synced.cpp:581
+                s.fine_peak_time_corrected_by_sto_fractional_64 = s.fine_peak_time_64 + (int64_t)std::lround(s.sto_fractional);
+                pcc_report_t& p = pcc_reports[i];
+                for (uint32_t t = 0; t < 2; ++t) {
+                    p.plcf_ok[t] = pcc[i].plcf_ok[t] != 0;
+                    std::memcpy(p.plcf[t].data(), pcc[i].plcf[t], 10);
+                    p.crc_mask[t] = pcc[i].crc_mask[t];
+                }
+                p.snr_dB = pcc[i].snr_dB;
+                if (!p.has_any_plcf()) continue;                // worker_tx_rx.cpp:129: no callback without a valid PLCF
+                ++stats.pcc_ok;
+                maclow[i] = tpoint.work_pcc(phy_maclow_t{s, p});
+                if (!maclow[i].continue_with_pdc || maclow[i].hp_rx == nullptr) continue;
+                keep[i] = 1;
+                ++stats.pdc_requested;
+            }
+            // HARQ slots: a receive process id IS its soft buffer slot [0, nof_process_rx); packets whose PDC is not
+            // wanted still pass through the batched decoder and use the scratch slots behind them
+            {
+                std::vector<uint8_t> used(nof_process_rx, 0);
+                for (uint32_t i = 0; i < n; ++i) {
+                    slot[i] = nof_process_rx + i;
+                    if (!keep[i]) continue;
+                    const uint32_t id = maclow[i].hp_rx->get_id();
+                    if (id >= nof_process_rx || used[id])
+                        throw std::runtime_error("HARQ process assigned twice in one batch or id beyond nof_process_rx");
+                    used[id] = 1; slot[i] = id; rv[i] = (uint8_t)maclow[i].hp_rx->get_rv();
+                    reset[i] = maclow[i].hp_rx->is_first_transmission() ? 1 : 0;
+                }
+            }
+            std::vector<uint8_t> tb((size_t)n * packet_sizes.N_TB_byte);
+            std::vector<dnrp_pdc_report_t> pdc(n);
+            check(dnrp_rx_pdc_batch(ctx, n, slot.data(), rv.data(), reset.data(), tb.data(), pdc.data(), nullptr), "dnrp_rx_pdc_batch");
+            for (uint32_t i = 0; i < n; ++i) {
+                if (!keep[i]) continue;
+                harq::process_rx_t* hp = maclow[i].hp_rx;
+                std::memcpy(hp->get_a_tb(), &tb[(size_t)i * packet_sizes.N_TB_byte], packet_sizes.N_TB_byte);
+                pdc_report_t rep;
+                rep.crc_status = pdc[i].crc_ok != 0;
+                rep.a_tb = hp->get_a_tb(); rep.N_TB_byte = packet_sizes.N_TB_byte;
+                rep.snr_dB = pdc[i].snr_dB;
+                rep.mimo_report.N_RX = pdc[i].mimo_N_RX; rep.mimo_report.N_TS_other = pdc[i].mimo_N_TS_other;
+                rep.mimo_report.tm_3_7_beamforming_idx = pdc[i].tm_3_7_beamforming_idx;
+                rep.mimo_report.tm_3_7_beamforming_reciprocal_idx = pdc[i].tm_3_7_beamforming_reciprocal_idx;
+                const phy_maclow_t pm{sync_reports[i], pcc_reports[i]};
+                const phy_machigh_t in{pm, maclow[i], rep};
+                machigh_phy_t out = rep.crc_status ? tpoint.work_pdc(in) : tpoint.work_pdc_error(in);
+                if (rep.crc_status) ++stats.pdc_crc_ok;
+                hp->finalize(rep.crc_status);                   // worker_tx_rx.cpp:228
+                for (auto& d : out.tx_descriptor_vec) tx_out.push_back(d);
+            }
+            return tx_out;
+        }
+
+    private:
+        dnrp_config_t config;
+        uint32_t max_windows, nof_process_rx;
+        dnrp_ctx_t* ctx{nullptr};
+        sp3::packet_sizes_t packet_sizes{};
+        uint32_t tx_stride{0}, rx_stride{0};
+        stats_t stats;
+        static void check(int rc, const char* what) {
+            if (rc != DNRP_OK) throw std::runtime_error(std::string(what) + ": " + dnrp_last_error_string());
+        }
+};
+
+}  // namespace phy
+}  // namespace dectnrp_b200

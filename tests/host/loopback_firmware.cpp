@@ -1,0 +1,158 @@
+// loopback_firmware.cpp -- test program for include/dnrp_host.hpp: a firmware in the style of the reference's
+// tfw_loopback (lib/src/upper/tpoint_firmware/loopback/tfw_loopback.cpp) written against the mirrored tpoint_t
+// callbacks.  Scenario 1: n packets at a good SNR -> every work_pcc sees its PLCF, every work_pdc its transport block.
+// Scenario 2 (HARQ): first transmission at a poor SNR fails (work_pdc_error, process keeps running), the
+// retransmission with the next redundancy version is combined in the same soft buffer slot and decodes.
+// Prints one JSON line; exit code 0 = all checks passed, 3 = no usable GPU (the library has no CPU fallback).
+#include <cstdio>
+#include <cstdlib>
+#include <map>
+#include <random>
+
+#include "dnrp_host.hpp"
+
+using namespace dectnrp_b200;
+
+struct firmware_t final : public upper::tpoint_t {
+    firmware_t(const sp3::packet_sizes_t& ps, uint32_t n_proc) : packet_sizes(ps), pool(ps, n_proc, n_proc) {}
+
+    phy::maclow_phy_t work_pcc(const phy::phy_maclow_t& in) override {
+        ++n_work_pcc;
+        order.push_back(in.sync_report.fine_peak_time_64);
+        const uint8_t* plcf = in.pcc_report.get_plcf_bytes(1);
+        if (!plcf) return phy::maclow_phy_t();
+        const uint32_t key = plcf[1] | (plcf[2] << 8);            // the firmware's own packet tag inside the PLCF
+        auto it = sent.find(key);
+        if (it == sent.end()) return phy::maclow_phy_t();
+        if (std::memcmp(plcf, it->second.plcf, 5) != 0) ++n_plcf_mismatch;
+        phy::harq::process_rx_t* hp;
+        auto run = running_rx.find(key);
+        if (run != running_rx.end()) {
+            hp = pool.get_process_rx_running(run->second, it->second.rv, frx);
+        } else {
+            hp = pool.get_process_rx(1, network_id, packet_sizes.psdef, it->second.rv, frx);
+            if (hp) running_rx[key] = hp->get_id();
+        }
+        if (!hp) return phy::maclow_phy_t();
+        return phy::maclow_phy_t(hp, phy::maclow_phy_handle_t(phy::handle_pcc2pdc_t::th10, key));
+    }
+    phy::machigh_phy_t work_pdc(const phy::phy_machigh_t& in) override {
+        ++n_work_pdc;
+        const uint32_t key = in.maclow_phy.get_handle_lrdid();
+        if (std::memcmp(in.pdc_report.a_tb, sent[key].tb.data(), packet_sizes.N_TB_byte) != 0) ++n_tb_mismatch;
+        snr_sum += in.pdc_report.snr_dB;
+        running_rx.erase(key);
+        return phy::machigh_phy_t();
+    }
+    phy::machigh_phy_t work_pdc_error(const phy::phy_machigh_t& in) override {
+        ++n_work_pdc_error;
+        (void)in;
+        return phy::machigh_phy_t();
+    }
+
+    struct sent_t { uint8_t plcf[10]; std::vector<uint8_t> tb; uint32_t rv; };
+    sp3::packet_sizes_t packet_sizes;
+    phy::harq::process_pool_t pool;
+    phy::harq::finalize_rx_t frx{phy::harq::finalize_rx_t::keep_running_or_reset_and_terminate_if_crc_correct};
+    uint32_t network_id{123456789};
+    std::map<uint32_t, sent_t> sent;
+    std::map<uint32_t, uint32_t> running_rx;
+    std::vector<int64_t> order;
+    uint32_t n_work_pcc{0}, n_work_pdc{0}, n_work_pdc_error{0}, n_plcf_mismatch{0}, n_tb_mismatch{0};
+    double snr_sum{0};
+};
+
+int main(int argc, char** argv) {
+    const uint32_t n = argc > 1 ? (uint32_t)std::atoi(argv[1]) : 32;
+    dnrp_config_t cfg{};
+    cfg.psdef = {1, 4, 1, 1, 0, 4, 2048};   // mu 1, beta 4, one slot, SISO, 16-QAM 3/4
+    cfg.N_RX = 2; cfg.oversampling = 1; cfg.resample_L = 10; cfg.resample_M = 9;
+    cfg.max_batch = n; cfg.network_id = 123456789; cfg.plcf_type = 1;
+    cfg.chestim_mode_lr = 1; cfg.chestim_mode_lr_t_stride = 2;
+    std::unique_ptr<phy::batch_phy_t> bp;
+    try {
+        bp = std::make_unique<phy::batch_phy_t>(cfg, 0, n);
+    } catch (const std::exception& e) {
+        std::fprintf(stderr, "loopback_firmware: %s\n", e.what());
+        return 3;
+    }
+    const sp3::packet_sizes_t ps = bp->get_packet_sizes();
+    firmware_t fw(ps, n);
+    std::mt19937 rng(7);
+    int fails = 0;
+    const phy::tx_meta_t tx_meta{false, 1.0f, 0.0f, 0.0f, 5};
+
+    auto transmit = [&](std::vector<phy::harq::process_tx_t*>& procs, float snr_dB, uint64_t seed) {
+        std::vector<phy::tx_descriptor_t> descs;
+        for (auto* hp : procs) descs.emplace_back(*hp, 0, tx_meta, radio::buffer_tx_meta_t{});
+        for (auto* hp : procs) fw.sent[hp->get_a_plcf()[1] | (hp->get_a_plcf()[2] << 8)].rv = hp->get_rv();
+        bp->generate_tx_packets(descs, nullptr);
+        std::vector<dnrp_channel_desc_t> ch(procs.size());
+        std::vector<int64_t> start(procs.size());
+        for (size_t i = 0; i < ch.size(); ++i) {
+            ch[i] = dnrp_channel_desc_t{};
+            ch[i].snr_dB = snr_dB; ch[i].net_bandwidth_norm = 0.9f; ch[i].t0 = 150 + (uint32_t)(rng() % 300);
+            ch[i].mode = 0; ch[i].seed = seed;
+            start[i] = 1000000 * (int64_t)(i + 1);
+        }
+        bp->channel(ch);
+        auto back = bp->process_windows((uint32_t)procs.size(), nullptr, start.data(), fw);
+        return back.size();
+    };
+
+    // ---- scenario 1: n fresh packets, good SNR
+    std::vector<phy::harq::process_tx_t*> procs;
+    for (uint32_t i = 0; i < n; ++i) {
+        auto* hp = fw.pool.get_process_tx(1, fw.network_id, ps.psdef, phy::harq::finalize_tx_t::reset_and_terminate);
+        if (!hp) { ++fails; break; }
+        firmware_t::sent_t s{};
+        s.plcf[0] = 0x20; s.plcf[1] = (uint8_t)i; s.plcf[2] = 1; s.plcf[3] = (uint8_t)rng(); s.plcf[4] = (uint8_t)rng();
+        s.tb.resize(ps.N_TB_byte);
+        for (auto& v : s.tb) v = (uint8_t)rng();
+        std::memcpy(hp->get_a_plcf(), s.plcf, 10);
+        std::memcpy(hp->get_a_tb(), s.tb.data(), ps.N_TB_byte);
+        fw.sent[s.plcf[1] | (s.plcf[2] << 8)] = s;
+        procs.push_back(hp);
+    }
+    transmit(procs, 28.0f, 11);
+    const uint32_t pcc1 = fw.n_work_pcc, pdc1 = fw.n_work_pdc, err1 = fw.n_work_pdc_error;
+    if (pcc1 != n || pdc1 != n || err1 != 0 || fw.n_plcf_mismatch || fw.n_tb_mismatch) ++fails;
+    for (size_t i = 1; i < fw.order.size(); ++i) if (fw.order[i] <= fw.order[i - 1]) ++fails;   // work_pcc FIFO
+    for (auto* hp : procs) if (hp->is_running()) ++fails;                                        // reset_and_terminate
+
+    // ---- scenario 2: HARQ, poor SNR first, retransmission with the next rv
+    procs.clear();
+    const uint32_t m = n < 8 ? n : 8;
+    for (uint32_t i = 0; i < m; ++i) {
+        auto* hp = fw.pool.get_process_tx(1, fw.network_id, ps.psdef, phy::harq::finalize_tx_t::increase_rv_and_keep_running);
+        firmware_t::sent_t s{};
+        s.plcf[0] = 0x20; s.plcf[1] = (uint8_t)i; s.plcf[2] = 2;
+        s.tb.resize(ps.N_TB_byte);
+        for (auto& v : s.tb) v = (uint8_t)rng();
+        std::memcpy(hp->get_a_plcf(), s.plcf, 10);
+        std::memcpy(hp->get_a_tb(), s.tb.data(), ps.N_TB_byte);
+        fw.sent[s.plcf[1] | (s.plcf[2] << 8)] = s;
+        procs.push_back(hp);
+    }
+    uint32_t rounds = 0;
+    const uint32_t pdc_before = fw.n_work_pdc;
+    while (fw.n_work_pdc - pdc_before < m && rounds < 4) {
+        std::vector<phy::harq::process_tx_t*> todo;
+        for (auto* hp : procs)
+            if (fw.running_rx.count(hp->get_a_plcf()[1] | (2u << 8)) || rounds == 0) todo.push_back(hp);
+        if (todo.empty()) break;
+        transmit(todo, 5.0f, 100 + rounds);   // 16-QAM 3/4 on two antennas does not decode at 5 dB in one shot
+        ++rounds;
+    }
+    const uint32_t err2 = fw.n_work_pdc_error - err1, pdc2 = fw.n_work_pdc - pdc_before;
+    if (pdc2 != m || err2 == 0 || rounds < 2 || fw.n_tb_mismatch) ++fails;
+
+    const auto& st = bp->get_stats();
+    std::printf("{\"n\": %u, \"work_pcc\": %u, \"work_pdc\": %u, \"work_pdc_error\": %u, \"plcf_mismatch\": %u, "
+                "\"tb_mismatch\": %u, \"harq_rounds\": %u, \"harq_first_round_errors\": %u, \"harq_decoded\": %u, "
+                "\"windows\": %llu, \"detections\": %llu, \"mean_snr_dB\": %.2f, \"fails\": %d}\n",
+                n, fw.n_work_pcc, fw.n_work_pdc, fw.n_work_pdc_error, fw.n_plcf_mismatch, fw.n_tb_mismatch, rounds, err2,
+                pdc2, (unsigned long long)st.windows, (unsigned long long)st.detections,
+                fw.n_work_pdc ? fw.snr_sum / fw.n_work_pdc : 0.0, fails);
+    return fails ? 1 : 0;
+}
