@@ -170,6 +170,29 @@ def run_reference(args):
         "gpu_launches": 0}))
 
 
+def rank_seed(base, rank):
+    """disjoint synthetic packet streams per rank (packets are sharded, no rank sees another's data)"""
+    return base + 1000003 * rank
+
+
+def reduce_over_ranks(times_ms, counters, world, device):
+    """the path's only collective: MAX over ranks of the device-timed step times, SUM of the PER / throughput counters
+    (NCCL over NVLink on the GPUs; gloo in the CPU test).  Returns (times, counters) valid on every rank."""
+    import torch
+    import torch.distributed as dist
+    t = torch.tensor(list(times_ms), dtype=torch.float64, device=device)
+    c = torch.tensor(list(counters), dtype=torch.int64, device=device)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        dist.all_reduce(c, op=dist.ReduceOp.SUM)
+    return [float(v) for v in t.cpu()], [int(v) for v in c.cpu()]
+
+
+def whole_job_value(total_bits, ms_step_max):
+    """decoded Mbit/s of the whole job: bits of all ranks / slowest rank's step time"""
+    return total_bits / (ms_step_max * 1e-3) / 1e6
+
+
 # ---- GPU arm ------------------------------------------------------------------------------------
 def run_b200(args):
     import torch
@@ -192,7 +215,7 @@ def run_b200(args):
     stride = phy.rx_stride()
 
     # ---- synthetic batch of this rank: TX and channel run on the device, IQ windows fetched once for e2e
-    rng = np.random.default_rng(1000 + rank)
+    rng = np.random.default_rng(rank_seed(1000, rank))
     tb = rng.integers(0, 256, (P, ps["N_TB_byte"]), dtype=np.uint8)
     plcf = rng.integers(0, 256, (P, 10), dtype=np.uint8)
     stf_len, pat = ps["N_samples_STF"], 16 * psdef[1]
@@ -255,20 +278,14 @@ def run_b200(args):
     e2e_s = (time.perf_counter() - t_start) / args.steps
 
     # ---- reduce over ranks: max of the times, sum of the counters (the one collective of this path)
-    times = torch.tensor([ms_step, e2e_s * 1e3], dtype=torch.float64, device="cuda")
-    counters = torch.tensor([P, n_ok_res, n_ok_res * ps["N_TB_bits"], n_ok, n_plcf_ok, n_sync_ok], dtype=torch.int64,
-                            device="cuda")
-    if world > 1:
-        dist.all_reduce(times, op=dist.ReduceOp.MAX)
-        dist.all_reduce(counters, op=dist.ReduceOp.SUM)
-    ms_step_max, e2e_ms_max = [float(v) for v in times.cpu()]
-    tot_P, tot_ok, tot_bits, tot_ok_e2e, tot_plcf, tot_sync = [int(v) for v in counters.cpu()]
+    (ms_step_max, e2e_ms_max), (tot_P, tot_ok, tot_bits, tot_ok_e2e, tot_plcf, tot_sync) = reduce_over_ranks(
+        [ms_step, e2e_s * 1e3], [P, n_ok_res, n_ok_res * ps["N_TB_bits"], n_ok, n_plcf_ok, n_sync_ok], world, "cuda")
     if rank != 0:
         if world > 1:
             dist.destroy_process_group()
         return
 
-    value = tot_bits / (ms_step_max * 1e-3) / 1e6
+    value = whole_job_value(tot_bits, ms_step_max)
     e2e_value = tot_ok_e2e * ps["N_TB_bits"] / (e2e_ms_max * 1e-3) / 1e6
     # roofline of the dominant kernel: algorithmic bytes per packet of the fused de-rate-match + HARQ +
     # turbo decode + CRC kernel (DESIGN.md "k_turbo_decode"): LLRs in, soft buffer out, TB + flags out
