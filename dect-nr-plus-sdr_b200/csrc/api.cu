@@ -99,7 +99,8 @@ int dnrp_ctx_create(const dnrp_config_t* cfg, int device, dnrp_ctx_t** out) {
     };
     if (!spec::get_packet_sizes(d, c->ps)) return fail(DNRP_ERR_INVALID, "packet configuration not possible");
     if ((rc = build_fec_plan(c->ps, c->fec)) != DNRP_OK) return fail(rc, "FEC plan failed");
-    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess)
+    if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->stream_copy, cudaStreamNonBlocking) != cudaSuccess)
         return fail(DNRP_ERR_CUDA, "cudaStreamCreate failed");
 
     const fec_plan_t& f = c->fec;
@@ -148,6 +149,8 @@ void dnrp_ctx_destroy(dnrp_ctx_t* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
+    if (ctx->stream_copy) cudaStreamDestroy(ctx->stream_copy);
+    for (cudaEvent_t e : ctx->chunk_events) cudaEventDestroy(e);
     for (auto& t : ctx->ktimer)
         for (cudaEvent_t e : t.ev) cudaEventDestroy(e);
     delete ctx;
@@ -200,16 +203,19 @@ int run_fec_decode_tb(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, boo
     const fec_plan_t& f = c->fec;
     tdec_params_t p{};
     p.cbs = c->d_rx_cbs.p; p.C = c->ps.C;
-    p.llr = c->d_llr.p; p.llr_stride = c->ps.G;
+    // packets [off, off + n): per-packet buffers are offset; HARQ state is addressed by slot (= packet without a slot
+    // array, then offset alike)
+    const size_t off = c->off, soff = have_slot ? 0 : off;
+    p.llr = c->d_llr.p + off * c->ps.G; p.llr_stride = c->ps.G;
     p.gold = c->d_gold_pdc.p; p.gold_bit_off = 0;
-    p.soft = c->d_soft.p; p.soft_stride = f.soft_stride;
-    p.cb_crc = c->d_cb_crc.p;
-    p.saved = c->d_saved.p; p.saved_stride = f.saved_stride;
-    p.slot = have_slot ? c->d_slot.p : nullptr;
-    p.rv = have_rv ? c->d_rv.p : nullptr;
-    p.reset = have_reset ? c->d_reset.p : nullptr;
-    p.tb_out = c->d_tb_out.p; p.tb_stride = f.tb_stride;
-    p.n_iter = c->d_n_iter.p;
+    p.soft = c->d_soft.p + soff * f.soft_stride; p.soft_stride = f.soft_stride;
+    p.cb_crc = c->d_cb_crc.p + soff * c->ps.C;
+    p.saved = c->d_saved.p + soff * f.saved_stride; p.saved_stride = f.saved_stride;
+    p.slot = have_slot ? c->d_slot.p + off : nullptr;
+    p.rv = have_rv ? c->d_rv.p + off : nullptr;
+    p.reset = have_reset ? c->d_reset.p + off : nullptr;
+    p.tb_out = c->d_tb_out.p + off * f.tb_stride; p.tb_stride = f.tb_stride;
+    p.n_iter = c->d_n_iter.p + off * c->ps.C;
     p.rm_arena = c->d_rm_arena.p; p.xp_arena = c->d_xp_arena.p;
     p.min_it = c->cfg.tdec_min_iter; p.max_it = c->cfg.tdec_max_iter;
     p.crc_mode = 0; p.plcf_mask = nullptr;
@@ -220,9 +226,9 @@ int run_fec_decode_tb(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, boo
     DNRP_LAUNCH(c, DNRP_KERNEL_TURBO_DECODE_PDC, launch_turbo_decode(p, n, geom, c->stream));
     tbfin_params_t t{};
     t.C = c->ps.C; t.tbs_bits = c->ps.N_TB_bits; t.chunk_bytes = f.tb_chunk_bytes;
-    t.slot = p.slot; t.cb_crc = c->d_cb_crc.p;
-    t.tb_out = c->d_tb_out.p; t.tb_stride = f.tb_stride;
-    t.xp_tb = c->d_xp_tb.p; t.tb_ok = c->d_tb_ok.p;
+    t.slot = p.slot; t.cb_crc = p.cb_crc;
+    t.tb_out = p.tb_out; t.tb_stride = f.tb_stride;
+    t.xp_tb = c->d_xp_tb.p; t.tb_ok = c->d_tb_ok.p + off;
     DNRP_LAUNCH(c, -1, launch_tb_finalize(t, n, c->stream));
     return DNRP_OK;
 }
@@ -231,17 +237,18 @@ int run_fec_decode_plcf(dnrp_ctx* c, uint32_t n) {
     const fec_plan_t& f = c->fec;
     tdec_params_t p{};
     p.cbs = c->d_rx_pcc.p; p.C = 2;
-    p.llr = c->d_llr_pcc.p; p.llr_stride = 196;
+    const size_t off = c->off;
+    p.llr = c->d_llr_pcc.p + off * 196; p.llr_stride = 196;
     p.gold = c->d_gold_pcc.p; p.gold_bit_off = 0;
-    p.soft = c->d_soft_pcc.p; p.soft_stride = 640;
-    p.cb_crc = c->d_pcc_crc.p;
+    p.soft = c->d_soft_pcc.p + off * 640; p.soft_stride = 640;
+    p.cb_crc = c->d_pcc_crc.p + off * 2;
     p.saved = nullptr; p.saved_stride = 0;
     p.slot = nullptr; p.rv = nullptr; p.reset = nullptr;
-    p.tb_out = c->d_plcf_out.p; p.tb_stride = 32;
-    p.n_iter = c->d_pcc_n_iter.p;
+    p.tb_out = c->d_plcf_out.p + off * 32; p.tb_stride = 32;
+    p.n_iter = c->d_pcc_n_iter.p + off * 2;
     p.rm_arena = c->d_rm_arena.p; p.xp_arena = c->d_xp_arena.p;
     p.min_it = 1; p.max_it = 5;  // pcc_enc.cpp:39
-    p.crc_mode = 1; p.plcf_mask = c->d_pcc_mask.p;
+    p.crc_mode = 1; p.plcf_mask = c->d_pcc_mask.p + off * 2;
     DNRP_LAUNCH(c, -1, launch_derm(p, n, spec::PCC_BITS, c->stream));
     DNRP_LAUNCH(c, -1, launch_turbo_decode(p, n, tdec_geometry(f.rx_pcc, 2), c->stream));
     return DNRP_OK;

@@ -1,5 +1,6 @@
 // api_rx.cu -- receiver side of the C ABI: batched rx_synced_t::demoddecod_rx_pcc / _pdc
 // (reference lib/src/phy/rx/rx_synced/rx_synced.cpp:186-436) on the context's device buffers.
+#include <algorithm>
 #include <cmath>
 #include <cstring>
 #include "ctx.hpp"
@@ -19,17 +20,22 @@ namespace dnrp {
 
 rx_params_t make_rx_params(dnrp_ctx* c) {
     rx_params_t p{};
-    p.d = c->dims;
+    const phy_dims_t& d = c->dims;
+    const size_t off = c->off;
+    p.d = d;
     if (c->resampling) {
-        p.iq = c->d_iq_rs.p; p.iq_stride = c->rs_stride; p.t0_zero = 1;
+        p.iq = c->d_iq_rs.p + off * d.N_RX * c->rs_stride; p.iq_stride = c->rs_stride; p.t0_zero = 1;
     } else {
-        p.iq = c->d_iq_rx.p; p.iq_stride = c->rx_stride; p.t0_zero = 0;
+        p.iq = c->d_iq_rx.p + off * d.N_RX * c->rx_stride; p.iq_stride = c->rx_stride; p.t0_zero = 0;
     }
-    p.state = c->d_rx_state.p;
-    p.Y = c->d_Y.p; p.hzf = c->d_hzf.p; p.hstf = c->d_hstf.p; p.snr_part = c->d_snr_part.p;
-    p.cls = c->d_cls.p; p.cls_stride = c->cls_stride;
-    p.llr_pcc = c->d_llr_pcc.p;
-    p.llr = c->d_llr.p; p.llr_stride = c->ps.G;
+    p.state = c->d_rx_state.p + off;
+    p.Y = c->d_Y.p + off * d.N_RX * d.N_DF * d.Nk;
+    p.hzf = c->d_hzf.p + off * d.N_RX * d.N_eff_TX * d.n_drs * d.NP;
+    p.hstf = c->d_hstf.p + off * d.N_RX * d.NP;
+    p.snr_part = c->d_snr_part.p + off * d.N_DF * d.N_RX;
+    p.cls = c->d_cls.p + off * c->cls_stride; p.cls_stride = c->cls_stride;
+    p.llr_pcc = c->d_llr_pcc.p + off * 196;
+    p.llr = c->d_llr.p + off * c->ps.G; p.llr_stride = c->ps.G;
     return p;
 }
 
@@ -55,7 +61,7 @@ int run_rx_pdc(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, bool have_
     const rx_params_t p = make_rx_params(c);
     DNRP_LAUNCH(c, DNRP_KERNEL_RX_DEMAP_PDC, launch_rx_demap(p, n, false, c->stream));
     mimo_params_t mp{};
-    mp.d = c->dims; mp.hzf = c->d_hzf.p; mp.out = c->d_mimo.p;
+    mp.d = c->dims; mp.hzf = p.hzf; mp.out = c->d_mimo.p + c->off;
     for (int s = 0; s < 2; ++s) {
         mp.W[s] = c->d_mimo_W[s].p; mp.W_scale[s] = c->d_mimo_scale[s].p;
         mp.n[s] = c->mimo_n[s]; mp.first[s] = c->mimo_first[s];
@@ -85,7 +91,9 @@ int run_sync(dnrp_ctx* c, uint32_t n, uint32_t search_length, bool hand_over) {
     const phy_dims_t& d = c->dims;
     sync_params_t p{};
     p.d = d;
-    p.iq_x = c->d_iq_rx.p; p.x_stride = c->rx_stride; p.x_len = c->rx_stride;
+    const size_t off = c->off;
+    const float2* iq_hw = c->d_iq_rx.p + off * d.N_RX * c->rx_stride;
+    p.iq_x = iq_hw; p.x_stride = c->rx_stride; p.x_len = c->rx_stride;
     p.rs_L = c->cfg.resample_L; p.rs_M = c->cfg.resample_M;
     p.xc_S = c->stf_len_rs;
     p.xc_sl = (uint32_t)((uint64_t)d.pat_len_os * p.rs_L / p.rs_M);  // crosscorrelator.cpp:52-56
@@ -95,24 +103,25 @@ int run_sync(dnrp_ctx* c, uint32_t n, uint32_t search_length, bool hand_over) {
         resample_params_t r{};
         r.L = c->rs_rx.L; r.M = c->rs_rx.M; r.SL = c->rs_rx.subfilter_length; r.delay = c->rs_rx.delay;
         r.taps = c->d_rs_rx_taps.p;
-        r.in = c->d_iq_rx.p; r.in_stride = c->rx_stride; r.n_in = c->rx_stride;
-        r.out = c->d_iq_sync.p; r.out_stride = c->sync_stride; r.n_out = c->sync_len; r.n_fill = c->sync_stride;
+        r.in = iq_hw; r.in_stride = c->rx_stride; r.n_in = c->rx_stride;
+        r.out = c->d_iq_sync.p + off * d.N_RX * c->sync_stride; r.out_stride = c->sync_stride;
+        r.n_out = c->sync_len; r.n_fill = c->sync_stride;
         r.n_ant = d.N_RX;
         DNRP_LAUNCH(c, DNRP_KERNEL_RESAMPLE, launch_resample(r, n, c->stream));
-        p.iq = c->d_iq_sync.p; p.iq_stride = c->sync_stride; p.len = c->sync_len;
+        p.iq = r.out; p.iq_stride = c->sync_stride; p.len = c->sync_len;
     } else {
-        p.iq = c->d_iq_rx.p; p.iq_stride = c->rx_stride; p.len = c->rx_stride;
+        p.iq = iq_hw; p.iq_stride = c->rx_stride; p.len = c->rx_stride;
     }
     p.n_ant = d.N_RX;  // RX_SYNC_PARAM_AUTOCORRELATOR_ANTENNA_LIMIT = 8 >= N_RX
     p.step = c->sync_step; p.n_steps = c->sync_n_steps;
     p.search_length = search_length ? search_length : p.len - d.stf_len_os - d.pat_len_os;
     // autocorrelator_detection.cpp:60-62: minimum rms scaled with the sample rate relative to 30.72 MS/s
     p.rms_min = 0.005f * (float)std::sqrt((double)d.u * d.b * c->cfg.oversampling * 1.728e6 / 30.72e6);
-    p.c_steps = c->d_sync_c.p; p.p_steps = c->d_sync_p.p;
+    p.c_steps = c->d_sync_c.p + off * d.N_RX * c->sync_n_steps; p.p_steps = c->d_sync_p.p + off * d.N_RX * c->sync_n_steps;
     p.templates = c->d_sync_tpl.p; p.n_tpl = c->sync_n_tpl;
-    p.xc = c->d_sync_xc.p;
-    p.result = c->d_sync_result.p;
-    p.rx_state = hand_over ? c->d_rx_state.p : nullptr;
+    p.xc = c->d_sync_xc.p + off * c->sync_n_tpl;
+    p.result = c->d_sync_result.p + off;
+    p.rx_state = hand_over ? c->d_rx_state.p + off : nullptr;
     c->launches += 3;  // launch_sync issues four kernels
     DNRP_LAUNCH(c, DNRP_KERNEL_SYNC, launch_sync(p, n, c->stream));
     return DNRP_OK;
@@ -125,11 +134,61 @@ int run_rx_resample(dnrp_ctx* c, uint32_t n) {
     resample_params_t r{};
     r.L = c->rs_rx.L; r.M = c->rs_rx.M; r.SL = c->rs_rx.subfilter_length; r.delay = c->rs_rx.delay;
     r.taps = c->d_rs_rx_taps.p;
-    r.in = c->d_iq_rx.p; r.in_stride = c->rx_stride; r.n_in = c->rx_stride;
-    r.start = &c->d_rx_state.p->t0; r.start_stride_words = sizeof(rx_state_t) / 4;
-    r.out = c->d_iq_rs.p; r.out_stride = c->rs_stride; r.n_out = d.n_no_gi_os; r.n_fill = c->rs_stride;
+    const size_t off = c->off;
+    r.in = c->d_iq_rx.p + off * d.N_RX * c->rx_stride; r.in_stride = c->rx_stride; r.n_in = c->rx_stride;
+    r.start = &(c->d_rx_state.p + off)->t0; r.start_stride_words = sizeof(rx_state_t) / 4;
+    r.out = c->d_iq_rs.p + off * d.N_RX * c->rs_stride; r.out_stride = c->rs_stride;
+    r.n_out = d.n_no_gi_os; r.n_fill = c->rs_stride;
     r.n_ant = d.N_RX;
     DNRP_LAUNCH(c, DNRP_KERNEL_RESAMPLE, launch_resample(r, n, c->stream));
+    return DNRP_OK;
+}
+
+// device -> host: results of the PCC stage for packets [0, n)
+int fetch_pcc_reports(dnrp_ctx* c, uint32_t n, dnrp_pcc_report_t* out) {
+    std::vector<uint8_t> ok(2 * n), plcf(32 * n);
+    std::vector<uint32_t> mask(2 * n);
+    DNRP_CUDA(cudaMemcpyAsync(c->h_rx_state.data(), c->d_rx_state.p, n * sizeof(rx_state_t),
+                              cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaMemcpyAsync(ok.data(), c->d_pcc_crc.p, 2 * n, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaMemcpyAsync(plcf.data(), c->d_plcf_out.p, 32 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaMemcpyAsync(mask.data(), c->d_pcc_mask.p, 8 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    for (uint32_t i = 0; i < n; ++i) {
+        const rx_state_t& s = c->h_rx_state[i];
+        dnrp_pcc_report_t& r = out[i];
+        std::memset(&r, 0, sizeof(r));
+        for (uint32_t t = 0; t < 2; ++t) {
+            r.plcf_ok[t] = ok[2 * i + t];
+            std::memcpy(r.plcf[t], &plcf[32 * i + 16 * t], 10);
+            r.crc_mask[t] = mask[2 * i + t];
+        }
+        r.snr_dB = s.snr_db_pcc;
+        r.cfo_residual_rad = s.cfo_left;
+        r.sto_fractional = s.sto_fractional;
+        for (uint32_t a = 0; a < 8; ++a) r.rms[a] = s.rms[a];
+    }
+    return DNRP_OK;
+}
+
+// device -> host: transport blocks and reports of the PDC stage for packets [0, n)
+int fetch_pdc_reports(dnrp_ctx* c, uint32_t n, uint8_t* tb_out, dnrp_pdc_report_t* out, uint8_t* n_iter) {
+    const fec_plan_t& f = c->fec;
+    std::vector<uint8_t> ok(n);
+    std::vector<mimo_report_dev_t> mimo(n);
+    DNRP_CUDA(cudaMemcpyAsync(mimo.data(), c->d_mimo.p, n * sizeof(mimo_report_dev_t), cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaMemcpy2DAsync(tb_out, c->ps.N_TB_byte, c->d_tb_out.p, f.tb_stride, c->ps.N_TB_byte, n,
+                                cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaMemcpyAsync(ok.data(), c->d_tb_ok.p, n, cudaMemcpyDeviceToHost, c->stream));
+    if (n_iter) DNRP_CUDA(cudaMemcpyAsync(n_iter, c->d_n_iter.p, (size_t)n * c->ps.C, cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    for (uint32_t i = 0; i < n; ++i) {
+        out[i].crc_ok = ok[i];
+        out[i].snr_dB = c->h_rx_state[i].snr_db_pdc;  // read back by the PCC stage (whole packet is known)
+        out[i].mimo_N_RX = mimo[i].N_RX; out[i].mimo_N_TS_other = mimo[i].N_TS_other;
+        out[i].tm_3_7_beamforming_idx = mimo[i].tm_3_7_beamforming_idx;
+        out[i].tm_3_7_beamforming_reciprocal_idx = mimo[i].tm_3_7_beamforming_reciprocal_idx;
+    }
     return DNRP_OK;
 }
 
@@ -182,29 +241,7 @@ int dnrp_rx_pcc_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, const
     int rc = run_rx_front(c, n);
     if (rc) return rc;
     if ((rc = run_rx_pcc(c, n)) != DNRP_OK) return rc;
-    std::vector<uint8_t> ok(2 * n), plcf(32 * n);
-    std::vector<uint32_t> mask(2 * n);
-    DNRP_CUDA(cudaMemcpyAsync(c->h_rx_state.data(), c->d_rx_state.p, n * sizeof(rx_state_t),
-                              cudaMemcpyDeviceToHost, c->stream));
-    DNRP_CUDA(cudaMemcpyAsync(ok.data(), c->d_pcc_crc.p, 2 * n, cudaMemcpyDeviceToHost, c->stream));
-    DNRP_CUDA(cudaMemcpyAsync(plcf.data(), c->d_plcf_out.p, 32 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
-    DNRP_CUDA(cudaMemcpyAsync(mask.data(), c->d_pcc_mask.p, 8 * (size_t)n, cudaMemcpyDeviceToHost, c->stream));
-    DNRP_CUDA(cudaStreamSynchronize(c->stream));
-    for (uint32_t i = 0; i < n; ++i) {
-        const rx_state_t& s = c->h_rx_state[i];
-        dnrp_pcc_report_t& r = out[i];
-        std::memset(&r, 0, sizeof(r));
-        for (uint32_t t = 0; t < 2; ++t) {
-            r.plcf_ok[t] = ok[2 * i + t];
-            std::memcpy(r.plcf[t], &plcf[32 * i + 16 * t], 10);
-            r.crc_mask[t] = mask[2 * i + t];
-        }
-        r.snr_dB = s.snr_db_pcc;
-        r.cfo_residual_rad = s.cfo_left;
-        r.sto_fractional = s.sto_fractional;
-        for (uint32_t a = 0; a < 8; ++a) r.rms[a] = s.rms[a];
-    }
-    return DNRP_OK;
+    return fetch_pcc_reports(c, n, out);
 }
 
 int dnrp_rx_pdc_batch(dnrp_ctx_t* c, uint32_t n, const uint32_t* harq_slot, const uint8_t* rv,
@@ -220,22 +257,58 @@ int dnrp_rx_pdc_batch(dnrp_ctx_t* c, uint32_t n, const uint32_t* harq_slot, cons
     if (harq_reset) DNRP_CUDA(cudaMemcpyAsync(c->d_reset.p, harq_reset, n, cudaMemcpyHostToDevice, c->stream));
     int rc = run_rx_pdc(c, n, harq_slot != nullptr, rv != nullptr, harq_reset != nullptr);
     if (rc) return rc;
-    std::vector<uint8_t> ok(n);
-    std::vector<mimo_report_dev_t> mimo(n);
-    DNRP_CUDA(cudaMemcpyAsync(mimo.data(), c->d_mimo.p, n * sizeof(mimo_report_dev_t), cudaMemcpyDeviceToHost, c->stream));
-    DNRP_CUDA(cudaMemcpy2DAsync(tb_out, c->ps.N_TB_byte, c->d_tb_out.p, f.tb_stride, c->ps.N_TB_byte, n,
-                                cudaMemcpyDeviceToHost, c->stream));
-    DNRP_CUDA(cudaMemcpyAsync(ok.data(), c->d_tb_ok.p, n, cudaMemcpyDeviceToHost, c->stream));
-    if (n_iter) DNRP_CUDA(cudaMemcpyAsync(n_iter, c->d_n_iter.p, (size_t)n * c->ps.C, cudaMemcpyDeviceToHost, c->stream));
-    DNRP_CUDA(cudaStreamSynchronize(c->stream));
-    for (uint32_t i = 0; i < n; ++i) {
-        out[i].crc_ok = ok[i];
-        out[i].snr_dB = c->h_rx_state[i].snr_db_pdc;  // read back by the PCC call (whole packet is known)
-        out[i].mimo_N_RX = mimo[i].N_RX; out[i].mimo_N_TS_other = mimo[i].N_TS_other;
-        out[i].tm_3_7_beamforming_idx = mimo[i].tm_3_7_beamforming_idx;
-        out[i].tm_3_7_beamforming_reciprocal_idx = mimo[i].tm_3_7_beamforming_reciprocal_idx;
+    return fetch_pdc_reports(c, n, tb_out, out, n_iter);
+}
+
+int dnrp_rx_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, uint32_t search_length, const uint32_t* harq_slot,
+                  const uint8_t* rv, const uint8_t* harq_reset, dnrp_sync_result_t* sync_out, dnrp_pcc_report_t* pcc_out,
+                  uint8_t* tb_out, dnrp_pdc_report_t* pdc_out, uint8_t* n_iter) {
+    DNRP_REQUIRE(c && iq_in && tb_out && pdc_out, "null argument");
+    DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
+    DNRP_REQUIRE(search_length <= c->sync_len, "search_length exceeds the (resampled) IQ window");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    const phy_dims_t& d = c->dims;
+    if (harq_slot)
+        for (uint32_t i = 0; i < n; ++i) DNRP_REQUIRE(harq_slot[i] < c->B, "harq slot out of range");
+    if (harq_slot) DNRP_CUDA(cudaMemcpyAsync(c->d_slot.p, harq_slot, 4 * n, cudaMemcpyHostToDevice, c->stream));
+    if (rv) DNRP_CUDA(cudaMemcpyAsync(c->d_rv.p, rv, n, cudaMemcpyHostToDevice, c->stream));
+    if (harq_reset) DNRP_CUDA(cudaMemcpyAsync(c->d_reset.p, harq_reset, n, cudaMemcpyHostToDevice, c->stream));
+    // chunks: the H2D copy of chunk k+1 runs on the copy stream while chunk k is processed on the compute stream
+    const uint32_t n_chunks = n >= 2048 ? 8 : (n >= 256 ? 4 : 1);
+    const uint32_t per = (n + n_chunks - 1) / n_chunks;
+    while (c->chunk_events.size() < n_chunks) {
+        cudaEvent_t e;
+        DNRP_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        c->chunk_events.push_back(e);
     }
-    return DNRP_OK;
+    const size_t win = (size_t)d.N_RX * c->rx_stride;
+    for (uint32_t k = 0; k < n_chunks; ++k) {
+        const uint32_t o = k * per, m = std::min(per, n - std::min(n, o));
+        if (m == 0) break;
+        DNRP_CUDA(cudaMemcpyAsync(c->d_iq_rx.p + o * win, reinterpret_cast<const float2*>(iq_in) + o * win,
+                                  m * win * sizeof(float2), cudaMemcpyHostToDevice, c->stream_copy));
+        DNRP_CUDA(cudaEventRecord(c->chunk_events[k], c->stream_copy));
+    }
+    int rc = DNRP_OK;
+    for (uint32_t k = 0; k < n_chunks && rc == DNRP_OK; ++k) {
+        const uint32_t o = k * per, m = std::min(per, n - std::min(n, o));
+        if (m == 0) break;
+        DNRP_CUDA(cudaStreamWaitEvent(c->stream, c->chunk_events[k], 0));
+        c->off = o;
+        rc = run_sync(c, m, search_length, true);
+        if (rc == DNRP_OK) rc = run_rx_front(c, m);
+        if (rc == DNRP_OK) rc = run_rx_pcc(c, m);
+        if (rc == DNRP_OK) rc = run_rx_pdc(c, m, harq_slot != nullptr, rv != nullptr, harq_reset != nullptr);
+    }
+    c->off = 0;
+    if (rc) return rc;
+    if (sync_out)
+        DNRP_CUDA(cudaMemcpyAsync(sync_out, c->d_sync_result.p, n * sizeof(dnrp_sync_result_t), cudaMemcpyDeviceToHost,
+                                  c->stream));
+    std::vector<dnrp_pcc_report_t> pcc_tmp;
+    if (!pcc_out) { pcc_tmp.resize(n); pcc_out = pcc_tmp.data(); }   // also refreshes h_rx_state for the PDC reports
+    if ((rc = fetch_pcc_reports(c, n, pcc_out)) != DNRP_OK) return rc;
+    return fetch_pdc_reports(c, n, tb_out, pdc_out, n_iter);
 }
 
 static bool tap_desc(const dnrp_ctx_t* c, int tap, uint32_t n, const void*& src, size_t& bytes) {

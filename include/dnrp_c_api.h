@@ -209,6 +209,16 @@ int dnrp_rx_pcc_batch(dnrp_ctx_t* ctx, uint32_t n, const dnrp_cf32_t* iq_in, con
 int dnrp_rx_pdc_batch(dnrp_ctx_t* ctx, uint32_t n, const uint32_t* harq_slot, const uint8_t* rv,
                       const uint8_t* harq_reset, uint8_t* tb_out, dnrp_pdc_report_t* out, uint8_t* n_iter);
 
+/* The whole receive chain for n host IQ windows in ONE call: dnrp_sync_batch -> dnrp_rx_pcc_batch ->
+ * dnrp_rx_pdc_batch for every window (no MAC decision between PCC and PDC: the simulator's / a monitor's use, where
+ * every PDC is wanted; firmware that decides per packet uses the three calls, see dnrp_host.hpp).  The windows are
+ * copied and processed in chunks so that the host-to-device transfer overlaps the kernels.  iq_in
+ * [n][N_RX][dnrp_rx_stride()] should be pinned.  sync_out / pcc_out / n_iter may be NULL. */
+int dnrp_rx_batch(dnrp_ctx_t* ctx, uint32_t n, const dnrp_cf32_t* iq_in, uint32_t search_length,
+                  const uint32_t* harq_slot, const uint8_t* rv, const uint8_t* harq_reset,
+                  dnrp_sync_result_t* sync_out, dnrp_pcc_report_t* pcc_out, uint8_t* tb_out,
+                  dnrp_pdc_report_t* pdc_out, uint8_t* n_iter);
+
 /* test / scope taps (the reference exposes the same data through its JSON export and TCP scope,
  * rx_synced.cpp:363-443): copies an intermediate device buffer of the last call to the host.
  * Returns DNRP_ERR_INVALID if dst_bytes is smaller than the buffer for n packets. */

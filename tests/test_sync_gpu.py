@@ -103,3 +103,33 @@ def test_sync_noise_only_and_handover(product):
     ok, tb_out, snr_db, _ = phy.rx_pdc(n)
     assert ok.all() and (tb_out == tb).all()
     phy.close()
+
+
+@pytest.mark.parametrize("resample,N_RX", [((1, 1), 1), ((10, 9), 2)])
+def test_rx_batch_pipelined_equals_three_calls(product, resample, N_RX):
+    """dnrp_rx_batch (chunked, copies overlapped with kernels) returns exactly what sync -> rx_pcc -> rx_pdc return"""
+    cfg = CONFIGS["C1_loopback"]
+    ps = spec.get_packet_sizes(*cfg)
+    n = 300                                   # four chunks, the last one shorter
+    phy = product.Phy(cfg, max_batch=n, N_RX=N_RX, network_id=NET, resample=resample)
+    rng = np.random.default_rng(9)
+    tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
+    plcf = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    phy.tx(plcf, tb, fetch=False)
+    L, M = resample
+    stf = ps["N_samples_STF"] * L // M
+    t0 = rng.integers(stf // 2, 2 * stf - 8, n)
+    win = phy.channel(n, snr_dB=14.0, t0=t0, mode=0, seed=5, fetch=True)
+    s1 = phy.sync(iq=win)
+    p1 = phy.rx_pcc(None, n=n, sync="device")
+    ok1, tb1, snr1, _ = phy.rx_pdc(n)
+    rep1 = phy.last_pdc_report.copy()
+    # scramble the device state in between so that stale results cannot pass
+    phy.channel(n, snr_dB=-20.0, t0=0, mode=0, seed=6)
+    phy.sync(n=n)
+    s2, p2, ok2, tb2, rep2 = phy.rx(win)
+    assert s2.tobytes() == s1.tobytes()
+    assert p2.tobytes() == p1.tobytes()
+    assert np.array_equal(ok1, ok2) and np.array_equal(tb1, tb2) and rep2.tobytes() == rep1.tobytes()
+    assert ok2.mean() > 0.9 and (tb2[ok2] == tb[ok2]).all()
+    phy.close()
