@@ -221,6 +221,11 @@ int run_fec_decode_tb(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, boo
     p.crc_mode = 0; p.plcf_mask = nullptr;
     uint32_t max_n_e = 0;
     for (const cb_desc_t& d : f.rx_cbs) max_n_e = std::max(max_n_e, d.n_e);
+    {   // room for the whole circular buffer (zero padded staging) if every block's fits into 48 KB
+        uint32_t max_N = 0;
+        for (const cb_desc_t& d : f.rx_cbs) max_N = std::max(max_N, 3 * (d.K + 4));
+        if (max_N <= 24576u) max_n_e = std::max(max_n_e, max_N);
+    }
     DNRP_LAUNCH(c, DNRP_KERNEL_DERM_PDC, launch_derm(p, n, max_n_e, c->stream));
     const tdec_geom_t geom = tdec_geometry(f.rx_cbs.data(), (uint32_t)f.rx_cbs.size());
     DNRP_LAUNCH(c, DNRP_KERNEL_TURBO_DECODE_PDC, launch_turbo_decode(p, n, geom, c->stream));
@@ -249,7 +254,7 @@ int run_fec_decode_plcf(dnrp_ctx* c, uint32_t n) {
     p.rm_arena = c->d_rm_arena.p; p.xp_arena = c->d_xp_arena.p;
     p.min_it = 1; p.max_it = 5;  // pcc_enc.cpp:39
     p.crc_mode = 1; p.plcf_mask = c->d_pcc_mask.p + off * 2;
-    DNRP_LAUNCH(c, -1, launch_derm(p, n, spec::PCC_BITS, c->stream));
+    DNRP_LAUNCH(c, -1, launch_derm(p, n, 304, c->stream));  // >= 196 LLRs and >= 3 (96 + 4) buffer positions
     DNRP_LAUNCH(c, -1, launch_turbo_decode(p, n, tdec_geometry(f.rx_pcc, 2), c->stream));
     return DNRP_OK;
 }

@@ -153,6 +153,8 @@ struct dnrp_ctx {
     // packet synchronisation: STF templates for N_eff_TX = 1, 2, 4, 8 (up to the context's), step sums, results
     uint32_t sync_n_tpl = 0, sync_step = 0, sync_n_steps = 0;
     dnrp::dbuf<float2> d_sync_tpl, d_sync_c, d_sync_xc;
+    uint32_t sync_fft_n = 0;                       // FFT size of the fast cross-correlation (0: direct)
+    dnrp::dbuf<float2> d_sync_tpl_spec, d_sync_tw; // conj(FFT(template)) / N, twiddles of that size
     dnrp::dbuf<float> d_sync_p;
     dnrp::dbuf<dnrp::sync_result_dev_t> d_sync_result;
 

@@ -47,50 +47,63 @@ __global__ void __launch_bounds__(256) k_derm(const tdec_params_t p, uint32_t ca
     const uint32_t rm_start = cb.rm_start[rv];
     int16_t* DSC = (int16_t*)smem;
     const bool staged = cb.n_e <= cap;
+    // rate >= 1/3 (n_e <= N) and room for N entries: zero pad the staged LLRs up to N, every circular-buffer
+    // position then reads exactly one entry (punctured positions read a zero) -- no loop, no bounds test
+    const bool single = staged && cb.n_e <= N && N <= cap;
+    auto descr = [&](uint32_t e, int v) -> int {   // srsran_scrambling_s_offset: sign flip where the Gold bit is 1
+        const uint32_t g = cb.rp + e + p.gold_bit_off;
+        return ((p.gold[g >> 3] >> (7 - (g & 7))) & 1) ? -v : v;
+    };
     if (staged) {
-        for (uint32_t e = tid; e < cb.n_e; e += nthr) {
-            const uint32_t g = cb.rp + e + p.gold_bit_off;
-            const int v = llr[e];
-            DSC[e] = (int16_t)(((p.gold[g >> 3] >> (7 - (g & 7))) & 1) ? -v : v);
+        if ((reinterpret_cast<uintptr_t>(llr) & 3) == 0) {
+            // two LLRs per 4-byte load
+            const uint32_t* llr2 = reinterpret_cast<const uint32_t*>(llr);
+            uint32_t* DSC2 = reinterpret_cast<uint32_t*>(DSC);
+            for (uint32_t e2 = tid; e2 < cb.n_e / 2; e2 += nthr) {
+                const uint32_t w = llr2[e2];
+                const int lo = descr(2 * e2, (int)(int16_t)(w & 0xffff)), hi = descr(2 * e2 + 1, (int)(int16_t)(w >> 16));
+                DSC2[e2] = ((uint32_t)lo & 0xffffu) | ((uint32_t)hi << 16);
+            }
+            if ((cb.n_e & 1) && tid == 0) DSC[cb.n_e - 1] = (int16_t)descr(cb.n_e - 1, llr[cb.n_e - 1]);
+        } else {
+            for (uint32_t e = tid; e < cb.n_e; e += nthr) DSC[e] = (int16_t)descr(e, llr[e]);
         }
+        if (single)
+            for (uint32_t e = cb.n_e + tid; e < N; e += nthr) DSC[e] = 0;
         __syncthreads();
     }
-    for (uint32_t n0 = tid; n0 < N; n0 += 4 * nthr) {
-        uint32_t e[4];
+    // four consecutive circular-buffer positions per thread: 8-byte table loads and soft-buffer stores (N is a
+    // multiple of 4 for every turbo block size, table and soft-buffer offsets are multiples of 4 elements)
+    const uint2* rm4 = reinterpret_cast<const uint2*>(rm_pos);
+    uint2* soft4 = reinterpret_cast<uint2*>(soft);
+    for (uint32_t q = tid; q < N / 4; q += nthr) {
+        const uint2 rp = rm4[q];
+        uint2 old = make_uint2(0u, 0u);
+        if (!reset) old = soft4[q];
+        const uint32_t pos[4] = {rp.x & 0xffffu, rp.x >> 16, rp.y & 0xffffu, rp.y >> 16};
+        const int prev[4] = {(int)(int16_t)(old.x & 0xffff), (int)(int16_t)(old.x >> 16), (int)(int16_t)(old.y & 0xffff),
+                             (int)(int16_t)(old.y >> 16)};
         int acc[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            const uint32_t n = n0 + u * nthr;
-            e[u] = 0xffffffffu;
-            acc[u] = 0;
-            if (n < N) {
-                uint32_t v = rm_pos[n] + N - rm_start;
-                e[u] = v >= N ? v - N : v;
-                if (!reset) acc[u] = soft[n];
-            }
-        }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            if (staged) {
-                for (uint32_t ee = e[u]; ee < cb.n_e; ee += N) acc[u] += DSC[ee];
+            const uint32_t v = pos[u] + N - rm_start;
+            acc[u] = prev[u];
+            if (single) {
+                acc[u] += DSC[v >= N ? v - N : v];
+            } else if (staged) {
+                for (uint32_t ee = v >= N ? v - N : v; ee < cb.n_e; ee += N) acc[u] += DSC[ee];
             } else {
-                for (uint32_t ee = e[u]; ee < cb.n_e; ee += N) {
-                    const uint32_t g = cb.rp + ee + p.gold_bit_off;
-                    const int v = llr[ee];
-                    acc[u] += ((p.gold[g >> 3] >> (7 - (g & 7))) & 1) ? -v : v;
-                }
+                for (uint32_t ee = v >= N ? v - N : v; ee < cb.n_e; ee += N) acc[u] += descr(ee, llr[ee]);
             }
         }
-#pragma unroll
-        for (int u = 0; u < 4; ++u) {
-            const uint32_t n = n0 + u * nthr;
-            if (n < N) soft[n] = (int16_t)acc[u];
-        }
+        soft4[q] = make_uint2(((uint32_t)acc[0] & 0xffffu) | ((uint32_t)acc[1] << 16),
+                              ((uint32_t)acc[2] & 0xffffu) | ((uint32_t)acc[3] << 16));
     }
 }
 
 cudaError_t launch_derm(const tdec_params_t& p, uint32_t n_packets, uint32_t max_n_e, cudaStream_t st) {
     // shared buffer for the largest code block's LLRs, at most 48 KB (no opt-in); larger ones gather from global
+    // (callers pass max(n_e, 3 (K + 4)) where that fits, so that the kernel's "single" path applies)
     const uint32_t cap = max_n_e < 24576u ? ((max_n_e + 7u) & ~7u) : 24576u;
     k_derm<<<dim3(p.C, n_packets), 256, (size_t)cap * 2, st>>>(p, cap);
     return cudaGetLastError();

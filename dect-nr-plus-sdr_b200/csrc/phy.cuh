@@ -162,6 +162,10 @@ struct sync_params_t {
     float* p_steps;                        // [packet][n_ant][n_steps]
     const float2* templates;               // [n_tpl][xc_S]
     uint32_t n_tpl;
+    // fast correlation (optional): FFT size >= lags + template length - 1, conj(FFT(template)) / N_fft, twiddles
+    uint32_t xc_fft_n;                     // 0: direct correlation
+    const float2* tpl_spec;                // [n_tpl][xc_fft_n]
+    const float2* xc_twiddle;              // [xc_fft_n]
     float2* xc;                            // [packet][n_tpl] (max abs(xcorr), lag)
     sync_result_dev_t* result;             // [packet]
     rx_state_t* rx_state;                  // [packet] optional: receives t0 / CFO / rms for the synced receiver

@@ -270,13 +270,16 @@ __global__ void __launch_bounds__(256) k_sync_steps(const sync_params_t p) {
     const float2* x = p.iq + ((size_t)pkt * p.d.N_RX + a) * p.iq_stride;
     const uint32_t pat = p.d.pat_len_os, m0 = j * p.step;
     float cr = 0.f, ci = 0.f, pw = 0.f;
-    for (uint32_t i = lane; i < p.step; i += 32) {
-        const float2 b = x[m0 + i];
-        pw += b.x * b.x + b.y * b.y;
+    // two samples per 16-byte load (steps, pattern length and window strides are even; windows are 16-byte aligned)
+    const float4* xb = reinterpret_cast<const float4*>(x + m0);
+    const float4* xe = reinterpret_cast<const float4*>(x + m0 - (m0 >= pat ? pat : 0));
+    for (uint32_t i = lane; i < p.step / 2; i += 32) {
+        const float4 b = xb[i];
+        pw += b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
         if (m0 >= pat) {
-            const float2 e = x[m0 + i - pat];
-            cr += e.x * b.x + e.y * b.y;
-            ci += e.y * b.x - e.x * b.y;
+            const float4 e = xe[i];
+            cr += e.x * b.x + e.y * b.y + e.z * b.z + e.w * b.w;
+            ci += e.y * b.x - e.x * b.y + e.w * b.z - e.z * b.w;
         }
     }
     cr = warp_sum(cr); ci = warp_sum(ci); pw = warp_sum(pw);
@@ -374,6 +377,75 @@ __global__ void __launch_bounds__(XC_THREADS) k_sync_xcorr(const sync_params_t p
     }
 }
 
+// ---- the same cross-correlation through the frequency domain: corr[j] = sum_i x[j + i] conj(t[i]) =
+// IFFT(FFT(x) . conj(FFT(t)))[j] for the lags j < n_lag when the FFT size covers lags + template length - 1 (no wrap
+// around).  One block per packet: one forward FFT of the CFO pre-rotated window, one inverse FFT per template.
+// 5 N log2 N flops per FFT instead of 8 n_lag S per template (14 x fewer for beta = 16).  The reference notes that
+// "frequency domain methods ... are not applicable" to its SIMD path (sync_param.hpp:283-285); on this hardware the
+// shared-memory FFT is the cheaper way to the same numbers (fp32 rounding differs, the arg max does not).
+constexpr uint32_t XF_THREADS = 256, XF_MAX_PER_THREAD = 16;
+
+__global__ void __launch_bounds__(XF_THREADS) k_sync_xcorr_fft(const sync_params_t p, uint32_t len) {
+    extern __shared__ float2 smem_f[];
+    __shared__ unsigned long long s_best;
+    const phy_dims_t& d = p.d;
+    const uint32_t pkt = blockIdx.x, tid = threadIdx.x, N = p.xc_fft_n;
+    const uint32_t S = p.xc_S, sl = p.xc_sl, n_lag = 2 * sl + 1, n_mix = n_lag + S - 1;
+    const sync_result_dev_t& res = p.result[pkt];
+    const long long w0 = (long long)res.coarse_peak_time_hw - sl;
+    if (!res.detected || w0 < 0 || w0 + n_mix > len) {
+        for (uint32_t t = tid; t < p.n_tpl; t += XF_THREADS) p.xc[(size_t)pkt * p.n_tpl + t] = make_float2(-1.f, 0.f);
+        return;
+    }
+    float2* A = smem_f;
+    float2* B = smem_f + N;
+    const float2* x = p.iq_x + ((size_t)pkt * d.N_RX + res.strongest_ant) * p.x_stride + w0;
+    const double inc = (double)((res.cfo_fractional_rad + res.cfo_integer_rad) * (float)p.rs_M / (float)p.rs_L);
+    for (uint32_t i = tid; i < N; i += XF_THREADS) {
+        float2 r = make_float2(0.f, 0.f);
+        if (i < n_mix) {
+            const float2 v = x[i];
+            double sd, cd;
+            sincos(inc * (double)i, &sd, &cd);
+            const float cs = (float)cd, sn = (float)sd;
+            r = make_float2(v.x * cs - v.y * sn, v.x * sn + v.y * cs);
+        }
+        A[i] = r;
+    }
+    const float2* X = block_fft<false>(A, B, N, p.xc_twiddle);
+    float2 Xr[XF_MAX_PER_THREAD];
+#pragma unroll
+    for (uint32_t r = 0; r < XF_MAX_PER_THREAD; ++r) {
+        const uint32_t k = tid + r * XF_THREADS;
+        Xr[r] = k < N ? X[k] : make_float2(0.f, 0.f);
+    }
+    for (uint32_t t = 0; t < p.n_tpl; ++t) {
+        const float2* T = p.tpl_spec + (size_t)t * N;
+        __syncthreads();
+        if (tid == 0) s_best = 0ull;
+#pragma unroll
+        for (uint32_t r = 0; r < XF_MAX_PER_THREAD; ++r) {
+            const uint32_t k = tid + r * XF_THREADS;
+            if (k < N) A[k] = cmul(Xr[r], T[k]);
+        }
+        const float2* c = block_fft<true>(A, B, N, p.xc_twiddle);
+        unsigned long long mine = 0ull;
+        for (uint32_t j = tid; j < n_lag; j += XF_THREADS) {
+            const float2 v = c[j];
+            const float m2 = v.x * v.x + v.y * v.y;
+            const unsigned long long key = ((unsigned long long)__float_as_uint(m2) << 32) | (0xffffffffu - j);
+            if (key > mine) mine = key;
+        }
+        atomicMax(&s_best, mine);
+        __syncthreads();
+        if (tid == 0) {
+            const unsigned long long bk = s_best;
+            p.xc[(size_t)pkt * p.n_tpl + t] =
+                make_float2(sqrtf(__uint_as_float((uint32_t)(bk >> 32))), (float)(0xffffffffu - (uint32_t)bk));
+        }
+    }
+}
+
 // ---- N_eff_TX decision, fine peak, hand-over to the synchronised receiver (crosscorrelator.cpp:205-249)
 __global__ void k_sync_final(const sync_params_t p, uint32_t n, uint32_t len) {
     const uint32_t pkt = blockIdx.x * blockDim.x + threadIdx.x;
@@ -421,6 +493,14 @@ cudaError_t launch_sync(const sync_params_t& p, uint32_t n, cudaStream_t st) {
     cudaError_t e = cudaFuncSetAttribute(k_sync_peak, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
     if (e != cudaSuccess) return e;
     k_sync_peak<<<n, 256, sm2, st>>>(p, len);
+    if (p.xc_fft_n) {
+        const size_t smf = 2 * (size_t)p.xc_fft_n * sizeof(float2);
+        e = cudaFuncSetAttribute(k_sync_xcorr_fft, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smf);
+        if (e != cudaSuccess) return e;
+        k_sync_xcorr_fft<<<n, XF_THREADS, smf, st>>>(p, p.x_len);
+        k_sync_final<<<(n + 127) / 128, 128, 0, st>>>(p, n, len);
+        return cudaGetLastError();
+    }
     const uint32_t n_lag = 2 * p.xc_sl + 1, LT = (n_lag + XC_LAGS - 1) / XC_LAGS, n_lag_pad = LT * XC_LAGS;
     uint32_t IC = XC_THREADS / LT;
     const uint32_t ic_max = p.xc_S / 32 ? p.xc_S / 32 : 1;

@@ -205,6 +205,41 @@ int build_phy_plan(dnrp_ctx* c) {
             }
         }
         UP(c->d_sync_tpl.upload(tpl));
+        {
+            // fast cross-correlation: smallest FFT size 2^a or 3 * 2^a (the sizes fft.cuh handles in one block) that
+            // covers lags + template length - 1; spectra by a direct DFT in double (init time only)
+            const uint32_t S = c->stf_len_rs;
+            const uint32_t sl = (uint32_t)((uint64_t)d.pat_len_os * c->cfg.resample_L / c->cfg.resample_M);
+            const uint32_t need = 2 * sl + 1 + S - 1;
+            uint32_t N = 0;
+            for (uint32_t cand = 64; cand <= 4096 && !N; cand *= 2) {
+                if (cand >= need) N = cand;
+                else if (cand / 2 * 3 >= need && cand / 2 * 3 <= 4096 && cand / 2 * 3 < cand * 2) N = cand / 2 * 3;
+            }
+            c->sync_fft_n = N;
+            if (N) {
+                std::vector<float2> twx(N), spec((size_t)c->sync_n_tpl * N);
+                std::vector<double> cs(N), sn(N);
+                for (uint32_t k = 0; k < N; ++k) {
+                    const double a = -2.0 * pi * (double)k / (double)N;
+                    cs[k] = std::cos(a); sn[k] = std::sin(a);
+                    twx[k] = make_float2((float)cs[k], (float)sn[k]);
+                }
+                for (uint32_t t = 0; t < c->sync_n_tpl; ++t)
+                    for (uint32_t k = 0; k < N; ++k) {
+                        double re = 0.0, im = 0.0;
+                        for (uint32_t i = 0; i < S; ++i) {
+                            const uint32_t m = (uint32_t)(((uint64_t)k * i) % N);
+                            const float2 v = tpl[(size_t)t * S + i];
+                            re += v.x * cs[m] - v.y * sn[m];
+                            im += v.x * sn[m] + v.y * cs[m];
+                        }
+                        spec[(size_t)t * N + k] = make_float2((float)(re / N), (float)(-im / N));   // conj / N
+                    }
+                UP(c->d_sync_tw.upload(twx));
+                UP(c->d_sync_tpl_spec.upload(spec));
+            }
+        }
         c->sync_step = d.pat_len_os / 4;
         c->sync_n_steps = c->sync_len / c->sync_step;
         const size_t nb = (size_t)c->B * d.N_RX * c->sync_n_steps;
