@@ -2,6 +2,7 @@
 // decode + CRC in ONE kernel per batch (grid = code blocks x packets), then a small per-packet kernel
 // for the transport-block level CRC logic.  Reference: lib/src/phy/fec/pdc_enc.cpp:291-492,
 // lib/src/phy/fec/pcc_enc.cpp:215-364 (file:line relative to /root/reference).
+#include <type_traits>
 #include "fec_rx.cuh"
 #include "turbo_dec.cuh"
 
@@ -114,7 +115,7 @@ cudaError_t launch_derm(const tdec_params_t& p, uint32_t n_packets, uint32_t max
 // Small ones (PLCF, K < ~2000: fewer than 32 window pairs): tg is a power of two <= 32 and many items
 // share a block, all groups moving through the same barriers in lockstep.
 template <bool GROUPED>
-__global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p, uint32_t tg, uint32_t smem_item_words,
+__global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_decode(const tdec_params_t p, uint32_t tg, uint32_t smem_item_words,
                                                       uint32_t n_items) {
     extern __shared__ uint32_t smem_all[];
     __shared__ uint32_t s_crc_all[128];
@@ -334,9 +335,12 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p, uin
                 uint32_t pi = (uint32_t)(((uint64_t)cb.f1 * j0 + (uint64_t)cb.f2 * j0 * j0) % K);
                 uint32_t g = (uint32_t)((cb.f1 + (uint64_t)cb.f2 * (2 * j0 + 1)) % K);
                 const uint32_t g2 = (2 * cb.f2) % K;
-                for (uint32_t c = 0; c < nck; ++c) {
+                // one chunk of S_CK steps; FULL = compile-time knowledge that the chunk is complete (always the case when
+                // L is a multiple of S_CK, e.g. L = 32): no per-step bounds predicates in the unrolled body
+                auto chunk = [&](uint32_t c, auto full_tag) {
+                    constexpr bool FULL = decltype(full_tag)::value;
                     const int k0 = c * S_CK;
-                    const int n = min((int)S_CK, (int)L - k0);
+                    const int n = FULL ? (int)S_CK : min((int)S_CK, (int)L - k0);
                     uint32_t bb[S_CK][8], xs[S_CK], ys[S_CK];
 #pragma unroll
                     for (int i = 0; i < S_CK; ++i) {
@@ -381,7 +385,11 @@ __global__ void __launch_bounds__(128) k_turbo_decode(const tdec_params_t p, uin
                             alpha_step(a, x, y);
                         }
                     }
-                }
+                };
+                const uint32_t n_full = L / S_CK;
+#pragma unroll 1
+                for (uint32_t c = 0; c < n_full; ++c) chunk(c, std::true_type{});
+                if (n_full < nck) chunk(n_full, std::false_type{});
 #pragma unroll
                 for (int s = 0; s < 8; ++s) ae_new[s] = a[s];
             }
