@@ -100,7 +100,8 @@ int dnrp_ctx_create(const dnrp_config_t* cfg, int device, dnrp_ctx_t** out) {
     if (!spec::get_packet_sizes(d, c->ps)) return fail(DNRP_ERR_INVALID, "packet configuration not possible");
     if ((rc = build_fec_plan(c->ps, c->fec)) != DNRP_OK) return fail(rc, "FEC plan failed");
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
-        cudaStreamCreateWithFlags(&c->stream_copy, cudaStreamNonBlocking) != cudaSuccess)
+        cudaStreamCreateWithFlags(&c->stream_copy, cudaStreamNonBlocking) != cudaSuccess ||
+        cudaStreamCreateWithFlags(&c->stream_d2h, cudaStreamNonBlocking) != cudaSuccess)
         return fail(DNRP_ERR_CUDA, "cudaStreamCreate failed");
 
     const fec_plan_t& f = c->fec;
@@ -150,7 +151,9 @@ void dnrp_ctx_destroy(dnrp_ctx_t* ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     if (ctx->stream_copy) cudaStreamDestroy(ctx->stream_copy);
+    if (ctx->stream_d2h) cudaStreamDestroy(ctx->stream_d2h);
     for (cudaEvent_t e : ctx->chunk_events) cudaEventDestroy(e);
+    for (cudaEvent_t e : ctx->chunk_done) cudaEventDestroy(e);
     for (auto& t : ctx->ktimer)
         for (cudaEvent_t e : t.ev) cudaEventDestroy(e);
     delete ctx;

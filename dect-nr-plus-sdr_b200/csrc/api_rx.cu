@@ -2,6 +2,7 @@
 // (reference lib/src/phy/rx/rx_synced/rx_synced.cpp:186-436) on the context's device buffers.
 #include <algorithm>
 #include <cmath>
+#include <cstdlib>
 #include <cstring>
 #include "ctx.hpp"
 #include "spec_channel.hpp"
@@ -173,13 +174,15 @@ int fetch_pcc_reports(dnrp_ctx* c, uint32_t n, dnrp_pcc_report_t* out) {
 }
 
 // device -> host: transport blocks and reports of the PDC stage for packets [0, n)
-int fetch_pdc_reports(dnrp_ctx* c, uint32_t n, uint8_t* tb_out, dnrp_pdc_report_t* out, uint8_t* n_iter) {
+int fetch_pdc_reports(dnrp_ctx* c, uint32_t n, uint8_t* tb_out, dnrp_pdc_report_t* out, uint8_t* n_iter,
+                      bool tb_already_copied) {
     const fec_plan_t& f = c->fec;
     std::vector<uint8_t> ok(n);
     std::vector<mimo_report_dev_t> mimo(n);
     DNRP_CUDA(cudaMemcpyAsync(mimo.data(), c->d_mimo.p, n * sizeof(mimo_report_dev_t), cudaMemcpyDeviceToHost, c->stream));
-    DNRP_CUDA(cudaMemcpy2DAsync(tb_out, c->ps.N_TB_byte, c->d_tb_out.p, f.tb_stride, c->ps.N_TB_byte, n,
-                                cudaMemcpyDeviceToHost, c->stream));
+    if (!tb_already_copied)
+        DNRP_CUDA(cudaMemcpy2DAsync(tb_out, c->ps.N_TB_byte, c->d_tb_out.p, f.tb_stride, c->ps.N_TB_byte, n,
+                                    cudaMemcpyDeviceToHost, c->stream));
     DNRP_CUDA(cudaMemcpyAsync(ok.data(), c->d_tb_ok.p, n, cudaMemcpyDeviceToHost, c->stream));
     if (n_iter) DNRP_CUDA(cudaMemcpyAsync(n_iter, c->d_n_iter.p, (size_t)n * c->ps.C, cudaMemcpyDeviceToHost, c->stream));
     DNRP_CUDA(cudaStreamSynchronize(c->stream));
@@ -275,12 +278,16 @@ int dnrp_rx_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, uint32_t 
     if (rv) DNRP_CUDA(cudaMemcpyAsync(c->d_rv.p, rv, n, cudaMemcpyHostToDevice, c->stream));
     if (harq_reset) DNRP_CUDA(cudaMemcpyAsync(c->d_reset.p, harq_reset, n, cudaMemcpyHostToDevice, c->stream));
     // chunks: the H2D copy of chunk k+1 runs on the copy stream while chunk k is processed on the compute stream
-    const uint32_t n_chunks = n >= 2048 ? 8 : (n >= 256 ? 4 : 1);
+    const char* env_chunks = std::getenv("DNRP_RX_CHUNKS");   // tuning knob, default below
+    uint32_t n_chunks = n >= 8192 ? 16 : (n >= 2048 ? 8 : (n >= 256 ? 4 : 1));
+    if (env_chunks && std::atoi(env_chunks) > 0) n_chunks = std::min<uint32_t>((uint32_t)std::atoi(env_chunks), n);
     const uint32_t per = (n + n_chunks - 1) / n_chunks;
     while (c->chunk_events.size() < n_chunks) {
-        cudaEvent_t e;
+        cudaEvent_t e, g;
         DNRP_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+        DNRP_CUDA(cudaEventCreateWithFlags(&g, cudaEventDisableTiming));
         c->chunk_events.push_back(e);
+        c->chunk_done.push_back(g);
     }
     const size_t win = (size_t)d.N_RX * c->rx_stride;
     for (uint32_t k = 0; k < n_chunks; ++k) {
@@ -300,6 +307,14 @@ int dnrp_rx_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, uint32_t 
         if (rc == DNRP_OK) rc = run_rx_front(c, m);
         if (rc == DNRP_OK) rc = run_rx_pcc(c, m);
         if (rc == DNRP_OK) rc = run_rx_pdc(c, m, harq_slot != nullptr, rv != nullptr, harq_reset != nullptr);
+        if (rc == DNRP_OK) {
+            // this chunk's transport blocks travel back while the next chunk is processed
+            DNRP_CUDA(cudaEventRecord(c->chunk_done[k], c->stream));
+            DNRP_CUDA(cudaStreamWaitEvent(c->stream_d2h, c->chunk_done[k], 0));
+            DNRP_CUDA(cudaMemcpy2DAsync(tb_out + (size_t)o * c->ps.N_TB_byte, c->ps.N_TB_byte,
+                                        c->d_tb_out.p + (size_t)o * c->fec.tb_stride, c->fec.tb_stride, c->ps.N_TB_byte, m,
+                                        cudaMemcpyDeviceToHost, c->stream_d2h));
+        }
     }
     c->off = 0;
     if (rc) return rc;
@@ -309,7 +324,9 @@ int dnrp_rx_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, uint32_t 
     std::vector<dnrp_pcc_report_t> pcc_tmp;
     if (!pcc_out) { pcc_tmp.resize(n); pcc_out = pcc_tmp.data(); }   // also refreshes h_rx_state for the PDC reports
     if ((rc = fetch_pcc_reports(c, n, pcc_out)) != DNRP_OK) return rc;
-    return fetch_pdc_reports(c, n, tb_out, pdc_out, n_iter);
+    rc = fetch_pdc_reports(c, n, tb_out, pdc_out, n_iter, true);
+    DNRP_CUDA(cudaStreamSynchronize(c->stream_d2h));
+    return rc;
 }
 
 static bool tap_desc(const dnrp_ctx_t* c, int tap, uint32_t n, const void*& src, size_t& bytes) {

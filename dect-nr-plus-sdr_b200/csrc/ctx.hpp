@@ -90,7 +90,8 @@ struct dnrp_ctx {
     uint32_t B = 0;  // max batch
     uint32_t off = 0;  // first packet the run_* stage functions work on (pipelined host calls process chunk by chunk)
     cudaStream_t stream_copy = nullptr;      // H2D copies of the pipelined receive call
-    std::vector<cudaEvent_t> chunk_events;
+    cudaStream_t stream_d2h = nullptr;       // transport blocks of finished chunks back to the host
+    std::vector<cudaEvent_t> chunk_events, chunk_done;
 
     dnrp::fec_plan_t fec;
     // device tables
@@ -208,6 +209,7 @@ int run_rx_pdc(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, bool have_
 int run_channel(dnrp_ctx* c, uint32_t n);
 int run_sync(dnrp_ctx* c, uint32_t n, uint32_t search_length, bool hand_over);
 int fetch_pcc_reports(dnrp_ctx* c, uint32_t n, dnrp_pcc_report_t* out);
-int fetch_pdc_reports(dnrp_ctx* c, uint32_t n, uint8_t* tb_out, dnrp_pdc_report_t* out, uint8_t* n_iter);
+int fetch_pdc_reports(dnrp_ctx* c, uint32_t n, uint8_t* tb_out, dnrp_pdc_report_t* out, uint8_t* n_iter,
+                      bool tb_already_copied = false);
 int run_rx_resample(dnrp_ctx* c, uint32_t n);          // hardware rate -> DECT rate from each packet's fine peak
 }  // namespace dnrp
