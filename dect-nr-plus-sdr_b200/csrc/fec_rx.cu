@@ -295,13 +295,24 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
                     const uint32_t* pxb = Xn + (size_t)(L - 1) * T;
                     const uint32_t* pyb = Yn + (size_t)(L - 1) * T;
                     uint32_t xb = *pxb, yb = *pyb, xa = *Xp, ya = *Yp;
-                    for (uint32_t i = 0; i < L; ++i) {
+                    // three steps without normalisation, the fourth with (turbo_dec.cuh: overflow bound); a remainder
+                    // of L % 4 steps is normalised every step, so the pass always ends normalised
+                    auto train_step = [&](auto norm_tag) {
+                        constexpr bool NORM = decltype(norm_tag)::value;
                         pxb -= T; pyb -= T; Xp += T; Yp += T;
                         const uint32_t xb_n = *pxb, yb_n = *pyb, xa_n = *Xp, ya_n = *Yp;
-                        beta_step(b, xb >> shn, yb >> shn);
-                        alpha_step(a, xa << shp, ya << shp);
+                        beta_step<NORM>(b, xb >> shn, yb >> shn);
+                        alpha_step<NORM>(a, xa << shp, ya << shp);
                         xb = xb_n; yb = yb_n; xa = xa_n; ya = ya_n;
+                    };
+                    uint32_t i = 0;
+#pragma unroll 1
+                    for (; i + 4 <= L; i += 4) {
+                        train_step(std::false_type{}); train_step(std::false_type{}); train_step(std::false_type{});
+                        train_step(std::true_type{});
                     }
+#pragma unroll 1
+                    for (; i < L; ++i) train_step(std::true_type{});
                     if (wh == P - 1) {
 #pragma unroll
                         for (int s = 0; s < 8; ++s) b[s] = (b[s] & 0xffffu) | ((uint32_t)tail[s] << 16);
@@ -316,7 +327,10 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
                     const uint32_t* X = XIN + t + (size_t)(L - 1) * T;
                     const uint32_t* Y = PAR + t + (size_t)(L - 1) * T;
                     uint32_t x = *X, y = *Y;
-                    for (int k = (int)L - 1; k >= 0; --k) {
+                    // normalised after the steps k with k % 4 == 0: every checkpoint ((k + 1) % S_CK == 0) and the final
+                    // metrics are normalised values, at most three steps in a row are not
+                    auto back_step = [&](int k, auto norm_tag) {
+                        constexpr bool NORM = decltype(norm_tag)::value;
                         X -= T; Y -= T;  // last prefetch: one row below, inside EXT / XIN, unused
                         const uint32_t x_n = *X, y_n = *Y;
                         if (((k + 1) % S_CK) == 0 || k + 1 == (int)L) {
@@ -324,8 +338,16 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
 #pragma unroll
                             for (int s = 1; s < 8; ++s) CK[(c * 7 + s - 1) * T + t] = b[s];
                         }
-                        beta_step(b, x, y);
+                        beta_step<NORM>(b, x, y);
                         x = x_n; y = y_n;
+                    };
+                    int k = (int)L - 1;
+#pragma unroll 1
+                    for (; (k & 3) != 3 && k >= 0; --k) back_step(k, std::true_type{});
+#pragma unroll 1
+                    for (; k >= 3; k -= 4) {
+                        back_step(k, std::false_type{}); back_step(k - 1, std::false_type{});
+                        back_step(k - 2, std::false_type{}); back_step(k - 3, std::true_type{});
                     }
                 }
 #pragma unroll

@@ -56,7 +56,13 @@ __device__ __forceinline__ uint32_t vclamp(uint32_t a, int lim) {
 __device__ __forceinline__ uint32_t swap16(uint32_t a) { return __byte_perm(a, 0, 0x1032); }
 __device__ __forceinline__ uint32_t pack(int lo, int hi) { return ((uint32_t)lo & 0xffff) | ((uint32_t)hi << 16); }
 
-// one backward step: b[] <- beta at the previous trellis time, normalised to state 0
+// one backward step: b[] <- beta at the previous trellis time, normalised to state 0 (NORM) or left as computed.
+// Normalisation only shifts all eight metrics alike, so skipping it changes no decision and no stored (normalised)
+// value as long as nothing overflows: normalised metrics lie within +-12.3k (three steps connect any two states,
+// |gamma| <= 4093), each un-normalised step moves them by at most 4093, so three un-normalised steps followed by a
+// normalised one stay below 12.3k + 4 * 4.1k = 28.7k < 2^15.  Used in the training and plain backward passes
+// (shorter dependency chains); every step that feeds an LLR is normalised.
+template <bool NORM = true>
 __device__ __forceinline__ void beta_step(uint32_t (&b)[8], uint32_t x, uint32_t y) {
     const uint32_t xy = vadd(x, y);
     uint32_t n[8];
@@ -68,12 +74,18 @@ __device__ __forceinline__ void beta_step(uint32_t (&b)[8], uint32_t x, uint32_t
     n[5] = vaddmax(b[6], y, vadd(b[2], x));      // u0->S6 (y) | u1->S2 (x)
     n[6] = vaddmax(b[3], xy, b[7]);              // u0->S7 (0) | u1->S3 (x+y)
     n[7] = vaddmax(b[7], xy, b[3]);              // u0->S3 (0) | u1->S7 (x+y)
-    b[0] = 0;
+    if (NORM) {
+        b[0] = 0;
 #pragma unroll
-    for (int s = 1; s < 8; ++s) b[s] = vsub(n[s], n[0]);
+        for (int s = 1; s < 8; ++s) b[s] = vsub(n[s], n[0]);
+    } else {
+#pragma unroll
+        for (int s = 0; s < 8; ++s) b[s] = n[s];
+    }
 }
 
 // one forward step: a[] <- alpha at the next trellis time, normalised to state 0
+template <bool NORM = true>
 __device__ __forceinline__ void alpha_step(uint32_t (&a)[8], uint32_t x, uint32_t y) {
     const uint32_t xy = vadd(x, y);
     uint32_t n[8];
@@ -85,9 +97,14 @@ __device__ __forceinline__ void alpha_step(uint32_t (&a)[8], uint32_t x, uint32_
     n[6] = vaddmax(a[5], y, vadd(a[4], x));
     n[7] = vaddmax(a[7], xy, a[6]);
     n[3] = vaddmax(a[6], xy, a[7]);
-    a[0] = 0;
+    if (NORM) {
+        a[0] = 0;
 #pragma unroll
-    for (int s = 1; s < 8; ++s) a[s] = vsub(n[s], n[0]);
+        for (int s = 1; s < 8; ++s) a[s] = vsub(n[s], n[0]);
+    } else {
+#pragma unroll
+        for (int s = 0; s < 8; ++s) a[s] = n[s];
+    }
 }
 
 // a-posteriori LLR of the step with alpha a[] (before), beta bn[] (after)

@@ -195,6 +195,13 @@ void orc_tdec_new_cb(tdec_t* t, const int16_t* soft, uint32_t K, uint32_t f1, ui
     t->range_violations = 0;
 }
 
+/* Normalisation schedule of the product kernel (csrc/fec_rx.cu k_turbo_decode): in the training passes and the
+ * plain backward pass the metrics are normalised to state 0 only every fourth step (and on every step of the
+ * L % 4 remainder).  Normalisation shifts all eight metrics alike, so the schedule changes no decision and no
+ * stored value; it is restated here so that chk() proves the 16-bit range of the un-normalised values too. */
+static inline int norm_train(uint32_t i, uint32_t L) { return (i & 3) == 3 || i >= (L & ~3u); }
+static inline int norm_back(uint32_t k, uint32_t L) { return (k & 3) == 0 || k >= (L & ~3u); }
+
 /* one constituent decoder over all windows; x = sys + a-priori (decoder order), y = parity;
  * writes llr (decoder order) */
 static void map_half(tdec_t* t, int dec, const int16_t* x, const int16_t* y, const int16_t* xt,
@@ -235,7 +242,9 @@ static void map_half(tdec_t* t, int dec, const int16_t* x, const int16_t* y, con
                     int32_t m1 = chk(t, b[S1] + xx + z1 * yy);
                     nb[S] = m0 > m1 ? m0 : m1;
                 }
-                for (int S = 0; S < 8; ++S) b[S] = chk(t, nb[S] - nb[0]);
+                const uint32_t i = L - 1 - (uint32_t)k;
+                const int32_t ref = norm_train(i, L) ? nb[0] : 0;
+                for (int S = 0; S < 8; ++S) b[S] = chk(t, nb[S] - ref);
             }
         }
         for (int S = 0; S < 8; ++S) beta[L][S] = (int16_t)b[S];
@@ -249,7 +258,10 @@ static void map_half(tdec_t* t, int dec, const int16_t* x, const int16_t* y, con
                 int32_t m1 = chk(t, b[S1] + xx + z1 * yy);
                 nb[S] = m0 > m1 ? m0 : m1;
             }
-            for (int S = 0; S < 8; ++S) { b[S] = chk(t, nb[S] - nb[0]); beta[k][S] = (int16_t)b[S]; }
+            /* beta[k] holds the normalised metrics (the product recomputes them, normalised, from normalised
+             * checkpoints); the running b[] follows the product's schedule for the range proof */
+            const int32_t ref = norm_back((uint32_t)k, L) ? nb[0] : 0;
+            for (int S = 0; S < 8; ++S) { b[S] = chk(t, nb[S] - ref); beta[k][S] = (int16_t)chk(t, nb[S] - nb[0]); }
         }
         for (int S = 0; S < 8; ++S) b_start_new[w][S] = (int16_t)b[S];
         /* ---- alpha initialisation: exact at the trellis start, otherwise a training pass over
@@ -269,7 +281,8 @@ static void map_half(tdec_t* t, int dec, const int16_t* x, const int16_t* y, con
                         int32_t g = chk(t, a[S] + u * xx + z * yy);
                         if (g > na[Sn]) na[Sn] = g;
                     }
-                for (int S = 0; S < 8; ++S) a[S] = chk(t, na[S] - na[0]);
+                const int32_t ref = norm_train(k, L) ? na[0] : 0;
+                for (int S = 0; S < 8; ++S) a[S] = chk(t, na[S] - ref);
             }
         }
         /* ---- forward recursion + LLR */

@@ -13,7 +13,7 @@ rng = np.random.default_rng(1)
 tb = rng.integers(0, 256, (P, phy.ps["N_TB_byte"]), dtype=np.uint8)
 plcf = rng.integers(0, 256, (P, 10), dtype=np.uint8)
 phy.tx(plcf, tb, fetch=False)
-t0 = rng.integers(64, 3000, P).astype(np.uint32)
+t0 = rng.integers(512, 3000, P).astype(np.uint32)
 phy.channel(P, snr_dB=25.0, t0=t0, mode=0, seed=3)
 for _ in range(2):
     ms = phy.time_stage(product.STAGE_SYNC_RX_CHAIN, P, reps=1)

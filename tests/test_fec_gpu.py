@@ -69,6 +69,27 @@ def test_decode_tb_bit_exact(product, name, snrs):
     phy.close()
 
 
+@pytest.mark.parametrize("name", ["C2_b16_siso_mcs7", "small_b2_mcs4"])
+def test_decode_tb_saturated_llrs_bit_exact(product, name):
+    """worst case for the path-metric range (the decoder normalises only every fourth step in its training and
+    backward passes): saturated LLRs with random / constant / alternating signs -- hard decisions, CRC outcome and
+    iteration counts still equal the oracle's, whose 32-bit arithmetic range-checks every value"""
+    cfg = CONFIGS[name]
+    ps = spec.get_packet_sizes(*cfg)
+    gold = fec.pdc_gold(NET, 1, ps["G"])
+    rng = np.random.default_rng(13)
+    G = ps["G"]
+    pats = [rng.choice([-1023, 1023], G), np.full(G, 1023), np.full(G, -1023), np.where(np.arange(G) % 2, 1023, -1023),
+            rng.integers(-1023, 1024, G), rng.choice([-32767, 32767], G)]
+    llr = np.stack(pats).astype(np.int16)
+    phy = product.Phy(cfg, max_batch=len(pats), network_id=NET, plcf_type=1)
+    ok, out, nit = phy.fec_decode_tb(llr)
+    for i in range(len(pats)):
+        rok, rout, rnit = fec.pdc_decode(llr[i], ps, 0, gold)
+        assert bool(ok[i]) == rok and (nit[i] == rnit).all() and (out[i] == rout).all(), (name, i)
+    phy.close()
+
+
 def test_decode_tb_harq_combining_bit_exact(product):
     cfg = CONFIGS["C2_b16_siso_mcs7"]
     ps = spec.get_packet_sizes(*cfg)

@@ -106,19 +106,24 @@ def test_plcf_chain_roundtrip_all_masks():
 
 
 def test_decoder_int16_range_never_violated():
-    import ctypes as C
+    """the decoder's int16 metric contract, including the product's normalise-every-4th-step schedule in the
+    training / backward passes (oracle/fec.c norm_train, norm_back): no value leaves 16 bits, even for saturated
+    and adversarial inputs, and for window lengths with L % 4 != 0"""
     L = fec._L()
     rng = np.random.default_rng(5)
-    K = 6144
-    f1, f2 = spec.QPP_F1F2[spec.TC_CB_SIZES.index(K)]
     t = L.orc_tdec_alloc()
-    bits = np.zeros(K, dtype=np.uint8)
-    for amp in (50, 1000, 32767):
-        soft = rng.integers(-amp, amp + 1, 3 * (K + 4)).astype(np.int16)
-        L.orc_tdec_new_cb(t, soft, K, f1, f2)
-        for _ in range(4):
-            L.orc_tdec_iteration(t, bits)
-        assert L.orc_tdec_range_violations(t) == 0
+    for K in (40, 72, 1056, 6144):
+        f1, f2 = spec.QPP_F1F2[spec.TC_CB_SIZES.index(K)]
+        bits = np.zeros(K, dtype=np.uint8)
+        n = 3 * (K + 4)
+        pats = [rng.integers(-a, a + 1, n) for a in (50, 1000, 32767)]
+        pats += [rng.choice([-32767, 32767], n), np.full(n, 32767), np.full(n, -32767),
+                 np.where(np.arange(n) % 2, 32767, -32767), np.where(np.arange(n) % 3 == 0, 32767, -32767)]
+        for soft in pats:
+            L.orc_tdec_new_cb(t, np.ascontiguousarray(soft, dtype=np.int16), K, f1, f2)
+            for _ in range(4):
+                L.orc_tdec_iteration(t, bits)
+            assert L.orc_tdec_range_violations(t) == 0, K
     L.orc_tdec_free(t)
 
 
