@@ -299,10 +299,13 @@ def run_b200(args):
         peak, peak_src = 6500.0, "fallback"
     k_ms_per_launch = k_ms / max(k_cnt, 1)
     achieved = alg_bytes * P / (k_ms_per_launch * 1e-3) / 1e9 if k_cnt else None
-    traffic = None
+    traffic, traffic_src = None, None
     tpath = os.path.join(ROOT, "profiles", "turbo_decode_traffic.json")
     if os.path.exists(tpath):
-        traffic = json.load(open(tpath)).get(args.workload)
+        t = json.load(open(tpath)).get(args.workload)
+        if t:  # ncu capture of a smaller launch, scaled linearly to this launch's packets (the kernel is per-packet)
+            traffic = t["dram_bytes_per_launch"] / t["packets_per_launch"] * P
+            traffic_src = "%s, scaled from %d to %d packets per launch" % (t["source"], t["packets_per_launch"], P)
 
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
@@ -335,7 +338,8 @@ def run_b200(args):
                 "ms_per_step": e2e_ms_max},
         "gpu_launches": int(launches),
         "roofline": {"bound": "hbm", "kernel": "k_turbo_decode", "achieved": achieved, "peak": peak, "unit": "GB/s",
-                     "frac": (achieved / peak) if achieved else None, "traffic": traffic, "peak_source": peak_src,
+                     "frac": (achieved / peak) if achieved else None, "traffic": traffic, "traffic_source": traffic_src,
+                     "peak_source": peak_src,
                      "alg_bytes_per_packet": alg_bytes, "ms_per_launch": k_ms_per_launch, "launches": k_cnt,
                      "share_of_step": k_ms_per_launch / ms_step_max if ms_step_max else None,
                      "note": "compute/shared-memory bound kernel: see profiles/ for issue-slot utilisation",
