@@ -8,7 +8,7 @@
  *   lib/include/dectnrp/phy/rx/sync/sync_param.hpp (constants as shipped, cover sequence active)
  * PARITY UNPINNED: the reference cannot be built here and ships no vectors for this path.
  * Not restated: the periodic "resum for numerical stability" (float drift control, no effect on the algorithm),
- * resampling (L = M = 1 only), beta / integer CFO search (disabled or unimplemented in the reference).
+ * resampling: see orc_sync_search2 (detection/coarse on the M/L-resampled window, xcorr at the hardware rate), beta / integer CFO search (disabled or unimplemented in the reference).
  */
 #include <math.h>
 #include <stdint.h>
