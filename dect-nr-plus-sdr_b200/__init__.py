@@ -295,11 +295,15 @@ class Phy:
         return out["crc_ok"].astype(bool), tb, out["snr_dB"].copy(), nit
 
     def rx(self, iq, harq_slot=None, rv=None, harq_reset=None, tb_out=None, search_length=0, want_sync=True,
-           want_pcc=True):
+           want_pcc=True, sc16_scale=1.0 / 32768.0):
         """dnrp_rx_batch: host IQ windows -> (sync results, PCC reports, crc_ok, transport blocks, PDC reports), copies
         pipelined against the kernels"""
         n = iq.shape[0]
-        assert iq.dtype == np.complex64 and iq.flags["C_CONTIGUOUS"] and iq.shape[1:] == (self.N_RX, self.rx_stride())
+        sc16 = iq.dtype == np.int16   # [n][N_RX][rx_stride][2] int16 I/Q: dnrp_rx_batch_sc16
+        if sc16:
+            assert iq.flags["C_CONTIGUOUS"] and iq.shape[1:] == (self.N_RX, self.rx_stride(), 2)
+        else:
+            assert iq.dtype == np.complex64 and iq.flags["C_CONTIGUOUS"] and iq.shape[1:] == (self.N_RX, self.rx_stride())
         tb = np.zeros((n, self.ps["N_TB_byte"]), dtype=np.uint8) if tb_out is None else tb_out
         slot = None if harq_slot is None else np.ascontiguousarray(harq_slot, dtype=np.uint32)
         rvv = None if rv is None else np.ascontiguousarray(rv, dtype=np.uint8)
@@ -307,11 +311,14 @@ class Phy:
         sres = np.zeros(n, dtype=SYNC_RESULT_DTYPE).view(np.recarray) if want_sync else None
         pcc = np.zeros(n, dtype=PCC_DTYPE).view(np.recarray) if want_pcc else None
         pdc = np.zeros(n, dtype=PDC_DTYPE).view(np.recarray)
-        _check(lib().dnrp_rx_batch(self._ctx, n, _ptr(iq, np.complex64), int(search_length), _ptr(slot, np.uint32),
-                                   _ptr(rvv, np.uint8), _ptr(rst, np.uint8),
-                                   None if sres is None else sres.ctypes.data_as(C.c_void_p),
-                                   None if pcc is None else pcc.ctypes.data_as(C.c_void_p), _ptr(tb, np.uint8),
-                                   pdc.ctypes.data_as(C.c_void_p), None))
+        tail = (int(search_length), _ptr(slot, np.uint32), _ptr(rvv, np.uint8), _ptr(rst, np.uint8),
+                None if sres is None else sres.ctypes.data_as(C.c_void_p),
+                None if pcc is None else pcc.ctypes.data_as(C.c_void_p), _ptr(tb, np.uint8),
+                pdc.ctypes.data_as(C.c_void_p), None)
+        if sc16:
+            _check(lib().dnrp_rx_batch_sc16(self._ctx, n, iq.ctypes.data_as(C.c_void_p), C.c_float(sc16_scale), *tail))
+        else:
+            _check(lib().dnrp_rx_batch(self._ctx, n, _ptr(iq, np.complex64), *tail))
         self.last_pdc_report = pdc
         return sres, pcc, pdc.crc_ok.astype(bool), tb, pdc
 

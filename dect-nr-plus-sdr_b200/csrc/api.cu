@@ -152,6 +152,7 @@ void dnrp_ctx_destroy(dnrp_ctx_t* ctx) {
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     if (ctx->stream_copy) cudaStreamDestroy(ctx->stream_copy);
     if (ctx->stream_d2h) cudaStreamDestroy(ctx->stream_d2h);
+    if (ctx->h_stage) cudaFreeHost(ctx->h_stage);
     for (cudaEvent_t e : ctx->chunk_events) cudaEventDestroy(e);
     for (cudaEvent_t e : ctx->chunk_done) cudaEventDestroy(e);
     for (auto& t : ctx->ktimer)

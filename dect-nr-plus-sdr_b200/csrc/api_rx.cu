@@ -264,24 +264,62 @@ int dnrp_rx_pdc_batch(dnrp_ctx_t* c, uint32_t n, const uint32_t* harq_slot, cons
     return fetch_pdc_reports(c, n, tb_out, out, n_iter);
 }
 
-int dnrp_rx_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, uint32_t search_length, const uint32_t* harq_slot,
-                  const uint8_t* rv, const uint8_t* harq_reset, dnrp_sync_result_t* sync_out, dnrp_pcc_report_t* pcc_out,
-                  uint8_t* tb_out, dnrp_pdc_report_t* pdc_out, uint8_t* n_iter) {
+// iq_in: float2 windows, or (sc16_scale != 0) int16 I/Q pairs that are converted on the device chunk by chunk
+static int rx_batch_impl(dnrp_ctx_t* c, uint32_t n, const void* iq_in, float sc16_scale, uint32_t search_length,
+                         const uint32_t* harq_slot, const uint8_t* rv, const uint8_t* harq_reset,
+                         dnrp_sync_result_t* sync_out, dnrp_pcc_report_t* pcc_out, uint8_t* tb_out,
+                         dnrp_pdc_report_t* pdc_out, uint8_t* n_iter) {
     DNRP_REQUIRE(c && iq_in && tb_out && pdc_out, "null argument");
     DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
     DNRP_REQUIRE(search_length <= c->sync_len, "search_length exceeds the (resampled) IQ window");
     DNRP_CUDA(cudaSetDevice(c->device));
     const phy_dims_t& d = c->dims;
+    const bool sc16 = sc16_scale != 0.f;
+    if (sc16 && !c->d_iq_sc16.p) {
+        DNRP_REQUIRE(c->rx_stride % 4 == 0, "sc16 ingest needs a window stride that is a multiple of 4");
+        DNRP_CUDA(c->d_iq_sc16.alloc((size_t)c->B * d.N_RX * c->rx_stride * 2));
+    }
     if (harq_slot)
         for (uint32_t i = 0; i < n; ++i) DNRP_REQUIRE(harq_slot[i] < c->B, "harq slot out of range");
     if (harq_slot) DNRP_CUDA(cudaMemcpyAsync(c->d_slot.p, harq_slot, 4 * n, cudaMemcpyHostToDevice, c->stream));
     if (rv) DNRP_CUDA(cudaMemcpyAsync(c->d_rv.p, rv, n, cudaMemcpyHostToDevice, c->stream));
     if (harq_reset) DNRP_CUDA(cudaMemcpyAsync(c->d_reset.p, harq_reset, n, cudaMemcpyHostToDevice, c->stream));
-    // chunks: the H2D copy of chunk k+1 runs on the copy stream while chunk k is processed on the compute stream
-    const char* env_chunks = std::getenv("DNRP_RX_CHUNKS");   // tuning knob, default below
-    uint32_t n_chunks = n >= 8192 ? 16 : (n >= 2048 ? 8 : (n >= 256 ? 4 : 1));
-    if (env_chunks && std::atoi(env_chunks) > 0) n_chunks = std::min<uint32_t>((uint32_t)std::atoi(env_chunks), n);
-    const uint32_t per = (n + n_chunks - 1) / n_chunks;
+    // chunks: the H2D copy of chunk k+1 runs on the copy stream while chunk k is processed on the compute stream and
+    // the records of chunk k-1 travel back on the third stream.  Smaller chunks at both ends, larger ones in the middle:
+    // the first kernels start after a short copy, the last copy is followed by a short computation (whichever of
+    // the two streams is the bottleneck), and the bulk runs in launches large enough to fill the GPU.
+    std::vector<uint32_t> bounds{0};
+    {
+        // Measured on C2 / 10 000 windows (scratch/e2e_weights.py): one chunk costs 0.19 ms + 1.51 us per packet.
+        // cf32 windows: the copy (2.17 us per packet over PCIe) is the bottleneck -> many gently tapered chunks, the
+        // last copy is followed by a short computation.  sc16 windows: the kernels are the bottleneck -> few chunks
+        // growing by <= 1.4x, so that the first kernels start early and no chunk waits for its copy.
+        static const uint32_t wc[] = {2, 2, 3, 3, 4, 4, 4, 4, 4, 4, 4, 4, 3, 3, 2, 2}, ws[] = {4, 6, 8, 11, 15, 21, 32},
+                              w6[] = {2, 3, 4, 4, 3, 2}, w3[] = {1, 1, 1}, w1[] = {1};
+        const uint32_t* w = n >= 8192 ? (sc16 ? ws : wc) : (n >= 2048 ? w6 : (n >= 256 ? w3 : w1));
+        uint32_t nw = n >= 8192 ? (sc16 ? 7 : 16) : (n >= 2048 ? 6 : (n >= 256 ? 3 : 1));
+        const char* env_chunks = std::getenv("DNRP_RX_CHUNKS");   // tuning knobs: that many equal chunks, or weights
+        const char* env_w = std::getenv("DNRP_RX_WEIGHTS");       // "3,4,5,..."
+        std::vector<uint32_t> eq;
+        if (env_w && *env_w) {
+            for (const char* q = env_w; *q;) {
+                eq.push_back((uint32_t)std::max(1L, std::strtol(q, const_cast<char**>(&q), 10)));
+                while (*q == ',' || *q == ' ') ++q;
+            }
+            w = eq.data(); nw = (uint32_t)eq.size();
+        } else if (env_chunks && std::atoi(env_chunks) > 0) {
+            eq.assign(std::min<uint32_t>((uint32_t)std::atoi(env_chunks), n), 1);
+            w = eq.data(); nw = (uint32_t)eq.size();
+        }
+        uint64_t tot = 0, acc = 0;
+        for (uint32_t k = 0; k < nw; ++k) tot += w[k];
+        for (uint32_t k = 0; k < nw; ++k) {
+            acc += w[k];
+            const uint32_t e = (uint32_t)((uint64_t)n * acc / tot);
+            if (e > bounds.back()) bounds.push_back(e);
+        }
+    }
+    const uint32_t n_chunks = (uint32_t)bounds.size() - 1;
     while (c->chunk_events.size() < n_chunks) {
         cudaEvent_t e, g;
         DNRP_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
@@ -289,44 +327,115 @@ int dnrp_rx_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, uint32_t 
         c->chunk_events.push_back(e);
         c->chunk_done.push_back(g);
     }
+    // pinned staging of the per-packet records (pageable destinations would serialise the copies)
+    const size_t B = c->B, C_cb = c->ps.C;
+    size_t so = 0;
+    auto carve = [&](size_t bytes) { const size_t o = so; so += (bytes + 63) & ~(size_t)63; return o; };
+    const size_t o_state = carve(B * sizeof(rx_state_t)), o_ok = carve(2 * B), o_plcf = carve(32 * B), o_mask = carve(8 * B),
+                 o_tbok = carve(B), o_mimo = carve(B * sizeof(mimo_report_dev_t)), o_nit = carve(B * C_cb),
+                 o_sync = carve(B * sizeof(dnrp_sync_result_t));
+    if (c->h_stage_bytes < so) {
+        if (c->h_stage) cudaFreeHost(c->h_stage);
+        c->h_stage = nullptr; c->h_stage_bytes = 0;
+        DNRP_CUDA(cudaMallocHost(&c->h_stage, so));
+        c->h_stage_bytes = so;
+    }
+    uint8_t* hs = static_cast<uint8_t*>(c->h_stage);
     const size_t win = (size_t)d.N_RX * c->rx_stride;
     for (uint32_t k = 0; k < n_chunks; ++k) {
-        const uint32_t o = k * per, m = std::min(per, n - std::min(n, o));
-        if (m == 0) break;
-        DNRP_CUDA(cudaMemcpyAsync(c->d_iq_rx.p + o * win, reinterpret_cast<const float2*>(iq_in) + o * win,
-                                  m * win * sizeof(float2), cudaMemcpyHostToDevice, c->stream_copy));
+        const size_t o = bounds[k], m = bounds[k + 1] - bounds[k];
+        if (sc16)
+            DNRP_CUDA(cudaMemcpyAsync(c->d_iq_sc16.p + o * win * 2, reinterpret_cast<const int16_t*>(iq_in) + o * win * 2,
+                                      m * win * 2 * sizeof(int16_t), cudaMemcpyHostToDevice, c->stream_copy));
+        else
+            DNRP_CUDA(cudaMemcpyAsync(c->d_iq_rx.p + o * win, reinterpret_cast<const float2*>(iq_in) + o * win,
+                                      m * win * sizeof(float2), cudaMemcpyHostToDevice, c->stream_copy));
         DNRP_CUDA(cudaEventRecord(c->chunk_events[k], c->stream_copy));
     }
     int rc = DNRP_OK;
     for (uint32_t k = 0; k < n_chunks && rc == DNRP_OK; ++k) {
-        const uint32_t o = k * per, m = std::min(per, n - std::min(n, o));
-        if (m == 0) break;
+        const size_t o = bounds[k];
+        const uint32_t m = bounds[k + 1] - bounds[k];
         DNRP_CUDA(cudaStreamWaitEvent(c->stream, c->chunk_events[k], 0));
-        c->off = o;
+        c->off = (uint32_t)o;
+        if (sc16)
+            DNRP_LAUNCH(c, -1, launch_sc16_to_cf32(c->d_iq_sc16.p + o * win * 2, c->d_iq_rx.p + o * win, m * win, sc16_scale,
+                                                   c->stream));
         rc = run_sync(c, m, search_length, true);
         if (rc == DNRP_OK) rc = run_rx_front(c, m);
         if (rc == DNRP_OK) rc = run_rx_pcc(c, m);
         if (rc == DNRP_OK) rc = run_rx_pdc(c, m, harq_slot != nullptr, rv != nullptr, harq_reset != nullptr);
         if (rc == DNRP_OK) {
-            // this chunk's transport blocks travel back while the next chunk is processed
+            // this chunk's transport blocks and records travel back while the next chunk is processed
             DNRP_CUDA(cudaEventRecord(c->chunk_done[k], c->stream));
-            DNRP_CUDA(cudaStreamWaitEvent(c->stream_d2h, c->chunk_done[k], 0));
-            DNRP_CUDA(cudaMemcpy2DAsync(tb_out + (size_t)o * c->ps.N_TB_byte, c->ps.N_TB_byte,
-                                        c->d_tb_out.p + (size_t)o * c->fec.tb_stride, c->fec.tb_stride, c->ps.N_TB_byte, m,
-                                        cudaMemcpyDeviceToHost, c->stream_d2h));
+            cudaStream_t sd = c->stream_d2h;
+            DNRP_CUDA(cudaStreamWaitEvent(sd, c->chunk_done[k], 0));
+            DNRP_CUDA(cudaMemcpy2DAsync(tb_out + o * c->ps.N_TB_byte, c->ps.N_TB_byte,
+                                        c->d_tb_out.p + o * c->fec.tb_stride, c->fec.tb_stride, c->ps.N_TB_byte, m,
+                                        cudaMemcpyDeviceToHost, sd));
+            auto back = [&](size_t off, const void* dev, size_t unit) {
+                return cudaMemcpyAsync(hs + off + o * unit, static_cast<const uint8_t*>(dev) + o * unit, m * unit,
+                                       cudaMemcpyDeviceToHost, sd);
+            };
+            DNRP_CUDA(back(o_state, c->d_rx_state.p, sizeof(rx_state_t)));
+            DNRP_CUDA(back(o_ok, c->d_pcc_crc.p, 2));
+            DNRP_CUDA(back(o_plcf, c->d_plcf_out.p, 32));
+            DNRP_CUDA(back(o_mask, c->d_pcc_mask.p, 8));
+            DNRP_CUDA(back(o_tbok, c->d_tb_ok.p, 1));
+            DNRP_CUDA(back(o_mimo, c->d_mimo.p, sizeof(mimo_report_dev_t)));
+            if (n_iter) DNRP_CUDA(back(o_nit, c->d_n_iter.p, C_cb));
+            if (sync_out) DNRP_CUDA(back(o_sync, c->d_sync_result.p, sizeof(dnrp_sync_result_t)));
         }
     }
     c->off = 0;
     if (rc) return rc;
-    if (sync_out)
-        DNRP_CUDA(cudaMemcpyAsync(sync_out, c->d_sync_result.p, n * sizeof(dnrp_sync_result_t), cudaMemcpyDeviceToHost,
-                                  c->stream));
-    std::vector<dnrp_pcc_report_t> pcc_tmp;
-    if (!pcc_out) { pcc_tmp.resize(n); pcc_out = pcc_tmp.data(); }   // also refreshes h_rx_state for the PDC reports
-    if ((rc = fetch_pcc_reports(c, n, pcc_out)) != DNRP_OK) return rc;
-    rc = fetch_pdc_reports(c, n, tb_out, pdc_out, n_iter, true);
     DNRP_CUDA(cudaStreamSynchronize(c->stream_d2h));
-    return rc;
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    // records -> ABI structs (same fields as fetch_pcc_reports / fetch_pdc_reports)
+    const rx_state_t* st = reinterpret_cast<const rx_state_t*>(hs + o_state);
+    const mimo_report_dev_t* mimo = reinterpret_cast<const mimo_report_dev_t*>(hs + o_mimo);
+    const uint32_t* mask = reinterpret_cast<const uint32_t*>(hs + o_mask);
+    std::memcpy(c->h_rx_state.data(), st, n * sizeof(rx_state_t));
+    if (sync_out) std::memcpy(sync_out, hs + o_sync, n * sizeof(dnrp_sync_result_t));
+    if (n_iter) std::memcpy(n_iter, hs + o_nit, n * C_cb);
+    for (uint32_t i = 0; i < n; ++i) {
+        if (pcc_out) {
+            dnrp_pcc_report_t& r = pcc_out[i];
+            std::memset(&r, 0, sizeof(r));
+            for (uint32_t t = 0; t < 2; ++t) {
+                r.plcf_ok[t] = hs[o_ok + 2 * i + t];
+                std::memcpy(r.plcf[t], hs + o_plcf + 32 * (size_t)i + 16 * t, 10);
+                r.crc_mask[t] = mask[2 * i + t];
+            }
+            r.snr_dB = st[i].snr_db_pcc;
+            r.cfo_residual_rad = st[i].cfo_left;
+            r.sto_fractional = st[i].sto_fractional;
+            for (uint32_t a = 0; a < 8; ++a) r.rms[a] = st[i].rms[a];
+        }
+        dnrp_pdc_report_t& q = pdc_out[i];
+        q.crc_ok = hs[o_tbok + i];
+        q.snr_dB = st[i].snr_db_pdc;
+        q.mimo_N_RX = mimo[i].N_RX; q.mimo_N_TS_other = mimo[i].N_TS_other;
+        q.tm_3_7_beamforming_idx = mimo[i].tm_3_7_beamforming_idx;
+        q.tm_3_7_beamforming_reciprocal_idx = mimo[i].tm_3_7_beamforming_reciprocal_idx;
+    }
+    return DNRP_OK;
+}
+
+int dnrp_rx_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, uint32_t search_length, const uint32_t* harq_slot,
+                  const uint8_t* rv, const uint8_t* harq_reset, dnrp_sync_result_t* sync_out, dnrp_pcc_report_t* pcc_out,
+                  uint8_t* tb_out, dnrp_pdc_report_t* pdc_out, uint8_t* n_iter) {
+    return rx_batch_impl(c, n, iq_in, 0.f, search_length, harq_slot, rv, harq_reset, sync_out, pcc_out, tb_out, pdc_out,
+                         n_iter);
+}
+
+int dnrp_rx_batch_sc16(dnrp_ctx_t* c, uint32_t n, const int16_t* iq_in, float scale, uint32_t search_length,
+                       const uint32_t* harq_slot, const uint8_t* rv, const uint8_t* harq_reset,
+                       dnrp_sync_result_t* sync_out, dnrp_pcc_report_t* pcc_out, uint8_t* tb_out,
+                       dnrp_pdc_report_t* pdc_out, uint8_t* n_iter) {
+    DNRP_REQUIRE(scale > 0.f, "scale must be > 0");
+    return rx_batch_impl(c, n, iq_in, scale, search_length, harq_slot, rv, harq_reset, sync_out, pcc_out, tb_out,
+                         pdc_out, n_iter);
 }
 
 static bool tap_desc(const dnrp_ctx_t* c, int tap, uint32_t n, const void*& src, size_t& bytes) {

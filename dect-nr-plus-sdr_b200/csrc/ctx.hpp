@@ -92,6 +92,8 @@ struct dnrp_ctx {
     cudaStream_t stream_copy = nullptr;      // H2D copies of the pipelined receive call
     cudaStream_t stream_d2h = nullptr;       // transport blocks of finished chunks back to the host
     std::vector<cudaEvent_t> chunk_events, chunk_done;
+    void* h_stage = nullptr;                 // pinned staging of the per-packet records of dnrp_rx_batch (first use)
+    size_t h_stage_bytes = 0;
 
     dnrp::fec_plan_t fec;
     // device tables
@@ -149,6 +151,7 @@ struct dnrp_ctx {
     uint32_t tx_os_stride = 0, sync_stride = 0, sync_len = 0, rs_stride = 0;
     dnrp::dbuf<float2> d_iq_tx_os;              // [B][N_TX][tx_os_stride] TX IQ before resampling
     dnrp::dbuf<float2> d_iq_sync;               // [B][N_RX][sync_stride] window resampled for detection / coarse peak
+    dnrp::dbuf<int16_t> d_iq_sc16;              // [B][N_RX][rx_stride][2] staging of dnrp_rx_batch_sc16 (allocated on first use)
     dnrp::dbuf<float2> d_iq_rs;                 // [B][N_RX][rs_stride] packet resampled from the fine peak
 
     // packet synchronisation: STF templates for N_eff_TX = 1, 2, 4, 8 (up to the context's), step sums, results

@@ -7,6 +7,7 @@
 // One block = RS_TILE consecutive outputs of one stream: the input span (about RS_TILE*M/L + SL samples) is staged in
 // shared memory with coalesced loads and zero extension, taps are read as [j][l] rows (at most L distinct banks per
 // warp), outputs are written coalesced.  HBM traffic = input once + output once.
+#include <algorithm>
 #include "phy.cuh"
 
 namespace dnrp {
@@ -76,6 +77,33 @@ cudaError_t launch_resample(const resample_params_t& p, uint32_t n_packets, cuda
     cudaError_t e = cudaFuncSetAttribute(k_resample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     k_resample<<<dim3((n_total + RS_TILE - 1) / RS_TILE, p.n_ant, n_packets), RS_THREADS, smem, st>>>(p, span_max);
+    return cudaGetLastError();
+}
+
+// ---- sc16 -> cf32 (the radio's wire format: int16 I/Q pairs; the reference lets UHD convert on the host CPU,
+// hw_usrp.cpp "fc32" cpu format): 4 complex samples per thread, 16 B in, 32 B out
+__global__ void __launch_bounds__(256) k_sc16_to_cf32(const int4* __restrict__ in, float4* __restrict__ out, size_t n4,
+                                                       float scale) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        const int4 v = __ldg(in + i);
+        const int w[4] = {v.x, v.y, v.z, v.w};
+        float f[8];
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+            f[2 * k] = (float)(int16_t)(w[k] & 0xffff) * scale;
+            f[2 * k + 1] = (float)(int16_t)(w[k] >> 16) * scale;
+        }
+        out[2 * i] = make_float4(f[0], f[1], f[2], f[3]);
+        out[2 * i + 1] = make_float4(f[4], f[5], f[6], f[7]);
+    }
+}
+
+cudaError_t launch_sc16_to_cf32(const int16_t* in, float2* out, size_t n_samples, float scale, cudaStream_t st) {
+    if (n_samples == 0) return cudaSuccess;
+    if (n_samples % 4) return cudaErrorInvalidValue;
+    const size_t n4 = n_samples / 4;
+    const unsigned grid = (unsigned)std::min<size_t>((n4 + 255) / 256, 148 * 16);
+    k_sc16_to_cf32<<<grid, 256, 0, st>>>(reinterpret_cast<const int4*>(in), reinterpret_cast<float4*>(out), n4, scale);
     return cudaGetLastError();
 }
 

@@ -219,6 +219,16 @@ int dnrp_rx_batch(dnrp_ctx_t* ctx, uint32_t n, const dnrp_cf32_t* iq_in, uint32_
                   dnrp_sync_result_t* sync_out, dnrp_pcc_report_t* pcc_out, uint8_t* tb_out,
                   dnrp_pdc_report_t* pdc_out, uint8_t* n_iter);
 
+/* dnrp_rx_batch for IQ in the radio's wire format: iq_in [n][N_RX][dnrp_rx_stride()][2] int16 (I, Q), each sample
+ * becomes (I * scale, Q * scale) on the device (scale = 1/32768 reproduces UHD's sc16 -> fc32 conversion, which the
+ * reference leaves to UHD on the host CPU: lib/src/radio/hw_usrp.cpp:436-438, cpu_format "fc32", otw_format "sc16").
+ * Halves the host-to-device bytes of dnrp_rx_batch; everything after the conversion is the same code path.
+ * dnrp_rx_stride() must be a multiple of 4. */
+int dnrp_rx_batch_sc16(dnrp_ctx_t* ctx, uint32_t n, const int16_t* iq_in, float scale, uint32_t search_length,
+                       const uint32_t* harq_slot, const uint8_t* rv, const uint8_t* harq_reset,
+                       dnrp_sync_result_t* sync_out, dnrp_pcc_report_t* pcc_out, uint8_t* tb_out,
+                       dnrp_pdc_report_t* pdc_out, uint8_t* n_iter);
+
 /* test / scope taps (the reference exposes the same data through its JSON export and TCP scope,
  * rx_synced.cpp:363-443): copies an intermediate device buffer of the last call to the host.
  * Returns DNRP_ERR_INVALID if dst_bytes is smaller than the buffer for n packets. */

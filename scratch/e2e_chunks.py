@@ -29,3 +29,23 @@ for ch in (1, 4, 8, 16, 32, 64):
     for _ in range(5): s, p, ok, o, d = phy.rx(win, tb_out=tbp.numpy())
     dt = (time.perf_counter() - t) / 5
     print("chunks %3d: %.2f ms  ok %d" % (ch, dt * 1e3, int(ok.sum())))
+# ---- sc16 ingest
+gain = np.float32(0.1 / np.sqrt(np.mean(np.abs(win[:64]) ** 2)) * 32768.0)
+h16 = torch.empty((P, 1, phy.rx_stride(), 2), dtype=torch.int16, pin_memory=True)
+w16 = h16.numpy()
+for i in range(0, P, 512):
+    w16[i:i + 512] = np.clip(np.rint(win[i:i + 512].view(np.float32).reshape(-1, 1, phy.rx_stride(), 2) * gain), -32768, 32767).astype(np.int16)
+for ch in (1, 2, 4, 8, 16, 32):
+    os.environ["DNRP_RX_CHUNKS"] = str(ch)
+    for _ in range(2): phy.rx(w16, tb_out=tbp.numpy(), sc16_scale=float(1 / gain))
+    t = time.perf_counter()
+    for _ in range(5): s, p, ok, o, d = phy.rx(w16, tb_out=tbp.numpy(), sc16_scale=float(1 / gain))
+    dt = (time.perf_counter() - t) / 5
+    print("sc16 chunks %3d: %.2f ms  ok %d" % (ch, dt * 1e3, int(ok.sum())))
+# where does the time go: resident chain in one piece vs python/report overhead
+ms = phy.time_stage(product.STAGE_SYNC_RX_CHAIN, P, reps=3)
+print("resident step %.2f ms" % ms)
+t = time.perf_counter()
+for _ in range(5):
+    np.zeros(P, dtype=product.PDC_DTYPE); np.zeros(P, dtype=product.PCC_DTYPE); np.zeros(P, dtype=product.SYNC_RESULT_DTYPE)
+print("numpy output allocation %.2f ms" % ((time.perf_counter() - t) / 5 * 1e3))

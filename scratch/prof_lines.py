@@ -12,7 +12,8 @@ for l in sass[start + 1:]:
     m = re.match(r'\s+/\*([0-9a-f]{4,})\*/\s+(.*?);', l)
     if m: seq.append((cur, m.group(2)))
     if (l.startswith(".text.") or l.startswith("//-----")) and seq: break
-out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"], capture_output=True, text=True).stdout
+extra = os.environ.get("NCU_ARGS", "").split()
+out = subprocess.run(["ncu", "-i", rep, "--page", "source", "--csv"] + extra, capture_output=True, text=True).stdout
 rows = list(csv.reader(out.split("\n"))); h = rows[1]; data = [r for r in rows[2:] if len(r) > 10]; idx = {n: i for i, n in enumerate(h)}
 print("sass", len(seq), "profile", len(data))
 ss = idx["# Samples"]; ie = idx["Instructions Executed"]

@@ -133,3 +133,32 @@ def test_rx_batch_pipelined_equals_three_calls(product, resample, N_RX):
     assert np.array_equal(ok1, ok2) and np.array_equal(tb1, tb2) and rep2.tobytes() == rep1.tobytes()
     assert ok2.mean() > 0.9 and (tb2[ok2] == tb[ok2]).all()
     phy.close()
+
+
+def test_rx_batch_sc16_equals_cf32_on_dequantised_windows(product):
+    """dnrp_rx_batch_sc16 (int16 I/Q in, converted on the device) returns bit for bit what dnrp_rx_batch returns for
+    the float windows int16 * scale -- the conversion is exact, everything after it is the same code path"""
+    cfg = CONFIGS["C1_loopback"]
+    ps = spec.get_packet_sizes(*cfg)
+    n = 300
+    phy = product.Phy(cfg, max_batch=n, N_RX=2, network_id=NET)
+    rng = np.random.default_rng(19)
+    tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
+    plcf = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    phy.tx(plcf, tb, fetch=False)
+    stf = ps["N_samples_STF"]
+    t0 = rng.integers(stf // 2, 2 * stf - 8, n)
+    win = phy.channel(n, snr_dB=14.0, t0=t0, mode=0, seed=5, fetch=True)
+    gain = np.float32(0.1 / np.sqrt(np.mean(np.abs(win) ** 2)) * 32768.0)
+    w16 = np.clip(np.rint(win.view(np.float32).reshape(n, 2, -1, 2) * gain), -32768, 32767).astype(np.int16)
+    scale = np.float32(1.0) / gain
+    deq = np.ascontiguousarray((w16.astype(np.float32) * scale).reshape(n, 2, -1)).view(np.complex64)
+    s1, p1, ok1, tb1, rep1 = phy.rx(deq)
+    rep1 = rep1.copy()
+    phy.channel(n, snr_dB=-20.0, t0=0, mode=0, seed=6)   # scramble the device state in between
+    phy.sync(n=n)
+    s2, p2, ok2, tb2, rep2 = phy.rx(w16, sc16_scale=float(scale))
+    assert s2.tobytes() == s1.tobytes() and p2.tobytes() == p1.tobytes()
+    assert np.array_equal(ok1, ok2) and np.array_equal(tb1, tb2) and rep2.tobytes() == rep1.tobytes()
+    assert ok2.mean() > 0.9 and (tb2[ok2] == tb[ok2]).all()
+    phy.close()
