@@ -390,7 +390,7 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
                             const uint32_t k = k0 + i;
                             const uint32_t x = xs[i], y = ys[i];
                             const uint32_t l = llr_step(a, bb[i], x, y);
-                            const uint32_t e = vclamp(vadd(l, vneg(x)), 2047);
+                            const uint32_t e = vclamp(vsub(l, x), 2047);
                             if (dec == 0) {
                                 EXT[k * T + t] = e;
                             } else {
