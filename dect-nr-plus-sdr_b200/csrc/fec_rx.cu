@@ -60,10 +60,17 @@ __global__ void __launch_bounds__(256) k_derm(const tdec_params_t p, uint32_t ca
             // two LLRs per 4-byte load
             const uint32_t* llr2 = reinterpret_cast<const uint32_t*>(llr);
             uint32_t* DSC2 = reinterpret_cast<uint32_t*>(DSC);
+            // the two Gold bits of a pair come from one 16-bit window of the sequence (independent of the LLR load)
+            const uint32_t g0 = cb.rp + p.gold_bit_off;
+#pragma unroll 4
             for (uint32_t e2 = tid; e2 < cb.n_e / 2; e2 += nthr) {
                 const uint32_t w = llr2[e2];
-                const int lo = descr(2 * e2, (int)(int16_t)(w & 0xffff)), hi = descr(2 * e2 + 1, (int)(int16_t)(w >> 16));
-                DSC2[e2] = ((uint32_t)lo & 0xffffu) | ((uint32_t)hi << 16);
+                const uint32_t g = g0 + 2 * e2;
+                const uint32_t gw = ((uint32_t)p.gold[g >> 3] << 8) | p.gold[(g >> 3) + 1];
+                const uint32_t b0 = (gw >> (15 - (g & 7))) & 1u, b1 = (gw >> (14 - (g & 7))) & 1u;
+                // sign flip of each half where its bit is set: (v ^ m) - m with m = 0xffff per flipped half
+                const uint32_t m = (b0 ? 0xffffu : 0u) | (b1 ? 0xffff0000u : 0u);
+                DSC2[e2] = __vsub2(w ^ m, m);
             }
             if ((cb.n_e & 1) && tid == 0) DSC[cb.n_e - 1] = (int16_t)descr(cb.n_e - 1, llr[cb.n_e - 1]);
         } else {
@@ -77,6 +84,7 @@ __global__ void __launch_bounds__(256) k_derm(const tdec_params_t p, uint32_t ca
     // multiple of 4 for every turbo block size, table and soft-buffer offsets are multiples of 4 elements)
     const uint2* rm4 = reinterpret_cast<const uint2*>(rm_pos);
     uint2* soft4 = reinterpret_cast<uint2*>(soft);
+#pragma unroll 2
     for (uint32_t q = tid; q < N / 4; q += nthr) {
         const uint2 rp = rm4[q];
         uint2 old = make_uint2(0u, 0u);

@@ -26,19 +26,24 @@ __device__ __forceinline__ float2 tw(const float2* __restrict__ table, uint32_t 
 }
 
 // One Stockham pass of radix R (Bainville's formulation): element j of N/R butterflies,
-// Ns = product of the radices of the previous passes.
-template <bool INV, int R>
+// Ns = product of the radices of the previous passes.  POW2: Ns is a power of two (every pass of a
+// power-of-two transform): index arithmetic by mask and shift instead of integer division.
+// k * r * tstep < Ns * R * N / (Ns * R) = N, so the twiddle index needs no reduction; the first pass
+// (Ns == 1) has unit twiddles.
+template <bool INV, int R, bool POW2>
 __device__ __forceinline__ void fft_pass(const float2* __restrict__ x, float2* __restrict__ y, uint32_t N,
-                                         uint32_t Ns, const float2* __restrict__ table) {
+                                         uint32_t Ns, uint32_t log2Ns, const float2* __restrict__ table) {
     const uint32_t M = N / R;
+    const uint32_t tstep = POW2 ? M >> log2Ns : N / (Ns * R);  // W_{Ns*R}^k = W_N^{k*tstep}
     for (uint32_t j = threadIdx.x; j < M; j += blockDim.x) {
-        const uint32_t k = j % Ns;
-        const uint32_t tstep = N / (Ns * R);  // W_{Ns*R}^k = W_N^{k*tstep}
+        const uint32_t k = POW2 ? (j & (Ns - 1)) : j % Ns;
         float2 v[R];
 #pragma unroll
-        for (int r = 0; r < R; ++r) {
-            v[r] = x[j + r * M];
-            if (r > 0) v[r] = cmul(v[r], tw<INV>(table, (k * r * tstep) % N));
+        for (int r = 0; r < R; ++r) v[r] = x[j + r * M];
+        if (Ns != 1) {
+            const uint32_t kt = k * tstep;
+#pragma unroll
+            for (int r = 1; r < R; ++r) v[r] = cmul(v[r], tw<INV>(table, kt * r));
         }
         if (R == 2) {
             const float2 a = v[0], b = v[1];
@@ -63,33 +68,44 @@ __device__ __forceinline__ void fft_pass(const float2* __restrict__ x, float2* _
             v[1] = cadd(t2, t3);
             v[2] = csub(t2, t3);
         }
-        const uint32_t j0 = (j / Ns) * Ns * R + k;
+        const uint32_t j0 = POW2 ? (((j >> log2Ns) << log2Ns) * R + k) : ((j / Ns) * Ns * R + k);
+        if (R == 4 && Ns == 1) {  // first pass: four consecutive outputs, two 16-byte stores (y is 16-byte aligned)
+            float4* y4 = reinterpret_cast<float4*>(y + 4 * j);
+            y4[0] = make_float4(v[0].x, v[0].y, v[1].x, v[1].y);
+            y4[1] = make_float4(v[2].x, v[2].y, v[3].x, v[3].y);
+        } else {
 #pragma unroll
-        for (int r = 0; r < R; ++r) y[j0 + r * Ns] = v[r];
+            for (int r = 0; r < R; ++r) y[j0 + r * Ns] = v[r];
+        }
     }
 }
 
 // In-block FFT of a[0..N); b is scratch of the same size.  Returns the buffer holding the result.
-// All threads of the block must call it; contains __syncthreads().
+// All threads of the block must call it; contains __syncthreads().  Radix-4 passes first, then one radix-2,
+// then the radix-3 passes: Ns stays a power of two through the last power-of-two pass and the first radix-3 pass
+// (the OFDM sizes have at most one factor 3), so no pass divides by a runtime value.
 template <bool INV>
 __device__ float2* block_fft(float2* a, float2* b, uint32_t N, const float2* __restrict__ table) {
-    uint32_t Ns = 1;
+    uint32_t Ns = 1, lg = 0;
     uint32_t rem = N;
     __syncthreads();
-    while (rem % 3 == 0) {
-        fft_pass<INV, 3>(a, b, N, Ns, table);
-        Ns *= 3; rem /= 3;
-        float2* t = a; a = b; b = t;
-        __syncthreads();
-    }
     while (rem % 4 == 0) {
-        fft_pass<INV, 4>(a, b, N, Ns, table);
-        Ns *= 4; rem /= 4;
+        fft_pass<INV, 4, true>(a, b, N, Ns, lg, table);
+        Ns *= 4; lg += 2; rem /= 4;
         float2* t = a; a = b; b = t;
         __syncthreads();
     }
-    if (rem == 2) {
-        fft_pass<INV, 2>(a, b, N, Ns, table);
+    if (rem % 2 == 0) {
+        fft_pass<INV, 2, true>(a, b, N, Ns, lg, table);
+        Ns *= 2; lg += 1; rem /= 2;
+        float2* t = a; a = b; b = t;
+        __syncthreads();
+    }
+    bool pow2 = true;
+    while (rem % 3 == 0) {
+        if (pow2) fft_pass<INV, 3, true>(a, b, N, Ns, lg, table);
+        else fft_pass<INV, 3, false>(a, b, N, Ns, 0, table);
+        Ns *= 3; rem /= 3; pow2 = false;
         float2* t = a; a = b; b = t;
         __syncthreads();
     }

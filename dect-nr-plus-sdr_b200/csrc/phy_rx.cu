@@ -43,7 +43,7 @@ __device__ __forceinline__ uint32_t bin_of_k(uint32_t k, const phy_dims_t& d) {
 // ---- STF stage, one block per packet (rx_synced.cpp:503-709, estimator_sto.cpp:47-173,
 // estimator_snr.cpp:48-145)
 __global__ void __launch_bounds__(256) k_rx_stf(const rx_params_t p) {
-    extern __shared__ float2 sm[];
+    extern __shared__ __align__(16) float2 sm[];
     const phy_dims_t& d = p.d;
     const uint32_t pkt = blockIdx.x, tid = threadIdx.x, nthr = blockDim.x;
     rx_state_t& st = p.state[pkt];
@@ -64,8 +64,11 @@ __global__ void __launch_bounds__(256) k_rx_stf(const rx_params_t p) {
     for (uint32_t a = 0; a < d.N_RX; ++a) {
         const float2* x = p.iq + ((size_t)pkt * d.N_RX + a) * p.iq_stride + t0;
         float2 pw = make_float2(0.f, 0.f);
+        float2 w = rot((double)inc0 * (double)tid);
+        const float2 ws = rot((double)inc0 * (double)nthr);
         for (uint32_t n = tid; n < d.stf_len_os; n += nthr) {
-            float2 v = cmul(x[n], rot((double)inc0 * (double)n));
+            float2 v = cmul(x[n], w);
+            w = cmul(w, ws);
             pw.x += v.x * v.x + v.y * v.y;
             const float cs = c[n / d.pat_len_os];
             S[n] = make_float2(v.x * cs, v.y * cs);
@@ -156,7 +159,7 @@ __device__ __forceinline__ float drs_sign_dev(const phy_dims_t& d, uint32_t l, u
 // FFT, un-mirroring, amplitude scaling, STO derotation (rx_synced.cpp:711-771); DRS symbols also
 // deliver the zero-forced pilots and their SNR sums (rx_synced.cpp:773-861, estimator_snr.cpp:76-86)
 __global__ void __launch_bounds__(256) k_rx_fft(const rx_params_t p) {
-    extern __shared__ float2 sm[];
+    extern __shared__ __align__(16) float2 sm[];
     const phy_dims_t& d = p.d;
     const uint32_t l = blockIdx.x + 1, a = blockIdx.y, pkt = blockIdx.z;
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
@@ -169,16 +172,26 @@ __global__ void __launch_bounds__(256) k_rx_fft(const rx_params_t p) {
     const float2* x = p.iq + ((size_t)pkt * d.N_RX + a) * p.iq_stride + (p.t0_zero ? 0 : st.t0) + n0;
     // mixer phase is continuous: inc0 over the STF, inc1 afterwards (rx_synced.cpp:239-245, 552-555)
     const double ph0 = (double)st.inc0 * (double)d.stf_len_os + (double)st.inc1 * (double)(n0 - d.stf_len_os);
-    for (uint32_t n = tid; n < d.N_os; n += nthr) X[n] = cmul(x[n], rot(ph0 + (double)st.inc1 * (double)n));
+    // one exact phasor per thread, then a rotation by nthr samples per iteration (<= 16 float rotations)
+    {
+        float2 w = rot(ph0 + (double)st.inc1 * (double)tid);
+        const float2 ws = rot((double)st.inc1 * (double)nthr);
+        for (uint32_t n = tid; n < d.N_os; n += nthr) {
+            X[n] = cmul(x[n], w);
+            w = cmul(w, ws);
+        }
+    }
     const float2* F = block_fft<false>(X, Yb, d.N_os, d.twiddle);
 
     const float fscale = sqrtf((float)d.N_OCC) / (float)d.N_os;
     float2* Yout = p.Y + (((size_t)pkt * d.N_RX + a) * d.N_DF + (l - 1)) * d.Nk;
     float2* Ys = (float2*)(F == X ? Yb : X);  // keep the output symbol in shared for the pilot stage
+    float2 wk = rot((double)st.sto_inc * (double)((int)tid - (int)(d.N_OCC / 2)));
+    const float2 wks = rot((double)st.sto_inc * (double)nthr);
+    wk = make_float2(wk.x * fscale, wk.y * fscale);
     for (uint32_t k = tid; k < d.Nk; k += nthr) {
-        const float2 y = F[bin_of_k(k, d)];
-        const float2 v = cmul(make_float2(y.x * fscale, y.y * fscale),
-                              rot((double)st.sto_inc * (double)((int)k - (int)(d.N_OCC / 2))));
+        const float2 v = cmul(F[bin_of_k(k, d)], wk);
+        wk = cmul(wk, wks);
         Yout[k] = v;
         Ys[k] = v;
     }
@@ -328,40 +341,50 @@ __device__ __forceinline__ float to_short(float v) {
 }
 
 // soft demapper to int16 LLRs, LLR > 0 <=> bit 1 (srsRAN demod_soft_demodulate_s restated, DESIGN.md
-// "Demapper"; called by rx_synced.cpp:997, 1287, 1297, 1322)
-__device__ void demap_cell(float2 z, uint32_t N_bps, int16_t* out) {
+// "Demapper"; called by rx_synced.cpp:997, 1287, 1297, 1322).  The N_bps LLRs of the cell come back packed two per
+// word, first LLR in the low half (BPSK: one LLR in the low half of w[0]); no dynamically indexed storage.
+__device__ __forceinline__ uint32_t pack_llr(float lo, float hi) {
+    return ((uint32_t)(uint16_t)(int16_t)lo) | ((uint32_t)(uint16_t)(int16_t)hi << 16);
+}
+__device__ __forceinline__ void demap_cell(float2 z, uint32_t N_bps, uint32_t (&w)[4]) {
+    w[1] = w[2] = w[3] = 0u;
     if (N_bps == 1) {
-        out[0] = (int16_t)to_short(-(100.f * (z.x + z.y) * 0.70710678118654752f));
+        w[0] = pack_llr(to_short(-(100.f * (z.x + z.y) * 0.70710678118654752f)), 0.f);
         return;
     }
     if (N_bps == 2) {
-        out[0] = (int16_t)to_short(z.x * (-100.f * 1.41421356237309505f));
-        out[1] = (int16_t)to_short(z.y * (-100.f * 1.41421356237309505f));
+        w[0] = pack_llr(to_short(z.x * (-100.f * 1.41421356237309505f)), to_short(z.y * (-100.f * 1.41421356237309505f)));
         return;
     }
     const float S = N_bps == 4 ? 400.f : (N_bps == 6 ? 700.f : 1000.f);
     const float nrm = N_bps == 4 ? 0.31622776601683794f : (N_bps == 6 ? 0.15430334996209191f : 0.07669649888473704f);
     const float yre = to_short(S * z.x), yim = to_short(S * z.y);
-    out[0] = (int16_t)(-yre);  // -(-32768) saturates below
-    out[1] = (int16_t)(-yim);
-    if (yre == -32768.f) out[0] = 32767;
-    if (yim == -32768.f) out[1] = 32767;
+    // -(-32768) saturates
+    w[0] = pack_llr(yre == -32768.f ? 32767.f : -yre, yim == -32768.f ? 32767.f : -yim);
     float th = (float)(N_bps == 4 ? 2 : (N_bps == 6 ? 4 : 8)) * S * nrm;
     float a0 = to_short(fabsf(yre) - th), a1 = to_short(fabsf(yim) - th);
-    out[2] = (int16_t)a0;
-    out[3] = (int16_t)a1;
-    for (uint32_t b = 4; b < N_bps; b += 2) {
+    w[1] = pack_llr(a0, a1);
+    if (N_bps >= 6) {
         th *= 0.5f;
         a0 = to_short(fabsf(a0) - th);
         a1 = to_short(fabsf(a1) - th);
-        out[b] = (int16_t)a0;
-        out[b + 1] = (int16_t)a1;
+        w[2] = pack_llr(a0, a1);
+    }
+    if (N_bps >= 8) {
+        th *= 0.5f;
+        a0 = to_short(fabsf(a0) - th);
+        a1 = to_short(fabsf(a1) - th);
+        w[3] = pack_llr(a0, a1);
     }
 }
 
 // ---- fused channel interpolation + MRC / Alamouti combining + demapping, one thread per cell (single
-// stream) or per cell pair (transmit diversity).  grid (ceil(units / 128), packets)
-__global__ void __launch_bounds__(128) k_rx_demap(const rx_params_t p, uint32_t pcc) {
+// stream) or per cell pair (transmit diversity).  grid (ceil(units / 128), packets).  A block's LLRs are one
+// contiguous span of the d-stream: they are collected in shared memory and stored as coalesced 32-bit words
+// (N_bps even; BPSK stores its int16 values directly).
+template <bool TXDIV>
+__global__ void __launch_bounds__(128, TXDIV ? 8 : 10) k_rx_demap(const rx_params_t p, uint32_t pcc) {
+    __shared__ uint32_t s_out[128 * 8];
     const phy_dims_t& d = p.d;
     const uint32_t pkt = blockIdx.y;
     const uint32_t n_cells = pcc ? 98u : d.N_PDC_subc;
@@ -369,51 +392,77 @@ __global__ void __launch_bounds__(128) k_rx_demap(const rx_params_t p, uint32_t 
     const uint32_t* lk = pcc ? d.pcc_lk : d.pdc_lk;
     int16_t* out = pcc ? p.llr_pcc + (size_t)pkt * 196 : p.llr + (size_t)pkt * p.llr_stride;
     const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
-    int16_t tmp[16];
-    if (d.N_eff_TX == 1) {
-        if (u >= n_cells) return;
-        const uint32_t l = lk[u] >> 16, k = lk[u] & 0xffffu;
-        float2 num = make_float2(0.f, 0.f);
-        float den = 0.f;
-        for (uint32_t a = 0; a < d.N_RX; ++a) {
-            const float2 y = p.Y[(((size_t)pkt * d.N_RX + a) * d.N_DF + (l - 1)) * d.Nk + k];
-            const float2 h = chan_est(p, pkt, a, 0, l, k, pcc);
-            num = cadd(num, cmulc(y, h));
-            den += h.x * h.x + h.y * h.y;
+    const uint32_t cells_per_unit = TXDIV ? 2u : 1u;
+    const uint32_t n_units = n_cells / cells_per_unit;
+    const uint32_t n_llr = cells_per_unit * N_bps;  // LLRs per thread
+    uint32_t w0[4] = {0u, 0u, 0u, 0u}, w1[4] = {0u, 0u, 0u, 0u};
+    if (u < n_units) {
+        if (!TXDIV) {
+            const uint32_t lkv = lk[u];
+            const uint32_t l = lkv >> 16, k = lkv & 0xffffu;
+            float2 num = make_float2(0.f, 0.f);
+            float den = 0.f;
+            for (uint32_t a = 0; a < d.N_RX; ++a) {
+                const float2 y = p.Y[(((size_t)pkt * d.N_RX + a) * d.N_DF + (l - 1)) * d.Nk + k];
+                const float2 h = chan_est(p, pkt, a, 0, l, k, pcc);
+                num = cadd(num, cmulc(y, h));
+                den += h.x * h.x + h.y * h.y;
+            }
+            demap_cell(make_float2(num.x / den, num.y / den), N_bps, w0);
+        } else {
+            const uint32_t q = 2 * u;
+            const uint32_t l = lk[q] >> 16, k0 = lk[q] & 0xffffu, k1 = lk[q + 1] & 0xffffu;
+            const uint32_t im = u % d.txdiv_modulo;
+            uint32_t tsA, tsB;
+            txdiv_pair_rx(d.N_eff_TX, im, tsA, tsB);
+            float2 n0 = make_float2(0.f, 0.f), n1 = n0;
+            float den = 0.f;
+            for (uint32_t a = 0; a < d.N_RX; ++a) {
+                const float2* Y = p.Y + (((size_t)pkt * d.N_RX + a) * d.N_DF + (l - 1)) * d.Nk;
+                const float2 r0 = Y[k0], r1 = Y[k1];
+                const float2 hA0 = chan_est(p, pkt, a, tsA, l, k0, pcc), hA1 = chan_est(p, pkt, a, tsA, l, k1, pcc);
+                const float2 hB0 = chan_est(p, pkt, a, tsB, l, k0, pcc), hB1 = chan_est(p, pkt, a, tsB, l, k1, pcc);
+                const float2 h0 = make_float2(0.5f * (hA0.x + hA1.x), 0.5f * (hA0.y + hA1.y));
+                const float2 h1 = make_float2(0.5f * (hB0.x + hB1.x), 0.5f * (hB0.y + hB1.y));
+                // conj(h0) r0 + h1 conj(r1)   and   -h1 conj(r0) + conj(h0) r1   (rx_synced.cpp:1372-1373)
+                n0 = cadd(n0, cadd(cmulc(r0, h0), cmulc(h1, r1)));
+                n1 = cadd(n1, csub(cmulc(r1, h0), cmulc(h1, r0)));
+                den += h0.x * h0.x + h0.y * h0.y + h1.x * h1.x + h1.y * h1.y;
+            }
+            demap_cell(make_float2(n0.x / den, n0.y / den), N_bps, w0);
+            demap_cell(make_float2(n1.x / den, n1.y / den), N_bps, w1);
         }
-        demap_cell(make_float2(num.x / den, num.y / den), N_bps, tmp);
-        for (uint32_t b = 0; b < N_bps; ++b) out[(size_t)u * N_bps + b] = tmp[b];
-    } else {
-        if (2 * u >= n_cells) return;
-        const uint32_t q = 2 * u;
-        const uint32_t l = lk[q] >> 16, k0 = lk[q] & 0xffffu, k1 = lk[q + 1] & 0xffffu;
-        const uint32_t im = u % d.txdiv_modulo;
-        uint32_t tsA, tsB;
-        txdiv_pair_rx(d.N_eff_TX, im, tsA, tsB);
-        float2 n0 = make_float2(0.f, 0.f), n1 = n0;
-        float den = 0.f;
-        for (uint32_t a = 0; a < d.N_RX; ++a) {
-            const float2* Y = p.Y + (((size_t)pkt * d.N_RX + a) * d.N_DF + (l - 1)) * d.Nk;
-            const float2 r0 = Y[k0], r1 = Y[k1];
-            const float2 hA0 = chan_est(p, pkt, a, tsA, l, k0, pcc), hA1 = chan_est(p, pkt, a, tsA, l, k1, pcc);
-            const float2 hB0 = chan_est(p, pkt, a, tsB, l, k0, pcc), hB1 = chan_est(p, pkt, a, tsB, l, k1, pcc);
-            const float2 h0 = make_float2(0.5f * (hA0.x + hA1.x), 0.5f * (hA0.y + hA1.y));
-            const float2 h1 = make_float2(0.5f * (hB0.x + hB1.x), 0.5f * (hB0.y + hB1.y));
-            // conj(h0) r0 + h1 conj(r1)   and   -h1 conj(r0) + conj(h0) r1   (rx_synced.cpp:1372-1373)
-            n0 = cadd(n0, cadd(cmulc(r0, h0), cmulc(h1, r1)));
-            n1 = cadd(n1, csub(cmulc(r1, h0), cmulc(h1, r0)));
-            den += h0.x * h0.x + h0.y * h0.y + h1.x * h1.x + h1.y * h1.y;
-        }
-        demap_cell(make_float2(n0.x / den, n0.y / den), N_bps, tmp);
-        demap_cell(make_float2(n1.x / den, n1.y / den), N_bps, tmp + N_bps);
-        for (uint32_t b = 0; b < 2 * N_bps; ++b) out[(size_t)q * N_bps + b] = tmp[b];
     }
+    if (n_llr & 1) {  // BPSK, single stream: one int16 per cell
+        if (u < n_units) out[u] = (int16_t)(w0[0] & 0xffffu);
+        return;
+    }
+    const uint32_t W = n_llr / 2;  // words per thread: 1 .. 8
+    if (u < n_units) {
+        uint32_t* so = s_out + threadIdx.x * W;
+        if (TXDIV && N_bps == 1) {
+            so[0] = (w0[0] & 0xffffu) | (w1[0] << 16);
+        } else {
+            const uint32_t wc = N_bps / 2;  // words per cell
+#pragma unroll
+            for (uint32_t i = 0; i < 4; ++i) {
+                if (i < wc) so[i] = w0[i];
+                if (TXDIV && i < wc) so[wc + i] = w1[i];
+            }
+        }
+    }
+    __syncthreads();
+    const uint32_t u0 = blockIdx.x * blockDim.x;
+    const uint32_t n_here = min(blockDim.x, n_units > u0 ? n_units - u0 : 0u);
+    uint32_t* out32 = reinterpret_cast<uint32_t*>(out) + (size_t)u0 * W;  // G even: 4-byte aligned
+    for (uint32_t i = threadIdx.x; i < n_here * W; i += blockDim.x) out32[i] = s_out[i];
 }
 
 cudaError_t launch_rx_demap(const rx_params_t& p, uint32_t n_packets, bool pcc, cudaStream_t st) {
     const uint32_t n_cells = pcc ? 98u : p.d.N_PDC_subc;
     const uint32_t units = p.d.N_eff_TX == 1 ? n_cells : n_cells / 2;
-    k_rx_demap<<<dim3((units + 127) / 128, n_packets), 128, 0, st>>>(p, pcc ? 1u : 0u);
+    if (p.d.N_eff_TX == 1) k_rx_demap<false><<<dim3((units + 127) / 128, n_packets), 128, 0, st>>>(p, pcc ? 1u : 0u);
+    else k_rx_demap<true><<<dim3((units + 127) / 128, n_packets), 128, 0, st>>>(p, pcc ? 1u : 0u);
     return cudaGetLastError();
 }
 

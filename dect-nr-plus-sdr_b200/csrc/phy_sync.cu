@@ -262,28 +262,36 @@ __global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32
     }
 }
 
-// ---- one warp per detection step: c_j = sum r[m - pat] conj(r[m]), p_j = sum abs(r[m])^2 over the step
+// ---- eight lanes per detection step, four steps per warp: c_j = sum r[m - pat] conj(r[m]), p_j = sum abs(r[m])^2 over
+// the step.  All 16-byte loads of a lane are independent (issued back to back), the reduction runs over 8 lanes.
 __global__ void __launch_bounds__(256) k_sync_steps(const sync_params_t p) {
-    const uint32_t j = blockIdx.x * 8 + (threadIdx.x >> 5), lane = threadIdx.x & 31;
+    const uint32_t lane = threadIdx.x & 31, sub = lane & 7;
+    const uint32_t j = (blockIdx.x * 8 + (threadIdx.x >> 5)) * 4 + (lane >> 3);
     const uint32_t a = blockIdx.y, pkt = blockIdx.z;
-    if (j >= p.n_steps) return;
+    const bool valid = j < p.n_steps;
     const float2* x = p.iq + ((size_t)pkt * p.d.N_RX + a) * p.iq_stride;
-    const uint32_t pat = p.d.pat_len_os, m0 = j * p.step;
+    const uint32_t pat = p.d.pat_len_os, m0 = valid ? j * p.step : 0;
     float cr = 0.f, ci = 0.f, pw = 0.f;
     // two samples per 16-byte load (steps, pattern length and window strides are even; windows are 16-byte aligned)
     const float4* xb = reinterpret_cast<const float4*>(x + m0);
     const float4* xe = reinterpret_cast<const float4*>(x + m0 - (m0 >= pat ? pat : 0));
-    for (uint32_t i = lane; i < p.step / 2; i += 32) {
+    const bool corr = m0 >= pat;
+    const uint32_t n4 = valid ? p.step / 2 : 0;
+#pragma unroll 4
+    for (uint32_t i = sub; i < n4; i += 8) {
         const float4 b = xb[i];
+        const float4 e = corr ? xe[i] : make_float4(0.f, 0.f, 0.f, 0.f);
         pw += b.x * b.x + b.y * b.y + b.z * b.z + b.w * b.w;
-        if (m0 >= pat) {
-            const float4 e = xe[i];
-            cr += e.x * b.x + e.y * b.y + e.z * b.z + e.w * b.w;
-            ci += e.y * b.x - e.x * b.y + e.w * b.z - e.z * b.w;
-        }
+        cr += e.x * b.x + e.y * b.y + e.z * b.z + e.w * b.w;
+        ci += e.y * b.x - e.x * b.y + e.w * b.z - e.z * b.w;
     }
-    cr = warp_sum(cr); ci = warp_sum(ci); pw = warp_sum(pw);
-    if (lane == 0) {
+#pragma unroll
+    for (int o = 4; o > 0; o >>= 1) {
+        cr += __shfl_xor_sync(0xffffffffu, cr, o);
+        ci += __shfl_xor_sync(0xffffffffu, ci, o);
+        pw += __shfl_xor_sync(0xffffffffu, pw, o);
+    }
+    if (sub == 0 && valid) {
         const size_t o = ((size_t)pkt * p.n_ant + a) * p.n_steps + j;
         p.c_steps[o] = make_float2(cr, ci);
         p.p_steps[o] = pw;
@@ -386,7 +394,7 @@ __global__ void __launch_bounds__(XC_THREADS) k_sync_xcorr(const sync_params_t p
 constexpr uint32_t XF_THREADS = 256, XF_MAX_PER_THREAD = 16;
 
 __global__ void __launch_bounds__(XF_THREADS) k_sync_xcorr_fft(const sync_params_t p, uint32_t len) {
-    extern __shared__ float2 smem_f[];
+    extern __shared__ __align__(16) float2 smem_f[];
     __shared__ unsigned long long s_best;
     const phy_dims_t& d = p.d;
     const uint32_t pkt = blockIdx.x, tid = threadIdx.x, N = p.xc_fft_n;
@@ -486,7 +494,7 @@ cudaError_t launch_sync(const sync_params_t& p, uint32_t n, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
     const phy_dims_t& d = p.d;
     const uint32_t len = p.len;
-    k_sync_steps<<<dim3((p.n_steps + 7) / 8, p.n_ant, n), 256, 0, st>>>(p);
+    k_sync_steps<<<dim3((p.n_steps + 31) / 32, p.n_ant, n), 256, 0, st>>>(p);
     const size_t sm_det = 3 * (size_t)(p.n_steps + 1) * sizeof(double);
     const size_t sm_peak = (3 * (size_t)(2 * d.stf_len_os + 1) + d.stf_len_os) * sizeof(float);
     const size_t sm2 = sm_det > sm_peak ? sm_det : sm_peak;

@@ -61,7 +61,7 @@ __device__ __forceinline__ float2 apply_w(int8_t w, float2 v) {
 }
 
 __global__ void __launch_bounds__(256) k_tx_ofdm(const txofdm_params_t p) {
-    extern __shared__ float2 sm[];
+    extern __shared__ __align__(16) float2 sm[];
     const phy_dims_t& d = p.d;
     const uint32_t l = blockIdx.x, ant = blockIdx.y, pkt = blockIdx.z;
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
