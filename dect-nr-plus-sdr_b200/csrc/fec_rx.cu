@@ -172,26 +172,31 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
     for (uint32_t i = tid; i < 4 * 7 * T; i += nthr) AE[i] = 0;  // AE and BS are contiguous
     __syncthreads();
 
-    // stage one K-long stream (systematic or a parity) into a window-transposed packed shared array:
-    // word (k, t) = (element t*L + k, element KH + t*L + k), both clamped to the channel range
-    // (add_ext: input of the first constituent decoder, systematic + a-priori, natural order).
-    // 8-byte loads (K/2 and every stream offset are multiples of 4 elements), several in flight per
-    // thread: a block has only three warps to cover the L2 / HBM latency.
-    auto stage = [&](uint32_t* dst, const int16_t* src, bool add_ext) {
-        const uint2* lo4 = reinterpret_cast<const uint2*>(src);
-        const uint2* hi4 = reinterpret_cast<const uint2*>(src + KH);
-#pragma unroll 4
+    // stage the parity stream of a constituent decoder (and, for the first decoder, the systematic stream plus the
+    // a-priori values in EXT) into window-transposed packed shared arrays: word (k, t) = (element t*L + k, element
+    // KH + t*L + k), channel values clamped to their range.  One loop for both streams: the address arithmetic is
+    // shared and the kernel is instruction-cache bound (less unrolling measured faster).  8-byte loads (K/2 and
+    // every stream offset are multiples of 4 elements).
+    auto stage = [&](const int16_t* par, bool with_x) {
+        const uint2* plo4 = reinterpret_cast<const uint2*>(par);
+        const uint2* phi4 = reinterpret_cast<const uint2*>(par + KH);
+        const uint2* xlo4 = reinterpret_cast<const uint2*>(soft);
+        const uint2* xhi4 = reinterpret_cast<const uint2*>(soft + KH);
+#pragma unroll 1
         for (uint32_t i4 = tid; i4 < KH / 4; i4 += nthr) {
-            const uint2 lo = lo4[i4], hi = hi4[i4];
+            const uint2 lo = plo4[i4], hi = phi4[i4];
+            uint2 xlo = make_uint2(0u, 0u), xhi = xlo;
+            if (with_x) { xlo = xlo4[i4]; xhi = xhi4[i4]; }
             const uint32_t lw[2] = {lo.x, lo.y}, hw[2] = {hi.x, hi.y};
+            const uint32_t xlw[2] = {xlo.x, xlo.y}, xhw[2] = {xhi.x, xhi.y};
 #pragma unroll
             for (int u = 0; u < 4; ++u) {
                 const uint32_t i = 4 * i4 + u;
                 const uint32_t q = __umulhi(i, cb.Linv), a = (i - q * L) * T + q;
                 // (low half: element i, high half: element i + K/2), clamped as a pair
-                uint32_t w = vclamp(__byte_perm(lw[u >> 1], hw[u >> 1], (u & 1) ? 0x7632 : 0x5410), 1023);
-                if (add_ext) w = vadd(w, EXT[a]);
-                dst[a] = w;
+                PAR[a] = vclamp(__byte_perm(lw[u >> 1], hw[u >> 1], (u & 1) ? 0x7632 : 0x5410), 1023);
+                if (with_x)
+                    XIN[a] = vadd(vclamp(__byte_perm(xlw[u >> 1], xhw[u >> 1], (u & 1) ? 0x7632 : 0x5410), 1023), EXT[a]);
             }
         }
     };
@@ -213,11 +218,10 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
 #pragma unroll 1  // one copy of the half-iteration body: the kernel is instruction-cache bound otherwise
         for (uint32_t dec = 0; dec < 2; ++dec) {
             // ---- parity of this constituent decoder -> shared, window-transposed
-            if (work) stage(PAR, soft + (1 + dec) * D, false);
-            // ---- decoder input x = systematic + a-priori, in decoder order
-            if (dec == 0) {
-                if (work) stage(XIN, soft, true);
-            } else if (active) {
+            // (first decoder: with its input x = systematic + a-priori in natural order)
+            if (work) stage(soft + (1 + dec) * D, dec == 0);
+            // ---- input of the second decoder, interleaved order
+            if (dec != 0 && active) {
                 const uint32_t j0 = t * L;
                 uint32_t pi = (uint32_t)(((uint64_t)cb.f1 * j0 + (uint64_t)cb.f2 * j0 * j0) % K);
                 uint32_t g = (uint32_t)((cb.f1 + (uint64_t)cb.f2 * (2 * j0 + 1)) % K);
@@ -228,7 +232,7 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
                     const uint32_t pw = up ? pi - KH : pi;
                     const uint32_t q = __umulhi(pw, cb.Linv);
                     const uint32_t a = (pw - q * L) * T + q;
-                    uint32_t w = vadd(pack(clampi(soft[pw], 1023), clampi(soft[pw + KH], 1023)), EXT[a]);
+                    uint32_t w = EXT[a];  // systematic + extrinsic, left there by the first decoder's LLR pass
                     if (up) w = swap16(w);
                     XIN[k * T + t] = w;
                     pi += g; if (pi >= K) pi -= K;
@@ -241,7 +245,7 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
             if (active) {
                 // ---- termination metrics of this decoder (three tail steps back from state 0)
                 int tail[8];
-                {
+                {   // (computed by every thread: restricting it to the windows at the trellis end measured slower)
                     const int16_t* d0 = soft; const int16_t* d1 = soft + D; const int16_t* d2 = soft + 2 * D;
                     int xt[3], zt[3];
                     if (dec == 0) {
@@ -400,7 +404,9 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
                             const uint32_t l = llr_step(a, bb[i], x, y);
                             const uint32_t e = vclamp(vsub(l, x), 2047);
                             if (dec == 0) {
-                                EXT[k * T + t] = e;
+                                // x = systematic + a-priori (EXT): store extrinsic + systematic, the second decoder's
+                                // input in natural order -- its gather then reads shared memory only
+                                EXT[k * T + t] = vadd(e, vsub(x, EXT[k * T + t]));
                             } else {
                                 const bool up = pi >= KH;
                                 const uint32_t pw = up ? pi - KH : pi;
@@ -437,7 +443,8 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
         if (work) ++n_iter;
         {
             uint32_t r = 0;
-            if (active) {
+            // below the minimum iteration count the remainder cannot stop the decoder: not computed (crc_mode 0)
+            if (active && (p.crc_mode != 0 || n_iter >= p.min_it)) {
                 uint32_t r_lo = 0, r_hi = 0;
                 const uint32_t top = 1u << cb.crc_order;
                 for (uint32_t k = 0; k < L; ++k) {
