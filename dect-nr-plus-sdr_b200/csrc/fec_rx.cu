@@ -127,6 +127,7 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
                                                       uint32_t n_items) {
     extern __shared__ uint32_t smem_all[];
     __shared__ uint32_t s_crc_all[128];
+    __shared__ int s_tail_all[(GROUPED ? 128 : 1) * 16];
     const uint32_t grp = GROUPED ? threadIdx.x / tg : 0;
     const uint32_t tid = GROUPED ? threadIdx.x % tg : threadIdx.x, nthr = GROUPED ? tg : blockDim.x;
     const uint32_t item = GROUPED ? blockIdx.x * (blockDim.x / tg) + grp : blockIdx.x;
@@ -135,6 +136,7 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
     const cb_desc_t cb = p.cbs[cbi];
     uint32_t* smem = smem_all + (size_t)grp * smem_item_words;
     uint32_t& s_crc = s_crc_all[grp];
+    int* s_tail = s_tail_all + grp * 16;
     const uint32_t slot = p.slot ? p.slot[pkt] : pkt;
     const uint32_t K = cb.K, L = cb.L, T = cb.P / 2, KH = K / 2, D = K + 4;
     const uint32_t nck = (L + S_CK - 1) / S_CK;
@@ -170,6 +172,31 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
     const int16_t* soft = p.soft + (size_t)slot * p.soft_stride + cb.soft_off;
     for (uint32_t i = tid; i < KH; i += nthr) EXT[i] = 0;
     for (uint32_t i = tid; i < 4 * 7 * T; i += nthr) AE[i] = 0;  // AE and BS are contiguous
+    // ---- termination metrics of the two constituent decoders (three tail steps back from state 0), thread dec of
+    // the group computes those of decoder dec (a one-thread group both)
+    for (uint32_t dec = tid; dec < 2 && !done; dec += nthr) {
+        const int16_t* d0 = soft; const int16_t* d1 = soft + D; const int16_t* d2 = soft + 2 * D;
+        int xt[3], zt[3];
+        if (dec == 0) {
+            xt[0] = d0[K]; zt[0] = d1[K]; xt[1] = d2[K]; zt[1] = d0[K + 1]; xt[2] = d1[K + 1]; zt[2] = d2[K + 1];
+        } else {
+            xt[0] = d0[K + 2]; zt[0] = d1[K + 2]; xt[1] = d2[K + 2]; zt[1] = d0[K + 3]; xt[2] = d1[K + 3]; zt[2] = d2[K + 3];
+        }
+        int b[8], nb[8];
+#pragma unroll
+        for (int s = 0; s < 8; ++s) b[s] = s == 0 ? 0 : -8192;
+#pragma unroll
+        for (int tt = 2; tt >= 0; --tt) {
+            const int x = clampi(xt[tt], 1023), z = clampi(zt[tt], 1023);
+            // allowed transition: u = s1^s2 (a = 0), parity z = s0^s2, next = (0, s0, s1)
+            nb[0] = b[0];          nb[1] = b[0] + x + z;  nb[2] = b[1] + x;      nb[3] = b[1] + z;
+            nb[4] = b[2] + z;      nb[5] = b[2] + x;      nb[6] = b[3] + x + z;  nb[7] = b[3];
+#pragma unroll
+            for (int s = 0; s < 8; ++s) b[s] = nb[s] - nb[0];
+        }
+#pragma unroll
+        for (int s = 0; s < 8; ++s) s_tail[dec * 8 + s] = b[s];
+    }
     __syncthreads();
 
     // stage the parity stream of a constituent decoder (and, for the first decoder, the systematic stream plus the
@@ -203,6 +230,12 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
 
     const uint32_t t = tid;
     const uint32_t wl = t, wh = t + T, P = cb.P;
+    // QPP position pi(j0) of this thread's first step j0 = t * L and its first difference g = pi(j0 + 1) - pi(j0)
+    // (second difference g2 = 2 f2): the 64-bit reductions are done once per code block, not per half iteration
+    const uint32_t qpp_j0 = t * L;
+    const uint32_t qpp_pi0 = (uint32_t)(((uint64_t)cb.f1 * qpp_j0 + (uint64_t)cb.f2 * qpp_j0 * qpp_j0) % K);
+    const uint32_t qpp_g0 = (uint32_t)((cb.f1 + (uint64_t)cb.f2 * (2 * qpp_j0 + 1)) % K);
+    const uint32_t qpp_g2 = (2 * cb.f2) % K;
     uint32_t n_iter = 0;
     bool crc_ok = false;
     uint32_t plcf_mask = 0;
@@ -222,10 +255,8 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
             if (work) stage(soft + (1 + dec) * D, dec == 0);
             // ---- input of the second decoder, interleaved order
             if (dec != 0 && active) {
-                const uint32_t j0 = t * L;
-                uint32_t pi = (uint32_t)(((uint64_t)cb.f1 * j0 + (uint64_t)cb.f2 * j0 * j0) % K);
-                uint32_t g = (uint32_t)((cb.f1 + (uint64_t)cb.f2 * (2 * j0 + 1)) % K);
-                const uint32_t g2 = (2 * cb.f2) % K;
+                uint32_t pi = qpp_pi0, g = qpp_g0;
+                const uint32_t g2 = qpp_g2;
 #pragma unroll 4
                 for (uint32_t k = 0; k < L; ++k) {
                     const bool up = pi >= KH;
@@ -244,30 +275,10 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
             uint32_t ae_new[8], bs_new[8];
             if (active) {
                 // ---- termination metrics of this decoder (three tail steps back from state 0)
+                // termination metrics of this decoder, computed once per code block (s_tail)
                 int tail[8];
-                {   // (computed by every thread: restricting it to the windows at the trellis end measured slower)
-                    const int16_t* d0 = soft; const int16_t* d1 = soft + D; const int16_t* d2 = soft + 2 * D;
-                    int xt[3], zt[3];
-                    if (dec == 0) {
-                        xt[0] = d0[K]; zt[0] = d1[K]; xt[1] = d2[K]; zt[1] = d0[K + 1]; xt[2] = d1[K + 1]; zt[2] = d2[K + 1];
-                    } else {
-                        xt[0] = d0[K + 2]; zt[0] = d1[K + 2]; xt[1] = d2[K + 2]; zt[1] = d0[K + 3]; xt[2] = d1[K + 3]; zt[2] = d2[K + 3];
-                    }
-                    int b[8], nb[8];
 #pragma unroll
-                    for (int s = 0; s < 8; ++s) b[s] = s == 0 ? 0 : -8192;
-#pragma unroll
-                    for (int tt = 2; tt >= 0; --tt) {
-                        const int x = clampi(xt[tt], 1023), z = clampi(zt[tt], 1023);
-                        // allowed transition: u = s1^s2 (a = 0), parity z = s0^s2, next = (0, s0, s1)
-                        nb[0] = b[0];          nb[1] = b[0] + x + z;  nb[2] = b[1] + x;      nb[3] = b[1] + z;
-                        nb[4] = b[2] + z;      nb[5] = b[2] + x;      nb[6] = b[3] + x + z;  nb[7] = b[3];
-#pragma unroll
-                        for (int s = 0; s < 8; ++s) b[s] = nb[s] - nb[0];
-                    }
-#pragma unroll
-                    for (int s = 0; s < 8; ++s) tail[s] = b[s];
-                }
+                for (int s = 0; s < 8; ++s) tail[s] = s_tail[dec * 8 + s];
                 const uint32_t* BSd = BS + dec * 7 * T;
                 const uint32_t* AEd = AE + dec * 7 * T;
                 // boundary metric of window v as int16: word v (low half) for v < T, word v - T (high half)
@@ -365,10 +376,8 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
 #pragma unroll
                 for (int s = 0; s < 8; ++s) bs_new[s] = b[s];
                 // QPP position of the first step of this thread (decoder 2 scatters to natural order)
-                const uint32_t j0 = t * L;
-                uint32_t pi = (uint32_t)(((uint64_t)cb.f1 * j0 + (uint64_t)cb.f2 * j0 * j0) % K);
-                uint32_t g = (uint32_t)((cb.f1 + (uint64_t)cb.f2 * (2 * j0 + 1)) % K);
-                const uint32_t g2 = (2 * cb.f2) % K;
+                uint32_t pi = qpp_pi0, g = qpp_g0;
+                const uint32_t g2 = qpp_g2;
                 // one chunk of S_CK steps; FULL = compile-time knowledge that the chunk is complete (always the case when
                 // L is a multiple of S_CK, e.g. L = 32): no per-step bounds predicates in the unrolled body
                 auto chunk = [&](uint32_t c, auto full_tag) {
