@@ -58,7 +58,7 @@ uint32_t gf2_xpow_host(uint32_t n, uint32_t poly, uint32_t order);
 
 struct fec_plan_t {
     // rate matching / CRC-combination tables shared by all code block sizes of the plan
-    std::vector<uint16_t> rm_arena;   // per K: src[N] then pos[N]
+    std::vector<uint16_t> rm_arena;   // per K: src[N], then pos[N] in the decoder soft-buffer order (plan_fec.cu)
     std::vector<uint32_t> xp_arena;
     std::vector<cb_desc_t> rx_cbs;    // PDC decode descriptors [C]
     std::vector<txcb_desc_t> tx_cbs;  // PDC encode descriptors [C]

@@ -125,7 +125,7 @@ cudaError_t launch_derm(const tdec_params_t& p, uint32_t n_packets, uint32_t max
 template <bool GROUPED>
 __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_decode(const tdec_params_t p, uint32_t tg, uint32_t smem_item_words,
                                                       uint32_t n_items) {
-    extern __shared__ uint32_t smem_all[];
+    extern __shared__ __align__(16) uint32_t smem_all[];
     __shared__ uint32_t s_crc_all[128];
     __shared__ int s_tail_all[(GROUPED ? 128 : 1) * 16];
     const uint32_t grp = GROUPED ? threadIdx.x / tg : 0;
@@ -168,19 +168,21 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
     uint32_t* BS = AE + 2 * 7 * T;           // [2][7][T]
     uint8_t* HARD = (uint8_t*)(BS + 2 * 7 * T);  // [KH]
 
-    // soft buffer of this code block, written by k_derm: d0 | d1 | d2, each D = K + 4 int16
+    // soft buffer of this code block, written by k_derm in the layout of plan_fec.cu: three streams of K/2 packed
+    // words in shared-array order, then the 12 termination values
     const int16_t* soft = p.soft + (size_t)slot * p.soft_stride + cb.soft_off;
     for (uint32_t i = tid; i < KH; i += nthr) EXT[i] = 0;
     for (uint32_t i = tid; i < 4 * 7 * T; i += nthr) AE[i] = 0;  // AE and BS are contiguous
     // ---- termination metrics of the two constituent decoders (three tail steps back from state 0), thread dec of
     // the group computes those of decoder dec (a one-thread group both)
     for (uint32_t dec = tid; dec < 2 && !done; dec += nthr) {
-        const int16_t* d0 = soft; const int16_t* d1 = soft + D; const int16_t* d2 = soft + 2 * D;
+        // termination values d_s[K + j] at soft[3 K + 4 s + j] (plan_fec.cu)
+        const int16_t* d0 = soft + 3 * K; const int16_t* d1 = d0 + 4; const int16_t* d2 = d0 + 8;
         int xt[3], zt[3];
         if (dec == 0) {
-            xt[0] = d0[K]; zt[0] = d1[K]; xt[1] = d2[K]; zt[1] = d0[K + 1]; xt[2] = d1[K + 1]; zt[2] = d2[K + 1];
+            xt[0] = d0[0]; zt[0] = d1[0]; xt[1] = d2[0]; zt[1] = d0[1]; xt[2] = d1[1]; zt[2] = d2[1];
         } else {
-            xt[0] = d0[K + 2]; zt[0] = d1[K + 2]; xt[1] = d2[K + 2]; zt[1] = d0[K + 3]; xt[2] = d1[K + 3]; zt[2] = d2[K + 3];
+            xt[0] = d0[2]; zt[0] = d1[2]; xt[1] = d2[2]; zt[1] = d0[3]; xt[2] = d1[3]; zt[2] = d2[3];
         }
         int b[8], nb[8];
 #pragma unroll
@@ -200,30 +202,23 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
     __syncthreads();
 
     // stage the parity stream of a constituent decoder (and, for the first decoder, the systematic stream plus the
-    // a-priori values in EXT) into window-transposed packed shared arrays: word (k, t) = (element t*L + k, element
-    // KH + t*L + k), channel values clamped to their range.  One loop for both streams: the address arithmetic is
-    // shared and the kernel is instruction-cache bound (less unrolling measured faster).  8-byte loads (K/2 and
-    // every stream offset are multiples of 4 elements).
-    auto stage = [&](const int16_t* par, bool with_x) {
-        const uint2* plo4 = reinterpret_cast<const uint2*>(par);
-        const uint2* phi4 = reinterpret_cast<const uint2*>(par + KH);
-        const uint2* xlo4 = reinterpret_cast<const uint2*>(soft);
-        const uint2* xhi4 = reinterpret_cast<const uint2*>(soft + KH);
-#pragma unroll 1
+    // a-priori values in EXT) into the shared arrays, clamped to the channel range.  k_derm wrote the streams in the
+    // layout of the shared arrays (plan_fec.cu: word a = k * T + t), so this is a straight 16-byte copy.
+    auto clamp4 = [](uint4 v) {
+        return make_uint4(vclamp(v.x, 1023), vclamp(v.y, 1023), vclamp(v.z, 1023), vclamp(v.w, 1023));
+    };
+    auto stage = [&](uint32_t stream, bool with_x) {
+        const uint4* p4 = reinterpret_cast<const uint4*>(soft + (size_t)stream * K);
+        const uint4* x4 = reinterpret_cast<const uint4*>(soft);
+        uint4* PAR4 = reinterpret_cast<uint4*>(PAR);
+        uint4* XIN4 = reinterpret_cast<uint4*>(XIN);
+        const uint4* EXT4 = reinterpret_cast<const uint4*>(EXT);
+#pragma unroll 1  // measured: any unrolling here is slower (instruction-cache bound kernel)
         for (uint32_t i4 = tid; i4 < KH / 4; i4 += nthr) {
-            const uint2 lo = plo4[i4], hi = phi4[i4];
-            uint2 xlo = make_uint2(0u, 0u), xhi = xlo;
-            if (with_x) { xlo = xlo4[i4]; xhi = xhi4[i4]; }
-            const uint32_t lw[2] = {lo.x, lo.y}, hw[2] = {hi.x, hi.y};
-            const uint32_t xlw[2] = {xlo.x, xlo.y}, xhw[2] = {xhi.x, xhi.y};
-#pragma unroll
-            for (int u = 0; u < 4; ++u) {
-                const uint32_t i = 4 * i4 + u;
-                const uint32_t q = __umulhi(i, cb.Linv), a = (i - q * L) * T + q;
-                // (low half: element i, high half: element i + K/2), clamped as a pair
-                PAR[a] = vclamp(__byte_perm(lw[u >> 1], hw[u >> 1], (u & 1) ? 0x7632 : 0x5410), 1023);
-                if (with_x)
-                    XIN[a] = vadd(vclamp(__byte_perm(xlw[u >> 1], xhw[u >> 1], (u & 1) ? 0x7632 : 0x5410), 1023), EXT[a]);
+            PAR4[i4] = clamp4(p4[i4]);
+            if (with_x) {
+                const uint4 x = clamp4(x4[i4]), e = EXT4[i4];
+                XIN4[i4] = make_uint4(vadd(x.x, e.x), vadd(x.y, e.y), vadd(x.z, e.z), vadd(x.w, e.w));
             }
         }
     };
@@ -252,7 +247,7 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
         for (uint32_t dec = 0; dec < 2; ++dec) {
             // ---- parity of this constituent decoder -> shared, window-transposed
             // (first decoder: with its input x = systematic + a-priori in natural order)
-            if (work) stage(soft + (1 + dec) * D, dec == 0);
+            if (work) stage(1 + dec, dec == 0);
             // ---- input of the second decoder, interleaved order
             if (dec != 0 && active) {
                 uint32_t pi = qpp_pi0, g = qpp_g0;

@@ -45,7 +45,10 @@ uint32_t gf2_xpow_host(uint32_t n, uint32_t poly, uint32_t order) {
 
 int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
     const spec::cbsegm_t& s = ps.seg;
-    std::map<uint32_t, uint32_t> rm_off;  // K -> offset of src[] (pos[] follows at +N)
+    // K -> offset of src[] (transmitter: circular buffer position -> source bit); the receiver's table follows at +N:
+    // pos[] in the order of the DECODER's soft-buffer layout (soft_layout_index below), so that k_derm, which walks
+    // table and soft buffer in lockstep, writes the streams exactly as k_turbo_decode stages them
+    std::map<uint32_t, uint32_t> rm_off;
     std::map<uint32_t, spec::rm_table_t> rm_tab;
     auto add_rm = [&](uint32_t K) {
         if (rm_off.count(K)) return;
@@ -53,7 +56,20 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         spec::build_rm_table(K, t);
         rm_off[K] = (uint32_t)f.rm_arena.size();
         f.rm_arena.insert(f.rm_arena.end(), t.src.begin(), t.src.end());
-        f.rm_arena.insert(f.rm_arena.end(), t.pos.begin(), t.pos.end());
+        // soft buffer of a code block (3K + 12 int16): three streams d0 d1 d2 of K/2 words, word a = k * T + t =
+        // (element t*L + k | element K/2 + t*L + k << 16) -- the window-transposed pair packing of the decoder's shared
+        // arrays --, then the 12 termination values d0[K..K+3] d1[K..K+3] d2[K..K+3]
+        const uint32_t L = tdec_window(K), T = K / L / 2, KH = K / 2, D = K + 4;
+        std::vector<uint16_t> posT(3 * D);
+        for (uint32_t st = 0; st < 3; ++st) {
+            for (uint32_t a = 0; a < KH; ++a) {
+                const uint32_t k = a / T, tt = a % T, i = tt * L + k;
+                posT[st * K + 2 * a] = t.pos[st * D + i];
+                posT[st * K + 2 * a + 1] = t.pos[st * D + i + KH];
+            }
+            for (uint32_t j = 0; j < 4; ++j) posT[3 * K + 4 * st + j] = t.pos[st * D + K + j];
+        }
+        f.rm_arena.insert(f.rm_arena.end(), posT.begin(), posT.end());
         rm_tab[K] = t;
     };
     auto add_xp = [&](uint32_t K, uint32_t L, uint32_t poly, uint32_t order) -> uint32_t {
@@ -126,7 +142,7 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         r.saved_off = saved_off;
         f.rx_cbs.push_back(r);
         out_byte += rlen / 8;
-        soft_off += 3 * (K + 4);
+        soft_off += (3 * (K + 4) + 7) & ~7u;  // code blocks start 16-byte aligned (16-byte loads in the decoder)
         saved_off += rlen / 8;
     }
     if (wp_tx != ps.G || rp_tx != s.tbs) return DNRP_ERR_INVALID;
