@@ -31,7 +31,7 @@ __device__ __forceinline__ uint32_t gf2_mulmod(uint32_t a, uint32_t b, uint32_t 
 // The code block's LLRs are first descrambled into shared memory with coalesced loads; the table driven
 // gather then reads shared memory.  cap = int16 capacity of the dynamic shared buffer.
 __global__ void __launch_bounds__(256) k_derm(const tdec_params_t p, uint32_t cap) {
-    extern __shared__ uint32_t smem[];
+    extern __shared__ __align__(16) uint32_t smem[];
     const cb_desc_t cb = p.cbs[blockIdx.x];
     const uint32_t pkt = blockIdx.y;
     const uint32_t slot = p.slot ? p.slot[pkt] : pkt;
@@ -44,8 +44,7 @@ __global__ void __launch_bounds__(256) k_derm(const tdec_params_t p, uint32_t ca
 
     int16_t* soft = p.soft + (size_t)slot * p.soft_stride + cb.soft_off;
     const int16_t* llr = p.llr + (size_t)pkt * p.llr_stride + cb.rp;
-    const uint16_t* rm_pos = p.rm_arena + cb.rm_off;
-    const uint32_t rm_start = cb.rm_start[rv];
+    const uint16_t* rm_pos = p.rm_arena + cb.rm_off + (size_t)rv * N;  // table of this redundancy version
     int16_t* DSC = (int16_t*)smem;
     const bool staged = cb.n_e <= cap;
     // rate >= 1/3 (n_e <= N) and room for N entries: zero pad the staged LLRs up to N, every circular-buffer
@@ -76,8 +75,13 @@ __global__ void __launch_bounds__(256) k_derm(const tdec_params_t p, uint32_t ca
         } else {
             for (uint32_t e = tid; e < cb.n_e; e += nthr) DSC[e] = (int16_t)descr(e, llr[e]);
         }
-        if (single)
-            for (uint32_t e = cb.n_e + tid; e < N; e += nthr) DSC[e] = 0;
+        if (single) {  // zero padding: a few int16 up to the next 16-byte boundary, then 16-byte stores
+            const uint32_t z8 = min((cb.n_e + 7u) & ~7u, N);
+            for (uint32_t e = cb.n_e + tid; e < z8; e += nthr) DSC[e] = 0;
+            uint4* Z = reinterpret_cast<uint4*>(DSC);
+            for (uint32_t e8 = z8 / 8 + tid; e8 < N / 8; e8 += nthr) Z[e8] = make_uint4(0u, 0u, 0u, 0u);
+            for (uint32_t e = (N & ~7u) + tid; e < N; e += nthr) if (e >= z8) DSC[e] = 0;
+        }
         __syncthreads();
     }
     // four consecutive circular-buffer positions per thread: 8-byte table loads and soft-buffer stores (N is a
@@ -95,14 +99,14 @@ __global__ void __launch_bounds__(256) k_derm(const tdec_params_t p, uint32_t ca
         int acc[4];
 #pragma unroll
         for (int u = 0; u < 4; ++u) {
-            const uint32_t v = pos[u] + N - rm_start;
+            const uint32_t v = pos[u];
             acc[u] = prev[u];
             if (single) {
-                acc[u] += DSC[v >= N ? v - N : v];
+                acc[u] += DSC[v];
             } else if (staged) {
-                for (uint32_t ee = v >= N ? v - N : v; ee < cb.n_e; ee += N) acc[u] += DSC[ee];
+                for (uint32_t ee = v; ee < cb.n_e; ee += N) acc[u] += DSC[ee];
             } else {
-                for (uint32_t ee = v >= N ? v - N : v; ee < cb.n_e; ee += N) acc[u] += descr(ee, llr[ee]);
+                for (uint32_t ee = v; ee < cb.n_e; ee += N) acc[u] += descr(ee, llr[ee]);
             }
         }
         soft4[q] = make_uint2(((uint32_t)acc[0] & 0xffffu) | ((uint32_t)acc[1] << 16),

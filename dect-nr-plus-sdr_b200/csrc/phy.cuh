@@ -31,6 +31,7 @@ struct phy_dims_t {
     // receiver
     uint32_t chestim_lr, chestim_stride;    // phy.json chestim_mode_lr_default / _t_stride_default
     uint32_t n_full_ps;                     // full processing stages in lr mode (rx_synced.cpp:1031-1032)
+    uint32_t N_step_inv, chestim_stride_inv;  // ceil(2^32 / x): i / x == __umulhi(i, inv) for the symbol indices used
     uint32_t pcc_l_max;                     // last OFDM symbol carrying PCC cells
     struct wiener_dev_t {
         const uint16_t* idx_pilot;          // [n_t][4][Nk]

@@ -280,7 +280,7 @@ __device__ float2 chan_est(const rx_params_t& p, uint32_t pkt, uint32_t a, uint3
     float2 h = make_float2(0.f, 0.f);
     if (pcc_stage || !d.chestim_lr || d.n_full_ps == 0) {
         // mode "l": DRS occurrence n at or before symbol l, non-interlaced pilots, LUT slot 0
-        uint32_t n = (l - 1) / d.N_step;
+        uint32_t n = __umulhi(l - 1, d.N_step_inv);  // (l - 1) / N_step
         if (n >= d.n_drs) n = d.n_drs - 1;
         const uint32_t j = d.N_eff_TX == 8 ? 2 * n + (ts >= 4 ? 1 : 0) : n;
         const phy_dims_t::wiener_dev_t& W = d.wiener_l[cls[j]];
@@ -296,13 +296,14 @@ __device__ float2 chan_est(const rx_params_t& p, uint32_t pkt, uint32_t a, uint3
         // mode "lr": processing stage ps between DRS occurrences ps (left) and ps + 1 (right)
         uint32_t ps = 0, r = 0;
         if (l > 1) {
-            ps = (l - 2) / d.N_step;
+            ps = __umulhi(l - 2, d.N_step_inv);  // (l - 2) / N_step
             if (ps > d.n_full_ps - 1) ps = d.n_full_ps - 1;
             r = l - 1 - ps * d.N_step;
         }
         const uint32_t rs = ps == 0 ? 0 : 1;
         const uint32_t re = r < d.N_step ? r : d.N_step;
-        const uint32_t rstar = rs + ((re - rs) / d.chestim_stride) * d.chestim_stride;
+        // rs + floor((re - rs) / stride) * stride
+        const uint32_t rstar = d.chestim_stride_inv ? rs + __umulhi(re - rs, d.chestim_stride_inv) * d.chestim_stride : re;
         const uint32_t j = d.N_eff_TX == 8 ? 2 * (ps + 1) + 1 : ps + 1;
         const phy_dims_t::wiener_dev_t& W = d.wiener_lr[cls[j]];
         const uint32_t pc = ((ts & 3) + 2 * (ps & 1)) & 3;

@@ -20,20 +20,31 @@ __device__ __forceinline__ float warp_sum(float v) {
     return v;
 }
 
+// exclusive offsets of the per-thread partial sums v (one per thread, blockDim.x <= 1024): warp shuffle scan, warp
+// totals through s_part[32 * slot ...]; returns the sum of the partials of all lower threads.  All threads call.
+template <typename F>
+__device__ __forceinline__ F block_exclusive(F v, F* s_part) {
+    const uint32_t lane = threadIdx.x & 31, w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    F inc = v;
+    for (int o = 1; o < 32; o <<= 1) {
+        const F u = __shfl_up_sync(0xffffffffu, inc, o);
+        if (lane >= (uint32_t)o) inc += u;
+    }
+    if (lane == 31) s_part[w] = inc;
+    __syncthreads();
+    F off = inc - v;
+    for (uint32_t i = 0; i < nw; ++i) if (i < w) off += s_part[i];
+    __syncthreads();
+    return off;
+}
+
 // inclusive block-wide prefix sum of a double array in shared memory, in place (n arbitrary)
 __device__ void block_scan(double* a, uint32_t n, double* s_part) {
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
     const uint32_t per = (n + nthr - 1) / nthr, lo = min(tid * per, n), hi = min(lo + per, n);
     double s = 0.0;
     for (uint32_t i = lo; i < hi; ++i) { s += a[i]; a[i] = s; }
-    s_part[tid] = s;
-    __syncthreads();
-    if (tid == 0) {
-        double acc = 0.0;
-        for (uint32_t t = 0; t < nthr; ++t) { const double v = s_part[t]; s_part[t] = acc; acc += v; }
-    }
-    __syncthreads();
-    const double off = s_part[tid];
+    const double off = block_exclusive(s, s_part);
     for (uint32_t i = lo; i < hi; ++i) a[i] += off;
     __syncthreads();
 }
@@ -157,16 +168,9 @@ __global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32
                 }
                 Qr[i + 1] = sr; Qi[i + 1] = si; PW[i + 1] = sp;
             }
-            float* part = reinterpret_cast<float*>(s_part);  // [3][nthr]
-            part[tid] = sr; part[nthr + tid] = si; part[2 * nthr + tid] = sp;
-            __syncthreads();
-            if (tid < 3) {
-                float acc = 0.f;
-                for (uint32_t t = 0; t < nthr; ++t) { const float v = part[tid * nthr + t]; part[tid * nthr + t] = acc; acc += v; }
-            }
+            float* part = reinterpret_cast<float*>(s_part);
             if (tid == 0) { Qr[0] = Qi[0] = PW[0] = 0.f; }
-            __syncthreads();
-            const float o_r = part[tid], o_i = part[nthr + tid], o_p = part[2 * nthr + tid];
+            const float o_r = block_exclusive(sr, part), o_i = block_exclusive(si, part + 32), o_p = block_exclusive(sp, part + 64);
             for (uint32_t i = lo; i < hi; ++i) { Qr[i + 1] += o_r; Qi[i + 1] += o_i; PW[i + 1] += o_p; }
             __syncthreads();
             for (uint32_t k = tid; k < stf_len; k += nthr) {
@@ -409,15 +413,17 @@ __global__ void __launch_bounds__(XF_THREADS) k_sync_xcorr_fft(const sync_params
     float2* B = smem_f + N;
     const float2* x = p.iq_x + ((size_t)pkt * d.N_RX + res.strongest_ant) * p.x_stride + w0;
     const double inc = (double)((res.cfo_fractional_rad + res.cfo_integer_rad) * (float)p.rs_M / (float)p.rs_L);
+    // CFO pre-rotation: one double-precision phasor per thread, then a float rotation by XF_THREADS samples per
+    // iteration (at most 16 of them)
+    double sd, cd;
+    sincos(inc * (double)tid, &sd, &cd);
+    float2 w = make_float2((float)cd, (float)sd);
+    sincos(inc * (double)XF_THREADS, &sd, &cd);
+    const float2 ws = make_float2((float)cd, (float)sd);
     for (uint32_t i = tid; i < N; i += XF_THREADS) {
         float2 r = make_float2(0.f, 0.f);
-        if (i < n_mix) {
-            const float2 v = x[i];
-            double sd, cd;
-            sincos(inc * (double)i, &sd, &cd);
-            const float cs = (float)cd, sn = (float)sd;
-            r = make_float2(v.x * cs - v.y * sn, v.x * sn + v.y * cs);
-        }
+        if (i < n_mix) r = cmul(x[i], w);
+        w = cmul(w, ws);
         A[i] = r;
     }
     const float2* X = block_fft<false>(A, B, N, p.xc_twiddle);

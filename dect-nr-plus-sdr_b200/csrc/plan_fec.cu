@@ -45,8 +45,8 @@ uint32_t gf2_xpow_host(uint32_t n, uint32_t poly, uint32_t order) {
 
 int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
     const spec::cbsegm_t& s = ps.seg;
-    // K -> offset of src[] (transmitter: circular buffer position -> source bit); the receiver's table follows at +N:
-    // pos[] in the order of the DECODER's soft-buffer layout (soft_layout_index below), so that k_derm, which walks
+    // K -> offset of src[] (transmitter: circular buffer position -> source bit); the receiver's tables follow at +N
+    // (four, one per redundancy version): pos[] in the order of the DECODER's soft-buffer layout (soft_layout_index below), so that k_derm, which walks
     // table and soft buffer in lockstep, writes the streams exactly as k_turbo_decode stages them
     std::map<uint32_t, uint32_t> rm_off;
     std::map<uint32_t, spec::rm_table_t> rm_tab;
@@ -69,7 +69,11 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
             }
             for (uint32_t j = 0; j < 4; ++j) posT[3 * K + 4 * st + j] = t.pos[st * D + K + j];
         }
-        f.rm_arena.insert(f.rm_arena.end(), posT.begin(), posT.end());
+        // one copy per redundancy version with the start offset folded in: entry = index of the received LLR (mod N,
+        // first pass over the circular buffer) that lands on this soft-buffer position
+        const uint32_t N = 3 * D;
+        for (int rv = 0; rv < 4; ++rv)
+            for (uint32_t n = 0; n < N; ++n) f.rm_arena.push_back((uint16_t)((posT[n] + N - t.start[rv]) % N));
         rm_tab[K] = t;
     };
     auto add_xp = [&](uint32_t K, uint32_t L, uint32_t poly, uint32_t order) -> uint32_t {

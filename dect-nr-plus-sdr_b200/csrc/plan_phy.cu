@@ -112,6 +112,8 @@ int build_phy_plan(dnrp_ctx* c) {
     // ---- receiver
     d.chestim_lr = c->cfg.chestim_mode_lr ? 1 : 0;
     d.chestim_stride = c->cfg.chestim_mode_lr_t_stride ? c->cfg.chestim_mode_lr_t_stride : 1;
+    d.N_step_inv = (uint32_t)(((1ull << 32) + d.N_step - 1) / d.N_step);
+    d.chestim_stride_inv = d.chestim_stride > 1 ? (uint32_t)(((1ull << 32) + d.chestim_stride - 1) / d.chestim_stride) : 0;
     {
         // rx_synced.cpp:1027-1032: stage length 6 / 11 / 12 symbols for N_step 5 / 10 / 10 (N_eff_TX 8)
         const uint32_t ps_len = d.N_eff_TX <= 2 ? 6 : (d.N_eff_TX == 4 ? 11 : 12);
