@@ -10,8 +10,10 @@
 //   upper/tpoint.hpp:128-170 (work_pcc, work_pdc, work_pdc_error)
 //   phy/pool/worker_tx_rx.cpp:117-240 (order of calls: work_pcc FIFO by job order, PDC only if continue_with_pdc,
 //   hp_rx->finalize(crc_status) after the callback, TX descriptors generated afterwards)
-// Not mirrored (out of scope, MAC layer): sp4::plcf_decoder_t / mac_pdu_decoder_t field codecs -- the reports carry
-// the raw PLCF / transport block bytes the reference's decoders would be fed with.
+//   sections_part4/physical_header_field/*.hpp (plcf_10/20/21_t, feedback info, plcf_decoder_t): dnrp_plcf.hpp;
+//   pcc_report_t::decode_plcf() runs rx_synced.cpp:1011-1026 on the bytes the device delivered
+// Not mirrored (out of scope, MAC layer): sp4::mac_pdu_decoder_t -- pdc_report_t carries the transport block bytes
+// the reference's MAC PDU decoder would be fed with.
 // There is no CPU fallback: construction throws if libdnrp_cuda.so cannot create its context.
 #pragma once
 #include <array>
@@ -27,6 +29,7 @@
 extern "C" {
 #include "dnrp_c_api.h"
 }
+#include "dnrp_plcf.hpp"
 
 namespace dectnrp_b200 {
 
@@ -270,6 +273,14 @@ struct pcc_report_t {
     /// nullptr if that type did not pass its CRC (plcf_decoder_t::get_plcf_base semantics)
     const uint8_t* get_plcf_bytes(uint32_t PLCF_type) const {
         return (PLCF_type == 1 || PLCF_type == 2) && plcf_ok[PLCF_type - 1] ? plcf[PLCF_type - 1].data() : nullptr;
+    }
+    /// rx_synced_t::run_pcc_decoding_and_candidate_search (rx_synced.cpp:1011-1026): every type whose CRC passed is
+    /// unpacked and checked against the radio device class; returns plcf_decoder.has_any_plcf()
+    uint32_t decode_plcf(sp4::plcf_decoder_t& plcf_decoder) const {
+        plcf_decoder.set_configuration();
+        for (uint32_t type = 1; type <= 2; ++type)
+            if (plcf_ok[type - 1]) plcf_decoder.decode_and_rdc_check(type, plcf[type - 1].data());
+        return plcf_decoder.has_any_plcf();
     }
 };
 

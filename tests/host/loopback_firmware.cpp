@@ -21,10 +21,16 @@ struct firmware_t final : public upper::tpoint_t {
         order.push_back(in.sync_report.fine_peak_time_64);
         const uint8_t* plcf = in.pcc_report.get_plcf_bytes(1);
         if (!plcf) return phy::maclow_phy_t();
-        const uint32_t key = plcf[1] | (plcf[2] << 8);            // the firmware's own packet tag inside the PLCF
+        // field decoding + radio device class check like rx_synced.cpp:1011-1026, then tfw_loopback-style reading
+        if (in.pcc_report.decode_plcf(plcf_decoder) != 1) { ++n_plcf_mismatch; return phy::maclow_phy_t(); }
+        const auto* p10 = static_cast<const sp4::plcf_10_t*>(plcf_decoder.get_plcf_base(1));
+        const uint32_t key = p10->TransmitterIdentity;             // the firmware's packet tag
         auto it = sent.find(key);
         if (it == sent.end()) return phy::maclow_phy_t();
-        if (std::memcmp(plcf, it->second.plcf, 5) != 0) ++n_plcf_mismatch;
+        if (std::memcmp(plcf, it->second.plcf, 5) != 0 || p10->ShortNetworkID != (network_id & 0xff) ||
+            p10->get_PacketLength() != packet_sizes.psdef.PacketLength || p10->DFMCS != packet_sizes.psdef.mcs_index ||
+            p10->get_TransmitPower_dBm() != 10 || p10->get_N_SS() != 1)
+            ++n_plcf_mismatch;
         phy::harq::process_rx_t* hp;
         auto run = running_rx.find(key);
         if (run != running_rx.end()) {
@@ -51,6 +57,21 @@ struct firmware_t final : public upper::tpoint_t {
     }
 
     struct sent_t { uint8_t plcf[10]; std::vector<uint8_t> tb; uint32_t rv; };
+    /// PLCF type 1 of a packet like tfw_loopback.cpp:253-289; tag = TransmitterIdentity (bytes 2, 3)
+    void make_plcf(uint8_t* a, uint32_t tag) const {
+        sp4::plcf_10_t p;
+        p.HeaderFormat = 0;
+        p.PacketLengthType = packet_sizes.psdef.PacketLengthType;
+        p.set_PacketLength_m1((int32_t)packet_sizes.psdef.PacketLength);
+        p.ShortNetworkID = network_id & 0xff;
+        p.TransmitterIdentity = tag;
+        p.set_TransmitPower(10);
+        p.DFMCS = packet_sizes.psdef.mcs_index;
+        std::memset(a, 0, 10);
+        p.pack(a);
+    }
+    static uint32_t key_of(const uint8_t* a) { return ((uint32_t)a[2] << 8) | a[3]; }
+    sp4::plcf_decoder_t plcf_decoder{16, 11, 8};
     sp3::packet_sizes_t packet_sizes;
     phy::harq::process_pool_t pool;
     phy::harq::finalize_rx_t frx{phy::harq::finalize_rx_t::keep_running_or_reset_and_terminate_if_crc_correct};
@@ -85,7 +106,7 @@ int main(int argc, char** argv) {
     auto transmit = [&](std::vector<phy::harq::process_tx_t*>& procs, float snr_dB, uint64_t seed) {
         std::vector<phy::tx_descriptor_t> descs;
         for (auto* hp : procs) descs.emplace_back(*hp, 0, tx_meta, radio::buffer_tx_meta_t{});
-        for (auto* hp : procs) fw.sent[hp->get_a_plcf()[1] | (hp->get_a_plcf()[2] << 8)].rv = hp->get_rv();
+        for (auto* hp : procs) fw.sent[firmware_t::key_of(hp->get_a_plcf())].rv = hp->get_rv();
         bp->generate_tx_packets(descs, nullptr);
         std::vector<dnrp_channel_desc_t> ch(procs.size());
         std::vector<int64_t> start(procs.size());
@@ -106,12 +127,12 @@ int main(int argc, char** argv) {
         auto* hp = fw.pool.get_process_tx(1, fw.network_id, ps.psdef, phy::harq::finalize_tx_t::reset_and_terminate);
         if (!hp) { ++fails; break; }
         firmware_t::sent_t s{};
-        s.plcf[0] = 0x20; s.plcf[1] = (uint8_t)i; s.plcf[2] = 1; s.plcf[3] = (uint8_t)rng(); s.plcf[4] = (uint8_t)rng();
+        fw.make_plcf(s.plcf, (1u << 8) | (i + 1));
         s.tb.resize(ps.N_TB_byte);
         for (auto& v : s.tb) v = (uint8_t)rng();
         std::memcpy(hp->get_a_plcf(), s.plcf, 10);
         std::memcpy(hp->get_a_tb(), s.tb.data(), ps.N_TB_byte);
-        fw.sent[s.plcf[1] | (s.plcf[2] << 8)] = s;
+        fw.sent[firmware_t::key_of(s.plcf)] = s;
         procs.push_back(hp);
     }
     transmit(procs, 28.0f, 11);
@@ -126,12 +147,12 @@ int main(int argc, char** argv) {
     for (uint32_t i = 0; i < m; ++i) {
         auto* hp = fw.pool.get_process_tx(1, fw.network_id, ps.psdef, phy::harq::finalize_tx_t::increase_rv_and_keep_running);
         firmware_t::sent_t s{};
-        s.plcf[0] = 0x20; s.plcf[1] = (uint8_t)i; s.plcf[2] = 2;
+        fw.make_plcf(s.plcf, (2u << 8) | (i + 1));
         s.tb.resize(ps.N_TB_byte);
         for (auto& v : s.tb) v = (uint8_t)rng();
         std::memcpy(hp->get_a_plcf(), s.plcf, 10);
         std::memcpy(hp->get_a_tb(), s.tb.data(), ps.N_TB_byte);
-        fw.sent[s.plcf[1] | (s.plcf[2] << 8)] = s;
+        fw.sent[firmware_t::key_of(s.plcf)] = s;
         procs.push_back(hp);
     }
     uint32_t rounds = 0;
@@ -139,7 +160,7 @@ int main(int argc, char** argv) {
     while (fw.n_work_pdc - pdc_before < m && rounds < 4) {
         std::vector<phy::harq::process_tx_t*> todo;
         for (auto* hp : procs)
-            if (fw.running_rx.count(hp->get_a_plcf()[1] | (2u << 8)) || rounds == 0) todo.push_back(hp);
+            if (fw.running_rx.count(firmware_t::key_of(hp->get_a_plcf())) || rounds == 0) todo.push_back(hp);
         if (todo.empty()) break;
         transmit(todo, 5.0f, 100 + rounds);   // 16-QAM 3/4 on two antennas does not decode at 5 dB in one shot
         ++rounds;
