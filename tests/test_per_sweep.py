@@ -1,0 +1,99 @@
+"""PER sweep tool (per_sweep.py, BASELINE.json configs[4]).  CPU: cell partition and the counter-matrix reduction over two
+gloo ranks, result files in the reference's rx_loopback_MCS_xxxx layout.  GPU: a small sweep on one device -- every
+CRC-passing transport block equals the transmitted one, PER falls with SNR, low-SNR points lose packets."""
+import json
+import os
+import socket
+import subprocess
+import sys
+
+import numpy as np
+import pytest
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+
+
+def _free_port():
+    s = socket.socket()
+    s.bind(("127.0.0.1", 0))
+    p = s.getsockname()[1]
+    s.close()
+    return p
+
+
+def _fake_row(ps, ci, n):
+    """deterministic counters of cell ci (stands in for the device pipeline in the CPU test)"""
+    ok = n - (ci * 7) % n
+    row = np.zeros(len(ps.COUNTERS), dtype=np.int64)
+    row[:ps.SUMMED] = [n, n, n - 1, ok, ok, ok - 1 if ok else 0, ok - 1 if ok else 0, 12 * n, 1000 * ci * max(ok - 1, 0)]
+    row[ps.SUMMED], row[ps.SUMMED + 1] = (1000 * ci - 5, 1000 * ci + 5) if ok > 1 else (ps.BIG, -ps.BIG)
+    return row
+
+
+def _worker(rank, world, port, q):
+    sys.path.insert(0, ROOT)
+    import per_sweep as ps
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    cells = ps.sweep_cells([0, 1], [1, 2, 3], [0.0, 5.0, 10.0, 15.0, 20.0])
+    mine = ps.cells_of_rank(len(cells), rank, world)
+    mat = ps.neutral_matrix(len(cells))
+    for ci in mine:
+        mat[ci] = _fake_row(ps, ci, 100)
+    out = ps.reduce_matrix(mat, world, "cpu")
+    q.put((rank, mine, out.tolist()))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_cells_are_partitioned_and_reduced_over_two_ranks():
+    import per_sweep as ps
+    world, port = 2, _free_port()
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    procs = [ctx.Process(target=_worker, args=(r, world, port, q)) for r in range(world)]
+    for p in procs:
+        p.start()
+    res = sorted(q.get(timeout=120) for _ in range(world))
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    (_, mine0, m0), (_, mine1, m1) = res
+    n_cells = 2 * 3 * 5
+    assert sorted(mine0 + mine1) == list(range(n_cells)) and not set(mine0) & set(mine1)
+    expect = np.stack([_fake_row(ps, ci, 100) for ci in range(n_cells)])
+    assert np.array_equal(np.array(m0), expect) and np.array_equal(np.array(m1), expect)
+
+
+def test_result_files_follow_the_reference_layout():
+    import per_sweep as ps
+    snr = [0.0, 5.0, 10.0]
+    cells = ps.sweep_cells([0], [2, 4], snr)
+    mat = np.stack([_fake_row(ps, ci, 50) for ci in range(len(cells))])
+    files = ps.result_files(cells, mat, 50, [0], [2, 4], snr)
+    assert sorted(files) == ["rx_loopback_MCS_0002", "rx_loopback_MCS_0004"]      # tfw_loopback_snr.cpp:163
+    j = files["rx_loopback_MCS_0004"]
+    assert j["experiment_range"] == {"snr_vec": snr, "nof_experiment_per_snr": 50} and j["parameter"]["mcs"] == 4
+    for k in ("snr_max_vec", "snr_min_vec", "PER_pcc_crc", "PER_pcc_crc_and_plcf", "PER_pdc_crc"):   # :174-178
+        assert len(j["result"][k]) == 3
+    ci = 3   # first cell of MCS 4
+    assert j["result"]["PER_pdc_crc"][0] == pytest.approx(1.0 - mat[ci, 5] / 50)
+    json.dumps(files)
+
+
+@pytest.mark.gpu
+def test_small_sweep_on_one_gpu(tmp_path):
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "per_sweep.py"), "--beta", "1", "--mcs", "1", "3", "--snr", "-4", "16", "4",
+                        "--packets", "200", "--out", str(tmp_path)], capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    s = json.loads(r.stdout.strip().splitlines()[-1])
+    assert s["cells"] == 12 and s["packets"] == 2400 and s["tb_mismatch_after_crc_ok"] == 0
+    for mcs in (1, 3):
+        j = json.load(open(tmp_path / ("rx_loopback_MCS_%04d.json" % mcs)))
+        per = j["result"]["PER_pdc_crc"]
+        assert per[0] > 0.5 and per[-1] < 0.02, per                       # -4 dB loses packets, 16 dB does not
+        assert all(per[i + 1] <= per[i] + 0.05 for i in range(len(per) - 1)), per
+        assert all(a <= b + 1e-9 for a, b in zip(j["result"]["PER_pcc_crc"], j["result"]["PER_pcc_crc_and_plcf"]))
