@@ -272,14 +272,18 @@ __global__ void k_rx_snr_class(const rx_params_t p, uint32_t n_packets) {
 // rx_synced_t::run_drs_ch_interpolation (rx_synced.cpp:893-960) holds in chestim[ts][k] at the moment
 // the reference collects the cells of symbol l.  Closed form of the processing stage bookkeeping of
 // rx_synced.cpp:1027-1152, see DESIGN.md "Receiver: which interpolation serves which symbol".
-__device__ float2 chan_est(const rx_params_t& p, uint32_t pkt, uint32_t a, uint32_t ts, uint32_t l, uint32_t k,
-                           bool pcc_stage) {
+// All NRX receive antennas at once: h[a] = estimate seen by antenna a.  Symbol plan, LUT indices and the weights are
+// the same for every antenna, so they are computed / loaded once and every tap is applied to the NRX pilot sets.
+template <int NRX>
+__device__ __forceinline__ void chan_est_rx(const rx_params_t& p, uint32_t pkt, uint32_t ts, uint32_t l, uint32_t k,
+                                            bool pcc_stage, float2 (&h)[NRX]) {
     const phy_dims_t& d = p.d;
     const uint8_t* cls = p.cls + (size_t)pkt * p.cls_stride;
-    const float2* hz_ts = p.hzf + (((size_t)pkt * d.N_RX + a) * d.N_eff_TX + ts) * d.n_drs * d.NP;
-    float2 h = make_float2(0.f, 0.f);
+    const size_t stride_a = (size_t)d.N_eff_TX * d.n_drs * d.NP;    // pilots of the next antenna
+    const float2* hz_ts = p.hzf + (((size_t)pkt * d.N_RX) * d.N_eff_TX + ts) * d.n_drs * d.NP;
+#pragma unroll
+    for (int a = 0; a < NRX; ++a) h[a] = make_float2(0.f, 0.f);
     if (pcc_stage || !d.chestim_lr || d.n_full_ps == 0) {
-        // mode "l": DRS occurrence n at or before symbol l, non-interlaced pilots, LUT slot 0
         uint32_t n = __umulhi(l - 1, d.N_step_inv);  // (l - 1) / N_step
         if (n >= d.n_drs) n = d.n_drs - 1;
         const uint32_t j = d.N_eff_TX == 8 ? 2 * n + (ts >= 4 ? 1 : 0) : n;
@@ -289,11 +293,15 @@ __device__ float2 chan_est(const rx_params_t& p, uint32_t pkt, uint32_t a, uint3
         const float* w = W.weights + (size_t)W.idx_weight[o] * W.n_interp;
         const float2* hz = hz_ts + (size_t)n * d.NP + W.idx_pilot[o];
         for (uint32_t i = 0; i < W.n_interp; ++i) {
-            h.x += w[i] * hz[i].x;
-            h.y += w[i] * hz[i].y;
+            const float wi = w[i];
+#pragma unroll
+            for (int a = 0; a < NRX; ++a) {
+                const float2 v = hz[a * stride_a + i];
+                h[a].x += wi * v.x;
+                h[a].y += wi * v.y;
+            }
         }
     } else {
-        // mode "lr": processing stage ps between DRS occurrences ps (left) and ps + 1 (right)
         uint32_t ps = 0, r = 0;
         if (l > 1) {
             ps = __umulhi(l - 2, d.N_step_inv);  // (l - 2) / N_step
@@ -302,7 +310,6 @@ __device__ float2 chan_est(const rx_params_t& p, uint32_t pkt, uint32_t a, uint3
         }
         const uint32_t rs = ps == 0 ? 0 : 1;
         const uint32_t re = r < d.N_step ? r : d.N_step;
-        // rs + floor((re - rs) / stride) * stride
         const uint32_t rstar = d.chestim_stride_inv ? rs + __umulhi(re - rs, d.chestim_stride_inv) * d.chestim_stride : re;
         const uint32_t j = d.N_eff_TX == 8 ? 2 * (ps + 1) + 1 : ps + 1;
         const phy_dims_t::wiener_dev_t& W = d.wiener_lr[cls[j]];
@@ -311,15 +318,20 @@ __device__ float2 chan_est(const rx_params_t& p, uint32_t pkt, uint32_t a, uint3
         const float* w = W.weights + (size_t)W.idx_weight[o] * W.n_interp;
         const uint32_t m0 = W.idx_pilot[o];
         const uint32_t flip = pc >= 2 ? 1 : 0;
+        const float2* hz_ps = hz_ts + (size_t)ps * d.NP;
         for (uint32_t i = 0; i < W.n_interp; ++i) {
             const uint32_t m = m0 + i;
             const uint32_t side = (m & 1) ^ flip;
-            const float2 v = hz_ts[(size_t)(ps + side) * d.NP + (m >> 1)];
-            h.x += w[i] * v.x;
-            h.y += w[i] * v.y;
+            const float2* hz = hz_ps + (size_t)side * d.NP + (m >> 1);
+            const float wi = w[i];
+#pragma unroll
+            for (int a = 0; a < NRX; ++a) {
+                const float2 v = hz[a * stride_a];
+                h[a].x += wi * v.x;
+                h[a].y += wi * v.y;
+            }
         }
     }
-    return h;
 }
 
 // transmit stream pair of Alamouti pair index i_mod (Table 6.3.3.2, reference
@@ -383,8 +395,8 @@ __device__ __forceinline__ void demap_cell(float2 z, uint32_t N_bps, uint32_t (&
 // stream) or per cell pair (transmit diversity).  grid (ceil(units / 128), packets).  A block's LLRs are one
 // contiguous span of the d-stream: they are collected in shared memory and stored as coalesced 32-bit words
 // (N_bps even; BPSK stores its int16 values directly).
-template <bool TXDIV>
-__global__ void __launch_bounds__(128, TXDIV ? 8 : 10) k_rx_demap(const rx_params_t p, uint32_t pcc) {
+template <bool TXDIV, int NRX>
+__global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_demap(const rx_params_t p, uint32_t pcc) {
     __shared__ uint32_t s_out[128 * 8];
     const phy_dims_t& d = p.d;
     const uint32_t pkt = blockIdx.y;
@@ -403,11 +415,13 @@ __global__ void __launch_bounds__(128, TXDIV ? 8 : 10) k_rx_demap(const rx_param
             const uint32_t l = lkv >> 16, k = lkv & 0xffffu;
             float2 num = make_float2(0.f, 0.f);
             float den = 0.f;
-            for (uint32_t a = 0; a < d.N_RX; ++a) {
-                const float2 y = p.Y[(((size_t)pkt * d.N_RX + a) * d.N_DF + (l - 1)) * d.Nk + k];
-                const float2 h = chan_est(p, pkt, a, 0, l, k, pcc);
-                num = cadd(num, cmulc(y, h));
-                den += h.x * h.x + h.y * h.y;
+            float2 h[NRX];
+            chan_est_rx<NRX>(p, pkt, 0, l, k, pcc, h);
+#pragma unroll
+            for (int a = 0; a < NRX; ++a) {
+                const float2 y = p.Y[(((size_t)pkt * NRX + a) * d.N_DF + (l - 1)) * d.Nk + k];
+                num = cadd(num, cmulc(y, h[a]));
+                den += h[a].x * h[a].x + h[a].y * h[a].y;
             }
             demap_cell(make_float2(num.x / den, num.y / den), N_bps, w0);
         } else {
@@ -418,17 +432,27 @@ __global__ void __launch_bounds__(128, TXDIV ? 8 : 10) k_rx_demap(const rx_param
             txdiv_pair_rx(d.N_eff_TX, im, tsA, tsB);
             float2 n0 = make_float2(0.f, 0.f), n1 = n0;
             float den = 0.f;
-            for (uint32_t a = 0; a < d.N_RX; ++a) {
-                const float2* Y = p.Y + (((size_t)pkt * d.N_RX + a) * d.N_DF + (l - 1)) * d.Nk;
+            // per antenna: h0 = mean of stream A's estimates at the two cells, h1 = the same for stream B
+            float2 h0[NRX], h1[NRX];
+            {
+                float2 t[NRX];
+                chan_est_rx<NRX>(p, pkt, tsA, l, k0, pcc, h0);
+                chan_est_rx<NRX>(p, pkt, tsA, l, k1, pcc, t);
+#pragma unroll
+                for (int a = 0; a < NRX; ++a) h0[a] = make_float2(0.5f * (h0[a].x + t[a].x), 0.5f * (h0[a].y + t[a].y));
+                chan_est_rx<NRX>(p, pkt, tsB, l, k0, pcc, h1);
+                chan_est_rx<NRX>(p, pkt, tsB, l, k1, pcc, t);
+#pragma unroll
+                for (int a = 0; a < NRX; ++a) h1[a] = make_float2(0.5f * (h1[a].x + t[a].x), 0.5f * (h1[a].y + t[a].y));
+            }
+#pragma unroll
+            for (int a = 0; a < NRX; ++a) {
+                const float2* Y = p.Y + (((size_t)pkt * NRX + a) * d.N_DF + (l - 1)) * d.Nk;
                 const float2 r0 = Y[k0], r1 = Y[k1];
-                const float2 hA0 = chan_est(p, pkt, a, tsA, l, k0, pcc), hA1 = chan_est(p, pkt, a, tsA, l, k1, pcc);
-                const float2 hB0 = chan_est(p, pkt, a, tsB, l, k0, pcc), hB1 = chan_est(p, pkt, a, tsB, l, k1, pcc);
-                const float2 h0 = make_float2(0.5f * (hA0.x + hA1.x), 0.5f * (hA0.y + hA1.y));
-                const float2 h1 = make_float2(0.5f * (hB0.x + hB1.x), 0.5f * (hB0.y + hB1.y));
                 // conj(h0) r0 + h1 conj(r1)   and   -h1 conj(r0) + conj(h0) r1   (rx_synced.cpp:1372-1373)
-                n0 = cadd(n0, cadd(cmulc(r0, h0), cmulc(h1, r1)));
-                n1 = cadd(n1, csub(cmulc(r1, h0), cmulc(h1, r0)));
-                den += h0.x * h0.x + h0.y * h0.y + h1.x * h1.x + h1.y * h1.y;
+                n0 = cadd(n0, cadd(cmulc(r0, h0[a]), cmulc(h1[a], r1)));
+                n1 = cadd(n1, csub(cmulc(r1, h0[a]), cmulc(h1[a], r0)));
+                den += h0[a].x * h0[a].x + h0[a].y * h0[a].y + h1[a].x * h1[a].x + h1[a].y * h1[a].y;
             }
             demap_cell(make_float2(n0.x / den, n0.y / den), N_bps, w0);
             demap_cell(make_float2(n1.x / den, n1.y / den), N_bps, w1);
@@ -462,8 +486,19 @@ __global__ void __launch_bounds__(128, TXDIV ? 8 : 10) k_rx_demap(const rx_param
 cudaError_t launch_rx_demap(const rx_params_t& p, uint32_t n_packets, bool pcc, cudaStream_t st) {
     const uint32_t n_cells = pcc ? 98u : p.d.N_PDC_subc;
     const uint32_t units = p.d.N_eff_TX == 1 ? n_cells : n_cells / 2;
-    if (p.d.N_eff_TX == 1) k_rx_demap<false><<<dim3((units + 127) / 128, n_packets), 128, 0, st>>>(p, pcc ? 1u : 0u);
-    else k_rx_demap<true><<<dim3((units + 127) / 128, n_packets), 128, 0, st>>>(p, pcc ? 1u : 0u);
+    const dim3 grid((units + 127) / 128, n_packets);
+    const uint32_t pf = pcc ? 1u : 0u;
+    const bool txdiv = p.d.N_eff_TX != 1;
+#define DNRP_DEMAP(NRX)                                                          \
+    case NRX:                                                                    \
+        if (txdiv) k_rx_demap<true, NRX><<<grid, 128, 0, st>>>(p, pf);           \
+        else k_rx_demap<false, NRX><<<grid, 128, 0, st>>>(p, pf);                \
+        break;
+    switch (p.d.N_RX) {
+        DNRP_DEMAP(1) DNRP_DEMAP(2) DNRP_DEMAP(4) DNRP_DEMAP(8)
+        default: return cudaErrorInvalidValue;   // N_RX is 1, 2, 4 or 8 (radio device classes)
+    }
+#undef DNRP_DEMAP
     return cudaGetLastError();
 }
 
