@@ -104,6 +104,10 @@ SYNC_RESULT_DTYPE = np.dtype([("detected", "u4"), ("detection_time_local", "u4")
                               ("fine_peak_time_local", "u4"), ("n_detections", "u4"), ("strongest_ant", "u4"),
                               ("coarse_peak_time_hw", "u4")], align=True)
 assert SYNC_RESULT_DTYPE.itemsize == 116
+# dnrp_stream_packet_t
+STREAM_PACKET_DTYPE = np.dtype({"names": ["fine_peak_time_64", "coarse_peak_time_64", "sync", "chunk", "round"],
+                                "formats": ["i8", "i8", SYNC_RESULT_DTYPE, "u4", "u4"],
+                                "offsets": [0, 8, 16, 132, 136], "itemsize": 144})
 
 
 def build(verbose=False):
@@ -281,6 +285,25 @@ class Phy:
         _check(lib().dnrp_sync_batch(self._ctx, n, _ptr(iq, np.complex64), int(search_length),
                                      None if out is None else out.ctypes.data_as(C.c_void_p)))
         return out
+
+    # ---- streaming front door (worker_sync_t / sync_chunk_t / baton_t): packet search over one continuous stream
+    def stream_sync(self, iq, chunk_hop=0, max_out=None):
+        """iq [N_RX][n_samples] complex64 host stream; returns the unique packets in time order (STREAM_PACKET_DTYPE)"""
+        iq = np.ascontiguousarray(iq, dtype=np.complex64)
+        assert iq.ndim == 2 and iq.shape[0] == self.N_RX, iq.shape
+        n_samples = iq.shape[1]
+        if max_out is None:
+            max_out = n_samples // max(self.ps["N_samples_STF"], 1) + 1
+        out = np.zeros(max_out, dtype=STREAM_PACKET_DTYPE)
+        n_out = C.c_uint32(0)
+        _check(lib().dnrp_stream_sync(self._ctx, C.c_uint64(n_samples), _ptr(iq, np.complex64), int(chunk_hop), int(max_out),
+                                      out.ctypes.data_as(C.c_void_p), C.byref(n_out)))
+        return out[:n_out.value].view(np.recarray)
+
+    def stream_extract(self, start_64, t0):
+        """windows of the synced receiver <- stream[start - t0, start - t0 + rx_stride) for every start (device copy)"""
+        start = np.ascontiguousarray(start_64, dtype=np.int64)
+        _check(lib().dnrp_stream_extract(self._ctx, len(start), start.ctypes.data_as(C.c_void_p), int(t0)))
 
     def rx_pdc(self, n, harq_slot=None, rv=None, harq_reset=None, tb_out=None):
         tb = np.zeros((n, self.ps["N_TB_byte"]), dtype=np.uint8) if tb_out is None else tb_out

@@ -162,6 +162,15 @@ struct dnrp_ctx {
     dnrp::dbuf<float> d_sync_p;
     dnrp::dbuf<dnrp::sync_result_dev_t> d_sync_result;
 
+    // streaming front door (api_stream.cu): the stream on the device, per-chunk work buffers (grown on demand)
+    dnrp::dbuf<float2> d_stream;                // [N_RX][stream_alloc] zero padded behind the last sample
+    size_t stream_alloc = 0, stream_len = 0;    // samples per antenna allocated / valid
+    uint32_t stream_chunks_alloc = 0, stream_steps_alloc = 0;
+    dnrp::dbuf<float2> d_stream_c, d_stream_xc;
+    dnrp::dbuf<float> d_stream_p;
+    dnrp::dbuf<dnrp::sync_result_dev_t> d_stream_result;
+    dnrp::dbuf<uint32_t> d_stream_resume;
+
     // measurement: launch counter and optional per-kernel event timers (dnrp_kernel_time_*)
     uint64_t launches = 0;
     bool ktime_on = false;

@@ -172,7 +172,21 @@ struct sync_params_t {
     float2* xc;                            // [packet][n_tpl] (max abs(xcorr), lag)
     sync_result_dev_t* result;             // [packet]
     rx_state_t* rx_state;                  // [packet] optional: receives t0 / CFO / rms for the synced receiver
+    // streaming front door (dnrp_stream_sync): "packets" are overlapping chunks of one continuous stream
+    // [N_RX][iq_stride]; chunk c starts iq_pkt_stride samples after chunk c - 1 (0: dense windows as above)
+    size_t iq_pkt_stride, x_pkt_stride;
+    const uint32_t* resume;                // [packet] optional: first sample the detection may end on (skip_after_peak);
+                                           // 0xffffffff = chunk finished
 };
+// first sample of antenna a of window / chunk pkt
+__device__ __forceinline__ const float2* sync_iq(const sync_params_t& p, uint32_t pkt, uint32_t a) {
+    return p.iq + (p.iq_pkt_stride ? (size_t)pkt * p.iq_pkt_stride + (size_t)a * p.iq_stride
+                                   : ((size_t)pkt * p.d.N_RX + a) * p.iq_stride);
+}
+__device__ __forceinline__ const float2* sync_iq_x(const sync_params_t& p, uint32_t pkt, uint32_t a) {
+    return p.iq_x + (p.x_pkt_stride ? (size_t)pkt * p.x_pkt_stride + (size_t)a * p.x_stride
+                                    : ((size_t)pkt * p.d.N_RX + a) * p.x_stride);
+}
 cudaError_t launch_sync(const sync_params_t& p, uint32_t n_packets, cudaStream_t st);
 
 // simulation channel (phy_channel.cu)

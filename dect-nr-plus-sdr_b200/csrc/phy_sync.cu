@@ -80,8 +80,18 @@ __global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32
     for (uint32_t i = 0; i + 1 < n_pat; ++i) uw[i] = c_cover[i] * c_cover[i + 1];
 
     uint32_t j_from = (stf_len + pat + step - 1) / step - 1;  // first step whose end reaches ignore_before_index
+    if (p.resume) {  // continuation inside a chunk: autocorrelator_detection_t::skip_after_peak moved ignore_before_index
+        const uint32_t r = p.resume[pkt];
+        if (r == 0xffffffffu) {
+            if (tid == 0) { res.detected = 0; res.n_detections = 0; }
+            return;
+        }
+        const uint32_t jr = r ? (r + step - 1) / step - 1 : 0;
+        if (jr > j_from) j_from = jr;
+    }
     uint32_t n_det_total = 0;
-    for (uint32_t attempt = 0; attempt < 8; ++attempt) {
+    uint32_t attempt = 0;
+    for (; attempt < 8; ++attempt) {
         // ---- detection: first (step, antenna) passing the gates
         uint32_t best_j = 0xffffffffu, best_a = 0;
         float best_metric = 0.f, best_rms = 0.f;
@@ -154,7 +164,7 @@ __global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32
         uint32_t peak_index[8];
         const uint32_t sm_right = bos, sm_len = 2 * bos + 1;
         for (uint32_t a = 0; a < p.n_ant; ++a) {
-            const float2* x = p.iq + ((size_t)pkt * d.N_RX + a) * p.iq_stride + A0;
+            const float2* x = sync_iq(p, pkt, a) + A0;
             // serial prefix per thread chunk + chunk offsets (three arrays at once)
             const uint32_t per = (S2 + nthr - 1) / nthr, lo = min(tid * per, S2), hi = min(lo + per, S2);
             float sr = 0.f, si = 0.f, sp = 0.f;
@@ -225,7 +235,7 @@ __global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32
         for (uint32_t a = 0; a < p.n_ant; ++a) {
             if (cpa[a] <= 0.f) continue;
             if (cpa[a] > cpa[strongest]) strongest = a;
-            const float2* x = p.iq + ((size_t)pkt * d.N_RX + a) * p.iq_stride + coarse;
+            const float2* x = sync_iq(p, pkt, a) + coarse;
             float3 acc = make_float3(0.f, 0.f, 0.f);
             for (uint32_t i = tid; i < stf_len; i += nthr) {
                 const float2 b = x[i];
@@ -260,6 +270,8 @@ __global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32
     if (tid == 0) {
         res.detected = 0;
         res.n_detections = n_det_total;
+        // streaming search: all attempts ended in invalid peaks, the chunk is not used up -- where to go on
+        res.detection_time_local = (p.resume && attempt == 8) ? (j_from + 1) * step : 0;
         res.N_eff_TX = 0; res.fine_peak_time_local = 0; res.coarse_peak_time_local = 0; res.coarse_peak_time_hw = 0;
         res.cfo_fractional_rad = 0.f; res.cfo_integer_rad = 0.f; res.strongest_ant = 0;
         for (uint32_t a = 0; a < 8; ++a) { res.coarse_peak_array[a] = 0.f; res.rms_array[a] = 0.f; }
@@ -273,7 +285,7 @@ __global__ void __launch_bounds__(256) k_sync_steps(const sync_params_t p) {
     const uint32_t j = (blockIdx.x * 8 + (threadIdx.x >> 5)) * 4 + (lane >> 3);
     const uint32_t a = blockIdx.y, pkt = blockIdx.z;
     const bool valid = j < p.n_steps;
-    const float2* x = p.iq + ((size_t)pkt * p.d.N_RX + a) * p.iq_stride;
+    const float2* x = sync_iq(p, pkt, a);
     const uint32_t pat = p.d.pat_len_os, m0 = valid ? j * p.step : 0;
     float cr = 0.f, ci = 0.f, pw = 0.f;
     // two samples per 16-byte load (steps, pattern length and window strides are even; windows are 16-byte aligned)
@@ -327,7 +339,7 @@ __global__ void __launch_bounds__(XC_THREADS) k_sync_xcorr(const sync_params_t p
     float2* mix = smem_x;                              // [xc_pos(n_lag_pad + S_pad)]
     float2* tp = mix + xc_pos(n_lag_pad + S_pad) + 1;  // [S_pad]
     float2* part = tp + S_pad;                         // [IC][n_lag_pad]
-    const float2* x = p.iq_x + ((size_t)pkt * d.N_RX + res.strongest_ant) * p.x_stride + w0;
+    const float2* x = sync_iq_x(p, pkt, res.strongest_ant) + w0;
     // the CFO was measured at the DECT rate; per hardware sample it is smaller by M / L (crosscorrelator.cpp:97-105)
     const double inc = (double)((res.cfo_fractional_rad + res.cfo_integer_rad) * (float)p.rs_M / (float)p.rs_L);
     const uint32_t n_mix = n_lag + S - 1;
@@ -411,7 +423,7 @@ __global__ void __launch_bounds__(XF_THREADS) k_sync_xcorr_fft(const sync_params
     }
     float2* A = smem_f;
     float2* B = smem_f + N;
-    const float2* x = p.iq_x + ((size_t)pkt * d.N_RX + res.strongest_ant) * p.x_stride + w0;
+    const float2* x = sync_iq_x(p, pkt, res.strongest_ant) + w0;
     const double inc = (double)((res.cfo_fractional_rad + res.cfo_integer_rad) * (float)p.rs_M / (float)p.rs_L);
     // CFO pre-rotation: one double-precision phasor per thread, then a float rotation by XF_THREADS samples per
     // iteration (at most 16 of them)

@@ -195,6 +195,29 @@ typedef struct {
 int dnrp_sync_batch(dnrp_ctx_t* ctx, uint32_t n, const dnrp_cf32_t* iq_in, uint32_t search_length,
                     dnrp_sync_result_t* out);
 
+/* Streaming front door: packet search over ONE continuous IQ stream instead of pre-cut windows -- the job of
+ * worker_sync_t / sync_chunk_t / baton_t (lib/src/phy/pool/worker_sync.cpp:112-221, src/phy/rx/sync/sync_chunk.cpp:
+ * 146-283, src/phy/pool/baton.cpp:157-169).  The stream is cut into chunks of chunk_hop samples (0: four packet
+ * lengths) that overlap by one STF + one pattern of history in front and the peak / cross-correlation range behind;
+ * all chunks are searched in parallel; a chunk that found a packet continues behind it (skip_after_peak: 2 STFs) in
+ * the next round until its detection range is used up; results are ordered by time and double detections closer than
+ * one STF pattern to their predecessor are dropped (RX_SYNC_PARAM_SYNC_TIME_UNIQUE_LIMIT_IN_STF_PATTERNS_DP).
+ * iq [N_RX][n_samples] host samples at the hardware rate (contexts without resampling only).  The stream stays on
+ * the device for dnrp_stream_extract.  out [max_out]: times are sample indices of the stream. */
+typedef struct {
+    int64_t fine_peak_time_64;         /* first sample of the packet (STF start) */
+    int64_t coarse_peak_time_64;
+    dnrp_sync_result_t sync;           /* chunk-local record of the search that found it */
+    uint32_t chunk, round;
+} dnrp_stream_packet_t;
+int dnrp_stream_sync(dnrp_ctx_t* ctx, uint64_t n_samples, const dnrp_cf32_t* iq, uint32_t chunk_hop, uint32_t max_out,
+                     dnrp_stream_packet_t* out, uint32_t* n_out);
+
+/* rx_pacer_t hand-over to rx_synced_t for n packets found by dnrp_stream_sync: copies, per packet i, the samples
+ * [start_64[i] - t0, start_64[i] - t0 + dnrp_rx_stride()) of the device-resident stream into IQ window i (zeros
+ * outside the stream).  dnrp_rx_pcc_batch(ctx, n, NULL, sync, ...) with sync[i].fine_peak_time_local = t0 continues. */
+int dnrp_stream_extract(dnrp_ctx_t* ctx, uint32_t n, const int64_t* start_64, uint32_t t0);
+
 /* rx_synced_t::demoddecod_rx_pcc (lib/src/phy/rx/rx_synced/rx_synced.cpp:115-274) for n packets.
  * iq_in [n][N_RX][dnrp_rx_stride()] host IQ windows (NULL: the windows already resident on the device,
  * e.g. written by dnrp_channel_batch); sync [n] or NULL (use the results of the preceding dnrp_sync_batch,

@@ -421,6 +421,54 @@ class batch_phy_t {
             std::vector<dnrp_pcc_report_t> pcc(n);
             check(dnrp_rx_pcc_batch(ctx, n, nullptr, nullptr, pcc.data()), "dnrp_rx_pcc_batch");
             stats.windows += n;
+            deliver(n, sres, pcc, window_start_64, tpoint, tx_out);
+            return tx_out;
+        }
+
+        /// The streaming front door: one continuous stream [N_RX][n_samples] at the hardware rate (first sample at
+        /// global time stream_start_64) instead of pre-cut windows -- worker_sync_t / sync_chunk_t / baton_t
+        /// (worker_sync.cpp:112-221): every unique packet found is handed to the synced receiver and the firmware in
+        /// time order, max_windows packets per device batch.
+        machigh_phy_t::tx_descriptor_vec_t process_stream(uint64_t n_samples, const cf_t* stream, int64_t stream_start_64,
+                                                          upper::tpoint_t& tpoint, uint32_t chunk_hop = 0) {
+            machigh_phy_t::tx_descriptor_vec_t tx_out;
+            const uint32_t max_out = (uint32_t)(n_samples / std::max<uint32_t>(packet_sizes.N_samples_STF, 1u)) + 1;
+            std::vector<dnrp_stream_packet_t> found(max_out);
+            uint32_t n_found = 0;
+            check(dnrp_stream_sync(ctx, n_samples, stream, chunk_hop, max_out, found.data(), &n_found), "dnrp_stream_sync");
+            const uint32_t t0 = packet_sizes.N_samples_STF / 2;   // room in front of the packet inside its window
+            for (uint32_t first = 0; first < n_found; first += max_windows) {
+                const uint32_t n = std::min(max_windows, n_found - first);
+                std::vector<int64_t> start(n), window_start(n);
+                std::vector<dnrp_sync_result_t> sres(n);
+                std::vector<dnrp_sync_report_t> sync_in(n);
+                for (uint32_t i = 0; i < n; ++i) {
+                    const dnrp_stream_packet_t& f = found[first + i];
+                    start[i] = f.fine_peak_time_64;
+                    window_start[i] = stream_start_64 + f.fine_peak_time_64 - (int64_t)t0;
+                    sres[i] = f.sync;                               // chunk-local record -> window-local times
+                    sres[i].fine_peak_time_local = t0;
+                    sres[i].coarse_peak_time_hw = (uint32_t)((int64_t)t0 + f.coarse_peak_time_64 - f.fine_peak_time_64);
+                    sres[i].coarse_peak_time_local = sres[i].coarse_peak_time_hw;
+                    sync_in[i] = dnrp_sync_report_t{};
+                    sync_in[i].fine_peak_time_local = t0;
+                    sync_in[i].cfo_fractional_rad = f.sync.cfo_fractional_rad;
+                    sync_in[i].cfo_integer_rad = f.sync.cfo_integer_rad;
+                    for (uint32_t a = 0; a < 8; ++a) sync_in[i].rms[a] = f.sync.rms_array[a];
+                }
+                check(dnrp_stream_extract(ctx, n, start.data(), t0), "dnrp_stream_extract");
+                std::vector<dnrp_pcc_report_t> pcc(n);
+                check(dnrp_rx_pcc_batch(ctx, n, nullptr, sync_in.data(), pcc.data()), "dnrp_rx_pcc_batch");
+                stats.windows += n;
+                deliver(n, sres, pcc, window_start.data(), tpoint, tx_out);
+            }
+            return tx_out;
+        }
+
+    private:
+        /// sync results + PCC reports of n windows -> work_pcc (FIFO) -> demoddecod_rx_pdc -> work_pdc / work_pdc_error
+        void deliver(uint32_t n, const std::vector<dnrp_sync_result_t>& sres, const std::vector<dnrp_pcc_report_t>& pcc,
+                     const int64_t* window_start_64, upper::tpoint_t& tpoint, machigh_phy_t::tx_descriptor_vec_t& tx_out) {
 
             std::vector<sync_report_t> sync_reports;
             std::vector<pcc_report_t> pcc_reports(n);
@@ -497,10 +545,8 @@ class batch_phy_t {
                 hp->finalize(rep.crc_status);                   // worker_tx_rx.cpp:228
                 for (auto& d : out.tx_descriptor_vec) tx_out.push_back(d);
             }
-            return tx_out;
         }
 
-    private:
         dnrp_config_t config;
         uint32_t max_windows, nof_process_rx;
         dnrp_ctx_t* ctx{nullptr};

@@ -79,3 +79,38 @@ def search(iq, u, b, os=1, N_eff_TX_max=1, search_length=None, resample=(1, 1)):
     elif rc != 0:
         raise RuntimeError("oracle sync failed (rc=%d)" % rc)
     return rep
+
+
+def stream_search(iq, u, b, os=1, N_eff_TX_max=1, window=None):
+    """Sequential packet search over one continuous stream iq [n_ant][n], the way ONE sync_chunk_t walks an arbitrarily
+    long chunk (sync_chunk.cpp:146-283): search, on a packet move ignore_before_index to coarse peak + 2 STFs
+    (autocorrelator_detection.cpp:137-146, RX_SYNC_PARAM_AUTOCORRELATOR_DETECTION_SKIP_AFTER_PEAK_IN_STFS_DP = 2),
+    continue.  Implemented with search() on slices that start on the global detection step grid one STF + one
+    pattern (the detector's history) before the position to resume from.  Returns [(fine, coarse, Report)] with global
+    sample indices."""
+    iq = np.ascontiguousarray(iq, dtype=np.complex64)
+    n = iq.shape[1]
+    npat = 7 if u == 1 else 9
+    stf = (112 if u == 1 else 144) * b * os
+    pat = stf // npat
+    step = pat // 4
+    lead, tail = stf + pat, 2 * stf + 3 * pat
+    if window is None:
+        window = 64 * stf
+    found = []
+    pos = lead                       # first sample a detection may end on
+    while pos + stf < n:
+        s = -(-(pos - lead) // step) * step          # ceil to the step grid
+        w = iq[:, s:s + lead + window + tail]
+        if w.shape[1] < lead + stf + tail:
+            w = np.concatenate([w, np.zeros((iq.shape[0], lead + stf + tail - w.shape[1]), dtype=np.complex64)], axis=1)
+        sl = w.shape[1] - tail
+        rep = search(w, u, b, os=os, N_eff_TX_max=N_eff_TX_max, search_length=sl)
+        if rep.detected:
+            fine, coarse = s + rep.fine_peak_time_local, s + rep.coarse_peak_time_local
+            if fine + stf <= n:
+                found.append((fine, coarse, rep))
+            pos = coarse + 2 * stf
+        else:
+            pos = s + sl
+    return found

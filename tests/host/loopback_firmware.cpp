@@ -168,12 +168,60 @@ int main(int argc, char** argv) {
     const uint32_t err2 = fw.n_work_pdc_error - err1, pdc2 = fw.n_work_pdc - pdc_before;
     if (pdc2 != m || err2 == 0 || rounds < 2 || fw.n_tb_mismatch) ++fails;
 
+    // ---- scenario 3: streaming front door -- the packets sit at random gaps in ONE continuous two-antenna stream
+    // (context without resampling); process_stream finds them, hands them to the synced receiver and the callbacks
+    uint32_t stream_found = 0;
+    {
+        dnrp_config_t cfg3 = cfg;
+        cfg3.resample_L = 1; cfg3.resample_M = 1;
+        phy::batch_phy_t bp3(cfg3, 0, n);
+        const uint32_t k = n < 12 ? n : 12, S = ps.N_samples_packet_no_GI, stride3 = bp3.get_tx_stride();
+        std::vector<phy::harq::process_tx_t*> p3;
+        for (uint32_t i = 0; i < k; ++i) {
+            auto* hp = fw.pool.get_process_tx(1, fw.network_id, ps.psdef, phy::harq::finalize_tx_t::reset_and_terminate);
+            if (!hp) { ++fails; break; }
+            firmware_t::sent_t s{};
+            fw.make_plcf(s.plcf, (3u << 8) | (i + 1));
+            s.tb.resize(ps.N_TB_byte);
+            for (auto& v : s.tb) v = (uint8_t)rng();
+            std::memcpy(hp->get_a_plcf(), s.plcf, 10);
+            std::memcpy(hp->get_a_tb(), s.tb.data(), ps.N_TB_byte);
+            s.rv = hp->get_rv();
+            fw.sent[firmware_t::key_of(s.plcf)] = s;
+            p3.push_back(hp);
+        }
+        std::vector<phy::tx_descriptor_t> descs;
+        for (auto* hp : p3) descs.emplace_back(*hp, 0, tx_meta, radio::buffer_tx_meta_t{});
+        std::vector<cf_t> iq((size_t)p3.size() * stride3);
+        bp3.generate_tx_packets(descs, iq.data());
+        std::vector<size_t> at(p3.size());
+        size_t t = 3 * ps.N_samples_STF;
+        for (size_t i = 0; i < p3.size(); ++i) { at[i] = t; t += S + ps.N_samples_GI + (i % 3 ? rng() % (2 * S) : 0); }
+        const size_t ns = t + 4 * ps.N_samples_STF;
+        std::vector<cf_t> stream(2 * ns);
+        std::normal_distribution<float> g(0.f, 0.05f);   // about 23 dB below the packets
+        for (auto& v : stream) { v.re = g(rng); v.im = g(rng); }
+        for (size_t i = 0; i < p3.size(); ++i)
+            for (uint32_t a = 0; a < 2; ++a)
+                for (uint32_t q = 0; q < S; ++q) {
+                    const cf_t x = iq[i * stride3 + q];
+                    cf_t& y = stream[a * ns + at[i] + q];
+                    y.re += a ? -x.im : x.re; y.im += a ? x.re : x.im;   // antenna 1: rotated by 90 degrees
+                }
+        const uint32_t pcc0 = fw.n_work_pcc, pdc0 = fw.n_work_pdc;
+        bp3.process_stream(ns, stream.data(), 5000000, fw, 2 * S);
+        stream_found = fw.n_work_pdc - pdc0;
+        if (fw.n_work_pcc - pcc0 != p3.size() || stream_found != p3.size() || fw.n_tb_mismatch || fw.n_plcf_mismatch) ++fails;
+        for (size_t i = 0; i < p3.size(); ++i)   // sync_report.fine_peak_time_64 = global time of the packet start
+            if (fw.order[fw.order.size() - p3.size() + i] != (int64_t)(5000000 + at[i])) { ++fails; break; }
+    }
+
     const auto& st = bp->get_stats();
     std::printf("{\"n\": %u, \"work_pcc\": %u, \"work_pdc\": %u, \"work_pdc_error\": %u, \"plcf_mismatch\": %u, "
                 "\"tb_mismatch\": %u, \"harq_rounds\": %u, \"harq_first_round_errors\": %u, \"harq_decoded\": %u, "
-                "\"windows\": %llu, \"detections\": %llu, \"mean_snr_dB\": %.2f, \"fails\": %d}\n",
+                "\"windows\": %llu, \"detections\": %llu, \"mean_snr_dB\": %.2f, \"stream_decoded\": %u, \"fails\": %d}\n",
                 n, fw.n_work_pcc, fw.n_work_pdc, fw.n_work_pdc_error, fw.n_plcf_mismatch, fw.n_tb_mismatch, rounds, err2,
                 pdc2, (unsigned long long)st.windows, (unsigned long long)st.detections,
-                fw.n_work_pdc ? fw.snr_sum / fw.n_work_pdc : 0.0, fails);
+                fw.n_work_pdc ? fw.snr_sum / fw.n_work_pdc : 0.0, stream_found, fails);
     return fails ? 1 : 0;
 }

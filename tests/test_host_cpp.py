@@ -1,7 +1,8 @@
 """The C++ host mirror (include/dnrp_host.hpp: tx_descriptor_t, harq processes, sync/pcc/pdc reports, tpoint_t::work_pcc /
 work_pdc / work_pdc_error, batch_phy_t) driven by a loopback firmware written like the reference's tfw_loopback.
 CPU: the program builds against the C ABI and fails loudly without a GPU (no CPU fallback).  GPU: it runs both
-scenarios (plain loopback with resampling 10/9 and two RX antennas; HARQ retransmission combining)."""
+scenarios (plain loopback with resampling 10/9 and two RX antennas; HARQ retransmission combining; packets found in one
+continuous stream by batch_phy_t::process_stream)."""
 import json
 import os
 import subprocess
@@ -40,3 +41,4 @@ def test_host_mirror_loopback_firmware(tmp_path):
     assert out["fails"] == 0 and out["plcf_mismatch"] == 0 and out["tb_mismatch"] == 0
     assert out["work_pcc"] >= 48 + 8 and out["harq_decoded"] == 8 and out["harq_first_round_errors"] > 0
     assert out["harq_rounds"] >= 2
+    assert out["stream_decoded"] == 12     # streaming front door: every packet of the continuous stream found and decoded
