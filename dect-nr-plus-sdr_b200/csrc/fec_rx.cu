@@ -175,6 +175,13 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
     // soft buffer of this code block, written by k_derm in the layout of plan_fec.cu: three streams of K/2 packed
     // words in shared-array order, then the 12 termination values
     const int16_t* soft = p.soft + (size_t)slot * p.soft_stride + cb.soft_off;
+    // the whole soft buffer of the code block towards L2 now (k_derm's writes went through to HBM): the staging loops
+    // of the first iteration then wait for one HBM latency instead of one per loop iteration
+    if (!done) {
+        const char* sb = reinterpret_cast<const char*>(soft);
+        for (uint32_t o = tid * 128u; o < (3 * K + 12) * 2u; o += nthr * 128u)
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(sb + o));
+    }
     for (uint32_t i = tid; i < KH; i += nthr) EXT[i] = 0;
     for (uint32_t i = tid; i < 4 * 7 * T; i += nthr) AE[i] = 0;  // AE and BS are contiguous
     // ---- termination metrics of the two constituent decoders (three tail steps back from state 0), thread dec of
