@@ -326,13 +326,19 @@ def run_b200(args):
         peak, peak_src = 6500.0, "fallback"
     k_ms_per_launch = k_ms / max(k_cnt, 1)
     achieved = alg_bytes * P / (k_ms_per_launch * 1e-3) / 1e9 if k_cnt else None
-    traffic, traffic_src = None, None
+    traffic, traffic_src, issue = None, None, None
     tpath = os.path.join(ROOT, "profiles", "turbo_decode_traffic.json")
     if os.path.exists(tpath):
         t = json.load(open(tpath)).get(args.workload)
         if t:  # ncu capture of a smaller launch, scaled linearly to this launch's packets (the kernel is per-packet)
             traffic = t["dram_bytes_per_launch"] / t["packets_per_launch"] * P
             traffic_src = "%s, scaled from %d to %d packets per launch" % (t["source"], t["packets_per_launch"], P)
+            if t.get("warp_inst_per_launch") and k_cnt:
+                # the bound that does describe this kernel: warp instructions issued per second against the issue
+                # slots of the chip (148 SMs x 4 schedulers x SM clock); instruction count from the same ncu capture
+                winst = t["warp_inst_per_launch"] / t["packets_per_launch"] * P
+                issue = {"warp_inst_per_launch": winst, "achieved_Ginst_per_s": winst / (k_ms_per_launch * 1e-3) / 1e9,
+                         "sm_count": 148, "schedulers_per_sm": 4}
 
     # per-kernel roofline of the other streaming kernels (algorithmic bytes per packet)
     S_win = stride                                  # samples per antenna window (packet + slack for the offset)
@@ -369,6 +375,9 @@ def run_b200(args):
 
     h2d = P * N_RX * stride * 8
     d2h = P * ps["N_TB_byte"] + P * (ps["C"] + 8 + 76 + 112)
+    if issue and clk.get("sm_mhz"):
+        issue["peak_Ginst_per_s"] = 148 * 4 * clk["sm_mhz"] * 1e6 / 1e9
+        issue["frac"] = issue["achieved_Ginst_per_s"] / issue["peak_Ginst_per_s"]
     out = {
         "metric": "decoded_pdc_throughput", "value": value, "unit": "Mbit/s", "n_gpus": world, "steps": args.steps,
         "warmup": args.warmup, "ms_per_step": ms_step_max, "higher_is_better": True, "scaling": "weak",
@@ -393,7 +402,8 @@ def run_b200(args):
                      "peak_source": peak_src,
                      "alg_bytes_per_packet": alg_bytes, "ms_per_launch": k_ms_per_launch, "launches": k_cnt,
                      "share_of_step": k_ms_per_launch / ms_step_max if ms_step_max else None,
-                     "note": "compute/shared-memory bound kernel: see profiles/ for issue-slot utilisation",
+                     "note": "compute/shared-memory bound kernel: issue_slots is the bound that describes it",
+                     "issue_slots": issue,
                      "other_kernels": kernels},
         "cpu_baseline": cpu,
     }
