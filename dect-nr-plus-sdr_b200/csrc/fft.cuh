@@ -25,40 +25,88 @@ __device__ __forceinline__ float2 tw(const float2* __restrict__ table, uint32_t 
     return w;
 }
 
-// One Stockham pass of radix R (Bainville's formulation): element j of N/R butterflies,
-// Ns = product of the radices of the previous passes.  POW2: Ns is a power of two (every pass of a
-// power-of-two transform): index arithmetic by mask and shift instead of integer division.
-// k * r * tstep < Ns * R * N / (Ns * R) = N, so the twiddle index needs no reduction; the first pass
-// (Ns == 1) has unit twiddles.
-template <bool INV, int R, bool POW2>
+// Buffers handed to block_fft hold fft_buf_len(N) elements: intermediate passes store with one pad element per 16
+// (index i at i + i/16), which spreads the stride-16 writes of the radix-16 passes over all banks.  The first pass
+// reads and the last pass writes plain indices, so callers never see the padding.
+__host__ __device__ __forceinline__ uint32_t fft_buf_len(uint32_t N) { return N + (N >> 4); }
+__device__ __forceinline__ uint32_t fft_pad(uint32_t i) { return i + (i >> 4); }
+
+// radix-4 butterfly, forward (INV: inverse) DFT of four values in place
+template <bool INV>
+__device__ __forceinline__ void dft4(float2& v0, float2& v1, float2& v2, float2& v3) {
+    const float2 a = cadd(v0, v2), b = csub(v0, v2);
+    const float2 c = cadd(v1, v3), d = csub(v1, v3);
+    const float2 id = INV ? make_float2(-d.y, d.x) : make_float2(d.y, -d.x);  // forward: -i*d, inverse: +i*d
+    v0 = cadd(a, c);
+    v1 = cadd(b, id);
+    v2 = csub(a, c);
+    v3 = csub(b, id);
+}
+
+// 16-point DFT in registers: n = c + 4m, k = q + 4p: X[q + 4p] = sum_c W4^(cp) W16^(cq) sum_m x[c + 4m] W4^(mq)
+template <bool INV>
+__device__ __forceinline__ void dft16(float2 (&v)[16]) {
+#pragma unroll
+    for (int c = 0; c < 4; ++c) dft4<INV>(v[c], v[c + 4], v[c + 8], v[c + 12]);  // v[c + 4q] = inner sum for (c, q)
+    // W16^(cq), c, q = 1..3 (forward: exp(-2 pi i cq / 16))
+    constexpr float C1 = 0.92387953251128674f, S1 = 0.38268343236508977f, R2 = 0.70710678118654752f;
+    const float sg = INV ? 1.f : -1.f;
+    auto rotm = [&](float2& x, float cr, float ci) { x = make_float2(x.x * cr - x.y * (sg * ci), x.x * (sg * ci) + x.y * cr); };
+    rotm(v[1 + 4], C1, S1);                       // cq = 1
+    rotm(v[2 + 4], R2, R2);                       // 2
+    rotm(v[3 + 4], S1, C1);                       // 3
+    rotm(v[1 + 8], R2, R2);                       // 2
+    rotm(v[2 + 8], 0.f, 1.f);                     // 4
+    rotm(v[3 + 8], -R2, R2);                      // 6
+    rotm(v[1 + 12], S1, C1);                      // 3
+    rotm(v[2 + 12], -R2, R2);                     // 6
+    rotm(v[3 + 12], -C1, -S1);                    // 9
+#pragma unroll
+    for (int q = 0; q < 4; ++q) dft4<INV>(v[4 * q], v[4 * q + 1], v[4 * q + 2], v[4 * q + 3]);  // over c -> p
+    // now v[4q + p] = X[q + 4p]: transpose to natural order
+    float2 o[16];
+#pragma unroll
+    for (int q = 0; q < 4; ++q)
+#pragma unroll
+        for (int pp = 0; pp < 4; ++pp) o[q + 4 * pp] = v[4 * q + pp];
+#pragma unroll
+    for (int i = 0; i < 16; ++i) v[i] = o[i];
+}
+
+// One Stockham pass of radix R (Bainville's formulation): butterfly j of N/R takes x[j + r N/R], multiplies by
+// W_{Ns R}^(k r), k = j mod Ns, and stores X[r] at (j / Ns) Ns R + k + r Ns.  Ns = product of the radices of the
+// previous passes.  POW2: Ns is a power of two: index arithmetic by mask and shift instead of integer division.
+// k * r * tstep < Ns * R * N / (Ns * R) = N, so the twiddle index needs no reduction; the first pass (Ns == 1) has unit
+// twiddles.  pin / pout: the source / destination buffer is padded (fft_pad); N/R and, from the second pass on, Ns are
+// multiples of 16, so the padded position of element r is base + r * padded stride.
+template <bool INV, int R, bool POW2, bool PAD>
 __device__ __forceinline__ void fft_pass(const float2* __restrict__ x, float2* __restrict__ y, uint32_t N,
-                                         uint32_t Ns, uint32_t log2Ns, const float2* __restrict__ table) {
+                                         uint32_t Ns, uint32_t log2Ns, const float2* __restrict__ table, bool pin_, bool pout_) {
+    const bool pin = PAD && pin_, pout = PAD && pout_;   // PAD = false: plain buffers, no index selects in the code
     const uint32_t M = N / R;
     const uint32_t tstep = POW2 ? M >> log2Ns : N / (Ns * R);  // W_{Ns*R}^k = W_N^{k*tstep}
+    const uint32_t xs = pin ? fft_pad(M) : M;                  // stride between the R inputs
+    const uint32_t ys = (pout && Ns >= 16) ? fft_pad(Ns) : Ns;  // stride between the R outputs
     for (uint32_t j = threadIdx.x; j < M; j += blockDim.x) {
         const uint32_t k = POW2 ? (j & (Ns - 1)) : j % Ns;
         float2 v[R];
+        const float2* xj = x + (pin ? fft_pad(j) : j);
 #pragma unroll
-        for (int r = 0; r < R; ++r) v[r] = x[j + r * M];
+        for (int r = 0; r < R; ++r) v[r] = xj[r * xs];
         if (Ns != 1) {
             const uint32_t kt = k * tstep;
 #pragma unroll
             for (int r = 1; r < R; ++r) v[r] = cmul(v[r], tw<INV>(table, kt * r));
         }
-        if (R == 2) {
+        if constexpr (R == 2) {
             const float2 a = v[0], b = v[1];
             v[0] = cadd(a, b);
             v[1] = csub(a, b);
-        } else if (R == 4) {
-            const float2 a = cadd(v[0], v[2]), b = csub(v[0], v[2]);
-            const float2 c = cadd(v[1], v[3]), d = csub(v[1], v[3]);
-            // forward: -i*d, inverse: +i*d
-            const float2 id = INV ? make_float2(-d.y, d.x) : make_float2(d.y, -d.x);
-            v[0] = cadd(a, c);
-            v[1] = cadd(b, id);
-            v[2] = csub(a, c);
-            v[3] = csub(b, id);
-        } else if (R == 3) {
+        } else if constexpr (R == 4) {
+            dft4<INV>(v[0], v[1], v[2], v[3]);
+        } else if constexpr (R == 16) {
+            dft16<INV>(v);
+        } else if constexpr (R == 3) {
             const float s = INV ? 0.8660254037844386f : -0.8660254037844386f;  // sin(-2pi/3) forward
             const float2 t1 = cadd(v[1], v[2]);
             const float2 t2 = make_float2(v[0].x - 0.5f * t1.x, v[0].y - 0.5f * t1.y);
@@ -69,46 +117,57 @@ __device__ __forceinline__ void fft_pass(const float2* __restrict__ x, float2* _
             v[2] = csub(t2, t3);
         }
         const uint32_t j0 = POW2 ? (((j >> log2Ns) << log2Ns) * R + k) : ((j / Ns) * Ns * R + k);
-        if (R == 4 && Ns == 1) {  // first pass: four consecutive outputs, two 16-byte stores (y is 16-byte aligned)
-            float4* y4 = reinterpret_cast<float4*>(y + 4 * j);
-            y4[0] = make_float4(v[0].x, v[0].y, v[1].x, v[1].y);
-            y4[1] = make_float4(v[2].x, v[2].y, v[3].x, v[3].y);
-        } else {
+        if (Ns == 1) {  // first pass: R consecutive outputs (padded: R j + r + j for R = 16)
+            float2* yj = y + (pout ? fft_pad(R * j) : R * j);
+            if constexpr (!PAD && R == 4) {  // two 16-byte stores (buffers are 16-byte aligned)
+                float4* y4 = reinterpret_cast<float4*>(yj);
+                y4[0] = make_float4(v[0].x, v[0].y, v[1].x, v[1].y);
+                y4[1] = make_float4(v[2].x, v[2].y, v[3].x, v[3].y);
+            } else {
 #pragma unroll
-            for (int r = 0; r < R; ++r) y[j0 + r * Ns] = v[r];
+                for (int r = 0; r < R; ++r) yj[r] = v[r];
+            }
+        } else {
+            float2* yj = y + (pout ? fft_pad(j0) : j0);
+#pragma unroll
+            for (int r = 0; r < R; ++r) yj[r * ys] = v[r];
         }
     }
 }
 
-// In-block FFT of a[0..N); b is scratch of the same size.  Returns the buffer holding the result.
-// All threads of the block must call it; contains __syncthreads().  Radix-4 passes first, then one radix-2,
-// then the radix-3 passes: Ns stays a power of two through the last power-of-two pass and the first radix-3 pass
-// (the OFDM sizes have at most one factor 3), so no pass divides by a runtime value.
-template <bool INV>
+// In-block FFT of a[0..N); a and b hold fft_buf_len(N) elements each, b is scratch.  Returns the buffer holding the
+// result (plain indices).  All threads of the block must call it; contains __syncthreads().  N = 2^a 3^b, a >= 4 (the
+// OFDM sizes are multiples of 64): radix-16 passes in registers first, then radix 4, 2 and 3 -- Ns stays a power of
+// two through the last power-of-two pass and the first radix-3 pass, so no pass divides by a runtime value.
+// RADIX16 = false: radix-4 passes only and no padding (kernels whose block has four times more threads than N / 16
+// butterflies: measured slower with radix 16 -- k_rx_fft 0.84 -> 1.13 ms at N = 1024 with 256 threads, 32 -> 70
+// registers); true: the long transforms of the fine synchronisation (N = 3072 at beta = 16: 0.60 -> 0.45 ms).
+template <bool INV, bool RADIX16 = false>
 __device__ float2* block_fft(float2* a, float2* b, uint32_t N, const float2* __restrict__ table) {
     uint32_t Ns = 1, lg = 0;
     uint32_t rem = N;
+    bool first = true;
     __syncthreads();
-    while (rem % 4 == 0) {
-        fft_pass<INV, 4, true>(a, b, N, Ns, lg, table);
-        Ns *= 4; lg += 2; rem /= 4;
-        float2* t = a; a = b; b = t;
-        __syncthreads();
+#define DNRP_FFT_PASS(R, P2, LGINC)                                                          \
+    {                                                                                        \
+        const bool last = rem == R;                                                          \
+        fft_pass<INV, R, P2, RADIX16>(a, b, N, Ns, lg, table, !first, !last);                \
+        Ns *= R; lg += LGINC; rem /= R; first = false;                                       \
+        float2* t = a; a = b; b = t;                                                         \
+        __syncthreads();                                                                     \
     }
-    if (rem % 2 == 0) {
-        fft_pass<INV, 2, true>(a, b, N, Ns, lg, table);
-        Ns *= 2; lg += 1; rem /= 2;
-        float2* t = a; a = b; b = t;
-        __syncthreads();
+    if constexpr (RADIX16) {
+        while (rem % 16 == 0) DNRP_FFT_PASS(16, true, 4)
     }
+    while (rem % 4 == 0) DNRP_FFT_PASS(4, true, 2)
+    if (rem % 2 == 0) DNRP_FFT_PASS(2, true, 1)
     bool pow2 = true;
     while (rem % 3 == 0) {
-        if (pow2) fft_pass<INV, 3, true>(a, b, N, Ns, lg, table);
-        else fft_pass<INV, 3, false>(a, b, N, Ns, 0, table);
-        Ns *= 3; rem /= 3; pow2 = false;
-        float2* t = a; a = b; b = t;
-        __syncthreads();
+        if (pow2) DNRP_FFT_PASS(3, true, 0)
+        else DNRP_FFT_PASS(3, false, 0)
+        pow2 = false;
     }
+#undef DNRP_FFT_PASS
     return a;
 }
 

@@ -50,8 +50,8 @@ __global__ void __launch_bounds__(256) k_rx_stf(const rx_params_t p) {
     const uint32_t NS = d.N_OCC / 4;
     float2* S = sm;                      // [stf_len_os] derotated STF with the cover sequence undone
     float2* X = S + d.stf_len_os;        // [N_os]
-    float2* Yb = X + d.N_os;             // [N_os]
-    float2* H = Yb + d.N_os;             // [N_RX][NS] zero-forced STF cells
+    float2* Yb = X + fft_buf_len(d.N_os);   // X, Yb: [fft_buf_len(N_os)]
+    float2* H = Yb + fft_buf_len(d.N_os);   // [N_RX][NS] zero-forced STF cells
     __shared__ float2 s_red[8];
     __shared__ float s_ang[8];
 
@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(256) k_rx_fft(const rx_params_t p) {
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
     const rx_state_t& st = p.state[pkt];
     float2* X = sm;
-    float2* Yb = sm + d.N_os;
+    float2* Yb = sm + fft_buf_len(d.N_os);
     __shared__ float2 s_red[8];
 
     const uint32_t n0 = d.stf_len_os + (l - 1) * d.sym_len_os + d.cp_os;  // relative to the first STF sample
@@ -567,7 +567,7 @@ cudaError_t launch_rx_snr_class(const rx_params_t& p, uint32_t n_packets, cudaSt
 }
 
 cudaError_t launch_rx_fft(const rx_params_t& p, uint32_t n_packets, cudaStream_t st) {
-    const size_t smem = sizeof(float2) * 2 * p.d.N_os;
+    const size_t smem = sizeof(float2) * 2 * fft_buf_len(p.d.N_os);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
         cudaError_t e = cudaFuncSetAttribute(k_rx_fft, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
@@ -579,7 +579,7 @@ cudaError_t launch_rx_fft(const rx_params_t& p, uint32_t n_packets, cudaStream_t
 }
 
 cudaError_t launch_rx_stf(const rx_params_t& p, uint32_t n_packets, cudaStream_t st) {
-    const size_t smem = sizeof(float2) * ((size_t)p.d.stf_len_os + 2 * p.d.N_os + (size_t)p.d.N_RX * (p.d.N_OCC / 4));
+    const size_t smem = sizeof(float2) * ((size_t)p.d.stf_len_os + 2 * fft_buf_len(p.d.N_os) + (size_t)p.d.N_RX * (p.d.N_OCC / 4));
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
         cudaError_t e = cudaFuncSetAttribute(k_rx_stf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);

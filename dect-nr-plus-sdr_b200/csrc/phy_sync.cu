@@ -422,7 +422,7 @@ __global__ void __launch_bounds__(XF_THREADS) k_sync_xcorr_fft(const sync_params
         return;
     }
     float2* A = smem_f;
-    float2* B = smem_f + N;
+    float2* B = smem_f + fft_buf_len(N);
     const float2* x = sync_iq_x(p, pkt, res.strongest_ant) + w0;
     const double inc = (double)((res.cfo_fractional_rad + res.cfo_integer_rad) * (float)p.rs_M / (float)p.rs_L);
     // CFO pre-rotation: one double-precision phasor per thread, then a float rotation by XF_THREADS samples per
@@ -438,7 +438,7 @@ __global__ void __launch_bounds__(XF_THREADS) k_sync_xcorr_fft(const sync_params
         w = cmul(w, ws);
         A[i] = r;
     }
-    const float2* X = block_fft<false>(A, B, N, p.xc_twiddle);
+    const float2* X = block_fft<false, true>(A, B, N, p.xc_twiddle);
     float2 Xr[XF_MAX_PER_THREAD];
 #pragma unroll
     for (uint32_t r = 0; r < XF_MAX_PER_THREAD; ++r) {
@@ -454,7 +454,7 @@ __global__ void __launch_bounds__(XF_THREADS) k_sync_xcorr_fft(const sync_params
             const uint32_t k = tid + r * XF_THREADS;
             if (k < N) A[k] = cmul(Xr[r], T[k]);
         }
-        const float2* c = block_fft<true>(A, B, N, p.xc_twiddle);
+        const float2* c = block_fft<true, true>(A, B, N, p.xc_twiddle);
         unsigned long long mine = 0ull;
         for (uint32_t j = tid; j < n_lag; j += XF_THREADS) {
             const float2 v = c[j];
@@ -520,7 +520,7 @@ cudaError_t launch_sync(const sync_params_t& p, uint32_t n, cudaStream_t st) {
     if (e != cudaSuccess) return e;
     k_sync_peak<<<n, 256, sm2, st>>>(p, len);
     if (p.xc_fft_n) {
-        const size_t smf = 2 * (size_t)p.xc_fft_n * sizeof(float2);
+        const size_t smf = 2 * (size_t)fft_buf_len(p.xc_fft_n) * sizeof(float2);
         e = cudaFuncSetAttribute(k_sync_xcorr_fft, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smf);
         if (e != cudaSuccess) return e;
         k_sync_xcorr_fft<<<n, XF_THREADS, smf, st>>>(p, p.x_len);

@@ -66,7 +66,7 @@ __global__ void __launch_bounds__(256) k_tx_ofdm(const txofdm_params_t p) {
     const uint32_t l = blockIdx.x, ant = blockIdx.y, pkt = blockIdx.z;
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
     float2* X = sm;
-    float2* Y = sm + d.N_os;
+    float2* Y = sm + fft_buf_len(d.N_os);
     const tx_meta_dev_t meta = p.meta[pkt];
     const uint8_t* pcc_bits = p.pcc_bits + (size_t)pkt * p.pcc_stride;
     const uint8_t* pdc_bits = p.pdc_bits + (size_t)pkt * p.pdc_stride;
@@ -149,7 +149,7 @@ __global__ void __launch_bounds__(256) k_tx_ofdm(const txofdm_params_t p) {
 }
 
 cudaError_t launch_tx_ofdm(const txofdm_params_t& p, uint32_t n_packets, cudaStream_t st) {
-    const size_t smem = 2 * sizeof(float2) * p.d.N_os;
+    const size_t smem = 2 * sizeof(float2) * fft_buf_len(p.d.N_os);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
         cudaError_t e = cudaFuncSetAttribute(k_tx_ofdm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
