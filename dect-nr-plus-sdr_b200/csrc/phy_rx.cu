@@ -419,7 +419,8 @@ __global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_dema
             chan_est_rx<NRX>(p, pkt, 0, l, k, pcc, h);
 #pragma unroll
             for (int a = 0; a < NRX; ++a) {
-                const float2 y = p.Y[(((size_t)pkt * NRX + a) * d.N_DF + (l - 1)) * d.Nk + k];
+                // streaming loads / stores (evict first): Y and the LLRs pass through once, the pilots stay in L1
+                const float2 y = __ldcs(&p.Y[(((size_t)pkt * NRX + a) * d.N_DF + (l - 1)) * d.Nk + k]);
                 num = cadd(num, cmulc(y, h[a]));
                 den += h[a].x * h[a].x + h[a].y * h[a].y;
             }
@@ -448,7 +449,7 @@ __global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_dema
 #pragma unroll
             for (int a = 0; a < NRX; ++a) {
                 const float2* Y = p.Y + (((size_t)pkt * NRX + a) * d.N_DF + (l - 1)) * d.Nk;
-                const float2 r0 = Y[k0], r1 = Y[k1];
+                const float2 r0 = __ldcs(&Y[k0]), r1 = __ldcs(&Y[k1]);
                 // conj(h0) r0 + h1 conj(r1)   and   -h1 conj(r0) + conj(h0) r1   (rx_synced.cpp:1372-1373)
                 n0 = cadd(n0, cadd(cmulc(r0, h0[a]), cmulc(h1[a], r1)));
                 n1 = cadd(n1, csub(cmulc(r1, h0[a]), cmulc(h1[a], r0)));
@@ -480,7 +481,7 @@ __global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_dema
     const uint32_t u0 = blockIdx.x * blockDim.x;
     const uint32_t n_here = min(blockDim.x, n_units > u0 ? n_units - u0 : 0u);
     uint32_t* out32 = reinterpret_cast<uint32_t*>(out) + (size_t)u0 * W;  // G even: 4-byte aligned
-    for (uint32_t i = threadIdx.x; i < n_here * W; i += blockDim.x) out32[i] = s_out[i];
+    for (uint32_t i = threadIdx.x; i < n_here * W; i += blockDim.x) __stcs(&out32[i], s_out[i]);
 }
 
 cudaError_t launch_rx_demap(const rx_params_t& p, uint32_t n_packets, bool pcc, cudaStream_t st) {

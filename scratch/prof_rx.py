@@ -7,14 +7,15 @@ sys.path.insert(0, "/root/repo/tests")
 from conftest import load_product
 product = load_product()
 P = int(sys.argv[1]) if len(sys.argv) > 1 else 2000
-cfg = (1, 16, 1, 1, 0, 7, 6144)
-phy = product.Phy(cfg, max_batch=P, N_RX=1, network_id=123456789)
+C3 = len(sys.argv) > 2 and sys.argv[2] == "C3"
+cfg = (1, 16, 1, 2, 5, 7, 6144) if C3 else (1, 16, 1, 1, 0, 7, 6144)
+phy = product.Phy(cfg, max_batch=P, N_RX=4 if C3 else 1, network_id=123456789)
 rng = np.random.default_rng(1)
 tb = rng.integers(0, 256, (P, phy.ps["N_TB_byte"]), dtype=np.uint8)
 plcf = rng.integers(0, 256, (P, 10), dtype=np.uint8)
 phy.tx(plcf, tb, fetch=False)
 t0 = rng.integers(512, 3000, P).astype(np.uint32)
-phy.channel(P, snr_dB=25.0, t0=t0, mode=0, seed=3)
+phy.channel(P, snr_dB=25.0, t0=t0, mode=1 if C3 else 0, seed=3)
 for _ in range(2):
     ms = phy.time_stage(product.STAGE_SYNC_RX_CHAIN, P, reps=1)
 ok = phy.tap(product.TAP_TB_OK, P).reshape(-1)
