@@ -70,7 +70,7 @@ int dnrp_stream_sync(dnrp_ctx_t* c, uint64_t n_samples, const dnrp_cf32_t* iq, u
     // ---- stream to the device, zero padded so that every chunk has the full length
     const size_t need = (size_t)(n_chunks - 1) * hop + len;
     if (need > c->stream_alloc) {
-        DNRP_CUDA(c->d_stream.alloc((size_t)d.N_RX * need));   // alloc() zero fills
+        DNRP_CUDA(c->d_stream.alloc((size_t)d.N_RX * need));   // alloc() zero fills and synchronises
         c->stream_alloc = need;
     } else {
         DNRP_CUDA(cudaMemsetAsync(c->d_stream.p, 0, (size_t)d.N_RX * c->stream_alloc * sizeof(float2), c->stream));

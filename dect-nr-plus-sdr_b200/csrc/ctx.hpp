@@ -44,6 +44,9 @@ struct dbuf {
         if (count == 0) return cudaSuccess;
         cudaError_t e = cudaMalloc((void**)&p, count * sizeof(T));
         if (e == cudaSuccess) e = cudaMemset(p, 0, count * sizeof(T));
+        // the zero fill runs on the default stream, the contexts' streams are non-blocking: without this barrier a
+        // lazily allocated buffer could be zeroed AFTER the first asynchronous copy / kernel wrote to it
+        if (e == cudaSuccess) e = cudaDeviceSynchronize();
         return e;
     }
     cudaError_t upload(const std::vector<T>& v) {

@@ -68,7 +68,12 @@ def test_stream_packets_decode_through_the_batched_receiver(product):
     cfg = (1, 2, 1, 1, 0, 3, 2048)
     n_pkt = 32
     phy, stream, starts, tb, plcf = _make_stream(product, cfg, n_pkt, snr_db=22.0, seed=11, N_RX=2)
-    got = phy.stream_sync(stream, chunk_hop=3000)
+    # pinned host memory: the upload is truly asynchronous (regression: the zero fill of the freshly allocated device
+    # stream buffer used to race with it on the first call)
+    import torch
+    pinned = torch.empty(stream.shape, dtype=torch.complex64, pin_memory=True)
+    pinned.numpy()[...] = stream
+    got = phy.stream_sync(pinned.numpy(), chunk_hop=3000)
     assert np.array_equal(got.fine_peak_time_64, starts)
     t0 = 64
     phy.stream_extract(got.fine_peak_time_64, t0)
