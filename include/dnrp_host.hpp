@@ -12,8 +12,9 @@
 //   hp_rx->finalize(crc_status) after the callback, TX descriptors generated afterwards)
 //   sections_part4/physical_header_field/*.hpp (plcf_10/20/21_t, feedback info, plcf_decoder_t): dnrp_plcf.hpp;
 //   pcc_report_t::decode_plcf() runs rx_synced.cpp:1011-1026 on the bytes the device delivered
-// Not mirrored (out of scope, MAC layer): sp4::mac_pdu_decoder_t -- pdc_report_t carries the transport block bytes
-// the reference's MAC PDU decoder would be fed with.
+//   sections_part4/mac_pdu/*.hpp (MAC header type, common headers, multiplexing header, mac_pdu_decoder_t framing):
+//   dnrp_mac_pdu.hpp; pdc_report_t::decode_mac_pdu() demultiplexes the SDUs of a transport block
+// Not mirrored (MAC layer): the parsers of the individual MAC messages / IEs (sections_part4/mac_messages_and_ie).
 // There is no CPU fallback: construction throws if libdnrp_cuda.so cannot create its context.
 #pragma once
 #include <array>
@@ -30,6 +31,7 @@ extern "C" {
 #include "dnrp_c_api.h"
 }
 #include "dnrp_plcf.hpp"
+#include "dnrp_mac_pdu.hpp"
 
 namespace dectnrp_b200 {
 
@@ -284,13 +286,21 @@ struct pcc_report_t {
     }
 };
 
-/// pdc_report.hpp:28-62 -- mac_pdu_decoder_t replaced by the decoded transport block bytes
+/// pdc_report.hpp:28-62 -- mac_pdu_decoder_t replaced by the decoded transport block bytes (decode_mac_pdu feeds one)
 struct pdc_report_t {
     bool crc_status{false};
     const uint8_t* a_tb{nullptr};
     uint32_t N_TB_byte{0};
     float snr_dB{0.f};
     mimo_report_t mimo_report{};
+    /// what rx_synced_t does code block by code block (rx_synced.cpp:394-400): MAC header type, common header and the
+    /// demultiplexed SDUs of the transport block; true if the decoder reached a valid final state
+    bool decode_mac_pdu(sp4::mac_pdu_decoder_t& mac_pdu_decoder, uint32_t mu = 1) const {
+        if (!crc_status || a_tb == nullptr) return false;
+        mac_pdu_decoder.set_configuration(a_tb, N_TB_byte, mu);
+        mac_pdu_decoder.decode(N_TB_byte);
+        return mac_pdu_decoder.has_reached_valid_final_state();
+    }
 };
 
 /// maclow_phy_handle.hpp:28-48

@@ -46,6 +46,15 @@ struct firmware_t final : public upper::tpoint_t {
         ++n_work_pdc;
         const uint32_t key = in.maclow_phy.get_handle_lrdid();
         if (std::memcmp(in.pdc_report.a_tb, sent[key].tb.data(), packet_sizes.N_TB_byte) != 0) ++n_tb_mismatch;
+        // MAC PDU framing: scenario 1 sends DATA MAC PDUs with one user plane data SDU (tag 1 << 8 | i + 1)
+        if ((key >> 8) == 1) {
+            if (!in.pdc_report.decode_mac_pdu(mac_pdu_decoder)) ++n_mac_mismatch;
+            const auto& v = mac_pdu_decoder.get_mmie_decoded_vec();
+            const auto* mch = mac_pdu_decoder.get_mac_common_header();
+            if (v.size() != 1 || !v[0].is_user_plane_data() || mch == nullptr || mch->Sequence_number != (key & 0xff) ||
+                v[0].N_bytes != packet_sizes.N_TB_byte - 10 || std::memcmp(v[0].data_ptr, sent[key].tb.data() + 6, v[0].N_bytes) != 0)
+                ++n_mac_mismatch;
+        }
         snr_sum += in.pdc_report.snr_dB;
         running_rx.erase(key);
         return phy::machigh_phy_t();
@@ -72,6 +81,8 @@ struct firmware_t final : public upper::tpoint_t {
     }
     static uint32_t key_of(const uint8_t* a) { return ((uint32_t)a[2] << 8) | a[3]; }
     sp4::plcf_decoder_t plcf_decoder{16, 11, 8};
+    sp4::mac_pdu_decoder_t mac_pdu_decoder;
+    uint32_t n_mac_mismatch{0};
     sp3::packet_sizes_t packet_sizes;
     phy::harq::process_pool_t pool;
     phy::harq::finalize_rx_t frx{phy::harq::finalize_rx_t::keep_running_or_reset_and_terminate_if_crc_correct};
@@ -129,7 +140,21 @@ int main(int argc, char** argv) {
         firmware_t::sent_t s{};
         fw.make_plcf(s.plcf, (1u << 8) | (i + 1));
         s.tb.resize(ps.N_TB_byte);
-        for (auto& v : s.tb) v = (uint8_t)rng();
+        {   // DATA MAC PDU: header type (1) + common header (2) + multiplexing header (3) + SDU + padding IE (4)
+            std::vector<uint8_t> payload(ps.N_TB_byte - 10);
+            for (auto& v : payload) v = (uint8_t)rng();
+            sp4::mac_header_type_t mht;
+            mht.Version = sp4::mac_header_type_t::version_ec::v00;
+            mht.MAC_security = sp4::mac_header_type_t::mac_security_ec::macsec_not_used;
+            mht.MAC_header_type = sp4::mac_header_type_t::mac_header_type_ec::DATA_MAC_PDU;
+            sp4::mac_common_header_t mch;
+            mch.kind = mht.MAC_header_type; mch.Sequence_number = i + 1;
+            sp4::mac_pdu_writer_t w(s.tb.data(), ps.N_TB_byte);
+            if (!w.begin(mht, mch) || !w.add_sdu(sp4::mac_multiplexing_header_t::User_Plane_Data_Flow_1, payload.data(),
+                                                 (uint32_t)payload.size()))
+                ++fails;
+            w.finish();
+        }
         std::memcpy(hp->get_a_plcf(), s.plcf, 10);
         std::memcpy(hp->get_a_tb(), s.tb.data(), ps.N_TB_byte);
         fw.sent[firmware_t::key_of(s.plcf)] = s;
@@ -137,7 +162,7 @@ int main(int argc, char** argv) {
     }
     transmit(procs, 28.0f, 11);
     const uint32_t pcc1 = fw.n_work_pcc, pdc1 = fw.n_work_pdc, err1 = fw.n_work_pdc_error;
-    if (pcc1 != n || pdc1 != n || err1 != 0 || fw.n_plcf_mismatch || fw.n_tb_mismatch) ++fails;
+    if (pcc1 != n || pdc1 != n || err1 != 0 || fw.n_plcf_mismatch || fw.n_tb_mismatch || fw.n_mac_mismatch) ++fails;
     for (size_t i = 1; i < fw.order.size(); ++i) if (fw.order[i] <= fw.order[i - 1]) ++fails;   // work_pcc FIFO
     for (auto* hp : procs) if (hp->is_running()) ++fails;                                        // reset_and_terminate
 
