@@ -304,6 +304,11 @@ def run_b200(args):
     barrier()
     e2e16_s = (time.perf_counter() - t_start) / args.steps
 
+    # ---- the other half of the path, outside the timed step: transmit chain (FEC encode + OFDM) and simulation
+    # channel on the resident batch (device time per pass over the P packets)
+    tx_ms = phy.time_stage(product.STAGE_TX_CHAIN, P, reps=3)
+    ch_ms = phy.time_stage(product.STAGE_CHANNEL, P, reps=3)
+
     # ---- reduce over ranks: max of the times, sum of the counters (the one collective of this path)
     (ms_step_max, e2e_ms_max, e2e16_ms_max), (tot_P, tot_ok, tot_bits, tot_ok_e2e, tot_plcf, tot_sync, tot_ok16) = \
         reduce_over_ranks([ms_step, e2e_s * 1e3, e2e16_s * 1e3],
@@ -406,6 +411,9 @@ def run_b200(args):
                      "issue_slots": issue,
                      "other_kernels": kernels},
         "cpu_baseline": cpu,
+        "other_stages": {"tx_chain_ms": tx_ms, "tx_packets_per_s": P / (tx_ms * 1e-3), "channel_ms": ch_ms,
+                         "channel_packets_per_s": P / (ch_ms * 1e-3),
+                         "note": "per rank, %d packets per pass; not part of the timed step" % P},
     }
     print(json.dumps(out))
     if world > 1:

@@ -188,7 +188,7 @@ int run_fec_encode(dnrp_ctx* c, uint32_t n, bool have_mask, bool have_rv) {
     p.plcf_mask = nullptr;
     p.gold = c->d_gold_pdc.p; p.gold_bit_off = 0;
     p.out = c->d_pdc_bits.p; p.out_stride = f.dbits_stride;
-    p.rm_arena = c->d_rm_arena.p;
+    p.rm_arena = c->d_rm_arena.p; p.xp_arena = c->d_xp_arena.p;
     DNRP_LAUNCH(c, -1, launch_tx_fec(p, n, f.Kmax, c->stream));
     // PLCF: one launch, the descriptor (type 1 or 2) is the plan's plcf_type
     txfec_params_t q{};
@@ -198,7 +198,7 @@ int run_fec_encode(dnrp_ctx* c, uint32_t n, bool have_mask, bool have_rv) {
     q.plcf_mask = have_mask ? c->d_plcf_mask.p : nullptr;
     q.gold = c->d_gold_pcc.p; q.gold_bit_off = 0;
     q.out = c->d_pcc_bits.p; q.out_stride = 28;
-    q.rm_arena = c->d_rm_arena.p;
+    q.rm_arena = c->d_rm_arena.p; q.xp_arena = c->d_xp_arena.p;
     DNRP_LAUNCH(c, -1, launch_tx_fec(q, n, 96, c->stream));
     return DNRP_OK;
 }

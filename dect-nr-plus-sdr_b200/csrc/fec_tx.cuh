@@ -14,7 +14,11 @@ struct txcb_desc_t {
     uint32_t wp, n_e, n_pad;   // output bit offset, rate matched bits, extra scrambled zero bits
     uint32_t rm_src_off;       // offset of this K's src[] table in the rate-matching arena
     uint32_t rm_start[4];
+    // CRC chunk combination: x^(bits behind thread t's chunk + order) mod g for the TX_FEC_THREADS chunks of the
+    // whole-message CRC (xp_tb_off) and of the code block CRC (xp_cb_off), offsets into the x^n arena
+    uint32_t xp_tb_off, xp_cb_off;
 };
+constexpr uint32_t TX_FEC_THREADS = 256;
 
 struct txfec_params_t {
     const txcb_desc_t* cbs;
@@ -28,6 +32,7 @@ struct txfec_params_t {
     uint8_t* out;              // [packet][out_stride] packed coded bits, zero-initialised, stride % 4 == 0
     size_t out_stride;
     const uint16_t* rm_arena;
+    const uint32_t* xp_arena;
 };
 
 cudaError_t launch_tx_fec(const txfec_params_t& p, uint32_t n_packets, uint32_t Kmax, cudaStream_t st);

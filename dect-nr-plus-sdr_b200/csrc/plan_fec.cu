@@ -2,6 +2,7 @@
 // decoder kernels, rate-matching tables, CRC combination tables.  Segmentation and the per-CB bit
 // budgets follow reference lib/src/phy/fec/pdc_enc.cpp:148-175 (encoder) and :322-337 (decoder,
 // including its '>' comparison inherited from srsRAN's sch.c), lib/src/phy/fec/pcc_enc.cpp:187-208.
+#include <algorithm>
 #include <map>
 #include "ctx.hpp"
 
@@ -82,6 +83,18 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         return off;
     };
 
+    // TX CRC tables: thread t of TX_FEC_THREADS owns bits [min(n, t c), min(n, t c + c)), c = ceil(n / threads); its partial
+    // remainder is multiplied by x^(n - end + order) mod g (fec_tx.cu: block_crc)
+    auto add_xp_tx = [&](uint32_t nbits, uint32_t poly, uint32_t order) -> uint32_t {
+        const uint32_t off = (uint32_t)f.xp_arena.size();
+        const uint32_t chunk = (nbits + TX_FEC_THREADS - 1) / TX_FEC_THREADS;
+        for (uint32_t t = 0; t < TX_FEC_THREADS; ++t) {
+            const uint32_t b0 = std::min(nbits, t * chunk), b1 = std::min(nbits, b0 + chunk);
+            f.xp_arena.push_back(gf2_xpow_host(nbits - b1 + order, poly, order));
+        }
+        return off;
+    };
+
     f.Kmax = 0;
     f.tdec_smem = 0;
     f.tdec_threads = 32;
@@ -120,6 +133,8 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         t.n_pad = 0;
         t.rm_src_off = rm_off[K];
         for (int rv = 0; rv < 4; ++rv) t.rm_start[rv] = rm_tab[K].start[rv];
+        t.xp_tb_off = t.tb_crc_bits ? add_xp_tx(t.tb_crc_len, t.tb_crc_poly, t.tb_crc_bits) : 0;
+        t.xp_cb_off = t.cb_crc ? add_xp_tx(t.n_data + t.tb_crc_bits, spec::CRC24B_POLY, 24) : 0;
         f.tx_cbs.push_back(t);
         rp_tx += t.n_data;
         wp_tx += t.n_e;
@@ -182,6 +197,8 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         t.wp = 0; t.n_e = spec::PCC_BITS; t.n_pad = 4;  // the reference scrambles 200 bits (pcc_enc.cpp:212)
         t.rm_src_off = rm_off[K];
         for (int rv = 0; rv < 4; ++rv) t.rm_start[rv] = rm_tab[K].start[rv];
+        t.xp_tb_off = add_xp_tx(t.tb_crc_len, t.tb_crc_poly, t.tb_crc_bits);
+        t.xp_cb_off = 0;
         f.tx_pcc[ty] = t;
         cb_desc_t r{};
         r.K = K; r.L = L; r.P = K / L; r.f1 = f1; r.f2 = f2;
