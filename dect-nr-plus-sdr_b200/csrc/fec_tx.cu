@@ -20,6 +20,34 @@ __device__ __forceinline__ uint32_t gf2_mulmod_tx(uint32_t a, uint32_t b, uint32
 
 // CRC (zero init) of nbits message bits fetched through getbit(i), computed by the whole block:
 // remainder of M(x) * x^order.  s_acc must be a shared word.
+// The same over packed message bytes (MSB first), chunks of whole bytes: one load per eight bits.  xp as below with
+// byte chunks (plan_fec.cu: add_xp_tx with byte_chunks).
+__device__ uint32_t block_crc_bytes(const uint8_t* __restrict__ msg, uint32_t nbytes, uint32_t poly, uint32_t order,
+                                    const uint32_t* __restrict__ xp, uint32_t* s_acc) {
+    const uint32_t tid = threadIdx.x, nthr = blockDim.x;
+    const uint32_t chunk = (nbytes + nthr - 1) / nthr;
+    const uint32_t b0 = min(nbytes, tid * chunk), b1 = min(nbytes, b0 + chunk);
+    const uint32_t top = 1u << order;
+    if (tid == 0) *s_acc = 0;
+    __syncthreads();
+    uint32_t r = 0;
+    for (uint32_t i = b0; i < b1; ++i) {
+        const uint32_t v = msg[i];
+#pragma unroll
+        for (int q = 7; q >= 0; --q) {
+            r = (r << 1) | ((v >> q) & 1u);
+            if (r & top) r ^= poly;
+        }
+    }
+    if (r) r = gf2_mulmod_tx(r, xp[tid], poly, order);
+    for (int o = 16; o > 0; o >>= 1) r ^= __shfl_xor_sync(0xffffffffu, r, o);
+    if ((tid & 31) == 0 && r) atomicXor(s_acc, r);
+    __syncthreads();
+    const uint32_t out = *s_acc;
+    __syncthreads();
+    return out;
+}
+
 // xp[t] = x^(nbits - end of thread t's chunk + order) mod g (host table, plan_fec.cu: add_xp_tx).
 template <typename F>
 __device__ uint32_t block_crc(F getbit, uint32_t nbits, uint32_t poly, uint32_t order, const uint32_t* __restrict__ xp,
@@ -154,11 +182,21 @@ __global__ void __launch_bounds__(256) k_tx_fec(const txfec_params_t p) {
     auto inbit = [&](uint32_t i) -> uint32_t { return (in[i >> 3] >> (7 - (i & 7))) & 1u; };
 
     // ---- payload bits of this code block
-    for (uint32_t i = tid; i < cb.n_data; i += nthr) c[i] = (uint8_t)inbit(cb.rp + i);
+    if (((cb.rp | cb.n_data) & 7u) == 0) {  // byte aligned (every TB / PLCF segmentation is): one load per eight bits
+        const uint8_t* inb = in + (cb.rp >> 3);
+        for (uint32_t B = tid; B < cb.n_data / 8; B += nthr) {
+            const uint32_t v = inb[B];
+#pragma unroll
+            for (uint32_t q = 0; q < 8; ++q) c[8 * B + q] = (uint8_t)((v >> (7 - q)) & 1u);
+        }
+    } else {
+        for (uint32_t i = tid; i < cb.n_data; i += nthr) c[i] = (uint8_t)inbit(cb.rp + i);
+    }
     uint32_t fill = cb.n_data;
     if (cb.tb_crc_bits) {
         // whole-message CRC (CRC24A over the TB in the last CB; CRC16 ^ mask for the PLCF)
-        uint32_t crc = block_crc(inbit, cb.tb_crc_len, cb.tb_crc_poly, cb.tb_crc_bits, p.xp_arena + cb.xp_tb_off, &s_acc);
+        // (tb_crc_len is a whole number of bytes for TBs and PLCFs; the table is built for byte chunks)
+        uint32_t crc = block_crc_bytes(in, cb.tb_crc_len / 8, cb.tb_crc_poly, cb.tb_crc_bits, p.xp_arena + cb.xp_tb_off, &s_acc);
         if (p.plcf_mask) crc ^= p.plcf_mask[pkt];
         if (tid < cb.tb_crc_bits) c[fill + tid] = (uint8_t)((crc >> (cb.tb_crc_bits - 1 - tid)) & 1);
         fill += cb.tb_crc_bits;
@@ -216,7 +254,7 @@ __global__ void __launch_bounds__(256) k_tx_fec(const txfec_params_t p) {
             if (g >= wp && g < we) {
                 const uint32_t e = g - wp;
                 if (e < cb.n_e) {
-                    uint32_t pos = start + e % N;
+                    uint32_t pos = start + (e < N ? e : e % N);   // repetition (e >= N) only below rate 1/3
                     if (pos >= N) pos -= N;
                     bit = d[src[pos]];
                 }

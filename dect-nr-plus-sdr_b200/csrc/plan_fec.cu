@@ -85,12 +85,13 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
 
     // TX CRC tables: thread t of TX_FEC_THREADS owns bits [min(n, t c), min(n, t c + c)), c = ceil(n / threads); its partial
     // remainder is multiplied by x^(n - end + order) mod g (fec_tx.cu: block_crc)
-    auto add_xp_tx = [&](uint32_t nbits, uint32_t poly, uint32_t order) -> uint32_t {
+    // unit = 1: chunks of bits (code block CRC over unpacked bits); unit = 8: chunks of whole bytes (message CRC)
+    auto add_xp_tx = [&](uint32_t nbits, uint32_t poly, uint32_t order, uint32_t unit) -> uint32_t {
         const uint32_t off = (uint32_t)f.xp_arena.size();
-        const uint32_t chunk = (nbits + TX_FEC_THREADS - 1) / TX_FEC_THREADS;
+        const uint32_t n = nbits / unit, chunk = (n + TX_FEC_THREADS - 1) / TX_FEC_THREADS;
         for (uint32_t t = 0; t < TX_FEC_THREADS; ++t) {
-            const uint32_t b0 = std::min(nbits, t * chunk), b1 = std::min(nbits, b0 + chunk);
-            f.xp_arena.push_back(gf2_xpow_host(nbits - b1 + order, poly, order));
+            const uint32_t b0 = std::min(n, t * chunk), b1 = std::min(n, b0 + chunk);
+            f.xp_arena.push_back(gf2_xpow_host((n - b1) * unit + order, poly, order));
         }
         return off;
     };
@@ -133,8 +134,8 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         t.n_pad = 0;
         t.rm_src_off = rm_off[K];
         for (int rv = 0; rv < 4; ++rv) t.rm_start[rv] = rm_tab[K].start[rv];
-        t.xp_tb_off = t.tb_crc_bits ? add_xp_tx(t.tb_crc_len, t.tb_crc_poly, t.tb_crc_bits) : 0;
-        t.xp_cb_off = t.cb_crc ? add_xp_tx(t.n_data + t.tb_crc_bits, spec::CRC24B_POLY, 24) : 0;
+        t.xp_tb_off = t.tb_crc_bits ? add_xp_tx(t.tb_crc_len, t.tb_crc_poly, t.tb_crc_bits, 8) : 0;
+        t.xp_cb_off = t.cb_crc ? add_xp_tx(t.n_data + t.tb_crc_bits, spec::CRC24B_POLY, 24, 1) : 0;
         f.tx_cbs.push_back(t);
         rp_tx += t.n_data;
         wp_tx += t.n_e;
@@ -164,7 +165,7 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         soft_off += (3 * (K + 4) + 7) & ~7u;  // code blocks start 16-byte aligned (16-byte loads in the decoder)
         saved_off += rlen / 8;
     }
-    if (wp_tx != ps.G || rp_tx != s.tbs) return DNRP_ERR_INVALID;
+    if (wp_tx != ps.G || rp_tx != s.tbs || s.tbs % 8 != 0) return DNRP_ERR_INVALID;  // (whole bytes: fec_tx.cu CRC chunks)
     f.soft_stride = (soft_off + 7) & ~7u;
     f.saved_stride = (saved_off + 15) & ~15u;
     f.tb_stride = (out_byte + 15) & ~15u;          // N_TB_byte + 3 (TB CRC) rounded up
@@ -197,7 +198,7 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         t.wp = 0; t.n_e = spec::PCC_BITS; t.n_pad = 4;  // the reference scrambles 200 bits (pcc_enc.cpp:212)
         t.rm_src_off = rm_off[K];
         for (int rv = 0; rv < 4; ++rv) t.rm_start[rv] = rm_tab[K].start[rv];
-        t.xp_tb_off = add_xp_tx(t.tb_crc_len, t.tb_crc_poly, t.tb_crc_bits);
+        t.xp_tb_off = add_xp_tx(t.tb_crc_len, t.tb_crc_poly, t.tb_crc_bits, 8);
         t.xp_cb_off = 0;
         f.tx_pcc[ty] = t;
         cb_desc_t r{};
