@@ -57,7 +57,7 @@ class ClockSampler:
     def start(self):
         try:
             self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
-                                          "--format=csv,noheader,nounits", "-lms", "100"],
+                                          "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -68,17 +68,22 @@ class ClockSampler:
         for line in self.proc.stdout:
             self.rows.append([v.strip() for v in line.split(",")])
 
-    def stop(self):
+    def stop(self, first=0):
+        """first = number of rows that had arrived when the timed region started: the rows from there on were taken
+        during the timed region; if the region was shorter than the sampling period, the rows of the loaded warm-up
+        right before it are used and samples_in_timed_region says so"""
         if self.proc is None:
             return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
         self.proc.terminate()
         self.thread.join(timeout=2)
-        sm = [float(r[0]) for r in self.rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
-        mx = [float(r[1]) for r in self.rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
+        timed = self.rows[first:]
+        rows = timed if timed else self.rows
+        sm = [float(r[0]) for r in rows if len(r) >= 6 and r[0].replace(".", "").isdigit()]
+        mx = [float(r[1]) for r in rows if len(r) >= 6 and r[1].replace(".", "").isdigit()]
         names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
-        reasons = sorted({names[i] for r in self.rows if len(r) >= 6 for i in range(4) if r[2 + i] == "Active"})
+        reasons = sorted({names[i] for r in rows if len(r) >= 6 for i in range(4) if r[2 + i] == "Active"})
         return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
-                "reasons": reasons, "samples": len(sm)}
+                "reasons": reasons, "samples": len(sm), "samples_in_timed_region": len(timed)}
 
 
 # ---- CPU arm: the oracle (scalar C port of the reference algorithms) on the host cores ---------------
@@ -247,17 +252,21 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     # ---- resident steps: IQ windows + sync reports already in HBM (left there by e2e_step)
+    clocks = ClockSampler(local)
+    clocks.start()
     for _ in range(args.warmup):
         phy.time_stage(product.STAGE_SYNC_RX_CHAIN, P, reps=1)
+    t_wait = time.perf_counter()   # nvidia-smi needs a moment to deliver its first row: keep the device loaded meanwhile
+    while clocks.proc is not None and not clocks.rows and time.perf_counter() - t_wait < 3.0:
+        phy.time_stage(product.STAGE_SYNC_RX_CHAIN, P, reps=1)
     phy.kernel_time_enable(True)
-    clocks = ClockSampler(local)
     barrier()
-    clocks.start()
+    rows_before = len(clocks.rows)
     l0 = phy.launch_count()
     ms_step = phy.time_stage(product.STAGE_SYNC_RX_CHAIN, P, reps=args.steps)   # CUDA events on the kernels' stream
     launches = phy.launch_count() - l0
     barrier()
-    clk = clocks.stop()
+    clk = clocks.stop(rows_before)
     k_ms, k_cnt = phy.kernel_time_read(product.KERNEL_TURBO_DECODE_PDC)
     others = {name: phy.kernel_time_read(k) for name, k in (("k_rx_fft", product.KERNEL_RX_FFT),
                                                             ("k_rx_demap_pdc", product.KERNEL_RX_DEMAP_PDC),
