@@ -11,11 +11,11 @@ namespace dnrp {
 
 // LTE Gray mapping, TS 36.211 7.1 (srsRAN lte_tables.c; reference fix/mod.cpp:137-174), bits MSB first
 __device__ __forceinline__ float2 qam_symbol(const uint8_t* __restrict__ bits, uint32_t off, uint32_t N_bps) {
-    uint32_t v = 0;
-    for (uint32_t i = 0; i < N_bps; ++i) {
-        const uint32_t g = off + i;
-        v = (v << 1) | ((bits[g >> 3] >> (7 - (g & 7))) & 1u);
-    }
+    // N_bps <= 8 bits span at most two bytes: one 16-bit window instead of a byte load per bit (the second byte is
+    // only touched when the symbol straddles it)
+    const uint32_t b = off >> 3;
+    const uint32_t win = ((uint32_t)bits[b] << 8) | ((off & 7) + N_bps > 8 ? (uint32_t)bits[b + 1] : 0u);
+    const uint32_t v = (win >> (16 - (off & 7) - N_bps)) & ((1u << N_bps) - 1u);
     if (N_bps == 1) {
         const float a = v ? -0.70710678118654752f : 0.70710678118654752f;
         return make_float2(a, a);
