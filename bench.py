@@ -210,6 +210,7 @@ def run_b200(args):
         raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback (use --impl reference)")
     torch.cuda.set_device(local)
     if world > 1:
+        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries the one JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     product = load_product()
     if not os.path.exists(product.LIB_PATH):
