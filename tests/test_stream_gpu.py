@@ -83,3 +83,25 @@ def test_stream_packets_decode_through_the_batched_receiver(product):
     assert pcc.plcf_ok[:, 0].all() and np.array_equal(pcc.plcf[:, 0, :5], plcf[:, :5])
     assert ok.all() and np.array_equal(tb_out, tb)
     phy.close()
+
+
+def test_stream_edge_cases(product):
+    """noise only: nothing found; a stream shorter than one STF plus its history is refused; one packet right at the
+    earliest detectable position and one cut off at the end of the stream"""
+    cfg = (1, 2, 1, 1, 0, 3, 2048)
+    phy, stream, starts, tb, plcf = _make_stream(product, cfg, 3, snr_db=20.0, seed=5)
+    rng = np.random.default_rng(1)
+    noise = (0.05 * (rng.standard_normal((1, 20000)) + 1j * rng.standard_normal((1, 20000)))).astype(np.complex64)
+    assert len(phy.stream_sync(noise)) == 0
+    with pytest.raises(product.DnrpError):
+        phy.stream_sync(noise[:, :300])
+    # cut the stream in the middle of the last packet: its STF is still there, so it is reported (the receiver will
+    # fail its CRC); cut inside its STF: not reported
+    S = phy.ps["N_samples_packet_no_GI"]
+    cut = stream[:, :starts[2] + S // 2]
+    got = phy.stream_sync(np.ascontiguousarray(cut))
+    assert np.array_equal(got.fine_peak_time_64, starts)
+    cut = stream[:, :starts[2] + phy.ps["N_samples_STF"] // 2]
+    got = phy.stream_sync(np.ascontiguousarray(cut))
+    assert np.array_equal(got.fine_peak_time_64, starts[:2])
+    phy.close()
