@@ -209,8 +209,12 @@ def run_b200(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py: no CUDA device; the product has no CPU fallback (use --impl reference)")
     torch.cuda.set_device(local)
+    # stdout carries the one JSON line only: library chatter written to file descriptor 1 (NCCL prints its version
+    # there) goes to stderr until the result is printed
+    sys.stdout.flush()
+    stdout_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries the one JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     product = load_product()
     if not os.path.exists(product.LIB_PATH):
@@ -425,7 +429,9 @@ def run_b200(args):
                          "channel_packets_per_s": P / (ch_ms * 1e-3),
                          "note": "per rank, %d packets per pass; not part of the timed step" % P},
     }
-    print(json.dumps(out))
+    sys.stdout.flush()
+    os.dup2(stdout_fd, 1)
+    print(json.dumps(out), flush=True)
     if world > 1:
         dist.destroy_process_group()
 

@@ -146,8 +146,12 @@ def main():
     if not torch.cuda.is_available():
         raise SystemExit("per_sweep.py: no CUDA device; the product has no CPU fallback")
     torch.cuda.set_device(local)
+    # stdout carries the one JSON line only: library chatter written to file descriptor 1 (NCCL prints its version
+    # there) goes to stderr until the result is printed
+    sys.stdout.flush()
+    stdout_fd = os.dup(1)
+    os.dup2(2, 1)
     if world > 1:
-        os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")   # stdout carries the one JSON line only
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     product = load_product()
     snr_list = [float(v) for v in np.arange(args.snr[0], args.snr[1] + 0.5 * args.snr[2], args.snr[2])]
@@ -181,9 +185,11 @@ def main():
                 with open(os.path.join(args.out, name + ".json"), "w") as f:
                     json.dump(j, f, indent=4)
         tot = mat[:, :SUMMED].sum(axis=0)
+        sys.stdout.flush()
+        os.dup2(stdout_fd, 1)
         print(json.dumps({"cells": len(cells), "n_gpus": world, "packets": int(tot[0]), "seconds": dt,
                           "packets_per_s": float(tot[0] / dt), "pdc_crc_ok": int(tot[5]), "tb_mismatch_after_crc_ok": int(tot[5] - tot[6]),
-                          "files": sorted(files)}))
+                          "files": sorted(files)}), flush=True)
     if world > 1:
         dist.destroy_process_group()
 
