@@ -54,6 +54,41 @@ __global__ void __launch_bounds__(256) k_derm(const tdec_params_t p, uint32_t ca
         const uint32_t g = cb.rp + e + p.gold_bit_off;
         return ((p.gold[g >> 3] >> (7 - (g & 7))) & 1) ? -v : v;
     };
+    if (single && (reinterpret_cast<uintptr_t>(llr) & 3) == 0) {
+        // ---- usual case (code rate >= 1/3, LLR pairs aligned): build the soft-buffer image in shared memory by
+        // SCATTERING the n_e descrambled LLRs through the inverse table into a zeroed image (n_e random 2-byte stores
+        // instead of N random 2-byte loads: N / n_e = 2.5 at R = 5/6), then stream the image out with 8-byte accesses
+        uint4* Z = reinterpret_cast<uint4*>(DSC);
+        for (uint32_t i = tid; i < (N + 7) / 8; i += nthr) Z[i] = make_uint4(0u, 0u, 0u, 0u);   // cap >= N rounded up to 8
+        __syncthreads();
+        const uint32_t* llr2 = reinterpret_cast<const uint32_t*>(llr);
+        const uint16_t* inv = p.rm_arena + cb.rm_inv_off + (size_t)rv * N;
+        const uint32_t g0 = cb.rp + p.gold_bit_off;
+#pragma unroll 4
+        for (uint32_t e2 = tid; e2 < cb.n_e / 2; e2 += nthr) {
+            const uint32_t w = llr2[e2];
+            const uint32_t g = g0 + 2 * e2;
+            const uint32_t gw = ((uint32_t)p.gold[g >> 3] << 8) | p.gold[(g >> 3) + 1];
+            const uint32_t b0 = (gw >> (15 - (g & 7))) & 1u, b1 = (gw >> (14 - (g & 7))) & 1u;
+            const uint32_t m = (b0 ? 0xffffu : 0u) | (b1 ? 0xffff0000u : 0u);
+            const uint32_t v = __vsub2(w ^ m, m);
+            DSC[inv[2 * e2]] = (int16_t)(v & 0xffffu);
+            DSC[inv[2 * e2 + 1]] = (int16_t)(v >> 16);
+        }
+        if ((cb.n_e & 1) && tid == 0) DSC[inv[cb.n_e - 1]] = (int16_t)descr(cb.n_e - 1, llr[cb.n_e - 1]);
+        __syncthreads();
+        const uint2* img = reinterpret_cast<const uint2*>(DSC);
+        uint2* soft4 = reinterpret_cast<uint2*>(soft);
+        for (uint32_t q = tid; q < N / 4; q += nthr) {
+            uint2 v = img[q];
+            if (!reset) {
+                const uint2 old = soft4[q];
+                v = make_uint2(__vadd2(v.x, old.x), __vadd2(v.y, old.y));   // int16 wrap-around adds, as below
+            }
+            soft4[q] = v;
+        }
+        return;
+    }
     if (staged) {
         if ((reinterpret_cast<uintptr_t>(llr) & 3) == 0) {
             // two LLRs per 4-byte load

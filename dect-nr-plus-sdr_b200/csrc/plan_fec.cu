@@ -75,6 +75,14 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         const uint32_t N = 3 * D;
         for (int rv = 0; rv < 4; ++rv)
             for (uint32_t n = 0; n < N; ++n) f.rm_arena.push_back((uint16_t)((posT[n] + N - t.start[rv]) % N));
+        // and the inverse per redundancy version: received LLR e (first pass over the circular buffer) -> soft-buffer
+        // position; k_derm scatters the n_e <= N LLRs of a code block through it into a zeroed shared image of the soft
+        // buffer (fewer random accesses than gathering all N positions at the usual code rates)
+        for (int rv = 0; rv < 4; ++rv) {
+            std::vector<uint16_t> inv(N);
+            for (uint32_t n = 0; n < N; ++n) inv[(posT[n] + N - t.start[rv]) % N] = (uint16_t)n;
+            f.rm_arena.insert(f.rm_arena.end(), inv.begin(), inv.end());
+        }
         rm_tab[K] = t;
     };
     auto add_xp = [&](uint32_t K, uint32_t L, uint32_t poly, uint32_t order) -> uint32_t {
@@ -155,6 +163,7 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         r.rlen_byte = rlen / 8;
         r.soft_off = soft_off;
         r.rm_off = rm_off[K] + 3 * (K + 4);  // pos[]
+        r.rm_inv_off = r.rm_off + 4 * 3 * (K + 4);
         for (int rv = 0; rv < 4; ++rv) r.rm_start[rv] = rm_tab[K].start[rv];
         r.crc_poly = poly;
         r.crc_order = 24;
@@ -209,6 +218,7 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         r.rlen_byte = nb / 8;
         r.soft_off = ty * 320;     // soft_pcc [packet][2][320]
         r.rm_off = rm_off[K] + 3 * (K + 4);
+        r.rm_inv_off = r.rm_off + 4 * 3 * (K + 4);
         for (int rv = 0; rv < 4; ++rv) r.rm_start[rv] = rm_tab[K].start[rv];
         r.crc_poly = spec::CRC16_POLY;
         r.crc_order = 16;

@@ -30,6 +30,7 @@ struct cb_desc_t {
     uint32_t out_byte, rlen_byte;  // where the decoded bytes go inside the TB, how many (CB CRC dropped)
     uint32_t soft_off;         // offset (int16 elements) of this CB inside the packet's soft buffer
     uint32_t rm_off;           // offset of this K's rate-matching table (pos[]) in the table arena
+    uint32_t rm_inv_off;       // offset of the inverse tables (per redundancy version: LLR index -> soft-buffer position)
     uint32_t rm_start[4];      // start position per redundancy version
     uint32_t crc_poly, crc_order;  // check polynomial of this CB (24B, 24A when C == 1, 16 for PLCF)
     uint32_t xp_off;           // offset of the per-window x^n mod g table in the table arena
