@@ -529,6 +529,28 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
     if (skipped) return;  // no barrier below
 
     // ---- outputs: packed bytes (MSB first), flags
+    if (L == 32) {
+        // a window is one 32-bit word of the code block: every thread packs its own two windows (conflict-free column
+        // reads, no index arithmetic) and stores their four bytes each
+        if (tid < T) {
+            uint32_t w_lo = 0, w_hi = 0;
+#pragma unroll 4
+            for (uint32_t k = 0; k < 32; ++k) {
+                const uint32_t hb = HARD[k * T + t];
+                w_lo = (w_lo << 1) | (hb & 1u);
+                w_hi = (w_hi << 1) | (hb >> 1);
+            }
+#pragma unroll
+            for (uint32_t j = 0; j < 8; ++j) {
+                const uint32_t bi = (j < 4 ? 0u : KH / 8) + 4 * t + (j & 3u);
+                const uint8_t v = (uint8_t)((j < 4 ? w_lo : w_hi) >> (24 - 8 * (j & 3u)));
+                if (bi < cb.rlen_byte) {
+                    tb_out[bi] = v;
+                    if (saved && crc_ok) saved[bi] = v;
+                }
+            }
+        }
+    } else
     for (uint32_t bi = tid; bi < K / 8; bi += nthr) {
         uint32_t v = 0;
 #pragma unroll
