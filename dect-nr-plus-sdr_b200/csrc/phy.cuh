@@ -23,6 +23,10 @@ struct phy_dims_t {
     const uint32_t* cell;      // [(N_DF+1)][Nk] cell words (spec_re.hpp)
     const uint32_t* pcc_lk;    // [98]
     const uint32_t* pdc_lk;    // [N_PDC_subc]
+    // channel-estimation plan per demapper unit (cell, or cell pair with transmit diversity) and stream slot (A, B):
+    // everything rx_synced's processing-stage bookkeeping derives from (symbol, stream), packed by ce_plan_word()
+    const uint32_t* pcc_plan;  // [units][2]
+    const uint32_t* pdc_plan;  // [units][2]
     const int8_t* stf_sign;    // [Nk]
     const int8_t* W;           // [n_cb_idx][N_TX][N_TS] codes 0, +-1, +-2 (= +-j)
     const float* W_scale;      // [n_cb_idx]
@@ -40,6 +44,12 @@ struct phy_dims_t {
         uint32_t n_interp, n_t;
     } wiener_l[3], wiener_lr[3];            // per SNR class {-5, 15, 35} dB (rx_synced_param.hpp:216-232)
 };
+
+// plan word: LUT slice base (o = base * Nk + k) | class slot j | pilot row | interlace flip | stream | mode lr
+__host__ __device__ __forceinline__ uint32_t ce_plan_word(uint32_t base, uint32_t j, uint32_t row, uint32_t flip, uint32_t ts,
+                                                          uint32_t lr) {
+    return base | j << 6 | row << 12 | flip << 17 | ts << 18 | lr << 21;
+}
 
 // per-packet receiver state, produced by the STF stage and consumed by every later stage
 // (the mutable part of sync_report_t + estimator_sto/snr state, reference rx_synced.cpp:503-619)

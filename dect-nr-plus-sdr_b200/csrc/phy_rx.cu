@@ -275,23 +275,23 @@ __global__ void k_rx_snr_class(const rx_params_t p, uint32_t n_packets) {
 // All NRX receive antennas at once: h[a] = estimate seen by antenna a.  Symbol plan, LUT indices and the weights are
 // the same for every antenna, so they are computed / loaded once and every tap is applied to the NRX pilot sets.
 template <int NRX>
-__device__ __forceinline__ void chan_est_rx(const rx_params_t& p, uint32_t pkt, uint32_t ts, uint32_t l, uint32_t k,
-                                            bool pcc_stage, float2 (&h)[NRX]) {
+__device__ __forceinline__ void chan_est_rx(const rx_params_t& p, uint32_t pkt, uint32_t plan, uint32_t k, float2 (&h)[NRX]) {
     const phy_dims_t& d = p.d;
-    const uint8_t* cls = p.cls + (size_t)pkt * p.cls_stride;
+    // plan word (plan_phy.cu, ce_plan_word): the symbol / stream bookkeeping was done on the host
+    const uint32_t base = plan & 63u, j = (plan >> 6) & 63u, row = (plan >> 12) & 31u, flip = (plan >> 17) & 1u,
+                   ts = (plan >> 18) & 7u, lr = (plan >> 21) & 1u;
+    const phy_dims_t::wiener_dev_t& W = lr ? d.wiener_lr[p.cls[(size_t)pkt * p.cls_stride + j]]
+                                           : d.wiener_l[p.cls[(size_t)pkt * p.cls_stride + j]];
     const size_t stride_a = (size_t)d.N_eff_TX * d.n_drs * d.NP;    // pilots of the next antenna
-    const float2* hz_ts = p.hzf + (((size_t)pkt * d.N_RX) * d.N_eff_TX + ts) * d.n_drs * d.NP;
+    const float2* hz_row = p.hzf + ((((size_t)pkt * d.N_RX) * d.N_eff_TX + ts) * d.n_drs + row) * d.NP;
+    const size_t o = (size_t)base * d.Nk + k;
+    const float* w = W.weights + (size_t)W.idx_weight[o] * W.n_interp;
+    const uint32_t m0 = W.idx_pilot[o];
 #pragma unroll
     for (int a = 0; a < NRX; ++a) h[a] = make_float2(0.f, 0.f);
-    if (pcc_stage || !d.chestim_lr || d.n_full_ps == 0) {
-        uint32_t n = __umulhi(l - 1, d.N_step_inv);  // (l - 1) / N_step
-        if (n >= d.n_drs) n = d.n_drs - 1;
-        const uint32_t j = d.N_eff_TX == 8 ? 2 * n + (ts >= 4 ? 1 : 0) : n;
-        const phy_dims_t::wiener_dev_t& W = d.wiener_l[cls[j]];
-        const uint32_t pc = ((ts & 3) + 2 * (n & 1)) & 3;
-        const size_t o = (size_t)pc * d.Nk + k;
-        const float* w = W.weights + (size_t)W.idx_weight[o] * W.n_interp;
-        const float2* hz = hz_ts + (size_t)n * d.NP + W.idx_pilot[o];
+    if (!lr) {
+        // mode "l": non-interlaced pilots of DRS occurrence row
+        const float2* hz = hz_row + m0;
         for (uint32_t i = 0; i < W.n_interp; ++i) {
             const float wi = w[i];
 #pragma unroll
@@ -302,27 +302,11 @@ __device__ __forceinline__ void chan_est_rx(const rx_params_t& p, uint32_t pkt, 
             }
         }
     } else {
-        uint32_t ps = 0, r = 0;
-        if (l > 1) {
-            ps = __umulhi(l - 2, d.N_step_inv);  // (l - 2) / N_step
-            if (ps > d.n_full_ps - 1) ps = d.n_full_ps - 1;
-            r = l - 1 - ps * d.N_step;
-        }
-        const uint32_t rs = ps == 0 ? 0 : 1;
-        const uint32_t re = r < d.N_step ? r : d.N_step;
-        const uint32_t rstar = d.chestim_stride_inv ? rs + __umulhi(re - rs, d.chestim_stride_inv) * d.chestim_stride : re;
-        const uint32_t j = d.N_eff_TX == 8 ? 2 * (ps + 1) + 1 : ps + 1;
-        const phy_dims_t::wiener_dev_t& W = d.wiener_lr[cls[j]];
-        const uint32_t pc = ((ts & 3) + 2 * (ps & 1)) & 3;
-        const size_t o = ((size_t)rstar * 4 + pc) * d.Nk + k;
-        const float* w = W.weights + (size_t)W.idx_weight[o] * W.n_interp;
-        const uint32_t m0 = W.idx_pilot[o];
-        const uint32_t flip = pc >= 2 ? 1 : 0;
-        const float2* hz_ps = hz_ts + (size_t)ps * d.NP;
+        // mode "lr": pilots interlaced over DRS occurrences row (left) and row + 1 (right)
         for (uint32_t i = 0; i < W.n_interp; ++i) {
             const uint32_t m = m0 + i;
             const uint32_t side = (m & 1) ^ flip;
-            const float2* hz = hz_ps + (size_t)side * d.NP + (m >> 1);
+            const float2* hz = hz_row + (size_t)side * d.NP + (m >> 1);
             const float wi = w[i];
 #pragma unroll
             for (int a = 0; a < NRX; ++a) {
@@ -332,19 +316,6 @@ __device__ __forceinline__ void chan_est_rx(const rx_params_t& p, uint32_t pkt, 
             }
         }
     }
-}
-
-// transmit stream pair of Alamouti pair index i_mod (Table 6.3.3.2, reference
-// transmit_diversity_precoding.cpp:45-72); same table as the transmitter
-__device__ __forceinline__ void txdiv_pair_rx(uint32_t N_TS, uint32_t i_mod, uint32_t& A, uint32_t& B) {
-    if (N_TS == 2) { A = 0; B = 1; return; }
-    if (N_TS == 4) {
-        A = (0x101020u >> (4 * i_mod)) & 0xfu;   // 0 2 0 1 0 1
-        B = (0x233231u >> (4 * i_mod)) & 0xfu;   // 1 3 2 3 3 2
-        return;
-    }
-    A = (uint32_t)((0x541032106420ull >> (4 * i_mod)) & 0xfull);  // 0 2 4 6 0 1 2 3 0 1 4 5
-    B = (uint32_t)((0x763276547531ull >> (4 * i_mod)) & 0xfull);  // 1 3 5 7 4 5 6 7 2 3 6 7
 }
 
 // float -> int16 like a C cast (toward zero), saturating
@@ -403,6 +374,7 @@ __global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_dema
     const uint32_t n_cells = pcc ? 98u : d.N_PDC_subc;
     const uint32_t N_bps = pcc ? 2u : d.N_bps;
     const uint32_t* lk = pcc ? d.pcc_lk : d.pdc_lk;
+    const uint32_t* plan = pcc ? d.pcc_plan : d.pdc_plan;
     int16_t* out = pcc ? p.llr_pcc + (size_t)pkt * 196 : p.llr + (size_t)pkt * p.llr_stride;
     const uint32_t u = blockIdx.x * blockDim.x + threadIdx.x;
     const uint32_t cells_per_unit = TXDIV ? 2u : 1u;
@@ -416,7 +388,7 @@ __global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_dema
             float2 num = make_float2(0.f, 0.f);
             float den = 0.f;
             float2 h[NRX];
-            chan_est_rx<NRX>(p, pkt, 0, l, k, pcc, h);
+            chan_est_rx<NRX>(p, pkt, plan[2 * u], k, h);
 #pragma unroll
             for (int a = 0; a < NRX; ++a) {
                 // streaming loads / stores (evict first): Y and the LLRs pass through once, the pilots stay in L1
@@ -428,21 +400,19 @@ __global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_dema
         } else {
             const uint32_t q = 2 * u;
             const uint32_t l = lk[q] >> 16, k0 = lk[q] & 0xffffu, k1 = lk[q + 1] & 0xffffu;
-            const uint32_t im = u % d.txdiv_modulo;
-            uint32_t tsA, tsB;
-            txdiv_pair_rx(d.N_eff_TX, im, tsA, tsB);
+            const uint32_t planA = plan[2 * u], planB = plan[2 * u + 1];   // streams A, B of this pair (Table 6.3.3.2)
             float2 n0 = make_float2(0.f, 0.f), n1 = n0;
             float den = 0.f;
             // per antenna: h0 = mean of stream A's estimates at the two cells, h1 = the same for stream B
             float2 h0[NRX], h1[NRX];
             {
                 float2 t[NRX];
-                chan_est_rx<NRX>(p, pkt, tsA, l, k0, pcc, h0);
-                chan_est_rx<NRX>(p, pkt, tsA, l, k1, pcc, t);
+                chan_est_rx<NRX>(p, pkt, planA, k0, h0);
+                chan_est_rx<NRX>(p, pkt, planA, k1, t);
 #pragma unroll
                 for (int a = 0; a < NRX; ++a) h0[a] = make_float2(0.5f * (h0[a].x + t[a].x), 0.5f * (h0[a].y + t[a].y));
-                chan_est_rx<NRX>(p, pkt, tsB, l, k0, pcc, h1);
-                chan_est_rx<NRX>(p, pkt, tsB, l, k1, pcc, t);
+                chan_est_rx<NRX>(p, pkt, planB, k0, h1);
+                chan_est_rx<NRX>(p, pkt, planB, k1, t);
 #pragma unroll
                 for (int a = 0; a < NRX; ++a) h1[a] = make_float2(0.5f * (h1[a].x + t[a].x), 0.5f * (h1[a].y + t[a].y));
             }

@@ -122,6 +122,52 @@ int build_phy_plan(dnrp_ctx* c) {
         d.pcc_l_max = 0;
         for (uint32_t v : m.pcc_lk) d.pcc_l_max = std::max(d.pcc_l_max, v >> 16);
     }
+    {
+        // which interpolation serves (stream ts, symbol l): closed form of rx_synced.cpp:1027-1152,
+        // evaluated once per demapper unit here instead of per cell and packet on the device
+        auto plan_word = [&](uint32_t ts, uint32_t l, bool pcc_stage) -> uint32_t {
+            if (pcc_stage || !d.chestim_lr || d.n_full_ps == 0) {
+                uint32_t n = (l - 1) / d.N_step;
+                if (n >= d.n_drs) n = d.n_drs - 1;
+                const uint32_t j = d.N_eff_TX == 8 ? 2 * n + (ts >= 4 ? 1 : 0) : n;
+                const uint32_t pc = ((ts & 3) + 2 * (n & 1)) & 3;
+                return ce_plan_word(pc, j, n, 0, ts, 0);
+            }
+            uint32_t ps_ = 0, r = 0;
+            if (l > 1) {
+                ps_ = (l - 2) / d.N_step;
+                if (ps_ > d.n_full_ps - 1) ps_ = d.n_full_ps - 1;
+                r = l - 1 - ps_ * d.N_step;
+            }
+            const uint32_t rs = ps_ == 0 ? 0 : 1, re = r < d.N_step ? r : d.N_step;
+            const uint32_t rstar = rs + ((re - rs) / d.chestim_stride) * d.chestim_stride;
+            const uint32_t j = d.N_eff_TX == 8 ? 2 * (ps_ + 1) + 1 : ps_ + 1;
+            const uint32_t pc = ((ts & 3) + 2 * (ps_ & 1)) & 3;
+            return ce_plan_word(rstar * 4 + pc, j, ps_, pc >= 2 ? 1 : 0, ts, 1);
+        };
+        auto pair_streams = [&](uint32_t im, uint32_t& A, uint32_t& B) {   // Table 6.3.3.2 (phy_rx.cu: txdiv_pair_rx)
+            static const uint8_t a4[6] = {0, 2, 0, 1, 0, 1}, b4[6] = {1, 3, 2, 3, 3, 2};
+            static const uint8_t a8[12] = {0, 2, 4, 6, 0, 1, 2, 3, 0, 1, 4, 5}, b8[12] = {1, 3, 5, 7, 4, 5, 6, 7, 2, 3, 6, 7};
+            if (d.N_eff_TX == 2) { A = 0; B = 1; }
+            else if (d.N_eff_TX == 4) { A = a4[im]; B = b4[im]; }
+            else { A = a8[im]; B = b8[im]; }
+        };
+        auto build = [&](const std::vector<uint32_t>& lk, bool pcc_stage) {
+            const bool txdiv = d.N_eff_TX != 1;
+            const uint32_t units = (uint32_t)lk.size() / (txdiv ? 2 : 1);
+            std::vector<uint32_t> t(2 * (size_t)units, 0u);
+            for (uint32_t u = 0; u < units; ++u) {
+                const uint32_t l = lk[txdiv ? 2 * u : u] >> 16;
+                uint32_t A = 0, B = 0;
+                if (txdiv) pair_streams(u % d.txdiv_modulo, A, B);
+                t[2 * u] = plan_word(A, l, pcc_stage);
+                t[2 * u + 1] = plan_word(B, l, pcc_stage);
+            }
+            return t;
+        };
+        UP(c->d_pcc_plan.upload(build(m.pcc_lk, true)));
+        UP(c->d_pdc_plan.upload(build(m.pdc_lk, false)));
+    }
     static const double nu_max[3] = {100.0, 100.0, 500.0}, tau_rms[3] = {0.1e-6, 0.1e-6, 1.0e-6},
                         snr_db[3] = {-5.0, 15.0, 35.0};
     static const uint32_t n_lr[3] = {14, 8, 3}, n_l[3] = {7, 4, 2};
@@ -288,6 +334,7 @@ int build_phy_plan(dnrp_ctx* c) {
         return DNRP_ERR_CUDA;
     }
     d.cell = c->d_cell.p; d.pcc_lk = c->d_pcc_lk.p; d.pdc_lk = c->d_pdc_lk.p;
+    d.pcc_plan = c->d_pcc_plan.p; d.pdc_plan = c->d_pdc_plan.p;
     d.stf_sign = c->d_stf_sign.p; d.W = c->d_W.p; d.W_scale = c->d_W_scale.p; d.W_scale_opt = c->d_W_scale_opt.p;
     d.twiddle = c->d_twiddle.p;
     return DNRP_OK;
