@@ -409,7 +409,7 @@ __global__ void __launch_bounds__(XC_THREADS) k_sync_xcorr(const sync_params_t p
 // shared-memory FFT is the cheaper way to the same numbers (fp32 rounding differs, the arg max does not).
 constexpr uint32_t XF_THREADS = 256, XF_MAX_PER_THREAD = 16;
 
-__global__ void __launch_bounds__(XF_THREADS) k_sync_xcorr_fft(const sync_params_t p, uint32_t len) {
+__global__ void __launch_bounds__(XF_THREADS, 3) k_sync_xcorr_fft(const sync_params_t p, uint32_t len) {
     extern __shared__ __align__(16) float2 smem_f[];
     __shared__ unsigned long long s_best;
     const phy_dims_t& d = p.d;
