@@ -293,8 +293,10 @@ static int rx_batch_impl(dnrp_ctx_t* c, uint32_t n, const void* iq_in, float sc1
         // Measured on C2 / 10 000 windows (scratch/e2e_weights.py): one chunk costs 0.19 ms + 1.51 us per packet.
         // cf32 windows: the copy (2.17 us per packet over PCIe) is the bottleneck -> many gently tapered chunks, the
         // last copy is followed by a short computation.  sc16 windows: the kernels are the bottleneck -> few chunks
-        // growing by <= 1.4x, so that the first kernels start early and no chunk waits for its copy.
-        static const uint32_t wc[] = {2, 2, 3, 3, 4, 4, 4, 4, 4, 4, 4, 4, 3, 3, 2, 2}, ws[] = {4, 6, 8, 11, 15, 21, 32},
+        // growing by <= 1.4x, so that the first kernels start early and no chunk waits for its copy.  (r01k: with the faster
+        // kernels copy and compute of the sc16 path are balanced too -- seven chunks tapered at both ends measured best:
+        // 15.7 -> 14.6 ms per 10 000 C2 windows.)
+        static const uint32_t wc[] = {2, 2, 3, 3, 4, 4, 4, 4, 4, 4, 4, 4, 3, 3, 2, 2}, ws[] = {2, 3, 4, 4, 4, 3, 2},
                               w6[] = {2, 3, 4, 4, 3, 2}, w3[] = {1, 1, 1}, w1[] = {1};
         const uint32_t* w = n >= 8192 ? (sc16 ? ws : wc) : (n >= 2048 ? w6 : (n >= 256 ? w3 : w1));
         uint32_t nw = n >= 8192 ? (sc16 ? 7 : 16) : (n >= 2048 ? 6 : (n >= 256 ? 3 : 1));
