@@ -218,6 +218,14 @@ class Phy:
                                           _ptr(plcf, np.uint8), _ptr(mask, np.uint32), _ptr(nit, np.uint8)))
         return ok.astype(bool), plcf, mask, nit
 
+    def fec_decode_plcf_noalloc(self, n, llr196_dev, ok_dev, plcf_dev, mask_dev, n_iter_dev, stream=None):
+        """dnrp_fec_decode_plcf_noalloc: all arguments are DEVICE addresses (ints) of caller-owned buffers
+        (llr196 [n][196] int16, ok [n][2] u8, plcf [n][2][16] u8, mask [n][2] u32, n_iter [n][2] u8); the call only
+        enqueues kernels (scratch = the library's static device array) and does not synchronise"""
+        _check(lib().dnrp_fec_decode_plcf_noalloc(self._ctx, C.c_uint32(n), C.c_void_p(llr196_dev), C.c_void_p(ok_dev),
+                                                  C.c_void_p(plcf_dev), C.c_void_p(mask_dev), C.c_void_p(n_iter_dev),
+                                                  C.c_void_p(stream)))
+
     # ---- tx_t::generate_tx_packet (reference lib/src/phy/tx/tx.cpp:165-314)
     def tx(self, plcf, tb, codebook_index=0, DAC_scale=1.0, iq_phase_rad=0.0, iq_phase_increment=0.0,
            GI_percentage=5, rv=0, optimal_scaling_DAC=False, fetch=True):

@@ -104,6 +104,24 @@ int dnrp_fec_decode_tb(dnrp_ctx_t* ctx, uint32_t n, const int16_t* llr, const ui
 int dnrp_fec_decode_plcf(dnrp_ctx_t* ctx, uint32_t n, const int16_t* llr196, uint8_t* ok, uint8_t* plcf,
                          uint32_t* mask, uint8_t* n_iter);
 
+/* dnrp_fec_decode_plcf for callers that must not allocate: code under CUDA graph capture, tight serving loops,
+ * harnesses that forbid cudaMalloc.  NO COUNTERPART IN THE REFERENCE.
+ * Same kernels and results as dnrp_fec_decode_plcf, but (i) inputs and outputs are DEVICE pointers owned by the
+ * caller, (ii) the decoder's scratch (the de-rate-matched soft buffers, 1280 bytes per packet) lives in a static
+ * __device__ array of DNRP_NOALLOC_MAX_PACKETS packets (5 MiB, held by every GPU that loads the library until the
+ * process exits) instead of a context workspace, (iii) the call only enqueues two kernels on `stream` (a
+ * cudaStream_t; NULL = the context's stream) and returns without synchronising; it calls no cudaMalloc / cudaFree /
+ * allocating library routine.  n > DNRP_NOALLOC_MAX_PACKETS returns DNRP_ERR_INVALID.  All calls on one GPU share
+ * the scratch array (it keeps the last call's contents; every value a decode reads is rewritten first, nothing needs
+ * clearing): calls that overlap on the GPU (different streams, or graphs replayed concurrently) RACE on it --
+ * serialise them.  The first call per device looks the array's device address up (cudaGetSymbolAddress); make that
+ * call outside stream capture.
+ * llr196_dev [n][196] int16; ok_dev [n][2]; plcf_dev [n][2][16] (the first 5 / 10 bytes of each entry are the PLCF);
+ * mask_dev [n][2] (matched CRC mask, 0xffffffff = none); n_iter_dev [n][2]. */
+#define DNRP_NOALLOC_MAX_PACKETS 4096
+int dnrp_fec_decode_plcf_noalloc(dnrp_ctx_t* ctx, uint32_t n, const int16_t* llr196_dev, uint8_t* ok_dev,
+                                 uint8_t* plcf_dev, uint32_t* mask_dev, uint8_t* n_iter_dev, void* stream);
+
 /* ---- transmitter ------------------------------------------------------------------------------
  * dnrp_tx_desc_t = tx_descriptor_t{codebook_index, tx_meta_t} + the HARQ redundancy version
  * (lib/include/dectnrp/phy/tx/tx_descriptor.hpp:43-78, tx_meta.hpp:32-58, harq/process_tx.hpp). */
