@@ -54,6 +54,8 @@ def lib():
         _lib.ref_rx_create.restype = C.c_void_p
         _lib.ref_resample_n_after.restype = C.c_uint32
         _lib.ref_rx_n_rx.restype = C.c_uint32
+        _lib.ref_pool_create.restype = C.c_void_p
+        _lib.ref_pool_threads.restype = C.c_uint32
     return _lib
 
 
@@ -245,3 +247,45 @@ def sync_stream(iq, psdef_max, os=1, resample=(1, 1), chunk_length=0, max_out=64
         d["rms_array"] = rms[i].copy()
         res.append(d)
     return res
+
+
+class Pool:
+    """n_threads workers (ring buffer + sync_chunk_t + rx_synced_t each), the reference's own scaling model; used by
+    bench.py's reference arm and cpu_baseline"""
+
+    def __init__(self, psdef_max, n_window, threads, os=1, resample=(1, 1), chestim_lr=True, stride=2, network_id=123456789):
+        self.ps_max = get_packet_sizes(*psdef_max)
+        self.n_window, self.network_id = n_window, network_id
+        self._h = C.c_void_p(lib().ref_pool_create(_p(_u32(psdef_max)), os, resample[0], resample[1], n_window, int(chestim_lr), stride,
+                                                   threads, C.c_uint32(network_id)))
+        assert self._h.value
+        self.N_RX = self.ps_max["N_TX"]
+        self.threads = lib().ref_pool_threads(self._h)
+
+    def close(self):
+        if self._h:
+            lib().ref_pool_destroy(self._h)
+            self._h = None
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def rx_windows(self, iq, psdef, plcf_type=1):
+        """iq [n][N_RX][n_window] complex64 -> dict(crc_ok, tb, fine_peak, plcf_ok, stage_ms)"""
+        iq = np.ascontiguousarray(iq, dtype=np.complex64)
+        n = iq.shape[0]
+        assert iq.shape[1] == self.N_RX and iq.shape[2] <= self.n_window
+        ps = get_packet_sizes(*psdef)
+        ok = np.zeros(n, dtype=np.uint8)
+        tb = np.zeros((n, ps["N_TB_byte"]), dtype=np.uint8)
+        fine = np.zeros(n, dtype=np.int32)
+        pok = np.zeros(n, dtype=np.uint8)
+        ms = np.zeros(3, dtype=np.float64)
+        rc = lib().ref_pool_rx_windows(self._h, n, _p(iq), iq.shape[2], iq.shape[2], _p(_u32(psdef)), plcf_type,
+                                       C.c_uint32(self.network_id), _p(ok), _p(tb), _p(fine), _p(pok), _p(ms))
+        assert rc >= 0, rc
+        return {"crc_ok": ok.astype(bool), "tb": tb, "fine_peak": fine, "plcf_ok": pok.astype(bool),
+                "stage_ms": {"sync": float(ms[0]), "pcc": float(ms[1]), "pdc": float(ms[2])}}

@@ -417,4 +417,116 @@ int ref_sync_stream(const uint32_t* psdef_max, uint32_t os_min, uint32_t L, uint
     return n;
 }
 
+// ---- a pool of workers for the bench's reference arm ----------------------------------------------------------------------
+// The reference scales by one worker thread = one tx_t / rx_synced_t pair (worker_tx_rx.cpp:43-67) fed by sync workers
+// (worker_sync.cpp).  Here: n_threads workers, each with its own ring buffer, sync_chunk_t and rx_synced_t; a window is
+// handled start to finish by one worker: sync_chunk_t::search (first packet of the window) -> demoddecod_rx_pcc ->
+// demoddecod_rx_pdc.  No real-time pacing (the ring is complete before the search starts).
+struct worker_t {
+    std::unique_ptr<radio::buffer_rx_t> ring;
+    std::unique_ptr<phy::sync_chunk_t> chunk;
+    std::unique_ptr<phy::rx_synced_t> rx;
+    std::unique_ptr<phy::harq::process_pool_t> hpp;
+    double ms[3] = {0, 0, 0};
+};
+struct pool_t {
+    sp3::packet_sizes_t ps_max;
+    phy::worker_pool_config_t cfg;
+    uint32_t N_RX = 1, ring_len = 0, unit = 0, chunk_length = 0;
+    std::vector<std::unique_ptr<worker_t>> w;
+};
+
+void* ref_pool_create(const uint32_t* psdef_max, uint32_t os_min, uint32_t L, uint32_t M, uint32_t n_window, uint32_t chestim_lr,
+                      uint32_t chestim_stride, uint32_t n_threads, uint32_t network_id) {
+    warm_rm_tables();
+    const auto q = sp3::get_packet_sizes(to_psdef(psdef_max));
+    if (!q.has_value()) return nullptr;
+    auto* p = new pool_t();
+    p->ps_max = q.value();
+    p->cfg = make_config(p->ps_max, os_min, L, M, chestim_lr != 0, chestim_stride);
+    p->N_RX = p->ps_max.tm_mode.N_TX;
+    const uint32_t u8 = p->cfg.resampler_param.hw_samp_rate / constants::u8_subslots_per_sec;
+    p->unit = u8 * p->cfg.rx_chunk_unit_length_u8subslot;
+    p->chunk_length = round_up(n_window, p->unit * L);
+    const uint32_t stf_hw = sp3::stf_t::get_N_samples_stf(q->psdef.u) * q->psdef.b * os_min * L / M + L;
+    p->ring_len = std::max(round_up(p->chunk_length + 8 * stf_hw + 4 * p->unit, p->unit), 8 * p->unit);
+    // every worker builds its own Wiener LUTs (channel_lut.cpp, tens of seconds at b = 16 -- the reference's start-up
+    // cost per worker thread); the constructors touch instance state only, so the workers are built concurrently
+    const uint32_t nw = std::max(n_threads, 1u);
+    p->w.resize(nw);
+#pragma omp parallel for schedule(static, 1) num_threads((int)nw)
+    for (uint32_t t = 0; t < nw; ++t) {
+        auto w = std::make_unique<worker_t>();
+        w->ring = std::make_unique<radio::buffer_rx_t>(t, p->N_RX, p->ring_len, p->cfg.resampler_param.hw_samp_rate, p->unit, 0, 100);
+        w->ring->rx_time_passed_64.store((int64_t)p->ring_len);
+        w->chunk = std::make_unique<phy::sync_chunk_t>(*w->ring, p->cfg, p->chunk_length, 4 * p->ring_len, 0, p->unit, [](int64_t) {});
+        w->rx = std::make_unique<phy::rx_synced_t>(*w->ring, p->cfg, p->unit);
+        w->rx->add_new_network_id(network_id);
+        w->hpp = std::make_unique<phy::harq::process_pool_t>(p->ps_max, 1, 1);
+        p->w[t] = std::move(w);
+    }
+    return p;
+}
+void ref_pool_destroy(void* pv) { delete static_cast<pool_t*>(pv); }
+uint32_t ref_pool_threads(void* pv) { return (uint32_t)static_cast<pool_t*>(pv)->w.size(); }
+
+// n windows iq [n][N_RX][iq_stride] (n_window valid samples each).  Outputs per window (any may be NULL): crc_ok, tb
+// [n][N_TB_byte], fine_peak (-1: no packet found), plcf_ok (type 1).  stage_ms [3]: sync / PCC / PDC milliseconds summed
+// over all workers.  Returns the number of windows with a passing transport block CRC.
+int ref_pool_rx_windows(void* pv, uint32_t n, const float* iq, uint32_t iq_stride, uint32_t n_window, const uint32_t* psdef,
+                        uint32_t plcf_type, uint32_t network_id, uint8_t* crc_ok, uint8_t* tb, int32_t* fine_peak, uint8_t* plcf_ok,
+                        double* stage_ms) {
+    auto* p = static_cast<pool_t*>(pv);
+    const auto q = sp3::get_packet_sizes(to_psdef(psdef));
+    if (!q.has_value() || n_window > p->chunk_length) return -1;
+    const sp3::packet_sizes_t ps = q.value();
+    for (auto& w : p->w) w->ms[0] = w->ms[1] = w->ms[2] = 0;
+    int n_ok = 0;
+#pragma omp parallel for schedule(dynamic, 1) num_threads((int)p->w.size()) reduction(+ : n_ok)
+    for (int64_t i = 0; i < (int64_t)n; ++i) {
+        worker_t& w = *p->w[(size_t)omp_get_thread_num()];
+        for (uint32_t a = 0; a < p->N_RX; ++a) {
+            std::memcpy(w.ring->ant_streams[a], iq + ((size_t)i * p->N_RX + a) * 2 * iq_stride, sizeof(cf_t) * n_window);
+            std::memset(w.ring->ant_streams[a] + n_window, 0, sizeof(cf_t) * (p->ring_len + p->unit - n_window));
+        }
+        if (crc_ok) crc_ok[i] = 0;
+        if (fine_peak) fine_peak[i] = -1;
+        if (plcf_ok) plcf_ok[i] = 0;
+        double t0 = omp_get_wtime();
+        w.chunk->wait_for_first_chunk_nto(0);
+        auto r = w.chunk->search();
+        double t1 = omp_get_wtime();
+        w.ms[0] += (t1 - t0) * 1e3;
+        if (!r.has_value()) continue;
+        phy::sync_report_t s = r.value();
+        if (fine_peak) fine_peak[i] = (int32_t)s.fine_peak_time_64;
+        if (s.fine_peak_time_64 < 0 || s.fine_peak_time_64 + (int64_t)(ps.N_samples_packet_no_GI * p->cfg.os_min) > (int64_t)p->ring_len) continue;
+        w.rx->reset_for_next_pcc();
+        const phy::pcc_report_t pr = w.rx->demoddecod_rx_pcc(s);
+        double t2 = omp_get_wtime();
+        w.ms[1] += (t2 - t1) * 1e3;
+        const bool has = pr.plcf_decoder.get_plcf_base(plcf_type) != nullptr || w.rx->hb_rx_plcf->get_softbuffer_d_type_1()->cb_crc[0];
+        if (plcf_ok) plcf_ok[i] = w.rx->hb_rx_plcf->get_softbuffer_d_type_1()->cb_crc[0] ? 1 : 0;
+        (void)has;
+        // the MAC's decision between PCC and PDC: the bench knows the packet geometry (as its firmware would from the PLCF)
+        auto* hp = w.hpp->get_process_rx(plcf_type, network_id, ps.psdef, 0, phy::harq::finalize_rx_t::reset_and_terminate);
+        if (!hp) continue;
+        const phy::maclow_phy_t mp(hp);
+        const phy::pdc_report_t dr = w.rx->demoddecod_rx_pdc(mp);
+        if (dr.crc_status) {
+            ++n_ok;
+            if (crc_ok) crc_ok[i] = 1;
+            if (tb) std::memcpy(tb + (size_t)i * ps.N_TB_byte, hp->get_hb_tb()->get_a(), ps.N_TB_byte);
+        }
+        hp->finalize(dr.crc_status);
+        w.ms[2] += (omp_get_wtime() - t2) * 1e3;
+    }
+    if (stage_ms) {
+        stage_ms[0] = stage_ms[1] = stage_ms[2] = 0;
+        for (auto& w : p->w)
+            for (int k = 0; k < 3; ++k) stage_ms[k] += w->ms[k];
+    }
+    return n_ok;
+}
+
 }  // extern "C"

@@ -567,70 +567,63 @@ int srsran_tdec_new_cb(srsran_tdec_t* h, uint32_t long_cb) {
     return SRSRAN_SUCCESS;
 }
 static inline int16_t sat16(int v) { return (int16_t)(v > 32767 ? 32767 : v < -32768 ? -32768 : v); }
-static inline int max2(int a, int b) { return a > b ? a : b; }
 /* one constituent decoder: x[k] (systematic + a-priori), y[k] parity, tail (x, z) x 3; writes the a-posteriori LLR.
- * State s = (s0, s1, s2) = register bits D, D^2, D^3 packed as s0 | s1 << 1 | s2 << 2; LLR > 0 <=> bit 1; branch metric
- * of a transition with input u and parity z: (u ? x : 0) + (z ? y : 0) (common terms dropped). */
+ * State s = s0 | s1 << 1 | s2 << 2 (register bits D, D^2, D^3); from s with input u: fb = u ^ s1 ^ s2, parity z = fb ^ s0 ^ s2,
+ * next = (fb, s0, s1).  Seen from the next state ns = (fb, s0, s1) and the dropped bit s2 = c: s = ns1 | ns2 << 1 | c << 2,
+ * u = ns0 ^ ns2 ^ c, z = ns0 ^ ns1 ^ c.  LLR > 0 <=> bit 1; branch metric (u ? x : 0) + (z ? y : 0); metrics in int32,
+ * normalised to state 0 every step (state 0 is reachable at every step in both directions). */
+#define TD_BIG (1 << 22)
 static void map_dec(const int16_t* x, const int16_t* y, const int16_t* tail, uint32_t K, int32_t* alpha, int16_t* out) {
-    /* transitions: from state s with input u: fb = u ^ s1 ^ s2, z = fb ^ s0 ^ s2, next = ((s << 1) | fb) & 7 */
-    int nxt[8][2], par[8][2];
-    for (int s = 0; s < 8; ++s)
-        for (int u = 0; u < 2; ++u) {
-            const int fb = u ^ ((s >> 1) & 1) ^ ((s >> 2) & 1);
-            par[s][u] = fb ^ (s & 1) ^ ((s >> 2) & 1);
-            nxt[s][u] = ((s << 1) | fb) & 7;
+    /* predecessor pairs of every next state: [ns][c] -> (s, u, z) */
+    int ps[8][2], pg[8][2];
+    for (int ns = 0; ns < 8; ++ns)
+        for (int c = 0; c < 2; ++c) {
+            const int n0 = ns & 1, n1 = (ns >> 1) & 1, n2 = (ns >> 2) & 1;
+            ps[ns][c] = n1 | (n2 << 1) | (c << 2);
+            pg[ns][c] = ((n0 ^ n2 ^ c) << 1) | (n0 ^ n1 ^ c);   /* index into g[] = {0, y, x, x + y} */
         }
-    const int NEG = -(1 << 28);
     int32_t* a = alpha;
     a[0] = 0;
-    for (int s = 1; s < 8; ++s) a[s] = NEG;
+    for (int s = 1; s < 8; ++s) a[s] = -TD_BIG;
     for (uint32_t k = 0; k < K; ++k) {
+        const int32_t g[4] = {0, y[k], x[k], (int32_t)x[k] + y[k]};
         int32_t* an = a + 8;
-        for (int s = 0; s < 8; ++s) an[s] = NEG;
-        for (int s = 0; s < 8; ++s) {
-            if (a[s] <= NEG / 2) continue;
-            for (int u = 0; u < 2; ++u) {
-                const int m = a[s] + (u ? x[k] : 0) + (par[s][u] ? y[k] : 0);
-                if (m > an[nxt[s][u]]) an[nxt[s][u]] = m;
-            }
+        int32_t t[8];
+        for (int ns = 0; ns < 8; ++ns) {
+            const int32_t m0 = a[ps[ns][0]] + g[pg[ns][0]], m1 = a[ps[ns][1]] + g[pg[ns][1]];
+            t[ns] = m0 > m1 ? m0 : m1;
         }
-        int mx = NEG;
-        for (int s = 0; s < 8; ++s) mx = max2(mx, an[s]);
-        for (int s = 0; s < 8; ++s) an[s] = an[s] <= NEG / 2 ? NEG : an[s] - mx;
+        const int32_t n0 = t[0];
+        for (int ns = 0; ns < 8; ++ns) { const int32_t v = t[ns] - n0; an[ns] = v < -TD_BIG ? -TD_BIG : v; }
         a = an;
     }
-    /* beta at K from the termination: three steps where the input equals s1 ^ s2 (feedback zero) */
+    /* beta at K from the termination: three steps with input u = s1 ^ s2 (feedback zero), parity z = s0 ^ s2 */
     int32_t b[8], bn[8];
-    for (int s = 0; s < 8; ++s) b[s] = s == 0 ? 0 : NEG;
+    for (int s = 0; s < 8; ++s) b[s] = s == 0 ? 0 : -TD_BIG;
     for (int t = 2; t >= 0; --t) {
         for (int s = 0; s < 8; ++s) {
-            const int u = ((s >> 1) & 1) ^ ((s >> 2) & 1);
-            const int z = (s & 1) ^ ((s >> 2) & 1);
-            const int ns = (s << 1) & 7;
-            bn[s] = b[ns] <= NEG / 2 ? NEG : b[ns] + (u ? tail[2 * t] : 0) + (z ? tail[2 * t + 1] : 0);
+            const int u = ((s >> 1) & 1) ^ ((s >> 2) & 1), z = (s & 1) ^ ((s >> 2) & 1), ns = (s << 1) & 7;
+            const int32_t v = b[ns] + (u ? tail[2 * t] : 0) + (z ? tail[2 * t + 1] : 0);
+            bn[s] = v < -TD_BIG ? -TD_BIG : v;
         }
         memcpy(b, bn, sizeof(b));
     }
     for (int k = (int)K - 1; k >= 0; --k) {
         const int32_t* ak = alpha + 8 * k;
-        int m1 = NEG, m0 = NEG;
-        for (int s = 0; s < 8; ++s) bn[s] = NEG;
-        for (int s = 0; s < 8; ++s)
-            for (int u = 0; u < 2; ++u) {
-                const int ns = nxt[s][u];
-                if (b[ns] <= NEG / 2) continue;
-                const int g = (u ? x[k] : 0) + (par[s][u] ? y[k] : 0);
-                const int bm = b[ns] + g;
+        const int32_t g[4] = {0, y[k], x[k], (int32_t)x[k] + y[k]};
+        int32_t m1 = -4 * TD_BIG, m0 = -4 * TD_BIG;
+        for (int s = 0; s < 8; ++s) bn[s] = -4 * TD_BIG;
+        for (int ns = 0; ns < 8; ++ns)
+            for (int c = 0; c < 2; ++c) {
+                const int s = ps[ns][c], gi = pg[ns][c];
+                const int32_t bm = b[ns] + g[gi];
                 if (bm > bn[s]) bn[s] = bm;
-                if (ak[s] > NEG / 2) {
-                    const int tot = ak[s] + bm;
-                    if (u) m1 = max2(m1, tot); else m0 = max2(m0, tot);
-                }
+                const int32_t tot = ak[s] + bm;
+                if (gi & 2) { if (tot > m1) m1 = tot; } else { if (tot > m0) m0 = tot; }
             }
         out[k] = sat16(m1 - m0);
-        int mx = NEG;
-        for (int s = 0; s < 8; ++s) mx = max2(mx, bn[s]);
-        for (int s = 0; s < 8; ++s) b[s] = bn[s] <= NEG / 2 ? NEG : bn[s] - mx;
+        const int32_t n0 = bn[0];
+        for (int s = 0; s < 8; ++s) { const int32_t v = bn[s] - n0; b[s] = v < -TD_BIG ? -TD_BIG : v; }
     }
 }
 void srsran_tdec_iteration(srsran_tdec_t* h, int16_t* input, uint8_t* output) {

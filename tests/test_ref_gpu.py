@@ -116,7 +116,7 @@ def test_rx_vs_reference(product, name):
     llr_pdc = phy.tap(product.TAP_LLR_PDC, n)
     gold = np.asarray(spec.gold_sequence(NET & 0xFF, ps["G"]))[:ps["G"]].astype(np.int32)
     r = ref.Rx(cfg, stride)
-    n_crc_differs = n_ok = 0
+    n_crc_differs = n_ok = n_wrong_type_differs = 0
     for i in range(n):
         p = r.pcc(win[i], t0, cfg[0], cfg[1], ps["N_eff_TX"], cfo_fractional_rad=-cfo, rms=rms[i])
         d = r.pdc(cfg, network_id=NET, plcf_type=1)
@@ -129,9 +129,14 @@ def test_rx_vs_reference(product, name):
         assert odd.size <= ps["N_bps"] and np.abs(np.abs(mine[odd]) - np.abs(theirs[odd])).max(initial=0) <= 2, (name, i, odd)
         dd[odd] = 0
         assert dd.max() <= 2 and (dd > 0).mean() < 0.02, (name, i, "pdc", dd.max(), (dd > 0).mean())
-        assert abs(pcc[i].snr_dB - p["snr_dB"]) < 0.05 and abs(snr[i] - d["snr_dB"]) < 0.05, (name, i)
+        assert abs(pcc[i].snr_dB - p["snr_dB"]) < 0.05, (name, i)
+        if d["crc_ok"]:   # the reference reports the PDC SNR only with a passing CRC (pdc_report.hpp:30-35)
+            assert abs(snr[i] - d["snr_dB"]) < 0.05, (name, i)
         assert abs(pcc[i].sto_fractional - p["sto_fractional"]) < 2e-3
-        assert bool(pcc[i].plcf_ok[0]) == bool(p["plcf_ok"][0]) and bool(pcc[i].plcf_ok[1]) == bool(p["plcf_ok"][1]), (name, i)
+        # the transmitted type must agree; the blind test of the OTHER type decodes noise, where a chance CRC match
+        # (4 masks x <= 5 iterations of a 16-bit CRC) depends on the decoder's arithmetic: counted, not required equal
+        assert bool(pcc[i].plcf_ok[0]) == bool(p["plcf_ok"][0]), (name, i)
+        n_wrong_type_differs += bool(pcc[i].plcf_ok[1]) != bool(p["plcf_ok"][1])
         if p["plcf_ok"][0]:
             assert bytes(pcc[i].plcf[0])[:5] == bytes(p["plcf"][0, :5])
         if bool(ok[i]) != d["crc_ok"]:
@@ -140,7 +145,7 @@ def test_rx_vs_reference(product, name):
         elif ok[i]:
             n_ok += 1
             assert np.array_equal(tb_out[i], d["tb"]) and np.array_equal(tb_out[i], tbs[i])
-    assert n_ok >= per and n_crc_differs <= 2, (name, n_ok, n_crc_differs)
+    assert n_ok >= per and n_crc_differs <= 2 and n_wrong_type_differs <= 1, (name, n_ok, n_crc_differs, n_wrong_type_differs)
     r.close()
     phy.close()
 
