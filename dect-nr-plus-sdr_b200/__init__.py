@@ -250,6 +250,48 @@ class Phy:
                                    _ptr(iq, np.complex64), _ptr(ns, np.uint32)))
         return iq, ns
 
+    # ---- several networks / PLCF types per batch (worker_pool_t::add_network_id, per-packet HARQ process fields)
+    def add_network_id(self, network_id):
+        _check(lib().dnrp_add_network_id(self._ctx, C.c_uint32(network_id)))
+
+    def harq_reset(self, slot):
+        _check(lib().dnrp_harq_reset(self._ctx, C.c_uint32(slot)))
+
+    def tx_ex(self, plcf, tb, network_id=None, plcf_type=None, codebook_index=0, rv=0, GI_percentage=5, fetch=True):
+        """dnrp_tx_batch_ex: network_id [n] / plcf_type [n] per packet (None = the context's)"""
+        n = tb.shape[0]
+        plcf = np.ascontiguousarray(plcf, dtype=np.uint8).reshape(n, 10)
+        tb = np.ascontiguousarray(tb, dtype=np.uint8).reshape(n, self.ps["N_TB_byte"])
+        descs = (TxDesc * n)()
+        rvv, cb = np.broadcast_to(np.asarray(rv), (n,)), np.broadcast_to(np.asarray(codebook_index), (n,))
+        for i in range(n):
+            descs[i] = TxDesc(int(cb[i]), 0, 1.0, 0.0, 0.0, int(GI_percentage), int(rvv[i]))
+        ids = None if network_id is None else np.ascontiguousarray(network_id, dtype=np.uint32)
+        tys = None if plcf_type is None else np.ascontiguousarray(plcf_type, dtype=np.uint8)
+        lib().dnrp_tx_stride.restype = C.c_uint32
+        stride = lib().dnrp_tx_stride(self._ctx)
+        iq = np.zeros((n, self.ps["N_TX"], stride), dtype=np.complex64) if fetch else None
+        ns = np.zeros(n, dtype=np.uint32)
+        _check(lib().dnrp_tx_batch_ex(self._ctx, n, descs, _ptr(ids, np.uint32), _ptr(tys, np.uint8), _ptr(plcf, np.uint8),
+                                      _ptr(tb, np.uint8), _ptr(iq, np.complex64), _ptr(ns, np.uint32)))
+        return iq, ns
+
+    def rx_pdc_ex(self, n, network_id=None, plcf_type=None, harq_slot=None, rv=None, harq_reset=None):
+        """dnrp_rx_pdc_batch_ex: network_id [n] / plcf_type [n] per packet (None = the context's)"""
+        tb = np.zeros((n, self.ps["N_TB_byte"]), dtype=np.uint8)
+        nit = np.zeros((n, self.ps["C"]), dtype=np.uint8)
+        slot = None if harq_slot is None else np.ascontiguousarray(harq_slot, dtype=np.uint32)
+        rvv = None if rv is None else np.ascontiguousarray(rv, dtype=np.uint8)
+        rst = None if harq_reset is None else np.ascontiguousarray(harq_reset, dtype=np.uint8)
+        ids = None if network_id is None else np.ascontiguousarray(network_id, dtype=np.uint32)
+        tys = None if plcf_type is None else np.ascontiguousarray(plcf_type, dtype=np.uint8)
+        out = np.zeros(n, dtype=PDC_DTYPE)
+        _check(lib().dnrp_rx_pdc_batch_ex(self._ctx, n, _ptr(slot, np.uint32), _ptr(rvv, np.uint8), _ptr(rst, np.uint8),
+                                          _ptr(ids, np.uint32), _ptr(tys, np.uint8), _ptr(tb, np.uint8),
+                                          out.ctypes.data_as(C.c_void_p), _ptr(nit, np.uint8)))
+        self.last_pdc_report = out.view(np.recarray)
+        return out["crc_ok"].astype(bool), tb, out["snr_dB"].copy(), nit
+
     # ---- rx_synced_t::demoddecod_rx_pcc / demoddecod_rx_pdc (reference rx_synced.cpp:186-436)
     def rx_stride(self):
         lib().dnrp_rx_stride.restype = C.c_uint32

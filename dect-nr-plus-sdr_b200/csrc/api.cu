@@ -72,6 +72,8 @@ uint32_t dnrp_resampler_n_after(uint32_t L, uint32_t M, uint32_t oversampling, u
 int dnrp_ctx_create(const dnrp_config_t* cfg, int device, dnrp_ctx_t** out) {
     DNRP_REQUIRE(cfg && out, "null argument");
     DNRP_REQUIRE(cfg->max_batch > 0, "max_batch must be > 0");
+    DNRP_REQUIRE(cfg->max_batch <= 65535, "max_batch must be <= 65535 (packets ride in a CUDA grid dimension); process larger "
+                                          "workloads as successive batches");
     DNRP_REQUIRE(cfg->plcf_type == 1 || cfg->plcf_type == 2, "plcf_type must be 1 or 2");
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || device < 0 || device >= ndev) {
@@ -116,7 +118,14 @@ int dnrp_ctx_create(const dnrp_config_t* cfg, int device, dnrp_ctx_t** out) {
     UP(c->d_tx_cbs.upload(f.tx_cbs));
     UP(c->d_rx_pcc.upload(std::vector<cb_desc_t>(f.rx_pcc, f.rx_pcc + 2)));
     UP(c->d_tx_pcc.upload(std::vector<txcb_desc_t>(f.tx_pcc, f.tx_pcc + 2)));
-    UP(c->d_gold_pdc.upload(spec::gold_sequence_packed(c_init, c->ps.G + 64)));
+    c->gold_cinit.assign(1, c_init);   // entry 0: the context's default; entry 1: the other PLCF type of the same id
+    {
+        const uint32_t other = cfg->plcf_type == 1 ? (cfg->network_id >> 8) : (cfg->network_id & 0xff);
+        if (other != c_init) c->gold_cinit.push_back(other);
+    }
+    ok = ok && upload_gold_table(c) == DNRP_OK;
+    UP(c->d_gold_sel.alloc(B));
+    UP(c->d_pcc_sel.alloc(B));
     UP(c->d_gold_pcc.upload(spec::gold_sequence_packed(spec::PCC_SCRAMBLING_INIT, 256)));
     UP(c->d_tb_in.alloc(B * f.tb_stride));
     UP(c->d_plcf_in.alloc(B * 16));
@@ -177,6 +186,26 @@ int dnrp_ctx_synchronize(dnrp_ctx_t* ctx) {
 // ---- device-side FEC stages on the context's own buffers (used by the full chain as well)
 namespace dnrp {
 
+int upload_gold_table(dnrp_ctx* c) {
+    const uint32_t bits = c->ps.G + 64;
+    c->gold_stride = ((bits + 7) / 8 + 15u) & ~15u;
+    std::vector<uint8_t> t((size_t)c->gold_stride * c->gold_cinit.size(), 0);
+    for (size_t i = 0; i < c->gold_cinit.size(); ++i) {
+        const std::vector<uint8_t> g = spec::gold_sequence_packed(c->gold_cinit[i], bits);
+        std::memcpy(t.data() + i * c->gold_stride, g.data(), std::min<size_t>(g.size(), c->gold_stride));
+    }
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));   // nothing in flight may still read the old table
+    DNRP_CUDA(c->d_gold_pdc.upload(t));
+    return DNRP_OK;
+}
+
+int gold_index(dnrp_ctx* c, uint32_t network_id, uint32_t plcf_type) {
+    const uint32_t c_init = plcf_type == 1 ? (network_id & 0xff) : (network_id >> 8);
+    for (size_t i = 0; i < c->gold_cinit.size(); ++i)
+        if (c->gold_cinit[i] == c_init) return (int)i;
+    return -1;
+}
+
 int run_fec_encode(dnrp_ctx* c, uint32_t n, bool have_mask, bool have_rv) {
     const fec_plan_t& f = c->fec;
     DNRP_CUDA(cudaMemsetAsync(c->d_pdc_bits.p, 0, (size_t)n * f.dbits_stride, c->stream));
@@ -187,12 +216,14 @@ int run_fec_encode(dnrp_ctx* c, uint32_t n, bool have_mask, bool have_rv) {
     p.rv = have_rv ? c->d_rv.p : nullptr;
     p.plcf_mask = nullptr;
     p.gold = c->d_gold_pdc.p; p.gold_bit_off = 0;
+    p.gold_sel = c->use_gold_sel ? c->d_gold_sel.p : nullptr; p.gold_stride = c->gold_stride;
     p.out = c->d_pdc_bits.p; p.out_stride = f.dbits_stride;
     p.rm_arena = c->d_rm_arena.p; p.xp_arena = c->d_xp_arena.p;
     DNRP_LAUNCH(c, -1, launch_tx_fec(p, n, f.Kmax, c->stream));
-    // PLCF: one launch, the descriptor (type 1 or 2) is the plan's plcf_type
+    // PLCF: one launch, the descriptor (type 1 or 2) is the plan's plcf_type or, in dnrp_tx_batch_ex, the packet's
     txfec_params_t q{};
-    q.cbs = c->d_tx_pcc.p + (c->cfg.plcf_type - 1); q.C = 1;
+    q.cbs = c->d_tx_pcc.p + (c->use_pcc_sel ? 0 : (c->cfg.plcf_type - 1)); q.C = 1;
+    q.cb_sel = c->use_pcc_sel ? c->d_pcc_sel.p : nullptr;
     q.in = c->d_plcf_in.p; q.in_stride = 16;
     q.rv = nullptr;
     q.plcf_mask = have_mask ? c->d_plcf_mask.p : nullptr;
@@ -212,6 +243,7 @@ int run_fec_decode_tb(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, boo
     const size_t off = c->off, soff = have_slot ? 0 : off;
     p.llr = c->d_llr.p + off * c->ps.G; p.llr_stride = c->ps.G;
     p.gold = c->d_gold_pdc.p; p.gold_bit_off = 0;
+    p.gold_sel = c->use_gold_sel ? c->d_gold_sel.p + off : nullptr; p.gold_stride = c->gold_stride;
     p.soft = c->d_soft.p + soff * f.soft_stride; p.soft_stride = f.soft_stride;
     p.cb_crc = c->d_cb_crc.p + soff * c->ps.C;
     p.saved = c->d_saved.p + soff * f.saved_stride; p.saved_stride = f.saved_stride;

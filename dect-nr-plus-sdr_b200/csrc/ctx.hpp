@@ -105,6 +105,13 @@ struct dnrp_ctx {
     dnrp::dbuf<dnrp::cb_desc_t> d_rx_cbs, d_rx_pcc;
     dnrp::dbuf<dnrp::txcb_desc_t> d_tx_cbs, d_tx_pcc;
     dnrp::dbuf<uint8_t> d_gold_pdc, d_gold_pcc;
+    // PDC scrambling sequences: entry 0 = the context's default (cfg.network_id, cfg.plcf_type), further entries added by
+    // dnrp_add_network_id (both PLCF types of the id: c_init = id & 0xff and id >> 8, scrambling_pdc.cpp:43-56)
+    std::vector<uint32_t> gold_cinit;
+    uint32_t gold_stride = 0;                      // bytes per sequence in d_gold_pdc
+    dnrp::dbuf<uint32_t> d_gold_sel;               // [B] per-packet sequence index of the *_ex calls
+    dnrp::dbuf<uint8_t> d_pcc_sel;                 // [B] per-packet PLCF type - 1 of dnrp_tx_batch_ex
+    bool use_gold_sel = false, use_pcc_sel = false;   // set for the duration of a *_ex call
     // device workspaces, [B] leading dimension
     dnrp::dbuf<uint8_t> d_tb_in, d_plcf_in, d_rv, d_reset, d_pdc_bits, d_pcc_bits;
     dnrp::dbuf<uint32_t> d_plcf_mask, d_slot;
@@ -213,6 +220,8 @@ struct kscope {
 
 namespace dnrp {
 int build_phy_plan(dnrp_ctx* c);
+int upload_gold_table(dnrp_ctx* c);
+int gold_index(dnrp_ctx* c, uint32_t network_id, uint32_t plcf_type);   // -1: not registered
 int run_fec_encode(dnrp_ctx* c, uint32_t n, bool have_mask, bool have_rv);
 int run_fec_decode_tb(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, bool have_reset);
 int run_fec_decode_plcf(dnrp_ctx* c, uint32_t n);

@@ -4,6 +4,7 @@
 // lib/src/phy/fec/pcc_enc.cpp:215-364 (file:line relative to /root/reference).
 #include <type_traits>
 #include "fec_rx.cuh"
+#include "launch_util.hpp"
 #include "turbo_dec.cuh"
 
 namespace dnrp {
@@ -39,6 +40,7 @@ __global__ void __launch_bounds__(256) k_derm(const tdec_params_t p, uint32_t ca
     const uint32_t N = 3 * (cb.K + 4);
     const bool reset = p.reset ? p.reset[pkt] != 0 : true;
     const uint32_t rv = p.rv ? p.rv[pkt] : 0;
+    const uint8_t* gold = p.gold + (p.gold_sel ? (size_t)p.gold_sel[pkt] * p.gold_stride : 0);
     // code block already decoded in an earlier transmission: nothing to combine (pdc_enc.cpp:404-406)
     if (!reset && p.cb_crc[(size_t)slot * p.C + blockIdx.x]) return;
 
@@ -52,7 +54,7 @@ __global__ void __launch_bounds__(256) k_derm(const tdec_params_t p, uint32_t ca
     const bool single = staged && cb.n_e <= N && N <= cap;
     auto descr = [&](uint32_t e, int v) -> int {   // srsran_scrambling_s_offset: sign flip where the Gold bit is 1
         const uint32_t g = cb.rp + e + p.gold_bit_off;
-        return ((p.gold[g >> 3] >> (7 - (g & 7))) & 1) ? -v : v;
+        return ((gold[g >> 3] >> (7 - (g & 7))) & 1) ? -v : v;
     };
     if (single && (reinterpret_cast<uintptr_t>(llr) & 3) == 0) {
         // ---- usual case (code rate >= 1/3, LLR pairs aligned): build the soft-buffer image in shared memory by
@@ -68,7 +70,7 @@ __global__ void __launch_bounds__(256) k_derm(const tdec_params_t p, uint32_t ca
         for (uint32_t e2 = tid; e2 < cb.n_e / 2; e2 += nthr) {
             const uint32_t w = llr2[e2];
             const uint32_t g = g0 + 2 * e2;
-            const uint32_t gw = ((uint32_t)p.gold[g >> 3] << 8) | p.gold[(g >> 3) + 1];
+            const uint32_t gw = ((uint32_t)gold[g >> 3] << 8) | gold[(g >> 3) + 1];
             const uint32_t b0 = (gw >> (15 - (g & 7))) & 1u, b1 = (gw >> (14 - (g & 7))) & 1u;
             const uint32_t m = (b0 ? 0xffffu : 0u) | (b1 ? 0xffff0000u : 0u);
             const uint32_t v = __vsub2(w ^ m, m);
@@ -100,7 +102,7 @@ __global__ void __launch_bounds__(256) k_derm(const tdec_params_t p, uint32_t ca
             for (uint32_t e2 = tid; e2 < cb.n_e / 2; e2 += nthr) {
                 const uint32_t w = llr2[e2];
                 const uint32_t g = g0 + 2 * e2;
-                const uint32_t gw = ((uint32_t)p.gold[g >> 3] << 8) | p.gold[(g >> 3) + 1];
+                const uint32_t gw = ((uint32_t)gold[g >> 3] << 8) | gold[(g >> 3) + 1];
                 const uint32_t b0 = (gw >> (15 - (g & 7))) & 1u, b1 = (gw >> (14 - (g & 7))) & 1u;
                 // sign flip of each half where its bit is set: (v ^ m) - m with m = 0xffff per flipped half
                 const uint32_t m = (b0 ? 0xffffu : 0u) | (b1 ? 0xffff0000u : 0u);
@@ -647,14 +649,14 @@ cudaError_t launch_turbo_decode(const tdec_params_t& p, uint32_t n_packets, cons
     while (threads > 32 && threads > g.tg && n_items / (threads / g.tg) < 2 * 148) threads /= 2;
     const uint32_t per_block = threads / g.tg;
     const size_t smem = per_block * g.smem_item;
-    static size_t configured = 0;
-    if (smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_turbo_decode<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    static smem_optin_t optin;   // per device (a second context may live on another GPU of this process)
+    cudaError_t e0 = optin.ensure(smem, [](size_t b) {
+        cudaError_t e = cudaFuncSetAttribute(k_turbo_decode<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
         if (e == cudaSuccess)
-            e = cudaFuncSetAttribute(k_turbo_decode<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-        if (e != cudaSuccess) return e;
-        configured = smem;
-    }
+            e = cudaFuncSetAttribute(k_turbo_decode<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
+        return e;
+    });
+    if (e0 != cudaSuccess) return e0;
     const dim3 grid((n_items + per_block - 1) / per_block);
     if (per_block == 1)
         k_turbo_decode<false><<<grid, threads, smem, st>>>(p, g.tg, (uint32_t)(g.smem_item / 4), n_items);

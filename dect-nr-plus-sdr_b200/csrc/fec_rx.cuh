@@ -12,8 +12,10 @@ struct tdec_params_t {
     uint32_t C;
     const int16_t* llr;        // [packet][llr_stride] demapper output (still scrambled)
     size_t llr_stride;
-    const uint8_t* gold;       // packed scrambling sequence (MSB first)
+    const uint8_t* gold;       // table of packed scrambling sequences (MSB first), gold_stride bytes each
     uint32_t gold_bit_off;
+    const uint32_t* gold_sel;  // [packet] sequence of the table (network id / PLCF type of the packet; null: sequence 0)
+    uint32_t gold_stride;
     int16_t* soft;             // [slot][soft_stride] HARQ soft buffers, d-stream layout [3][K+4] per CB
     size_t soft_stride;
     uint8_t* cb_crc;           // [slot][C]

@@ -168,8 +168,9 @@ __device__ void block_rsc(MR make_reader, uint32_t K, uint8_t* par, uint8_t* xt,
 
 __global__ void __launch_bounds__(256) k_tx_fec(const txfec_params_t p) {
     extern __shared__ uint8_t sm8[];
-    const txcb_desc_t cb = p.cbs[blockIdx.x];
     const uint32_t pkt = blockIdx.y, tid = threadIdx.x, nthr = blockDim.x;
+    const txcb_desc_t cb = p.cbs[blockIdx.x + (p.cb_sel ? p.cb_sel[pkt] : 0u)];
+    const uint8_t* gold = p.gold + (p.gold_sel ? (size_t)p.gold_sel[pkt] * p.gold_stride : 0);
     const uint32_t K = cb.K, D = K + 4, N = 3 * D;
     uint8_t* c = sm8;            // [K] input bits of the code block
     uint8_t* d = c + K;          // [3][K+4]
@@ -259,7 +260,7 @@ __global__ void __launch_bounds__(256) k_tx_fec(const txfec_params_t p) {
                     bit = d[src[pos]];
                 }
                 const uint32_t gg = g + p.gold_bit_off;
-                bit ^= (p.gold[gg >> 3] >> (7 - (gg & 7))) & 1u;
+                bit ^= (gold[gg >> 3] >> (7 - (gg & 7))) & 1u;
             }
             v = (v << 1) | bit;
         }

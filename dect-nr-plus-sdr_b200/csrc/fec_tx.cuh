@@ -27,8 +27,11 @@ struct txfec_params_t {
     size_t in_stride;
     const uint8_t* rv;         // [packet] or null
     const uint32_t* plcf_mask; // [packet] CRC mask (PLCF only) or null
-    const uint8_t* gold;
+    const uint8_t* gold;       // table of packed scrambling sequences, gold_stride bytes each
     uint32_t gold_bit_off;
+    const uint32_t* gold_sel;  // [packet] sequence of the table this packet is scrambled with (null: sequence 0)
+    uint32_t gold_stride;
+    const uint8_t* cb_sel;     // [packet] offset added to the code block index (PLCF: 0 = type 1, 1 = type 2; null: 0)
     uint8_t* out;              // [packet][out_stride] packed coded bits, zero-initialised, stride % 4 == 0
     size_t out_stride;
     const uint16_t* rm_arena;

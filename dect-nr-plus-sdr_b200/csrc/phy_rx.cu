@@ -2,6 +2,7 @@
 // rx_synced.cpp): STF stage (CFO derotation, cover sequence, residual CFO, FFT, zero-forcing at the STF
 // cells, fractional STO, SNR), data field FFTs with DRS zero-forcing, Wiener class selection, and the
 // fused channel interpolation + MRC/Alamouti combining + soft demapping kernel.
+#include "launch_util.hpp"
 #include "fft.cuh"
 #include "phy.cuh"
 
@@ -539,11 +540,12 @@ cudaError_t launch_rx_snr_class(const rx_params_t& p, uint32_t n_packets, cudaSt
 
 cudaError_t launch_rx_fft(const rx_params_t& p, uint32_t n_packets, cudaStream_t st) {
     const size_t smem = sizeof(float2) * 2 * fft_buf_len(p.d.N_os);
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_rx_fft, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 48 * 1024) {
+        static smem_optin_t optin;   // per device
+        cudaError_t e = optin.ensure(smem, [](size_t b) {
+            return cudaFuncSetAttribute(k_rx_fft, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
+        });
         if (e != cudaSuccess) return e;
-        configured = smem;
     }
     k_rx_fft<<<dim3(p.d.N_DF, p.d.N_RX, n_packets), 256, smem, st>>>(p);
     return cudaGetLastError();
@@ -551,11 +553,12 @@ cudaError_t launch_rx_fft(const rx_params_t& p, uint32_t n_packets, cudaStream_t
 
 cudaError_t launch_rx_stf(const rx_params_t& p, uint32_t n_packets, cudaStream_t st) {
     const size_t smem = sizeof(float2) * ((size_t)p.d.stf_len_os + 2 * fft_buf_len(p.d.N_os) + (size_t)p.d.N_RX * (p.d.N_OCC / 4));
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_rx_stf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 48 * 1024) {
+        static smem_optin_t optin;   // per device
+        cudaError_t e = optin.ensure(smem, [](size_t b) {
+            return cudaFuncSetAttribute(k_rx_stf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
+        });
         if (e != cudaSuccess) return e;
-        configured = smem;
     }
     k_rx_stf<<<n_packets, 256, smem, st>>>(p);
     return cudaGetLastError();

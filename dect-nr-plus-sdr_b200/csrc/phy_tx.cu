@@ -4,6 +4,7 @@
 // pass through shared memory.  Replaces the per-symbol loop of reference
 // lib/src/phy/tx/tx.cpp:216-279 (run_stf, run_pcc, run_drs, run_pdc, run_beamforming,
 // run_ifft_cp_scale, stf_t::apply_cover_sequence, mixer) for L = M = 1.
+#include "launch_util.hpp"
 #include "fft.cuh"
 #include "phy.cuh"
 
@@ -150,11 +151,12 @@ __global__ void __launch_bounds__(256) k_tx_ofdm(const txofdm_params_t p) {
 
 cudaError_t launch_tx_ofdm(const txofdm_params_t& p, uint32_t n_packets, cudaStream_t st) {
     const size_t smem = 2 * sizeof(float2) * fft_buf_len(p.d.N_os);
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-        cudaError_t e = cudaFuncSetAttribute(k_tx_ofdm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 48 * 1024) {
+        static smem_optin_t optin;   // per device
+        cudaError_t e = optin.ensure(smem, [](size_t b) {
+            return cudaFuncSetAttribute(k_tx_ofdm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
+        });
         if (e != cudaSuccess) return e;
-        configured = smem;
     }
     k_tx_ofdm<<<dim3(p.d.N_DF + 1, p.d.N_TX, n_packets), 256, smem, st>>>(p);
     return cudaGetLastError();

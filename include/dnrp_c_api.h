@@ -8,7 +8,9 @@
  * (file:line relative to /root/reference); INTEGRATION.md shows the binding a maintainer would add.
  *
  * Batching model: one context = one device + one packet geometry ("plan": psdef, antennas, resampling)
- * + a maximum batch size.  A call processes n <= max_batch packets of that geometry.  Buffers passed in
+ * + a maximum batch size (<= 65535: packets ride in a CUDA grid dimension).  A call processes n <= max_batch packets
+ * of that geometry; network id and PLCF type may differ per packet (the *_ex calls); packets of several geometries
+ * are bucketed per context by the host adapter (dnrp_host.hpp, batch_phy_t).  Buffers passed in
  * are HOST pointers unless the name ends in _dev.
  */
 #ifndef DNRP_C_API_H
@@ -249,6 +251,29 @@ int dnrp_rx_pcc_batch(dnrp_ctx_t* ctx, uint32_t n, const dnrp_cf32_t* iq_in, con
  * harq_slot / rv / harq_reset as in dnrp_fec_decode_tb; tb_out [n][N_TB_byte]; n_iter [n][C] or NULL. */
 int dnrp_rx_pdc_batch(dnrp_ctx_t* ctx, uint32_t n, const uint32_t* harq_slot, const uint8_t* rv,
                       const uint8_t* harq_reset, uint8_t* tb_out, dnrp_pdc_report_t* out, uint8_t* n_iter);
+
+/* ---- several networks / PLCF types per batch ---------------------------------------------------------------
+ * worker_pool_t::add_network_id -> tx_rx_t::add_new_network_id (lib/src/phy/worker_pool.cpp:109-114, tx_rx.cpp):
+ * precomputes the PDC scrambling sequences of both PLCF types of this id (scrambling_pdc.cpp:43-56: c_init = id & 0xff
+ * for type 1, id >> 8 for type 2).  The context's own network_id is registered at creation.  Not on the hot path. */
+int dnrp_add_network_id(dnrp_ctx_t* ctx, uint32_t network_id);
+
+/* dnrp_tx_batch with the network id and PLCF type taken PER PACKET, as tx_t reads them from each packet's HARQ process
+ * (tx.cpp:176-186: hp_tx.get_PLCF_type(), get_network_id()).  network_id [n] / plcf_type [n] (1 or 2); NULL = the
+ * context's value.  DNRP_ERR_STATE if an id was not registered with dnrp_add_network_id. */
+int dnrp_tx_batch_ex(dnrp_ctx_t* ctx, uint32_t n, const dnrp_tx_desc_t* descs, const uint32_t* network_id,
+                     const uint8_t* plcf_type, const uint8_t* plcf, const uint8_t* tb, dnrp_cf32_t* iq_out,
+                     uint32_t* n_samples_out);
+
+/* dnrp_rx_pdc_batch with network id and PLCF type per packet, as rx_synced_t::demoddecod_rx_pdc reads them from
+ * maclow_phy.hp_rx (rx_synced.cpp:325-350): the firmware's work_pcc decides both from the decoded PLCF. */
+int dnrp_rx_pdc_batch_ex(dnrp_ctx_t* ctx, uint32_t n, const uint32_t* harq_slot, const uint8_t* rv,
+                         const uint8_t* harq_reset, const uint32_t* network_id, const uint8_t* plcf_type,
+                         uint8_t* tb_out, dnrp_pdc_report_t* out, uint8_t* n_iter);
+
+/* process_rx_t::reset_and_terminate_func (lib/src/phy/harq/process_rx.cpp:56-66) for one HARQ slot: soft values, code
+ * block CRC flags and saved code blocks are cleared (a decode with harq_reset = 1 does the same implicitly). */
+int dnrp_harq_reset(dnrp_ctx_t* ctx, uint32_t harq_slot);
 
 /* The whole receive chain for n host IQ windows in ONE call: dnrp_sync_batch -> dnrp_rx_pcc_batch ->
  * dnrp_rx_pdc_batch for every window (no MAC decision between PCC and PDC: the simulator's / a monitor's use, where
