@@ -81,13 +81,14 @@ __device__ __forceinline__ void dft16(float2 (&v)[16]) {
 // multiples of 16, so the padded position of element r is base + r * padded stride.
 template <bool INV, int R, bool POW2, bool PAD>
 __device__ __forceinline__ void fft_pass(const float2* __restrict__ x, float2* __restrict__ y, uint32_t N,
-                                         uint32_t Ns, uint32_t log2Ns, const float2* __restrict__ table, bool pin_, bool pout_) {
+                                         uint32_t Ns, uint32_t log2Ns, const float2* __restrict__ table, bool pin_, bool pout_,
+                                         uint32_t tid = threadIdx.x, uint32_t nthr = blockDim.x) {
     const bool pin = PAD && pin_, pout = PAD && pout_;   // PAD = false: plain buffers, no index selects in the code
     const uint32_t M = N / R;
     const uint32_t tstep = POW2 ? M >> log2Ns : N / (Ns * R);  // W_{Ns*R}^k = W_N^{k*tstep}
     const uint32_t xs = pin ? fft_pad(M) : M;                  // stride between the R inputs
     const uint32_t ys = (pout && Ns >= 16) ? fft_pad(Ns) : Ns;  // stride between the R outputs
-    for (uint32_t j = threadIdx.x; j < M; j += blockDim.x) {
+    for (uint32_t j = tid; j < M; j += nthr) {
         const uint32_t k = POW2 ? (j & (Ns - 1)) : j % Ns;
         float2 v[R];
         const float2* xj = x + (pin ? fft_pad(j) : j);
@@ -168,6 +169,45 @@ __device__ float2* block_fft(float2* a, float2* b, uint32_t N, const float2* __r
         pow2 = false;
     }
 #undef DNRP_FFT_PASS
+    return a;
+}
+
+// FFT of one symbol by a GROUP of N / 16 threads (several groups per block, all moving through the same barriers):
+// thread t of the group enters with v[m] = x[t + (N / 16) m], m = 0..15, in registers -- the first radix-16 pass
+// (Ns = 1, unit twiddles) needs no shared memory on its input side -- and the remaining passes alternate between the
+// group's two padded buffers a and b (fft_buf_len(N) elements each).  N = 1024: passes 16, 16, 4 = two exchanges
+// through shared memory instead of the four of the radix-4 plan.  Returns the buffer holding the result (plain
+// indices).  Every thread of the block must call it (active = false: only takes part in the barriers).
+template <bool INV>
+__device__ float2* group_fft16(float2 (&v)[16], float2* a, float2* b, uint32_t N, const float2* __restrict__ table,
+                               uint32_t tid, uint32_t nthr, bool active) {
+    uint32_t Ns = 16, lg = 4, rem = N / 16;
+    if (active) {
+        dft16<INV>(v);
+        const bool last = rem == 1;
+        float2* yj = a + (last ? 16 * tid : fft_pad(16 * tid));
+#pragma unroll
+        for (int r = 0; r < 16; ++r) yj[r] = v[r];
+    }
+    __syncthreads();
+#define DNRP_GFFT_PASS(R, P2, LGINC)                                                              \
+    {                                                                                             \
+        const bool last = rem == R;                                                               \
+        if (active) fft_pass<INV, R, P2, true>(a, b, N, Ns, lg, table, true, !last, tid, nthr);   \
+        Ns *= R; lg += LGINC; rem /= R;                                                           \
+        float2* t = a; a = b; b = t;                                                              \
+        __syncthreads();                                                                          \
+    }
+    while (rem % 16 == 0) DNRP_GFFT_PASS(16, true, 4)
+    while (rem % 4 == 0) DNRP_GFFT_PASS(4, true, 2)
+    if (rem % 2 == 0) DNRP_GFFT_PASS(2, true, 1)
+    bool pow2 = true;
+    while (rem % 3 == 0) {
+        if (pow2) DNRP_GFFT_PASS(3, true, 0)
+        else DNRP_GFFT_PASS(3, false, 0)
+        pow2 = false;
+    }
+#undef DNRP_GFFT_PASS
     return a;
 }
 

@@ -156,76 +156,95 @@ __device__ __forceinline__ float drs_sign_dev(const phy_dims_t& d, uint32_t l, u
     return ((d.cell[(size_t)l * d.Nk + k] >> 26) & 1u) ? -1.f : 1.f;
 }
 
-// ---- data field: one block per (symbol l = 1..N_DF, RX antenna, packet): CFO derotation, CP removal,
-// FFT, un-mirroring, amplitude scaling, STO derotation (rx_synced.cpp:711-771); DRS symbols also
-// deliver the zero-forced pilots and their SNR sums (rx_synced.cpp:773-861, estimator_snr.cpp:76-86)
-__global__ void __launch_bounds__(256) k_rx_fft(const rx_params_t p) {
+// ---- data field: a GROUP of N_os / 16 threads per (symbol l = 1..N_DF, RX antenna), several groups per block, packet in
+// gridDim.y: CFO derotation, CP removal, FFT, un-mirroring, amplitude scaling, STO derotation (rx_synced.cpp:711-771);
+// DRS symbols also deliver the zero-forced pilots and their SNR sums (rx_synced.cpp:773-861, estimator_snr.cpp:76-86).
+// Every thread loads its 16 samples (stride N_os / 16: coalesced across the group) straight into registers, derotates
+// them there and runs the first radix-16 pass without touching shared memory (fft.cuh, group_fft16).
+__global__ void __launch_bounds__(256) k_rx_fft(const rx_params_t p, uint32_t GT, uint32_t groups) {
     extern __shared__ __align__(16) float2 sm[];
     const phy_dims_t& d = p.d;
-    const uint32_t l = blockIdx.x + 1, a = blockIdx.y, pkt = blockIdx.z;
-    const uint32_t tid = threadIdx.x, nthr = blockDim.x;
+    const uint32_t grp = threadIdx.x / GT, tid = threadIdx.x - grp * GT, nthr = GT;
+    const uint32_t item = blockIdx.x * groups + grp;          // (symbol, antenna) of this group
+    const uint32_t pkt = blockIdx.y;
+    const bool active = grp < groups && item < d.N_DF * d.N_RX;
+    const uint32_t l = (active ? item / d.N_RX : 0) + 1, a = active ? item % d.N_RX : 0;
     const rx_state_t& st = p.state[pkt];
-    float2* X = sm;
-    float2* Yb = sm + fft_buf_len(d.N_os);
-    __shared__ float2 s_red[8];
+    const uint32_t blen = fft_buf_len(d.N_os);
+    float2* A = sm + (size_t)grp * 2 * blen;
+    float2* B = A + blen;
+    float* s_part = reinterpret_cast<float*>(sm + (size_t)groups * 2 * blen);   // [blockDim][2] SNR partial sums
 
     const uint32_t n0 = d.stf_len_os + (l - 1) * d.sym_len_os + d.cp_os;  // relative to the first STF sample
-    const float2* x = p.iq + ((size_t)pkt * d.N_RX + a) * p.iq_stride + (p.t0_zero ? 0 : st.t0) + n0;
-    // mixer phase is continuous: inc0 over the STF, inc1 afterwards (rx_synced.cpp:239-245, 552-555)
-    const double ph0 = (double)st.inc0 * (double)d.stf_len_os + (double)st.inc1 * (double)(n0 - d.stf_len_os);
-    // one exact phasor per thread, then a rotation by nthr samples per iteration (<= 16 float rotations)
-    {
+    float2 v[16];
+    if (active) {
+        const float2* x = p.iq + ((size_t)pkt * d.N_RX + a) * p.iq_stride + (p.t0_zero ? 0 : st.t0) + n0;
+        // mixer phase is continuous: inc0 over the STF, inc1 afterwards (rx_synced.cpp:239-245, 552-555); one exact
+        // phasor per thread, then 15 float rotations by N_os / 16 samples
+        const double ph0 = (double)st.inc0 * (double)d.stf_len_os + (double)st.inc1 * (double)(n0 - d.stf_len_os);
         float2 w = rot(ph0 + (double)st.inc1 * (double)tid);
-        const float2 ws = rot((double)st.inc1 * (double)nthr);
-        for (uint32_t n = tid; n < d.N_os; n += nthr) {
-            X[n] = cmul(x[n], w);
+        const float2 ws = rot((double)st.inc1 * (double)GT);
+#pragma unroll
+        for (int m = 0; m < 16; ++m) {
+            v[m] = cmul(__ldcs(x + tid + m * GT), w);
             w = cmul(w, ws);
         }
     }
-    const float2* F = block_fft<false>(X, Yb, d.N_os, d.twiddle);
+    const float2* F = group_fft16<false>(v, A, B, d.N_os, d.twiddle, tid, nthr, active);
 
-    const float fscale = sqrtf((float)d.N_OCC) / (float)d.N_os;
-    float2* Yout = p.Y + (((size_t)pkt * d.N_RX + a) * d.N_DF + (l - 1)) * d.Nk;
-    float2* Ys = (float2*)(F == X ? Yb : X);  // keep the output symbol in shared for the pilot stage
-    float2 wk = rot((double)st.sto_inc * (double)((int)tid - (int)(d.N_OCC / 2)));
-    const float2 wks = rot((double)st.sto_inc * (double)nthr);
-    wk = make_float2(wk.x * fscale, wk.y * fscale);
-    for (uint32_t k = tid; k < d.Nk; k += nthr) {
-        const float2 v = cmul(F[bin_of_k(k, d)], wk);
-        wk = cmul(wk, wks);
-        Yout[k] = v;
-        Ys[k] = v;
-    }
-    __syncthreads();
-
-    // ---- DRS of this symbol (if any): stream group g0..g1 at occurrence n
     float2 sn = make_float2(0.f, 0.f);
     bool any = false;
-    for (uint32_t ts = 0; ts < d.N_eff_TX; ++ts) {
-        const uint32_t lt = l - 1 - ts / 4;  // symbols since the first DRS symbol of this stream
-        if (l < 1 + ts / 4 || lt % d.N_step != 0) continue;
-        const uint32_t n = lt / d.N_step;
-        if (n >= d.n_drs) continue;
-        any = true;
-        const uint32_t pc = ((ts & 3) + 2 * (n & 1)) & 3;
-        float2* hz = p.hzf + ((((size_t)pkt * d.N_RX + a) * d.N_eff_TX + ts) * d.n_drs + n) * d.NP;
-        for (uint32_t i = tid; i < d.NP; i += nthr) {
-            const uint32_t q = 4 * i + pc;
-            const uint32_t k = q < d.N_OCC / 2 ? q : q + 1;
-            const float sg = drs_sign_dev(d, l, k);
-            const float2 h = make_float2(Ys[k].x * sg, Ys[k].y * sg);  // division by +-1
-            hz[i] = h;
-            sn.x += h.x * h.x + h.y * h.y;
-            if (i + 1 < d.NP) {
-                const uint32_t q2 = q + 4, k2 = q2 < d.N_OCC / 2 ? q2 : q2 + 1;
-                const float sg2 = drs_sign_dev(d, l, k2);
-                const float2 dlt = csub(h, make_float2(Ys[k2].x * sg2, Ys[k2].y * sg2));
-                sn.y += 0.5f * (dlt.x * dlt.x + dlt.y * dlt.y);
+    if (active) {
+        const float fscale = sqrtf((float)d.N_OCC) / (float)d.N_os;
+        float2* Yout = p.Y + (((size_t)pkt * d.N_RX + a) * d.N_DF + (l - 1)) * d.Nk;
+        float2* Ys = (float2*)(F == A ? B : A);  // keep the output symbol in shared for the pilot stage
+        float2 wk = rot((double)st.sto_inc * (double)((int)tid - (int)(d.N_OCC / 2)));
+        const float2 wks = rot((double)st.sto_inc * (double)nthr);
+        wk = make_float2(wk.x * fscale, wk.y * fscale);
+        for (uint32_t k = tid; k < d.Nk; k += nthr) {
+            const float2 y = cmul(F[bin_of_k(k, d)], wk);
+            wk = cmul(wk, wks);
+            Yout[k] = y;
+            Ys[k] = y;
+        }
+    }
+    __syncthreads();
+    if (active) {
+        const float2* Ys = (F == A ? B : A);
+        // ---- DRS of this symbol (if any): stream ts at occurrence n
+        for (uint32_t ts = 0; ts < d.N_eff_TX; ++ts) {
+            const uint32_t lt = l - 1 - ts / 4;  // symbols since the first DRS symbol of this stream
+            if (l < 1 + ts / 4 || lt % d.N_step != 0) continue;
+            const uint32_t n = lt / d.N_step;
+            if (n >= d.n_drs) continue;
+            any = true;
+            const uint32_t pc = ((ts & 3) + 2 * (n & 1)) & 3;
+            float2* hz = p.hzf + ((((size_t)pkt * d.N_RX + a) * d.N_eff_TX + ts) * d.n_drs + n) * d.NP;
+            for (uint32_t i = tid; i < d.NP; i += nthr) {
+                const uint32_t q = 4 * i + pc;
+                const uint32_t k = q < d.N_OCC / 2 ? q : q + 1;
+                const float sg = drs_sign_dev(d, l, k);
+                const float2 h = make_float2(Ys[k].x * sg, Ys[k].y * sg);  // division by +-1
+                hz[i] = h;
+                sn.x += h.x * h.x + h.y * h.y;
+                if (i + 1 < d.NP) {
+                    const uint32_t q2 = q + 4, k2 = q2 < d.N_OCC / 2 ? q2 : q2 + 1;
+                    const float sg2 = drs_sign_dev(d, l, k2);
+                    const float2 dlt = csub(h, make_float2(Ys[k2].x * sg2, Ys[k2].y * sg2));
+                    sn.y += 0.5f * (dlt.x * dlt.x + dlt.y * dlt.y);
+                }
             }
         }
     }
-    sn = block_sum2(sn, s_red);
-    if (tid == 0) p.snr_part[((size_t)pkt * d.N_DF + (l - 1)) * d.N_RX + a] = any ? sn : make_float2(0.f, 0.f);
+    // group-wide sum in a fixed order (deterministic): partials to shared memory, thread 0 of the group adds them up
+    s_part[2 * threadIdx.x] = sn.x;
+    s_part[2 * threadIdx.x + 1] = sn.y;
+    __syncthreads();
+    if (active && tid == 0) {
+        float sx = 0.f, sy = 0.f;
+        for (uint32_t i = 0; i < GT; ++i) { sx += s_part[2 * (grp * GT + i)]; sy += s_part[2 * (grp * GT + i) + 1]; }
+        p.snr_part[((size_t)pkt * d.N_DF + (l - 1)) * d.N_RX + a] = any ? make_float2(sx, sy) : make_float2(0.f, 0.f);
+    }
 }
 
 // ---- Wiener class per DRS symbol, one thread per packet: replays estimator_snr_t in symbol order and
@@ -539,7 +558,14 @@ cudaError_t launch_rx_snr_class(const rx_params_t& p, uint32_t n_packets, cudaSt
 }
 
 cudaError_t launch_rx_fft(const rx_params_t& p, uint32_t n_packets, cudaStream_t st) {
-    const size_t smem = sizeof(float2) * 2 * fft_buf_len(p.d.N_os);
+    // one group of N_os / 16 threads per symbol; as many groups per block as fit into 256 threads (at most 8)
+    const uint32_t GT = p.d.N_os / 16;
+    uint32_t groups = GT >= 256 ? 1 : 256 / GT;
+    if (groups > 8) groups = 8;
+    const uint32_t items = p.d.N_DF * p.d.N_RX;
+    if (groups > items) groups = items;
+    const uint32_t threads = ((groups * GT + 31) / 32) * 32;
+    const size_t smem = sizeof(float2) * 2 * fft_buf_len(p.d.N_os) * groups + sizeof(float) * 2 * threads;
     if (smem > 48 * 1024) {
         static smem_optin_t optin;   // per device
         cudaError_t e = optin.ensure(smem, [](size_t b) {
@@ -547,7 +573,7 @@ cudaError_t launch_rx_fft(const rx_params_t& p, uint32_t n_packets, cudaStream_t
         });
         if (e != cudaSuccess) return e;
     }
-    k_rx_fft<<<dim3(p.d.N_DF, p.d.N_RX, n_packets), 256, smem, st>>>(p);
+    k_rx_fft<<<dim3((items + groups - 1) / groups, n_packets), threads, smem, st>>>(p, GT, groups);
     return cudaGetLastError();
 }
 
