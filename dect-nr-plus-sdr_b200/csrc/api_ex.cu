@@ -99,3 +99,37 @@ int dnrp_rx_pdc_batch_ex(dnrp_ctx_t* c, uint32_t n, const uint32_t* harq_slot, c
 }
 
 }  // extern "C"
+
+// ---- several packet geometries behind one receiver: windows travel between contexts on the device ---------------------
+namespace {
+__global__ void k_copy_windows(float2* __restrict__ dst, uint32_t dst_stride, const float2* __restrict__ src, uint32_t src_stride,
+                               const uint32_t* __restrict__ src_idx, uint32_t n_ant) {
+    const uint32_t i = blockIdx.z, a = blockIdx.y;
+    const float2* s = src + ((size_t)src_idx[i] * n_ant + a) * src_stride;
+    float2* d = dst + ((size_t)i * n_ant + a) * dst_stride;
+    for (uint32_t n = blockIdx.x * blockDim.x + threadIdx.x; n < dst_stride; n += gridDim.x * blockDim.x)
+        d[n] = n < src_stride ? s[n] : make_float2(0.f, 0.f);
+}
+}  // namespace
+
+extern "C" int dnrp_rx_import_windows(dnrp_ctx_t* dst, dnrp_ctx_t* src, uint32_t n, const uint32_t* src_idx) {
+    DNRP_REQUIRE(dst && src && src_idx, "null argument");
+    DNRP_REQUIRE(dst->device == src->device, "both contexts must live on the same device");
+    DNRP_REQUIRE(dst->dims.N_RX == src->dims.N_RX, "both contexts must have the same number of receive antennas");
+    DNRP_REQUIRE(dst->cfg.oversampling == src->cfg.oversampling && dst->cfg.resample_L == src->cfg.resample_L &&
+                     dst->cfg.resample_M == src->cfg.resample_M && dst->cfg.psdef.u == src->cfg.psdef.u &&
+                     dst->cfg.psdef.b == src->cfg.psdef.b,
+                 "both contexts must share mu, beta, oversampling and resampling (one sample rate)");
+    DNRP_REQUIRE(n > 0 && n <= dst->B, "batch size out of range");
+    for (uint32_t i = 0; i < n; ++i) DNRP_REQUIRE(src_idx[i] < src->B, "source window index out of range");
+    DNRP_CUDA(cudaSetDevice(dst->device));
+    DNRP_CUDA(cudaStreamSynchronize(src->stream));   // the source windows are complete
+    DNRP_CUDA(cudaMemcpyAsync(dst->d_slot.p, src_idx, 4 * (size_t)n, cudaMemcpyHostToDevice, dst->stream));
+    const dim3 grid((dst->rx_stride + 1023) / 1024, dst->dims.N_RX, n);
+    k_copy_windows<<<grid, 256, 0, dst->stream>>>(dst->d_iq_rx.p, dst->rx_stride, src->d_iq_rx.p, src->rx_stride,
+                                                  dst->d_slot.p, dst->dims.N_RX);
+    DNRP_CUDA(cudaGetLastError());
+    DNRP_CUDA(cudaStreamSynchronize(dst->stream));   // src_idx is caller memory
+    ++dst->launches;
+    return DNRP_OK;
+}

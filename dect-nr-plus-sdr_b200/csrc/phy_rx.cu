@@ -302,17 +302,20 @@ __device__ __forceinline__ void chan_est_rx(const rx_params_t& p, uint32_t pkt, 
                    ts = (plan >> 18) & 7u, lr = (plan >> 21) & 1u;
     const phy_dims_t::wiener_dev_t& W = lr ? d.wiener_lr[p.cls[(size_t)pkt * p.cls_stride + j]]
                                            : d.wiener_l[p.cls[(size_t)pkt * p.cls_stride + j]];
-    const size_t stride_a = (size_t)d.N_eff_TX * d.n_drs * d.NP;    // pilots of the next antenna
-    const float2* hz_row = p.hzf + ((((size_t)pkt * d.N_RX) * d.N_eff_TX + ts) * d.n_drs + row) * d.NP;
-    const size_t o = (size_t)base * d.Nk + k;
-    const float* w = W.weights + (size_t)W.idx_weight[o] * W.n_interp;
+    // all offsets inside one packet's pilots fit 32 bits: one 64-bit base per packet, 32-bit element offsets per tap
+    const uint32_t stride_a = d.N_eff_TX * d.n_drs * d.NP;          // pilots of the next antenna
+    const float2* hz_pkt = p.hzf + (size_t)pkt * d.N_RX * stride_a;
+    const uint32_t off_row = (ts * d.n_drs + row) * d.NP;
+    const uint32_t o = base * d.Nk + k;
+    const float* w = W.weights + (uint32_t)W.idx_weight[o] * W.n_interp;
     const uint32_t m0 = W.idx_pilot[o];
+    const uint32_t n_interp = W.n_interp;
 #pragma unroll
     for (int a = 0; a < NRX; ++a) h[a] = make_float2(0.f, 0.f);
     if (!lr) {
         // mode "l": non-interlaced pilots of DRS occurrence row
-        const float2* hz = hz_row + m0;
-        for (uint32_t i = 0; i < W.n_interp; ++i) {
+        const float2* hz = hz_pkt + off_row + m0;
+        for (uint32_t i = 0; i < n_interp; ++i) {
             const float wi = w[i];
 #pragma unroll
             for (int a = 0; a < NRX; ++a) {
@@ -322,15 +325,19 @@ __device__ __forceinline__ void chan_est_rx(const rx_params_t& p, uint32_t pkt, 
             }
         }
     } else {
-        // mode "lr": pilots interlaced over DRS occurrences row (left) and row + 1 (right)
-        for (uint32_t i = 0; i < W.n_interp; ++i) {
-            const uint32_t m = m0 + i;
-            const uint32_t side = (m & 1) ^ flip;
-            const float2* hz = hz_row + (size_t)side * d.NP + (m >> 1);
+        // mode "lr": pilots interlaced over DRS occurrences row (left) and row + 1 (right): tap m sits on side
+        // (m & 1) ^ flip at index m >> 1.  Two running offsets, one per parity of m.
+        uint32_t off_e = off_row + (flip ? d.NP : 0u) + ((m0 + 1) >> 1);      // next even m
+        uint32_t off_o = off_row + (flip ? 0u : d.NP) + (m0 >> 1);            // next odd m
+        bool odd = (m0 & 1u) != 0u;
+        for (uint32_t i = 0; i < n_interp; ++i) {
+            const uint32_t off = odd ? off_o : off_e;
+            if (odd) ++off_o; else ++off_e;
+            odd = !odd;
             const float wi = w[i];
 #pragma unroll
             for (int a = 0; a < NRX; ++a) {
-                const float2 v = hz[a * stride_a];
+                const float2 v = hz_pkt[off + a * stride_a];
                 h[a].x += wi * v.x;
                 h[a].y += wi * v.y;
             }

@@ -271,6 +271,16 @@ int dnrp_rx_pdc_batch_ex(dnrp_ctx_t* ctx, uint32_t n, const uint32_t* harq_slot,
                          const uint8_t* harq_reset, const uint32_t* network_id, const uint8_t* plcf_type,
                          uint8_t* tb_out, dnrp_pdc_report_t* out, uint8_t* n_iter);
 
+/* Several packet geometries on one receiver.  The reference processes the PCC under the pool's MAXIMUM packet sizes
+ * and learns the packet's own geometry from the decoded PLCF (tpoint.cpp:119-141, worksub_psdef); rx_synced_t then
+ * takes the packet sizes from hp_rx (rx_synced.cpp:325-350).  Here a context has one geometry: the host runs sync + PCC
+ * on the context of the longest packet, then copies the IQ windows of the packets that announced another geometry into
+ * the context created for it -- on the device, window src_idx[i] of `src` becomes window i of `dst` (zero filled
+ * behind the shorter window) -- and runs dnrp_rx_pcc_batch (with the sync reports of the first pass) +
+ * dnrp_rx_pdc_batch there.  Both contexts: same device, mu, beta, oversampling, resampling, N_RX.
+ * dnrp_host.hpp (batch_phy_t::add_plan) does all of this behind the tpoint_t callbacks. */
+int dnrp_rx_import_windows(dnrp_ctx_t* dst, dnrp_ctx_t* src, uint32_t n, const uint32_t* src_idx);
+
 /* process_rx_t::reset_and_terminate_func (lib/src/phy/harq/process_rx.cpp:56-66) for one HARQ slot: soft values, code
  * block CRC flags and saved code blocks are cleared (a decode with harq_reset = 1 does the same implicitly). */
 int dnrp_harq_reset(dnrp_ctx_t* ctx, uint32_t harq_slot);

@@ -17,6 +17,7 @@
 // Not mirrored (MAC layer): the parsers of the individual MAC messages / IEs (sections_part4/mac_messages_and_ie).
 // There is no CPU fallback: construction throws if libdnrp_cuda.so cannot create its context.
 #pragma once
+#include <algorithm>
 #include <array>
 #include <cmath>
 #include <cstdint>
@@ -371,13 +372,50 @@ class batch_phy_t {
         batch_phy_t(const dnrp_config_t& cfg, int device, uint32_t nof_process_rx_) : config(cfg), max_windows(cfg.max_batch),
                                                                                      nof_process_rx(nof_process_rx_) {
             config.max_batch = max_windows + nof_process_rx;
+            device_index = device;
             if (dnrp_ctx_create(&config, device, &ctx) != DNRP_OK)
                 throw std::runtime_error(std::string("dnrp_ctx_create: ") + dnrp_last_error_string());
             dnrp_ctx_get_packet_sizes(ctx, &packet_sizes);
             tx_stride = dnrp_tx_stride(ctx);
             rx_stride = dnrp_rx_stride(ctx);
+            plans.push_back(plan_t{config.psdef, ctx, packet_sizes, tx_stride, rx_stride});
+            network_ids.push_back(config.network_id);
         }
-        ~batch_phy_t() { dnrp_ctx_destroy(ctx); }
+        ~batch_phy_t() {
+            for (auto& pl : plans) dnrp_ctx_destroy(pl.ctx);
+        }
+
+        /// A further packet geometry this PHY accepts (the reference allocates for the radio device class' maximum and
+        /// takes every packet's own sizes from its HARQ process: tpoint.cpp:119-141, rx_synced.cpp:325-350).  The
+        /// constructor's psdef is the MAXIMUM: sync and PCC run under it, its IQ window holds the longest packet.  A plan
+        /// shares mu, beta, the number of effective TX antennas (the PCC layout) and the antenna / rate configuration.
+        void add_plan(const sp3::packet_sizes_def_t& psdef) {
+            if (find_plan(psdef) >= 0) return;
+            dnrp_config_t c = config;
+            c.psdef = psdef;
+            plan_t pl{};
+            pl.psdef = psdef;
+            if (dnrp_ctx_create(&c, device_index, &pl.ctx) != DNRP_OK)
+                throw std::runtime_error(std::string("dnrp_ctx_create (add_plan): ") + dnrp_last_error_string());
+            dnrp_ctx_get_packet_sizes(pl.ctx, &pl.ps);
+            pl.tx_stride = dnrp_tx_stride(pl.ctx);
+            pl.rx_stride = dnrp_rx_stride(pl.ctx);
+            if (pl.ps.psdef.u != packet_sizes.psdef.u || pl.ps.psdef.b != packet_sizes.psdef.b ||
+                pl.ps.N_eff_TX != packet_sizes.N_eff_TX || pl.rx_stride > rx_stride) {
+                dnrp_ctx_destroy(pl.ctx);
+                throw std::invalid_argument("add_plan: geometry must share mu, beta and N_eff_TX with the maximum geometry and "
+                                            "must not be longer than it");
+            }
+            for (uint32_t id : network_ids) check(dnrp_add_network_id(pl.ctx, id), "dnrp_add_network_id");
+            plans.push_back(pl);
+        }
+
+        /// worker_pool_t::add_network_id (worker_pool.cpp:109-114): scrambling sequences of a further network
+        void add_network_id(uint32_t network_id) {
+            for (uint32_t id : network_ids) if (id == network_id) return;
+            network_ids.push_back(network_id);
+            for (auto& pl : plans) check(dnrp_add_network_id(pl.ctx, network_id), "dnrp_add_network_id");
+        }
         batch_phy_t(const batch_phy_t&) = delete;
         batch_phy_t& operator=(const batch_phy_t&) = delete;
 
@@ -394,19 +432,49 @@ class batch_phy_t {
         void generate_tx_packets(std::vector<tx_descriptor_t>& descs, cf_t* iq_out, std::vector<uint32_t>* n_samples = nullptr) {
             const uint32_t n = (uint32_t)descs.size();
             if (n == 0) return;
-            std::vector<dnrp_tx_desc_t> d(n);
-            std::vector<uint8_t> plcf(10 * (size_t)n), tb((size_t)n * packet_sizes.N_TB_byte);
-            for (uint32_t i = 0; i < n; ++i) {
-                const tx_meta_t& m = descs[i].tx_meta;
-                if (std::memcmp(&descs[i].hp_tx.get_psdef(), &config.psdef, sizeof(dnrp_psdef_t)) != 0)
-                    throw std::invalid_argument("tx_descriptor_t: packet geometry differs from the context's");
-                d[i] = {descs[i].codebook_index, m.optimal_scaling_DAC ? 1u : 0u, m.DAC_scale, m.iq_phase_rad,
-                        m.iq_phase_increment_s2s_post_resampling_rad, m.GI_percentage, descs[i].hp_tx.get_rv()};
-                std::memcpy(&plcf[10 * (size_t)i], descs[i].hp_tx.get_a_plcf(), 10);
-                std::memcpy(&tb[(size_t)i * packet_sizes.N_TB_byte], descs[i].hp_tx.get_a_tb(), packet_sizes.N_TB_byte);
-            }
             std::vector<uint32_t> ns(n);
-            check(dnrp_tx_batch(ctx, n, d.data(), plcf.data(), tb.data(), iq_out, ns.data()), "dnrp_tx_batch");
+            // one device batch per geometry; network id and PLCF type ride per packet (tx.cpp:176-186)
+            std::vector<std::vector<uint32_t>> bucket(plans.size());
+            for (uint32_t i = 0; i < n; ++i) {
+                const int pl = find_plan(descs[i].hp_tx.get_psdef());
+                if (pl < 0) throw std::invalid_argument("tx_descriptor_t: packet geometry not registered (batch_phy_t::add_plan)");
+                bucket[(size_t)pl].push_back(i);
+            }
+            if (bucket[0].size() != n && iq_out == nullptr)
+                throw std::invalid_argument("packets of several geometries need a host IQ buffer (device hand-over is per context)");
+            for (size_t pl = 0; pl < plans.size(); ++pl) {
+                const std::vector<uint32_t>& idx = bucket[pl];
+                const uint32_t m = (uint32_t)idx.size();
+                if (m == 0) continue;
+                const plan_t& P = plans[pl];
+                std::vector<dnrp_tx_desc_t> d(m);
+                std::vector<uint32_t> ids(m), nsm(m);
+                std::vector<uint8_t> tys(m), plcf(10 * (size_t)m), tb((size_t)m * P.ps.N_TB_byte);
+                for (uint32_t q = 0; q < m; ++q) {
+                    tx_descriptor_t& D = descs[idx[q]];
+                    const tx_meta_t& mt = D.tx_meta;
+                    d[q] = {D.codebook_index, mt.optimal_scaling_DAC ? 1u : 0u, mt.DAC_scale, mt.iq_phase_rad,
+                            mt.iq_phase_increment_s2s_post_resampling_rad, mt.GI_percentage, D.hp_tx.get_rv()};
+                    ids[q] = D.hp_tx.get_network_id();
+                    tys[q] = (uint8_t)D.hp_tx.get_PLCF_type();
+                    std::memcpy(&plcf[10 * (size_t)q], D.hp_tx.get_a_plcf(), 10);
+                    std::memcpy(&tb[(size_t)q * P.ps.N_TB_byte], D.hp_tx.get_a_tb(), P.ps.N_TB_byte);
+                }
+                const bool direct = pl == 0 && m == n;      // one geometry: IQ straight into the caller's buffer
+                std::vector<cf_t> tmp;
+                if (!direct && iq_out) tmp.resize((size_t)m * P.ps.N_TX * P.tx_stride);
+                check(dnrp_tx_batch_ex(P.ctx, m, d.data(), ids.data(), tys.data(), plcf.data(), tb.data(),
+                                       direct ? iq_out : (iq_out ? tmp.data() : nullptr), nsm.data()), "dnrp_tx_batch_ex");
+                for (uint32_t q = 0; q < m; ++q) {
+                    ns[idx[q]] = nsm[q];
+                    if (!direct && iq_out)     // packet slots of the caller's buffer have the maximum geometry's stride
+                        for (uint32_t a = 0; a < P.ps.N_TX; ++a) {
+                            cf_t* dst = iq_out + ((size_t)idx[q] * packet_sizes.N_TX + a) * tx_stride;
+                            std::memset(dst, 0, sizeof(cf_t) * tx_stride);
+                            std::memcpy(dst, &tmp[((size_t)q * P.ps.N_TX + a) * P.tx_stride], sizeof(cf_t) * std::min(P.tx_stride, tx_stride));
+                        }
+                }
+            }
             for (uint32_t i = 0; i < n; ++i) descs[i].hp_tx.finalize();
             if (n_samples) *n_samples = ns;
             stats.tx_packets += n;
@@ -483,8 +551,7 @@ class batch_phy_t {
             std::vector<sync_report_t> sync_reports;
             std::vector<pcc_report_t> pcc_reports(n);
             std::vector<maclow_phy_t> maclow(n);
-            std::vector<uint32_t> slot(n), job(n, 0);
-            std::vector<uint8_t> rv(n, 0), reset(n, 1), keep(n, 0);
+            std::vector<uint8_t> keep(n, 0);
             sync_reports.reserve(n);
             const uint32_t N_RX = get_N_RX();
             for (uint32_t i = 0; i < n; ++i) {               // FIFO: job order = window order (worker_tx_rx.cpp:165-170)
@@ -520,43 +587,92 @@ class batch_phy_t {
                 keep[i] = 1;
                 ++stats.pdc_requested;
             }
-            // HARQ slots: a receive process id IS its soft buffer slot [0, nof_process_rx); packets whose PDC is not
-            // wanted still pass through the batched decoder and use the scratch slots behind them
-            {
-                std::vector<uint8_t> used(nof_process_rx, 0);
-                for (uint32_t i = 0; i < n; ++i) {
-                    slot[i] = nof_process_rx + i;
-                    if (!keep[i]) continue;
-                    const uint32_t id = maclow[i].hp_rx->get_id();
-                    if (id >= nof_process_rx || used[id])
-                        throw std::runtime_error("HARQ process assigned twice in one batch or id beyond nof_process_rx");
-                    used[id] = 1; slot[i] = id; rv[i] = (uint8_t)maclow[i].hp_rx->get_rv();
-                    reset[i] = maclow[i].hp_rx->is_first_transmission() ? 1 : 0;
-                }
-            }
-            std::vector<uint8_t> tb((size_t)n * packet_sizes.N_TB_byte);
-            std::vector<dnrp_pdc_report_t> pdc(n);
-            check(dnrp_rx_pdc_batch(ctx, n, slot.data(), rv.data(), reset.data(), tb.data(), pdc.data(), nullptr), "dnrp_rx_pdc_batch");
+            // one PDC batch per geometry: the maximum geometry's context holds every window already (sync + PCC ran
+            // there); packets that announced another registered geometry travel to its context on the device, where
+            // the front end runs again under that geometry (rx_synced.cpp:325-350 takes the sizes from hp_rx)
+            std::vector<std::vector<uint32_t>> bucket(plans.size());
             for (uint32_t i = 0; i < n; ++i) {
                 if (!keep[i]) continue;
-                harq::process_rx_t* hp = maclow[i].hp_rx;
-                std::memcpy(hp->get_a_tb(), &tb[(size_t)i * packet_sizes.N_TB_byte], packet_sizes.N_TB_byte);
-                pdc_report_t rep;
-                rep.crc_status = pdc[i].crc_ok != 0;
-                rep.a_tb = hp->get_a_tb(); rep.N_TB_byte = packet_sizes.N_TB_byte;
-                rep.snr_dB = pdc[i].snr_dB;
-                rep.mimo_report.N_RX = pdc[i].mimo_N_RX; rep.mimo_report.N_TS_other = pdc[i].mimo_N_TS_other;
-                rep.mimo_report.tm_3_7_beamforming_idx = pdc[i].tm_3_7_beamforming_idx;
-                rep.mimo_report.tm_3_7_beamforming_reciprocal_idx = pdc[i].tm_3_7_beamforming_reciprocal_idx;
-                const phy_maclow_t pm{sync_reports[i], pcc_reports[i]};
-                const phy_machigh_t in{pm, maclow[i], rep};
-                machigh_phy_t out = rep.crc_status ? tpoint.work_pdc(in) : tpoint.work_pdc_error(in);
-                if (rep.crc_status) ++stats.pdc_crc_ok;
-                hp->finalize(rep.crc_status);                   // worker_tx_rx.cpp:228
-                for (auto& d : out.tx_descriptor_vec) tx_out.push_back(d);
+                const int pl = find_plan(maclow[i].hp_rx->get_psdef());
+                if (pl < 0) throw std::runtime_error("work_pcc chose a packet geometry that is not registered (batch_phy_t::add_plan)");
+                bucket[(size_t)pl].push_back(i);
+            }
+            for (size_t pl = 0; pl < plans.size(); ++pl) {
+                const std::vector<uint32_t>& idx = bucket[pl];
+                if (idx.empty()) continue;
+                const plan_t& P = plans[pl];
+                // windows of this batch: plan 0 decodes all n in place (the unwanted ones on scratch slots), another
+                // plan its own m
+                const uint32_t m = pl == 0 ? n : (uint32_t)idx.size();
+                std::vector<uint32_t> slot(m), ids(m, config.network_id), win(m);
+                std::vector<uint8_t> rv(m, 0), reset(m, 1), tys(m, (uint8_t)config.plcf_type), mine(m, 0);
+                std::vector<uint8_t> used(nof_process_rx, 0);
+                for (uint32_t q = 0; q < m; ++q) { slot[q] = nof_process_rx + q; win[q] = pl == 0 ? q : idx[q]; }
+                for (uint32_t z = 0; z < (uint32_t)idx.size(); ++z) {
+                    const uint32_t i = idx[z], q = pl == 0 ? i : z;
+                    harq::process_rx_t* hp = maclow[i].hp_rx;
+                    const uint32_t id = hp->get_id();
+                    // a receive process id IS its soft buffer slot [0, nof_process_rx) in the context of its geometry
+                    if (id >= nof_process_rx || used[id])
+                        throw std::runtime_error("HARQ process assigned twice in one batch or id beyond nof_process_rx");
+                    used[id] = 1; slot[q] = id; rv[q] = (uint8_t)hp->get_rv();
+                    reset[q] = hp->is_first_transmission() ? 1 : 0;
+                    ids[q] = hp->get_network_id(); tys[q] = (uint8_t)hp->get_PLCF_type(); mine[q] = 1;
+                }
+                if (pl != 0) {
+                    check(dnrp_rx_import_windows(P.ctx, ctx, m, win.data()), "dnrp_rx_import_windows");
+                    std::vector<dnrp_sync_report_t> sync_in(m);
+                    std::vector<dnrp_pcc_report_t> pcc2(m);
+                    for (uint32_t q = 0; q < m; ++q) {
+                        const dnrp_sync_result_t& r = sres[win[q]];
+                        sync_in[q] = dnrp_sync_report_t{};
+                        sync_in[q].fine_peak_time_local = r.fine_peak_time_local;
+                        sync_in[q].cfo_fractional_rad = r.cfo_fractional_rad;
+                        sync_in[q].cfo_integer_rad = r.cfo_integer_rad;
+                        for (uint32_t a = 0; a < 8; ++a) sync_in[q].rms[a] = r.rms_array[a];
+                    }
+                    check(dnrp_rx_pcc_batch(P.ctx, m, nullptr, sync_in.data(), pcc2.data()), "dnrp_rx_pcc_batch");
+                }
+                std::vector<uint8_t> tb((size_t)m * P.ps.N_TB_byte);
+                std::vector<dnrp_pdc_report_t> pdc(m);
+                check(dnrp_rx_pdc_batch_ex(P.ctx, m, slot.data(), rv.data(), reset.data(), ids.data(), tys.data(), tb.data(),
+                                           pdc.data(), nullptr), "dnrp_rx_pdc_batch_ex");
+                for (uint32_t q = 0; q < m; ++q) {
+                    if (!mine[q]) continue;
+                    const uint32_t i = win[q];
+                    harq::process_rx_t* hp = maclow[i].hp_rx;
+                    std::memcpy(hp->get_a_tb(), &tb[(size_t)q * P.ps.N_TB_byte], P.ps.N_TB_byte);
+                    pdc_report_t rep;
+                    rep.crc_status = pdc[q].crc_ok != 0;
+                    rep.a_tb = hp->get_a_tb(); rep.N_TB_byte = P.ps.N_TB_byte;
+                    rep.snr_dB = pdc[q].snr_dB;
+                    rep.mimo_report.N_RX = pdc[q].mimo_N_RX; rep.mimo_report.N_TS_other = pdc[q].mimo_N_TS_other;
+                    rep.mimo_report.tm_3_7_beamforming_idx = pdc[q].tm_3_7_beamforming_idx;
+                    rep.mimo_report.tm_3_7_beamforming_reciprocal_idx = pdc[q].tm_3_7_beamforming_reciprocal_idx;
+                    const phy_maclow_t pm{sync_reports[i], pcc_reports[i]};
+                    const phy_machigh_t in{pm, maclow[i], rep};
+                    machigh_phy_t out = rep.crc_status ? tpoint.work_pdc(in) : tpoint.work_pdc_error(in);
+                    if (rep.crc_status) ++stats.pdc_crc_ok;
+                    hp->finalize(rep.crc_status);                   // worker_tx_rx.cpp:228
+                    for (auto& d : out.tx_descriptor_vec) tx_out.push_back(d);
+                }
             }
         }
 
+        struct plan_t {
+            sp3::packet_sizes_def_t psdef;
+            dnrp_ctx_t* ctx;
+            sp3::packet_sizes_t ps;
+            uint32_t tx_stride, rx_stride;
+        };
+        std::vector<plan_t> plans;           // [0] = the maximum geometry (sync + PCC run there)
+        std::vector<uint32_t> network_ids;
+        int device_index{0};
+        int find_plan(const sp3::packet_sizes_def_t& psdef) const {
+            for (size_t i = 0; i < plans.size(); ++i)
+                if (std::memcmp(&plans[i].psdef, &psdef, sizeof(psdef)) == 0) return (int)i;
+            return -1;
+        }
         dnrp_config_t config;
         uint32_t max_windows, nof_process_rx;
         dnrp_ctx_t* ctx{nullptr};

@@ -1,9 +1,11 @@
 """profiling driver: one resident receive-chain step (sync + rx chain) on P packets of C2, run twice (the second
 repetition is the one to capture: ncu --launch-skip 19 -c 15)"""
+import os
 import sys
 import numpy as np
-sys.path.insert(0, "/root/repo")
-sys.path.insert(0, "/root/repo/tests")
+ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
 from conftest import load_product
 product = load_product()
 P = int(sys.argv[1]) if len(sys.argv) > 1 else 2000
