@@ -59,6 +59,11 @@ int run_rx_pcc(dnrp_ctx* c, uint32_t n) {
 }
 
 int run_rx_pdc(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, bool have_reset) {
+    if (c->dims.N_SS > 1 && c->dims.N_RX < c->dims.N_SS) {
+        set_last_error("spatial multiplexing with " + std::to_string(c->dims.N_SS) + " streams needs at least as many receive antennas (N_RX = " +
+                       std::to_string(c->dims.N_RX) + ")");
+        return DNRP_ERR_INVALID;
+    }
     const rx_params_t p = make_rx_params(c);
     DNRP_LAUNCH(c, DNRP_KERNEL_RX_DEMAP_PDC, launch_rx_demap(p, n, false, c->stream));
     mimo_params_t mp{};

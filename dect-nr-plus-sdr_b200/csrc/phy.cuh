@@ -26,7 +26,7 @@ struct phy_dims_t {
     // channel-estimation plan per demapper unit (cell, or cell pair with transmit diversity) and stream slot (A, B):
     // everything rx_synced's processing-stage bookkeeping derives from (symbol, stream), packed by ce_plan_word()
     const uint32_t* pcc_plan;  // [units][2]
-    const uint32_t* pdc_plan;  // [units][2]
+    const uint32_t* pdc_plan;  // [units][2]; spatial multiplexing (N_SS > 1): [cells][N_SS], one word per stream
     const int8_t* stf_sign;    // [Nk]
     const int8_t* W;           // [n_cb_idx][N_TX][N_TS] codes 0, +-1, +-2 (= +-j)
     const float* W_scale;      // [n_cb_idx]
@@ -64,6 +64,7 @@ struct rx_state_t {
     float SpN_sum, N_sum;    // estimator_snr accumulators after the STF (boost removed)
     uint32_t SpN_cnt, N_cnt;
     float snr_db_pcc, snr_db_pdc;
+    float sm_rho_ref;        // spatial multiplexing: the packet's reference loss (phy_rx.cu k_rx_sm_ref)
 };
 
 struct rx_params_t {

@@ -357,8 +357,8 @@ __device__ __forceinline__ float to_short(float v) {
 __device__ __forceinline__ uint32_t pack_llr(float lo, float hi) {
     return ((uint32_t)(uint16_t)(int16_t)lo) | ((uint32_t)(uint16_t)(int16_t)hi << 16);
 }
-__device__ __forceinline__ void demap_cell(float2 z, uint32_t N_bps, uint32_t (&w)[4]) {
-    w[1] = w[2] = w[3] = 0u;
+__device__ __forceinline__ void demap_cell(float2 z, uint32_t N_bps, uint32_t (&w)[5]) {
+    w[1] = w[2] = w[3] = w[4] = 0u;
     if (N_bps == 1) {
         w[0] = pack_llr(to_short(-(100.f * (z.x + z.y) * 0.70710678118654752f)), 0.f);
         return;
@@ -367,25 +367,25 @@ __device__ __forceinline__ void demap_cell(float2 z, uint32_t N_bps, uint32_t (&
         w[0] = pack_llr(to_short(z.x * (-100.f * 1.41421356237309505f)), to_short(z.y * (-100.f * 1.41421356237309505f)));
         return;
     }
-    const float S = N_bps == 4 ? 400.f : (N_bps == 6 ? 700.f : 1000.f);
-    const float nrm = N_bps == 4 ? 0.31622776601683794f : (N_bps == 6 ? 0.15430334996209191f : 0.07669649888473704f);
+    // 1024-QAM (MCS 10, 11) is outside srsRAN and the reference (tx.cpp:53-60): the same recursion one level deeper,
+    // scale 1300, first threshold 16 / sqrt(682) -- own extension, DESIGN.md "1024-QAM"
+    const float S = N_bps == 4 ? 400.f : (N_bps == 6 ? 700.f : (N_bps == 8 ? 1000.f : 1300.f));
+    const float nrm = N_bps == 4 ? 0.31622776601683794f
+                                 : (N_bps == 6 ? 0.15430334996209191f : (N_bps == 8 ? 0.07669649888473704f : 0.03829197905337418f));
     const float yre = to_short(S * z.x), yim = to_short(S * z.y);
     // -(-32768) saturates
     w[0] = pack_llr(yre == -32768.f ? 32767.f : -yre, yim == -32768.f ? 32767.f : -yim);
-    float th = (float)(N_bps == 4 ? 2 : (N_bps == 6 ? 4 : 8)) * S * nrm;
+    float th = (float)(1u << (N_bps / 2 - 1)) * S * nrm;
     float a0 = to_short(fabsf(yre) - th), a1 = to_short(fabsf(yim) - th);
     w[1] = pack_llr(a0, a1);
-    if (N_bps >= 6) {
-        th *= 0.5f;
-        a0 = to_short(fabsf(a0) - th);
-        a1 = to_short(fabsf(a1) - th);
-        w[2] = pack_llr(a0, a1);
-    }
-    if (N_bps >= 8) {
-        th *= 0.5f;
-        a0 = to_short(fabsf(a0) - th);
-        a1 = to_short(fabsf(a1) - th);
-        w[3] = pack_llr(a0, a1);
+#pragma unroll
+    for (uint32_t i = 2; i < 5; ++i) {
+        if (N_bps >= 2 * i + 2) {
+            th *= 0.5f;
+            a0 = to_short(fabsf(a0) - th);
+            a1 = to_short(fabsf(a1) - th);
+            w[i] = pack_llr(a0, a1);
+        }
     }
 }
 
@@ -395,7 +395,7 @@ __device__ __forceinline__ void demap_cell(float2 z, uint32_t N_bps, uint32_t (&
 // (N_bps even; BPSK stores its int16 values directly).
 template <bool TXDIV, int NRX>
 __global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_demap(const rx_params_t p, uint32_t pcc) {
-    __shared__ uint32_t s_out[128 * 8];
+    __shared__ uint32_t s_out[128 * 10];
     const phy_dims_t& d = p.d;
     const uint32_t pkt = blockIdx.y;
     const uint32_t n_cells = pcc ? 98u : d.N_PDC_subc;
@@ -407,7 +407,7 @@ __global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_dema
     const uint32_t cells_per_unit = TXDIV ? 2u : 1u;
     const uint32_t n_units = n_cells / cells_per_unit;
     const uint32_t n_llr = cells_per_unit * N_bps;  // LLRs per thread
-    uint32_t w0[4] = {0u, 0u, 0u, 0u}, w1[4] = {0u, 0u, 0u, 0u};
+    uint32_t w0[5] = {0u, 0u, 0u, 0u, 0u}, w1[5] = {0u, 0u, 0u, 0u, 0u};
     if (u < n_units) {
         if (!TXDIV) {
             const uint32_t lkv = lk[u];
@@ -460,7 +460,7 @@ __global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_dema
         if (u < n_units) out[u] = (int16_t)(w0[0] & 0xffffu);
         return;
     }
-    const uint32_t W = n_llr / 2;  // words per thread: 1 .. 8
+    const uint32_t W = n_llr / 2;  // words per thread: 1 .. 10
     if (u < n_units) {
         uint32_t* so = s_out + threadIdx.x * W;
         if (TXDIV && N_bps == 1) {
@@ -468,7 +468,7 @@ __global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_dema
         } else {
             const uint32_t wc = N_bps / 2;  // words per cell
 #pragma unroll
-            for (uint32_t i = 0; i < 4; ++i) {
+            for (uint32_t i = 0; i < 5; ++i) {
                 if (i < wc) so[i] = w0[i];
                 if (TXDIV && i < wc) so[wc + i] = w1[i];
             }
@@ -481,7 +481,170 @@ __global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_dema
     for (uint32_t i = threadIdx.x; i < n_here * W; i += blockDim.x) __stcs(&out32[i], s_out[i]);
 }
 
+// ---- spatial multiplexing (transmission modes 2, 4, 6, 8, 9, 11).  The reference stops at a stub
+// (rx_synced.cpp:1331-1333 run_pdc_mode_AxA_MIMO), so the specification is this repo's own, DESIGN.md "Spatial
+// multiplexing receive", restated in oracle/rx.c detect_sm / finish_sm and oracle/rx_mimo.py:
+//   per cell: A = H^H H, b = H^H y, Cholesky A = L L^H (pivot floor 1e-6 A_jj), M = L^-1, x = M^H M b (zero forcing),
+//             rho_s = min(1, 1 / ([A^-1]_ss A_ss)) = loss of stream s against its matched filter bound;
+//   per packet: rho_ref = mean of rho over the cells 0, 8, 16, ... (all streams);
+//   LLRs of (cell q, stream s) at (q N_SS + s) N_bps = trunc(min(rho_s / rho_ref, 4) * demap(x_s)).
+// Everything of one cell lives in the registers of one thread (8 x 8 spills to local memory, a rare mode).
+template <int NSS, int NRX>
+__device__ __forceinline__ void sm_solve(const rx_params_t& p, uint32_t pkt, uint32_t q, float2 (&x)[NSS], float (&rho)[NSS]) {
+    const phy_dims_t& d = p.d;
+    const uint32_t lkv = d.pdc_lk[q], l = lkv >> 16, k = lkv & 0xffffu;
+    float2 H[NSS][NRX];   // H[s][a]: stream s seen by antenna a
+#pragma unroll
+    for (int s = 0; s < NSS; ++s) chan_est_rx<NRX>(p, pkt, d.pdc_plan[q * NSS + s], k, H[s]);
+    float2 y[NRX];
+#pragma unroll
+    for (int a = 0; a < NRX; ++a) y[a] = __ldcs(&p.Y[(((size_t)pkt * NRX + a) * d.N_DF + (l - 1)) * d.Nk + k]);
+    float2 L[NSS][NSS], b[NSS];   // lower triangle; after the factorisation the diagonal holds 1 / L_jj in .x
+    float g[NSS];
+#pragma unroll
+    for (int i = 0; i < NSS; ++i) {
+#pragma unroll
+        for (int j = 0; j <= i; ++j) {
+            float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int a = 0; a < NRX; ++a) acc = cadd(acc, cmulc(H[j][a], H[i][a]));   // conj(H[a][i]) H[a][j]
+            L[i][j] = acc;
+        }
+        float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int a = 0; a < NRX; ++a) acc = cadd(acc, cmulc(y[a], H[i][a]));
+        b[i] = acc;
+        g[i] = L[i][i].x;
+    }
+#pragma unroll
+    for (int j = 0; j < NSS; ++j) {
+        float dj = L[j][j].x;
+#pragma unroll
+        for (int c = 0; c < j; ++c) dj -= L[j][c].x * L[j][c].x + L[j][c].y * L[j][c].y;
+        const float fl = 1.0e-6f * g[j] + 1.0e-30f;
+        if (!(dj > fl)) dj = fl;
+        const float inv = 1.0f / sqrtf(dj);
+        L[j][j] = make_float2(inv, 0.f);
+#pragma unroll
+        for (int i = j + 1; i < NSS; ++i) {
+            float2 acc = L[i][j];
+#pragma unroll
+            for (int c = 0; c < j; ++c) acc = csub(acc, cmulc(L[i][c], L[j][c]));
+            L[i][j] = make_float2(acc.x * inv, acc.y * inv);
+        }
+    }
+    // M = L^-1 column by column, kept in the upper triangle of the same array: M(i, j) -> L[j][i] for i > j
+    float2 z[NSS];
+#pragma unroll
+    for (int j = 0; j < NSS; ++j) {
+#pragma unroll
+        for (int i = j + 1; i < NSS; ++i) {
+            float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+            for (int c = j; c < i; ++c) acc = cadd(acc, cmul(L[i][c], c == j ? L[j][j] : L[j][c]));
+            const float s = -L[i][i].x;
+            L[j][i] = make_float2(acc.x * s, acc.y * s);
+        }
+    }
+#pragma unroll
+    for (int i = 0; i < NSS; ++i) {
+        float2 acc = make_float2(0.f, 0.f);
+#pragma unroll
+        for (int c = 0; c <= i; ++c) acc = cadd(acc, cmul(c == i ? L[i][i] : L[c][i], b[c]));
+        z[i] = acc;
+    }
+#pragma unroll
+    for (int i = 0; i < NSS; ++i) {
+        float2 acc = make_float2(0.f, 0.f);
+        float v = 0.f;
+#pragma unroll
+        for (int c = i; c < NSS; ++c) {
+            const float2 m = c == i ? L[i][i] : L[i][c];   // M(c, i)
+            acc = cadd(acc, cmulc(z[c], m));
+            v += m.x * m.x + m.y * m.y;
+        }
+        x[i] = acc;
+        const float r = 1.0f / (v * g[i] + 1.0e-30f);
+        rho[i] = r < 1.0f ? r : 1.0f;
+    }
+}
+
+// reference loss of every packet: one block per packet over the cells 0, 8, 16, ...; fixed summation tree
+template <int NSS, int NRX>
+__global__ void __launch_bounds__(128) k_rx_sm_ref(const rx_params_t p) {
+    __shared__ float2 s_red[4];
+    const uint32_t pkt = blockIdx.x;
+    const uint32_t n_sub = (p.d.N_PDC_subc + 7) / 8;
+    float sum = 0.f;
+    for (uint32_t i = threadIdx.x; i < n_sub; i += blockDim.x) {
+        float2 x[NSS];
+        float rho[NSS];
+        sm_solve<NSS, NRX>(p, pkt, 8 * i, x, rho);
+#pragma unroll
+        for (int s = 0; s < NSS; ++s) sum += rho[s];
+    }
+    const float2 t = block_sum2(make_float2(sum, 0.f), s_red);
+    if (threadIdx.x == 0) p.state[pkt].sm_rho_ref = t.x / (float)(n_sub * NSS);
+}
+
+template <int NSS, int NRX>
+__global__ void __launch_bounds__(128) k_rx_demap_sm(const rx_params_t p) {
+    extern __shared__ uint32_t s_sm[];   // [128][NSS * N_bps / 2] packed LLR pairs
+    const phy_dims_t& d = p.d;
+    const uint32_t pkt = blockIdx.y, N_bps = d.N_bps;
+    const uint32_t q = blockIdx.x * blockDim.x + threadIdx.x;
+    const uint32_t W = NSS * N_bps / 2;   // words per cell (N_SS is even)
+    if (q < d.N_PDC_subc) {
+        float2 x[NSS];
+        float rho[NSS];
+        sm_solve<NSS, NRX>(p, pkt, q, x, rho);
+        const float ref = p.state[pkt].sm_rho_ref;
+        const float inv = 1.0f / (ref > 1.0e-12f ? ref : 1.0e-12f);
+        int16_t* so = reinterpret_cast<int16_t*>(s_sm + threadIdx.x * W);
+#pragma unroll
+        for (int s = 0; s < NSS; ++s) {
+            uint32_t w[5];
+            demap_cell(x[s], N_bps, w);
+            float wt = rho[s] * inv;
+            wt = wt < 4.0f ? wt : 4.0f;
+#pragma unroll
+            for (uint32_t e = 0; e < 10; ++e)
+                if (e < N_bps) {
+                    const int16_t raw = (int16_t)((w[e >> 1] >> (16 * (e & 1))) & 0xffffu);
+                    so[s * N_bps + e] = (int16_t)to_short(wt * (float)raw);
+                }
+        }
+    }
+    __syncthreads();
+    const uint32_t q0 = blockIdx.x * blockDim.x;
+    const uint32_t n_here = min(blockDim.x, d.N_PDC_subc > q0 ? d.N_PDC_subc - q0 : 0u);
+    uint32_t* out32 = reinterpret_cast<uint32_t*>(p.llr + (size_t)pkt * p.llr_stride) + (size_t)q0 * W;
+    for (uint32_t i = threadIdx.x; i < n_here * W; i += blockDim.x) __stcs(&out32[i], s_sm[i]);
+}
+
+template <int NSS, int NRX>
+static cudaError_t launch_sm(const rx_params_t& p, uint32_t n_packets, cudaStream_t st) {
+    k_rx_sm_ref<NSS, NRX><<<n_packets, 128, 0, st>>>(p);
+    const size_t smem = 128 * (size_t)(NSS * p.d.N_bps / 2) * sizeof(uint32_t);   // at most 20 KiB
+    k_rx_demap_sm<NSS, NRX><<<dim3((p.d.N_PDC_subc + 127) / 128, n_packets), 128, smem, st>>>(p);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_rx_demap(const rx_params_t& p, uint32_t n_packets, bool pcc, cudaStream_t st) {
+    if (!pcc && p.d.N_SS > 1) {
+        // more streams than receive antennas cannot be separated; N_RX = N_TX of the largest packet in the reference
+        // (rx_synced.cpp:74), so this only triggers on a hand-made configuration
+        if (p.d.N_RX < p.d.N_SS) return cudaErrorInvalidValue;
+        switch (p.d.N_SS * 16 + p.d.N_RX) {
+            case 2 * 16 + 2: return launch_sm<2, 2>(p, n_packets, st);
+            case 2 * 16 + 4: return launch_sm<2, 4>(p, n_packets, st);
+            case 2 * 16 + 8: return launch_sm<2, 8>(p, n_packets, st);
+            case 4 * 16 + 4: return launch_sm<4, 4>(p, n_packets, st);
+            case 4 * 16 + 8: return launch_sm<4, 8>(p, n_packets, st);
+            case 8 * 16 + 8: return launch_sm<8, 8>(p, n_packets, st);
+            default: return cudaErrorInvalidValue;
+        }
+    }
     const uint32_t n_cells = pcc ? 98u : p.d.N_PDC_subc;
     const uint32_t units = p.d.N_eff_TX == 1 ? n_cells : n_cells / 2;
     const dim3 grid((units + 127) / 128, n_packets);

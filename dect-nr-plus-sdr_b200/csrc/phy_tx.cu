@@ -12,11 +12,11 @@ namespace dnrp {
 
 // LTE Gray mapping, TS 36.211 7.1 (srsRAN lte_tables.c; reference fix/mod.cpp:137-174), bits MSB first
 __device__ __forceinline__ float2 qam_symbol(const uint8_t* __restrict__ bits, uint32_t off, uint32_t N_bps) {
-    // N_bps <= 8 bits span at most two bytes: one 16-bit window instead of a byte load per bit (the second byte is
-    // only touched when the symbol straddles it)
-    const uint32_t b = off >> 3;
-    const uint32_t win = ((uint32_t)bits[b] << 8) | ((off & 7) + N_bps > 8 ? (uint32_t)bits[b + 1] : 0u);
-    const uint32_t v = (win >> (16 - (off & 7) - N_bps)) & ((1u << N_bps) - 1u);
+    // N_bps <= 10 bits span at most three bytes: one 24-bit window instead of a byte load per bit (a later byte is
+    // only touched when the symbol reaches into it)
+    const uint32_t b = off >> 3, end = (off & 7) + N_bps;
+    const uint32_t win = ((uint32_t)bits[b] << 16) | (end > 8 ? (uint32_t)bits[b + 1] << 8 : 0u) | (end > 16 ? (uint32_t)bits[b + 2] : 0u);
+    const uint32_t v = (win >> (24 - end)) & ((1u << N_bps) - 1u);
     if (N_bps == 1) {
         const float a = v ? -0.70710678118654752f : 0.70710678118654752f;
         return make_float2(a, a);
@@ -34,8 +34,10 @@ __device__ __forceinline__ float2 qam_symbol(const uint8_t* __restrict__ bits, u
     const float c0 = (float)(1u << (half - 1));
     re = (((v >> (N_bps - 1)) & 1u) ? -1.f : 1.f) * (c0 - re);
     im = (((v >> (N_bps - 2)) & 1u) ? -1.f : 1.f) * (c0 - im);
+    // half == 5: 1024-QAM (MCS 10, 11), outside the reference (tx.cpp:53-60) -- own extension, 1 / sqrt(682)
     const float norm = half == 1 ? 0.70710678118654752f
-                                 : (half == 2 ? 0.31622776601683794f : (half == 3 ? 0.15430334996209191f : 0.07669649888473704f));
+                     : (half == 2 ? 0.31622776601683794f
+                     : (half == 3 ? 0.15430334996209191f : (half == 4 ? 0.07669649888473704f : 0.03829197905337418f)));
     return make_float2(re * norm, im * norm);
 }
 

@@ -165,8 +165,15 @@ int build_phy_plan(dnrp_ctx* c) {
             }
             return t;
         };
+        // spatial multiplexing: every cell carries all N_SS streams, one plan word per (cell, stream)
+        auto build_sm = [&](const std::vector<uint32_t>& lk) {
+            std::vector<uint32_t> t(lk.size() * (size_t)d.N_SS, 0u);
+            for (size_t q = 0; q < lk.size(); ++q)
+                for (uint32_t s_ = 0; s_ < d.N_SS; ++s_) t[q * d.N_SS + s_] = plan_word(s_, lk[q] >> 16, false);
+            return t;
+        };
         UP(c->d_pcc_plan.upload(build(m.pcc_lk, true)));
-        UP(c->d_pdc_plan.upload(build(m.pdc_lk, false)));
+        UP(c->d_pdc_plan.upload(d.N_SS > 1 ? build_sm(m.pdc_lk) : build(m.pdc_lk, false)));
     }
     static const double nu_max[3] = {100.0, 100.0, 500.0}, tau_rms[3] = {0.1e-6, 0.1e-6, 1.0e-6},
                         snr_db[3] = {-5.0, 15.0, 35.0};

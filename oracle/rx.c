@@ -222,6 +222,7 @@ orc_wiener_t* orc_wiener_build(int b, int u, int N_step_virtual, double nu_max_h
 typedef struct {
     int32_t b, u, N_eff_TX, N_RX, N_os, cp_os, stf_cp_os, n_pat;
     int32_t N_DF, N_bps, chestim_lr, stride, n_pdc, literal_neff8;
+    int32_t N_SS;              /* spatial streams of the PDC (1 = MRC / transmit diversity like the reference) */
     const int8_t* stf_sign;   /* [Nk] sign s of the STF cell value s*(1+j)/sqrt(2), 0 = no STF cell */
     const uint8_t* cell_type;  /* [(N_DF+1)][Nk] 0 none, 1 DRS, 2 PCC, 3 PDC */
     const int8_t* cell_ts;     /* DRS cells: transmit stream */
@@ -258,6 +259,7 @@ typedef struct {
     float sto_inc;
     int PCC_idx, PDC_subc_idx, PDC_bits_idx;
     int16_t* llr_pcc; int16_t* llr_pdc;
+    float* sm_rho;       /* [n_pdc][N_SS] spatial multiplexing: loss of every (cell, stream) against the matched filter bound */
     cf_t* Y_out;         /* optional [N_RX][N_DF][Nk] */
     cf_t* H_out;         /* optional [N_RX][N_eff_TX][N_DF][Nk]: chestim at the time symbol l was collected */
     orc_rx_report_t* rep;
@@ -483,7 +485,20 @@ static int abs_i(int v) { return v < 0 ? -v : v; }
 
 static void demap(cf_t z, int N_bps, int16_t* out) {
     const float SCALE_QPSK = 100.f, SCALE_16 = 400.f, SCALE_64 = 700.f, SCALE_256 = 1000.f;
+    /* 1024-QAM (MCS 10, 11) has no srsRAN counterpart (tx.cpp:53-60 stops at 256-QAM): own extension of the same
+     * recursion, scale 1300 continuing 100 sqrt(2) / 400 / 700 / 1000, thresholds 16, 8, 4, 2 over sqrt(682) */
+    const float SCALE_1024 = 1300.f;
     switch (N_bps) {
+        case 10: {
+            const int16_t yre = to_short(SCALE_1024 * z.re), yim = to_short(SCALE_1024 * z.im);
+            out[0] = neg_short(yre); out[1] = neg_short(yim);
+            out[2] = to_short((float)abs_i(yre) - 16.f * SCALE_1024 / sqrtf(682.f));
+            out[3] = to_short((float)abs_i(yim) - 16.f * SCALE_1024 / sqrtf(682.f));
+            for (int i = 4, t = 8; i < 10; i += 2, t /= 2) {
+                out[i] = to_short((float)abs_i(out[i - 2]) - (float)t * SCALE_1024 / sqrtf(682.f));
+                out[i + 1] = to_short((float)abs_i(out[i - 1]) - (float)t * SCALE_1024 / sqrtf(682.f));
+            }
+        } break;
         case 1: out[0] = to_short(-(SCALE_QPSK * (z.re + z.im) * (float)M_SQRT1_2)); break;
         case 2:
             out[0] = to_short(z.re * (-SCALE_QPSK * sqrtf(2.f)));
@@ -562,6 +577,93 @@ static void combine_cells(rxs_t* s, const int32_t* k, int n, int PXX_idx, cf_t* 
     }
 }
 
+/* Spatial multiplexing (transmission modes 2, 4, 6, 8, 9, 11).  The reference has only a stub here
+ * (rx_synced.cpp:1331-1333 run_pdc_mode_AxA_MIMO, "todo"), so this is the repo's OWN specification (DESIGN.md
+ * "Spatial multiplexing receive"), restated sequentially: per cell zero-forcing through the Cholesky factor of
+ * A = H^H H, every stream's LLRs weighted by rho_s = 1 / ([A^-1]_ss A_ss) in (0, 1], the loss against the matched
+ * filter bound; rho = 1 for orthogonal columns, where the result equals the reference's MRC arithmetic.
+ * Stream s of cell q owns the LLRs (q N_SS + s) N_bps ... (tx.cpp:1054-1060 layer order). */
+static void detect_sm(rxs_t* s, const int32_t* k, int n, int PDC_idx) {
+    const orc_rx_cfg_t* c = s->c;
+    const int N = c->N_SS, R = c->N_RX;
+    for (int i = 0; i < n; ++i) {
+        cf_t A[8][8], L[8][8], M[8][8], b[8], z[8], x[8];
+        float g[8];
+        for (int p = 0; p < N; ++p) {
+            for (int q = 0; q <= p; ++q) {
+                cf_t acc = cf(0, 0);
+                for (int a = 0; a < R; ++a)   /* conj(H[a][p]) H[a][q] */
+                    acc = cf_add(acc, cf_mulc(s->chestim[((long)a * 8 + q) * s->Nk + k[i]], s->chestim[((long)a * 8 + p) * s->Nk + k[i]]));
+                A[p][q] = acc;
+            }
+            cf_t acc = cf(0, 0);
+            for (int a = 0; a < R; ++a) acc = cf_add(acc, cf_mulc(s->now[a][k[i]], s->chestim[((long)a * 8 + p) * s->Nk + k[i]]));
+            b[p] = acc;
+            g[p] = A[p][p].re;
+        }
+        for (int j = 0; j < N; ++j) {
+            float d = A[j][j].re;
+            for (int q = 0; q < j; ++q) d -= L[j][q].re * L[j][q].re + L[j][q].im * L[j][q].im;
+            const float floor_ = 1.0e-6f * g[j] + 1.0e-30f;
+            if (!(d > floor_)) d = floor_;
+            const float inv = 1.0f / sqrtf(d);
+            L[j][j] = cf(inv, 0);   /* the diagonal is kept as its reciprocal */
+            for (int p = j + 1; p < N; ++p) {
+                cf_t acc = A[p][j];
+                for (int q = 0; q < j; ++q) acc = cf_sub(acc, cf_mulc(L[p][q], L[j][q]));
+                L[p][j] = cf_scale(acc, inv);
+            }
+        }
+        for (int j = 0; j < N; ++j) {   /* M = L^-1, column by column */
+            M[j][j] = L[j][j];
+            for (int p = j + 1; p < N; ++p) {
+                cf_t acc = cf(0, 0);
+                for (int q = j; q < p; ++q) acc = cf_add(acc, cf_mul(L[p][q], M[q][j]));
+                M[p][j] = cf_scale(acc, -L[p][p].re);
+            }
+        }
+        for (int p = 0; p < N; ++p) {
+            cf_t acc = cf(0, 0);
+            for (int q = 0; q <= p; ++q) acc = cf_add(acc, cf_mul(M[p][q], b[q]));
+            z[p] = acc;
+        }
+        for (int p = 0; p < N; ++p) {
+            cf_t acc = cf(0, 0);
+            float v = 0.f;
+            for (int q = p; q < N; ++q) {   /* conj(M[q][p]) z[q] */
+                acc = cf_add(acc, cf_mulc(z[q], M[q][p]));
+                v += M[q][p].re * M[q][p].re + M[q][p].im * M[q][p].im;
+            }
+            x[p] = acc;
+            float rho = 1.0f / (v * g[p] + 1.0e-30f);
+            if (!(rho < 1.0f)) rho = 1.0f;
+            /* unweighted LLRs now, the weights once the packet's reference loss is known (finish_sm) */
+            demap(x[p], c->N_bps, s->llr_pdc + ((long)(PDC_idx + i) * N + p) * c->N_bps);
+            s->sm_rho[(long)(PDC_idx + i) * N + p] = rho;
+        }
+    }
+}
+
+/* second half of the spatial multiplexing specification: the packet's reference loss is the mean of rho over every
+ * 8th cell (all streams); each LLR is weighted by min(rho / rho_ref, 4) and truncated.  A flat channel (one rho for
+ * the whole packet) therefore keeps the demapper's own scale, which is what the decoder's +-1023 input range expects. */
+static void finish_sm(rxs_t* s) {
+    const orc_rx_cfg_t* c = s->c;
+    const int N = c->N_SS;
+    float sum = 0.f;
+    int cnt = 0;
+    for (int q = 0; q < c->n_pdc; q += 8)
+        for (int p = 0; p < N; ++p) { sum += s->sm_rho[(long)q * N + p]; ++cnt; }
+    const float ref = sum / (float)cnt;
+    const float inv = 1.0f / (ref > 1.0e-12f ? ref : 1.0e-12f);
+    for (long i = 0; i < (long)c->n_pdc * N; ++i) {
+        float w = s->sm_rho[i] * inv;
+        if (!(w < 4.0f)) w = 4.0f;
+        int16_t* out = s->llr_pdc + i * c->N_bps;
+        for (int e = 0; e < c->N_bps; ++e) out[e] = to_short(w * (float)out[e]);
+    }
+}
+
 static void snapshot_H(rxs_t* s, int l) {
     if (!s->H_out) return;
     const orc_rx_cfg_t* c = s->c;
@@ -590,13 +692,17 @@ static void run_pdc(rxs_t* s, int l) {
     int n = 0;
     while (s->PDC_subc_idx + n < c->n_pdc && c->pdc_l[s->PDC_subc_idx + n] == l) ++n;
     if (n == 0) return;
-    cf_t* z = (cf_t*)malloc(sizeof(cf_t) * n);
-    combine_cells(s, c->pdc_k + s->PDC_subc_idx, n, s->PDC_subc_idx, z);
-    for (int i = 0; i < n; ++i) demap(z[i], c->N_bps, s->llr_pdc + (long)(s->PDC_subc_idx + i) * c->N_bps);
-    free(z);
+    if (c->N_SS > 1) {
+        detect_sm(s, c->pdc_k + s->PDC_subc_idx, n, s->PDC_subc_idx);
+    } else {
+        cf_t* z = (cf_t*)malloc(sizeof(cf_t) * n);
+        combine_cells(s, c->pdc_k + s->PDC_subc_idx, n, s->PDC_subc_idx, z);
+        for (int i = 0; i < n; ++i) demap(z[i], c->N_bps, s->llr_pdc + (long)(s->PDC_subc_idx + i) * c->N_bps);
+        free(z);
+    }
     snapshot_H(s, l);
     s->PDC_subc_idx += n;
-    s->PDC_bits_idx += n * c->N_bps;
+    s->PDC_bits_idx += n * c->N_bps * (c->N_SS > 1 ? c->N_SS : 1);
 }
 
 static int is_drs_symbol(const rxs_t* s, int l) {
@@ -700,6 +806,7 @@ int orc_rx_packet(const orc_rx_cfg_t* c, const cf_t* iq, long iq_stride, int t0,
     s->zfi = (cf_t*)calloc((size_t)c->N_RX * 8 * 2 * s->NP, sizeof(cf_t));
     s->chestim = (cf_t*)calloc((size_t)c->N_RX * 8 * s->Nk, sizeof(cf_t));
     s->llr_pcc = llr_pcc; s->llr_pdc = llr_pdc; s->Y_out = Y_out; s->H_out = H_out;
+    if (c->N_SS > 1) s->sm_rho = (float*)calloc((size_t)c->n_pdc * c->N_SS, sizeof(float));
     for (int a = 0; a < 8; ++a) rep->rms[a] = rms_in ? rms_in[a] : 0.0f;
 
     /* ---- PCC */
@@ -728,6 +835,8 @@ int orc_rx_packet(const orc_rx_cfg_t* c, const cf_t* iq, long iq_stride, int t0,
     rep->snr_db_pdc = snr_db_now(s);
 
     const int ok = s->PCC_idx == 98 && s->PDC_subc_idx == c->n_pdc;
+    if (ok && c->N_SS > 1) finish_sm(s);
+    free(s->sm_rho);
     fft_free(s->fft);
     free(s->mixer_stage); free(s->fft_stage); free(s->stage); free(s->now); free(s->zf); free(s->zfi); free(s->chestim);
     return ok ? 0 : -1;

@@ -18,7 +18,7 @@ N_INTERP_L = (7, 4, 2)
 
 class _Cfg(C.Structure):
     _fields_ = [(n, C.c_int32) for n in ("b", "u", "N_eff_TX", "N_RX", "N_os", "cp_os", "stf_cp_os", "n_pat",
-                                         "N_DF", "N_bps", "chestim_lr", "stride", "n_pdc", "literal_neff8")] + \
+                                         "N_DF", "N_bps", "chestim_lr", "stride", "n_pdc", "literal_neff8", "N_SS")] + \
                [(n, C.c_void_p) for n in ("stf_sign", "cell_type", "cell_ts", "cell_sign", "pcc_l", "pcc_k",
                                           "pdc_l", "pdc_k")] + \
                [("lut_l", C.c_void_p * 3), ("lut_lr", C.c_void_p * 3)]
@@ -111,6 +111,7 @@ class RxConfig:
         c.n_pat = 7 if u == 1 else 9
         c.N_DF, c.N_bps, c.chestim_lr, c.stride, c.n_pdc = N_DF, ps["N_bps"], int(chestim_lr), stride, len(dl)
         c.literal_neff8 = int(literal_neff8)  # see rx.c run_pdc_ps_in_chestim_mode_lr_t
+        c.N_SS = ps["N_SS"]                   # > 1: spatial multiplexing, rx.c detect_sm (own specification)
         for name in ("stf_sign", "cell_type", "cell_ts", "cell_sign", "pcc_l", "pcc_k", "pdc_l", "pdc_k"):
             setattr(c, name, getattr(self, name).ctypes.data)
         for i in range(3):

@@ -7,6 +7,7 @@ FFT: the reference calls FFTW3f through srsran_dft (unnormalised c2c, no mirrori
 here numpy's double precision FFT is used and the result cast to complex64 -> "math-pinned", fp32
 tolerance applies to every IQ comparison.
 """
+import functools
 import math
 import numpy as np
 from . import fec, spec
@@ -15,11 +16,14 @@ from . import fec, spec
 # index = bits MSB first; used by reference tx.cpp:55-64 / fix/mod.cpp:137-174
 
 
+@functools.lru_cache(maxsize=None)
 def mod_table(N_bps):
+    # N_bps = 10 (1024-QAM, MCS 10/11) is outside the reference (tx.cpp:53-60 stops at 256-QAM): the same recursion one
+    # level deeper, normalised by sqrt(682) -- own extension, DESIGN.md "1024-QAM"
     if N_bps == 1:
         return np.array([(1 + 1j), (-1 - 1j)], dtype=np.complex128) / math.sqrt(2)
     half = N_bps // 2
-    norm = {1: 2.0, 2: 10.0, 3: 42.0, 4: 170.0}[half]
+    norm = {1: 2.0, 2: 10.0, 3: 42.0, 4: 170.0, 5: 682.0}[half]
     tab = np.zeros(1 << N_bps, dtype=np.complex128)
     for idx in range(1 << N_bps):
         bits = [(idx >> (N_bps - 1 - i)) & 1 for i in range(N_bps)]

@@ -21,6 +21,11 @@ TX_CASES = {
     "b12_siso_256qam": dict(cfg=(4, 12, 0, 3, 0, 9, 6144)),
     "bpsk_b1_os2": dict(cfg=(1, 1, 1, 2, 0, 0, 2048), os=2),
     "b8_os4_mix": dict(cfg=(1, 8, 0, 1, 0, 5, 6144), os=4, iq_phase_rad=0.3, iq_phase_increment=0.0123, DAC_scale=0.5),
+    # 1024-QAM (MCS 10 / 11): outside the reference (tx.cpp:53-60), own extension of the modulation recursion
+    "b2_siso_1024qam_mcs10": dict(cfg=(1, 2, 1, 2, 0, 10, 2048)),
+    "txdiv2_b1_1024qam_mcs11": dict(cfg=(1, 1, 1, 3, 1, 11, 2048)),
+    "mimo4x4_b2_cb3": dict(cfg=(1, 2, 1, 2, 9, 3, 2048), codebook_index=3),
+    "mimo8x8_b1": dict(cfg=(1, 1, 1, 6, 11, 2, 2048)),
 }
 
 
