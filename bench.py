@@ -40,6 +40,10 @@ WORKLOADS = {
     "C2_mu1_b16_siso_64qam_r56_awgn25": dict(psdef=(1, 16, 1, 1, 0, 7, 6144), N_RX=1, snr_dB=25.0, mode=0),
     "C3_mu1_b16_txdiv4_64qam_r56_flat25": dict(psdef=(1, 16, 1, 2, 5, 7, 6144), N_RX=4, snr_dB=25.0, mode=1),
     "C1_mu1_b1_siso_qpsk_awgn10": dict(psdef=(1, 1, 1, 1, 0, 2, 2048), N_RX=1, snr_dB=10.0, mode=0),
+    # spatial multiplexing, 4 layers (transmission mode 6): per-cell 4x4 solves in k_rx_demap_sm.  The reference's receiver
+    # stops at a stub for N_SS > 1 (rx_synced.cpp:1331-1333), so the CPU arm of this workload is the oracle port.
+    "TM6_mu1_b16_sm4x4_16qam_r34_tdl_doubly_1_100_50_snr30":
+        dict(psdef=(1, 16, 1, 2, 6, 4, 6144), N_RX=4, snr_dB=30.0, mode=2, pdp_idx=1, tau_rms_ns=100.0, fD_Hz=50.0),
 }
 DEFAULT_WORKLOAD = "C3_mu1_b16_txdiv4_4x4_64qam_r56_tdl_doubly_1_100_50_snr25"
 NETWORK_ID = 123456789
@@ -129,7 +133,9 @@ class CpuReceiver:
         from oracle import ref
         self.workload, self.threads = workload, threads
         self.w = WORKLOADS[workload]
-        self.kind = "reference" if ref.available() else "port"
+        from oracle import spec as ospec
+        sm = ospec.get_packet_sizes(*self.w["psdef"])["N_SS"] > 1   # no reference receiver exists for these modes
+        self.kind = "reference" if ref.available() and not sm else "port"
         if self.kind == "reference":
             t0 = time.perf_counter()
             self.pool = ref.Pool(self.w["psdef"], n_window, threads, network_id=NETWORK_ID)
@@ -187,7 +193,8 @@ class CpuReceiver:
             return ("oracle/_ref: the reference's own sync_chunk_t + rx_synced_t + fec_t sources compiled for this host "
                     "(x86-64-v3, asserts on), its third-party SIMD libraries (srsRAN turbo decoder, VOLK, FFTW) replaced "
                     "by plain-C stand-ins -- slower per core than a build against the real libraries")
-        return "CPU restatement (oracle/, scalar C) of the reference algorithms; oracle/_ref is not built on this box"
+        return ("CPU restatement (oracle/, scalar C) of the reference algorithms; oracle/_ref is not built on this box or "
+                "the workload is spatial multiplexing, which the reference's receiver does not implement")
 
 
 def run_reference(args):

@@ -350,6 +350,21 @@ class Phy:
                                       out.ctypes.data_as(C.c_void_p), C.byref(n_out)))
         return out[:n_out.value].view(np.recarray)
 
+    def stream_open(self, max_push_samples, chunk_hop=0):
+        _check(lib().dnrp_stream_open(self._ctx, int(max_push_samples), int(chunk_hop)))
+
+    def stream_push(self, iq, max_out=256):
+        """iq [N_RX][n] complex64 hardware-rate samples (n may be 0) -> the packets complete after this push"""
+        iq = np.ascontiguousarray(iq, dtype=np.complex64).reshape(self.N_RX, -1)
+        out = np.zeros(max_out, dtype=STREAM_PACKET_DTYPE)
+        n_out = C.c_uint32(0)
+        _check(lib().dnrp_stream_push(self._ctx, iq.shape[1], _ptr(iq, np.complex64) if iq.shape[1] else None, int(max_out),
+                                      out.ctypes.data_as(C.c_void_p), C.byref(n_out)))
+        return out[:n_out.value].view(np.recarray)
+
+    def stream_close(self):
+        _check(lib().dnrp_stream_close(self._ctx))
+
     def stream_extract(self, start_64, t0):
         """windows of the synced receiver <- stream[start - t0, start - t0 + rx_stride) for every start (device copy)"""
         start = np.ascontiguousarray(start_64, dtype=np.int64)

@@ -179,7 +179,30 @@ struct dnrp_ctx {
     dnrp::dbuf<float2> d_stream_c, d_stream_xc;
     dnrp::dbuf<float> d_stream_p;
     dnrp::dbuf<dnrp::sync_result_dev_t> d_stream_result;
-    dnrp::dbuf<uint32_t> d_stream_resume;
+    dnrp::dbuf<uint32_t> d_stream_resume, d_stream_limit, d_stream_map;
+    // what dnrp_stream_extract reads: the one-shot stream above or the ring of the stateful front door below
+    struct stream_view_t {
+        const float2* p = nullptr;   // [N_RX][stride] hardware-rate samples
+        size_t stride = 0, len = 0;  // antenna stride, valid samples per antenna
+        int64_t base = 0;            // absolute index of element 0
+    } stream_view;
+    // stateful streaming front door (dnrp_stream_open / _push): hardware-rate ring, the same stream at the DECT rate
+    // (x oversampling) when L != M, search cursor, packets found but not yet complete
+    struct stream_state_t {
+        bool open = false;
+        uint32_t hop = 0, lead = 0, tail = 0, Q = 0, len = 0;   // DECT-rate samples; Q = grid of chunk starts
+        uint32_t max_push = 0, max_chunks = 0;
+        size_t cap_hw = 0, cap_rs = 0;
+        int cur = 0;
+        dnrp::dbuf<float2> hw[2], rs[2];
+        int64_t hw_base = 0, rs_base = 0;    // absolute index of element 0 of the current buffers
+        size_t hw_len = 0, rs_len = 0;       // samples held per antenna
+        int64_t search_from = 0;             // absolute DECT-rate index of the next detection position
+        int64_t carry_resume = 0;            // skip_after_peak of the last packet, when it reaches behind search_from
+        int64_t last_fine = INT64_MIN / 2;   // baton_t::is_sync_time_unique across pushes
+        bool first = true;
+        std::vector<dnrp_stream_packet_t> pending;
+    } ss;
 
     // measurement: launch counter and optional per-kernel event timers (dnrp_kernel_time_*)
     uint64_t launches = 0;

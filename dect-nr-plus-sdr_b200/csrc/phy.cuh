@@ -188,7 +188,11 @@ struct sync_params_t {
     size_t iq_pkt_stride, x_pkt_stride;
     const uint32_t* resume;                // [packet] optional: first sample the detection may end on (skip_after_peak);
                                            // 0xffffffff = chunk finished
+    const uint32_t* limit;                 // [packet] optional: end of the chunk's detection range (else search_length)
+    const uint32_t* chunk_map;             // optional: block i of the search kernels works on chunk chunk_map[i] (the
+                                           // chunks still active in a continuation round)
 };
+__device__ __forceinline__ uint32_t sync_chunk(const sync_params_t& p, uint32_t i) { return p.chunk_map ? p.chunk_map[i] : i; }
 // first sample of antenna a of window / chunk pkt
 __device__ __forceinline__ const float2* sync_iq(const sync_params_t& p, uint32_t pkt, uint32_t a) {
     return p.iq + (p.iq_pkt_stride ? (size_t)pkt * p.iq_pkt_stride + (size_t)a * p.iq_stride
@@ -199,6 +203,12 @@ __device__ __forceinline__ const float2* sync_iq_x(const sync_params_t& p, uint3
                                     : ((size_t)pkt * p.d.N_RX + a) * p.x_stride);
 }
 cudaError_t launch_sync(const sync_params_t& p, uint32_t n_packets, cudaStream_t st);
+// the two halves of launch_sync: per-step sums of every window (independent of resume / limit), and detection -> coarse
+// peak -> fine peak over n_active windows (all of them, or the ones listed in chunk_map)
+cudaError_t launch_sync_steps(const sync_params_t& p, uint32_t n_packets, cudaStream_t st);
+cudaError_t launch_sync_search(const sync_params_t& p, uint32_t n_active, cudaStream_t st);
+// dynamic shared memory k_sync_peak needs for n_steps detection steps (bounded by the device's opt-in limit)
+size_t sync_peak_smem(const phy_dims_t& d, uint32_t n_steps);
 
 // simulation channel (phy_channel.cu)
 struct chan_meta_dev_t {

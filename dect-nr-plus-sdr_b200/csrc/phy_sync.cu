@@ -70,7 +70,7 @@ __global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32
     __shared__ uint32_t s_min;
     __shared__ unsigned long long s_best;
     const phy_dims_t& d = p.d;
-    const uint32_t pkt = blockIdx.x, tid = threadIdx.x, nthr = blockDim.x;
+    const uint32_t pkt = sync_chunk(p, blockIdx.x), tid = threadIdx.x, nthr = blockDim.x;
     const uint32_t n_pat = d.n_pat, pat = d.pat_len_os, stf_len = d.stf_len_os, step = p.step;
     const uint32_t W = 4 * n_pat, Wc = 4 * (n_pat - 1);
     const float prefactor = (float)n_pat / (float)(n_pat - 1);
@@ -79,6 +79,7 @@ __global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32
     float uw[8];
     for (uint32_t i = 0; i + 1 < n_pat; ++i) uw[i] = c_cover[i] * c_cover[i + 1];
 
+    const uint32_t search_length = p.limit ? p.limit[pkt] : p.search_length;
     uint32_t j_from = (stf_len + pat + step - 1) / step - 1;  // first step whose end reaches ignore_before_index
     if (p.resume) {  // continuation inside a chunk: autocorrelator_detection_t::skip_after_peak moved ignore_before_index
         const uint32_t r = p.resume[pkt];
@@ -112,7 +113,7 @@ __global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32
             block_scan(Pi + 1, p.n_steps, s_part);
             for (uint32_t j = j_from + tid; j < p.n_steps; j += nthr) {
                 const uint32_t n = (j + 1) * step;
-                if (n - step >= p.search_length || n > len || j + 1 < W) continue;
+                if (n - step >= search_length || n > len || j + 1 < W) continue;
                 const float power = (float)(Pp[j + 1] - Pp[j + 1 - W]);
                 const float rms = sqrtf(power / (float)stf_len);
                 if (rms < p.rms_min || 2.0f < rms) continue;
@@ -325,7 +326,7 @@ __global__ void __launch_bounds__(XC_THREADS) k_sync_xcorr(const sync_params_t p
     extern __shared__ float2 smem_x[];
     __shared__ unsigned long long s_best;
     const phy_dims_t& d = p.d;
-    const uint32_t tpl = blockIdx.x, pkt = blockIdx.y, tid = threadIdx.x;
+    const uint32_t tpl = blockIdx.x, pkt = sync_chunk(p, blockIdx.y), tid = threadIdx.x;
     const uint32_t S = p.xc_S, sl = p.xc_sl, n_lag = 2 * sl + 1;  // 16 b os L/M samples to either side
     const uint32_t LT = (n_lag + XC_LAGS - 1) / XC_LAGS, n_lag_pad = LT * XC_LAGS;
     const sync_result_dev_t& res = p.result[pkt];
@@ -413,7 +414,7 @@ __global__ void __launch_bounds__(XF_THREADS, 3) k_sync_xcorr_fft(const sync_par
     extern __shared__ __align__(16) float2 smem_f[];
     __shared__ unsigned long long s_best;
     const phy_dims_t& d = p.d;
-    const uint32_t pkt = blockIdx.x, tid = threadIdx.x, N = p.xc_fft_n;
+    const uint32_t pkt = sync_chunk(p, blockIdx.x), tid = threadIdx.x, N = p.xc_fft_n;
     const uint32_t S = p.xc_S, sl = p.xc_sl, n_lag = 2 * sl + 1, n_mix = n_lag + S - 1;
     const sync_result_dev_t& res = p.result[pkt];
     const long long w0 = (long long)res.coarse_peak_time_hw - sl;
@@ -474,8 +475,9 @@ __global__ void __launch_bounds__(XF_THREADS, 3) k_sync_xcorr_fft(const sync_par
 
 // ---- N_eff_TX decision, fine peak, hand-over to the synchronised receiver (crosscorrelator.cpp:205-249)
 __global__ void k_sync_final(const sync_params_t p, uint32_t n, uint32_t len) {
-    const uint32_t pkt = blockIdx.x * blockDim.x + threadIdx.x;
-    if (pkt >= n) return;
+    const uint32_t idx = blockIdx.x * blockDim.x + threadIdx.x;
+    if (idx >= n) return;
+    const uint32_t pkt = sync_chunk(p, idx);
     sync_result_dev_t& res = p.result[pkt];
     const uint32_t sl = p.xc_sl;
     if (res.detected) {
@@ -508,14 +510,28 @@ __global__ void k_sync_final(const sync_params_t p, uint32_t n, uint32_t len) {
     }
 }
 
+size_t sync_peak_smem(const phy_dims_t& d, uint32_t n_steps) {
+    const size_t sm_det = 3 * (size_t)(n_steps + 1) * sizeof(double);
+    const size_t sm_peak = (3 * (size_t)(2 * d.stf_len_os + 1) + d.stf_len_os) * sizeof(float);
+    return sm_det > sm_peak ? sm_det : sm_peak;
+}
+
+cudaError_t launch_sync_steps(const sync_params_t& p, uint32_t n, cudaStream_t st) {
+    if (n == 0) return cudaSuccess;
+    k_sync_steps<<<dim3((p.n_steps + 31) / 32, p.n_ant, n), 256, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_sync(const sync_params_t& p, uint32_t n, cudaStream_t st) {
+    cudaError_t e = launch_sync_steps(p, n, st);
+    return e != cudaSuccess ? e : launch_sync_search(p, n, st);
+}
+
+cudaError_t launch_sync_search(const sync_params_t& p, uint32_t n, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
     const phy_dims_t& d = p.d;
     const uint32_t len = p.len;
-    k_sync_steps<<<dim3((p.n_steps + 31) / 32, p.n_ant, n), 256, 0, st>>>(p);
-    const size_t sm_det = 3 * (size_t)(p.n_steps + 1) * sizeof(double);
-    const size_t sm_peak = (3 * (size_t)(2 * d.stf_len_os + 1) + d.stf_len_os) * sizeof(float);
-    const size_t sm2 = sm_det > sm_peak ? sm_det : sm_peak;
+    const size_t sm2 = sync_peak_smem(d, p.n_steps);
     cudaError_t e = cudaFuncSetAttribute(k_sync_peak, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
     if (e != cudaSuccess) return e;
     k_sync_peak<<<n, 256, sm2, st>>>(p, len);

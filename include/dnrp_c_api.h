@@ -222,7 +222,9 @@ int dnrp_sync_batch(dnrp_ctx_t* ctx, uint32_t n, const dnrp_cf32_t* iq_in, uint3
  * all chunks are searched in parallel; a chunk that found a packet continues behind it (skip_after_peak: 2 STFs) in
  * the next round until its detection range is used up; results are ordered by time and double detections closer than
  * one STF pattern to their predecessor are dropped (RX_SYNC_PARAM_SYNC_TIME_UNIQUE_LIMIT_IN_STF_PATTERNS_DP).
- * iq [N_RX][n_samples] host samples at the hardware rate (contexts without resampling only).  The stream stays on
+ * iq [N_RX][n_samples] host samples at the hardware rate (contexts without resampling only; dnrp_stream_push below
+ * handles any L / M).  A chunk_hop whose detection prefix sums exceed the device's shared memory is refused with
+ * DNRP_ERR_INVALID.  The stream stays on
  * the device for dnrp_stream_extract.  out [max_out]: times are sample indices of the stream. */
 typedef struct {
     int64_t fine_peak_time_64;         /* first sample of the packet (STF start) */
@@ -233,7 +235,25 @@ typedef struct {
 int dnrp_stream_sync(dnrp_ctx_t* ctx, uint64_t n_samples, const dnrp_cf32_t* iq, uint32_t chunk_hop, uint32_t max_out,
                      dnrp_stream_packet_t* out, uint32_t* n_out);
 
-/* rx_pacer_t hand-over to rx_synced_t for n packets found by dnrp_stream_sync: copies, per packet i, the samples
+/* The same search with state, for a radio that delivers its samples piece by piece (the reference's RX ring buffer,
+ * radio/buffer_rx.hpp, read by worker_sync_t chunk after chunk; resampling with carried history, rx_pacer.cpp:106-143,
+ * 265-327).  dnrp_stream_open sizes a ring on the device for pushes of up to max_push_samples hardware-rate samples per
+ * antenna (chunk_hop as above, in DECT-rate samples) and resets the stream clock; dnrp_stream_push appends
+ * iq [N_RX][n_samples], resamples the new part to the DECT rate when resample_L != resample_M (absolute phase: the
+ * result equals resampling the whole stream at once), searches every detection position whose coarse / fine peak
+ * range has fully arrived, and keeps for the next call: the detector's history, the unsearched tail, and the samples
+ * of packets whose end has not arrived.  out [max_out] receives, in time order, the packets that are COMPLETE (last
+ * sample of the packet including its guard interval is in the ring): times are hardware-rate sample indices counted
+ * from the first sample ever pushed; a packet found in one push may be handed out by a later one; complete packets
+ * beyond max_out stay queued (push with n_samples = 0 to drain).  dnrp_stream_extract reads the ring, so call it for
+ * the packets of one push before the next push.  Results do not depend on how the stream is cut into pushes, except
+ * for double detections within one STF pattern, which are dropped in either case. */
+int dnrp_stream_open(dnrp_ctx_t* ctx, uint32_t max_push_samples, uint32_t chunk_hop);
+int dnrp_stream_push(dnrp_ctx_t* ctx, uint32_t n_samples, const dnrp_cf32_t* iq, uint32_t max_out, dnrp_stream_packet_t* out,
+                     uint32_t* n_out);
+int dnrp_stream_close(dnrp_ctx_t* ctx);
+
+/* rx_pacer_t hand-over to rx_synced_t for n packets found by dnrp_stream_sync / dnrp_stream_push: copies, per packet i, the samples
  * [start_64[i] - t0, start_64[i] - t0 + dnrp_rx_stride()) of the device-resident stream into IQ window i (zeros
  * outside the stream).  dnrp_rx_pcc_batch(ctx, n, NULL, sync, ...) with sync[i].fine_peak_time_local = t0 continues. */
 int dnrp_stream_extract(dnrp_ctx_t* ctx, uint32_t n, const int64_t* start_64, uint32_t t0);

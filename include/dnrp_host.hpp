@@ -514,7 +514,41 @@ class batch_phy_t {
             std::vector<dnrp_stream_packet_t> found(max_out);
             uint32_t n_found = 0;
             check(dnrp_stream_sync(ctx, n_samples, stream, chunk_hop, max_out, found.data(), &n_found), "dnrp_stream_sync");
-            const uint32_t t0 = packet_sizes.N_samples_STF / 2;   // room in front of the packet inside its window
+            deliver_found(found.data(), n_found, stream_start_64, tpoint, tx_out);
+            return tx_out;
+        }
+
+        /// The same for a radio that delivers its samples piece by piece (radio/buffer_rx.hpp read chunk after chunk by
+        /// worker_sync_t, resampled with carried history by rx_pacer_t): open_stream sizes the ring on the device and
+        /// starts the stream clock at stream_start_64; every push_stream appends hardware-rate samples [N_RX][n_samples]
+        /// and hands every packet that is complete by then to the synced receiver and the firmware, in time order.
+        /// Works with and without resampling.
+        void open_stream(uint32_t max_push_samples, int64_t stream_start_64, uint32_t chunk_hop = 0) {
+            check(dnrp_stream_open(ctx, max_push_samples, chunk_hop), "dnrp_stream_open");
+            stream_clock_64 = stream_start_64;
+        }
+        machigh_phy_t::tx_descriptor_vec_t push_stream(uint32_t n_samples, const cf_t* samples, upper::tpoint_t& tpoint) {
+            machigh_phy_t::tx_descriptor_vec_t tx_out;
+            std::vector<dnrp_stream_packet_t> found(max_windows);
+            const cf_t* src = samples;
+            for (uint32_t n = n_samples;; n = 0, src = nullptr) {   // further rounds drain packets beyond max_windows
+                uint32_t n_found = 0;
+                check(dnrp_stream_push(ctx, n, src, max_windows, found.data(), &n_found), "dnrp_stream_push");
+                deliver_found(found.data(), n_found, stream_clock_64, tpoint, tx_out);
+                if (n_found < max_windows) break;
+            }
+            return tx_out;
+        }
+        void close_stream() { check(dnrp_stream_close(ctx), "dnrp_stream_close"); }
+
+    private:
+        int64_t stream_clock_64{0};
+
+        /// packets found in the device-resident stream -> receiver windows -> PCC -> firmware, max_windows per batch
+        void deliver_found(const dnrp_stream_packet_t* found, uint32_t n_found, int64_t stream_start_64, upper::tpoint_t& tpoint,
+                           machigh_phy_t::tx_descriptor_vec_t& tx_out) {
+            // room in front of the packet inside its window (the window has two hardware-rate STFs of slack)
+            const uint32_t t0 = packet_sizes.N_samples_STF / 2;
             for (uint32_t first = 0; first < n_found; first += max_windows) {
                 const uint32_t n = std::min(max_windows, n_found - first);
                 std::vector<int64_t> start(n), window_start(n);
@@ -540,10 +574,7 @@ class batch_phy_t {
                 stats.windows += n;
                 deliver(n, sres, pcc, window_start.data(), tpoint, tx_out);
             }
-            return tx_out;
         }
-
-    private:
         /// sync results + PCC reports of n windows -> work_pcc (FIFO) -> demoddecod_rx_pdc -> work_pdc / work_pdc_error
         void deliver(uint32_t n, const std::vector<dnrp_sync_result_t>& sres, const std::vector<dnrp_pcc_report_t>& pcc,
                      const int64_t* window_start_64, upper::tpoint_t& tpoint, machigh_phy_t::tx_descriptor_vec_t& tx_out) {

@@ -86,9 +86,20 @@ static const float COVER[9] = {1, -1, 1, 1, -1, -1, -1, -1, -1};  /* stf.hpp:146
  * the detection may consume (A + B of sync_chunk.hpp:108-124).  The cross-correlation runs on the hardware-rate
  * samples iq_hw [n_ant][stride_hw] (NULL: = iq, L = M = 1) against templates [n_tpl][tpl_len] that went through the
  * TX resampler (tpl_len = stf_len * L / M), hardware rate = DECT rate * L / M. */
+int orc_sync_search3(const cf_t* iq, long stride, int len, int n_ant, int u, int b, int os, const cf_t* templates,
+                     int n_tpl, int search_length, double samp_rate, const cf_t* iq_hw, long stride_hw, int len_hw,
+                     int L, int M, int tpl_len, int ignore_before_min, orc_sync_report_t* rep);
 int orc_sync_search2(const cf_t* iq, long stride, int len, int n_ant, int u, int b, int os, const cf_t* templates,
                      int n_tpl, int search_length, double samp_rate, const cf_t* iq_hw, long stride_hw, int len_hw,
                      int L, int M, int tpl_len, orc_sync_report_t* rep) {
+    return orc_sync_search3(iq, stride, len, n_ant, u, b, os, templates, n_tpl, search_length, samp_rate, iq_hw, stride_hw,
+                            len_hw, L, M, tpl_len, 0, rep);
+}
+/* ignore_before_min: the caller resumes a longer walk inside this window (autocorrelator_detection_t::skip_after_peak
+ * moved ignore_before_index, autocorrelator_detection.cpp:137-146): no detection may end before that sample */
+int orc_sync_search3(const cf_t* iq, long stride, int len, int n_ant, int u, int b, int os, const cf_t* templates,
+                     int n_tpl, int search_length, double samp_rate, const cf_t* iq_hw, long stride_hw, int len_hw,
+                     int L, int M, int tpl_len, int ignore_before_min, orc_sync_report_t* rep) {
     if (!iq_hw) { iq_hw = iq; stride_hw = stride; len_hw = len; L = M = 1; }
     const int bos = b * os;
     const int n_pat = u == 1 ? 7 : 9;
@@ -112,7 +123,7 @@ int orc_sync_search2(const cf_t* iq, long stride, int len, int n_ant, int u, int
             msf_pop_push(&mp[a], conj_dot(A, A, step).re);
         }
     cnt_r = pat;
-    int ignore_before = search_start;
+    int ignore_before = search_start > ignore_before_min ? search_start : ignore_before_min;
     while (cnt_r < search_length && !rep->detected) {
         /* ---- autocorrelator_detection_t::search_by_correlation, one step */
         if (cnt_r + step > len) break;

@@ -81,6 +81,74 @@ def search(iq, u, b, os=1, N_eff_TX_max=1, search_length=None, resample=(1, 1)):
     return rep
 
 
+def search_rs(iq_rs, iq_hw, u, b, os, N_eff_TX_max, search_length, resample, ignore_before=0):
+    """search() on a window that is already resampled (iq_rs at the DECT rate, iq_hw the same span at the hardware rate,
+    iq_rs sample r <-> iq_hw sample r L / M), detections ending before ignore_before suppressed"""
+    lb = lib()
+    L_, M_ = resample
+    iq_rs = np.ascontiguousarray(iq_rs, dtype=np.complex64)
+    iq_hw = np.ascontiguousarray(iq_hw, dtype=np.complex64)
+    tpl = np.ascontiguousarray(templates(u, b, N_eff_TX_max, os, L_, M_))
+    rep = Report()
+    lb.orc_sync_search3.restype = C.c_int
+    lb.orc_sync_search3.argtypes = [C.c_void_p, C.c_long, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+                                    C.c_int, C.c_int, C.c_double, C.c_void_p, C.c_long, C.c_int, C.c_int, C.c_int,
+                                    C.c_int, C.c_int, C.c_void_p]
+    rc = lb.orc_sync_search3(iq_rs.ctypes.data, iq_rs.shape[1], iq_rs.shape[1], iq_rs.shape[0], u, b, os, tpl.ctypes.data,
+                             tpl.shape[0], int(search_length), float(u * b * os * 1.728e6), iq_hw.ctypes.data,
+                             iq_hw.shape[1], iq_hw.shape[1], L_, M_, tpl.shape[1], int(ignore_before), C.addressof(rep))
+    if rc == -2:
+        rep.detected = 0
+    elif rc != 0:
+        raise RuntimeError("oracle sync failed (rc=%d)" % rc)
+    return rep
+
+
+def stream_search_resampled(iq_hw, u, b, os=1, N_eff_TX_max=1, resample=(10, 9), window=None):
+    """stream_search for a radio at L / M times the DECT rate: the WHOLE stream goes through the RX resampler once
+    (rx_pacer_t with carried history == one pass, no flush), one sync_chunk_t walks the resampled stream; the
+    cross-correlation runs on the hardware-rate stream around round(coarse L / M) (sync_chunk.cpp:204-205).  Windows
+    start on multiples of lcm(step, 2 M) so that their first sample is an integer hardware-rate sample; the position to
+    resume from is handed to the detector as ignore_before_index.  Returns [(fine_hw, coarse_hw, Report)]."""
+    import math
+    from . import resample as rs
+    L_, M_ = resample
+    iq_hw = np.ascontiguousarray(iq_hw, dtype=np.complex64)
+    iq = np.ascontiguousarray(np.stack([rs.stream(x, M_, L_, os, flush=False) for x in iq_hw]))
+    n = iq.shape[1]
+    npat = 7 if u == 1 else 9
+    stf = (112 if u == 1 else 144) * b * os
+    pat = stf // npat
+    step = pat // 4
+    Q = math.lcm(step, 2 * M_)
+    lead, tail = stf + pat, 2 * stf + 3 * pat
+    if window is None:
+        window = 64 * stf
+    found = []
+    pos = lead
+    n_pkt_guard = stf * L_ // M_
+    while pos + stf < n:
+        s = max(pos - lead, 0) // Q * Q                 # floor to the window grid
+        w = iq[:, s:s + (pos - s) + window + tail]
+        need = (pos - s) + stf + tail
+        if w.shape[1] < need:
+            w = np.concatenate([w, np.zeros((iq.shape[0], need - w.shape[1]), dtype=np.complex64)], axis=1)
+        sl = w.shape[1] - tail
+        sh = s * L_ // M_
+        wh = iq_hw[:, sh:sh + w.shape[1] * L_ // M_ + 8]
+        if wh.shape[1] < w.shape[1] * L_ // M_ + 8:
+            wh = np.concatenate([wh, np.zeros((wh.shape[0], w.shape[1] * L_ // M_ + 8 - wh.shape[1]), dtype=np.complex64)], axis=1)
+        rep = search_rs(w, wh, u, b, os, N_eff_TX_max, sl, resample, ignore_before=pos - s)
+        if rep.detected:
+            fine, coarse = sh + rep.fine_peak_time_local, sh + rep.coarse_peak_time_hw
+            if fine + n_pkt_guard <= iq_hw.shape[1]:
+                found.append((fine, coarse, rep))
+            pos = s + rep.coarse_peak_time_local + 2 * stf
+        else:
+            pos = s + sl
+    return found
+
+
 def stream_search(iq, u, b, os=1, N_eff_TX_max=1, window=None):
     """Sequential packet search over one continuous stream iq [n_ant][n], the way ONE sync_chunk_t walks an arbitrarily
     long chunk (sync_chunk.cpp:146-283): search, on a packet move ignore_before_index to coarse peak + 2 STFs

@@ -241,12 +241,69 @@ int main(int argc, char** argv) {
             if (fw.order[fw.order.size() - p3.size() + i] != (int64_t)(5000000 + at[i])) { ++fails; break; }
     }
 
+    // ---- scenario 4: the same for a radio that delivers its samples piece by piece, at 10/9 of the DECT rate (the main
+    // context): open_stream / push_stream keep the overlap, the resampler history and unfinished packets between pushes
+    uint32_t push_found = 0;
+    {
+        const uint32_t k = n < 12 ? n : 12, stride4 = bp->get_tx_stride();
+        std::vector<phy::harq::process_tx_t*> p4;
+        for (uint32_t i = 0; i < k; ++i) {
+            auto* hp = fw.pool.get_process_tx(1, fw.network_id, ps.psdef, phy::harq::finalize_tx_t::reset_and_terminate);
+            if (!hp) { ++fails; break; }
+            firmware_t::sent_t s{};
+            fw.make_plcf(s.plcf, (4u << 8) | (i + 1));
+            s.tb.resize(ps.N_TB_byte);
+            for (auto& v : s.tb) v = (uint8_t)rng();
+            std::memcpy(hp->get_a_plcf(), s.plcf, 10);
+            std::memcpy(hp->get_a_tb(), s.tb.data(), ps.N_TB_byte);
+            s.rv = hp->get_rv();
+            fw.sent[firmware_t::key_of(s.plcf)] = s;
+            p4.push_back(hp);
+        }
+        std::vector<phy::tx_descriptor_t> descs;
+        for (auto* hp : p4) descs.emplace_back(*hp, 0, tx_meta, radio::buffer_tx_meta_t{});
+        std::vector<cf_t> iq((size_t)p4.size() * stride4);
+        std::vector<uint32_t> ns4;
+        bp->generate_tx_packets(descs, iq.data(), &ns4);
+        const uint32_t S = ns4.empty() ? 0 : ns4[0], stf_hw = ps.N_samples_STF * 10 / 9 + 1;
+        std::vector<size_t> at(p4.size());
+        size_t t = 3 * stf_hw;
+        for (size_t i = 0; i < p4.size(); ++i) { at[i] = t; t += S + stf_hw / 2 + (i % 3 ? rng() % (2 * S) : 0); }
+        const size_t total = t + 6 * stf_hw;
+        std::vector<cf_t> stream(2 * total);
+        std::normal_distribution<float> g(0.f, 0.05f);
+        for (auto& v : stream) { v.re = g(rng); v.im = g(rng); }
+        for (size_t i = 0; i < p4.size(); ++i)
+            for (uint32_t a = 0; a < 2; ++a)
+                for (uint32_t q = 0; q < S; ++q) {
+                    const cf_t x = iq[i * stride4 + q];
+                    cf_t& y = stream[a * total + at[i] + q];
+                    y.re += a ? -x.im : x.re; y.im += a ? x.re : x.im;
+                }
+        const uint32_t pcc0 = fw.n_work_pcc, pdc0 = fw.n_work_pdc;
+        const uint32_t max_push = 3 * S;
+        bp->open_stream(max_push, 7000000);
+        std::vector<cf_t> piece;
+        for (size_t pos = 0; pos < total;) {   // pushes of uneven length, cuts wherever they fall
+            const size_t len = std::min<size_t>(total - pos, 1 + rng() % max_push);
+            piece.resize(2 * len);
+            for (uint32_t a = 0; a < 2; ++a) std::memcpy(&piece[a * len], &stream[a * total + pos], len * sizeof(cf_t));
+            bp->push_stream((uint32_t)len, piece.data(), fw);
+            pos += len;
+        }
+        bp->close_stream();
+        push_found = fw.n_work_pdc - pdc0;
+        if (fw.n_work_pcc - pcc0 != p4.size() || push_found != p4.size() || fw.n_tb_mismatch || fw.n_plcf_mismatch) ++fails;
+        for (size_t i = 0; i < p4.size() && fw.order.size() >= p4.size(); ++i)
+            if (fw.order[fw.order.size() - p4.size() + i] != (int64_t)(7000000 + at[i])) { ++fails; break; }
+    }
+
     const auto& st = bp->get_stats();
     std::printf("{\"n\": %u, \"work_pcc\": %u, \"work_pdc\": %u, \"work_pdc_error\": %u, \"plcf_mismatch\": %u, "
                 "\"tb_mismatch\": %u, \"harq_rounds\": %u, \"harq_first_round_errors\": %u, \"harq_decoded\": %u, "
-                "\"windows\": %llu, \"detections\": %llu, \"mean_snr_dB\": %.2f, \"stream_decoded\": %u, \"fails\": %d}\n",
+                "\"windows\": %llu, \"detections\": %llu, \"mean_snr_dB\": %.2f, \"stream_decoded\": %u, \"push_decoded\": %u, \"fails\": %d}\n",
                 n, fw.n_work_pcc, fw.n_work_pdc, fw.n_work_pdc_error, fw.n_plcf_mismatch, fw.n_tb_mismatch, rounds, err2,
                 pdc2, (unsigned long long)st.windows, (unsigned long long)st.detections,
-                fw.n_work_pdc ? fw.snr_sum / fw.n_work_pdc : 0.0, stream_found, fails);
+                fw.n_work_pdc ? fw.snr_sum / fw.n_work_pdc : 0.0, stream_found, push_found, fails);
     return fails ? 1 : 0;
 }

@@ -42,6 +42,7 @@ def test_host_mirror_loopback_firmware(tmp_path):
     assert out["work_pcc"] >= 48 + 8 and out["harq_decoded"] == 8 and out["harq_first_round_errors"] > 0
     assert out["harq_rounds"] >= 2
     assert out["stream_decoded"] == 12     # streaming front door: every packet of the continuous stream found and decoded
+    assert out["push_decoded"] == 12       # the same pushed piece by piece through the 10/9 resampler (open_stream / push_stream)
 
 
 def test_multi_plan_firmware_builds_and_refuses_to_run_without_gpu(tmp_path):

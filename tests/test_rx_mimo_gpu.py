@@ -102,3 +102,33 @@ def test_device_loopback_sm(product):
     assert good.mean() >= 0.8, float(good.mean())
     assert np.array_equal(tb_out[good], tb[good])
     phy.close()
+
+
+@pytest.mark.parametrize("cfg,N_RX,cb", [((1, 4, 1, 2, 6, 3, 2048), 4, 0), ((1, 2, 1, 3, 4, 4, 2048), 2, 2)])
+def test_sm_over_tdl_channel_matches_oracle(product, cfg, N_RX, cb):
+    """the bench's channel (doubly selective TDL, profile 1, 100 ns, 50 Hz) in front of the spatial multiplexing
+    receiver: device TX -> device channel, the fetched windows go through the oracle"""
+    n, t0 = 4, 9
+    ps = spec.get_packet_sizes(*cfg)
+    phy = product.Phy(cfg, max_batch=n, N_RX=N_RX, network_id=NET, plcf_type=1)
+    rng = np.random.default_rng(17)
+    tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
+    plcf = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    phy.tx(plcf, tb, fetch=False, codebook_index=cb)
+    win = phy.channel(n, snr_dB=32.0, t0=t0, mode=2, seed=99, pdp_idx=1, tau_rms_ns=100.0, fD_Hz=50.0, fetch=True)
+    pcc = phy.rx_pcc(None, t0=t0, n=n)
+    ok, tb_out, snr, nit = phy.rx_pdc(n)
+    llr = phy.tap(product.TAP_LLR_PDC, n)
+    orc = rx.RxConfig(ps, N_RX=N_RX)
+    gold = fec.pdc_gold(NET, 1, ps["G"])
+    for i in range(n):
+        r = orc.rx_packet(win[i], t0=t0)
+        ref = r["llr_pdc"].astype(np.int32)
+        d = np.abs(llr[i].astype(np.int32) - ref)
+        assert np.mean(d <= 2) >= 0.995 and (d <= 2 + 0.02 * np.maximum(np.abs(ref), 100)).all(), (i, int(d.max()))
+        o_ok, o_tb, _ = fec.pdc_decode(r["llr_pdc"], ps, 0, gold)
+        assert bool(ok[i]) == o_ok
+        if o_ok:
+            assert np.array_equal(tb_out[i], o_tb) and np.array_equal(tb_out[i], tb[i])
+    assert ok.sum() >= n - 1
+    phy.close()

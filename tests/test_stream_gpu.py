@@ -105,3 +105,118 @@ def test_stream_edge_cases(product):
     got = phy.stream_sync(np.ascontiguousarray(cut))
     assert np.array_equal(got.fine_peak_time_64, starts[:2])
     phy.close()
+
+
+# ---- stateful front door: dnrp_stream_open / dnrp_stream_push ------------------------------------------------------------
+def _make_stream_hw(product, cfg, n_pkt, snr_db, seed, N_RX=1, os_=1, resample=(1, 1)):
+    """like _make_stream, at the hardware rate of a context with oversampling / resampling"""
+    rng = np.random.default_rng(seed)
+    phy = product.Phy(cfg, max_batch=n_pkt, N_RX=N_RX, network_id=NET, plcf_type=1, oversampling=os_, resample=resample)
+    ps = phy.ps
+    tb = rng.integers(0, 256, (n_pkt, ps["N_TB_byte"]), dtype=np.uint8)
+    plcf = rng.integers(0, 256, (n_pkt, 10), dtype=np.uint8)
+    iq, ns = phy.tx(plcf, tb)
+    S = int(ns[0])
+    stf = ps["N_samples_STF"] * os_ * resample[0] // resample[1]
+    gaps = rng.integers(stf // 4, 2 * S, n_pkt)
+    gaps[::5] = S // 20                                # every fifth packet follows its predecessor almost back to back
+    starts = np.zeros(n_pkt, dtype=np.int64)
+    t = 3 * stf
+    for i in range(n_pkt):
+        starts[i] = t
+        t += S + int(gaps[i])
+    n = int(t + 6 * stf)
+    sigma = 10 ** (-snr_db / 20)
+    stream = (sigma / np.sqrt(2)) * (rng.standard_normal((N_RX, n)) + 1j * rng.standard_normal((N_RX, n)))
+    for i in range(n_pkt):
+        for a in range(N_RX):
+            stream[a, starts[i]:starts[i] + S] += iq[i, 0, :S] * np.exp(1j * 0.7 * a)
+    return phy, stream.astype(np.complex64), starts, tb, plcf, S
+
+
+def _push_all(phy, stream, cuts, max_push, hop, decode=None):
+    """feed stream[:, cuts[i]:cuts[i+1]] push by push; returns the records handed out, in order"""
+    phy.stream_open(max_push, chunk_hop=hop)
+    got = []
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        r = phy.stream_push(np.ascontiguousarray(stream[:, a:b]))
+        if len(r):
+            assert (r.fine_peak_time_64 + 1 <= b).all()           # nothing from the future
+            if decode is not None:
+                decode(r)
+            got.append(r.copy())
+    phy.stream_close()
+    return np.concatenate(got).view(np.recarray) if got else np.zeros(0)
+
+
+@pytest.mark.parametrize("cfg,os_,resample,hop", [((1, 2, 1, 1, 0, 3, 2048), 1, (1, 1), 0), ((1, 2, 1, 1, 0, 3, 2048), 1, (1, 1), 1100),
+                                                  ((1, 1, 1, 1, 0, 2, 2048), 2, (10, 9), 0),
+                                                  ((1, 2, 1, 1, 0, 3, 2048), 2, (10, 9), 2000)])
+def test_stream_push_matches_sequential_oracle(product, cfg, os_, resample, hop):
+    """one long stream in 7 unequal pushes (packets and STFs straddle the cuts), without and with resampling 10/9 (C1,
+    the reference's loopback configuration, is the third case): the oracle's packets at the oracle's samples, the same
+    for a different cut of the same stream, and every packet handed out decodes"""
+    n_pkt = 24
+    phy, stream, starts, tb, plcf, S = _make_stream_hw(product, cfg, n_pkt, snr_db=20.0, seed=8, os_=os_, resample=resample)
+    n = stream.shape[1]
+    if resample == (1, 1):
+        ref = osync.stream_search(stream, cfg[0], cfg[1], os=os_, N_eff_TX_max=1)
+    else:
+        ref = osync.stream_search_resampled(stream, cfg[0], cfg[1], os=os_, N_eff_TX_max=1, resample=resample)
+    ref_fine = np.array([f for f, _, _ in ref], dtype=np.int64)
+    assert np.array_equal(ref_fine, starts), (ref_fine[:6], starts[:6])
+    rng = np.random.default_rng(5)
+    # 7 pushes: cuts inside an STF, inside a packet body, one tiny push, one large
+    cuts = np.array([0, starts[2] + 40, starts[5] + S // 2, starts[5] + S // 2 + 64, starts[11] - 3, starts[17] + 7, starts[20] + S - 1, n])
+    assert np.all(np.diff(cuts) > 0)
+    max_push = int(np.diff(cuts).max())
+    t0 = 64
+    decoded = {}
+
+    def decode(r):
+        m = len(r)
+        phy.stream_extract(r.fine_peak_time_64, t0)
+        sync = phy.make_sync(m, t0=t0, cfo_fractional_rad=r.sync.cfo_fractional_rad, rms=r.sync.rms_array)
+        phy.rx_pcc(None, n=m, sync=sync)
+        ok, tb_out, _, _ = phy.rx_pdc(m)
+        for i in range(m):
+            decoded[int(r.fine_peak_time_64[i])] = (bool(ok[i]), tb_out[i].copy())
+
+    got = _push_all(phy, stream, cuts, max_push, hop, decode)
+    fine = got.fine_peak_time_64
+    assert np.all(np.diff(fine) > 0)
+    assert np.isin(ref_fine, fine).all(), np.setdiff1d(ref_fine, fine)
+    assert len(np.setdiff1d(fine, ref_fine)) <= 2
+    by_time = {f: (c, r) for f, c, r in ref}
+    for g in got[np.isin(fine, ref_fine)]:
+        c, r = by_time[int(g.fine_peak_time_64)]
+        assert g.coarse_peak_time_64 == c
+        assert g.sync.N_eff_TX == r.N_eff_TX
+        assert abs(g.sync.cfo_fractional_rad - r.cfo_fractional_rad) < 2e-5
+    for i, s in enumerate(starts):
+        ok, out = decoded[int(s)]
+        assert ok and np.array_equal(out, tb[i]), i
+    # a different cut of the same stream (equal pushes): the same packets
+    cuts2 = np.linspace(0, n, 12).astype(np.int64)
+    got2 = _push_all(phy, stream, cuts2, int(np.diff(cuts2).max()), hop)
+    assert np.array_equal(np.intersect1d(got2.fine_peak_time_64, ref_fine), ref_fine)
+    phy.close()
+
+
+def test_stream_push_limits(product):
+    cfg = (1, 2, 1, 1, 0, 3, 2048)
+    phy = product.Phy(cfg, max_batch=4, network_id=NET, plcf_type=1)
+    with pytest.raises(product.DnrpError, match="dnrp_stream_open first"):
+        phy.stream_push(np.zeros((1, 16), dtype=np.complex64))
+    phy.stream_open(1000)
+    with pytest.raises(product.DnrpError, match="max_push_samples"):
+        phy.stream_push(np.zeros((1, 1001), dtype=np.complex64))
+    assert len(phy.stream_push(np.zeros((1, 1000), dtype=np.complex64))) == 0
+    assert len(phy.stream_push(np.zeros((1, 0), dtype=np.complex64))) == 0
+    phy.stream_close()
+    # a chunk hop whose detection prefix sums cannot fit the shared memory of a block is refused with a message
+    with pytest.raises(product.DnrpError, match="shared memory"):
+        phy.stream_open(1000, chunk_hop=10_000_000)
+    with pytest.raises(product.DnrpError, match="shared memory"):
+        phy.stream_sync(np.zeros((1, 4000), dtype=np.complex64), chunk_hop=10_000_000)
+    phy.close()
