@@ -318,6 +318,28 @@ int dnrp_fec_encode(dnrp_ctx_t* c, uint32_t n, const uint8_t* plcf, const uint32
     return DNRP_OK;
 }
 
+}  // extern "C"
+
+int dnrp::validate_harq_slots(dnrp_ctx* c, uint32_t n, const uint32_t* harq_slot) {
+    if (!harq_slot) return DNRP_OK;   // packet i uses slot i
+    std::vector<uint8_t> seen(c->B, 0);
+    for (uint32_t i = 0; i < n; ++i) {
+        if (harq_slot[i] >= c->B) {
+            set_last_error("harq slot out of range");
+            return DNRP_ERR_INVALID;
+        }
+        if (seen[harq_slot[i]]) {
+            set_last_error("harq slot " + std::to_string(harq_slot[i]) + " appears twice in one batch (its soft buffer would be "
+                           "combined by two packets at once)");
+            return DNRP_ERR_INVALID;
+        }
+        seen[harq_slot[i]] = 1;
+    }
+    return DNRP_OK;
+}
+
+extern "C" {
+
 int dnrp_fec_decode_tb(dnrp_ctx_t* c, uint32_t n, const int16_t* llr, const uint32_t* harq_slot,
                        const uint8_t* rv, const uint8_t* harq_reset, uint8_t* tb_out, uint8_t* crc_ok,
                        uint8_t* n_iter) {
@@ -325,8 +347,10 @@ int dnrp_fec_decode_tb(dnrp_ctx_t* c, uint32_t n, const int16_t* llr, const uint
     DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
     DNRP_CUDA(cudaSetDevice(c->device));
     const fec_plan_t& f = c->fec;
-    if (harq_slot)
-        for (uint32_t i = 0; i < n; ++i) DNRP_REQUIRE(harq_slot[i] < c->B, "harq slot out of range");
+    {
+        const int rcs = validate_harq_slots(c, n, harq_slot);
+        if (rcs) return rcs;
+    }
     DNRP_CUDA(cudaMemcpyAsync(c->d_llr.p, llr, (size_t)n * c->ps.G * 2, cudaMemcpyHostToDevice, c->stream));
     if (harq_slot) DNRP_CUDA(cudaMemcpyAsync(c->d_slot.p, harq_slot, 4 * n, cudaMemcpyHostToDevice, c->stream));
     if (rv) DNRP_CUDA(cudaMemcpyAsync(c->d_rv.p, rv, n, cudaMemcpyHostToDevice, c->stream));

@@ -259,12 +259,12 @@ int dnrp_rx_pdc_batch(dnrp_ctx_t* c, uint32_t n, const uint32_t* harq_slot, cons
     DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
     DNRP_CUDA(cudaSetDevice(c->device));
     const fec_plan_t& f = c->fec;
-    if (harq_slot)
-        for (uint32_t i = 0; i < n; ++i) DNRP_REQUIRE(harq_slot[i] < c->B, "harq slot out of range");
+    int rc = validate_harq_slots(c, n, harq_slot);
+    if (rc) return rc;
     if (harq_slot) DNRP_CUDA(cudaMemcpyAsync(c->d_slot.p, harq_slot, 4 * n, cudaMemcpyHostToDevice, c->stream));
     if (rv) DNRP_CUDA(cudaMemcpyAsync(c->d_rv.p, rv, n, cudaMemcpyHostToDevice, c->stream));
     if (harq_reset) DNRP_CUDA(cudaMemcpyAsync(c->d_reset.p, harq_reset, n, cudaMemcpyHostToDevice, c->stream));
-    int rc = run_rx_pdc(c, n, harq_slot != nullptr, rv != nullptr, harq_reset != nullptr);
+    rc = run_rx_pdc(c, n, harq_slot != nullptr, rv != nullptr, harq_reset != nullptr);
     if (rc) return rc;
     return fetch_pdc_reports(c, n, tb_out, out, n_iter);
 }
@@ -284,8 +284,23 @@ static int rx_batch_impl(dnrp_ctx_t* c, uint32_t n, const void* iq_in, float sc1
         DNRP_REQUIRE(c->rx_stride % 4 == 0, "sc16 ingest needs a window stride that is a multiple of 4");
         DNRP_CUDA(c->d_iq_sc16.alloc((size_t)c->B * d.N_RX * c->rx_stride * 2));
     }
-    if (harq_slot)
-        for (uint32_t i = 0; i < n; ++i) DNRP_REQUIRE(harq_slot[i] < c->B, "harq slot out of range");
+    {
+        const int rcs = validate_harq_slots(c, n, harq_slot);
+        if (rcs) return rcs;
+    }
+    // from here on every early return leaves the context as it found it: window offset back to 0, the three streams
+    // drained (a later call must not see half a batch in flight or work on offset buffers)
+    struct batch_guard_t {
+        dnrp_ctx* c;
+        bool done = false;
+        ~batch_guard_t() {
+            c->off = 0;
+            if (done) return;
+            cudaStreamSynchronize(c->stream_copy);
+            cudaStreamSynchronize(c->stream);
+            cudaStreamSynchronize(c->stream_d2h);
+        }
+    } guard{c};
     if (harq_slot) DNRP_CUDA(cudaMemcpyAsync(c->d_slot.p, harq_slot, 4 * n, cudaMemcpyHostToDevice, c->stream));
     if (rv) DNRP_CUDA(cudaMemcpyAsync(c->d_rv.p, rv, n, cudaMemcpyHostToDevice, c->stream));
     if (harq_reset) DNRP_CUDA(cudaMemcpyAsync(c->d_reset.p, harq_reset, n, cudaMemcpyHostToDevice, c->stream));
@@ -398,6 +413,7 @@ static int rx_batch_impl(dnrp_ctx_t* c, uint32_t n, const void* iq_in, float sc1
     if (rc) return rc;
     DNRP_CUDA(cudaStreamSynchronize(c->stream_d2h));
     DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    guard.done = true;
     // records -> ABI structs (same fields as fetch_pcc_reports / fetch_pdc_reports)
     const rx_state_t* st = reinterpret_cast<const rx_state_t*>(hs + o_state);
     const mimo_report_dev_t* mimo = reinterpret_cast<const mimo_report_dev_t*>(hs + o_mimo);

@@ -245,6 +245,8 @@ namespace dnrp {
 int build_phy_plan(dnrp_ctx* c);
 int upload_gold_table(dnrp_ctx* c);
 int gold_index(dnrp_ctx* c, uint32_t network_id, uint32_t plcf_type);   // -1: not registered
+// every slot < max_batch and no slot twice in one batch (two packets on one slot would race on its soft buffer)
+int validate_harq_slots(dnrp_ctx* c, uint32_t n, const uint32_t* harq_slot);
 int run_fec_encode(dnrp_ctx* c, uint32_t n, bool have_mask, bool have_rv);
 int run_fec_decode_tb(dnrp_ctx* c, uint32_t n, bool have_slot, bool have_rv, bool have_reset);
 int run_fec_decode_plcf(dnrp_ctx* c, uint32_t n);

@@ -503,7 +503,10 @@ __global__ void k_sync_final(const sync_params_t p, uint32_t n, uint32_t len) {
             s.inc0 = res.cfo_fractional_rad + res.cfo_integer_rad;
             for (uint32_t a = 0; a < 8; ++a) s.rms[a] = res.rms_array[a];
         } else {
-            s.t0 = 0;  // nothing found: the receiver runs on the window start and fails its CRCs
+            // nothing found, or the packet does not fit behind its fine peak: the receiver runs on the window start and
+            // fails its CRCs; the record says "not detected" so that no caller mistakes offset 0 for a packet
+            res.detected = 0;
+            s.t0 = 0;
             for (uint32_t a = 0; a < 8; ++a) s.rms[a] = 1.f;
         }
         p.rx_state[pkt] = s;

@@ -309,7 +309,12 @@ int dnrp_harq_reset(dnrp_ctx_t* ctx, uint32_t harq_slot);
  * dnrp_rx_pdc_batch for every window (no MAC decision between PCC and PDC: the simulator's / a monitor's use, where
  * every PDC is wanted; firmware that decides per packet uses the three calls, see dnrp_host.hpp).  The windows are
  * copied and processed in chunks so that the host-to-device transfer overlaps the kernels.  iq_in
- * [n][N_RX][dnrp_rx_stride()] should be pinned.  sync_out / pcc_out / n_iter may be NULL. */
+ * [n][N_RX][dnrp_rx_stride()] and tb_out [n][N_TB_byte] should be pinned (cudaHostAlloc / cudaHostRegister): both are
+ * the target of per-chunk asynchronous copies, pageable memory makes every such copy block the host and removes the
+ * overlap (the result is the same).  sync_out / pcc_out / n_iter may be NULL.  harq_slot (here, in dnrp_rx_pdc_batch,
+ * dnrp_rx_pdc_batch_ex and dnrp_fec_decode_tb): every slot < max_batch and no slot twice in one batch -- two packets on
+ * one slot would combine into the same soft buffer concurrently; refused with DNRP_ERR_INVALID.  On any error the call
+ * drains its streams and leaves the context usable. */
 int dnrp_rx_batch(dnrp_ctx_t* ctx, uint32_t n, const dnrp_cf32_t* iq_in, uint32_t search_length,
                   const uint32_t* harq_slot, const uint8_t* rv, const uint8_t* harq_reset,
                   dnrp_sync_result_t* sync_out, dnrp_pcc_report_t* pcc_out, uint8_t* tb_out,

@@ -143,3 +143,25 @@ def test_decode_plcf_bit_exact(product):
                 n_ok += 1
     assert n_ok >= n // 2
     phy.close()
+
+
+def test_duplicate_or_out_of_range_harq_slots_are_refused(product):
+    """two packets of one batch on the same HARQ slot would combine into one soft buffer concurrently: the C entry points
+    refuse that (the reference hands out each HARQ process once, process_pool.cpp) and stay usable afterwards"""
+    cfg = CONFIGS["small_b2_mcs4"]
+    ps = spec.get_packet_sizes(*cfg)
+    phy = product.Phy(cfg, max_batch=4, network_id=123456789)
+    llr = np.zeros((3, ps["G"]), dtype=np.int16)
+    with pytest.raises(product.DnrpError, match="appears twice"):
+        phy.fec_decode_tb(llr, harq_slot=[1, 2, 1])
+    with pytest.raises(product.DnrpError, match="out of range"):
+        phy.fec_decode_tb(llr, harq_slot=[0, 1, 4])
+    win = np.zeros((3, 1, phy.rx_stride()), dtype=np.complex64)
+    with pytest.raises(product.DnrpError, match="appears twice"):
+        phy.rx(win, harq_slot=[3, 3, 0])
+    phy.rx_pcc(win, t0=0)
+    with pytest.raises(product.DnrpError, match="appears twice"):
+        phy.rx_pdc(3, harq_slot=[2, 0, 2])
+    ok, tb, nit = phy.fec_decode_tb(llr, harq_slot=[2, 0, 1])   # still usable
+    assert ok.shape == (3,) and not tb.any()
+    phy.close()
