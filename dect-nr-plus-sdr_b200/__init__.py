@@ -93,7 +93,7 @@ CHANNEL_DTYPE = np.dtype([("snr_dB", "f4"), ("net_bandwidth_norm", "f4"), ("t0",
                           ("seed", "u8"), ("pdp_idx", "u4"), ("tau_rms_ns", "f4"), ("fD_Hz", "f4"), ("time_64", "i8")],
                          align=True)
 assert CHANNEL_DTYPE.itemsize == C.sizeof(ChannelDesc)
-TAP_Y, TAP_DRS_ZF, TAP_STF_ZF, TAP_LLR_PCC, TAP_LLR_PDC, TAP_WIENER_CLASS, TAP_TB_OK = 1, 2, 3, 4, 5, 6, 7
+TAP_Y, TAP_DRS_ZF, TAP_STF_ZF, TAP_LLR_PCC, TAP_LLR_PDC, TAP_WIENER_CLASS, TAP_TB_OK, TAP_CHESTIM = 1, 2, 3, 4, 5, 6, 7, 8
 KERNEL_TURBO_DECODE_PDC, KERNEL_RX_FFT, KERNEL_RX_DEMAP_PDC, KERNEL_RX_STF, KERNEL_DERM_PDC, KERNEL_SYNC, \
     KERNEL_RESAMPLE = range(7)
 # dnrp_sync_result_t
@@ -415,7 +415,7 @@ class Phy:
         nbytes = lib().dnrp_tap_bytes(self._ctx, which, n)
         buf = np.zeros(nbytes, dtype=np.uint8)
         _check(lib().dnrp_tap_read(self._ctx, which, n, _ptr(buf, np.uint8), C.c_size_t(nbytes)))
-        if which in (TAP_Y, TAP_DRS_ZF, TAP_STF_ZF):
+        if which in (TAP_Y, TAP_DRS_ZF, TAP_STF_ZF, TAP_CHESTIM):
             return buf.view(np.complex64).reshape(n, -1)
         if which in (TAP_LLR_PCC, TAP_LLR_PDC):
             return buf.view(np.int16).reshape(n, -1)

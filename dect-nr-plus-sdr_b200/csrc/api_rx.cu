@@ -479,6 +479,7 @@ static bool tap_desc(const dnrp_ctx_t* c, int tap, uint32_t n, const void*& src,
 size_t dnrp_tap_bytes(const dnrp_ctx_t* c, int tap, uint32_t n) {
     const void* src;
     size_t bytes = 0;
+    if (c && tap == DNRP_TAP_CHESTIM) return (size_t)n * c->dims.N_RX * c->dims.N_eff_TX * c->dims.Nk * sizeof(float2);
     if (!c || !tap_desc(c, tap, n, src, bytes)) return 0;
     return bytes;
 }
@@ -488,9 +489,21 @@ int dnrp_tap_read(dnrp_ctx_t* c, int tap, uint32_t n, void* dst, size_t dst_byte
     DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
     const void* src;
     size_t bytes = 0;
+    DNRP_CUDA(cudaSetDevice(c->device));
+    if (tap == DNRP_TAP_CHESTIM) {
+        // computed on demand from the zero-forced pilots and Wiener classes the last receiver call left on the device
+        bytes = dnrp_tap_bytes(c, tap, n);
+        DNRP_REQUIRE(dst_bytes >= bytes, "destination too small");
+        const size_t need = (size_t)c->B * c->dims.N_RX * c->dims.N_eff_TX * c->dims.Nk;
+        if (c->d_chestim_tap.n < need) DNRP_CUDA(c->d_chestim_tap.alloc(need));
+        const rx_params_t p = make_rx_params(c);
+        DNRP_LAUNCH(c, -1, launch_rx_chestim_tap(p, c->d_chestim_tap.p, n, c->stream));
+        DNRP_CUDA(cudaMemcpyAsync(dst, c->d_chestim_tap.p, bytes, cudaMemcpyDeviceToHost, c->stream));
+        DNRP_CUDA(cudaStreamSynchronize(c->stream));
+        return DNRP_OK;
+    }
     DNRP_REQUIRE(tap_desc(c, tap, n, src, bytes), "unknown tap");
     DNRP_REQUIRE(dst_bytes >= bytes, "destination too small");
-    DNRP_CUDA(cudaSetDevice(c->device));
     DNRP_CUDA(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDeviceToHost, c->stream));
     DNRP_CUDA(cudaStreamSynchronize(c->stream));
     return DNRP_OK;

@@ -141,6 +141,7 @@ struct dnrp_ctx {
     dnrp::dbuf<float2> d_iq_rx, d_Y, d_hzf, d_hstf, d_snr_part;
     dnrp::dbuf<dnrp::rx_state_t> d_rx_state;
     dnrp::dbuf<uint8_t> d_cls;
+    dnrp::dbuf<float2> d_chestim_tap;           // DNRP_TAP_CHESTIM, allocated by the first read
     std::vector<dnrp::rx_state_t> h_rx_state;
     dnrp::dbuf<dnrp::chan_meta_dev_t> d_chan_meta;
     // MIMO report: single-stream codebooks W(1, N_eff_TX) and W(1, N_RX)

@@ -37,6 +37,7 @@ struct phy_dims_t {
     uint32_t n_full_ps;                     // full processing stages in lr mode (rx_synced.cpp:1031-1032)
     uint32_t N_step_inv, chestim_stride_inv;  // ceil(2^32 / x): i / x == __umulhi(i, inv) for the symbol indices used
     uint32_t pcc_l_max;                     // last OFDM symbol carrying PCC cells
+    uint32_t last_plan[8];                  // plan word of (stream ts, last data field symbol): the estimate left at packet end
     struct wiener_dev_t {
         const uint16_t* idx_pilot;          // [n_t][4][Nk]
         const uint16_t* idx_weight;         // [n_t][4][Nk]
@@ -104,6 +105,9 @@ cudaError_t launch_rx_stf(const rx_params_t& p, uint32_t n_packets, cudaStream_t
 cudaError_t launch_rx_fft(const rx_params_t& p, uint32_t n_packets, cudaStream_t st);
 cudaError_t launch_rx_snr_class(const rx_params_t& p, uint32_t n_packets, cudaStream_t st);
 cudaError_t launch_rx_demap(const rx_params_t& p, uint32_t n_packets, bool pcc, cudaStream_t st);
+// out [packet][N_RX][N_eff_TX][Nk]: the channel estimate the reference holds in channel_antennas[a]->chestim[ts] when the
+// packet is done (rx_synced.cpp:444-480 exports exactly that)
+cudaError_t launch_rx_chestim_tap(const rx_params_t& p, float2* out, uint32_t n_packets, cudaStream_t st);
 
 // per-packet transmit parameters: tx_descriptor_t::codebook_index + tx_meta_t
 // (reference lib/include/dectnrp/phy/tx/tx_descriptor.hpp:43-78, tx_meta.hpp:32-58)

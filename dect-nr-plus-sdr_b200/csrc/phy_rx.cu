@@ -717,6 +717,31 @@ __global__ void k_rx_mimo(const mimo_params_t p, uint32_t n) {
     p.out[pkt] = r;
 }
 
+// ---- scope / JSON tap: the interpolated channel of every (RX antenna, stream) over all subcarriers as it stands after
+// the last data field symbol (rx_synced_t::get_json, rx_synced.cpp:444-480: "last known channel measurement")
+template <int NRX>
+__global__ void __launch_bounds__(128) k_rx_chestim_tap(const rx_params_t p, float2* __restrict__ out) {
+    const phy_dims_t& d = p.d;
+    const uint32_t k = blockIdx.x * blockDim.x + threadIdx.x, ts = blockIdx.y, pkt = blockIdx.z;
+    if (k >= d.Nk) return;
+    float2 h[NRX];
+    chan_est_rx<NRX>(p, pkt, d.last_plan[ts], k, h);
+#pragma unroll
+    for (int a = 0; a < NRX; ++a) out[(((size_t)pkt * NRX + a) * d.N_eff_TX + ts) * d.Nk + k] = h[a];
+}
+
+cudaError_t launch_rx_chestim_tap(const rx_params_t& p, float2* out, uint32_t n_packets, cudaStream_t st) {
+    const dim3 grid((p.d.Nk + 127) / 128, p.d.N_eff_TX, n_packets);
+    switch (p.d.N_RX) {
+        case 1: k_rx_chestim_tap<1><<<grid, 128, 0, st>>>(p, out); break;
+        case 2: k_rx_chestim_tap<2><<<grid, 128, 0, st>>>(p, out); break;
+        case 4: k_rx_chestim_tap<4><<<grid, 128, 0, st>>>(p, out); break;
+        case 8: k_rx_chestim_tap<8><<<grid, 128, 0, st>>>(p, out); break;
+        default: return cudaErrorInvalidValue;
+    }
+    return cudaGetLastError();
+}
+
 cudaError_t launch_rx_mimo(const mimo_params_t& p, uint32_t n_packets, cudaStream_t st) {
     k_rx_mimo<<<(n_packets + 63) / 64, 64, 0, st>>>(p, n_packets);
     return cudaGetLastError();

@@ -172,6 +172,7 @@ int build_phy_plan(dnrp_ctx* c) {
                 for (uint32_t s_ = 0; s_ < d.N_SS; ++s_) t[q * d.N_SS + s_] = plan_word(s_, lk[q] >> 16, false);
             return t;
         };
+        for (uint32_t ts = 0; ts < 8; ++ts) d.last_plan[ts] = ts < d.N_eff_TX ? plan_word(ts, d.N_DF, false) : 0u;
         UP(c->d_pcc_plan.upload(build(m.pcc_lk, true)));
         UP(c->d_pdc_plan.upload(d.N_SS > 1 ? build_sm(m.pdc_lk) : build(m.pdc_lk, false)));
     }

@@ -340,7 +340,9 @@ typedef enum {
     DNRP_TAP_LLR_PCC = 4,  /* int16 [n][196] */
     DNRP_TAP_LLR_PDC = 5,  /* int16 [n][G] */
     DNRP_TAP_WIENER_CLASS = 6, /* uint8 [n][dnrp_tap_bytes/n] class after each DRS symbol */
-    DNRP_TAP_TB_OK = 7         /* uint8 [n] transport block CRC flags of the last PDC decode */
+    DNRP_TAP_TB_OK = 7,        /* uint8 [n] transport block CRC flags of the last PDC decode */
+    DNRP_TAP_CHESTIM = 8       /* cf32 [n][N_RX][N_eff_TX][N_b_OCC+1] interpolated channel after the last data field symbol:
+                                * what rx_synced_t::get_json exports as ch_<rx>_<ts> (rx_synced.cpp:444-480) */
 } dnrp_tap_t;
 size_t dnrp_tap_bytes(const dnrp_ctx_t* ctx, int tap, uint32_t n);
 int dnrp_tap_read(dnrp_ctx_t* ctx, int tap, uint32_t n, void* dst, size_t dst_bytes);

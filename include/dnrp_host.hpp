@@ -31,6 +31,7 @@
 extern "C" {
 #include "dnrp_c_api.h"
 }
+#include "dnrp_json_export.hpp"
 #include "dnrp_plcf.hpp"
 #include "dnrp_mac_pdu.hpp"
 
@@ -541,6 +542,19 @@ class batch_phy_t {
         }
         void close_stream() { check(dnrp_stream_close(ctx), "dnrp_stream_close"); }
 
+        /// PHY_JSON_SWITCH_IMPLEMENT_ANY_JSON_FUNCTIONALITY of the reference (worker_tx_rx.cpp:356-414): from now on every
+        /// packet whose PDC is decoded adds one entry in the reference's layout; a file "<prefix_file><0000000000>" every
+        /// json_length entries (json_export_t, lib/src/common/json/json_export.cpp)
+        void enable_json_export(uint32_t json_length, const std::string& prefix_file) {
+            json_export = std::make_unique<common::json_export_t>(json_length, prefix_file);
+        }
+        /// writes the entries that do not fill a file yet; returns the files written so far
+        std::vector<std::string> flush_json_export() {
+            if (!json_export) return {};
+            json_export->flush();
+            return json_export->get_files();
+        }
+
     private:
         int64_t stream_clock_64{0};
 
@@ -668,10 +682,45 @@ class batch_phy_t {
                 std::vector<dnrp_pdc_report_t> pdc(m);
                 check(dnrp_rx_pdc_batch_ex(P.ctx, m, slot.data(), rv.data(), reset.data(), ids.data(), tys.data(), tb.data(),
                                            pdc.data(), nullptr), "dnrp_rx_pdc_batch_ex");
+                std::vector<float> chestim;
+                const uint32_t Nk = P.ps.N_b_OCC + 1, N_eff = P.ps.N_eff_TX;
+                if (json_export) {   // worker_tx_rx.cpp:356-414: one JSON entry per packet whose PDC was decoded
+                    chestim.resize(2 * (size_t)m * N_RX * N_eff * Nk);
+                    check(dnrp_tap_read(P.ctx, DNRP_TAP_CHESTIM, m, chestim.data(), chestim.size() * sizeof(float)), "dnrp_tap_read");
+                }
                 for (uint32_t q = 0; q < m; ++q) {
                     if (!mine[q]) continue;
                     const uint32_t i = win[q];
                     harq::process_rx_t* hp = maclow[i].hp_rx;
+                    if (json_export) {
+                        common::json_packet_t j;
+                        const sync_report_t& sr = sync_reports[i];
+                        j.worker_id = (uint32_t)device_index;
+                        const double dect_os = (double)config.psdef.u * config.psdef.b * 1.728e6 * config.oversampling;
+                        j.samp_rate = (uint32_t)std::lround(dect_os * config.resample_L / config.resample_M);
+                        j.N_TX_min = N_RX;
+                        j.enforce_dectnrp_samp_rate_by_resampling = config.resample_L != config.resample_M;
+                        j.L = config.resample_L; j.M = config.resample_M;
+                        j.dect_samp_rate_max_oversampled = (uint32_t)std::lround(dect_os);
+                        j.detection_ant_idx = sr.detection_ant_idx; j.detection_rms = sr.detection_rms;
+                        j.detection_metric = sr.detection_metric;
+                        j.u = sr.u; j.b = sr.b; j.N_eff_TX = sr.N_eff_TX;
+                        for (uint32_t a = 0; a < N_RX && a < 8; ++a) {
+                            j.coarse_peak_array[a] = sr.coarse_peak_array.at(a); j.rms_array[a] = sr.rms_array.at(a);
+                        }
+                        j.cfo_f = sr.cfo_fractional_rad; j.cfo_i = sr.cfo_integer_rad; j.sto_fractional = sr.sto_fractional;
+                        j.coarse_peak_time = sr.coarse_peak_time_64; j.fine_peak_time = sr.fine_peak_time_64;
+                        j.fine_peak_time_corrected_by_sto_fractional = sr.fine_peak_time_corrected_by_sto_fractional_64;
+                        j.snr = pdc[q].snr_dB; j.mcs = P.psdef.mcs_index;
+                        j.N_b_DFT = P.ps.N_b_DFT; j.N_b_OCC_plus_DC = Nk; j.N_RX = N_RX;
+                        // the export loops over sync_report.N_eff_TX streams; the estimate holds the geometry's
+                        j.N_eff_TX = N_eff;
+                        j.chestim = &chestim[2 * (size_t)q * N_RX * N_eff * Nk];
+                        j.PLCF_type = hp->get_PLCF_type();
+                        const uint8_t* pb = pcc_reports[i].get_plcf_bytes(j.PLCF_type);
+                        j.HeaderFormat = pb ? (uint32_t)(pb[0] >> 5) : 0u;
+                        json_export->append(j);
+                    }
                     std::memcpy(hp->get_a_tb(), &tb[(size_t)q * P.ps.N_TB_byte], P.ps.N_TB_byte);
                     pdc_report_t rep;
                     rep.crc_status = pdc[q].crc_ok != 0;
@@ -689,6 +738,8 @@ class batch_phy_t {
                 }
             }
         }
+
+        std::unique_ptr<common::json_export_t> json_export;
 
         struct plan_t {
             sp3::packet_sizes_def_t psdef;

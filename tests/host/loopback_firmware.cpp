@@ -108,6 +108,8 @@ int main(int argc, char** argv) {
         std::fprintf(stderr, "loopback_firmware: %s\n", e.what());
         return 3;
     }
+    // optional second argument: prefix of the per-packet JSON export (the reference's worker_pool_* files), 8 entries per file
+    if (argc > 2) bp->enable_json_export(8, argv[2]);
     const sp3::packet_sizes_t ps = bp->get_packet_sizes();
     firmware_t fw(ps, n);
     std::mt19937 rng(7);
@@ -298,12 +300,13 @@ int main(int argc, char** argv) {
             if (fw.order[fw.order.size() - p4.size() + i] != (int64_t)(7000000 + at[i])) { ++fails; break; }
     }
 
+    const size_t json_files = bp->flush_json_export().size();
     const auto& st = bp->get_stats();
     std::printf("{\"n\": %u, \"work_pcc\": %u, \"work_pdc\": %u, \"work_pdc_error\": %u, \"plcf_mismatch\": %u, "
                 "\"tb_mismatch\": %u, \"harq_rounds\": %u, \"harq_first_round_errors\": %u, \"harq_decoded\": %u, "
-                "\"windows\": %llu, \"detections\": %llu, \"mean_snr_dB\": %.2f, \"stream_decoded\": %u, \"push_decoded\": %u, \"fails\": %d}\n",
+                "\"windows\": %llu, \"detections\": %llu, \"mean_snr_dB\": %.2f, \"stream_decoded\": %u, \"push_decoded\": %u, \"json_files\": %zu, \"fails\": %d}\n",
                 n, fw.n_work_pcc, fw.n_work_pdc, fw.n_work_pdc_error, fw.n_plcf_mismatch, fw.n_tb_mismatch, rounds, err2,
                 pdc2, (unsigned long long)st.windows, (unsigned long long)st.detections,
-                fw.n_work_pdc ? fw.snr_sum / fw.n_work_pdc : 0.0, stream_found, push_found, fails);
+                fw.n_work_pdc ? fw.snr_sum / fw.n_work_pdc : 0.0, stream_found, push_found, json_files, fails);
     return fails ? 1 : 0;
 }

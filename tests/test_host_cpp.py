@@ -7,6 +7,7 @@ import json
 import os
 import subprocess
 
+import numpy as np
 import pytest
 
 from conftest import ROOT, load_product
@@ -35,14 +36,63 @@ def test_host_mirror_builds_and_refuses_to_run_without_gpu(tmp_path):
 @pytest.mark.gpu
 def test_host_mirror_loopback_firmware(tmp_path):
     exe = build_program(tmp_path)
-    r = subprocess.run([exe, "48"], capture_output=True, text=True, timeout=600)
+    prefix = str(tmp_path / "worker_pool_0000_")
+    r = subprocess.run([exe, "48", prefix], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
     out = json.loads(r.stdout.strip().splitlines()[-1])
+    _check_json_export(prefix, out)
     assert out["fails"] == 0 and out["plcf_mismatch"] == 0 and out["tb_mismatch"] == 0
     assert out["work_pcc"] >= 48 + 8 and out["harq_decoded"] == 8 and out["harq_first_round_errors"] > 0
     assert out["harq_rounds"] >= 2
     assert out["stream_decoded"] == 12     # streaming front door: every packet of the continuous stream found and decoded
     assert out["push_decoded"] == 12       # the same pushed piece by piece through the 10/9 resampler (open_stream / push_stream)
+
+
+def _kind(x):
+    if isinstance(x, dict):
+        return {k: _kind(v) for k, v in x.items()}
+    if isinstance(x, list):
+        return ["%s[%d]" % (type(x[0]).__name__ if x else "none", len(x))]
+    return type(x).__name__
+
+
+def _check_json_export(prefix, out):
+    """the per-packet JSON export (dnrp_json_export.hpp, batch_phy_t::enable_json_export) against the key tree of the
+    reference's own example file (tests/golden/json_export_keys.json, made by tests/golden/make_json_export_keys.py):
+    same file naming, entry naming, key names, nesting, order and value kinds for RADIO and PHY; the MAC section follows
+    the current source (worker_tx_rx.cpp:399-400, plcf_decoder.cpp:154-164)"""
+    gold = json.load(open(os.path.join(ROOT, "tests", "golden", "json_export_keys.json")))
+    files = sorted(f for f in os.listdir(os.path.dirname(prefix)) if f.startswith(os.path.basename(prefix)))
+    assert len(files) == out["json_files"] and files[0].endswith("_0000000000") and len(files) >= 2
+    n_entries = 0
+    for fi, name in enumerate(files):
+        d = json.load(open(os.path.join(os.path.dirname(prefix), name)))
+        assert len(d) == 8 or fi == len(files) - 1
+        for key, e in d.items():
+            assert key == gold["entry_prefix"] + str(n_entries)
+            n_entries += 1
+            got = _kind(e)
+            assert list(got) == list(gold["tree"])                                  # top level: names and order
+            for sec in ("RADIO",):
+                assert got[sec] == gold["tree"][sec]
+            for sec in ("worker_pool_config", "sync_report"):
+                assert got["PHY"][sec] == gold["tree"]["PHY"][sec], sec
+            rs, ref = got["PHY"]["rx_synced"], gold["tree"]["PHY"]["rx_synced"]
+            fixed = [k for k in ref if not k.startswith("ch_")]
+            assert [k for k in rs if not k.startswith("ch_")] == fixed and all(rs[k] == ref[k] for k in fixed)
+            Nk = e["PHY"]["rx_synced"]["N_b_OCC_plus_DC"]
+            chans = [k for k in rs if k.startswith("ch_")]
+            assert chans == ["ch_%d_%d" % (a, t) for a in range(2) for t in range(e["PHY"]["sync_report"]["N_eff_TX"])]
+            for k in chans:
+                assert rs[k] == {"re": ["int[%d]" % Nk], "im": ["int[%d]" % Nk]}
+            assert e["32fc_int32_scale"] == 100000.0 and e["PHY"]["worker_pool_config"]["L"] == 10
+            assert e["PHY"]["rx_synced"]["mcs"] == 4 and -5.0 < e["PHY"]["rx_synced"]["snr"] < 40.0
+            assert e["MAC"]["plcf"]["PLCF_type"] in (1, 2)
+            # a flat unit-gain channel (two antennas, the second rotated): magnitudes of the exported estimate near 1
+            h = (np.array(e["PHY"]["rx_synced"]["ch_0_0"]["re"]) + 1j * np.array(e["PHY"]["rx_synced"]["ch_0_0"]["im"])) / 1e5
+            assert 0.3 < np.median(np.abs(h)) < 3.0
+    # scenario 3 runs on a second batch_phy_t without export
+    assert n_entries == out["work_pdc"] + out["work_pdc_error"] - out["stream_decoded"]
 
 
 def test_multi_plan_firmware_builds_and_refuses_to_run_without_gpu(tmp_path):

@@ -167,3 +167,29 @@ def test_mimo_report(product, cfg, N_RX):
     if N_TS == 1:
         assert (rep.tm_3_7_beamforming_idx == 0).all()
     phy.close()
+
+
+@pytest.mark.parametrize("name", ["C3_b16_txdiv4_25dB", "b2_mcs4_mode_l", "txdiv2_b4_2rx_12dB"])
+def test_chestim_tap_matches_oracle(product, name):
+    """DNRP_TAP_CHESTIM (what the reference exports per packet as ch_<rx>_<ts>, rx_synced.cpp:444-480): the interpolated
+    channel after the last data field symbol, against the oracle's snapshot of chestim at that symbol"""
+    case = dict(RX_CASES[name])
+    cfg, N_RX = case["cfg"], case.get("N_RX", 1)
+    lr, stride_t = case.get("chestim_lr", True), case.get("stride", 2)
+    ps = spec.get_packet_sizes(*cfg)
+    n = 2
+    phy = product.Phy(cfg, max_batch=n, N_RX=N_RX, network_id=NET, plcf_type=1, chestim_mode_lr=lr, chestim_stride=stride_t)
+    rng = np.random.default_rng(4)
+    win, tbs, plcfs = make_windows(ps, case, n, phy.rx_stride(), rng, 1)
+    t0 = case.get("t0", 0)
+    cfo = case.get("cfo", 0.0) + case.get("cfo_err", 0.0)
+    phy.rx_pcc(win, t0=t0, cfo_fractional_rad=cfo)
+    phy.rx_pdc(n)
+    Nk = 56 * ps["b"] + 1
+    got = phy.tap(product.TAP_CHESTIM, n).reshape(n, N_RX, ps["N_eff_TX"], Nk)
+    orc = rx.RxConfig(ps, N_RX=N_RX, chestim_lr=lr, stride=stride_t)
+    for i in range(n):
+        r = orc.rx_packet(win[i], t0=t0, cfo_fractional_rad=cfo, want_H=True)
+        ref = r["H"][:, :, ps["N_DF_symb"] - 1, :]
+        assert rel_err(got[i], ref) < 2e-4, (name, i, rel_err(got[i], ref))
+    phy.close()
