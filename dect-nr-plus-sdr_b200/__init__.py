@@ -86,12 +86,13 @@ assert PDC_DTYPE.itemsize == C.sizeof(PdcReport)
 class ChannelDesc(C.Structure):
     _fields_ = [("snr_dB", C.c_float), ("net_bandwidth_norm", C.c_float), ("t0", C.c_uint32), ("mode", C.c_uint32),
                 ("seed", C.c_uint64), ("pdp_idx", C.c_uint32), ("tau_rms_ns", C.c_float), ("fD_Hz", C.c_float),
-                ("time_64", C.c_int64)]
+                ("time_64", C.c_int64), ("large_scale", C.c_float), ("clip_limit", C.c_float), ("dac_bits", C.c_uint32),
+                ("adc_bits", C.c_uint32)]
 
 
 CHANNEL_DTYPE = np.dtype([("snr_dB", "f4"), ("net_bandwidth_norm", "f4"), ("t0", "u4"), ("mode", "u4"),
-                          ("seed", "u8"), ("pdp_idx", "u4"), ("tau_rms_ns", "f4"), ("fD_Hz", "f4"), ("time_64", "i8")],
-                         align=True)
+                          ("seed", "u8"), ("pdp_idx", "u4"), ("tau_rms_ns", "f4"), ("fD_Hz", "f4"), ("time_64", "i8"),
+                          ("large_scale", "f4"), ("clip_limit", "f4"), ("dac_bits", "u4"), ("adc_bits", "u4")], align=True)
 assert CHANNEL_DTYPE.itemsize == C.sizeof(ChannelDesc)
 TAP_Y, TAP_DRS_ZF, TAP_STF_ZF, TAP_LLR_PCC, TAP_LLR_PDC, TAP_WIENER_CLASS, TAP_TB_OK, TAP_CHESTIM = 1, 2, 3, 4, 5, 6, 7, 8
 KERNEL_TURBO_DECODE_PDC, KERNEL_RX_FFT, KERNEL_RX_DEMAP_PDC, KERNEL_RX_STF, KERNEL_DERM_PDC, KERNEL_SYNC, \
@@ -148,6 +149,15 @@ def _ptr(a, dtype):
         return None
     assert a.dtype == dtype and a.flags["C_CONTIGUOUS"], (a.dtype, dtype)
     return a.ctypes.data_as(C.c_void_p)
+
+
+def large_scale_via_pathloss(tx_power_ant_0dBFS, rx_power_ant_0dBFS, distance_m, freq_Hz, same_node=False,
+                             tx_into_rx_leakage_dB=0.0):
+    """dnrp_large_scale_via_pathloss: channel_t::get_large_scale_via_pathloss (channel.cpp:53-73)"""
+    f = lib().dnrp_large_scale_via_pathloss
+    f.restype = C.c_float
+    f.argtypes = [C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_float]
+    return float(f(tx_power_ant_0dBFS, rx_power_ant_0dBFS, distance_m, freq_Hz, int(same_node), tx_into_rx_leakage_dB))
 
 
 class Phy:
@@ -426,13 +436,14 @@ class Phy:
 
     # ---- simulation channel (reference simulation/vspace.cpp:437-512, wireless/channel_{awgn,flat}.cpp)
     def channel(self, n, snr_dB=100.0, t0=0, mode=0, seed=1, net_bandwidth_norm=None, fetch=False, pdp_idx=0,
-                tau_rms_ns=0.0, fD_Hz=0.0, time_64=0):
+                tau_rms_ns=0.0, fD_Hz=0.0, time_64=0, large_scale=0.0, clip_limit=0.0, dac_bits=0, adc_bits=0):
         if net_bandwidth_norm is None:
             net_bandwidth_norm = self.resample[1] / (self.resample[0] * self.oversampling)
         descs = np.zeros(n, dtype=CHANNEL_DTYPE)
         descs["snr_dB"], descs["net_bandwidth_norm"], descs["t0"], descs["mode"] = snr_dB, net_bandwidth_norm, t0, mode
         descs["seed"] = seed
         descs["pdp_idx"], descs["tau_rms_ns"], descs["fD_Hz"], descs["time_64"] = pdp_idx, tau_rms_ns, fD_Hz, time_64
+        descs["large_scale"], descs["clip_limit"], descs["dac_bits"], descs["adc_bits"] = large_scale, clip_limit, dac_bits, adc_bits
         out = np.zeros((n, self.N_RX, self.rx_stride()), dtype=np.complex64) if fetch else None
         _check(lib().dnrp_channel_batch(self._ctx, n, descs.ctypes.data_as(C.c_void_p), _ptr(out, np.complex64)))
         return out

@@ -509,6 +509,20 @@ int dnrp_tap_read(dnrp_ctx_t* c, int tap, uint32_t n, void* dst, size_t dst_byte
     return DNRP_OK;
 }
 
+float dnrp_large_scale_via_pathloss(float tx_power_ant_0dBFS, float rx_power_ant_0dBFS, float distance_m, float freq_Hz,
+                                    int same_node, float tx_into_rx_leakage_dB) {
+    float fading_dB = tx_into_rx_leakage_dB;   // the node's own transmitter leaking into its receiver
+    if (!same_node) {
+        // pathloss::fspl (pathloss.cpp:28-38): free space, never below 0 dB, 0 for a null request
+        fading_dB = 0.0f;
+        if (distance_m > 0.0f && freq_Hz > 0.0f) {
+            const double v = 20.0 * std::log10((double)distance_m) + 20.0f * std::log10((double)freq_Hz) - 147.55;
+            fading_dB = v < 0.0 ? 0.0f : (float)v;
+        }
+    }
+    return powf(10.0f, (tx_power_ant_0dBFS - fading_dB - rx_power_ant_0dBFS) / 20.0f);   // adt::db2mag
+}
+
 int dnrp_channel_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_channel_desc_t* descs, dnrp_cf32_t* iq_rx_out) {
     DNRP_REQUIRE(c && descs, "null argument");
     DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
@@ -526,6 +540,13 @@ int dnrp_channel_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_channel_desc_t* des
         std::memset(&m, 0, sizeof(m));
         m.t0 = descs[i].t0; m.mode = descs[i].mode; m.sigma = powf(10.0f, n0_dBFS / 20.0f);
         m.seed_lo = (uint32_t)descs[i].seed; m.seed_hi = (uint32_t)(descs[i].seed >> 32);
+        DNRP_REQUIRE(descs[i].large_scale >= 0.f && descs[i].clip_limit >= 0.f && descs[i].dac_bits <= 24 && descs[i].adc_bits <= 24,
+                     "large_scale / clip_limit must not be negative, at most 24 converter bits");
+        m.large_scale = descs[i].large_scale > 0.f ? descs[i].large_scale : 1.0f;
+        m.clip = descs[i].clip_limit;
+        // hw_simulator.cpp:720-725: step 2 clip / 2^bits, only together with clipping
+        m.dac_lsb = m.clip > 0.f && descs[i].dac_bits ? 2.0f * m.clip / powf(2.0f, (float)descs[i].dac_bits) : 0.f;
+        m.adc_lsb = m.clip > 0.f && descs[i].adc_bits ? 2.0f * m.clip / powf(2.0f, (float)descs[i].adc_bits) : 0.f;
         if (descs[i].mode == 2) {
             // link.cpp:44-46 asserts these bounds
             DNRP_REQUIRE(descs[i].pdp_idx < spec::TDL_PROFILES, "pdp_idx out of bound");

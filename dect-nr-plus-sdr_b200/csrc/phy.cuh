@@ -220,6 +220,9 @@ struct chan_meta_dev_t {
     uint32_t mode;      // 0 = awgn (unit links), 1 = flat (one CN(0,1) coefficient per link and packet),
                         // 2 = doubly selective (tapped delay line, 40 sinusoids per tap and link)
     float sigma;        // standard deviation of the complex noise sample, sqrt(10^(n0_dBFS / 10))
+    float large_scale;  // magnitude gain of every link (channel_t::get_large_scale_via_pathloss), 1 = none
+    float clip;         // simulated radio (hw_simulator_t::clip_and_quantize): symmetric clipping amplitude, 0 = off
+    float dac_lsb, adc_lsb;  // quantisation steps 2 clip / 2^bits of the TX / RX samples, 0 = clip only
     uint32_t seed_lo, seed_hi;
     // mode 2: link_t::set_pdp result (host), Doppler, absolute time of the window's first sample
     uint32_t n_taps;

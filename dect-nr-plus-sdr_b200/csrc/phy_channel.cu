@@ -33,6 +33,19 @@ __device__ __forceinline__ float2 cn01(uint32_t a, uint32_t b) {
 }
 
 // grid (ceil(rx_stride / 512), N_RX, packets), 256 threads, two samples per thread
+// hw_simulator_t::clip_and_quantize (hw_simulator.cpp:710-731, simulation/hardware/clip.cpp, quantize.cpp)
+__device__ __forceinline__ float2 hw_clip_quantize(float2 v, float clip, float lsb) {
+    if (clip > 0.f) {
+        v.x = fminf(fmaxf(v.x, -clip), clip);
+        v.y = fminf(fmaxf(v.y, -clip), clip);
+        if (lsb > 0.f) {
+            v.x = roundf(__fdiv_rn(v.x, lsb)) * lsb;
+            v.y = roundf(__fdiv_rn(v.y, lsb)) * lsb;
+        }
+    }
+    return v;
+}
+
 __global__ void __launch_bounds__(256) k_channel(const channel_params_t p) {
     const uint32_t a = blockIdx.y, pkt = blockIdx.z;
     const chan_meta_dev_t m = p.meta[pkt];
@@ -61,10 +74,12 @@ __global__ void __launch_bounds__(256) k_channel(const channel_params_t p) {
         const uint32_t n = n0 + i;
         if (n >= m.t0 && n - m.t0 < p.n_samples) {
             for (uint32_t t = 0; t < p.N_TX; ++t) {
-                const float2 x = p.tx[((size_t)pkt * p.N_TX + t) * p.tx_stride + (n - m.t0)];
-                y[i] = cadd(y[i], cmul(g[t], x));
+                const float2 x = hw_clip_quantize(p.tx[((size_t)pkt * p.N_TX + t) * p.tx_stride + (n - m.t0)], m.clip, m.dac_lsb);
+                const float2 gx = cmul(g[t], x);
+                y[i] = cadd(y[i], make_float2(gx.x * m.large_scale, gx.y * m.large_scale));
             }
         }
+        y[i] = hw_clip_quantize(y[i], m.clip, m.adc_lsb);
     }
     float2* out = p.rx + ((size_t)pkt * p.N_RX + a) * p.rx_stride + n0;
     if (n0 + 1 < p.rx_stride) *reinterpret_cast<float4*>(out) = make_float4(y[0].x, y[0].y, y[1].x, y[1].y);
@@ -161,7 +176,7 @@ __global__ void __launch_bounds__(TDL_THREADS) k_channel_tdl(const channel_param
             for (uint32_t r = 0; r < TDL_R; ++r) {
                 const long long k = (long long)(base + tid + r * TDL_THREADS) - off;
                 if (k >= 0 && k < (long long)p.n_samples)
-                    y[r] = cadd(y[r], cmul(make_float2(acc[r].x * sc, acc[r].y * sc), x[k]));
+                    y[r] = cadd(y[r], cmul(make_float2(acc[r].x * sc, acc[r].y * sc), hw_clip_quantize(x[k], m.clip, m.dac_lsb)));
             }
         }
     }
@@ -172,7 +187,8 @@ __global__ void __launch_bounds__(TDL_THREADS) k_channel_tdl(const channel_param
         if (n >= p.rx_stride) continue;
         const uint4 q = philox4x32_10(make_uint4(n >> 1, a, pkt, 0u), make_uint2(m.seed_lo, m.seed_hi));
         const float2 w = (n & 1u) ? cn01(q.z, q.w) : cn01(q.x, q.y);
-        out[n] = make_float2(y[r].x + w.x * m.sigma, y[r].y + w.y * m.sigma);
+        out[n] = hw_clip_quantize(make_float2(y[r].x * m.large_scale + w.x * m.sigma, y[r].y * m.large_scale + w.y * m.sigma),
+                                  m.clip, m.adc_lsb);
     }
 }
 

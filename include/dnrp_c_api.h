@@ -374,7 +374,20 @@ typedef struct {
     float tau_rms_ns;
     float fD_Hz;
     int64_t time_64;
+    /* large-scale fading and the simulated radio's converters (all 0 = not used, the behaviour before these fields):
+     * large_scale = magnitude gain of every link, channel_t::get_large_scale_via_pathloss (channel.cpp:53-73; helper
+     * below); clip_limit = hw_simulator_t::symmetric_clipping_amplitude (1.0 in the reference, hw_simulator.hpp:116):
+     * I and Q of the TX samples are clipped and rounded to 2 clip_limit / 2^dac_bits before the channel
+     * (hw_simulator.cpp:560-566), those of the RX samples -- after the noise -- with adc_bits (hw_simulator.cpp:685-691);
+     * bits = 0: clip only */
+    float large_scale;
+    float clip_limit;
+    uint32_t dac_bits, adc_bits;
 } dnrp_channel_desc_t;
+/* channel_t::get_large_scale_via_pathloss: db2mag(tx_power_ant_0dBFS - fading - rx_power_ant_0dBFS), fading = free space
+ * path loss over distance_m at freq_Hz (pathloss.cpp:28-38) or, for same_node != 0, tx_into_rx_leakage_dB.  Host only. */
+float dnrp_large_scale_via_pathloss(float tx_power_ant_0dBFS, float rx_power_ant_0dBFS, float distance_m, float freq_Hz,
+                                    int same_node, float tx_into_rx_leakage_dB);
 
 /* reads the n packets left on the device by dnrp_tx_batch, writes the receiver's IQ windows (device);
  * iq_rx_out [n][N_RX][dnrp_rx_stride()] receives a host copy unless NULL */

@@ -164,3 +164,32 @@ void orc_channel_doubly(const cf_t* tx, long tx_stride, int N_TX, int n_samples,
             }
     }
 }
+
+/* ---- hardware effects of the simulated radio and large-scale fading (row a38 of SURVEY.md section 8) ------------------------
+ * hw_simulator_t::clip_and_quantize (hw_simulator.cpp:710-731): symmetric clipping of I and Q at clip_limit
+ * (simulation/hardware/clip.cpp:27-37), then rounding to multiples of 2 clip_limit / 2^n_bits
+ * (simulation/hardware/quantize.cpp:27-45, roundf = half away from zero); n_bits = 0: clip only; clip_limit <= 0: nothing. */
+void orc_hw_clip_quantize(cf_t* x, long n, float clip_limit, uint32_t n_bits) {
+    if (!(clip_limit > 0.0f)) return;
+    const float w = 2.0f * clip_limit / powf(2.0f, (float)n_bits);
+    for (long i = 0; i < n; ++i) {
+        float re = x[i].re < -clip_limit ? -clip_limit : (x[i].re > clip_limit ? clip_limit : x[i].re);
+        float im = x[i].im < -clip_limit ? -clip_limit : (x[i].im > clip_limit ? clip_limit : x[i].im);
+        if (n_bits > 0) { re = roundf(re / w) * w; im = roundf(im / w) * w; }
+        x[i].re = re; x[i].im = im;
+    }
+}
+/* channel_t::get_large_scale_via_pathloss (channel.cpp:53-73) with pathloss::fspl (pathloss.cpp:28-38): magnitude gain of
+ * one TX antenna into one RX antenna; same_node: the node's own TX leaking into its RX */
+float orc_large_scale_via_pathloss(float tx_power_ant_0dBFS, float rx_power_ant_0dBFS, float distance_m, float freq_Hz,
+                                   int same_node, float tx_into_rx_leakage_dB) {
+    float fading_dB;
+    if (!same_node) {
+        if (distance_m <= 0.0f || freq_Hz <= 0.0f) fading_dB = 0.0f;
+        else {
+            const double v = 20.0 * log10((double)distance_m) + 20.0f * log10((double)freq_Hz) - 147.55;
+            fading_dB = v < 0.0 ? 0.0f : (float)v;
+        }
+    } else fading_dB = tx_into_rx_leakage_dB;
+    return powf(10.0f, (tx_power_ant_0dBFS - fading_dB - rx_power_ant_0dBFS) / 20.0f);
+}

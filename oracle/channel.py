@@ -48,3 +48,31 @@ def channel_doubly(tx_iq, rx_stride, N_RX, samp_rate, t0=0, snr_dB=100.0, net_ba
     L.orc_channel_doubly(tx_iq.ctypes.data, tx_stride, N_TX, n_samples, rx.ctypes.data, rx_stride, N_RX, t0, snr_dB,
                          net_bandwidth_norm, seed, pkt, float(samp_rate), pdp_idx, tau_rms_ns, fD_Hz, time_64)
     return rx
+
+
+def hw_clip_quantize(x, clip_limit, n_bits):
+    """hw_simulator_t::clip_and_quantize on a copy of x (complex64, any shape)"""
+    L = lib()
+    y = np.array(x, dtype=np.complex64, copy=True, order="C")
+    L.orc_hw_clip_quantize.argtypes = [C.c_void_p, C.c_long, C.c_float, C.c_uint32]
+    L.orc_hw_clip_quantize.restype = None
+    L.orc_hw_clip_quantize(y.ctypes.data, y.size, float(clip_limit), int(n_bits))
+    return y
+
+
+def large_scale_via_pathloss(tx_power_ant_0dBFS, rx_power_ant_0dBFS, distance_m, freq_Hz, same_node=False,
+                             tx_into_rx_leakage_dB=0.0):
+    L = lib()
+    L.orc_large_scale_via_pathloss.restype = C.c_float
+    L.orc_large_scale_via_pathloss.argtypes = [C.c_float, C.c_float, C.c_float, C.c_float, C.c_int, C.c_float]
+    return float(L.orc_large_scale_via_pathloss(tx_power_ant_0dBFS, rx_power_ant_0dBFS, distance_m, freq_Hz, int(same_node),
+                                                tx_into_rx_leakage_dB))
+
+
+def with_hardware(fn, tx_iq, *args, large_scale=1.0, clip_limit=0.0, dac_bits=0, adc_bits=0, **kw):
+    """the simulated radio around a channel function (channel / channel_doubly): DAC clip + quantise on the TX samples
+    (hw_simulator.cpp:560-566), large-scale gain (channel.cpp:53-73), channel + noise, ADC clip + quantise on the RX
+    samples (hw_simulator.cpp:685-691)"""
+    x = hw_clip_quantize(tx_iq, clip_limit, dac_bits)
+    x = (x * np.float32(large_scale)).astype(np.complex64)
+    return hw_clip_quantize(fn(x, *args, **kw), clip_limit, adc_bits)

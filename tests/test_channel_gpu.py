@@ -115,3 +115,50 @@ def test_channel_doubly_decodes(product):
     assert res.detected.sum() >= n * 3 // 4
     assert ok.sum() >= n // 2 and (tb_out[ok] == tb[ok]).all()
     phy.close()
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+def test_large_scale_clip_and_quantise_match_oracle(product, mode):
+    """row a38 of SURVEY.md section 8: large-scale gain from the path loss (channel.cpp:53-73, pathloss.cpp:28-38) and the
+    simulated radio's converters (hw_simulator.cpp:560-566, 685-691, 710-731: symmetric clipping at 1.0, DAC / ADC
+    quantisation).  The ADC step is 2 / 2^12: a sample may fall on the other side of a rounding boundary because of fp32
+    rounding in front of it -> at most one step, on fewer than 0.1 % of the samples"""
+    cfg = CONFIGS["txdiv2_b4_mcs3"]
+    ps = spec.get_packet_sizes(*cfg)
+    n, N_RX = 2, 2
+    phy = product.Phy(cfg, max_batch=n, N_RX=N_RX, network_id=NET)
+    rng = np.random.default_rng(6)
+    tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
+    plcf = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    iq_tx, ns = phy.tx(plcf, tb, DAC_scale=2.5)        # hot enough that the DAC clips
+    assert (np.abs(iq_tx.real) > 1.0).mean() > 0.01
+    ls = product.large_scale_via_pathloss(10.0, -30.0, 25.0, 1.9e9)
+    assert abs(ls - ochan.large_scale_via_pathloss(10.0, -30.0, 25.0, 1.9e9)) < 1e-6 * ls
+    assert abs(20 * np.log10(ls) - (10.0 + 30.0 - (20 * np.log10(25.0) + 20 * np.log10(1.9e9) - 147.55))) < 1e-3
+    leak = product.large_scale_via_pathloss(10.0, -30.0, 0.0, 0.0, same_node=True, tx_into_rx_leakage_dB=60.0)
+    assert abs(leak - ochan.large_scale_via_pathloss(10.0, -30.0, 0.0, 0.0, True, 60.0)) < 1e-6 * leak
+    t0, seed, snr = 11, 0x55AA55AA12345678, 35.0
+    kw = dict(pdp_idx=1, tau_rms_ns=200.0, fD_Hz=100.0, time_64=123456) if mode == 2 else {}
+    rx = phy.channel(n, snr_dB=snr, t0=t0, mode=mode, seed=seed, fetch=True, large_scale=ls, clip_limit=1.0, dac_bits=14,
+                     adc_bits=12, **kw)
+    step = 2.0 / 2 ** 12
+    fs = cfg[0] * cfg[1] * 1.728e6
+    for i in range(n):
+        if mode == 2:
+            ref = ochan.with_hardware(ochan.channel_doubly, iq_tx[i], phy.rx_stride(), N_RX, fs, t0=t0, snr_dB=snr, seed=seed,
+                                      pkt=i, n_samples=ps["N_samples_packet"], large_scale=ls, clip_limit=1.0, dac_bits=14,
+                                      adc_bits=12, **kw)
+        else:
+            ref = ochan.with_hardware(ochan.channel, iq_tx[i], phy.rx_stride(), N_RX, t0=t0, mode=mode, snr_dB=snr, seed=seed,
+                                      pkt=i, n_samples=ps["N_samples_packet"], large_scale=ls, clip_limit=1.0, dac_bits=14,
+                                      adc_bits=12)
+        # every sample sits on the ADC grid and inside the clipping range
+        q = rx[i].view(np.float32) / np.float32(step)
+        assert np.array_equal(q, np.round(q)) and np.abs(rx[i].view(np.float32)).max() <= 1.0
+        d = np.abs(rx[i].view(np.float32) - ref.view(np.float32))
+        assert d.max() <= step * 1.001 and (d > 0).mean() < 1e-3, (mode, i, float(d.max()), float((d > 0).mean()))
+    # the fields left at 0 change nothing
+    a = phy.channel(n, snr_dB=snr, t0=t0, mode=mode, seed=seed, fetch=True, **kw)
+    b = phy.channel(n, snr_dB=snr, t0=t0, mode=mode, seed=seed, fetch=True, large_scale=1.0, **kw)
+    assert np.array_equal(a, b)
+    phy.close()
