@@ -44,6 +44,8 @@ WORKLOADS = {
     # stops at a stub for N_SS > 1 (rx_synced.cpp:1331-1333), so the CPU arm of this workload is the oracle port.
     "TM6_mu1_b16_sm4x4_16qam_r34_tdl_doubly_1_100_50_snr30":
         dict(psdef=(1, 16, 1, 2, 6, 4, 6144), N_RX=4, snr_dB=30.0, mode=2, pdp_idx=1, tau_rms_ns=100.0, fD_Hz=50.0),
+    "TM6_mu1_b16_sm4x4_qpsk_r12_tdl_doubly_1_100_50_snr30":
+        dict(psdef=(1, 16, 1, 2, 6, 1, 6144), N_RX=4, snr_dB=30.0, mode=2, pdp_idx=1, tau_rms_ns=100.0, fD_Hz=50.0),
 }
 DEFAULT_WORKLOAD = "C3_mu1_b16_txdiv4_4x4_64qam_r56_tdl_doubly_1_100_50_snr25"
 NETWORK_ID = 123456789

@@ -345,6 +345,64 @@ __device__ __forceinline__ void chan_est_rx(const rx_params_t& p, uint32_t pkt, 
     }
 }
 
+// The transmit diversity combiner uses, per stream, the MEAN of the estimates at the two subcarriers of a cell pair
+// (rx_synced.cpp:1360-1369).  Both Wiener windows cover the same pilots or are shifted by one pilot against each other
+// (the subcarriers are at most two apart, pilots four), so the mean is ONE dot product over the union window with the
+// weights 0.5 (w_k0 + w_k1): n_interp + 1 taps instead of 2 n_interp, i.e. about half the pilot loads and MACs.
+// Differs from averaging two separately rounded estimates by fp32 rounding only.
+template <int NRX>
+__device__ __forceinline__ void chan_est_rx_pair(const rx_params_t& p, uint32_t pkt, uint32_t plan, uint32_t k0, uint32_t k1,
+                                                 float2 (&h)[NRX]) {
+    const phy_dims_t& d = p.d;
+    const uint32_t base = plan & 63u, j = (plan >> 6) & 63u, row = (plan >> 12) & 31u, flip = (plan >> 17) & 1u,
+                   ts = (plan >> 18) & 7u, lr = (plan >> 21) & 1u;
+    const phy_dims_t::wiener_dev_t& W = lr ? d.wiener_lr[p.cls[(size_t)pkt * p.cls_stride + j]]
+                                           : d.wiener_l[p.cls[(size_t)pkt * p.cls_stride + j]];
+    const uint32_t o0 = base * d.Nk + k0, o1 = base * d.Nk + k1;
+    const uint32_t m0 = W.idx_pilot[o0], m1 = W.idx_pilot[o1];
+    const uint32_t mmin = min(m0, m1), d0 = m0 - mmin, d1 = m1 - mmin;
+    if (d0 + d1 > 1u) {   // windows further apart (not with the DECT pilot grid): the plain way
+        float2 t[NRX];
+        chan_est_rx<NRX>(p, pkt, plan, k0, h);
+        chan_est_rx<NRX>(p, pkt, plan, k1, t);
+#pragma unroll
+        for (int a = 0; a < NRX; ++a) h[a] = make_float2(0.5f * (h[a].x + t[a].x), 0.5f * (h[a].y + t[a].y));
+        return;
+    }
+    const uint32_t n_interp = W.n_interp, nt = n_interp + d0 + d1;
+    const float* w0 = W.weights + (uint32_t)W.idx_weight[o0] * n_interp - d0;   // tap t of the union uses w0[t - d0]
+    const float* w1 = W.weights + (uint32_t)W.idx_weight[o1] * n_interp - d1;
+    const uint32_t stride_a = d.N_eff_TX * d.n_drs * d.NP;
+    const float2* hz_pkt = p.hzf + (size_t)pkt * d.N_RX * stride_a;
+    const uint32_t off_row = (ts * d.n_drs + row) * d.NP;
+#pragma unroll
+    for (int a = 0; a < NRX; ++a) h[a] = make_float2(0.f, 0.f);
+    // lr: tap m sits on side (m & 1) ^ flip at index m >> 1 (two running offsets); l: plain index
+    uint32_t off_e = off_row + (lr ? (flip ? d.NP : 0u) + ((mmin + 1) >> 1) : 0u);
+    uint32_t off_o = off_row + (lr ? (flip ? 0u : d.NP) + (mmin >> 1) : 0u);
+    uint32_t off_l = off_row + mmin;
+    bool odd = (mmin & 1u) != 0u;
+    for (uint32_t t = 0; t < nt; ++t) {
+        uint32_t off;
+        if (lr) {
+            off = odd ? off_o : off_e;
+            if (odd) ++off_o; else ++off_e;
+            odd = !odd;
+        } else {
+            off = off_l++;
+        }
+        const float a0 = (t >= d0 && t - d0 < n_interp) ? w0[t] : 0.f;
+        const float a1 = (t >= d1 && t - d1 < n_interp) ? w1[t] : 0.f;
+        const float wi = 0.5f * (a0 + a1);
+#pragma unroll
+        for (int a = 0; a < NRX; ++a) {
+            const float2 v = hz_pkt[off + a * stride_a];
+            h[a].x += wi * v.x;
+            h[a].y += wi * v.y;
+        }
+    }
+}
+
 // float -> int16 like a C cast (toward zero), saturating
 __device__ __forceinline__ float to_short(float v) {
     v = truncf(v);
@@ -432,17 +490,8 @@ __global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_dema
             float den = 0.f;
             // per antenna: h0 = mean of stream A's estimates at the two cells, h1 = the same for stream B
             float2 h0[NRX], h1[NRX];
-            {
-                float2 t[NRX];
-                chan_est_rx<NRX>(p, pkt, planA, k0, h0);
-                chan_est_rx<NRX>(p, pkt, planA, k1, t);
-#pragma unroll
-                for (int a = 0; a < NRX; ++a) h0[a] = make_float2(0.5f * (h0[a].x + t[a].x), 0.5f * (h0[a].y + t[a].y));
-                chan_est_rx<NRX>(p, pkt, planB, k0, h1);
-                chan_est_rx<NRX>(p, pkt, planB, k1, t);
-#pragma unroll
-                for (int a = 0; a < NRX; ++a) h1[a] = make_float2(0.5f * (h1[a].x + t[a].x), 0.5f * (h1[a].y + t[a].y));
-            }
+            chan_est_rx_pair<NRX>(p, pkt, planA, k0, k1, h0);
+            chan_est_rx_pair<NRX>(p, pkt, planB, k0, k1, h1);
 #pragma unroll
             for (int a = 0; a < NRX; ++a) {
                 const float2* Y = p.Y + (((size_t)pkt * NRX + a) * d.N_DF + (l - 1)) * d.Nk;
