@@ -573,7 +573,75 @@ static inline int16_t sat16(int v) { return (int16_t)(v > 32767 ? 32767 : v < -3
  * u = ns0 ^ ns2 ^ c, z = ns0 ^ ns1 ^ c.  LLR > 0 <=> bit 1; branch metric (u ? x : 0) + (z ? y : 0); metrics in int32,
  * normalised to state 0 every step (state 0 is reachable at every step in both directions). */
 #define TD_BIG (1 << 22)
+#ifdef __AVX2__
+#include <immintrin.h>
+/* The same arithmetic with the eight state metrics of a trellis step in one 256-bit register (8 x int32): what a production
+ * build gets from srsRAN's SIMD decoders, here only to make the CPU baseline less of a straw man.  Bit-identical to the
+ * scalar form below (int32 add / max, same normalisation and clamps; tests/test_ref_cpu.py pins both against the oracle). */
+static inline int32_t hmax8(__m256i v) {
+    __m128i m = _mm_max_epi32(_mm256_castsi256_si128(v), _mm256_extracti128_si256(v, 1));
+    m = _mm_max_epi32(m, _mm_shuffle_epi32(m, 0x4e));
+    m = _mm_max_epi32(m, _mm_shuffle_epi32(m, 0xb1));
+    return _mm_cvtsi128_si32(m);
+}
 static void map_dec(const int16_t* x, const int16_t* y, const int16_t* tail, uint32_t K, int32_t* alpha, int16_t* out) {
+    int32_t ps0[8], ps1[8], pg0[8], pg1[8], nu0[8], nu1[8], gu0[8], gu1[8];
+    for (int ns = 0; ns < 8; ++ns) {   /* predecessors of every next state (forward) */
+        const int n0 = ns & 1, n1 = (ns >> 1) & 1, n2 = (ns >> 2) & 1;
+        ps0[ns] = n1 | (n2 << 1);            pg0[ns] = ((n0 ^ n2) << 1) | (n0 ^ n1);
+        ps1[ns] = n1 | (n2 << 1) | 4;        pg1[ns] = ((n0 ^ n2 ^ 1) << 1) | (n0 ^ n1 ^ 1);
+    }
+    for (int st = 0; st < 8; ++st) {   /* successors of every state for u = 0, 1 (backward) */
+        const int s0 = st & 1, s1 = (st >> 1) & 1, s2 = (st >> 2) & 1;
+        for (int u = 0; u < 2; ++u) {
+            const int fb = u ^ s1 ^ s2, z = fb ^ s0 ^ s2, ns = fb | (s0 << 1) | (s1 << 2);
+            if (u) { nu1[st] = ns; gu1[st] = 2 | z; } else { nu0[st] = ns; gu0[st] = z; }
+        }
+    }
+    const __m256i iPS0 = _mm256_loadu_si256((const __m256i*)ps0), iPS1 = _mm256_loadu_si256((const __m256i*)ps1);
+    const __m256i iPG0 = _mm256_loadu_si256((const __m256i*)pg0), iPG1 = _mm256_loadu_si256((const __m256i*)pg1);
+    const __m256i iNU0 = _mm256_loadu_si256((const __m256i*)nu0), iNU1 = _mm256_loadu_si256((const __m256i*)nu1);
+    const __m256i iGU0 = _mm256_loadu_si256((const __m256i*)gu0), iGU1 = _mm256_loadu_si256((const __m256i*)gu1);
+    const __m256i vmin = _mm256_set1_epi32(-TD_BIG), zero = _mm256_setzero_si256();
+    __m256i a = _mm256_setr_epi32(0, -TD_BIG, -TD_BIG, -TD_BIG, -TD_BIG, -TD_BIG, -TD_BIG, -TD_BIG);
+    _mm256_storeu_si256((__m256i*)alpha, a);
+    for (uint32_t k = 0; k < K; ++k) {
+        const int32_t xv = x[k], yv = y[k];
+        const __m256i g = _mm256_setr_epi32(0, yv, xv, xv + yv, 0, yv, xv, xv + yv);
+        const __m256i m0 = _mm256_add_epi32(_mm256_permutevar8x32_epi32(a, iPS0), _mm256_permutevar8x32_epi32(g, iPG0));
+        const __m256i m1 = _mm256_add_epi32(_mm256_permutevar8x32_epi32(a, iPS1), _mm256_permutevar8x32_epi32(g, iPG1));
+        const __m256i t = _mm256_max_epi32(m0, m1);
+        a = _mm256_max_epi32(_mm256_sub_epi32(t, _mm256_permutevar8x32_epi32(t, zero)), vmin);
+        _mm256_storeu_si256((__m256i*)(alpha + 8 * (k + 1)), a);
+    }
+    int32_t b8[8], bn8[8];
+    for (int st = 0; st < 8; ++st) b8[st] = st == 0 ? 0 : -TD_BIG;
+    for (int t = 2; t >= 0; --t) {   /* termination, three steps: scalar */
+        for (int st = 0; st < 8; ++st) {
+            const int u = ((st >> 1) & 1) ^ ((st >> 2) & 1), z = (st & 1) ^ ((st >> 2) & 1), ns = (st << 1) & 7;
+            const int32_t v = b8[ns] + (u ? tail[2 * t] : 0) + (z ? tail[2 * t + 1] : 0);
+            bn8[st] = v < -TD_BIG ? -TD_BIG : v;
+        }
+        memcpy(b8, bn8, sizeof(b8));
+    }
+    __m256i b = _mm256_loadu_si256((const __m256i*)b8);
+    for (int k = (int)K - 1; k >= 0; --k) {
+        const __m256i ak = _mm256_loadu_si256((const __m256i*)(alpha + 8 * k));
+        const int32_t xv = x[k], yv = y[k];
+        const __m256i g = _mm256_setr_epi32(0, yv, xv, xv + yv, 0, yv, xv, xv + yv);
+        const __m256i bm0 = _mm256_add_epi32(_mm256_permutevar8x32_epi32(b, iNU0), _mm256_permutevar8x32_epi32(g, iGU0));
+        const __m256i bm1 = _mm256_add_epi32(_mm256_permutevar8x32_epi32(b, iNU1), _mm256_permutevar8x32_epi32(g, iGU1));
+        const int32_t l0 = hmax8(_mm256_add_epi32(ak, bm0)), l1 = hmax8(_mm256_add_epi32(ak, bm1));
+        out[k] = sat16(l1 - l0);
+        const __m256i bn = _mm256_max_epi32(bm0, bm1);
+        b = _mm256_max_epi32(_mm256_sub_epi32(bn, _mm256_permutevar8x32_epi32(bn, zero)), vmin);
+    }
+}
+#define map_dec_scalar map_dec_unused
+#else
+#define map_dec_scalar map_dec
+#endif
+__attribute__((unused)) static void map_dec_scalar(const int16_t* x, const int16_t* y, const int16_t* tail, uint32_t K, int32_t* alpha, int16_t* out) {
     /* predecessor pairs of every next state: [ns][c] -> (s, u, z) */
     int ps[8][2], pg[8][2];
     for (int ns = 0; ns < 8; ++ns)
