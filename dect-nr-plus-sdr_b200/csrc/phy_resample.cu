@@ -67,11 +67,105 @@ __global__ void __launch_bounds__(RS_THREADS) k_resample(const resample_params_t
     for (uint32_t m = z0 + tid; m < z1; m += RS_THREADS) y[m] = make_float2(0.f, 0.f);
 }
 
+// ---- register-blocked form for the common ratios (10/9 and 9/10 at the DECT rate): the outputs m, m + L, m + 2L, m + 3L
+// share their polyphase branch (p = delay + m M, (m + L) M = m M + L M: same p mod L) and their input windows overlap
+// (shift M < SL), so a thread that computes all four keeps the SL taps in registers and loads every input sample once:
+// 3 M + SL sample loads + SL tap loads per four outputs instead of 4 SL of each.  Every output is accumulated in the
+// same order as in k_resample (tap 0 first): bit-identical results.
+template <int L, int M, int SL>
+__global__ void __launch_bounds__(RS_THREADS) k_resample_blk(const resample_params_t p, uint32_t span_max) {
+    constexpr int R = 4, G = RS_THREADS / L, TILE = G * L * R;
+    extern __shared__ float2 s_x[];
+    float* s_t = reinterpret_cast<float*>(s_x + span_max);
+    const uint32_t tile0 = blockIdx.x * TILE, a = blockIdx.y, pkt = blockIdx.z, tid = threadIdx.x;
+    const int32_t start = p.start ? p.start[(size_t)pkt * p.start_stride_words] : 0;
+    const long long avail = (long long)p.in_stride - start;
+    const uint32_t n_in = avail <= 0 ? 0u : (avail < (long long)p.n_in ? (uint32_t)avail : p.n_in);
+    const float2* x = p.in + ((size_t)pkt * p.n_ant + a) * p.in_stride + start;
+    float2* y = p.out + ((size_t)pkt * p.n_ant + a) * p.out_stride;
+    const uint32_t m_end = min(tile0 + (uint32_t)TILE, p.n_out);
+    if (tile0 < p.n_out) {
+        const uint32_t p_lo = p.delay + tile0 * M, p_hi = p.delay + (m_end - 1) * M;
+        const int32_t i_lo = (int32_t)(p_lo / L) - (int32_t)(SL - 1);
+        const uint32_t span = (uint32_t)((int32_t)(p_hi / L) - i_lo + 1);
+        for (uint32_t i = tid; i < span; i += RS_THREADS) {
+            const int32_t idx = i_lo + (int32_t)i;
+            s_x[i] = (idx >= 0 && (uint32_t)idx < n_in) ? x[idx] : make_float2(0.f, 0.f);
+        }
+        for (uint32_t i = tid; i < SL * L; i += RS_THREADS) s_t[i] = p.taps[i];
+        __syncthreads();
+        float ph0 = 0.f, inc = 0.f;
+        bool mix = false;
+        if (p.meta) {
+            ph0 = p.meta[pkt].iq_phase_rad; inc = p.meta[pkt].iq_phase_increment;
+            mix = ph0 != 0.f || inc != 0.f;
+        }
+        const uint32_t m0 = tile0 + (tid / L) * (L * R) + tid % L;
+        if (tid < G * L && m0 < m_end) {
+            const uint32_t pp = p.delay + m0 * M, l = pp % L;
+            const float2* v = s_x + ((int32_t)(pp / L) - i_lo);   // sample of tap 0 of output m0; output j: v[j M]
+            float c[SL];
+#pragma unroll
+            for (int k = 0; k < SL; ++k) c[k] = s_t[l + k * L];
+            float2 acc[R];
+#pragma unroll
+            for (int j = 0; j < R; ++j) acc[j] = make_float2(0.f, 0.f);
+            // input offset e relative to v, newest first: output j uses it with tap k = j M - e
+#pragma unroll
+            for (int e = (R - 1) * M; e >= -(SL - 1); --e) {
+                // outputs beyond the tile's last one read samples that were not staged: their sums are never stored,
+                // the reads stay inside the shared array (span_max is sized for a full tile)
+                const float2 sv = v[e];
+#pragma unroll
+                for (int j = 0; j < R; ++j) {
+                    const int k = j * M - e;
+                    if (k >= 0 && k < SL) {
+                        acc[j].x = fmaf(c[k], sv.x, acc[j].x);
+                        acc[j].y = fmaf(c[k], sv.y, acc[j].y);
+                    }
+                }
+            }
+#pragma unroll
+            for (int j = 0; j < R; ++j) {
+                const uint32_t m = m0 + j * L;
+                if (m >= m_end) break;
+                float re = acc[j].x, im = acc[j].y;
+                if (mix) {
+                    double ph = (double)ph0 + (double)inc * (double)m;
+                    ph -= 6.283185307179586476925 * rint(ph * 0.15915494309189533577);
+                    float sn, cs;
+                    sincosf((float)ph, &sn, &cs);
+                    const float r2 = re * cs - im * sn;
+                    im = re * sn + im * cs;
+                    re = r2;
+                }
+                y[m] = make_float2(re, im);
+            }
+        }
+    }
+    const uint32_t z0 = max(tile0, p.n_out), z1 = min(tile0 + (uint32_t)TILE, p.n_fill);
+    for (uint32_t m = z0 + tid; m < z1; m += RS_THREADS) y[m] = make_float2(0.f, 0.f);
+}
+
+template <int L, int M, int SL>
+static cudaError_t launch_resample_blk(const resample_params_t& p, uint32_t n_packets, uint32_t n_total, cudaStream_t st) {
+    constexpr uint32_t TILE = (RS_THREADS / L) * L * 4;
+    const uint32_t span_max = (TILE * M) / L + SL + 2 + 4 * M;   // + the reach of the unused partial outputs
+    const size_t smem = (size_t)span_max * sizeof(float2) + (size_t)SL * L * sizeof(float);
+    cudaError_t e = cudaFuncSetAttribute(k_resample_blk<L, M, SL>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (e != cudaSuccess) return e;
+    k_resample_blk<L, M, SL><<<dim3((n_total + TILE - 1) / TILE, p.n_ant, n_packets), RS_THREADS, smem, st>>>(p, span_max);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_resample(const resample_params_t& p, uint32_t n_packets, cudaStream_t st) {
     if (n_packets == 0) return cudaSuccess;
     const uint32_t n_total = p.n_out > p.n_fill ? p.n_out : p.n_fill;
     if (n_total == 0) return cudaSuccess;
     if ((uint64_t)p.delay + (uint64_t)p.n_out * p.M >= (1ull << 31)) return cudaErrorInvalidValue;
+    // the ratios of the reference's radio configurations (hardware = 10/9 DECT rate, resampler_param.hpp) at oversampling 1
+    if (p.L == 9 && p.M == 10 && p.SL == 25) return launch_resample_blk<9, 10, 25>(p, n_packets, n_total, st);
+    if (p.L == 10 && p.M == 9 && p.SL == 23) return launch_resample_blk<10, 9, 23>(p, n_packets, n_total, st);
     const uint32_t span_max = (RS_TILE * p.M) / p.L + p.SL + 2;
     const size_t smem = (size_t)span_max * sizeof(float2) + (size_t)p.SL * p.L * sizeof(float);
     cudaError_t e = cudaFuncSetAttribute(k_resample, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
