@@ -95,6 +95,17 @@ int run_channel(dnrp_ctx* c, uint32_t n) {
 
 int run_sync(dnrp_ctx* c, uint32_t n, uint32_t search_length, bool hand_over) {
     const phy_dims_t& d = c->dims;
+    {
+        // the coarse peak stage keeps prefix sums over two STFs in shared memory; at oversampling factors that make the
+        // STF longer than about 8000 samples this no longer fits: refuse with a reason instead of a launch failure
+        int lim = 0;
+        DNRP_CUDA(cudaDeviceGetAttribute(&lim, cudaDevAttrMaxSharedMemoryPerBlockOptin, c->device));
+        if (sync_peak_smem(d, c->sync_n_steps) > (size_t)lim || (!c->sync_fft_n && 2 * ((uint64_t)d.pat_len_os * c->cfg.resample_L / c->cfg.resample_M) + 1 > 4096)) {
+            set_last_error("packet synchronisation is not available for an STF of " + std::to_string(d.stf_len_os) +
+                           " samples (oversampling too high for the shared-memory search); hand sync reports to dnrp_rx_pcc_batch");
+            return DNRP_ERR_INVALID;
+        }
+    }
     sync_params_t p{};
     p.d = d;
     const size_t off = c->off;

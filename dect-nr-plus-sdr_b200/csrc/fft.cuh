@@ -82,7 +82,7 @@ __device__ __forceinline__ void dft16(float2 (&v)[16]) {
 template <bool INV, int R, bool POW2, bool PAD>
 __device__ __forceinline__ void fft_pass(const float2* __restrict__ x, float2* __restrict__ y, uint32_t N,
                                          uint32_t Ns, uint32_t log2Ns, const float2* __restrict__ table, bool pin_, bool pout_,
-                                         uint32_t tid = threadIdx.x, uint32_t nthr = blockDim.x) {
+                                         uint32_t tid = threadIdx.x, uint32_t nthr = blockDim.x, uint32_t tmul = 1) {
     const bool pin = PAD && pin_, pout = PAD && pout_;   // PAD = false: plain buffers, no index selects in the code
     const uint32_t M = N / R;
     const uint32_t tstep = POW2 ? M >> log2Ns : N / (Ns * R);  // W_{Ns*R}^k = W_N^{k*tstep}
@@ -95,7 +95,7 @@ __device__ __forceinline__ void fft_pass(const float2* __restrict__ x, float2* _
 #pragma unroll
         for (int r = 0; r < R; ++r) v[r] = xj[r * xs];
         if (Ns != 1) {
-            const uint32_t kt = k * tstep;
+            const uint32_t kt = k * tstep * tmul;   // tmul: the table belongs to a transform tmul times longer
 #pragma unroll
             for (int r = 1; r < R; ++r) v[r] = cmul(v[r], tw<INV>(table, kt * r));
         }
@@ -209,6 +209,71 @@ __device__ float2* group_fft16(float2 (&v)[16], float2* a, float2* b, uint32_t N
     }
 #undef DNRP_GFFT_PASS
     return a;
+}
+
+// ---- transforms longer than 4096 (6144 ... 16384: a packet received at several times its own bandwidth, tx_rx.hpp:66-69):
+// two full ping-pong buffers no longer fit the shared memory of a block, so N = 16 M is split four-step style and done
+// IN PLACE in one array a[N]:
+//   step A  for every column n2 < M: 16-point DFT over x[n2 + M n1], times W_N^(n2 k1), stored at a[k1 M + n2]
+//           (the same 16 positions the column was read from);
+//   step B  for every row k1 < 16: M-point FFT of a[k1 M .. k1 M + M) through two small padded scratch buffers
+//           (s1, s2: fft_buf_len(M) each), back into the row.
+// Result: X[k1 + 16 k2] = a[k1 M + k2], i.e. bin k sits at big_fft_at(k, M).  Shared memory N + 2 fft_buf_len(M).
+__host__ __device__ __forceinline__ bool fft_is_big(uint32_t N) { return N > 4096; }
+__device__ __forceinline__ uint32_t big_fft_at(uint32_t k, uint32_t M) { return (k & 15u) * M + (k >> 4); }
+
+// step A for one column held in registers: v[n1] = x[n2 + M n1] -> a[k1 M + n2]
+template <bool INV>
+__device__ __forceinline__ void big_fft_col(float2 (&v)[16], float2* a, uint32_t n2, uint32_t M, const float2* __restrict__ table) {
+    dft16<INV>(v);
+    a[n2] = v[0];
+#pragma unroll
+    for (int k1 = 1; k1 < 16; ++k1) a[k1 * M + n2] = cmul(v[k1], tw<INV>(table, n2 * k1));   // n2 k1 < N
+}
+
+// step B: all nthr threads (ids tid) of the block / group take part; contains __syncthreads()
+template <bool INV>
+__device__ void big_fft_rows(float2* a, float2* s1, float2* s2, uint32_t N, const float2* __restrict__ table, uint32_t tid,
+                             uint32_t nthr, bool active) {
+    const uint32_t M = N / 16;
+    __syncthreads();
+    for (uint32_t k1 = 0; k1 < 16; ++k1) {
+        float2* row = a + k1 * M;
+        const float2* src = row;
+        uint32_t Ns = 1, lg = 0, rem = M, pass = 0;
+#define DNRP_BFFT_PASS(R, P2, LGINC)                                                                              \
+        {                                                                                                         \
+            const bool last = rem == R;                                                                           \
+            float2* dst = last ? row : ((pass & 1) ? s2 : s1);                                                    \
+            if (active) fft_pass<INV, R, P2, true>(src, dst, M, Ns, lg, table, pass != 0, !last, tid, nthr, 16);  \
+            Ns *= R; lg += LGINC; rem /= R; ++pass; src = dst;                                                    \
+            __syncthreads();                                                                                      \
+        }
+        while (rem % 16 == 0 && rem > 16) DNRP_BFFT_PASS(16, true, 4)   // never as the only pass: row -> row would alias
+        while (rem % 4 == 0) DNRP_BFFT_PASS(4, true, 2)
+        if (rem % 2 == 0) DNRP_BFFT_PASS(2, true, 1)
+        bool pow2 = true;
+        while (rem % 3 == 0) {
+            if (pow2) DNRP_BFFT_PASS(3, true, 0)
+            else DNRP_BFFT_PASS(3, false, 0)
+            pow2 = false;
+        }
+#undef DNRP_BFFT_PASS
+    }
+}
+
+// whole transform of a[0..N) in shared memory (block-wide; every thread calls)
+template <bool INV>
+__device__ void big_fft(float2* a, float2* s1, float2* s2, uint32_t N, const float2* __restrict__ table) {
+    const uint32_t M = N / 16;
+    __syncthreads();
+    for (uint32_t n2 = threadIdx.x; n2 < M; n2 += blockDim.x) {
+        float2 v[16];
+#pragma unroll
+        for (int n1 = 0; n1 < 16; ++n1) v[n1] = a[n2 + n1 * M];
+        big_fft_col<INV>(v, a, n2, M, table);
+    }
+    big_fft_rows<INV>(a, s1, s2, N, table, threadIdx.x, blockDim.x, true);
 }
 
 }  // namespace dnrp

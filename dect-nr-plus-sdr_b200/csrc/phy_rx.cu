@@ -43,16 +43,21 @@ __device__ __forceinline__ uint32_t bin_of_k(uint32_t k, const phy_dims_t& d) {
 
 // ---- STF stage, one block per packet (rx_synced.cpp:503-709, estimator_sto.cpp:47-173,
 // estimator_snr.cpp:48-145)
+template <bool BIG>
 __global__ void __launch_bounds__(256) k_rx_stf(const rx_params_t p) {
     extern __shared__ __align__(16) float2 sm[];
     const phy_dims_t& d = p.d;
     const uint32_t pkt = blockIdx.x, tid = threadIdx.x, nthr = blockDim.x;
     rx_state_t& st = p.state[pkt];
     const uint32_t NS = d.N_OCC / 4;
-    float2* S = sm;                      // [stf_len_os] derotated STF with the cover sequence undone
-    float2* X = S + d.stf_len_os;        // [N_os]
-    float2* Yb = X + fft_buf_len(d.N_os);   // X, Yb: [fft_buf_len(N_os)]
-    float2* H = Yb + fft_buf_len(d.N_os);   // [N_RX][NS] zero-forced STF cells
+    // N_os <= 4096: the derotated STF is staged once (S) and read three times; longer transforms (fft.cuh, four-step in
+    // place) have no room for it: the samples are derotated from global memory again where they are needed
+    constexpr bool big = BIG;
+    const uint32_t Mb = d.N_os / 16;
+    float2* S = sm;                      // [stf_len_os] derotated STF with the cover sequence undone (not when big)
+    float2* X = big ? sm : S + d.stf_len_os;   // [N_os]
+    float2* Yb = X + (big ? d.N_os : fft_buf_len(d.N_os));   // ping-pong partner of X, or the two row scratch buffers
+    float2* H = Yb + (big ? 2 * fft_buf_len(Mb) : fft_buf_len(d.N_os));   // [N_RX][NS] zero-forced STF cells
     __shared__ float2 s_red[8];
     __shared__ float s_ang[8];
 
@@ -67,27 +72,57 @@ __global__ void __launch_bounds__(256) k_rx_stf(const rx_params_t p) {
         float2 pw = make_float2(0.f, 0.f);
         float2 w = rot((double)inc0 * (double)tid);
         const float2 ws = rot((double)inc0 * (double)nthr);
-        for (uint32_t n = tid; n < d.stf_len_os; n += nthr) {
-            float2 v = cmul(x[n], w);
-            w = cmul(w, ws);
-            pw.x += v.x * v.x + v.y * v.y;
-            const float cs = c[n / d.pat_len_os];
-            S[n] = make_float2(v.x * cs, v.y * cs);
+        const uint32_t npair = (d.n_pat - 1) * d.pat_len_os;
+        float2 cr = make_float2(0.f, 0.f);
+        if (big) {
+            const float2 wp = rot((double)inc0 * (double)d.pat_len_os);   // one pattern further
+            for (uint32_t n = tid; n < d.stf_len_os; n += nthr) {
+                const float2 v = cmul(x[n], w);
+                pw.x += v.x * v.x + v.y * v.y;
+                if (n < npair) {
+                    const float cc = c[n / d.pat_len_os] * c[n / d.pat_len_os + 1];
+                    const float2 v2 = cmul(x[n + d.pat_len_os], cmul(w, wp));
+                    const float2 pr = cmulc(v, v2);
+                    cr = cadd(cr, make_float2(pr.x * cc, pr.y * cc));
+                }
+                w = cmul(w, ws);
+            }
+        } else {
+            for (uint32_t n = tid; n < d.stf_len_os; n += nthr) {
+                float2 v = cmul(x[n], w);
+                w = cmul(w, ws);
+                pw.x += v.x * v.x + v.y * v.y;
+                const float cs = c[n / d.pat_len_os];
+                S[n] = make_float2(v.x * cs, v.y * cs);
+            }
         }
         pw = block_sum2(pw, s_red);
         if (tid == 0 && !(st.rms[a] > 0.f)) st.rms[a] = sqrtf(pw.x / (float)d.stf_len_os);
         // residual CFO: sum over pattern pairs of <pattern j, conj(pattern j+1)> (rx_synced.cpp:536-550)
-        float2 cr = make_float2(0.f, 0.f);
-        const uint32_t npair = (d.n_pat - 1) * d.pat_len_os;
-        for (uint32_t n = tid; n < npair; n += nthr) cr = cadd(cr, cmulc(S[n], S[n + d.pat_len_os]));
+        if (!big)
+            for (uint32_t n = tid; n < npair; n += nthr) cr = cadd(cr, cmulc(S[n], S[n + d.pat_len_os]));
         cr = block_sum2(cr, s_red);
         corr = cadd(corr, cr);
         // FFT of the last N_os samples, un-mirror, scale, zero-forcing at the STF cells
-        for (uint32_t n = tid; n < d.N_os; n += nthr) X[n] = S[d.stf_cp_os + n];
-        const float2* F = block_fft<false>(X, Yb, d.N_os, d.twiddle);
+        const float2* F;
+        if (big) {
+            float2 w2 = rot((double)inc0 * (double)(d.stf_cp_os + tid));
+            for (uint32_t n = tid; n < d.N_os; n += nthr) {
+                const float cs = c[(d.stf_cp_os + n) / d.pat_len_os];
+                const float2 v = cmul(x[d.stf_cp_os + n], w2);
+                w2 = cmul(w2, ws);
+                X[n] = make_float2(v.x * cs, v.y * cs);
+            }
+            big_fft<false>(X, Yb, Yb + fft_buf_len(Mb), d.N_os, d.twiddle);
+            F = X;   // bin k at big_fft_at(k, Mb)
+        } else {
+            for (uint32_t n = tid; n < d.N_os; n += nthr) X[n] = S[d.stf_cp_os + n];
+            F = block_fft<false>(X, Yb, d.N_os, d.twiddle);
+        }
         for (uint32_t i = tid; i < NS; i += nthr) {
             const uint32_t k = stf_cell_k(i, d.N_OCC);
-            const float2 y = F[bin_of_k(k, d)];
+            const uint32_t bin = bin_of_k(k, d);
+            const float2 y = F[big ? big_fft_at(bin, Mb) : bin];
             const float sg = 0.70710678118654752f * (float)d.stf_sign[k];
             // y / (sg + j*sg) = y * conj(ref) / |ref|^2, |ref|^2 = 1
             H[a * NS + i] = cmulc(make_float2(y.x * fscale, y.y * fscale), make_float2(sg, sg));
@@ -161,7 +196,9 @@ __device__ __forceinline__ float drs_sign_dev(const phy_dims_t& d, uint32_t l, u
 // DRS symbols also deliver the zero-forced pilots and their SNR sums (rx_synced.cpp:773-861, estimator_snr.cpp:76-86).
 // Every thread loads its 16 samples (stride N_os / 16: coalesced across the group) straight into registers, derotates
 // them there and runs the first radix-16 pass without touching shared memory (fft.cuh, group_fft16).
-__global__ void __launch_bounds__(256) k_rx_fft(const rx_params_t p, uint32_t GT, uint32_t groups) {
+// BIG (N_os > 4096): one group of N_os / 16 (up to 1024) threads per block, four-step in-place transform (fft.cuh).
+template <bool BIG>
+__global__ void __launch_bounds__(BIG ? 1024 : 256) k_rx_fft(const rx_params_t p, uint32_t GT, uint32_t groups) {
     extern __shared__ __align__(16) float2 sm[];
     const phy_dims_t& d = p.d;
     const uint32_t grp = threadIdx.x / GT, tid = threadIdx.x - grp * GT, nthr = GT;
@@ -170,9 +207,12 @@ __global__ void __launch_bounds__(256) k_rx_fft(const rx_params_t p, uint32_t GT
     const bool active = grp < groups && item < d.N_DF * d.N_RX;
     const uint32_t l = (active ? item / d.N_RX : 0) + 1, a = active ? item % d.N_RX : 0;
     const rx_state_t& st = p.state[pkt];
-    const uint32_t blen = fft_buf_len(d.N_os);
+    // per group: two ping-pong buffers of fft_buf_len(N_os); BIG: the array of N_os, two row scratch buffers and the
+    // output symbol (Nk)
+    const uint32_t Mb = d.N_os / 16;
+    const uint32_t blen = BIG ? (d.N_os + 2 * fft_buf_len(Mb) + d.Nk + 1) / 2 : fft_buf_len(d.N_os);
     float2* A = sm + (size_t)grp * 2 * blen;
-    float2* B = A + blen;
+    float2* B = BIG ? A + d.N_os : A + blen;
     float* s_part = reinterpret_cast<float*>(sm + (size_t)groups * 2 * blen);   // [blockDim][2] SNR partial sums
 
     const uint32_t n0 = d.stf_len_os + (l - 1) * d.sym_len_os + d.cp_os;  // relative to the first STF sample
@@ -190,19 +230,28 @@ __global__ void __launch_bounds__(256) k_rx_fft(const rx_params_t p, uint32_t GT
             w = cmul(w, ws);
         }
     }
-    const float2* F = group_fft16<false>(v, A, B, d.N_os, d.twiddle, tid, nthr, active);
+    const float2* F;
+    if constexpr (BIG) {
+        if (active) big_fft_col<false>(v, A, tid, Mb, d.twiddle);   // thread tid holds column n2 = tid
+        big_fft_rows<false>(A, B, B + fft_buf_len(Mb), d.N_os, d.twiddle, tid, nthr, active);
+        F = A;   // bin k at big_fft_at(k, Mb)
+    } else {
+        F = group_fft16<false>(v, A, B, d.N_os, d.twiddle, tid, nthr, active);
+    }
 
     float2 sn = make_float2(0.f, 0.f);
     bool any = false;
     if (active) {
         const float fscale = sqrtf((float)d.N_OCC) / (float)d.N_os;
         float2* Yout = p.Y + (((size_t)pkt * d.N_RX + a) * d.N_DF + (l - 1)) * d.Nk;
-        float2* Ys = (float2*)(F == A ? B : A);  // keep the output symbol in shared for the pilot stage
+        // keep the output symbol in shared for the pilot stage
+        float2* Ys = BIG ? B + 2 * fft_buf_len(Mb) : (float2*)(F == A ? B : A);
         float2 wk = rot((double)st.sto_inc * (double)((int)tid - (int)(d.N_OCC / 2)));
         const float2 wks = rot((double)st.sto_inc * (double)nthr);
         wk = make_float2(wk.x * fscale, wk.y * fscale);
         for (uint32_t k = tid; k < d.Nk; k += nthr) {
-            const float2 y = cmul(F[bin_of_k(k, d)], wk);
+            const uint32_t bin = bin_of_k(k, d);
+            const float2 y = cmul(F[BIG ? big_fft_at(bin, Mb) : bin], wk);
             wk = cmul(wk, wks);
             Yout[k] = y;
             Ys[k] = y;
@@ -210,7 +259,7 @@ __global__ void __launch_bounds__(256) k_rx_fft(const rx_params_t p, uint32_t GT
     }
     __syncthreads();
     if (active) {
-        const float2* Ys = (F == A ? B : A);
+        const float2* Ys = BIG ? B + 2 * fft_buf_len(Mb) : (F == A ? B : A);
         // ---- DRS of this symbol (if any): stream ts at occurrence n
         for (uint32_t ts = 0; ts < d.N_eff_TX; ++ts) {
             const uint32_t lt = l - 1 - ts / 4;  // symbols since the first DRS symbol of this stream
@@ -809,28 +858,45 @@ cudaError_t launch_rx_fft(const rx_params_t& p, uint32_t n_packets, cudaStream_t
     const uint32_t items = p.d.N_DF * p.d.N_RX;
     if (groups > items) groups = items;
     const uint32_t threads = ((groups * GT + 31) / 32) * 32;
+    if (fft_is_big(p.d.N_os)) {
+        const uint32_t Mb = p.d.N_os / 16;
+        const uint32_t blen = (p.d.N_os + 2 * fft_buf_len(Mb) + p.d.Nk + 1) / 2;
+        const size_t smem = sizeof(float2) * 2 * blen + sizeof(float) * 2 * threads;
+        static smem_optin_t optin;   // per device
+        cudaError_t e = optin.ensure(smem, [](size_t b) {
+            return cudaFuncSetAttribute(k_rx_fft<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
+        });
+        if (e != cudaSuccess) return e;
+        k_rx_fft<true><<<dim3(items, n_packets), threads, smem, st>>>(p, GT, 1);
+        return cudaGetLastError();
+    }
     const size_t smem = sizeof(float2) * 2 * fft_buf_len(p.d.N_os) * groups + sizeof(float) * 2 * threads;
     if (smem > 48 * 1024) {
         static smem_optin_t optin;   // per device
         cudaError_t e = optin.ensure(smem, [](size_t b) {
-            return cudaFuncSetAttribute(k_rx_fft, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
+            return cudaFuncSetAttribute(k_rx_fft<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
         });
         if (e != cudaSuccess) return e;
     }
-    k_rx_fft<<<dim3((items + groups - 1) / groups, n_packets), threads, smem, st>>>(p, GT, groups);
+    k_rx_fft<false><<<dim3((items + groups - 1) / groups, n_packets), threads, smem, st>>>(p, GT, groups);
     return cudaGetLastError();
 }
 
 cudaError_t launch_rx_stf(const rx_params_t& p, uint32_t n_packets, cudaStream_t st) {
-    const size_t smem = sizeof(float2) * ((size_t)p.d.stf_len_os + 2 * fft_buf_len(p.d.N_os) + (size_t)p.d.N_RX * (p.d.N_OCC / 4));
+    const size_t smem = fft_is_big(p.d.N_os)
+        ? sizeof(float2) * ((size_t)p.d.N_os + 2 * fft_buf_len(p.d.N_os / 16) + (size_t)p.d.N_RX * (p.d.N_OCC / 4))
+        : sizeof(float2) * ((size_t)p.d.stf_len_os + 2 * fft_buf_len(p.d.N_os) + (size_t)p.d.N_RX * (p.d.N_OCC / 4));
     if (smem > 48 * 1024) {
-        static smem_optin_t optin;   // per device
-        cudaError_t e = optin.ensure(smem, [](size_t b) {
-            return cudaFuncSetAttribute(k_rx_stf, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
+        static smem_optin_t optin[2];   // per device and variant
+        const bool big = fft_is_big(p.d.N_os);
+        cudaError_t e = optin[big].ensure(smem, [big](size_t b) {
+            return big ? cudaFuncSetAttribute(k_rx_stf<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b)
+                       : cudaFuncSetAttribute(k_rx_stf<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
         });
         if (e != cudaSuccess) return e;
     }
-    k_rx_stf<<<n_packets, 256, smem, st>>>(p);
+    if (fft_is_big(p.d.N_os)) k_rx_stf<true><<<n_packets, 256, smem, st>>>(p);
+    else k_rx_stf<false><<<n_packets, 256, smem, st>>>(p);
     return cudaGetLastError();
 }
 

@@ -63,13 +63,17 @@ __device__ __forceinline__ float2 apply_w(int8_t w, float2 v) {
     }
 }
 
+template <bool BIG>
 __global__ void __launch_bounds__(256) k_tx_ofdm(const txofdm_params_t p) {
     extern __shared__ __align__(16) float2 sm[];
     const phy_dims_t& d = p.d;
     const uint32_t l = blockIdx.x, ant = blockIdx.y, pkt = blockIdx.z;
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
+    // N_os <= 4096: two ping-pong buffers of fft_buf_len(N_os); longer: one array of N_os + two row scratch buffers (fft.cuh)
+    constexpr bool big = BIG;
+    const uint32_t Mb = d.N_os / 16;
     float2* X = sm;
-    float2* Y = sm + fft_buf_len(d.N_os);
+    float2* Y = sm + (big ? d.N_os : fft_buf_len(d.N_os));
     const tx_meta_dev_t meta = p.meta[pkt];
     const uint8_t* pcc_bits = p.pcc_bits + (size_t)pkt * p.pcc_stride;
     const uint8_t* pdc_bits = p.pdc_bits + (size_t)pkt * p.pdc_stride;
@@ -123,7 +127,13 @@ __global__ void __launch_bounds__(256) k_tx_ofdm(const txofdm_params_t p) {
         X[bin] = make_float2(acc.x * scale, acc.y * scale);
     }
 
-    const float2* x = block_fft<true>(X, Y, d.N_os, d.twiddle);
+    const float2* x;
+    if (big) {
+        big_fft<true>(X, Y, Y + fft_buf_len(Mb), d.N_os, d.twiddle);
+        x = X;   // time sample n at big_fft_at(n, Mb)
+    } else {
+        x = block_fft<true>(X, Y, d.N_os, d.twiddle);
+    }
 
     // ---- cyclic prefix, STF cover sequence, mixer
     const uint32_t cp = l == 0 ? d.stf_cp_os : d.cp_os;
@@ -133,7 +143,7 @@ __global__ void __launch_bounds__(256) k_tx_ofdm(const txofdm_params_t p) {
     const bool mix = !p.no_mix && (meta.iq_phase_rad != 0.f || meta.iq_phase_increment != 0.f);
     for (uint32_t n = tid; n < len; n += nthr) {
         uint32_t src = (n + d.N_os - (cp % d.N_os)) % d.N_os;
-        float2 v = x[src];
+        float2 v = x[big ? big_fft_at(src, Mb) : src];
         if (l == 0) {
             const float c[9] = {1.f, -1.f, 1.f, 1.f, -1.f, -1.f, -1.f, -1.f, -1.f};  // stf.hpp:146-151
             const float cs = c[n / d.pat_len_os];
@@ -152,15 +162,20 @@ __global__ void __launch_bounds__(256) k_tx_ofdm(const txofdm_params_t p) {
 }
 
 cudaError_t launch_tx_ofdm(const txofdm_params_t& p, uint32_t n_packets, cudaStream_t st) {
-    const size_t smem = 2 * sizeof(float2) * fft_buf_len(p.d.N_os);
+    const size_t smem = fft_is_big(p.d.N_os) ? sizeof(float2) * (p.d.N_os + 2 * (size_t)fft_buf_len(p.d.N_os / 16))
+                                             : 2 * sizeof(float2) * fft_buf_len(p.d.N_os);
+    const bool big = fft_is_big(p.d.N_os);
     if (smem > 48 * 1024) {
-        static smem_optin_t optin;   // per device
-        cudaError_t e = optin.ensure(smem, [](size_t b) {
-            return cudaFuncSetAttribute(k_tx_ofdm, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
+        static smem_optin_t optin[2];   // per device and variant
+        cudaError_t e = optin[big].ensure(smem, [big](size_t b) {
+            return big ? cudaFuncSetAttribute(k_tx_ofdm<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b)
+                       : cudaFuncSetAttribute(k_tx_ofdm<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
         });
         if (e != cudaSuccess) return e;
     }
-    k_tx_ofdm<<<dim3(p.d.N_DF + 1, p.d.N_TX, n_packets), 256, smem, st>>>(p);
+    const dim3 grid(p.d.N_DF + 1, p.d.N_TX, n_packets);
+    if (big) k_tx_ofdm<true><<<grid, 256, smem, st>>>(p);
+    else k_tx_ofdm<false><<<grid, 256, smem, st>>>(p);
     return cudaGetLastError();
 }
 

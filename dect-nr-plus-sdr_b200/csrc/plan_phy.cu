@@ -26,9 +26,16 @@ int build_phy_plan(dnrp_ctx* c) {
     d.N_PDC_subc = ps.N_PDC_subc; d.G = ps.G;
     d.n_no_gi_os = ps.N_samples_packet_no_GI * os; d.n_packet_os = ps.N_samples_packet * os;
     d.txdiv_modulo = spec::txdiv_modulo(d.N_TS);
-    if (d.N_os > 4096) {
-        set_last_error("FFT sizes above 4096 are not implemented yet");
-        return DNRP_ERR_INVALID;
+    {
+        // 64 ... 4096 in one pass structure, 6144 ... 16384 four-step in place (fft.cuh; tx_rx.hpp:66-69 lists the sizes
+        // the reference plans); radices 2 and 3 only
+        uint32_t r = d.N_os;
+        while (r % 2 == 0) r /= 2;
+        while (r % 3 == 0) r /= 3;
+        if (r != 1 || d.N_os > 16384) {
+            set_last_error("FFT size " + std::to_string(d.N_os) + " (64 * beta * oversampling) must be 2^a 3^b and at most 16384");
+            return DNRP_ERR_INVALID;
+        }
     }
 
     spec::re_map_t& m = c->re_map;

@@ -28,6 +28,11 @@ RX_CASES = {
     "b12_256qam_38dB": dict(cfg=(4, 12, 0, 3, 0, 9, 6144), snr_db=38.0, t0=11),
     "bpsk_b1_os2_6dB": dict(cfg=(1, 1, 1, 2, 0, 0, 2048), snr_db=6.0, os=2, cfo=5e-4, t0=2),
     "b8_os4_20dB": dict(cfg=(1, 8, 0, 1, 0, 5, 6144), snr_db=20.0, os=4, t0=30),
+    # FFT sizes above 4096: k_rx_stf<BIG>, k_rx_fft<BIG> (four-step in place)
+    "b12_os8_fft6144_18dB": dict(cfg=(1, 12, 0, 2, 0, 3, 2048), snr_db=18.0, os=8, t0=21, cfo=2e-5),
+    "b16_os8_fft8192_txdiv2_2rx_22dB": dict(cfg=(1, 16, 1, 1, 1, 4, 6144), snr_db=22.0, os=8, N_RX=2, t0=100),
+    "b12_os16_fft12288_15dB": dict(cfg=(1, 12, 0, 2, 0, 2, 2048), snr_db=15.0, os=16, t0=7),
+    "b16_os16_fft16384_25dB": dict(cfg=(1, 16, 1, 1, 0, 5, 6144), snr_db=25.0, os=16, t0=64, cfo=1e-5, cfo_err=1e-6),
 }
 
 

@@ -162,3 +162,13 @@ def test_rx_batch_sc16_equals_cf32_on_dequantised_windows(product):
     assert np.array_equal(ok1, ok2) and np.array_equal(tb1, tb2) and rep2.tobytes() == rep1.tobytes()
     assert ok2.mean() > 0.9 and (tb2[ok2] == tb[ok2]).all()
     phy.close()
+
+
+def test_sync_refused_with_a_reason_at_very_high_oversampling(product):
+    """FFT sizes above 4096 are supported by the transmitter and the synchronised receiver; the packet search keeps two
+    STFs of prefix sums in shared memory and says so instead of failing at launch"""
+    phy = product.Phy((1, 16, 1, 1, 0, 4, 6144), max_batch=1, oversampling=8)
+    win = np.zeros((1, 1, phy.rx_stride()), dtype=np.complex64)
+    with pytest.raises(product.DnrpError, match="packet synchronisation is not available"):
+        phy.sync(win)
+    phy.close()

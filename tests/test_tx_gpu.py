@@ -26,6 +26,11 @@ TX_CASES = {
     "txdiv2_b1_1024qam_mcs11": dict(cfg=(1, 1, 1, 3, 1, 11, 2048)),
     "mimo4x4_b2_cb3": dict(cfg=(1, 2, 1, 2, 9, 3, 2048), codebook_index=3),
     "mimo8x8_b1": dict(cfg=(1, 1, 1, 6, 11, 2, 2048)),
+    # FFT sizes above 4096 (tx_rx.hpp:66-69: 6144, 8192, 12288, 16384): four-step in-place transforms
+    "b12_os8_fft6144": dict(cfg=(1, 12, 0, 2, 0, 2, 2048), os=8),
+    "b16_os8_fft8192_txdiv2": dict(cfg=(1, 16, 1, 1, 1, 3, 2048), os=8),
+    "b12_os16_fft12288": dict(cfg=(1, 12, 0, 2, 0, 1, 2048), os=16),
+    "b16_os16_fft16384": dict(cfg=(1, 16, 1, 1, 0, 4, 6144), os=16, iq_phase_rad=0.1, iq_phase_increment=0.0007),
 }
 
 
