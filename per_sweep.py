@@ -126,6 +126,91 @@ def run_cell(product, phy, cell, n_packets, seed, plcf_type=1):
     return row
 
 
+def ratio_cells(ratio_list, snr_list):
+    """tfw_loopback_ratio: parameter = power ratio of the interferer in dB (outside), SNR inside"""
+    return [(ratio, snr) for ratio in ratio_list for snr in snr_list]
+
+
+def run_ratio_cell(product, phy, cell, n_exp, seed):
+    """The near-far experiment of tfw_loopback_ratio.cpp:125-147: packet A (identity A, amplitude db2mag(ratio)) and,
+    starting exactly one packet length later, packet B (identity B, amplitude 1, the wanted one); the noise level is set
+    against B.  All n_exp experiments sit in ONE stream that goes through the streaming front door (packet search ->
+    receiver windows -> PCC -> PDC).  Counters as in the firmware: n_pcc = every packet that reached work_pcc (A and B:
+    the error rate can be negative, like the reference's), n_pcc_and_plcf = B's PLCF, n_pdc = B's transport block."""
+    ratio, snr = cell
+    ps = phy.ps
+    rng = np.random.default_rng(seed)
+    n = 2 * n_exp
+    tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
+    plcf = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    plcf[0::2, 1] = 0xA5                         # stands for the transmitter identity: A on even, B on odd packets
+    plcf[1::2, 1] = 0x5B
+    amp = np.ones(n, dtype=np.float32)
+    amp[0::2] = 10.0 ** (float(ratio) / 20.0)
+    iq, ns = phy.tx(plcf, tb, DAC_scale=amp)
+    S, stf = int(ps["N_samples_packet"]), int(ps["N_samples_STF"])
+    gap = 6 * stf + int(rng.integers(0, 64))
+    period = 2 * S + gap
+    lead = 4 * stf
+    total = lead + n_exp * period
+    sigma = 10.0 ** (-float(snr) / 20.0)         # B has unit power per antenna (DAC_scale 1)
+    stream = (sigma / np.sqrt(2.0)) * (rng.standard_normal((phy.N_RX, total)) + 1j * rng.standard_normal((phy.N_RX, total)))
+    startB = np.zeros(n_exp, dtype=np.int64)
+    for i in range(n_exp):
+        a0 = lead + i * period
+        startB[i] = a0 + S
+        for a in range(phy.N_RX):
+            stream[a, a0:a0 + int(ns[2 * i])] += iq[2 * i, a % iq.shape[1], :int(ns[2 * i])]
+            stream[a, a0 + S:a0 + S + int(ns[2 * i + 1])] += iq[2 * i + 1, a % iq.shape[1], :int(ns[2 * i + 1])]
+    found = phy.stream_sync(stream.astype(np.complex64), max_out=4 * n)
+    row = np.zeros(len(COUNTERS), dtype=np.int64)
+    row[0] = n_exp
+    row[SUMMED], row[SUMMED + 1] = BIG, -BIG
+    if len(found) == 0:
+        return row
+    found = found[:phy.max_batch]
+    m, t0 = len(found), stf // 2
+    phy.stream_extract(found.fine_peak_time_64, t0)
+    sync = phy.make_sync(m, t0=t0, cfo_fractional_rad=found.sync.cfo_fractional_rad, rms=found.sync.rms_array)
+    pcc = phy.rx_pcc(None, n=m, sync=sync)
+    ok, tb_out, snr_est, nit = phy.rx_pdc(m)
+    pcc_ok = pcc.plcf_ok[:, 0] != 0
+    # which experiment's B is it: PLCF content (the firmware compares the transmitter identity), not the position
+    is_b = np.zeros(m, dtype=bool)
+    pdc_b = np.zeros(m, dtype=bool)
+    seen = set()
+    for q in range(m):
+        if not pcc_ok[q]:
+            continue
+        hit = np.nonzero((plcf[1::2, :5] == pcc.plcf[q, 0, :5]).all(axis=1))[0]
+        if hit.size and int(hit[0]) not in seen:
+            seen.add(int(hit[0]))
+            is_b[q] = True
+            pdc_b[q] = bool(ok[q]) and np.array_equal(tb_out[q], tb[2 * int(hit[0]) + 1])
+    snr_m = np.round(snr_est[pdc_b].astype(np.float64) * 1000.0).astype(np.int64)
+    exact = int(np.isin(found.fine_peak_time_64, startB).sum())
+    row[:SUMMED] = [n_exp, m, exact, int(pcc_ok.sum()), int(is_b.sum()), int(pdc_b.sum()), int(pdc_b.sum()), int(nit[pdc_b].sum()),
+                    int(snr_m.sum())]
+    if snr_m.size:
+        row[SUMMED], row[SUMMED + 1] = int(snr_m.min()), int(snr_m.max())
+    return row
+
+
+def ratio_result_files(cells, mat, n_exp, ratio_list, snr_list):
+    """rx_loopback_ratio_<idx>_<ratio> in the layout of tfw_loopback_ratio_t::save_all_results_to_file (:173-201)"""
+    files = {}
+    for idx, ratio in enumerate(ratio_list):
+        rows = [i for i, c in enumerate(cells) if c[0] == ratio]
+        per = lambda k: [float(1.0 - mat[i, COUNTERS.index(k)] / max(mat[i, 0], 1)) for i in rows]
+        files["rx_loopback_ratio_%03d_%d" % (idx, int(ratio))] = {
+            "experiment_range": {"snr_vec": [float(cells[i][1]) for i in rows], "nof_experiment_per_snr": int(n_exp)},
+            "parameter": {"ratio": int(ratio)},
+            "result": {"snr_max_vec": [mat[i, SUMMED + 1] / 1000.0 if mat[i, SUMMED + 1] > -BIG else -100.0e6 for i in rows],
+                       "snr_min_vec": [mat[i, SUMMED] / 1000.0 if mat[i, SUMMED] < BIG else 100.0e6 for i in rows],
+                       "PER_pcc_crc": per("pcc_crc"), "PER_pcc_crc_and_plcf": per("pcc_crc_and_plcf"), "PER_pdc_crc": per("pdc_crc")}}
+    return files
+
+
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--mu", type=int, default=1)
@@ -137,6 +222,10 @@ def main():
     ap.add_argument("--packets", type=int, default=1000, help="packets per (mode, MCS, SNR) cell")
     ap.add_argument("--n-rx", type=int, default=1)
     ap.add_argument("--out", default="", help="directory for the rx_loopback_MCS_xxxx JSON files (rank 0)")
+    ap.add_argument("--experiment", choices=("snr", "ratio"), default="snr",
+                    help="snr: tfw_loopback_snr (PER over MCS and SNR); ratio: tfw_loopback_ratio (a strong packet right in "
+                         "front of the wanted one, PER over power ratio and SNR)")
+    ap.add_argument("--ratio", type=int, nargs="+", default=[30, 40, 50, 60, 70, 80], help="--experiment ratio: dB")
     args = ap.parse_args()
 
     import torch
@@ -155,11 +244,19 @@ def main():
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
     product = load_product()
     snr_list = [float(v) for v in np.arange(args.snr[0], args.snr[1] + 0.5 * args.snr[2], args.snr[2])]
-    cells = sweep_cells(args.tm, args.mcs, snr_list)
+    ratio = args.experiment == "ratio"
+    cells = ratio_cells(args.ratio, snr_list) if ratio else sweep_cells(args.tm, args.mcs, snr_list)
     mine = cells_of_rank(len(cells), rank, world)
     mat = neutral_matrix(len(cells))
     t_start = time.perf_counter()
     phys = {}
+    if ratio:   # one geometry (tfw_loopback.cpp:93-99: the firmware's MCS), every cell = one stream of n experiments
+        psdef = (args.mu, args.beta, 1, args.packet_length, args.tm[0], args.mcs[0], 2048 if args.beta < 4 else 6144)
+        phy = product.Phy(psdef, max_batch=4 * args.packets, N_RX=args.n_rx, network_id=123456789, plcf_type=1, device=local)
+        for ci in mine:
+            mat[ci] = run_ratio_cell(product, phy, cells[ci], args.packets, seed=0x5EED1000 + ci)
+        phy.close()
+        mine = []
     for ci in mine:
         tm, mcs, _ = cells[ci]
         if (tm, mcs) not in phys:      # one context per packet geometry, reused over the SNR points
@@ -178,7 +275,8 @@ def main():
         dist.barrier()
     dt = time.perf_counter() - t_start
     if rank == 0:
-        files = result_files(cells, mat, args.packets, args.tm, args.mcs, snr_list)
+        files = (ratio_result_files(cells, mat, args.packets, args.ratio, snr_list) if ratio else
+                 result_files(cells, mat, args.packets, args.tm, args.mcs, snr_list))
         if args.out:
             os.makedirs(args.out, exist_ok=True)
             for name, j in files.items():

@@ -97,3 +97,34 @@ def test_small_sweep_on_one_gpu(tmp_path):
         assert per[0] > 0.5 and per[-1] < 0.02, per                       # -4 dB loses packets, 16 dB does not
         assert all(per[i + 1] <= per[i] + 0.05 for i in range(len(per) - 1)), per
         assert all(a <= b + 1e-9 for a, b in zip(j["result"]["PER_pcc_crc"], j["result"]["PER_pcc_crc_and_plcf"]))
+
+
+def test_ratio_result_files_follow_the_reference_layout():
+    import per_sweep as ps
+    snr = [0.0, 5.0, 10.0]
+    cells = ps.ratio_cells([30, 60], snr)
+    mat = np.stack([_fake_row(ps, ci, 100) for ci in range(len(cells))])
+    files = ps.ratio_result_files(cells, mat, 100, [30, 60], snr)
+    assert sorted(files) == ["rx_loopback_ratio_000_30", "rx_loopback_ratio_001_60"]      # tfw_loopback_ratio.cpp:176-178
+    j = files["rx_loopback_ratio_001_60"]
+    assert j["experiment_range"] == {"snr_vec": snr, "nof_experiment_per_snr": 100} and j["parameter"] == {"ratio": 60}
+    assert sorted(j["result"]) == sorted(["snr_max_vec", "snr_min_vec", "PER_pcc_crc", "PER_pcc_crc_and_plcf", "PER_pdc_crc"])
+    json.dumps(files)
+
+
+@pytest.mark.gpu
+def test_ratio_experiment_on_one_gpu(tmp_path):
+    """tfw_loopback_ratio through the streaming front door: with both packets equally strong (0 dB) the wanted packet
+    decodes at 15 dB and the PCC counter sees both packets of every experiment (error rate -1, like the reference's
+    counting); the error rate of the wanted packet does not fall when the interferer grows by 40 dB"""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "per_sweep.py"), "--experiment", "ratio", "--beta", "1", "--mcs", "2",
+                        "--ratio", "0", "40", "--snr", "5", "15", "10", "--packets", "40", "--out", str(tmp_path)],
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    s = json.loads(r.stdout.strip().splitlines()[-1])
+    assert s["cells"] == 4 and s["tb_mismatch_after_crc_ok"] == 0
+    j0 = json.load(open(tmp_path / "rx_loopback_ratio_000_0.json"))
+    j40 = json.load(open(tmp_path / "rx_loopback_ratio_001_40.json"))
+    assert j0["experiment_range"]["snr_vec"] == [5.0, 15.0] and j0["parameter"]["ratio"] == 0
+    assert j0["result"]["PER_pdc_crc"][1] <= 0.05 and j0["result"]["PER_pcc_crc"][1] <= -0.9
+    assert j40["result"]["PER_pdc_crc"][1] >= j0["result"]["PER_pdc_crc"][1] - 1e-9
