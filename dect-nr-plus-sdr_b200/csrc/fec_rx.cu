@@ -2,6 +2,7 @@
 // decode + CRC in ONE kernel per batch (grid = code blocks x packets), then a small per-packet kernel
 // for the transport-block level CRC logic.  Reference: lib/src/phy/fec/pdc_enc.cpp:291-492,
 // lib/src/phy/fec/pcc_enc.cpp:215-364 (file:line relative to /root/reference).
+#include <cstdlib>
 #include <type_traits>
 #include "fec_rx.cuh"
 #include "launch_util.hpp"
@@ -163,11 +164,16 @@ cudaError_t launch_derm(const tdec_params_t& p, uint32_t n_packets, uint32_t max
 // blockDim.x / tg groups.  Large code blocks: one group per block (tg = blockDim.x, a multiple of 32).
 // Small ones (PLCF, K < ~2000: fewer than 32 window pairs): tg is a power of two <= 32 and many items
 // share a block, all groups moving through the same barriers in lockstep.
-template <bool GROUPED>
+// BULK (one item per block only): the streams of the soft buffer are staged by the copy engine (cp.async.bulk + mbarrier,
+// turbo_dec.cuh) and clamped in place, instead of a load / clamp / store loop per thread; the copy of the next half
+// iteration's parity stream is issued as soon as the shared arrays are free, so it overlaps the boundary / CRC work.
+template <bool GROUPED, bool BULK = false>
 __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_decode(const tdec_params_t p, uint32_t tg, uint32_t smem_item_words,
                                                       uint32_t n_items) {
+    static_assert(!(GROUPED && BULK), "bulk staging is for one item per block");
     extern __shared__ __align__(16) uint32_t smem_all[];
-    __shared__ uint32_t s_crc_all[128];
+    __shared__ uint32_t s_crc_all[GROUPED ? 128 : 1];
+    __shared__ __align__(8) uint64_t s_bar;   // BULK: completion barrier of the staging copies
     __shared__ int s_tail_all[(GROUPED ? 128 : 1) * 16];
     const uint32_t grp = GROUPED ? threadIdx.x / tg : 0;
     const uint32_t tid = GROUPED ? threadIdx.x % tg : threadIdx.x, nthr = GROUPED ? tg : blockDim.x;
@@ -198,6 +204,7 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
     }
     const bool skipped = done;
     if (!GROUPED && done) return;  // single item per block: nothing left to do
+    if (BULK && threadIdx.x == 0) mbar_init(&s_bar, 1);   // visible to the block after the barrier below
 
     // the systematic stream stays in the (L2 resident) soft buffer and is re-read once per half
     // iteration: one K/2-word array less per block = one more resident block per SM
@@ -207,7 +214,12 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
     uint32_t* CK = PAR + KH;                 // [nck][7][T]
     uint32_t* AE = CK + nck * 7 * T;         // [2][7][T]
     uint32_t* BS = AE + 2 * 7 * T;           // [2][7][T]
-    uint8_t* HARD = (uint8_t*)(BS + 2 * 7 * T);  // [KH]
+    // The hard decisions need no array of their own: the second decoder leaves 2 e + (LLR > 0) in EXT (the extrinsic
+    // values are clamped to +-2047, so the doubled value fits an int16); the CRC and output stages read bit 0 of each
+    // half, the next iteration's staging halves the words back (ext_strip).  K = 5952: 59.5 -> 56.6 KB per block, i.e.
+    // four instead of three resident blocks per SM.
+    auto ext_strip = [](uint32_t w) { return ((w >> 1) & 0x7fff7fffu) | (w & 0x80008000u); };   // per half: >> 1, signed
+    auto strip4 = [&](uint4 v) { return make_uint4(ext_strip(v.x), ext_strip(v.y), ext_strip(v.z), ext_strip(v.w)); };
 
     // soft buffer of this code block, written by k_derm in the layout of plan_fec.cu: three streams of K/2 packed
     // words in shared-array order, then the 12 termination values
@@ -260,16 +272,46 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
         const uint4* x4 = reinterpret_cast<const uint4*>(soft);
         uint4* PAR4 = reinterpret_cast<uint4*>(PAR);
         uint4* XIN4 = reinterpret_cast<uint4*>(XIN);
-        const uint4* EXT4 = reinterpret_cast<const uint4*>(EXT);
+        uint4* EXT4 = reinterpret_cast<uint4*>(EXT);
 #pragma unroll 1  // measured: any unrolling here is slower (instruction-cache bound kernel)
         for (uint32_t i4 = tid; i4 < KH / 4; i4 += nthr) {
             PAR4[i4] = clamp4(p4[i4]);
             if (with_x) {
-                const uint4 x = clamp4(x4[i4]), e = EXT4[i4];
+                const uint4 x = clamp4(x4[i4]), e = strip4(EXT4[i4]);
+                EXT4[i4] = e;
                 XIN4[i4] = make_uint4(vadd(x.x, e.x), vadd(x.y, e.y), vadd(x.z, e.z), vadd(x.w, e.w));
             }
         }
     };
+
+    // BULK: thread 0 issues the copies of a half iteration (parity stream, with_x: also the systematic stream into XIN);
+    // all threads wait for them and clamp / add the a-priori values in place (each thread its own words)
+    uint32_t bar_phase = 0;
+    auto stage_issue = [&](uint32_t stream, bool with_x) {
+        if (threadIdx.x == 0) {
+            fence_proxy_async();   // the block's earlier reads / writes of PAR and XIN (ordered by the barrier before)
+            mbar_expect_tx(&s_bar, (with_x ? 2u : 1u) * K * 2u);
+            bulk_g2s(PAR, soft + (size_t)stream * K, K * 2u, &s_bar);
+            if (with_x) bulk_g2s(XIN, soft, K * 2u, &s_bar);
+        }
+    };
+    auto stage_finish = [&](bool with_x) {
+        mbar_wait(&s_bar, bar_phase);
+        bar_phase ^= 1u;
+        uint4* PAR4 = reinterpret_cast<uint4*>(PAR);
+        uint4* XIN4 = reinterpret_cast<uint4*>(XIN);
+        uint4* EXT4 = reinterpret_cast<uint4*>(EXT);
+#pragma unroll 1
+        for (uint32_t i4 = tid; i4 < KH / 4; i4 += nthr) {
+            PAR4[i4] = clamp4(PAR4[i4]);
+            if (with_x) {
+                const uint4 x = clamp4(XIN4[i4]), e = strip4(EXT4[i4]);
+                EXT4[i4] = e;
+                XIN4[i4] = make_uint4(vadd(x.x, e.x), vadd(x.y, e.y), vadd(x.z, e.z), vadd(x.w, e.w));
+            }
+        }
+    };
+    if (BULK) stage_issue(1, true);
 
     const uint32_t t = tid;
     const uint32_t wl = t, wh = t + T, P = cb.P;
@@ -295,7 +337,8 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
         for (uint32_t dec = 0; dec < 2; ++dec) {
             // ---- parity of this constituent decoder -> shared, window-transposed
             // (first decoder: with its input x = systematic + a-priori in natural order)
-            if (work) stage(1 + dec, dec == 0);
+            if (BULK) stage_finish(dec == 0);
+            else if (work) stage(1 + dec, dec == 0);
             // ---- input of the second decoder, interleaved order
             if (dec != 0 && active) {
                 uint32_t pi = qpp_pi0, g = qpp_g0;
@@ -464,9 +507,9 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
                                 const uint32_t pw = up ? pi - KH : pi;
                                 const uint32_t q = __umulhi(pw, cb.Linv);
                                 const uint32_t ad = (pw - q * L) * T + q;
-                                const uint32_t hb = ((int16_t)(l & 0xffff) > 0 ? 1u : 0u) | ((int16_t)(l >> 16) > 0 ? 2u : 0u);
-                                EXT[ad] = up ? swap16(e) : e;
-                                HARD[ad] = (uint8_t)(up ? ((hb >> 1) | ((hb & 1) << 1)) : hb);
+                                // extrinsic doubled, hard decision (LLR > 0) in bit 0 of each half
+                                const uint32_t w = vadd(e, e) | (__vcmpgts2(l, 0u) & 0x00010001u);
+                                EXT[ad] = up ? swap16(w) : w;
                                 pi += g; if (pi >= K) pi -= K;
                                 g += g2; if (g >= K) g -= K;
                             }
@@ -483,6 +526,7 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
             }
             if (tid == 0) s_crc = 0;
             __syncthreads();
+            if (BULK && dec == 0) stage_issue(2, false);   // PAR is free: the second decoder's parity stream
             if (active) {
 #pragma unroll
                 for (int s = 1; s < 8; ++s) {
@@ -500,10 +544,10 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
                 uint32_t r_lo = 0, r_hi = 0;
                 const uint32_t top = 1u << cb.crc_order;
                 for (uint32_t k = 0; k < L; ++k) {
-                    const uint32_t hb = HARD[k * T + t];
+                    const uint32_t hb = EXT[k * T + t];
                     r_lo = (r_lo << 1) | (hb & 1);
                     if (r_lo & top) r_lo ^= cb.crc_poly;
-                    r_hi = (r_hi << 1) | (hb >> 1);
+                    r_hi = (r_hi << 1) | ((hb >> 16) & 1);
                     if (r_hi & top) r_hi ^= cb.crc_poly;
                 }
                 const uint32_t* xp = p.xp_arena + cb.xp_off;
@@ -526,6 +570,7 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
             }
             done = crc_ok;
         }
+        if (BULK && !done && it + 1 < p.max_it) stage_issue(1, true);   // next iteration (nothing may be left in flight at exit)
         __syncthreads();
     }
     if (skipped) return;  // no barrier below
@@ -538,9 +583,9 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
             uint32_t w_lo = 0, w_hi = 0;
 #pragma unroll 4
             for (uint32_t k = 0; k < 32; ++k) {
-                const uint32_t hb = HARD[k * T + t];
+                const uint32_t hb = EXT[k * T + t];
                 w_lo = (w_lo << 1) | (hb & 1u);
-                w_hi = (w_hi << 1) | (hb >> 1);
+                w_hi = (w_hi << 1) | ((hb >> 16) & 1u);
             }
 #pragma unroll
             for (uint32_t j = 0; j < 8; ++j) {
@@ -560,8 +605,8 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
             const uint32_t pos = bi * 8 + q;
             const uint32_t pw = pos >= KH ? pos - KH : pos;
             const uint32_t qq = __umulhi(pw, cb.Linv);
-            const uint32_t hb = HARD[(pw - qq * L) * T + qq];
-            v = (v << 1) | (pos >= KH ? (hb >> 1) : (hb & 1));
+            const uint32_t hb = EXT[(pw - qq * L) * T + qq];
+            v = (v << 1) | (pos >= KH ? ((hb >> 16) & 1u) : (hb & 1u));
         }
         if (bi < cb.rlen_byte) {
             tb_out[bi] = (uint8_t)v;
@@ -620,7 +665,7 @@ __global__ void __launch_bounds__(256) k_tb_finalize(const tbfin_params_t p) {
 
 size_t tdec_smem_bytes(uint32_t K, uint32_t L) {
     const uint32_t T = K / L / 2, nck = (L + tdec::S_CK - 1) / tdec::S_CK;
-    return (size_t)4 * (3 * (K / 2) + nck * 7 * T + 4 * 7 * T) + K / 2 + 16;
+    return (size_t)4 * (3 * (K / 2) + nck * 7 * T + 4 * 7 * T) + 16;
 }
 
 tdec_geom_t tdec_geometry(const cb_desc_t* cbs, uint32_t n) {
@@ -653,12 +698,18 @@ cudaError_t launch_turbo_decode(const tdec_params_t& p, uint32_t n_packets, cons
     cudaError_t e0 = optin.ensure(smem, [](size_t b) {
         cudaError_t e = cudaFuncSetAttribute(k_turbo_decode<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
         if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(k_turbo_decode<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
+        if (e == cudaSuccess)
             e = cudaFuncSetAttribute(k_turbo_decode<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
         return e;
     });
     if (e0 != cudaSuccess) return e0;
     const dim3 grid((n_items + per_block - 1) / per_block);
-    if (per_block == 1)
+    // DNRP_TDEC_BULK=0: the per-thread staging loop instead of the copy engine (for A/B measurements; same results)
+    static const bool bulk = [] { const char* e = getenv("DNRP_TDEC_BULK"); return !(e && e[0] == '0'); }();
+    if (per_block == 1 && bulk)
+        k_turbo_decode<false, true><<<grid, threads, smem, st>>>(p, g.tg, (uint32_t)(g.smem_item / 4), n_items);
+    else if (per_block == 1)
         k_turbo_decode<false><<<grid, threads, smem, st>>>(p, g.tg, (uint32_t)(g.smem_item / 4), n_items);
     else
         k_turbo_decode<true><<<grid, threads, smem, st>>>(p, g.tg, (uint32_t)(g.smem_item / 4), n_items);

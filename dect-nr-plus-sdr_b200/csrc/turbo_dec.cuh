@@ -57,6 +57,31 @@ __device__ __forceinline__ uint32_t vclamp(uint32_t a, int lim) {
 __device__ __forceinline__ uint32_t swap16(uint32_t a) { return __byte_perm(a, 0, 0x1032); }
 __device__ __forceinline__ uint32_t pack(int lo, int hi) { return ((uint32_t)lo & 0xffff) | ((uint32_t)hi << 16); }
 
+// ---- bulk staging of one stream of the soft buffer into shared memory by the copy engine (cp.async.bulk, SASS
+// UBLKCP): one elected thread arms the mbarrier with the byte count and issues the copy, every thread of the block
+// waits on the barrier's phase.  dst / src / bytes are multiples of 16.
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_addr(bar)), "r"(count) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_addr(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+    uint32_t ok;
+    do {
+        asm volatile("{\n.reg .pred p;\nmbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\nselp.u32 %0, 1, 0, p;\n}"
+                     : "=r"(ok) : "r"(smem_addr(bar)), "r"(parity) : "memory");
+    } while (!ok);
+}
+// generic-proxy accesses to shared memory issued so far are ordered before the async-proxy writes that follow
+__device__ __forceinline__ void fence_proxy_async() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+__device__ __forceinline__ void bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];"
+                 ::"r"(smem_addr(dst)), "l"(src), "r"(bytes), "r"(smem_addr(bar)) : "memory");
+}
+
 // one backward step: b[] <- beta at the previous trellis time, normalised to state 0 (NORM) or left as computed.
 // Normalisation only shifts all eight metrics alike, so skipping it changes no decision and no stored (normalised)
 // value as long as nothing overflows: normalised metrics lie within +-12.3k (three steps connect any two states,
