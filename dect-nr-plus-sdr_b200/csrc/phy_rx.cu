@@ -2,6 +2,7 @@
 // rx_synced.cpp): STF stage (CFO derotation, cover sequence, residual CFO, FFT, zero-forcing at the STF
 // cells, fractional STO, SNR), data field FFTs with DRS zero-forcing, Wiener class selection, and the
 // fused channel interpolation + MRC/Alamouti combining + soft demapping kernel.
+#include <cstdlib>
 #include "launch_util.hpp"
 #include "fft.cuh"
 #include "phy.cuh"
@@ -294,6 +295,147 @@ __global__ void __launch_bounds__(BIG ? 1024 : 256) k_rx_fft(const rx_params_t p
         for (uint32_t i = 0; i < GT; ++i) { sx += s_part[2 * (grp * GT + i)]; sy += s_part[2 * (grp * GT + i) + 1]; }
         p.snr_part[((size_t)pkt * d.N_DF + (l - 1)) * d.N_RX + a] = any ? make_float2(sx, sy) : make_float2(0.f, 0.f);
     }
+}
+
+// ---- the same for N_os = 1024 (beta = 16 at the DECT rate: BASELINE configs C2, C3, C4) with every size fixed at
+// compile time: 64 threads per (symbol, antenna), four groups per block, passes 16 x 16 x 4 with the data staying in
+// registers between the passes -- ONE padded buffer per group instead of a ping-pong pair (read all, group barrier,
+// write back), so four blocks instead of three are resident per SM; groups synchronise among themselves through named
+// barriers (bar.sync id, 64) and never wait for each other.  The DRS stage reads the symbol back from global memory
+// (L1 / L2 hits; only three symbols in twenty carry DRS cells) instead of keeping a copy in shared memory.  Same
+// butterflies, twiddles and operation order as group_fft16 (fft.cuh): bit-identical Y; the SNR partial sums are
+// reduced in a different (fixed) order.
+__device__ __forceinline__ void group_bar(uint32_t grp) {   // literal ids: the kernel reserves five barriers, not sixteen
+    switch (grp) {
+        case 0: asm volatile("bar.sync 1, 64;" ::: "memory"); break;
+        case 1: asm volatile("bar.sync 2, 64;" ::: "memory"); break;
+        case 2: asm volatile("bar.sync 3, 64;" ::: "memory"); break;
+        default: asm volatile("bar.sync 4, 64;" ::: "memory"); break;
+    }
+}
+
+__global__ void __launch_bounds__(256, 4) k_rx_fft1024(const rx_params_t p) {
+    constexpr uint32_t N = 1024, GT = 64, G = 4, BL = N + N / 16;
+    extern __shared__ __align__(16) float2 sm[];   // [G][BL], then [G][2] warp partial sums
+    const phy_dims_t& d = p.d;
+    const uint32_t grp = threadIdx.x >> 6, tid = threadIdx.x & 63;
+    const uint32_t item = blockIdx.x * G + grp, pkt = blockIdx.y;
+    if (item >= d.N_DF * d.N_RX) return;   // whole groups leave; only group barriers below
+    const uint32_t l = item / d.N_RX + 1, a = item - (l - 1) * d.N_RX;
+    const rx_state_t& st = p.state[pkt];
+    float2* A = sm + grp * BL;
+    const float2* __restrict__ table = d.twiddle;
+
+    const uint32_t n0 = d.stf_len_os + (l - 1) * d.sym_len_os + d.cp_os;
+    float2 v[16];
+    {
+        const float2* x = p.iq + ((size_t)pkt * d.N_RX + a) * p.iq_stride + (p.t0_zero ? 0 : st.t0) + n0;
+        const double ph0 = (double)st.inc0 * (double)d.stf_len_os + (double)st.inc1 * (double)(n0 - d.stf_len_os);
+        float2 w = rot(ph0 + (double)st.inc1 * (double)tid);
+        const float2 ws = rot((double)st.inc1 * (double)GT);
+#pragma unroll
+        for (int m = 0; m < 16; ++m) {
+            v[m] = cmul(__ldcs(x + tid + m * GT), w);
+            w = cmul(w, ws);
+        }
+    }
+    // pass 1 (Ns = 1): X[r] of butterfly tid at element 16 tid + r (padded 17 tid + r)
+    dft16<false>(v);
+#pragma unroll
+    for (int r = 0; r < 16; ++r) A[17 * tid + r] = v[r];
+    group_bar(grp);
+    // pass 2 (Ns = 16): inputs at tid + 64 r, twiddle W_256^(k r), outputs at 256 (tid / 16) + k + 16 r
+    {
+        const uint32_t k = tid & 15u, q = tid >> 4;
+        const float2* xj = A + tid + q;
+#pragma unroll
+        for (int r = 0; r < 16; ++r) v[r] = xj[68 * r];
+        group_bar(grp);
+#pragma unroll
+        for (int r = 1; r < 16; ++r) v[r] = cmul(v[r], __ldg(table + 4 * k * r));
+        dft16<false>(v);
+        float2* yj = A + 272 * q + k;
+#pragma unroll
+        for (int r = 0; r < 16; ++r) yj[17 * r] = v[r];
+    }
+    group_bar(grp);
+    // pass 3 (Ns = 256, radix 4): butterflies j = tid + 64 i, inputs at j + 256 r (padded), outputs at j + 256 r (plain)
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const uint32_t j = tid + 64 * i;
+        const float2* xj = A + j + (j >> 4);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) v[4 * i + r] = xj[272 * r];
+    }
+    group_bar(grp);
+#pragma unroll
+    for (int i = 0; i < 4; ++i) {
+        const uint32_t j = tid + 64 * i;
+#pragma unroll
+        for (int r = 1; r < 4; ++r) v[4 * i + r] = cmul(v[4 * i + r], __ldg(table + j * r));
+        dft4<false>(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
+#pragma unroll
+        for (int r = 0; r < 4; ++r) A[j + 256 * r] = v[4 * i + r];
+    }
+    group_bar(grp);
+
+    // un-mirror, scale, STO derotation -> Y
+    float2* Yout = p.Y + (((size_t)pkt * d.N_RX + a) * d.N_DF + (l - 1)) * d.Nk;
+    {
+        const float fscale = sqrtf((float)d.N_OCC) / (float)N;
+        float2 wk = rot((double)st.sto_inc * (double)((int)tid - (int)(d.N_OCC / 2)));
+        const float2 wks = rot((double)st.sto_inc * (double)GT);
+        wk = make_float2(wk.x * fscale, wk.y * fscale);
+        const uint32_t half = d.N_OCC / 2;
+        for (uint32_t k = tid; k < d.Nk; k += GT) {
+            const uint32_t bin = k >= half ? k - half : N - half + k;
+            Yout[k] = cmul(A[bin], wk);
+            wk = cmul(wk, wks);
+        }
+    }
+    // ---- DRS of this symbol (if any): streams 0..3 at symbols 1 + n N_step, streams 4..7 one symbol later
+    const uint32_t q0 = (l - 1) / d.N_step, r0 = (l - 1) - q0 * d.N_step;
+    const bool drs_lo = r0 == 0 && q0 < d.n_drs;
+    const bool drs_hi = d.N_eff_TX > 4 && r0 == 1 && q0 < d.n_drs;   // (l - 2) % N_step == 0, N_step >= 5
+    float2* part = sm + G * BL + 2 * grp;
+    if (!(drs_lo || drs_hi)) {
+        if (tid == 0) p.snr_part[((size_t)pkt * d.N_DF + (l - 1)) * d.N_RX + a] = make_float2(0.f, 0.f);
+        return;
+    }
+    group_bar(grp);   // the group's stores to Yout are visible to the group
+    float2 sn = make_float2(0.f, 0.f);
+    const uint32_t ts0 = drs_lo ? 0u : 4u, ts1 = drs_lo ? min(d.N_eff_TX, 4u) : d.N_eff_TX;
+    const uint32_t n = q0;
+    const volatile float2* Yv = Yout;
+    for (uint32_t ts = ts0; ts < ts1; ++ts) {
+        const uint32_t pc = ((ts & 3) + 2 * (n & 1)) & 3;
+        float2* hz = p.hzf + ((((size_t)pkt * d.N_RX + a) * d.N_eff_TX + ts) * d.n_drs + n) * d.NP;
+        for (uint32_t i = tid; i < d.NP; i += GT) {
+            const uint32_t q = 4 * i + pc;
+            const uint32_t k = q < d.N_OCC / 2 ? q : q + 1;
+            const float sg = drs_sign_dev(d, l, k);
+            const float yx = Yv[k].x, yy = Yv[k].y;
+            const float2 h = make_float2(yx * sg, yy * sg);  // division by +-1
+            hz[i] = h;
+            sn.x += h.x * h.x + h.y * h.y;
+            if (i + 1 < d.NP) {
+                const uint32_t q2 = q + 4, k2 = q2 < d.N_OCC / 2 ? q2 : q2 + 1;
+                const float sg2 = drs_sign_dev(d, l, k2);
+                const float2 dlt = csub(h, make_float2(Yv[k2].x * sg2, Yv[k2].y * sg2));
+                sn.y += 0.5f * (dlt.x * dlt.x + dlt.y * dlt.y);
+            }
+        }
+    }
+    // group-wide sum in a fixed order: butterfly inside each warp, then warp 0 + warp 1
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+        sn.x += __shfl_xor_sync(0xffffffffu, sn.x, o);
+        sn.y += __shfl_xor_sync(0xffffffffu, sn.y, o);
+    }
+    if ((tid & 31u) == 0) part[tid >> 5] = sn;
+    group_bar(grp);
+    if (tid == 0)
+        p.snr_part[((size_t)pkt * d.N_DF + (l - 1)) * d.N_RX + a] = make_float2(part[0].x + part[1].x, part[0].y + part[1].y);
 }
 
 // ---- Wiener class per DRS symbol, one thread per packet: replays estimator_snr_t in symbol order and
@@ -868,6 +1010,13 @@ cudaError_t launch_rx_fft(const rx_params_t& p, uint32_t n_packets, cudaStream_t
         });
         if (e != cudaSuccess) return e;
         k_rx_fft<true><<<dim3(items, n_packets), threads, smem, st>>>(p, GT, 1);
+        return cudaGetLastError();
+    }
+    // DNRP_FFT_GENERIC=1: the run-time sized kernel also at N_os = 1024 (A/B measurements; Y is bit-identical)
+    static const bool generic = [] { const char* e = getenv("DNRP_FFT_GENERIC"); return e && e[0] == '1'; }();
+    if (p.d.N_os == 1024 && !generic) {
+        const size_t smem1k = sizeof(float2) * (4 * (1024 + 64) + 2 * 4);
+        k_rx_fft1024<<<dim3((items + 3) / 4, n_packets), 256, smem1k, st>>>(p);
         return cudaGetLastError();
     }
     const size_t smem = sizeof(float2) * 2 * fft_buf_len(p.d.N_os) * groups + sizeof(float) * 2 * threads;
