@@ -136,6 +136,10 @@ struct dnrp_ctx {
         dnrp::dbuf<uint16_t> idx_pilot, idx_weight;
         dnrp::dbuf<float> weights;
     } d_wiener_l[3], d_wiener_lr[3];
+    struct pair_bufs_t {
+        dnrp::dbuf<uint16_t> info;
+        dnrp::dbuf<float> w;
+    } d_pcc_pair[3], d_pdc_pair[3];
     uint32_t rx_stride = 0;  // samples per antenna in d_iq_rx
     uint32_t cls_stride = 0;
     dnrp::dbuf<float2> d_iq_rx, d_Y, d_hzf, d_hstf, d_snr_part;

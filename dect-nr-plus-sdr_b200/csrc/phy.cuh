@@ -44,6 +44,14 @@ struct phy_dims_t {
         const float* weights;               // [n_vec][n_interp]
         uint32_t n_interp, n_t;
     } wiener_l[3], wiener_lr[3];            // per SNR class {-5, 15, 35} dB (rx_synced_param.hpp:216-232)
+    // transmit diversity: the two Wiener windows of a cell pair merged into ONE window per (unit, stream slot) on the host
+    // (chan_est_rx_pair): first pilot and tap count, and the weights 0.5 (w_k0 + w_k1) stored tap-major so that the
+    // threads of a warp (adjacent units) read one contiguous line per tap
+    struct pair_lut_t {
+        const uint16_t* info;               // [2][units]: first pilot m | taps << 10; 0xffff: windows too far apart
+        const float* w;                     // [n_interp + 1][2][units]
+        uint32_t units;
+    } pcc_pair[3], pdc_pair[3];             // per SNR class; info == nullptr: not built (single stream / spatial multiplexing PDC)
 };
 
 // plan word: LUT slice base (o = base * Nk + k) | class slot j | pilot row | interlace flip | stream | mode lr

@@ -541,12 +541,57 @@ __device__ __forceinline__ void chan_est_rx(const rx_params_t& p, uint32_t pkt, 
 // (the subcarriers are at most two apart, pilots four), so the mean is ONE dot product over the union window with the
 // weights 0.5 (w_k0 + w_k1): n_interp + 1 taps instead of 2 n_interp, i.e. about half the pilot loads and MACs.
 // Differs from averaging two separately rounded estimates by fp32 rounding only.
+// pair_luts: the host-merged windows of this list (phy_dims_t::pair_lut_t, per SNR class), slot = stream slot (A / B) of
+// unit u: first pilot, tap count and weights come straight from the tables (one coalesced load per tap).
 template <int NRX>
 __device__ __forceinline__ void chan_est_rx_pair(const rx_params_t& p, uint32_t pkt, uint32_t plan, uint32_t k0, uint32_t k1,
-                                                 float2 (&h)[NRX]) {
+                                                 float2 (&h)[NRX], const phy_dims_t::pair_lut_t* pair_luts, uint32_t u,
+                                                 uint32_t slot) {
     const phy_dims_t& d = p.d;
     const uint32_t base = plan & 63u, j = (plan >> 6) & 63u, row = (plan >> 12) & 31u, flip = (plan >> 17) & 1u,
                    ts = (plan >> 18) & 7u, lr = (plan >> 21) & 1u;
+    {
+        const phy_dims_t::pair_lut_t& PL = pair_luts[p.cls[(size_t)pkt * p.cls_stride + j]];
+        const uint32_t info = PL.info ? PL.info[slot * PL.units + u] : 0xffffu;
+        if (info != 0xffffu) {
+            const uint32_t mmin = info & 1023u, nt = info >> 10;
+            const float* wp = PL.w + slot * PL.units + u;
+            const uint32_t wstride = 2 * PL.units;
+            const uint32_t stride_a = d.N_eff_TX * d.n_drs * d.NP;
+            const float2* hz_pkt = p.hzf + (size_t)pkt * d.N_RX * stride_a;
+            const uint32_t off_row = (ts * d.n_drs + row) * d.NP;
+#pragma unroll
+            for (int a = 0; a < NRX; ++a) h[a] = make_float2(0.f, 0.f);
+            if (lr) {
+                // tap m sits on side (m & 1) ^ flip at index m >> 1: the taps alternate between two rows of pilots
+                uint32_t off_a = off_row + (flip ? d.NP : 0u) + ((mmin + 1) >> 1);      // even m
+                uint32_t off_b = off_row + (flip ? 0u : d.NP) + (mmin >> 1);            // odd m
+                if (mmin & 1u) { const uint32_t t_ = off_a; off_a = off_b; off_b = t_; }   // off_a: taps 0, 2, ...
+                for (uint32_t t = 0; t < nt; ++t) {
+                    const uint32_t off = (t & 1u) ? off_b + (t >> 1) : off_a + (t >> 1);
+                    const float wi = wp[t * wstride];
+#pragma unroll
+                    for (int a = 0; a < NRX; ++a) {
+                        const float2 v = hz_pkt[off + a * stride_a];
+                        h[a].x += wi * v.x;
+                        h[a].y += wi * v.y;
+                    }
+                }
+            } else {
+                const float2* hz = hz_pkt + off_row + mmin;
+                for (uint32_t t = 0; t < nt; ++t) {
+                    const float wi = wp[t * wstride];
+#pragma unroll
+                    for (int a = 0; a < NRX; ++a) {
+                        const float2 v = hz[t + a * stride_a];
+                        h[a].x += wi * v.x;
+                        h[a].y += wi * v.y;
+                    }
+                }
+            }
+            return;
+        }
+    }
     const phy_dims_t::wiener_dev_t& W = lr ? d.wiener_lr[p.cls[(size_t)pkt * p.cls_stride + j]]
                                            : d.wiener_l[p.cls[(size_t)pkt * p.cls_stride + j]];
     const uint32_t o0 = base * d.Nk + k0, o1 = base * d.Nk + k1;
@@ -681,8 +726,9 @@ __global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_dema
             float den = 0.f;
             // per antenna: h0 = mean of stream A's estimates at the two cells, h1 = the same for stream B
             float2 h0[NRX], h1[NRX];
-            chan_est_rx_pair<NRX>(p, pkt, planA, k0, k1, h0);
-            chan_est_rx_pair<NRX>(p, pkt, planB, k0, k1, h1);
+            const phy_dims_t::pair_lut_t* pl = pcc ? d.pcc_pair : d.pdc_pair;
+            chan_est_rx_pair<NRX>(p, pkt, planA, k0, k1, h0, pl, u, 0);
+            chan_est_rx_pair<NRX>(p, pkt, planB, k0, k1, h1, pl, u, 1);
 #pragma unroll
             for (int a = 0; a < NRX; ++a) {
                 const float2* Y = p.Y + (((size_t)pkt * NRX + a) * d.N_DF + (l - 1)) * d.Nk;

@@ -129,6 +129,7 @@ int build_phy_plan(dnrp_ctx* c) {
         d.pcc_l_max = 0;
         for (uint32_t v : m.pcc_lk) d.pcc_l_max = std::max(d.pcc_l_max, v >> 16);
     }
+    std::vector<uint32_t> pcc_plan_h, pdc_plan_h;
     {
         // which interpolation serves (stream ts, symbol l): closed form of rx_synced.cpp:1027-1152,
         // evaluated once per demapper unit here instead of per cell and packet on the device
@@ -180,8 +181,10 @@ int build_phy_plan(dnrp_ctx* c) {
             return t;
         };
         for (uint32_t ts = 0; ts < 8; ++ts) d.last_plan[ts] = ts < d.N_eff_TX ? plan_word(ts, d.N_DF, false) : 0u;
-        UP(c->d_pcc_plan.upload(build(m.pcc_lk, true)));
-        UP(c->d_pdc_plan.upload(d.N_SS > 1 ? build_sm(m.pdc_lk) : build(m.pdc_lk, false)));
+        pcc_plan_h = build(m.pcc_lk, true);
+        pdc_plan_h = d.N_SS > 1 ? build_sm(m.pdc_lk) : build(m.pdc_lk, false);
+        UP(c->d_pcc_plan.upload(pcc_plan_h));
+        UP(c->d_pdc_plan.upload(pdc_plan_h));
     }
     static const double nu_max[3] = {100.0, 100.0, 500.0}, tau_rms[3] = {0.1e-6, 0.1e-6, 1.0e-6},
                         snr_db[3] = {-5.0, 15.0, 35.0};
@@ -203,6 +206,50 @@ int build_phy_plan(dnrp_ctx* c) {
                          Ll.n_interp, Ll.n_t};
         d.wiener_lr[i] = {c->d_wiener_lr[i].idx_pilot.p, c->d_wiener_lr[i].idx_weight.p,
                           c->d_wiener_lr[i].weights.p, Llr.n_interp, Llr.n_t};
+        // transmit diversity: merged window per (unit, stream slot), the arithmetic of chan_est_rx_pair done once here
+        auto build_pair = [&](const std::vector<uint32_t>& lk, const std::vector<uint32_t>& plan, dnrp_ctx::pair_bufs_t& buf,
+                              phy_dims_t::pair_lut_t& out) -> int {
+            const uint32_t units = (uint32_t)lk.size() / 2;
+            out = {nullptr, nullptr, units};
+            if (units == 0) return DNRP_OK;
+            const bool lr = ((plan[0] >> 21) & 1u) != 0u;     // one mode per list (plan_word above)
+            const spec::wiener_lut_t& L = lr ? Llr : Ll;
+            const uint32_t NT = L.n_interp + 1;
+            std::vector<uint16_t> info(2 * (size_t)units, 0xffffu);
+            std::vector<float> w((size_t)NT * 2 * units, 0.f);
+            for (uint32_t u = 0; u < units; ++u)
+                for (uint32_t s_ = 0; s_ < 2; ++s_) {
+                    const uint32_t pw = plan[2 * u + s_], base = pw & 63u;
+                    if ((((pw >> 21) & 1u) != 0u) != lr) return DNRP_ERR_INVALID;
+                    const uint32_t k0 = lk[2 * u] & 0xffffu, k1 = lk[2 * u + 1] & 0xffffu;
+                    const uint32_t o0 = base * d.Nk + k0, o1 = base * d.Nk + k1;
+                    const uint32_t m0 = L.idx_pilot[o0], m1 = L.idx_pilot[o1];
+                    const uint32_t mmin = std::min(m0, m1), d0 = m0 - mmin, d1 = m1 - mmin;
+                    if (d0 + d1 > 1u || mmin > 1023u) continue;
+                    const uint32_t nt = L.n_interp + d0 + d1;
+                    const float* w0 = L.weights.data() + (size_t)L.idx_weight[o0] * L.n_interp;
+                    const float* w1 = L.weights.data() + (size_t)L.idx_weight[o1] * L.n_interp;
+                    for (uint32_t t = 0; t < nt; ++t) {
+                        const float a0 = (t >= d0 && t - d0 < L.n_interp) ? w0[t - d0] : 0.f;
+                        const float a1 = (t >= d1 && t - d1 < L.n_interp) ? w1[t - d1] : 0.f;
+                        w[((size_t)t * 2 + s_) * units + u] = 0.5f * (a0 + a1);
+                    }
+                    info[(size_t)s_ * units + u] = (uint16_t)(mmin | nt << 10);
+                }
+            UP(buf.info.upload(info));
+            UP(buf.w.upload(w));
+            out = {buf.info.p, buf.w.p, units};
+            return DNRP_OK;
+        };
+        d.pcc_pair[i] = {nullptr, nullptr, 0};
+        d.pdc_pair[i] = {nullptr, nullptr, 0};
+        if (d.N_eff_TX != 1) {
+            if (build_pair(m.pcc_lk, pcc_plan_h, c->d_pcc_pair[i], d.pcc_pair[i]) != DNRP_OK ||
+                (d.N_SS == 1 && build_pair(m.pdc_lk, pdc_plan_h, c->d_pdc_pair[i], d.pdc_pair[i]) != DNRP_OK)) {
+                set_last_error("merged Wiener window tables: construction failed");
+                return DNRP_ERR_INVALID;
+            }
+        }
     }
     // RX window: the packet plus room for two STFs (the detection ignores the first STF + 1 pattern of a window
     // and the fine search looks one pattern to either side of the coarse peak)

@@ -427,6 +427,31 @@ int dnrp_kernel_time_read(dnrp_ctx_t* ctx, int kernel, float* ms_total, uint32_t
 /* number of kernel launches issued on the context's stream since creation (all kernels of this library) */
 uint64_t dnrp_launch_count(const dnrp_ctx_t* ctx);
 
+/* ---- multi-GPU: the counter reduction --------------------------------------------------------
+ * Packets (and sweep cells) shard across GPUs with no data-path exchange; the only collective is one all-reduce over the
+ * experiment's counter vector.  The reference has no multi-device code: its counters are the members of
+ * one result_t / worker statistics object in one process (lib/src/upper/loopback/result.cpp:26-103,
+ * lib/src/phy/pool/worker_tx_rx.cpp:96-198 stats.rx_pcc_* / rx_pdc_*); these entry points replace "add into the shared object" by ncclAllReduce over
+ * NVLink / NVSwitch.  NCCL is bound at run time (dlopen of libnccl.so.2; nothing else in this library needs it) --
+ * DNRP_ERR_STATE if it cannot be loaded.
+ *
+ * One communicator per context.  Multi-process (one rank per GPU, e.g. under torchrun / MPI): rank 0 calls
+ * dnrp_comm_unique_id and hands the 128 bytes to the others by any means, then every rank calls dnrp_comm_init_rank (a
+ * collective).  Single process, several GPUs (one batch_phy_t per GPU): dnrp_comm_init_all over the
+ * contexts, and the reduction through dnrp_counters_allreduce_all (one NCCL group).
+ * dnrp_counters_allreduce: counters[n] int64 (host memory), reduced in place over all ranks; op 0 = sum, 1 = min,
+ * 2 = max; n <= DNRP_COMM_MAX_COUNTERS; a collective: every rank calls it with the same n and op.  The reduction runs
+ * on the context's stream behind whatever was queued there. */
+#define DNRP_COMM_ID_BYTES 128
+#define DNRP_COMM_MAX_COUNTERS 65536
+int dnrp_comm_unique_id(uint8_t id[DNRP_COMM_ID_BYTES]);
+int dnrp_comm_init_rank(dnrp_ctx_t* ctx, int n_ranks, int rank, const uint8_t id[DNRP_COMM_ID_BYTES]);
+int dnrp_comm_init_all(dnrp_ctx_t* const* ctxs, int n_ctx);
+int dnrp_counters_allreduce(dnrp_ctx_t* ctx, int64_t* counters, uint32_t n, int op);
+/* counters [n_ctx][n]: row i belongs to ctxs[i]; every row holds the reduced vector afterwards */
+int dnrp_counters_allreduce_all(dnrp_ctx_t* const* ctxs, int n_ctx, int64_t* counters, uint32_t n, int op);
+int dnrp_comm_destroy(dnrp_ctx_t* ctx);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,6 @@
+python -m pytest tests/test_rx_gpu.py tests/test_golden_gpu.py tests/test_ref_gpu.py tests/test_rx_mimo_gpu.py tests/test_resample_gpu.py tests/test_host_cpp.py tests/test_multi_network_gpu.py -m gpu -x -q 2>&1 | tail -3
+python bench.py --steps 10 --warmup 3 > gpurun_out/ab_demap.json 2>/dev/null; python - <<PY
+import json
+d=json.loads(open('gpurun_out/ab_demap.json').read().strip().splitlines()[-1])
+print(d['ms_per_step'], [(k['kernel'],round(k['ms_per_step'],3)) for k in d['roofline']['kernels']], d['config']['crc_ok'])
+PY
