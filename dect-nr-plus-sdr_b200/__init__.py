@@ -160,6 +160,40 @@ def large_scale_via_pathloss(tx_power_ant_0dBFS, rx_power_ant_0dBFS, distance_m,
     return float(f(tx_power_ant_0dBFS, rx_power_ant_0dBFS, distance_m, freq_Hz, int(same_node), tx_into_rx_leakage_dB))
 
 
+def _nccl_of_torch_first():
+    # the library binds NCCL with dlopen("libnccl.so.2"); the loader keeps ONE library per soname, so the copy PyTorch
+    # ships must be mapped before ours asks -- otherwise a later `import torch` would find the system's (older) NCCL
+    # under that name and fail to resolve its symbols
+    try:
+        import torch  # noqa: F401
+    except ImportError:
+        pass
+
+
+def comm_unique_id():
+    """dnrp_comm_unique_id: the 128 bytes rank 0 hands to every other rank before comm_init_rank"""
+    _nccl_of_torch_first()
+    buf = C.create_string_buffer(128)
+    _check(lib().dnrp_comm_unique_id(buf))
+    return buf.raw
+
+
+def comm_init_all(phys):
+    """dnrp_comm_init_all: one communicator over several contexts (one per GPU) of this process"""
+    _nccl_of_torch_first()
+    arr = (C.c_void_p * len(phys))(*[p._ctx for p in phys])
+    _check(lib().dnrp_comm_init_all(arr, len(phys)))
+
+
+def counters_allreduce_all(phys, counters, op="sum"):
+    """dnrp_counters_allreduce_all: counters [len(phys)][n], row i belongs to phys[i]; every row holds the result"""
+    a = np.ascontiguousarray(counters, dtype=np.int64).copy()
+    assert a.ndim == 2 and a.shape[0] == len(phys)
+    arr = (C.c_void_p * len(phys))(*[p._ctx for p in phys])
+    _check(lib().dnrp_counters_allreduce_all(arr, len(phys), _ptr(a, np.int64), a.shape[1], {"sum": 0, "min": 1, "max": 2}[op]))
+    return a
+
+
 class Phy:
     """One context = one GPU + one packet geometry + a maximum batch size."""
 
@@ -178,6 +212,20 @@ class Phy:
         self.oversampling = oversampling
         self.resample = tuple(resample)
         self.dbits_stride = ((self.ps["G"] + 7) // 8 + 3) & ~3
+
+    # ---- multi-GPU counter reduction (api_comm.cu; one NCCL all-reduce over the counter vector)
+    def comm_init_rank(self, n_ranks, rank, unique_id):
+        """dnrp_comm_init_rank: collective over all ranks; unique_id = comm_unique_id() of rank 0 (128 bytes)"""
+        assert len(unique_id) == 128
+        _nccl_of_torch_first()
+        _check(lib().dnrp_comm_init_rank(self._ctx, int(n_ranks), int(rank), C.c_char_p(bytes(unique_id))))
+
+    def counters_allreduce(self, counters, op="sum"):
+        """dnrp_counters_allreduce: int64 vector reduced in place over all ranks (op: sum, min, max)"""
+        a = np.ascontiguousarray(counters, dtype=np.int64).reshape(-1).copy()
+        _nccl_of_torch_first()
+        _check(lib().dnrp_counters_allreduce(self._ctx, _ptr(a, np.int64), a.size, {"sum": 0, "min": 1, "max": 2}[op]))
+        return a.reshape(np.shape(counters))
 
     def close(self):
         if self._ctx:

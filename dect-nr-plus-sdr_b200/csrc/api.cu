@@ -157,6 +157,7 @@ int dnrp_ctx_create(const dnrp_config_t* cfg, int device, dnrp_ctx_t** out) {
 
 void dnrp_ctx_destroy(dnrp_ctx_t* ctx) {
     if (!ctx) return;
+    dnrp_comm_destroy(ctx);   // communicator and staging buffer of the counter reduction, if any (api_comm.cu)
     cudaSetDevice(ctx->device);
     if (ctx->stream) cudaStreamDestroy(ctx->stream);
     if (ctx->stream_copy) cudaStreamDestroy(ctx->stream_copy);

@@ -5,6 +5,7 @@
 // the library has no link-time dependency on it and a process that never reduces never loads it.
 #include <dlfcn.h>
 #include <nccl.h>
+#include <cstdlib>
 #include <cstring>
 #include <mutex>
 #include <unordered_map>
@@ -39,8 +40,12 @@ const nccl_api_t* nccl() {
     static std::once_flag once;
     static bool ok = false;
     std::call_once(once, [] {
-        // a copy already mapped into the process (e.g. the one bundled with PyTorch) answers by its soname
-        api.so = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
+        // a copy already mapped into the process (e.g. the one bundled with PyTorch) answers by its soname -- and the
+        // other way round: a process that loads PyTorch LATER gets this copy for PyTorch's own NCCL calls, so such a
+        // process imports torch first (the Python binding does) or names the library to use in DNRP_NCCL_LIB
+        const char* path = getenv("DNRP_NCCL_LIB");
+        if (path && path[0]) api.so = dlopen(path, RTLD_NOW | RTLD_LOCAL);
+        if (!api.so) api.so = dlopen("libnccl.so.2", RTLD_NOW | RTLD_LOCAL);
         if (!api.so) api.so = dlopen("libnccl.so", RTLD_NOW | RTLD_LOCAL);
         if (!api.so) return;
 #define DNRP_SYM(name) api.name = reinterpret_cast<decltype(api.name)>(dlsym(api.so, "nccl" #name))
@@ -145,8 +150,6 @@ int dnrp_counters_allreduce_all(dnrp_ctx_t* const* ctxs, int n_ctx, int64_t* cou
     DNRP_REQUIRE(ctxs && counters && n_ctx >= 1, "null argument");
     DNRP_REQUIRE(n >= 1 && n <= DNRP_COMM_MAX_COUNTERS, "counter count out of range");
     DNRP_REQUIRE(op >= 0 && op <= 2, "op: 0 sum, 1 min, 2 max");
-    const nccl_api_t* api = nccl();
-    if (!api) return DNRP_ERR_STATE;
     std::vector<comm_state_t*> st(n_ctx);
     for (int i = 0; i < n_ctx; ++i) {
         DNRP_REQUIRE(ctxs[i], "null context");
@@ -156,6 +159,8 @@ int dnrp_counters_allreduce_all(dnrp_ctx_t* const* ctxs, int n_ctx, int64_t* cou
             return DNRP_ERR_STATE;
         }
     }
+    const nccl_api_t* api = nccl();   // after the state checks: a call that is refused does not load NCCL
+    if (!api) return DNRP_ERR_STATE;
     for (int i = 0; i < n_ctx; ++i) {
         DNRP_CUDA(cudaSetDevice(ctxs[i]->device));
         DNRP_CUDA(cudaMemcpyAsync(st[i]->d_buf, counters + (size_t)i * n, sizeof(int64_t) * n, cudaMemcpyHostToDevice,

@@ -425,6 +425,34 @@ class batch_phy_t {
         uint32_t get_rx_stride() const { return rx_stride; }
         uint32_t get_N_RX() const { return config.N_RX ? config.N_RX : 1; }
         const stats_t& get_stats() const { return stats; }
+
+        /// Several batch_phy_t of ONE process, one per GPU: the sum of their counters in one NCCL all-reduce over the
+        /// GPUs (dnrp_comm_init_all / dnrp_counters_allreduce_all; the reference adds into the members of one
+        /// worker_pool_t / result_t of one process, worker_tx_rx.cpp:96-198, result.cpp:78-95).  The communicator is
+        /// created by the first call.  Every PHY's own stats stay untouched; the totals are returned.
+        static stats_t reduce_stats(const std::vector<batch_phy_t*>& phys) {
+            std::vector<dnrp_ctx_t*> ctxs;
+            for (batch_phy_t* p : phys) ctxs.push_back(p->ctx);
+            bool have = true;
+            for (batch_phy_t* p : phys) have = have && p->comm_ready;
+            if (!have) {
+                for (batch_phy_t* p : phys) if (p->comm_ready) { dnrp_comm_destroy(p->ctx); p->comm_ready = false; }
+                check(dnrp_comm_init_all(ctxs.data(), (int)ctxs.size()), "dnrp_comm_init_all");
+                for (batch_phy_t* p : phys) p->comm_ready = true;
+            }
+            constexpr uint32_t NC = 6;
+            std::vector<int64_t> c(NC * phys.size());
+            for (size_t i = 0; i < phys.size(); ++i) {
+                const stats_t& s = phys[i]->stats;
+                const uint64_t v[NC] = {s.windows, s.detections, s.pcc_ok, s.pdc_requested, s.pdc_crc_ok, s.tx_packets};
+                for (uint32_t j = 0; j < NC; ++j) c[i * NC + j] = (int64_t)v[j];
+            }
+            check(dnrp_counters_allreduce_all(ctxs.data(), (int)ctxs.size(), c.data(), NC, 0), "dnrp_counters_allreduce_all");
+            stats_t t;
+            t.windows = (uint64_t)c[0]; t.detections = (uint64_t)c[1]; t.pcc_ok = (uint64_t)c[2];
+            t.pdc_requested = (uint64_t)c[3]; t.pdc_crc_ok = (uint64_t)c[4]; t.tx_packets = (uint64_t)c[5];
+            return t;
+        }
         dnrp_ctx_t* get_ctx() { return ctx; }
 
         /// tx_t::generate_tx_packet for every descriptor (worker_tx_rx.cpp:300-335): IQ [n][N_TX][tx_stride] into iq_out
@@ -761,6 +789,7 @@ class batch_phy_t {
         sp3::packet_sizes_t packet_sizes{};
         uint32_t tx_stride{0}, rx_stride{0};
         stats_t stats;
+        bool comm_ready{false};
         static void check(int rc, const char* what) {
             if (rc != DNRP_OK) throw std::runtime_error(std::string(what) + ": " + dnrp_last_error_string());
         }

@@ -135,6 +135,26 @@ int main(int argc, char** argv) {
         std::fprintf(stderr, "multi_plan_firmware: %s\n", e.what());
         return 2;
     }
+    // the counters of all PHYs of this process in one NCCL all-reduce (one rank per GPU; a single GPU reduces over itself)
+    try {
+        std::vector<phy::batch_phy_t*> all;
+        uint64_t crc_sum = 0, win_sum = 0;
+        for (int d = 0; d < used; ++d) {
+            all.push_back(bp[d].get());
+            crc_sum += bp[d]->get_stats().pdc_crc_ok;
+            win_sum += bp[d]->get_stats().windows;
+        }
+        const phy::batch_phy_t::stats_t tot = phy::batch_phy_t::reduce_stats(all);
+        if (tot.pdc_crc_ok != crc_sum || tot.windows != win_sum || tot.pdc_crc_ok == 0) {
+            std::fprintf(stderr, "multi_plan_firmware: reduced counters %llu / %llu differ from the host sums %llu / %llu\n",
+                         (unsigned long long)tot.pdc_crc_ok, (unsigned long long)tot.windows, (unsigned long long)crc_sum,
+                         (unsigned long long)win_sum);
+            ++fails;
+        }
+    } catch (const std::exception& e) {
+        std::fprintf(stderr, "multi_plan_firmware: counter reduction: %s\n", e.what());
+        return 2;
+    }
     std::printf("{\"n\": %u, \"gpus\": %d, \"work_pcc\": %u, \"work_pdc\": %u, \"work_pdc_error\": %u, \"plcf_mismatch\": %u, "
                 "\"tb_mismatch\": %u, \"fails\": %d}\n", n, used, fw[0]->n_work_pcc, fw[0]->n_work_pdc, fw[0]->n_work_pdc_error,
                 fw[0]->n_plcf_mismatch, fw[0]->n_tb_mismatch, fails);
