@@ -126,7 +126,7 @@ struct dnrp_ctx {
     dnrp::dbuf<uint32_t> d_cell, d_pcc_lk, d_pdc_lk, d_pcc_plan, d_pdc_plan;
     dnrp::dbuf<int8_t> d_stf_sign, d_W;
     dnrp::dbuf<float> d_W_scale, d_W_scale_opt;
-    dnrp::dbuf<float2> d_twiddle;
+    dnrp::dbuf<float2> d_twiddle, d_twiddle_1k;
     uint32_t tx_stride = 0;  // samples per antenna in d_iq_tx
     dnrp::dbuf<float2> d_iq_tx;
     dnrp::dbuf<dnrp::tx_meta_dev_t> d_tx_meta;

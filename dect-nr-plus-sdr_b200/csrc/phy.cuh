@@ -32,6 +32,8 @@ struct phy_dims_t {
     const float* W_scale;      // [n_cb_idx]
     const float* W_scale_opt;  // [n_cb_idx] "optimal DAC" variant
     const float2* twiddle;     // [N_os]
+    const float2* twiddle_1k;  // N_os = 1024 only: the same values in the order k_rx_fft1024 reads them -- [15][16]
+                               // W_256^(k r) at (r - 1) 16 + k, then [3][256] W_1024^(j r) at 240 + (r - 1) 256 + j
     // receiver
     uint32_t chestim_lr, chestim_stride;    // phy.json chestim_mode_lr_default / _t_stride_default
     uint32_t n_full_ps;                     // full processing stages in lr mode (rx_synced.cpp:1031-1032)

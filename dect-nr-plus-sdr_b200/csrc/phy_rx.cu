@@ -324,7 +324,8 @@ __global__ void __launch_bounds__(256, 4) k_rx_fft1024(const rx_params_t p) {
     const uint32_t l = item / d.N_RX + 1, a = item - (l - 1) * d.N_RX;
     const rx_state_t& st = p.state[pkt];
     float2* A = sm + grp * BL;
-    const float2* __restrict__ table = d.twiddle;
+    const float2* __restrict__ tw16 = d.twiddle_1k;          // [15][16] W_256^(k r)
+    const float2* __restrict__ tw4 = d.twiddle_1k + 240;     // [3][256] W_1024^(j r)
 
     const uint32_t n0 = d.stf_len_os + (l - 1) * d.sym_len_os + d.cp_os;
     float2 v[16];
@@ -352,7 +353,7 @@ __global__ void __launch_bounds__(256, 4) k_rx_fft1024(const rx_params_t p) {
         for (int r = 0; r < 16; ++r) v[r] = xj[68 * r];
         group_bar(grp);
 #pragma unroll
-        for (int r = 1; r < 16; ++r) v[r] = cmul(v[r], __ldg(table + 4 * k * r));
+        for (int r = 1; r < 16; ++r) v[r] = cmul(v[r], __ldg(tw16 + (r - 1) * 16 + k));
         dft16<false>(v);
         float2* yj = A + 272 * q + k;
 #pragma unroll
@@ -372,7 +373,7 @@ __global__ void __launch_bounds__(256, 4) k_rx_fft1024(const rx_params_t p) {
     for (int i = 0; i < 4; ++i) {
         const uint32_t j = tid + 64 * i;
 #pragma unroll
-        for (int r = 1; r < 4; ++r) v[4 * i + r] = cmul(v[4 * i + r], __ldg(table + j * r));
+        for (int r = 1; r < 4; ++r) v[4 * i + r] = cmul(v[4 * i + r], __ldg(tw4 + (r - 1) * 256 + j));
         dft4<false>(v[4 * i], v[4 * i + 1], v[4 * i + 2], v[4 * i + 3]);
 #pragma unroll
         for (int r = 0; r < 4; ++r) A[j + 256 * r] = v[4 * i + r];
