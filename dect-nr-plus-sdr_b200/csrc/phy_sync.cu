@@ -169,15 +169,27 @@ __global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32
             // serial prefix per thread chunk + chunk offsets (three arrays at once)
             const uint32_t per = (S2 + nthr - 1) / nthr, lo = min(tid * per, S2), hi = min(lo + per, S2);
             float sr = 0.f, si = 0.f, sp = 0.f;
-            for (uint32_t i = lo; i < hi; ++i) {
-                const float2 b = x[i];
+            auto acc1 = [&](uint32_t i, float2 b, float2 e) {   // one sample, in index order (the sums are order sensitive)
                 sp += b.x * b.x + b.y * b.y;
                 if (i >= pat) {
-                    const float2 e = x[i - pat];
                     sr += e.x * b.x + e.y * b.y;
                     si += e.y * b.x - e.x * b.y;
                 }
                 Qr[i + 1] = sr; Qi[i + 1] = si; PW[i + 1] = sp;
+            };
+            // a thread walks `per` consecutive samples, so a warp's load touches 32 different lines whatever its width:
+            // two samples per 16-byte load halve the number of such loads (same values, same order of additions)
+            const bool vec = ((per | lo | hi | pat) & 1u) == 0u && ((reinterpret_cast<uintptr_t>(x) & 15u) == 0u);
+            if (vec) {
+                const float4* x4 = reinterpret_cast<const float4*>(x);
+                for (uint32_t i = lo; i < hi; i += 2) {
+                    const float4 b = x4[i >> 1];
+                    const float4 e = i >= pat ? x4[(i - pat) >> 1] : make_float4(0.f, 0.f, 0.f, 0.f);
+                    acc1(i, make_float2(b.x, b.y), make_float2(e.x, e.y));
+                    acc1(i + 1, make_float2(b.z, b.w), make_float2(e.z, e.w));
+                }
+            } else {
+                for (uint32_t i = lo; i < hi; ++i) acc1(i, x[i], i >= pat ? x[i - pat] : make_float2(0.f, 0.f));
             }
             float* part = reinterpret_cast<float*>(s_part);
             if (tid == 0) { Qr[0] = Qi[0] = PW[0] = 0.f; }
@@ -199,14 +211,42 @@ __global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32
             if (tid == 0) s_best = 0ull;
             __syncthreads();
             unsigned long long mine = 0ull;
-            for (uint32_t k = tid; k < stf_len; k += nthr) {
-                float s = 0.f;
-                const uint32_t k0 = k + 1 >= sm_len ? k + 1 - sm_len : 0;
-                for (uint32_t q = k0; q <= k; ++q) s += M[q];
+            auto consider = [&](uint32_t k, float s) {
                 const float mean = s / (float)sm_len;
                 // larger mean wins, first position on ties: key = (float bits, inverted position)
                 const unsigned long long key = ((unsigned long long)__float_as_uint(mean) << 32) | (0xffffffffu - k);
                 if (mean > 0.f && key > mine) mine = key;
+            };
+            constexpr uint32_t SMK = 7, SML = 33;   // beta x oversampling = 16 with 256 threads: 7 positions per thread
+            if (sm_len == SML && stf_len == SMK * nthr) {
+                // a thread takes SMK CONSECUTIVE positions: their windows overlap, the SML + SMK - 1 metrics are read once
+                // into registers; every window is still summed from its oldest element upwards (same rounding)
+                const uint32_t kf = tid * SMK;
+                if (kf + 1 >= SML) {
+                    float m[SML + SMK - 1];
+#pragma unroll
+                    for (uint32_t q = 0; q < SML + SMK - 1; ++q) m[q] = M[kf + 1 - SML + q];
+#pragma unroll
+                    for (uint32_t i = 0; i < SMK; ++i) {
+                        float s = 0.f;
+#pragma unroll
+                        for (uint32_t q = 0; q < SML; ++q) s += m[i + q];
+                        consider(kf + i, s);
+                    }
+                } else {
+                    for (uint32_t k = kf; k < kf + SMK; ++k) {
+                        float s = 0.f;
+                        const uint32_t k0 = k + 1 >= sm_len ? k + 1 - sm_len : 0;
+                        for (uint32_t q = k0; q <= k; ++q) s += M[q];
+                        consider(k, s);
+                    }
+                }
+            } else
+            for (uint32_t k = tid; k < stf_len; k += nthr) {
+                float s = 0.f;
+                const uint32_t k0 = k + 1 >= sm_len ? k + 1 - sm_len : 0;
+                for (uint32_t q = k0; q <= k; ++q) s += M[q];
+                consider(k, s);
             }
             atomicMax(&s_best, mine);
             __syncthreads();
