@@ -138,6 +138,7 @@ int run_sync(dnrp_ctx* c, uint32_t n, uint32_t search_length, bool hand_over) {
     p.templates = c->d_sync_tpl.p; p.n_tpl = c->sync_n_tpl;
     p.xc = c->d_sync_xc.p + off * c->sync_n_tpl;
     p.xc_fft_n = c->sync_fft_n; p.tpl_spec = c->d_sync_tpl_spec.p; p.xc_twiddle = c->d_sync_tw.p;
+    p.xc_twiddle_p16 = c->d_sync_tw_p16.p;
     p.result = c->d_sync_result.p + off;
     p.rx_state = hand_over ? c->d_rx_state.p + off : nullptr;
     c->launches += 3;  // launch_sync issues four kernels

@@ -85,6 +85,7 @@ sync_params_t stream_sync_params(dnrp_ctx* c, uint32_t len, uint32_t n_steps) {
     p.templates = c->d_sync_tpl.p; p.n_tpl = c->sync_n_tpl;
     p.xc = c->d_stream_xc.p;
     p.xc_fft_n = c->sync_fft_n; p.tpl_spec = c->d_sync_tpl_spec.p; p.xc_twiddle = c->d_sync_tw.p;
+    p.xc_twiddle_p16 = c->d_sync_tw_p16.p;
     p.result = c->d_stream_result.p;
     p.rx_state = nullptr;
     p.resume = c->d_stream_resume.p;

@@ -126,7 +126,7 @@ struct dnrp_ctx {
     dnrp::dbuf<uint32_t> d_cell, d_pcc_lk, d_pdc_lk, d_pcc_plan, d_pdc_plan;
     dnrp::dbuf<int8_t> d_stf_sign, d_W;
     dnrp::dbuf<float> d_W_scale, d_W_scale_opt;
-    dnrp::dbuf<float2> d_twiddle, d_twiddle_1k;
+    dnrp::dbuf<float2> d_twiddle, d_twiddle_p4, d_twiddle_p16;
     uint32_t tx_stride = 0;  // samples per antenna in d_iq_tx
     dnrp::dbuf<float2> d_iq_tx;
     dnrp::dbuf<dnrp::tx_meta_dev_t> d_tx_meta;
@@ -173,6 +173,7 @@ struct dnrp_ctx {
     uint32_t sync_n_tpl = 0, sync_step = 0, sync_n_steps = 0;
     dnrp::dbuf<float2> d_sync_tpl, d_sync_c, d_sync_xc;
     uint32_t sync_fft_n = 0;                       // FFT size of the fast cross-correlation (0: direct)
+    dnrp::dbuf<float2> d_sync_tw_p16;
     dnrp::dbuf<float2> d_sync_tpl_spec, d_sync_tw; // conj(FFT(template)) / N, twiddles of that size
     dnrp::dbuf<float> d_sync_p;
     dnrp::dbuf<dnrp::sync_result_dev_t> d_sync_result;

@@ -79,10 +79,14 @@ __device__ __forceinline__ void dft16(float2 (&v)[16]) {
 // k * r * tstep < Ns * R * N / (Ns * R) = N, so the twiddle index needs no reduction; the first pass (Ns == 1) has unit
 // twiddles.  pin / pout: the source / destination buffer is padded (fft_pad); N/R and, from the second pass on, Ns are
 // multiples of 16, so the padded position of element r is base + r * padded stride.
+// ptab (optional): this pass's twiddles in the order the lanes read them, W_{Ns R}^(k r) at (r - 1) Ns + k
+// (fft_pass_tables below) -- consecutive butterflies read consecutive entries, one or two 128-byte lines per warp load,
+// where table[k r tstep] scatters a warp over up to sixteen lines.  Same values, same results.
 template <bool INV, int R, bool POW2, bool PAD>
 __device__ __forceinline__ void fft_pass(const float2* __restrict__ x, float2* __restrict__ y, uint32_t N,
                                          uint32_t Ns, uint32_t log2Ns, const float2* __restrict__ table, bool pin_, bool pout_,
-                                         uint32_t tid = threadIdx.x, uint32_t nthr = blockDim.x, uint32_t tmul = 1) {
+                                         uint32_t tid = threadIdx.x, uint32_t nthr = blockDim.x, uint32_t tmul = 1,
+                                         const float2* __restrict__ ptab = nullptr) {
     const bool pin = PAD && pin_, pout = PAD && pout_;   // PAD = false: plain buffers, no index selects in the code
     const uint32_t M = N / R;
     const uint32_t tstep = POW2 ? M >> log2Ns : N / (Ns * R);  // W_{Ns*R}^k = W_N^{k*tstep}
@@ -95,9 +99,14 @@ __device__ __forceinline__ void fft_pass(const float2* __restrict__ x, float2* _
 #pragma unroll
         for (int r = 0; r < R; ++r) v[r] = xj[r * xs];
         if (Ns != 1) {
-            const uint32_t kt = k * tstep * tmul;   // tmul: the table belongs to a transform tmul times longer
+            if (ptab) {
 #pragma unroll
-            for (int r = 1; r < R; ++r) v[r] = cmul(v[r], tw<INV>(table, kt * r));
+                for (int r = 1; r < R; ++r) v[r] = cmul(v[r], tw<INV>(ptab, (r - 1) * Ns + k));
+            } else {
+                const uint32_t kt = k * tstep * tmul;   // tmul: the table belongs to a transform tmul times longer
+#pragma unroll
+                for (int r = 1; r < R; ++r) v[r] = cmul(v[r], tw<INV>(table, kt * r));
+            }
         }
         if constexpr (R == 2) {
             const float2 a = v[0], b = v[1];
@@ -143,8 +152,10 @@ __device__ __forceinline__ void fft_pass(const float2* __restrict__ x, float2* _
 // RADIX16 = false: radix-4 passes only and no padding (kernels whose block has four times more threads than N / 16
 // butterflies: measured slower with radix 16 -- k_rx_fft 0.84 -> 1.13 ms at N = 1024 with 256 threads, 32 -> 70
 // registers); true: the long transforms of the fine synchronisation (N = 3072 at beta = 16: 0.60 -> 0.45 ms).
+// ptab: per-pass twiddle tables of this size and plan (fft_pass_tables(N, RADIX16)), or nullptr.
 template <bool INV, bool RADIX16 = false>
-__device__ float2* block_fft(float2* a, float2* b, uint32_t N, const float2* __restrict__ table) {
+__device__ float2* block_fft(float2* a, float2* b, uint32_t N, const float2* __restrict__ table,
+                             const float2* __restrict__ ptab = nullptr) {
     uint32_t Ns = 1, lg = 0;
     uint32_t rem = N;
     bool first = true;
@@ -152,7 +163,8 @@ __device__ float2* block_fft(float2* a, float2* b, uint32_t N, const float2* __r
 #define DNRP_FFT_PASS(R, P2, LGINC)                                                          \
     {                                                                                        \
         const bool last = rem == R;                                                          \
-        fft_pass<INV, R, P2, RADIX16>(a, b, N, Ns, lg, table, !first, !last);                \
+        fft_pass<INV, R, P2, RADIX16>(a, b, N, Ns, lg, table, !first, !last, threadIdx.x, blockDim.x, 1, ptab); \
+        if (ptab && Ns != 1) ptab += (R - 1) * Ns;                                           \
         Ns *= R; lg += LGINC; rem /= R; first = false;                                       \
         float2* t = a; a = b; b = t;                                                         \
         __syncthreads();                                                                     \
@@ -180,7 +192,7 @@ __device__ float2* block_fft(float2* a, float2* b, uint32_t N, const float2* __r
 // indices).  Every thread of the block must call it (active = false: only takes part in the barriers).
 template <bool INV>
 __device__ float2* group_fft16(float2 (&v)[16], float2* a, float2* b, uint32_t N, const float2* __restrict__ table,
-                               uint32_t tid, uint32_t nthr, bool active) {
+                               uint32_t tid, uint32_t nthr, bool active, const float2* __restrict__ ptab = nullptr) {
     uint32_t Ns = 16, lg = 4, rem = N / 16;
     if (active) {
         dft16<INV>(v);
@@ -193,7 +205,8 @@ __device__ float2* group_fft16(float2 (&v)[16], float2* a, float2* b, uint32_t N
 #define DNRP_GFFT_PASS(R, P2, LGINC)                                                              \
     {                                                                                             \
         const bool last = rem == R;                                                               \
-        if (active) fft_pass<INV, R, P2, true>(a, b, N, Ns, lg, table, true, !last, tid, nthr);   \
+        if (active) fft_pass<INV, R, P2, true>(a, b, N, Ns, lg, table, true, !last, tid, nthr, 1, ptab);   \
+        if (ptab) ptab += (R - 1) * Ns;                                                           \
         Ns *= R; lg += LGINC; rem /= R;                                                           \
         float2* t = a; a = b; b = t;                                                              \
         __syncthreads();                                                                          \
@@ -276,4 +289,30 @@ __device__ void big_fft(float2* a, float2* s1, float2* s2, uint32_t N, const flo
     big_fft_rows<INV>(a, s1, s2, N, table, threadIdx.x, blockDim.x, true);
 }
 
+}  // namespace dnrp
+
+#include <vector>
+namespace dnrp {
+// Host: the per-pass twiddle tables of one transform size, concatenated in pass order.  tw = W_N^k (k < N); radix16 = the
+// plan of block_fft<.., true> / group_fft16 (16s, then 4s, 2, 3s), else that of block_fft<.., false> (4s, 2, 3s).  A pass
+// of radix R entered with Ns > 1 contributes W_{Ns R}^(k r) = tw[k r N / (Ns R)] at (r - 1) Ns + k; the first pass
+// (Ns = 1) has unit twiddles and no entries.  N = 1024, radix16: [15][16], then [3][256] (k_rx_fft1024 reads these).
+inline std::vector<float2> fft_pass_tables(const std::vector<float2>& tw, bool radix16) {
+    const uint32_t N = (uint32_t)tw.size();
+    std::vector<float2> out;
+    uint32_t Ns = 1, rem = N;
+    auto pass = [&](uint32_t R) {
+        if (Ns != 1) {
+            const uint32_t tstep = N / (Ns * R);
+            for (uint32_t r = 1; r < R; ++r)
+                for (uint32_t k = 0; k < Ns; ++k) out.push_back(tw[(size_t)k * tstep * r]);
+        }
+        Ns *= R; rem /= R;
+    };
+    if (radix16) while (rem % 16 == 0) pass(16);
+    while (rem % 4 == 0) pass(4);
+    if (rem % 2 == 0) pass(2);
+    while (rem % 3 == 0) pass(3);
+    return out;
+}
 }  // namespace dnrp

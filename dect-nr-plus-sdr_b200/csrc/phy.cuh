@@ -32,8 +32,10 @@ struct phy_dims_t {
     const float* W_scale;      // [n_cb_idx]
     const float* W_scale_opt;  // [n_cb_idx] "optimal DAC" variant
     const float2* twiddle;     // [N_os]
-    const float2* twiddle_1k;  // N_os = 1024 only: the same values in the order k_rx_fft1024 reads them -- [15][16]
-                               // W_256^(k r) at (r - 1) 16 + k, then [3][256] W_1024^(j r) at 240 + (r - 1) 256 + j
+    // the same values per pass in the order the lanes read them (fft.cuh fft_pass_tables): radix-4 plan / radix-16 plan;
+    // N_os = 1024, radix 16: [15][16] W_256^(k r), then [3][256] W_1024^(j r)
+    const float2* twiddle_p4;
+    const float2* twiddle_p16;
     // receiver
     uint32_t chestim_lr, chestim_stride;    // phy.json chestim_mode_lr_default / _t_stride_default
     uint32_t n_full_ps;                     // full processing stages in lr mode (rx_synced.cpp:1031-1032)
@@ -194,6 +196,7 @@ struct sync_params_t {
     uint32_t xc_fft_n;                     // 0: direct correlation
     const float2* tpl_spec;                // [n_tpl][xc_fft_n]
     const float2* xc_twiddle;              // [xc_fft_n]
+    const float2* xc_twiddle_p16;          // per-pass tables of that size, radix-16 plan (fft.cuh fft_pass_tables)
     float2* xc;                            // [packet][n_tpl] (max abs(xcorr), lag)
     sync_result_dev_t* result;             // [packet]
     rx_state_t* rx_state;                  // [packet] optional: receives t0 / CFO / rms for the synced receiver

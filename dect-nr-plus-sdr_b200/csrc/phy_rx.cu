@@ -118,7 +118,7 @@ __global__ void __launch_bounds__(256) k_rx_stf(const rx_params_t p) {
             F = X;   // bin k at big_fft_at(k, Mb)
         } else {
             for (uint32_t n = tid; n < d.N_os; n += nthr) X[n] = S[d.stf_cp_os + n];
-            F = block_fft<false>(X, Yb, d.N_os, d.twiddle);
+            F = block_fft<false>(X, Yb, d.N_os, d.twiddle, d.twiddle_p4);
         }
         for (uint32_t i = tid; i < NS; i += nthr) {
             const uint32_t k = stf_cell_k(i, d.N_OCC);
@@ -237,7 +237,7 @@ __global__ void __launch_bounds__(BIG ? 1024 : 256) k_rx_fft(const rx_params_t p
         big_fft_rows<false>(A, B, B + fft_buf_len(Mb), d.N_os, d.twiddle, tid, nthr, active);
         F = A;   // bin k at big_fft_at(k, Mb)
     } else {
-        F = group_fft16<false>(v, A, B, d.N_os, d.twiddle, tid, nthr, active);
+        F = group_fft16<false>(v, A, B, d.N_os, d.twiddle, tid, nthr, active, d.twiddle_p16);
     }
 
     float2 sn = make_float2(0.f, 0.f);
@@ -324,8 +324,8 @@ __global__ void __launch_bounds__(256, 4) k_rx_fft1024(const rx_params_t p) {
     const uint32_t l = item / d.N_RX + 1, a = item - (l - 1) * d.N_RX;
     const rx_state_t& st = p.state[pkt];
     float2* A = sm + grp * BL;
-    const float2* __restrict__ tw16 = d.twiddle_1k;          // [15][16] W_256^(k r)
-    const float2* __restrict__ tw4 = d.twiddle_1k + 240;     // [3][256] W_1024^(j r)
+    const float2* __restrict__ tw16 = d.twiddle_p16;         // [15][16] W_256^(k r)
+    const float2* __restrict__ tw4 = d.twiddle_p16 + 240;    // [3][256] W_1024^(j r)
 
     const uint32_t n0 = d.stf_len_os + (l - 1) * d.sym_len_os + d.cp_os;
     float2 v[16];

@@ -479,7 +479,7 @@ __global__ void __launch_bounds__(XF_THREADS, 3) k_sync_xcorr_fft(const sync_par
         w = cmul(w, ws);
         A[i] = r;
     }
-    const float2* X = block_fft<false, true>(A, B, N, p.xc_twiddle);
+    const float2* X = block_fft<false, true>(A, B, N, p.xc_twiddle, p.xc_twiddle_p16);
     float2 Xr[XF_MAX_PER_THREAD];
 #pragma unroll
     for (uint32_t r = 0; r < XF_MAX_PER_THREAD; ++r) {
@@ -495,7 +495,7 @@ __global__ void __launch_bounds__(XF_THREADS, 3) k_sync_xcorr_fft(const sync_par
             const uint32_t k = tid + r * XF_THREADS;
             if (k < N) A[k] = cmul(Xr[r], T[k]);
         }
-        const float2* c = block_fft<true, true>(A, B, N, p.xc_twiddle);
+        const float2* c = block_fft<true, true>(A, B, N, p.xc_twiddle, p.xc_twiddle_p16);
         unsigned long long mine = 0ull;
         for (uint32_t j = tid; j < n_lag; j += XF_THREADS) {
             const float2 v = c[j];

@@ -132,7 +132,7 @@ __global__ void __launch_bounds__(256) k_tx_ofdm(const txofdm_params_t p) {
         big_fft<true>(X, Y, Y + fft_buf_len(Mb), d.N_os, d.twiddle);
         x = X;   // time sample n at big_fft_at(n, Mb)
     } else {
-        x = block_fft<true>(X, Y, d.N_os, d.twiddle);
+        x = block_fft<true>(X, Y, d.N_os, d.twiddle, d.twiddle_p4);
     }
 
     // ---- cyclic prefix, STF cover sequence, mixer

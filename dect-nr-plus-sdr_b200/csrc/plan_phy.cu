@@ -4,6 +4,7 @@
 #include <cmath>
 #include <cstring>
 #include "ctx.hpp"
+#include "fft.cuh"
 #include "spec_wiener.hpp"
 
 namespace dnrp {
@@ -80,15 +81,11 @@ int build_phy_plan(dnrp_ctx* c) {
     UP(c->d_W_scale.upload(Ws));
     UP(c->d_W_scale_opt.upload(Wso));
     UP(c->d_twiddle.upload(tw));
-    if (d.N_os == 1024) {
-        // k_rx_fft1024 reads its twiddles lane-contiguously: a warp's load touches one or two 128-byte lines instead of
-        // up to sixteen (the loads of table[4 k r] were half of the kernel's load/store wavefronts)
-        std::vector<float2> t1k(240 + 768);
-        for (uint32_t r = 1; r < 16; ++r)
-            for (uint32_t k = 0; k < 16; ++k) t1k[(r - 1) * 16 + k] = tw[4 * k * r];
-        for (uint32_t r = 1; r < 4; ++r)
-            for (uint32_t j = 0; j < 256; ++j) t1k[240 + (r - 1) * 256 + j] = tw[j * r];
-        UP(c->d_twiddle_1k.upload(t1k));
+    // the same twiddles per pass, lane-contiguous (a warp's load then touches one or two 128-byte lines instead of up to
+    // sixteen: those scattered loads were half of the FFT kernels' load/store wavefronts)
+    if (d.N_os <= 4096) {
+        UP(c->d_twiddle_p4.upload(fft_pass_tables(tw, false)));
+        UP(c->d_twiddle_p16.upload(fft_pass_tables(tw, true)));
     }
     // ---- resampling to the hardware rate (tx.cpp:519-560 sample counts; resampler.cpp design)
     {
@@ -357,6 +354,7 @@ int build_phy_plan(dnrp_ctx* c) {
                         spec[(size_t)t * N + k] = make_float2((float)(re / N), (float)(-im / N));   // conj / N
                     }
                 UP(c->d_sync_tw.upload(twx));
+                UP(c->d_sync_tw_p16.upload(fft_pass_tables(twx, true)));
                 UP(c->d_sync_tpl_spec.upload(spec));
             }
         }
@@ -409,7 +407,8 @@ int build_phy_plan(dnrp_ctx* c) {
     d.pcc_plan = c->d_pcc_plan.p; d.pdc_plan = c->d_pdc_plan.p;
     d.stf_sign = c->d_stf_sign.p; d.W = c->d_W.p; d.W_scale = c->d_W_scale.p; d.W_scale_opt = c->d_W_scale_opt.p;
     d.twiddle = c->d_twiddle.p;
-    d.twiddle_1k = c->d_twiddle_1k.p;
+    d.twiddle_p4 = c->d_twiddle_p4.p;     // nullptr for the four-step sizes above 4096
+    d.twiddle_p16 = c->d_twiddle_p16.p;
     return DNRP_OK;
 }
 
