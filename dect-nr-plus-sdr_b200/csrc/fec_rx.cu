@@ -167,7 +167,11 @@ cudaError_t launch_derm(const tdec_params_t& p, uint32_t n_packets, uint32_t max
 // BULK (one item per block only): the streams of the soft buffer are staged by the copy engine (cp.async.bulk + mbarrier,
 // turbo_dec.cuh) and clamped in place, instead of a load / clamp / store loop per thread; the copy of the next half
 // iteration's parity stream is issued as soon as the shared arrays are free, so it overlaps the boundary / CRC work.
-template <bool GROUPED, bool BULK = false>
+// CKALIAS (one item per block only): the first two checkpoints of the backward pass are kept in the running decoder's
+// rows of AE / BS (dead between the boundary fetch and the store of the new boundaries) at the price of one more barrier
+// per half iteration: 14 rows of T words less, which lets K = 6080 ... 6144 keep four resident blocks per SM.  Sizes that
+// fit four blocks anyway run without it (the barrier and seven more registers cost 6 % there; launch_turbo_decode).
+template <bool GROUPED, bool BULK = false, bool CKALIAS = false>
 __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_decode(const tdec_params_t p, uint32_t tg, uint32_t smem_item_words,
                                                       uint32_t n_items) {
     static_assert(!(GROUPED && BULK), "bulk staging is for one item per block");
@@ -211,13 +215,19 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
     uint32_t* EXT = smem;
     uint32_t* XIN = EXT + KH;
     uint32_t* PAR = XIN + KH;
-    uint32_t* CK = PAR + KH;                 // [nck][7][T]
-    uint32_t* AE = CK + nck * 7 * T;         // [2][7][T]
+    const uint32_t nck_own = CKALIAS ? (nck > 2 ? nck - 2 : 0) : nck;   // CKALIAS: checkpoints 0 and 1 live in AE / BS (ck_rows)
+    uint32_t* CK = PAR + KH;                 // [nck_own][7][T]
+    uint32_t* AE = CK + nck_own * 7 * T;     // [2][7][T]
     uint32_t* BS = AE + 2 * 7 * T;           // [2][7][T]
     // The hard decisions need no array of their own: the second decoder leaves 2 e + (LLR > 0) in EXT (the extrinsic
     // values are clamped to +-2047, so the doubled value fits an int16); the CRC and output stages read bit 0 of each
     // half, the next iteration's staging halves the words back (ext_strip).  K = 5952: 59.5 -> 56.6 KB per block, i.e.
     // four instead of three resident blocks per SM.
+    // checkpoint c of the running decoder dec: c = 0 in its rows of AE, c = 1 in its rows of BS, the others in CK
+    auto ck_rows = [&](uint32_t dec, uint32_t c) -> uint32_t* {
+        if (!CKALIAS) return CK + c * 7 * T;
+        return c == 0 ? AE + dec * 7 * T : (c == 1 ? BS + dec * 7 * T : CK + (c - 2) * 7 * T);
+    };
     auto ext_strip = [](uint32_t w) { return ((w >> 1) & 0x7fff7fffu) | (w & 0x80008000u); };   // per half: >> 1, signed
     auto strip4 = [&](uint4 v) { return make_uint4(ext_strip(v.x), ext_strip(v.y), ext_strip(v.z), ext_strip(v.w)); };
 
@@ -359,10 +369,10 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
             __syncthreads();
 
             uint32_t ae_new[8], bs_new[8];
+            uint32_t b[8], a[8];
+            int tail[8];
             if (active) {
-                // ---- termination metrics of this decoder (three tail steps back from state 0)
-                // termination metrics of this decoder, computed once per code block (s_tail)
-                int tail[8];
+                // ---- termination metrics of this decoder, computed once per code block (s_tail)
 #pragma unroll
                 for (int s = 0; s < 8; ++s) tail[s] = s_tail[dec * 8 + s];
                 const uint32_t* BSd = BS + dec * 7 * T;
@@ -379,7 +389,6 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
                 // ---- training passes: beta over window w+1 and alpha over window w-1 are independent
                 // recursions, run in one loop (two dependency chains in flight) with the next step's
                 // shared-memory words prefetched one iteration ahead
-                uint32_t b[8], a[8];
                 b[0] = pack(b_lo_end ? tail[0] : 0, b_hi_end ? tail[0] : 0);
                 a[0] = 0;
 #pragma unroll
@@ -392,6 +401,11 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
                     const int ahi = a_hi_beg ? -8192 : (int)pa_hi[row];
                     a[s] = pack(alo, ahi);
                 }
+            }
+            // CKALIAS: every boundary metric of this decoder is in registers now; until the new ones are stored at the end
+            // of the half iteration its rows of AE and BS hold the first two checkpoints of the backward pass (ck_rows)
+            if (CKALIAS) __syncthreads();
+            if (active) {
                 {
                     const bool wrapn = (t + 1 == T), wrapp = (t == 0);
                     const uint32_t* Xn = XIN + (wrapn ? 0 : t + 1);
@@ -443,9 +457,9 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
                         X -= T; Y -= T;  // last prefetch: one row below, inside EXT / XIN, unused
                         const uint32_t x_n = *X, y_n = *Y;
                         if (((k + 1) % S_CK) == 0 || k + 1 == (int)L) {
-                            const int c = k / S_CK;
+                            uint32_t* ckc = ck_rows(dec, k / S_CK);
 #pragma unroll
-                            for (int s = 1; s < 8; ++s) CK[(c * 7 + s - 1) * T + t] = b[s];
+                            for (int s = 1; s < 8; ++s) ckc[(s - 1) * T + t] = b[s];
                         }
                         beta_step<NORM>(b, x, y);
                         x = x_n; y = y_n;
@@ -471,6 +485,7 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
                     const int k0 = c * S_CK;
                     const int n = FULL ? (int)S_CK : min((int)S_CK, (int)L - k0);
                     uint32_t bb[S_CK][8], xs[S_CK], ys[S_CK];
+                    const uint32_t* ckc = ck_rows(dec, c);
 #pragma unroll
                     for (int i = 0; i < S_CK; ++i) {
                         bb[i][0] = 0;
@@ -483,7 +498,7 @@ __global__ void __launch_bounds__(GROUPED ? 128 : 96, GROUPED ? 1 : 4) k_turbo_d
                     for (int i = S_CK - 1; i >= 0; --i) {
                         if (i == n - 1) {
 #pragma unroll
-                            for (int s = 1; s < 8; ++s) bb[i][s] = CK[(c * 7 + s - 1) * T + t];
+                            for (int s = 1; s < 8; ++s) bb[i][s] = ckc[(s - 1) * T + t];
                         } else if (i < n - 1) {
 #pragma unroll
                             for (int s = 0; s < 8; ++s) bb[i][s] = bb[i + 1][s];
@@ -663,19 +678,25 @@ __global__ void __launch_bounds__(256) k_tb_finalize(const tbfin_params_t p) {
     if (tid == 0) p.tb_ok[pkt] = ok ? 1 : 0;
 }
 
-size_t tdec_smem_bytes(uint32_t K, uint32_t L) {
+size_t tdec_smem_bytes(uint32_t K, uint32_t L, bool ck_alias) {
     const uint32_t T = K / L / 2, nck = (L + tdec::S_CK - 1) / tdec::S_CK;
-    return (size_t)4 * (3 * (K / 2) + nck * 7 * T + 4 * 7 * T) + 16;
+    return (size_t)4 * (3 * (K / 2) + (ck_alias ? (nck > 2 ? nck - 2 : 0) : nck) * 7 * T + 4 * 7 * T) + 16;
 }
 
 tdec_geom_t tdec_geometry(const cb_desc_t* cbs, uint32_t n) {
-    tdec_geom_t g{32, 32, 0};
+    tdec_geom_t g{32, 32, 0, false};
     uint32_t Tmax = 1;
+    size_t aliased = 0;
     for (uint32_t i = 0; i < n; ++i) {
         Tmax = std::max(Tmax, cbs[i].P / 2);
-        g.smem_item = std::max(g.smem_item, tdec_smem_bytes(cbs[i].K, cbs[i].L));
+        g.smem_item = std::max(g.smem_item, tdec_smem_bytes(cbs[i].K, cbs[i].L, false));
+        aliased = std::max(aliased, tdec_smem_bytes(cbs[i].K, cbs[i].L, true));
     }
     g.smem_item = (g.smem_item + 15) & ~(size_t)15;
+    aliased = (aliased + 15) & ~(size_t)15;
+    // four blocks per SM: 228 KB of shared memory, 1 KB of it reserved per block, 80 B static per block
+    const size_t four = 233472 / 4 - 1024 - 128;
+    if (Tmax >= 32 && g.smem_item > four && aliased <= four) { g.smem_item = aliased; g.ck_alias = true; }
     if (Tmax >= 32) {  // one item per block
         g.threads = g.tg = ((Tmax + 31) / 32) * 32;
     } else {           // many small items per block: power-of-two groups inside 128 threads
@@ -700,6 +721,8 @@ cudaError_t launch_turbo_decode(const tdec_params_t& p, uint32_t n_packets, cons
         if (e == cudaSuccess)
             e = cudaFuncSetAttribute(k_turbo_decode<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
         if (e == cudaSuccess)
+            e = cudaFuncSetAttribute(k_turbo_decode<false, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
+        if (e == cudaSuccess)
             e = cudaFuncSetAttribute(k_turbo_decode<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)b);
         return e;
     });
@@ -707,7 +730,9 @@ cudaError_t launch_turbo_decode(const tdec_params_t& p, uint32_t n_packets, cons
     const dim3 grid((n_items + per_block - 1) / per_block);
     // DNRP_TDEC_BULK=0: the per-thread staging loop instead of the copy engine (for A/B measurements; same results)
     static const bool bulk = [] { const char* e = getenv("DNRP_TDEC_BULK"); return !(e && e[0] == '0'); }();
-    if (per_block == 1 && bulk)
+    if (per_block == 1 && g.ck_alias)
+        k_turbo_decode<false, true, true><<<grid, threads, smem, st>>>(p, g.tg, (uint32_t)(g.smem_item / 4), n_items);
+    else if (per_block == 1 && bulk)
         k_turbo_decode<false, true><<<grid, threads, smem, st>>>(p, g.tg, (uint32_t)(g.smem_item / 4), n_items);
     else if (per_block == 1)
         k_turbo_decode<false><<<grid, threads, smem, st>>>(p, g.tg, (uint32_t)(g.smem_item / 4), n_items);

@@ -44,7 +44,7 @@ struct tbfin_params_t {
     uint8_t* tb_ok;            // [packet]
 };
 
-size_t tdec_smem_bytes(uint32_t K, uint32_t L);
+size_t tdec_smem_bytes(uint32_t K, uint32_t L, bool ck_alias = false);
 // descramble + de-rate-match + HARQ combine into the soft buffers; must precede launch_turbo_decode.
 // max_n_e = largest LLR count of a code block in p.cbs (sizes the shared staging buffer)
 cudaError_t launch_derm(const tdec_params_t& p, uint32_t n_packets, uint32_t max_n_e, cudaStream_t st);
@@ -52,6 +52,7 @@ cudaError_t launch_derm(const tdec_params_t& p, uint32_t n_packets, uint32_t max
 struct tdec_geom_t {
     uint32_t threads, tg;  // block size, threads per (code block, packet) item
     size_t smem_item;      // dynamic shared bytes per item
+    bool ck_alias;         // k_turbo_decode<.., CKALIAS = true>: checkpoints 0 and 1 in the AE / BS rows (four blocks per SM)
 };
 tdec_geom_t tdec_geometry(const cb_desc_t* cbs, uint32_t n);
 cudaError_t launch_turbo_decode(const tdec_params_t& p, uint32_t n_packets, const tdec_geom_t& g, cudaStream_t st);

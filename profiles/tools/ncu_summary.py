@@ -11,6 +11,7 @@ cols = [("Kernel Name", "kernel"), ("launch__grid_size", "grid"), ("launch__bloc
         ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue%"),
         ("sm__warps_active.avg.pct_of_peak_sustained_active", "occ%"),
         ("l1tex__data_bank_conflicts_pipe_lsu_mem_shared.sum", "smem_conflicts"),
+        ("l1tex__data_pipe_lsu_wavefronts.sum.pct_of_peak_sustained_elapsed", "lsu_pipe%"),
         ("smsp__inst_executed.sum", "warp_inst")]
 idx = [(hdr.index(c) if c in hdr else None, n) for c, n in cols]
 print(" | ".join(n + ("[" + units[i] + "]" if i is not None and units[i] else "") for i, n in idx))
