@@ -535,6 +535,21 @@ float dnrp_large_scale_via_pathloss(float tx_power_ant_0dBFS, float rx_power_ant
     return powf(10.0f, (tx_power_ant_0dBFS - fading_dB - rx_power_ant_0dBFS) / 20.0f);   // adt::db2mag
 }
 
+// Knot distance of k_channel_tdl's interpolated tap coefficients.  A coefficient is a sum of 40 unit phasors whose phase
+// advances by at most w = 2 pi fD / fs per sample; linear interpolation between knots h samples apart is off by at most
+// (h w)^2 / 8 per phasor, i.e. relative to the coefficient's rms (sqrt(40)) by sqrt(40) (h w)^2 / 8.  h = the largest power
+// of two <= 256 that keeps this below 2e-6 (two orders of magnitude inside the 2e-4 the IQ is compared at); below 8 the
+// kernel evaluates every sample exactly.  DNRP_TDL_EXACT=1 forces that path (A/B runs, tests).
+static uint32_t tdl_interp_h(float fD_Hz, double samp_rate) {
+    static const bool exact = [] { const char* e = getenv("DNRP_TDL_EXACT"); return e && e[0] == '1'; }();
+    if (exact) return 0;
+    const double w = 2.0 * 3.14159265358979323846 * (double)fD_Hz / samp_rate;
+    const double hmax = w > 0.0 ? std::sqrt(8.0 * 2e-6 / std::sqrt(40.0)) / w : 256.0;
+    uint32_t h = 256;
+    while (h > 1 && (double)h > hmax) h >>= 1;
+    return h >= 8 ? h : 0;
+}
+
 int dnrp_channel_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_channel_desc_t* descs, dnrp_cf32_t* iq_rx_out) {
     DNRP_REQUIRE(c && descs, "null argument");
     DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
@@ -574,6 +589,7 @@ int dnrp_channel_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_channel_desc_t* des
                 m.tap_scale[k] = sc;
             }
             m.fD_Hz = descs[i].fD_Hz; m.time_64 = descs[i].time_64;
+            m.interp_h = tdl_interp_h(m.fD_Hz, samp_rate_hw);
             any_tdl = true;
         }
     }

@@ -244,6 +244,9 @@ struct chan_meta_dev_t {
     float fD_Hz;
     double samp_rate;
     long long time_64;
+    // knot distance (samples, a power of two >= 8) for the interpolated evaluation of the tap coefficients, 0 = every
+    // sample exactly (k_channel_tdl; chosen by the host from the largest Doppler increment per sample)
+    uint32_t interp_h;
 };
 // one sinusoid of one tap of one link (link.cpp:165-215): period in samples (sign = sense of rotation), start phase
 struct tdl_sin_t {

@@ -151,6 +151,51 @@ __global__ void __launch_bounds__(TDL_THREADS) k_channel_tdl(const channel_param
     float2 y[TDL_R];
 #pragma unroll
     for (uint32_t r = 0; r < TDL_R; ++r) y[r] = make_float2(0.f, 0.f);
+    const uint32_t h = m.interp_h;
+    if (h) {
+        // ---- slowly varying coefficients (chan_meta_dev_t::interp_h): every tap coefficient of the tile is evaluated
+        // exactly at knots h samples apart (one thread per knot, the 40 sinusoids in a fixed order) and interpolated
+        // linearly in between -- 40 / h sinusoid evaluations per sample and tap instead of 40
+        constexpr uint32_t TILE = TDL_THREADS * TDL_R;
+        const uint32_t nk = TILE / h + 1, lg = 31u - (uint32_t)__clz(h);
+        const float hinv = 1.0f / (float)h;
+        float2* knot = reinterpret_cast<float2*>(s_s2s + per_ant);   // [n_taps][nk], tap scale folded in
+        for (uint32_t t = 0; t < p.N_TX; ++t) {
+            const float2* x = p.tx + ((size_t)pkt * p.N_TX + t) * p.tx_stride;
+            __syncthreads();   // the previous antenna's knots are consumed
+            for (uint32_t e = tid; e < m.n_taps * nk; e += TDL_THREADS) {
+                const uint32_t i = e / nk, k = e - i * nk;
+                const uint32_t e0 = (t * TDL_TAPS + i) * TDL_SIN;
+                const float dn = (float)(k * h);
+                float2 c = make_float2(0.f, 0.f);
+                for (uint32_t j = 0; j < TDL_SIN; ++j) {
+                    const float4 rt = s_rot[e0 + j];
+                    float sn, cs;
+                    sincosf(s_s2s[e0 + j] * dn, &sn, &cs);
+                    c = cadd(c, cmul(make_float2(rt.x, rt.y), make_float2(cs, sn)));
+                }
+                const float sc = m.tap_scale[i];
+                knot[e] = make_float2(c.x * sc, c.y * sc);
+            }
+            __syncthreads();
+            for (uint32_t i = 0; i < m.n_taps; ++i) {
+                const long long off = (long long)m.t0 + m.tap_delay[i];
+                const float2* kn = knot + i * nk;
+#pragma unroll
+                for (uint32_t r = 0; r < TDL_R; ++r) {
+                    const uint32_t pos = tid + r * TDL_THREADS;
+                    const long long k = (long long)(base + pos) - off;
+                    if (k >= 0 && k < (long long)p.n_samples) {
+                        const uint32_t kk = pos >> lg;
+                        const float f = (float)(pos & (h - 1u)) * hinv;
+                        const float2 c0 = kn[kk], c1 = kn[kk + 1];
+                        const float2 c = make_float2(c0.x + f * (c1.x - c0.x), c0.y + f * (c1.y - c0.y));
+                        y[r] = cadd(y[r], cmul(c, hw_clip_quantize(x[k], m.clip, m.dac_lsb)));
+                    }
+                }
+            }
+        }
+    } else
     for (uint32_t t = 0; t < p.N_TX; ++t) {
         const float2* x = p.tx + ((size_t)pkt * p.N_TX + t) * p.tx_stride;
         for (uint32_t i = 0; i < m.n_taps; ++i) {
@@ -194,7 +239,9 @@ __global__ void __launch_bounds__(TDL_THREADS) k_channel_tdl(const channel_param
 
 cudaError_t launch_channel_tdl(const channel_params_t& p, uint32_t n_packets, cudaStream_t st) {
     k_channel_tdl_setup<<<n_packets, 256, 0, st>>>(p);
-    const size_t smem = (size_t)p.N_TX * TDL_TAPS * TDL_SIN * (sizeof(float4) + sizeof(float));
+    // phasors and increments per (tx, tap, sinusoid), then the knots of one TX antenna: [9 taps][2048 / 8 + 1]
+    const size_t smem = (size_t)p.N_TX * TDL_TAPS * TDL_SIN * (sizeof(float4) + sizeof(float)) +
+                        (size_t)TDL_TAPS * (TDL_THREADS * TDL_R / 8 + 1) * sizeof(float2);
     cudaError_t e = cudaFuncSetAttribute(k_channel_tdl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     const uint32_t per_block = TDL_THREADS * TDL_R;

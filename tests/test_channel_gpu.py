@@ -162,3 +162,51 @@ def test_large_scale_clip_and_quantise_match_oracle(product, mode):
     b = phy.channel(n, snr_dB=snr, t0=t0, mode=mode, seed=seed, fetch=True, large_scale=1.0, **kw)
     assert np.array_equal(a, b)
     phy.close()
+
+
+_TDL_SCRIPT = r"""
+import sys, numpy as np
+sys.path.insert(0, {root!r}); sys.path.insert(0, {root!r} + "/tests")
+from conftest import load_product, CONFIGS
+from oracle import spec
+product = load_product()
+cfg = CONFIGS["C3_b16_txdiv4_mcs7"]
+ps = spec.get_packet_sizes(*cfg)
+n = 2
+phy = product.Phy(cfg, max_batch=n, N_RX=4, network_id=123456789)
+rng = np.random.default_rng(21)
+tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
+plcf = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+phy.tx(plcf, tb, fetch=False)
+out = []
+for fD in (50.0, 400.0, 2000.0):
+    out.append(phy.channel(n, snr_dB=60.0, t0=np.array([5, 300]), mode=2, seed=77, fetch=True, pdp_idx=1, tau_rms_ns=100.0,
+                           fD_Hz=fD, time_64=987654321))
+np.save(sys.argv[1], np.stack(out))
+"""
+
+
+def test_tdl_interpolated_coefficients_equal_the_exact_evaluation(tmp_path):
+    """k_channel_tdl evaluates the tap coefficients at knots and interpolates where the Doppler is slow (knot distance
+    from dnrp_channel_batch: 128 samples at 50 Hz / 27.648 MS/s, 16 at 400 Hz, 0 = every sample at 2000 Hz); DNRP_TDL_EXACT=1
+    forces the exact path (read once per process: two subprocesses).  Bound of the design: 2e-6 of the coefficient's rms"""
+    import os
+    import subprocess
+    import sys
+    from conftest import ROOT
+    script = tmp_path / "tdl.py"
+    script.write_text(_TDL_SCRIPT.format(root=ROOT))
+    res = {}
+    for tag, env in (("interp", {}), ("exact", {"DNRP_TDL_EXACT": "1"})):
+        e = dict(os.environ)
+        e.pop("DNRP_TDL_EXACT", None)
+        e.update(env)
+        f = str(tmp_path / (tag + ".npy"))
+        subprocess.run([sys.executable, str(script), f], check=True, env=e, timeout=600)
+        res[tag] = np.load(f)
+    for i, fD in enumerate((50.0, 400.0, 2000.0)):
+        a, b = res["interp"][i], res["exact"][i]
+        err = np.abs(a - b).max() / np.abs(b).max()
+        assert err <= 2e-5, (fD, float(err))
+    assert np.array_equal(res["interp"][2], res["exact"][2])   # 2000 Hz: both runs take the exact path
+    assert not np.array_equal(res["interp"][0], res["exact"][0])   # 50 Hz: the interpolated path did run
