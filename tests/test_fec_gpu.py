@@ -165,3 +165,32 @@ def test_duplicate_or_out_of_range_harq_slots_are_refused(product):
     ok, tb, nit = phy.fec_decode_tb(llr, harq_slot=[2, 0, 1])   # still usable
     assert ok.shape == (3,) and not tb.any()
     phy.close()
+
+
+@pytest.mark.parametrize("cfg,snrs", [((1, 16, 1, 1, 1, 3, 6144), (0.5, 1.5, 3.0)), ((1, 12, 1, 1, 1, 5, 6144), (2.0, 3.0, 4.5))])
+def test_decode_tb_bit_exact_largest_code_blocks(product, cfg, snrs):
+    """K = 6144 (two code blocks) and K = 6144 / 6080 mixed (three): the sizes whose decoder keeps its first two backward
+    checkpoints in the boundary rows to stay at four blocks per SM (k_turbo_decode<.., CKALIAS>) --
+    outcomes, iteration counts and bytes equal the oracle's across the waterfall"""
+    ps = spec.get_packet_sizes(*cfg)
+    assert ps["seg"]["K1"] == 6144
+    gold = fec.pdc_gold(NET, 1, ps["G"])
+    rng = np.random.default_rng(12)
+    per = 4
+    n = per * len(snrs)
+    phy = product.Phy(cfg, max_batch=n, network_id=NET, plcf_type=1)
+    tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
+    llr = np.zeros((n, ps["G"]), dtype=np.int16)
+    for i in range(n):
+        bits = fec.unpack_bits(fec.pdc_encode(tb[i], ps, 0, gold), ps["G"]).astype(np.float64)
+        llr[i] = _noisy_llr(bits, snrs[i // per], rng)
+    ok, out, nit = phy.fec_decode_tb(llr)
+    n_ok = 0
+    for i in range(n):
+        rok, rout, rnit = fec.pdc_decode(llr[i], ps, 0, gold)
+        assert bool(ok[i]) == rok, (cfg, i)
+        assert (nit[i] == rnit).all(), (cfg, i, nit[i], rnit)
+        assert (out[i] == rout).all(), (cfg, i)
+        n_ok += rok
+    assert 0 < n_ok < n, n_ok   # the SNR grid straddles the waterfall
+    phy.close()
