@@ -85,6 +85,7 @@ int run_channel(dnrp_ctx* c, uint32_t n) {
     p.n_samples = c->n_packet_rs;
     p.meta = c->d_chan_meta.p;
     p.sin_tab = c->d_chan_sin.p;
+    p.tdl_min_h = c->chan_min_h;
     DNRP_LAUNCH(c, -1, launch_channel(p, n, c->stream));
     if (c->chan_any_tdl) {
         ++c->launches;  // setup + main kernel
@@ -557,6 +558,7 @@ int dnrp_channel_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_channel_desc_t* des
     const phy_dims_t& d = c->dims;
     std::vector<chan_meta_dev_t> meta(n);
     bool any_tdl = false;
+    uint32_t min_h = 0;
     const double samp_rate_hw = (double)d.u * d.b * c->cfg.oversampling * 1.728e6 * c->cfg.resample_L / c->cfg.resample_M;
     for (uint32_t i = 0; i < n; ++i) {
         DNRP_REQUIRE(descs[i].t0 + c->n_packet_rs <= c->rx_stride, "offset exceeds the IQ window");
@@ -590,10 +592,14 @@ int dnrp_channel_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_channel_desc_t* des
             }
             m.fD_Hz = descs[i].fD_Hz; m.time_64 = descs[i].time_64;
             m.interp_h = tdl_interp_h(m.fD_Hz, samp_rate_hw);
+            for (uint32_t k = 0; k < m.n_taps; ++k)
+                if (m.tap_delay[k] > TDL_HALO) m.interp_h = 0;   // the staged tile has room for delays up to TDL_HALO samples
+            if (m.interp_h && (min_h == 0 || m.interp_h < min_h)) min_h = m.interp_h;
             any_tdl = true;
         }
     }
     c->chan_any_tdl = any_tdl;
+    c->chan_min_h = min_h;
     if (any_tdl && c->d_chan_sin.n == 0)
         DNRP_CUDA(c->d_chan_sin.alloc((size_t)c->B * d.N_RX * d.N_TX * 9 * 40));
     DNRP_CUDA(cudaMemcpyAsync(c->d_chan_meta.p, meta.data(), n * sizeof(chan_meta_dev_t), cudaMemcpyHostToDevice,

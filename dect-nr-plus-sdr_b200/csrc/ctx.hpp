@@ -155,6 +155,7 @@ struct dnrp_ctx {
     dnrp::dbuf<dnrp::mimo_report_dev_t> d_mimo;
     dnrp::dbuf<dnrp::tdl_sin_t> d_chan_sin;   // allocated by the first doubly selective channel call
     bool chan_any_tdl = false;
+    uint32_t chan_min_h = 0;                  // smallest non-zero interp_h of the resident channel descriptors
 
     // resampling between the DECT rate (x oversampling) and the hardware rate: hw = dect * L / M (TX direction);
     // the receive direction uses M / L.  All IQ crossing the C ABI is at the hardware rate.

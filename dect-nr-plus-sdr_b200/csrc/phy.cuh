@@ -261,7 +261,9 @@ struct channel_params_t {
     uint32_t n_samples;                    // TX samples superimposed (rest of the window is noise only)
     const chan_meta_dev_t* meta;           // [packet]
     tdl_sin_t* sin_tab;                    // [packet][N_RX][N_TX][9][40], mode 2 only
+    uint32_t tdl_min_h;                    // smallest non-zero chan_meta_dev_t::interp_h of the batch (sizes the knot buffer), 0 = none
 };
+constexpr uint32_t TDL_HALO = 512;         // largest tap delay (+ nothing else) the interpolated path stages in front of a tile
 cudaError_t launch_channel(const channel_params_t& p, uint32_t n_packets, cudaStream_t st);
 cudaError_t launch_channel_tdl(const channel_params_t& p, uint32_t n_packets, cudaStream_t st);
 

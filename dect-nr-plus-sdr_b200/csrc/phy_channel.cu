@@ -159,39 +159,58 @@ __global__ void __launch_bounds__(TDL_THREADS) k_channel_tdl(const channel_param
         constexpr uint32_t TILE = TDL_THREADS * TDL_R;
         const uint32_t nk = TILE / h + 1, lg = 31u - (uint32_t)__clz(h);
         const float hinv = 1.0f / (float)h;
-        float2* knot = reinterpret_cast<float2*>(s_s2s + per_ant);   // [n_taps][nk], tap scale folded in
+        // knots of one TX antenna: two partial sums (sinusoids 0..19 / 20..39, one thread each) [2][n_taps][nk_max], added
+        // into the first half afterwards -- twice the threads busy, half the serial chain, fixed order of additions.
+        // Behind them the antenna's samples of the tile, clipped / quantised once, zero outside the packet, with
+        // TDL_HALO samples in front for the tap delays: the taps then read shared memory without range tests.
+        const uint32_t nk_max = TILE / p.tdl_min_h + 1;
+        float2* knot = reinterpret_cast<float2*>(s_s2s + per_ant);
+        float2* xs = knot + 2 * TDL_TAPS * nk_max;          // [TDL_HALO + TILE]
+        const uint32_t nkt = m.n_taps * nk;
+        uint32_t kk[TDL_R];
+        float fr[TDL_R];
+#pragma unroll
+        for (uint32_t r = 0; r < TDL_R; ++r) {
+            const uint32_t pos = tid + r * TDL_THREADS;
+            kk[r] = pos >> lg;
+            fr[r] = (float)(pos & (h - 1u)) * hinv;
+        }
+        const int k_first = (int)base - (int)m.t0 - (int)TDL_HALO;   // TX sample behind xs[0]
         for (uint32_t t = 0; t < p.N_TX; ++t) {
             const float2* x = p.tx + ((size_t)pkt * p.N_TX + t) * p.tx_stride;
-            __syncthreads();   // the previous antenna's knots are consumed
-            for (uint32_t e = tid; e < m.n_taps * nk; e += TDL_THREADS) {
+            __syncthreads();   // the previous antenna's knots and samples are consumed
+            for (uint32_t j = tid; j < TDL_HALO + TILE; j += TDL_THREADS) {
+                const int k = k_first + (int)j;
+                xs[j] = (k >= 0 && k < (int)p.n_samples) ? hw_clip_quantize(x[k], m.clip, m.dac_lsb) : make_float2(0.f, 0.f);
+            }
+            for (uint32_t e2 = tid; e2 < 2 * nkt; e2 += TDL_THREADS) {
+                const uint32_t hf = e2 >= nkt ? 1u : 0u, e = e2 - hf * nkt;
                 const uint32_t i = e / nk, k = e - i * nk;
-                const uint32_t e0 = (t * TDL_TAPS + i) * TDL_SIN;
+                const uint32_t e0 = (t * TDL_TAPS + i) * TDL_SIN + hf * (TDL_SIN / 2);
                 const float dn = (float)(k * h);
                 float2 c = make_float2(0.f, 0.f);
-                for (uint32_t j = 0; j < TDL_SIN; ++j) {
+                for (uint32_t j = 0; j < TDL_SIN / 2; ++j) {
                     const float4 rt = s_rot[e0 + j];
                     float sn, cs;
-                    sincosf(s_s2s[e0 + j] * dn, &sn, &cs);
+                    // the knot path is only taken for w h <= 1.6e-3 rad, i.e. arguments below 0.4 rad over the tile:
+                    // the fast intrinsic is exact to 1e-7 there
+                    __sincosf(s_s2s[e0 + j] * dn, &sn, &cs);
                     c = cadd(c, cmul(make_float2(rt.x, rt.y), make_float2(cs, sn)));
                 }
                 const float sc = m.tap_scale[i];
-                knot[e] = make_float2(c.x * sc, c.y * sc);
+                knot[e2] = make_float2(c.x * sc, c.y * sc);
             }
             __syncthreads();
+            for (uint32_t e = tid; e < nkt; e += TDL_THREADS) knot[e] = cadd(knot[e], knot[nkt + e]);
+            __syncthreads();
             for (uint32_t i = 0; i < m.n_taps; ++i) {
-                const long long off = (long long)m.t0 + m.tap_delay[i];
                 const float2* kn = knot + i * nk;
+                const float2* xi = xs + TDL_HALO - m.tap_delay[i] + tid;
 #pragma unroll
                 for (uint32_t r = 0; r < TDL_R; ++r) {
-                    const uint32_t pos = tid + r * TDL_THREADS;
-                    const long long k = (long long)(base + pos) - off;
-                    if (k >= 0 && k < (long long)p.n_samples) {
-                        const uint32_t kk = pos >> lg;
-                        const float f = (float)(pos & (h - 1u)) * hinv;
-                        const float2 c0 = kn[kk], c1 = kn[kk + 1];
-                        const float2 c = make_float2(c0.x + f * (c1.x - c0.x), c0.y + f * (c1.y - c0.y));
-                        y[r] = cadd(y[r], cmul(c, hw_clip_quantize(x[k], m.clip, m.dac_lsb)));
-                    }
+                    const float2 c0 = kn[kk[r]], c1 = kn[kk[r] + 1];
+                    const float2 c = make_float2(c0.x + fr[r] * (c1.x - c0.x), c0.y + fr[r] * (c1.y - c0.y));
+                    y[r] = cadd(y[r], cmul(c, xi[r * TDL_THREADS]));
                 }
             }
         }
@@ -239,9 +258,11 @@ __global__ void __launch_bounds__(TDL_THREADS) k_channel_tdl(const channel_param
 
 cudaError_t launch_channel_tdl(const channel_params_t& p, uint32_t n_packets, cudaStream_t st) {
     k_channel_tdl_setup<<<n_packets, 256, 0, st>>>(p);
-    // phasors and increments per (tx, tap, sinusoid), then the knots of one TX antenna: [9 taps][2048 / 8 + 1]
-    const size_t smem = (size_t)p.N_TX * TDL_TAPS * TDL_SIN * (sizeof(float4) + sizeof(float)) +
-                        (size_t)TDL_TAPS * (TDL_THREADS * TDL_R / 8 + 1) * sizeof(float2);
+    // phasors and increments per (tx, tap, sinusoid); interpolated path (some packet has a knot distance): the knots of
+    // one TX antenna [2 partial sums][9 taps][2048 / h_min + 1] and the staged samples of the tile [TDL_HALO + 2048]
+    size_t smem = (size_t)p.N_TX * TDL_TAPS * TDL_SIN * (sizeof(float4) + sizeof(float));
+    if (p.tdl_min_h)
+        smem += (2 * (size_t)TDL_TAPS * (TDL_THREADS * TDL_R / p.tdl_min_h + 1) + TDL_HALO + TDL_THREADS * TDL_R) * sizeof(float2);
     cudaError_t e = cudaFuncSetAttribute(k_channel_tdl, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     if (e != cudaSuccess) return e;
     const uint32_t per_block = TDL_THREADS * TDL_R;
