@@ -124,6 +124,8 @@ struct dnrp_ctx {
     dnrp::phy_dims_t dims;
     dnrp::spec::re_map_t re_map;
     dnrp::dbuf<uint32_t> d_cell, d_pcc_lk, d_pdc_lk, d_pcc_plan, d_pdc_plan;
+    dnrp::dbuf<uint8_t> d_cell_ab;
+    dnrp::dbuf<float2> d_qam_lut;
     dnrp::dbuf<int8_t> d_stf_sign, d_W;
     dnrp::dbuf<float> d_W_scale, d_W_scale_opt;
     dnrp::dbuf<float2> d_twiddle, d_twiddle_p4, d_twiddle_p16;

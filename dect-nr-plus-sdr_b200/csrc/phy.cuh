@@ -21,6 +21,8 @@ struct phy_dims_t {
     uint32_t txdiv_modulo;
     // device tables
     const uint32_t* cell;      // [(N_DF+1)][Nk] cell words (spec_re.hpp)
+    const uint8_t* cell_ab;    // [(N_DF+1)][Nk] transmit diversity: streams A | B << 4 of the cell's pair (Table 6.3.3.2), else 0
+    const float2* qam_lut;     // constellation points, LTE Gray mapping: entry qam_lut_base(N_bps) + v (v = the N_bps bits, MSB first)
     const uint32_t* pcc_lk;    // [98]
     const uint32_t* pdc_lk;    // [N_PDC_subc]
     // channel-estimation plan per demapper unit (cell, or cell pair with transmit diversity) and stream slot (A, B):
@@ -58,6 +60,10 @@ struct phy_dims_t {
     } pcc_pair[3], pdc_pair[3];             // per SNR class; info == nullptr: not built (single stream / spatial multiplexing PDC)
 };
 
+// first entry of the N_bps-bit constellation in phy_dims_t::qam_lut (1, 2, 4, 6, 8, 10 bits: 2 + 4 + 16 + 64 + 256 + 1024 entries)
+__host__ __device__ __forceinline__ uint32_t qam_lut_base(uint32_t N_bps) {
+    return N_bps == 1 ? 0u : (N_bps == 2 ? 2u : (N_bps == 4 ? 6u : (N_bps == 6 ? 22u : (N_bps == 8 ? 86u : 342u))));
+}
 // plan word: LUT slice base (o = base * Nk + k) | class slot j | pilot row | interlace flip | stream | mode lr
 __host__ __device__ __forceinline__ uint32_t ce_plan_word(uint32_t base, uint32_t j, uint32_t row, uint32_t flip, uint32_t ts,
                                                           uint32_t lr) {

@@ -12,46 +12,16 @@
 namespace dnrp {
 
 // LTE Gray mapping, TS 36.211 7.1 (srsRAN lte_tables.c; reference fix/mod.cpp:137-174), bits MSB first
-__device__ __forceinline__ float2 qam_symbol(const uint8_t* __restrict__ bits, uint32_t off, uint32_t N_bps) {
+__device__ __forceinline__ float2 qam_symbol(const uint8_t* __restrict__ bits, uint32_t off, uint32_t N_bps,
+                                             const float2* __restrict__ lut) {
     // N_bps <= 10 bits span at most three bytes: one 24-bit window instead of a byte load per bit (a later byte is
-    // only touched when the symbol reaches into it)
+    // only touched when the symbol reaches into it); the constellation point comes from the host-built table
+    // (plan_phy.cu: the recursion (1-2b0)(2^(h-1) - (1-2b2)(2^(h-2) - ...)) / sqrt(2 / 10 / 42 / 170 / 682); 1024-QAM, MCS
+    // 10 and 11, is outside the reference, tx.cpp:53-60 -- own extension)
     const uint32_t b = off >> 3, end = (off & 7) + N_bps;
     const uint32_t win = ((uint32_t)bits[b] << 16) | (end > 8 ? (uint32_t)bits[b + 1] << 8 : 0u) | (end > 16 ? (uint32_t)bits[b + 2] : 0u);
     const uint32_t v = (win >> (24 - end)) & ((1u << N_bps) - 1u);
-    if (N_bps == 1) {
-        const float a = v ? -0.70710678118654752f : 0.70710678118654752f;
-        return make_float2(a, a);
-    }
-    const uint32_t half = N_bps >> 1;
-    float re = 0.f, im = 0.f;
-    // axis amplitude (1-2b0)(2^(h-1) - (1-2b2)(2^(h-2) - ...)), I from even bit positions, Q from odd
-    for (int i = (int)half - 1; i >= 1; --i) {
-        const float bi = ((v >> (N_bps - 1 - 2 * i)) & 1u) ? -1.f : 1.f;
-        const float bq = ((v >> (N_bps - 2 - 2 * i)) & 1u) ? -1.f : 1.f;
-        const float c = (float)(1u << (half - 1 - i));
-        re = bi * (c - re);
-        im = bq * (c - im);
-    }
-    const float c0 = (float)(1u << (half - 1));
-    re = (((v >> (N_bps - 1)) & 1u) ? -1.f : 1.f) * (c0 - re);
-    im = (((v >> (N_bps - 2)) & 1u) ? -1.f : 1.f) * (c0 - im);
-    // half == 5: 1024-QAM (MCS 10, 11), outside the reference (tx.cpp:53-60) -- own extension, 1 / sqrt(682)
-    const float norm = half == 1 ? 0.70710678118654752f
-                     : (half == 2 ? 0.31622776601683794f
-                     : (half == 3 ? 0.15430334996209191f : (half == 4 ? 0.07669649888473704f : 0.03829197905337418f)));
-    return make_float2(re * norm, im * norm);
-}
-
-__device__ __forceinline__ void txdiv_pair_dev(uint32_t N_TS, uint32_t i_mod, uint32_t& A, uint32_t& B) {
-    // Y_i index table, reference transmit_diversity_precoding.cpp:45-72
-    if (N_TS == 2) { A = 0; B = 1; return; }
-    if (N_TS == 4) {
-        const uint8_t a4[6] = {0, 2, 0, 1, 0, 1}, b4[6] = {1, 3, 2, 3, 3, 2};
-        A = a4[i_mod]; B = b4[i_mod];
-        return;
-    }
-    const uint8_t a8[12] = {0, 2, 4, 6, 0, 1, 2, 3, 0, 1, 4, 5}, b8[12] = {1, 3, 5, 7, 4, 5, 6, 7, 2, 3, 6, 7};
-    A = a8[i_mod]; B = b8[i_mod];
+    return __ldg(lut + v);
 }
 
 __device__ __forceinline__ float2 apply_w(int8_t w, float2 v) {
@@ -85,22 +55,23 @@ __device__ __forceinline__ float2 tx_cell(const phy_dims_t& d, uint32_t l, uint3
     } else if (type == 2 || type == 3) {
         const uint8_t* bits = type == 2 ? pcc_bits : pdc_bits;
         const uint32_t nbps = type == 2 ? 2u : d.N_bps;
+        const float2* lut = d.qam_lut + qam_lut_base(nbps);
         if (d.N_TS == 1) {
-            acc = apply_w(W[0], qam_symbol(bits, idx * nbps, nbps));
+            acc = apply_w(W[0], qam_symbol(bits, idx * nbps, nbps, lut));
         } else if (type == 2 || d.txdiv) {
-            // Alamouti pair (q even, q odd): stream A carries s[q], stream B the flipped partner
-            uint32_t A, B;
-            txdiv_pair_dev(d.N_TS, (idx >> 1) % d.txdiv_modulo, A, B);
-            if (W[A] != 0) acc = apply_w(W[A], qam_symbol(bits, idx * nbps, nbps));
+            // Alamouti pair (q even, q odd): stream A carries s[q], stream B the flipped partner; the pair's streams
+            // (Table 6.3.3.2) come from the per-cell table
+            const uint32_t ab = d.cell_ab[l * d.Nk + k], A = ab & 15u, B = ab >> 4;
+            if (W[A] != 0) acc = apply_w(W[A], qam_symbol(bits, idx * nbps, nbps, lut));
             if (W[B] != 0) {
-                const float2 o = qam_symbol(bits, (idx ^ 1u) * nbps, nbps);
+                const float2 o = qam_symbol(bits, (idx ^ 1u) * nbps, nbps, lut);
                 const float2 f = (idx & 1u) ? make_float2(o.x, -o.y) : make_float2(-o.x, o.y);
                 acc = cadd(acc, apply_w(W[B], f));
             }
         } else {
             // spatial multiplexing: symbol idx*N_SS + s on stream s (tx.cpp:1054-1060)
             for (uint32_t s = 0; s < d.N_SS; ++s)
-                if (W[s] != 0) acc = cadd(acc, apply_w(W[s], qam_symbol(bits, (idx * d.N_SS + s) * nbps, nbps)));
+                if (W[s] != 0) acc = cadd(acc, apply_w(W[s], qam_symbol(bits, (idx * d.N_SS + s) * nbps, nbps, lut)));
         }
     }
     return acc;

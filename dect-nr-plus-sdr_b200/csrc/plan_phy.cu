@@ -74,6 +74,50 @@ int build_phy_plan(dnrp_ctx* c) {
     bool ok = true;
 #define UP(x) ok = ok && ((x) == cudaSuccess)
     UP(c->d_cell.upload(m.cell));
+    {
+        // transmitter look-ups: stream pair of every PCC / PDC cell under transmit diversity (the pair index is
+        // (symbol index / 2) mod txdiv_modulo, transmit_diversity_precoding.cpp:45-72) and the constellations
+        static const uint8_t a4[6] = {0, 2, 0, 1, 0, 1}, b4[6] = {1, 3, 2, 3, 3, 2};
+        static const uint8_t a8[12] = {0, 2, 4, 6, 0, 1, 2, 3, 0, 1, 4, 5}, b8[12] = {1, 3, 5, 7, 4, 5, 6, 7, 2, 3, 6, 7};
+        std::vector<uint8_t> ab(m.cell.size(), 0);
+        for (size_t i = 0; i < m.cell.size(); ++i) {
+            const uint32_t cw = m.cell[i], type = cw >> 30, idx = cw & 0x03ffffffu;
+            if ((type != 2 && type != 3) || d.N_TS == 1) continue;
+            const uint32_t im = (idx >> 1) % d.txdiv_modulo;
+            const uint32_t A = d.N_TS == 2 ? 0u : (d.N_TS == 4 ? a4[im] : a8[im]);
+            const uint32_t Bv = d.N_TS == 2 ? 1u : (d.N_TS == 4 ? b4[im] : b8[im]);
+            ab[i] = (uint8_t)(A | Bv << 4);
+        }
+        UP(c->d_cell_ab.upload(ab));
+        // the arithmetic of the former device function, in float: (1-2b0)(2^(h-1) - (1-2b2)(2^(h-2) - ...)) * norm
+        std::vector<float2> lut(342 + 1024);
+        for (uint32_t nb : {1u, 2u, 4u, 6u, 8u, 10u}) {
+            const uint32_t base = qam_lut_base(nb), half = nb >> 1;
+            for (uint32_t v = 0; v < (1u << nb); ++v) {
+                if (nb == 1) {
+                    const float a = v ? -0.70710678118654752f : 0.70710678118654752f;
+                    lut[base + v] = make_float2(a, a);
+                    continue;
+                }
+                float re = 0.f, im = 0.f;
+                for (int i = (int)half - 1; i >= 1; --i) {
+                    const float bi = ((v >> (nb - 1 - 2 * i)) & 1u) ? -1.f : 1.f;
+                    const float bq = ((v >> (nb - 2 - 2 * i)) & 1u) ? -1.f : 1.f;
+                    const float cc = (float)(1u << (half - 1 - i));
+                    re = bi * (cc - re);
+                    im = bq * (cc - im);
+                }
+                const float c0 = (float)(1u << (half - 1));
+                re = (((v >> (nb - 1)) & 1u) ? -1.f : 1.f) * (c0 - re);
+                im = (((v >> (nb - 2)) & 1u) ? -1.f : 1.f) * (c0 - im);
+                const float norm = half == 1 ? 0.70710678118654752f
+                                 : (half == 2 ? 0.31622776601683794f
+                                 : (half == 3 ? 0.15430334996209191f : (half == 4 ? 0.07669649888473704f : 0.03829197905337418f)));
+                lut[base + v] = make_float2(re * norm, im * norm);
+            }
+        }
+        UP(c->d_qam_lut.upload(lut));
+    }
     UP(c->d_pcc_lk.upload(m.pcc_lk));
     UP(c->d_pdc_lk.upload(m.pdc_lk));
     UP(c->d_stf_sign.upload(spec::build_stf_sign(d.b, d.N_eff_TX)));
@@ -403,6 +447,7 @@ int build_phy_plan(dnrp_ctx* c) {
         set_last_error("device allocation failed (phy plan)");
         return DNRP_ERR_CUDA;
     }
+    d.cell_ab = c->d_cell_ab.p; d.qam_lut = c->d_qam_lut.p;
     d.cell = c->d_cell.p; d.pcc_lk = c->d_pcc_lk.p; d.pdc_lk = c->d_pdc_lk.p;
     d.pcc_plan = c->d_pcc_plan.p; d.pdc_plan = c->d_pdc_plan.p;
     d.stf_sign = c->d_stf_sign.p; d.W = c->d_W.p; d.W_scale = c->d_W_scale.p; d.W_scale_opt = c->d_W_scale_opt.p;
