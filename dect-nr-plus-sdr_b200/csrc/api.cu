@@ -408,9 +408,9 @@ extern "C" int dnrp_time_stage(dnrp_ctx_t* c, int stage, uint32_t n, uint32_t re
                 if (rc == DNRP_OK) rc = run_tx_ofdm(c, n);
                 break;
             case DNRP_STAGE_CHANNEL: rc = run_channel(c, n); break;
-            case DNRP_STAGE_SYNC: rc = run_sync(c, n, 0, true); break;
+            case DNRP_STAGE_SYNC: rc = run_sync(c, n, c->last_search_length, true); break;
             case DNRP_STAGE_SYNC_RX_CHAIN:
-                rc = run_sync(c, n, 0, true);
+                rc = run_sync(c, n, c->last_search_length, true);
                 if (rc == DNRP_OK) rc = run_rx_front(c, n);
                 if (rc == DNRP_OK) rc = run_rx_pcc(c, n);
                 if (rc == DNRP_OK) rc = run_rx_pdc(c, n, false, false, false);

@@ -133,6 +133,10 @@ int run_sync(dnrp_ctx* c, uint32_t n, uint32_t search_length, bool hand_over) {
     p.n_ant = d.N_RX;  // RX_SYNC_PARAM_AUTOCORRELATOR_ANTENNA_LIMIT = 8 >= N_RX
     p.step = c->sync_step; p.n_steps = c->sync_n_steps;
     p.search_length = search_length ? search_length : p.len - d.stf_len_os - d.pat_len_os;
+    // the detection accepts step j only if it starts inside search_length (j step < search_length, k_sync_peak): the steps
+    // behind are neither summed nor scanned -- a caller who knows where a packet can still fit into the window
+    // (search_length) does not pay for reading the rest of it
+    p.n_steps_use = std::min(p.n_steps, (p.search_length + p.step - 1) / p.step + 1);
     // autocorrelator_detection.cpp:60-62: minimum rms scaled with the sample rate relative to 30.72 MS/s
     p.rms_min = 0.005f * (float)std::sqrt((double)d.u * d.b * c->cfg.oversampling * 1.728e6 / 30.72e6);
     p.c_steps = c->d_sync_c.p + off * d.N_RX * c->sync_n_steps; p.p_steps = c->d_sync_p.p + off * d.N_RX * c->sync_n_steps;
@@ -228,6 +232,7 @@ int dnrp_sync_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, uint32_
     if (iq_in)
         DNRP_CUDA(cudaMemcpyAsync(c->d_iq_rx.p, iq_in, (size_t)n * c->dims.N_RX * c->rx_stride * sizeof(float2),
                                   cudaMemcpyHostToDevice, c->stream));
+    c->last_search_length = search_length;
     const int rc = run_sync(c, n, search_length, true);
     if (rc) return rc;
     if (out)
@@ -290,6 +295,7 @@ static int rx_batch_impl(dnrp_ctx_t* c, uint32_t n, const void* iq_in, float sc1
     DNRP_REQUIRE(c && iq_in && tb_out && pdc_out, "null argument");
     DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
     DNRP_REQUIRE(search_length <= c->sync_len, "search_length exceeds the (resampled) IQ window");
+    c->last_search_length = search_length;
     DNRP_CUDA(cudaSetDevice(c->device));
     const phy_dims_t& d = c->dims;
     const bool sc16 = sc16_scale != 0.f;

@@ -174,6 +174,7 @@ struct dnrp_ctx {
 
     // packet synchronisation: STF templates for N_eff_TX = 1, 2, 4, 8 (up to the context's), step sums, results
     uint32_t sync_n_tpl = 0, sync_step = 0, sync_n_steps = 0;
+    uint32_t last_search_length = 0;               // of the last dnrp_sync_batch / dnrp_rx_batch call (dnrp_time_stage re-runs with it)
     dnrp::dbuf<float2> d_sync_tpl, d_sync_c, d_sync_xc;
     uint32_t sync_fft_n = 0;                       // FFT size of the fast cross-correlation (0: direct)
     dnrp::dbuf<float2> d_sync_tw_p16;

@@ -192,6 +192,8 @@ struct sync_params_t {
     uint32_t n_no_gi_hw;                   // packet length the receiver needs behind the fine peak (hardware rate)
     uint32_t n_ant;                        // antennas used (RX_SYNC_PARAM_AUTOCORRELATOR_ANTENNA_LIMIT = 8)
     uint32_t step, n_steps;                // detection step (pattern / 4) and number of steps in the window
+    uint32_t n_steps_use;                  // steps the detection can reach (<= n_steps: those that start inside search_length);
+                                           // only these are summed and scanned, 0 = all
     uint32_t search_length;                // samples the detection may consume
     float rms_min;
     float2* c_steps;                       // [packet][n_ant][n_steps]

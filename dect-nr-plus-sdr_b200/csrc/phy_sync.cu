@@ -101,17 +101,18 @@ __global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32
             double* Pr = Pp + p.n_steps + 1;
             double* Pi = Pr + p.n_steps + 1;
             const size_t o = ((size_t)pkt * p.n_ant + a) * p.n_steps;
-            for (uint32_t j = tid; j < p.n_steps; j += nthr) {
+            const uint32_t n_use = p.n_steps_use ? p.n_steps_use : p.n_steps;   // steps that start inside search_length
+            for (uint32_t j = tid; j < n_use; j += nthr) {
                 Pp[j + 1] = p.p_steps[o + j];
                 Pr[j + 1] = p.c_steps[o + j].x;
                 Pi[j + 1] = p.c_steps[o + j].y;
             }
             if (tid == 0) { Pp[0] = Pr[0] = Pi[0] = 0.0; s_min = 0xffffffffu; }
             __syncthreads();
-            block_scan(Pp + 1, p.n_steps, s_part);
-            block_scan(Pr + 1, p.n_steps, s_part);
-            block_scan(Pi + 1, p.n_steps, s_part);
-            for (uint32_t j = j_from + tid; j < p.n_steps; j += nthr) {
+            block_scan(Pp + 1, n_use, s_part);
+            block_scan(Pr + 1, n_use, s_part);
+            block_scan(Pi + 1, n_use, s_part);
+            for (uint32_t j = j_from + tid; j < n_use; j += nthr) {
                 const uint32_t n = (j + 1) * step;
                 if (n - step >= search_length || n > len || j + 1 < W) continue;
                 const float power = (float)(Pp[j + 1] - Pp[j + 1 - W]);
@@ -325,7 +326,7 @@ __global__ void __launch_bounds__(256) k_sync_steps(const sync_params_t p) {
     const uint32_t lane = threadIdx.x & 31, sub = lane & 7;
     const uint32_t j = (blockIdx.x * 8 + (threadIdx.x >> 5)) * 4 + (lane >> 3);
     const uint32_t a = blockIdx.y, pkt = blockIdx.z;
-    const bool valid = j < p.n_steps;
+    const bool valid = j < (p.n_steps_use ? p.n_steps_use : p.n_steps);
     const float2* x = sync_iq(p, pkt, a);
     const uint32_t pat = p.d.pat_len_os, m0 = valid ? j * p.step : 0;
     float cr = 0.f, ci = 0.f, pw = 0.f;
@@ -561,7 +562,8 @@ size_t sync_peak_smem(const phy_dims_t& d, uint32_t n_steps) {
 
 cudaError_t launch_sync_steps(const sync_params_t& p, uint32_t n, cudaStream_t st) {
     if (n == 0) return cudaSuccess;
-    k_sync_steps<<<dim3((p.n_steps + 31) / 32, p.n_ant, n), 256, 0, st>>>(p);
+    const uint32_t n_use = p.n_steps_use ? p.n_steps_use : p.n_steps;
+    k_sync_steps<<<dim3((n_use + 31) / 32, p.n_ant, n), 256, 0, st>>>(p);
     return cudaGetLastError();
 }
 

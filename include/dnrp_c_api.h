@@ -407,6 +407,7 @@ typedef enum {
     DNRP_STAGE_SYNC = 7,       /* packet synchronisation on the resident IQ windows, hand-over to the receiver */
     DNRP_STAGE_SYNC_RX_CHAIN = 8 /* 7 followed by 4: raw IQ windows -> transport blocks */
 } dnrp_stage_t;
+/* the synchronisation stages run with the search_length of the last dnrp_sync_batch / dnrp_rx_batch call on this context */
 int dnrp_time_stage(dnrp_ctx_t* ctx, int stage, uint32_t n, uint32_t reps, float* ms_per_rep);
 
 /* Per-kernel device time inside the stages above: while enabled, every launch of the named kernel is
