@@ -394,6 +394,21 @@ class Phy:
                                      None if out is None else out.ctypes.data_as(C.c_void_p)))
         return out
 
+    # ---- coarse_peak_f_domain_t between coarse and fine peak: beta search and integer CFO (off by default)
+    def sync_set_fdomain(self, beta_threshold_dB=0.0, cfo_search_range_subc=0):
+        """dnrp_sync_set_fdomain: beta_threshold_dB < 0 switches the beta search on (reference: -10 dB),
+        cfo_search_range_subc >= 4 the integer CFO search (reference: 4)"""
+        f = lib().dnrp_sync_set_fdomain
+        f.argtypes = [C.c_void_p, C.c_float, C.c_uint32]
+        _check(f(self._ctx, float(beta_threshold_dB), int(cfo_search_range_subc)))
+
+    def sync_fdomain_read(self, n):
+        """dnrp_sync_fdomain_read: (estimated beta [n], integer CFO of the signal in subcarriers [n]) of the last search"""
+        b = np.zeros(n, dtype=np.uint32)
+        cfo = np.zeros(n, dtype=np.int32)
+        _check(lib().dnrp_sync_fdomain_read(self._ctx, n, _ptr(b, np.uint32), _ptr(cfo, np.int32)))
+        return b, cfo
+
     # ---- streaming front door (worker_sync_t / sync_chunk_t / baton_t): packet search over one continuous stream
     def stream_sync(self, iq, chunk_hop=0, max_out=None):
         """iq [N_RX][n_samples] complex64 host stream; returns the unique packets in time order (STREAM_PACKET_DTYPE)"""

@@ -137,6 +137,10 @@ int run_sync(dnrp_ctx* c, uint32_t n, uint32_t search_length, bool hand_over) {
     // behind are neither summed nor scanned -- a caller who knows where a packet can still fit into the window
     // (search_length) does not pay for reading the rest of it
     p.n_steps_use = std::min(p.n_steps, (p.search_length + p.step - 1) / p.step + 1);
+    if (c->fd_beta_thr > 0.f || c->fd_cfo_range >= 4) {
+        p.fd_beta_thr = c->fd_beta_thr; p.fd_cfo_range = c->fd_cfo_range;
+        p.fd_seq = c->d_fd_seq.p; p.fd_b = c->d_fd_b.p + off; p.fd_cfo = c->d_fd_cfo.p + off;
+    }
     // autocorrelator_detection.cpp:60-62: minimum rms scaled with the sample rate relative to 30.72 MS/s
     p.rms_min = 0.005f * (float)std::sqrt((double)d.u * d.b * c->cfg.oversampling * 1.728e6 / 30.72e6);
     p.c_steps = c->d_sync_c.p + off * d.N_RX * c->sync_n_steps; p.p_steps = c->d_sync_p.p + off * d.N_RX * c->sync_n_steps;
@@ -221,6 +225,49 @@ int fetch_pdc_reports(dnrp_ctx* c, uint32_t n, uint8_t* tb_out, dnrp_pdc_report_
 }  // namespace dnrp
 
 extern "C" {
+
+// coarse_peak_f_domain_t between coarse and fine peak (k_sync_fdomain): the reference switches both parts at compile time
+// (sync_param.hpp:244, 252, both commented out); here per context at run time, off by default
+int dnrp_sync_set_fdomain(dnrp_ctx_t* c, float beta_threshold_dB, uint32_t cfo_search_range_subc) {
+    DNRP_REQUIRE(c, "null argument");
+    DNRP_REQUIRE(cfo_search_range_subc <= 32, "integer CFO search range: at most 32 subcarriers");
+    const bool on = beta_threshold_dB < 0.f || cfo_search_range_subc >= 4;
+    DNRP_REQUIRE(!on || (c->dims.N_os <= 4096 && !c->resampling),
+                 "the frequency-domain stage needs N_b_DFT_os <= 4096 and a context without resampling");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    if (on && c->d_fd_b.n == 0) {
+        std::vector<int8_t> seq(6 * 224, 0);
+        const uint32_t tab[6] = {1, 2, 4, 8, 12, 16};
+        for (uint32_t bi = 0; bi < 6; ++bi) {
+            const std::vector<int8_t> sg = spec::build_stf_sign(tab[bi], 1);   // by subcarrier; cell i of the comb:
+            const uint32_t NS = 14 * tab[bi], N_OCC = 56 * tab[bi];
+            for (uint32_t i = 0; i < NS; ++i) {
+                const uint32_t q = i < NS / 2 ? 4 * i : N_OCC / 2 + 3 + 4 * (i - NS / 2);
+                seq[bi * 224 + i] = sg[spec::occ2k(q, N_OCC)];
+            }
+        }
+        DNRP_CUDA(c->d_fd_seq.upload(seq));
+        DNRP_CUDA(c->d_fd_b.alloc(c->B));
+        DNRP_CUDA(c->d_fd_cfo.alloc(c->B));
+    }
+    // the reference converts its dB threshold with db2mag (coarse_peak_f_domain.cpp:140-141)
+    c->fd_beta_thr = beta_threshold_dB < 0.f ? powf(10.0f, beta_threshold_dB / 20.0f) : 0.f;
+    c->fd_cfo_range = cfo_search_range_subc >= 4 ? cfo_search_range_subc : 0;
+    return DNRP_OK;
+}
+
+int dnrp_sync_fdomain_read(dnrp_ctx_t* c, uint32_t n, uint32_t* beta_out, int32_t* cfo_subc_out) {
+    DNRP_REQUIRE(c && n > 0 && n <= c->B, "invalid argument");
+    if (c->d_fd_b.n == 0) {
+        set_last_error("the frequency-domain stage was never switched on (dnrp_sync_set_fdomain)");
+        return DNRP_ERR_STATE;
+    }
+    DNRP_CUDA(cudaSetDevice(c->device));
+    if (beta_out) DNRP_CUDA(cudaMemcpyAsync(beta_out, c->d_fd_b.p, n * sizeof(uint32_t), cudaMemcpyDeviceToHost, c->stream));
+    if (cfo_subc_out) DNRP_CUDA(cudaMemcpyAsync(cfo_subc_out, c->d_fd_cfo.p, n * sizeof(int32_t), cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    return DNRP_OK;
+}
 
 int dnrp_sync_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, uint32_t search_length,
                     dnrp_sync_result_t* out) {

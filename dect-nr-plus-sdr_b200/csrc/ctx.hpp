@@ -174,6 +174,11 @@ struct dnrp_ctx {
 
     // packet synchronisation: STF templates for N_eff_TX = 1, 2, 4, 8 (up to the context's), step sums, results
     uint32_t sync_n_tpl = 0, sync_step = 0, sync_n_steps = 0;
+    float fd_beta_thr = 0.f;                       // dnrp_sync_set_fdomain: linear threshold of the beta search, 0 = off
+    uint32_t fd_cfo_range = 0;                     // integer CFO search range in subcarriers, 0 = off
+    dnrp::dbuf<int8_t> d_fd_seq;                   // [6][224] STF base sequences
+    dnrp::dbuf<uint32_t> d_fd_b;                   // [B]
+    dnrp::dbuf<int32_t> d_fd_cfo;                  // [B]
     uint32_t last_search_length = 0;               // of the last dnrp_sync_batch / dnrp_rx_batch call (dnrp_time_stage re-runs with it)
     dnrp::dbuf<float2> d_sync_tpl, d_sync_c, d_sync_xc;
     uint32_t sync_fft_n = 0;                       // FFT size of the fast cross-correlation (0: direct)

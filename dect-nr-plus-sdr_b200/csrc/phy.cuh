@@ -216,6 +216,12 @@ struct sync_params_t {
     const uint32_t* limit;                 // [packet] optional: end of the chunk's detection range (else search_length)
     const uint32_t* chunk_map;             // optional: block i of the search kernels works on chunk chunk_map[i] (the
                                            // chunks still active in a continuation round)
+    // frequency-domain stage between coarse and fine peak (coarse_peak_f_domain_t, k_sync_fdomain), optional:
+    float fd_beta_thr;                     // linear threshold of the beta search (db2mag of the dB value), 0 = off: b = context beta
+    uint32_t fd_cfo_range;                 // integer CFO search range in subcarriers (multiples of 4 are tested), 0 = off
+    const int8_t* fd_seq;                  // [6][224] STF base sequences y_b for b = 1, 2, 4, 8, 12, 16 (no cyclic shift)
+    uint32_t* fd_b;                        // [packet] estimated beta
+    int32_t* fd_cfo;                       // [packet] integer CFO in subcarriers
 };
 __device__ __forceinline__ uint32_t sync_chunk(const sync_params_t& p, uint32_t i) { return p.chunk_map ? p.chunk_map[i] : i; }
 // first sample of antenna a of window / chunk pkt

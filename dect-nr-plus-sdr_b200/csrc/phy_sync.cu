@@ -50,6 +50,18 @@ __device__ void block_scan(double* a, uint32_t n, double* s_part) {
 }
 }  // namespace
 
+// block-wide sum of a float2 (result in every thread); s_red: 8 entries
+__device__ float2 block_sum2f(float2 v, float2* s_red) {
+    v.x = warp_sum(v.x); v.y = warp_sum(v.y);
+    const uint32_t w = threadIdx.x >> 5, nw = (blockDim.x + 31) >> 5;
+    __syncthreads();
+    if ((threadIdx.x & 31) == 0) s_red[w] = v;
+    __syncthreads();
+    float2 t = make_float2(0.f, 0.f);
+    for (uint32_t i = 0; i < nw; ++i) { t.x += s_red[i].x; t.y += s_red[i].y; }
+    return t;
+}
+
 // block-wide sum of three floats (result in every thread)
 __device__ float3 block_sum3(float3 v, float3* s_red) {
     v.x = warp_sum(v.x); v.y = warp_sum(v.y); v.z = warp_sum(v.z);
@@ -320,6 +332,155 @@ __global__ void __launch_bounds__(256) k_sync_peak(const sync_params_t p, uint32
     }
 }
 
+// ---- frequency-domain stage between coarse and fine peak (reference coarse_peak_f_domain_t::process,
+// coarse_peak_f_domain.cpp:70-201; both parts are compiled out there, sync_param.hpp:238-252).  One block per window: the
+// N_os samples behind the STF's cyclic prefix at the coarse peak, fractional CFO removed, cover sequence undone, are
+// transformed per antenna (the reference leaves the CFO correction as a to-do and does not undo the cover sequence; the
+// power comparison below does not depend on either).
+//  * beta search (estimate_beta, :94-190): power per subcarrier summed over the antennas; starting from b = 1 the next
+//    larger b of {1, 2, 4, 8, 12, 16} is accepted while the mean power of the two side bands it adds exceeds
+//    threshold x the mean power of the band found so far.  The side bands are taken symmetrically (the reference
+//    advances its right-hand index by the NEW band width instead of the old one, :150-151: a slip in disabled code).
+//  * integer CFO (estimate_integer_cfo is "#error not implemented", :193-200; own specification): the
+//    fractional estimate of the pattern autocorrelation is unambiguous within +-2 subcarriers, what is left is a multiple
+//    of 4.  For every shift 4 s inside the search range and every cyclic shift of the STF sequence (N_eff_TX = 1, 2, 4,
+//    8 <= the context's) the differential correlation D = sum_a sum_i X_a[c_i + 4 s] conj(X_a[c_(i+1) + 4 s]) y_i y_(i+1)
+//    over neighbouring STF cells (c_i = multiples of 4 without 0) is formed; timing offset and a smooth channel turn all
+//    products alike, so |D| peaks at the true shift.  fd_cfo = 4 s (where the signal sits, in subcarriers),
+//    cfo_integer_rad = -2 pi 4 s / N_os per sample (a correction increment like cfo_fractional_rad).
+constexpr uint32_t FD_THREADS = 256;
+
+__device__ __forceinline__ uint32_t fd_b_idx(uint32_t b) { return b == 1 ? 0u : (b == 2 ? 1u : (b == 4 ? 2u : (b == 8 ? 3u : (b == 12 ? 4u : 5u)))); }
+
+__global__ void __launch_bounds__(FD_THREADS) k_sync_fdomain(const sync_params_t p, uint32_t len) {
+    extern __shared__ __align__(16) float2 smem_fd[];
+    __shared__ float2 s_red2[8];
+    __shared__ float2 s_hyp[4 * 17];     // [cyclic shift][s + S], S <= 8
+    __shared__ uint32_t s_b;
+    const phy_dims_t& d = p.d;
+    const uint32_t pkt = sync_chunk(p, blockIdx.x), tid = threadIdx.x, N = d.N_os;
+    sync_result_dev_t& res = p.result[pkt];
+    const uint32_t start = res.coarse_peak_time_local + d.stf_cp_os;
+    if (!res.detected || start + N > len) {
+        if (tid == 0) { p.fd_b[pkt] = d.b; p.fd_cfo[pkt] = 0; }
+        return;
+    }
+    float2* A = smem_fd;
+    float2* Bf = smem_fd + fft_buf_len(N);
+    float* P = reinterpret_cast<float*>(smem_fd + 2 * fft_buf_len(N));   // [N] power per bin over the antennas
+    const uint32_t os = N / (64u * d.b);       // oversampling of the context
+    const uint32_t S = p.fd_cfo_range / 4 > 8 ? 8u : p.fd_cfo_range / 4;
+    uint32_t n_lg = 0;
+    for (uint32_t n = d.N_eff_TX; n >= 1; n >>= 1) ++n_lg;     // cyclic shifts 0, 2, 4, 6 for N_eff_TX = 1, 2, 4, 8
+    for (uint32_t i = tid; i < N; i += FD_THREADS) P[i] = 0.f;
+    for (uint32_t i = tid; i < 4 * 17; i += FD_THREADS) s_hyp[i] = make_float2(0.f, 0.f);
+    uint32_t b_est = d.b;
+    for (uint32_t a = 0; a < p.n_ant; ++a) {
+        const float2* x = sync_iq(p, pkt, a) + start;
+        __syncthreads();
+        for (uint32_t n = tid; n < N; n += FD_THREADS) {
+            double sd, cd;
+            sincos((double)res.cfo_fractional_rad * (double)n, &sd, &cd);   // the correction increment, as in the receiver
+            // patterns 3 .. 6 of the STF (the cyclic prefix holds 0 .. 2): cover sequence 1 -1 -1 -1 undone
+            const float cv = n < N / 4 ? 1.f : -1.f;
+            A[n] = cmul(x[n], make_float2((float)cd * cv, (float)sd * cv));
+        }
+        const float2* X = block_fft<false, false>(A, Bf, N, d.twiddle, d.twiddle_p4);
+        for (uint32_t i = tid; i < N; i += FD_THREADS) P[i] += X[i].x * X[i].x + X[i].y * X[i].y;
+        __syncthreads();
+        if (a + 1 == p.n_ant && tid == 0) {
+            // ---- beta search on the summed power (bin of subcarrier c: (c + N) % N)
+            uint32_t be = d.b;
+            if (p.fd_beta_thr > 0.f && d.b > 1) {
+                auto band = [&](int lo, int hi) {   // power of the subcarriers lo .. hi - 1 and -hi .. -lo - 1 (the reference's two arrays)
+                    float s = 0.f;
+                    for (int c = lo; c < hi; ++c) s += P[(uint32_t)(c + (int)N) % N] + P[(uint32_t)(-c - 1 + (int)N) % N];
+                    return s;
+                };
+                const uint32_t tab[6] = {1, 2, 4, 8, 12, 16};
+                be = 1;
+                float central = band(0, 32);
+                for (uint32_t bi = 1; bi < 6 && tab[bi] <= d.b; ++bi) {
+                    const uint32_t bt = tab[bi];
+                    const float side = band(32 * (int)be, 32 * (int)bt);
+                    const float cn = central / (float)(be * 64u), sn = side / (float)((bt - be) * 64u);
+                    if (sn / cn > p.fd_beta_thr) { be = bt; central += side; }
+                    else break;
+                }
+            }
+            s_b = be;
+        }
+        if (a + 1 == p.n_ant) { __syncthreads(); b_est = s_b; }
+        if (S == 0) continue;
+        // ---- differential correlation of this antenna for every hypothesis; the sequence and the comb belong to beta:
+        // the context's unless the beta search is on (then the estimate is only known after the last antenna, and the
+        // antennas are revisited below)
+        if (p.fd_beta_thr > 0.f && d.b > 1) continue;
+        const uint32_t NS = 14 * b_est;
+        const int8_t* y = p.fd_seq + fd_b_idx(b_est) * 224;
+        for (uint32_t lg = 0; lg < n_lg; ++lg)
+            for (int s = -(int)S; s <= (int)S; ++s) {
+                float2 acc = make_float2(0.f, 0.f);
+                for (uint32_t i = tid; i + 1 < NS; i += FD_THREADS) {
+                    if (i + 1 == NS / 2) continue;   // the pair across DC is 8 subcarriers apart
+                    const int c0 = (i < NS / 2 ? -(int)(2 * NS) + 4 * (int)i : 4 * (int)(i - NS / 2) + 4) + 4 * s;
+                    const float sg = (float)(y[(i + 2 * lg) % NS] * y[(i + 1 + 2 * lg) % NS]);
+                    const float2 v = cmulc(X[(uint32_t)(c0 + (int)N) % N], X[(uint32_t)(c0 + 4 + (int)N) % N]);
+                    acc.x += sg * v.x; acc.y += sg * v.y;
+                }
+                acc = block_sum2f(acc, s_red2);
+                if (tid == 0) { float2& h = s_hyp[lg * 17 + (uint32_t)(s + (int)S)]; h.x += acc.x; h.y += acc.y; }
+            }
+    }
+    (void)os;
+    if (S != 0 && p.fd_beta_thr > 0.f && d.b > 1) {
+        // beta search on: second sweep over the antennas with the comb and sequence of the estimated beta
+        const uint32_t NS = 14 * b_est;
+        const int8_t* y = p.fd_seq + fd_b_idx(b_est) * 224;
+        for (uint32_t a = 0; a < p.n_ant; ++a) {
+            const float2* x = sync_iq(p, pkt, a) + start;
+            __syncthreads();
+            for (uint32_t n = tid; n < N; n += FD_THREADS) {
+                double sd, cd;
+                sincos((double)res.cfo_fractional_rad * (double)n, &sd, &cd);
+                const float cv = n < N / 4 ? 1.f : -1.f;
+                A[n] = cmul(x[n], make_float2((float)cd * cv, (float)sd * cv));
+            }
+            const float2* X = block_fft<false, false>(A, Bf, N, d.twiddle, d.twiddle_p4);
+            for (uint32_t lg = 0; lg < n_lg; ++lg)
+                for (int s = -(int)S; s <= (int)S; ++s) {
+                    float2 acc = make_float2(0.f, 0.f);
+                    for (uint32_t i = tid; i + 1 < NS; i += FD_THREADS) {
+                        if (i + 1 == NS / 2) continue;
+                        const int c0 = (i < NS / 2 ? -(int)(2 * NS) + 4 * (int)i : 4 * (int)(i - NS / 2) + 4) + 4 * s;
+                        const float sg = (float)(y[(i + 2 * lg) % NS] * y[(i + 1 + 2 * lg) % NS]);
+                        const float2 v = cmulc(X[(uint32_t)(c0 + (int)N) % N], X[(uint32_t)(c0 + 4 + (int)N) % N]);
+                        acc.x += sg * v.x; acc.y += sg * v.y;
+                    }
+                    acc = block_sum2f(acc, s_red2);
+                    if (tid == 0) { float2& h = s_hyp[lg * 17 + (uint32_t)(s + (int)S)]; h.x += acc.x; h.y += acc.y; }
+                }
+        }
+    }
+    __syncthreads();
+    if (tid == 0) {
+        int s_best = 0;
+        if (S != 0) {
+            float best = -1.f;
+            for (uint32_t lg = 0; lg < n_lg; ++lg)
+                for (int s = -(int)S; s <= (int)S; ++s) {
+                    const float2 h = s_hyp[lg * 17 + (uint32_t)(s + (int)S)];
+                    const float m = h.x * h.x + h.y * h.y;
+                    if (m > best) { best = m; s_best = s; }
+                }
+        }
+        p.fd_b[pkt] = b_est;
+        p.fd_cfo[pkt] = 4 * s_best;
+        // the signal sits 4 s subcarriers up: the correction increment (same sense as cfo_fractional_rad) is negative
+        res.cfo_integer_rad = -6.283185307179586f * (float)(4 * s_best) / (float)N;
+    }
+}
+
 // ---- eight lanes per detection step, four steps per warp: c_j = sum r[m - pat] conj(r[m]), p_j = sum abs(r[m])^2 over
 // the step.  All 16-byte loads of a lane are independent (issued back to back), the reduction runs over 8 lanes.
 __global__ void __launch_bounds__(256) k_sync_steps(const sync_params_t p) {
@@ -580,6 +741,12 @@ cudaError_t launch_sync_search(const sync_params_t& p, uint32_t n, cudaStream_t 
     cudaError_t e = cudaFuncSetAttribute(k_sync_peak, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)sm2);
     if (e != cudaSuccess) return e;
     k_sync_peak<<<n, 256, sm2, st>>>(p, len);
+    if ((p.fd_beta_thr > 0.f || p.fd_cfo_range >= 4) && p.fd_b && d.N_os <= 4096) {
+        const size_t smfd = 2 * (size_t)fft_buf_len(d.N_os) * sizeof(float2) + (size_t)d.N_os * sizeof(float);
+        e = cudaFuncSetAttribute(k_sync_fdomain, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smfd);
+        if (e != cudaSuccess) return e;
+        k_sync_fdomain<<<n, FD_THREADS, smfd, st>>>(p, len);
+    }
     if (p.xc_fft_n) {
         const size_t smf = 2 * (size_t)fft_buf_len(p.xc_fft_n) * sizeof(float2);
         e = cudaFuncSetAttribute(k_sync_xcorr_fft, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smf);

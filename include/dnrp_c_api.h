@@ -407,6 +407,21 @@ typedef enum {
     DNRP_STAGE_SYNC = 7,       /* packet synchronisation on the resident IQ windows, hand-over to the receiver */
     DNRP_STAGE_SYNC_RX_CHAIN = 8 /* 7 followed by 4: raw IQ windows -> transport blocks */
 } dnrp_stage_t;
+/* ---- frequency-domain stage of the packet search: beta estimate and integer CFO -------------------------------
+ * coarse_peak_f_domain_t::process (lib/src/phy/rx/sync/coarse_peak_f_domain.cpp:70-201), which the reference runs between
+ * coarse and fine peak and switches at compile time (sync_param.hpp:244 RX_SYNC_PARAM_AUTOCORRELATOR_PEAK_FIND_BETA_
+ * THRESHOLD_DB_OR_ASSUME_MAX_OF_RDC -10.0f, :252 ..._FIND_INTEGER_CFO_SEARCH_RANGE_OR_ASSUME_ZERO 4; both commented out,
+ * the integer CFO part "#error not implemented").  Here per context at run time, off by default:
+ *   beta_threshold_dB < 0: beta search on (the context's beta is the maximum, as the radio device class' in the
+ *       reference); >= 0: off, every packet is taken to have the context's beta;
+ *   cfo_search_range_subc >= 4: integer CFO search over the multiples of 4 subcarriers inside +- that range (the STF's
+ *       fractional estimate covers +-2); the result is added to the sync result's cfo_integer_rad, which the fine peak
+ *       search and the receiver already honour.  Own specification, DESIGN.md 5b.
+ * Needs N_b_DFT_os <= 4096 and L = M.  dnrp_sync_fdomain_read: results of the last dnrp_sync_batch / dnrp_rx_batch on this
+ * context: estimated beta and where the signal sits in subcarriers (cfo_integer_rad = -2 pi x that / N_b_DFT_os). */
+int dnrp_sync_set_fdomain(dnrp_ctx_t* ctx, float beta_threshold_dB, uint32_t cfo_search_range_subc);
+int dnrp_sync_fdomain_read(dnrp_ctx_t* ctx, uint32_t n, uint32_t* beta_out, int32_t* cfo_subc_out);
+
 /* the synchronisation stages run with the search_length of the last dnrp_sync_batch / dnrp_rx_batch call on this context */
 int dnrp_time_stage(dnrp_ctx_t* ctx, int stage, uint32_t n, uint32_t reps, float* ms_per_rep);
 

@@ -426,6 +426,13 @@ class batch_phy_t {
         uint32_t get_N_RX() const { return config.N_RX ? config.N_RX : 1; }
         const stats_t& get_stats() const { return stats; }
 
+        /// coarse_peak_f_domain_t of the packet search (sync_param.hpp:238-252, compiled out in the reference): beta search
+        /// with the given threshold (< 0 dB switches it on, the reference suggests -10) and integer CFO search over
+        /// +- cfo_search_range_subc subcarriers (>= 4 switches it on, the reference suggests 4) for every following search
+        void set_sync_fdomain(float beta_threshold_dB, uint32_t cfo_search_range_subc) {
+            check(dnrp_sync_set_fdomain(ctx, beta_threshold_dB, cfo_search_range_subc), "dnrp_sync_set_fdomain");
+        }
+
         /// Several batch_phy_t of ONE process, one per GPU: the sum of their counters in one NCCL all-reduce over the
         /// GPUs (dnrp_comm_init_all / dnrp_counters_allreduce_all; the reference adds into the members of one
         /// worker_pool_t / result_t of one process, worker_tx_rx.cpp:96-198, result.cpp:78-95).  The communicator is
