@@ -18,7 +18,7 @@ def _packets(product, cfg, os, n, N_RX, snr, seed, inc=0.0):
     tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
     plcf = rng.integers(0, 256, (n, 10), dtype=np.uint8)
     phy.tx(plcf, tb, iq_phase_increment=inc, fetch=False)
-    t0 = rng.integers(100, 2 * ps["N_samples_STF"] * os - 64, n)
+    t0 = rng.integers(32 * cfg[1] * os + 64, 2 * ps["N_samples_STF"] * os - 64, n)   # behind the two patterns the search skips
     win = phy.channel(n, snr_dB=snr, t0=t0, mode=0, seed=seed + 1, fetch=True)
     stride = phy.rx_stride()
     phy.close()
@@ -47,8 +47,9 @@ def test_beta_search_tells_every_beta_apart(product):
     rx.close()
 
 
-@pytest.mark.parametrize("cfg,N_RX", [((1, 4, 1, 1, 0, 3, 2048), 1), ((1, 16, 1, 2, 5, 7, 6144), 4)])
-def test_integer_cfo_search(product, cfg, N_RX):
+@pytest.mark.parametrize("cfg,N_RX,mode", [((1, 4, 1, 1, 0, 3, 2048), 1, 0), ((1, 16, 1, 2, 5, 7, 6144), 4, 0),
+                                           ((1, 16, 1, 2, 5, 4, 6144), 4, 2)])
+def test_integer_cfo_search(product, cfg, N_RX, mode):
     """the transmitter sits 4 s + f subcarriers off (s = -1, 0, 1, 2; f inside the +-2 the STF resolves): with the search
     on, the integer part is found (equal to the specification), fine peak and decoding work; without it only s = 0 does"""
     ps = spec.get_packet_sizes(*cfg)
@@ -61,8 +62,9 @@ def test_integer_cfo_search(product, cfg, N_RX):
     tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
     plcf = np.zeros((n, 10), dtype=np.uint8)
     phy.tx(plcf, tb, iq_phase_increment=inc, fetch=False)
-    t0 = rng.integers(100, 2 * ps["N_samples_STF"] - 64, n)
-    win = phy.channel(n, snr_dB=25.0, t0=t0, mode=0, seed=3, fetch=True)
+    t0 = rng.integers(32 * cfg[1] + 64, 2 * ps["N_samples_STF"] - 64, n)   # behind the two patterns the search skips
+    kw = dict(pdp_idx=1, tau_rms_ns=100.0, fD_Hz=50.0, time_64=1000) if mode == 2 else {}
+    win = phy.channel(n, snr_dB=25.0, t0=t0, mode=mode, seed=3, fetch=True, **kw)
     # off: the fine peak search decorrelates under an integer CFO (sync_param.hpp:246-252), those packets are lost
     sres, pcc, ok, tbo, _ = phy.rx(win)
     for i, (s, f) in enumerate(shifts):
@@ -74,8 +76,12 @@ def test_integer_cfo_search(product, cfg, N_RX):
     for i, (s, f) in enumerate(shifts):
         assert cfo[i] == 4 * s, (i, s, cfo)
         assert abs(sres.cfo_integer_rad[i] + 2 * np.pi * 4 * s / N) < 1e-6
-        assert abs(sres.cfo_fractional_rad[i] + 2 * np.pi * f / N) < 2e-4, (i, f, sres.cfo_fractional_rad[i] * N / 2 / np.pi)
-        assert int(sres.fine_peak_time_local[i]) == int(t0[i]), (i, sres.fine_peak_time_local[i], t0[i])
+        assert abs(sres.cfo_fractional_rad[i] + 2 * np.pi * f / N) < (2e-4 if mode == 0 else 1e-3), \
+            (i, f, sres.cfo_fractional_rad[i] * N / 2 / np.pi)
+        if mode == 0:   # a dispersive channel moves the fine peak by a few samples
+            assert int(sres.fine_peak_time_local[i]) == int(t0[i]), (i, sres.fine_peak_time_local[i], t0[i])
+        else:
+            assert abs(int(sres.fine_peak_time_local[i]) - int(t0[i])) <= 8
         bo, so = ofd.fdomain(win[i], sres.coarse_peak_time_local[i], sres.cfo_fractional_rad[i], cfg[1], 1, 12 * cfg[1] * 4,
                              cfo_range=8, N_eff_TX_max=ps["N_eff_TX"])
         assert so == cfo[i], (i, so, cfo[i])
