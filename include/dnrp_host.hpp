@@ -429,6 +429,11 @@ class batch_phy_t {
         /// coarse_peak_f_domain_t of the packet search (sync_param.hpp:238-252, compiled out in the reference): beta search
         /// with the given threshold (< 0 dB switches it on, the reference suggests -10) and integer CFO search over
         /// +- cfo_search_range_subc subcarriers (>= 4 switches it on, the reference suggests 4) for every following search
+        /// samples of a window the packet search may consume (sync_chunk_t's search range); 0 = the whole window.  The
+        /// device only sums the detection steps inside it: with windows of one packet plus slack,
+        /// window - packet + STF + 2 patterns covers every packet that still fits
+        void set_search_length(uint32_t n_samples) { search_length = n_samples; }
+
         void set_sync_fdomain(float beta_threshold_dB, uint32_t cfo_search_range_subc) {
             check(dnrp_sync_set_fdomain(ctx, beta_threshold_dB, cfo_search_range_subc), "dnrp_sync_set_fdomain");
         }
@@ -531,7 +536,7 @@ class batch_phy_t {
             if (n == 0) return tx_out;
             if (n > max_windows) throw std::invalid_argument("more windows than the context was created for");
             std::vector<dnrp_sync_result_t> sres(n);
-            check(dnrp_sync_batch(ctx, n, windows, 0, sres.data()), "dnrp_sync_batch");
+            check(dnrp_sync_batch(ctx, n, windows, search_length, sres.data()), "dnrp_sync_batch");
             std::vector<dnrp_pcc_report_t> pcc(n);
             check(dnrp_rx_pcc_batch(ctx, n, nullptr, nullptr, pcc.data()), "dnrp_rx_pcc_batch");
             stats.windows += n;
@@ -797,6 +802,7 @@ class batch_phy_t {
         uint32_t tx_stride{0}, rx_stride{0};
         stats_t stats;
         bool comm_ready{false};
+        uint32_t search_length{0};
         static void check(int rc, const char* what) {
             if (rc != DNRP_OK) throw std::runtime_error(std::string(what) + ": " + dnrp_last_error_string());
         }
