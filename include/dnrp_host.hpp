@@ -437,6 +437,12 @@ class batch_phy_t {
         void set_sync_fdomain(float beta_threshold_dB, uint32_t cfo_search_range_subc) {
             check(dnrp_sync_set_fdomain(ctx, beta_threshold_dB, cfo_search_range_subc), "dnrp_sync_set_fdomain");
         }
+        /// beta estimates and integer CFOs (subcarriers) of the windows of the last search (set_sync_fdomain switched on)
+        void read_sync_fdomain(uint32_t n, std::vector<uint32_t>& beta, std::vector<int32_t>& cfo_subc) {
+            beta.assign(n, 0);
+            cfo_subc.assign(n, 0);
+            check(dnrp_sync_fdomain_read(ctx, n, beta.data(), cfo_subc.data()), "dnrp_sync_fdomain_read");
+        }
 
         /// Several batch_phy_t of ONE process, one per GPU: the sum of their counters in one NCCL all-reduce over the
         /// GPUs (dnrp_comm_init_all / dnrp_counters_allreduce_all; the reference adds into the members of one
@@ -806,6 +812,82 @@ class batch_phy_t {
         static void check(int rc, const char* what) {
             if (rc != DNRP_OK) throw std::runtime_error(std::string(what) + ": " + dnrp_last_error_string());
         }
+};
+
+/// Several beta behind one receiver.  The reference's synchronisation, configured for the radio device class' largest
+/// beta, "is triggered by packets for b=8,4,2,1" and can "find the best fitting b in frequency domain" (sync_param.hpp:
+/// 238-244; the option is compiled out there).  Here: one batch_phy_t per beta, all at the same sample rate (beta x
+/// oversampling constant, so windows, STF length and detection are common).  The largest beta's PHY searches every
+/// window with the beta search on and receives its own packets; the windows whose estimate names a smaller beta are
+/// handed, gathered, to that beta's PHY, which searches and receives them under its own geometry.  The firmware learns a
+/// packet's beta from sync_report_t::b.  work_pcc order: FIFO inside every beta, the largest beta first.
+class multi_beta_phy_t {
+    public:
+        multi_beta_phy_t(const dnrp_config_t& cfg_largest_beta, int device_, uint32_t nof_process_rx_,
+                         float beta_threshold_dB = -10.0f)
+            : device(device_), nof_process_rx(nof_process_rx_), base(cfg_largest_beta) {
+            phys.emplace_back(std::make_unique<batch_phy_t>(cfg_largest_beta, device, nof_process_rx));
+            phys[0]->set_sync_fdomain(beta_threshold_dB, 0);
+        }
+        /// a smaller beta (its largest packet geometry, as for batch_phy_t); oversampling follows from the common rate
+        batch_phy_t& add_beta(const sp3::packet_sizes_def_t& psdef_largest_of_beta) {
+            const uint32_t b = psdef_largest_of_beta.b, rate = base.psdef.b * base.oversampling;
+            if (psdef_largest_of_beta.u != base.psdef.u || b == 0 || b >= base.psdef.b || rate % b != 0)
+                throw std::invalid_argument("add_beta: same mu, a smaller beta that divides beta x oversampling of the receiver");
+            dnrp_config_t c = base;
+            c.psdef = psdef_largest_of_beta;
+            c.oversampling = rate / b;
+            phys.emplace_back(std::make_unique<batch_phy_t>(c, device, nof_process_rx));
+            if (phys.back()->get_rx_stride() > phys[0]->get_rx_stride()) {
+                phys.pop_back();
+                throw std::invalid_argument("add_beta: the packet must fit the windows of the largest beta");
+            }
+            return *phys.back();
+        }
+        batch_phy_t& get(uint32_t b) {
+            for (auto& p : phys) if (p->get_packet_sizes().psdef.b == b) return *p;
+            throw std::invalid_argument("no PHY for this beta");
+        }
+        /// n host windows [n][N_RX][rx_stride of the largest beta]; returns all TX descriptors handed back
+        machigh_phy_t::tx_descriptor_vec_t process_windows(uint32_t n, const cf_t* windows, const int64_t* window_start_64,
+                                                           upper::tpoint_t& tpoint) {
+            if (!windows) throw std::invalid_argument("multi_beta_phy_t needs the windows in host memory");
+            machigh_phy_t::tx_descriptor_vec_t tx = phys[0]->process_windows(n, windows, window_start_64, tpoint);
+            std::vector<uint32_t> beta;
+            std::vector<int32_t> cfo;
+            phys[0]->read_sync_fdomain(n, beta, cfo);
+            last_beta = beta;
+            const size_t wlen = (size_t)phys[0]->get_N_RX() * phys[0]->get_rx_stride();
+            for (size_t k = 1; k < phys.size(); ++k) {
+                batch_phy_t& P = *phys[k];
+                const uint32_t b = P.get_packet_sizes().psdef.b;
+                const size_t plen = (size_t)P.get_N_RX() * P.get_rx_stride();
+                std::vector<cf_t> sub;
+                std::vector<int64_t> start;
+                for (uint32_t i = 0; i < n; ++i) {
+                    if (beta[i] != b) continue;
+                    // antenna by antenna: the smaller beta's window may be shorter than the receiver's
+                    for (uint32_t a = 0; a < P.get_N_RX(); ++a) {
+                        const cf_t* src = windows + (size_t)i * wlen + (size_t)a * phys[0]->get_rx_stride();
+                        sub.insert(sub.end(), src, src + P.get_rx_stride());
+                    }
+                    start.push_back(window_start_64 ? window_start_64[i] : 0);
+                }
+                const uint32_t m = (uint32_t)(sub.size() / std::max<size_t>(plen, 1));
+                if (m == 0) continue;
+                machigh_phy_t::tx_descriptor_vec_t t = P.process_windows(m, sub.data(), start.data(), tpoint);
+                for (const auto& d : t) tx.push_back(d);
+            }
+            return tx;
+        }
+        const std::vector<uint32_t>& get_last_beta() const { return last_beta; }
+
+    private:
+        int device;
+        uint32_t nof_process_rx;
+        dnrp_config_t base;
+        std::vector<std::unique_ptr<batch_phy_t>> phys;
+        std::vector<uint32_t> last_beta;
 };
 
 }  // namespace phy

@@ -114,3 +114,25 @@ def test_several_geometries_networks_and_plcf_types_in_one_call(tmp_path):
     assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
     out = json.loads(r.stdout.strip().splitlines()[-1])
     assert out["fails"] == 0 and out["work_pcc"] == 32 and out["work_pdc"] == 32 and out["tb_mismatch"] == 0
+
+
+def test_multi_beta_firmware_builds_and_refuses_to_run_without_gpu(tmp_path):
+    import torch
+    exe = build_program(tmp_path, "multi_beta_firmware")
+    if torch.cuda.is_available():
+        pytest.skip("GPU present: covered by the gpu test")
+    r = subprocess.run([exe, "6"], capture_output=True, text=True)
+    assert r.returncode == 3 and "no CPU fallback" in r.stderr, (r.returncode, r.stderr)
+
+
+@pytest.mark.gpu
+def test_one_receiver_for_packets_of_beta_4_2_and_1(tmp_path):
+    """multi_beta_phy_t: a receiver configured for beta = 4 gets windows that carry packets of beta 4, 2 and 1 at its sample
+    rate (sync_param.hpp:238-244: the synchronisation is triggered by every smaller beta); the beta search names each
+    window's beta, the window is received under that geometry, the firmware reads the beta from sync_report.b and every
+    transport block arrives"""
+    exe = build_program(tmp_path, "multi_beta_firmware")
+    r = subprocess.run([exe, "24"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["fails"] == 0 and out["beta_wrong"] == 0 and out["work_pdc"] == 24 and out["mismatch"] == 0
