@@ -409,6 +409,21 @@ class Phy:
         _check(lib().dnrp_sync_fdomain_read(self._ctx, n, _ptr(b, np.uint32), _ptr(cfo, np.int32)))
         return b, cfo
 
+    # ---- residual CFO / STO tracking on the DRS (off by default; rx_synced_param.hpp:156-181)
+    def rx_set_tracking(self, residual_cfo=True, residual_sto=True):
+        """dnrp_rx_set_tracking"""
+        f = lib().dnrp_rx_set_tracking
+        f.argtypes = [C.c_void_p, C.c_int, C.c_int]
+        _check(f(self._ctx, int(bool(residual_cfo)), int(bool(residual_sto))))
+
+    def rx_tracking_read(self, n):
+        """dnrp_rx_tracking_read: [n][2] float32 (dphi, dpsi): phase advance per N_step symbols, common and per subcarrier"""
+        out = np.zeros((n, 2), dtype=np.float32)
+        f = lib().dnrp_rx_tracking_read
+        f.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p]
+        _check(f(self._ctx, n, out.ctypes.data_as(C.c_void_p)))
+        return out
+
     # ---- streaming front door (worker_sync_t / sync_chunk_t / baton_t): packet search over one continuous stream
     def stream_sync(self, iq, chunk_hop=0, max_out=None):
         """iq [N_RX][n_samples] complex64 host stream; returns the unique packets in time order (STREAM_PACKET_DTYPE)"""

@@ -37,6 +37,8 @@ rx_params_t make_rx_params(dnrp_ctx* c) {
     p.cls = c->d_cls.p + off * c->cls_stride; p.cls_stride = c->cls_stride;
     p.llr_pcc = c->d_llr_pcc.p + off * 196;
     p.llr = c->d_llr.p + off * c->ps.G; p.llr_stride = c->ps.G;
+    p.track = (c->track_cfo || c->track_sto) ? c->d_track.p + off : nullptr;
+    p.track_cfo = c->track_cfo; p.track_sto = c->track_sto;
     return p;
 }
 
@@ -48,6 +50,7 @@ int run_rx_front(dnrp_ctx* c, uint32_t n) {
     const rx_params_t p = make_rx_params(c);
     DNRP_LAUNCH(c, DNRP_KERNEL_RX_STF, launch_rx_stf(p, n, c->stream));
     DNRP_LAUNCH(c, DNRP_KERNEL_RX_FFT, launch_rx_fft(p, n, c->stream));
+    if (p.track) DNRP_LAUNCH(c, -1, launch_rx_track(p, n, c->stream));
     DNRP_LAUNCH(c, -1, launch_rx_snr_class(p, n, c->stream));
     return DNRP_OK;
 }
@@ -253,6 +256,29 @@ int dnrp_sync_set_fdomain(dnrp_ctx_t* c, float beta_threshold_dB, uint32_t cfo_s
     // the reference converts its dB threshold with db2mag (coarse_peak_f_domain.cpp:140-141)
     c->fd_beta_thr = beta_threshold_dB < 0.f ? powf(10.0f, beta_threshold_dB / 20.0f) : 0.f;
     c->fd_cfo_range = cfo_search_range_subc >= 4 ? cfo_search_range_subc : 0;
+    return DNRP_OK;
+}
+
+// residual CFO / STO tracking on the DRS: RX_SYNCED_PARAM_CFO_RESIDUAL_BASED_ON_DRS / RX_SYNCED_PARAM_STO_RESIDUAL_BASED_ON_DRS
+// of the reference (rx_synced_param.hpp:156-181, both commented out, "not functional yet"); here per context at run time
+int dnrp_rx_set_tracking(dnrp_ctx_t* c, int residual_cfo, int residual_sto) {
+    DNRP_REQUIRE(c, "null argument");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    if ((residual_cfo || residual_sto) && c->d_track.n == 0) DNRP_CUDA(c->d_track.alloc(c->B));
+    c->track_cfo = residual_cfo != 0;
+    c->track_sto = residual_sto != 0;
+    return DNRP_OK;
+}
+
+int dnrp_rx_tracking_read(dnrp_ctx_t* c, uint32_t n, float* out) {
+    DNRP_REQUIRE(c && out && n > 0 && n <= c->B, "invalid argument");
+    if (c->d_track.n == 0 || !(c->track_cfo || c->track_sto)) {
+        set_last_error("residual CFO / STO tracking is off (dnrp_rx_set_tracking)");
+        return DNRP_ERR_STATE;
+    }
+    DNRP_CUDA(cudaSetDevice(c->device));
+    DNRP_CUDA(cudaMemcpyAsync(out, c->d_track.p, n * sizeof(float2), cudaMemcpyDeviceToHost, c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
     return DNRP_OK;
 }
 

@@ -145,6 +145,8 @@ struct dnrp_ctx {
     uint32_t rx_stride = 0;  // samples per antenna in d_iq_rx
     uint32_t cls_stride = 0;
     dnrp::dbuf<float2> d_iq_rx, d_Y, d_hzf, d_hstf, d_snr_part;
+    dnrp::dbuf<float2> d_track;            // residual CFO / STO estimates (dnrp_rx_set_tracking), allocated on first use
+    bool track_cfo{false}, track_sto{false};
     dnrp::dbuf<dnrp::rx_state_t> d_rx_state;
     dnrp::dbuf<uint8_t> d_cls;
     dnrp::dbuf<float2> d_chestim_tap;           // DNRP_TAP_CHESTIM, allocated by the first read

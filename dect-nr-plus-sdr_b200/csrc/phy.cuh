@@ -101,6 +101,10 @@ struct rx_params_t {
     int16_t* llr_pcc;        // [packet][196]
     int16_t* llr;            // [packet][llr_stride]
     size_t llr_stride;
+    // residual CFO / STO tracking on the DRS (k_rx_track; nullptr = off): per packet the phase advance per N_step symbols,
+    // .x common to all subcarriers (residual CFO), .y per subcarrier (drift of the symbol timing)
+    float2* track;           // [packet]
+    uint32_t track_cfo, track_sto;
 };
 
 // mimo_report_t (lib/include/dectnrp/phy/rx/rx_synced/mimo/mimo_report.hpp:27-59)
@@ -122,6 +126,7 @@ cudaError_t launch_rx_mimo(const mimo_params_t& p, uint32_t n_packets, cudaStrea
 cudaError_t launch_rx_stf(const rx_params_t& p, uint32_t n_packets, cudaStream_t st);
 cudaError_t launch_rx_fft(const rx_params_t& p, uint32_t n_packets, cudaStream_t st);
 cudaError_t launch_rx_snr_class(const rx_params_t& p, uint32_t n_packets, cudaStream_t st);
+cudaError_t launch_rx_track(const rx_params_t& p, uint32_t n_packets, cudaStream_t st);
 cudaError_t launch_rx_demap(const rx_params_t& p, uint32_t n_packets, bool pcc, cudaStream_t st);
 // out [packet][N_RX][N_eff_TX][Nk]: the channel estimate the reference holds in channel_antennas[a]->chestim[ts] when the
 // packet is done (rx_synced.cpp:444-480 exports exactly that)

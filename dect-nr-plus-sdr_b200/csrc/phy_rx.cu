@@ -480,6 +480,91 @@ __global__ void k_rx_snr_class(const rx_params_t p, uint32_t n_packets) {
     st.snr_db_pdc = snr_db;
 }
 
+// ---- residual CFO / STO tracking on the DRS (own specification, DESIGN.md "Residual CFO / STO on the DRS"; the
+// reference plans it: rx_synced_param.hpp:156-181, estimator_cfo.cpp:31-70, rx_synced.cpp:839-851, "not functional yet").
+// Batched form: one estimate per packet over ALL its DRS symbols instead of a feedback loop from symbol to symbol.
+//   pilot i of occurrence n + 1 lies midway between two pilots of occurrence n (interlaced by two subcarriers):
+//               P_i = h_{n+1}[i] conj((h_n[i'] + h_n[i' + 1]) / 2)   has the phase dphi + (k_i - k_DC) dpsi
+//   STO drift:  dpsi = arg(sum P_{i+1} conj(P_i)) / 4   (the pair across DC, 5 subcarriers apart, left out)
+//   CFO:        dphi = arg(sum P_i e^{-j (k_i - k_DC) dpsi})          (sums over antennas, streams, occurrences, pilots)
+// both are phase advances per N_step OFDM symbols.  Cell (l, k) is taken back to the phase reference of the first DRS
+// symbol by e^{-j f (dphi + (k - k_DC) dpsi)}, f = (l - 1) / N_step: the pilots here in place, Y where it is loaded.
+__device__ __forceinline__ float2 track_phasor(const phy_dims_t& d, float2 tr, uint32_t l, uint32_t k) {
+    const float f = (float)(l - 1) / (float)d.N_step;
+    float turns = -f * (tr.x + (float)((int)k - (int)(d.N_OCC / 2)) * tr.y) * 0.15915494309189535f;
+    turns -= rintf(turns);
+    float sn, cs;
+    __sincosf(6.283185307179586f * turns, &sn, &cs);
+    return make_float2(cs, sn);
+}
+
+__global__ void __launch_bounds__(128) k_rx_track(const rx_params_t p) {
+    __shared__ float2 s_red[4];
+    const phy_dims_t& d = p.d;
+    const uint32_t pkt = blockIdx.x, tid = threadIdx.x;
+    const uint32_t stride_a = d.N_eff_TX * d.n_drs * d.NP;
+    float2* hz_pkt = p.hzf + (size_t)pkt * d.N_RX * stride_a;
+    float2 tr = make_float2(0.f, 0.f);
+    if (d.n_drs >= 2) {
+        // P(n, ts, a, i) = h_{n+1}[i] conj(midpoint of its two neighbours in occurrence n): the channel cancels, the phase
+        // that is left is dphi + (k - k_DC) dpsi
+        auto P = [&](const float2* h0, const float2* h1, uint32_t i, uint32_t lo) {
+            const float2 ref = make_float2(0.5f * (h0[i - lo].x + h0[i - lo + 1].x), 0.5f * (h0[i - lo].y + h0[i - lo + 1].y));
+            return cmulc(h1[i], ref);
+        };
+        for (int pass = p.track_sto ? 0 : 1; pass < (p.track_cfo ? 2 : 1); ++pass) {
+            float2 Z = make_float2(0.f, 0.f);
+            for (uint32_t n = 0; n + 1 < d.n_drs; ++n)
+                for (uint32_t ts = 0; ts < d.N_eff_TX; ++ts) {
+                    const uint32_t pc = ((ts & 3) + 2 * (n & 1)) & 3, pc1 = (pc + 2) & 3;   // occurrences n, n + 1
+                    const uint32_t lo = pc < 2 ? 0u : 1u;          // pilot i of n + 1 between i - lo and i - lo + 1 of n
+                    for (uint32_t a = 0; a < d.N_RX; ++a) {
+                        const float2* h0 = hz_pkt + a * stride_a + (ts * d.n_drs + n) * d.NP;
+                        const float2* h1 = h0 + d.NP;
+                        if (pass == 0) {
+                            // slope of the phase of P over the subcarriers: neighbours 4 apart (5 across DC: left out)
+                            for (uint32_t i = tid + lo; i + 2 - lo < d.NP; i += blockDim.x) {
+                                const uint32_t q = 4 * i + pc1;
+                                if (q < d.N_OCC / 2 && q + 4 >= d.N_OCC / 2) continue;
+                                Z = cadd(Z, cmulc(P(h0, h1, i + 1, lo), P(h0, h1, i, lo)));
+                            }
+                        } else {
+                            for (uint32_t i = tid + lo; i + 1 - lo < d.NP; i += blockDim.x) {
+                                float2 z = P(h0, h1, i, lo);
+                                if (p.track_sto) {
+                                    const uint32_t q = 4 * i + pc1, k = q < d.N_OCC / 2 ? q : q + 1;
+                                    z = cmul(z, track_phasor(d, make_float2(0.f, tr.y), 1 + d.N_step, k));
+                                }
+                                Z = cadd(Z, z);
+                            }
+                        }
+                    }
+                }
+            Z = block_sum2(Z, s_red);
+            const float ang = (Z.x != 0.f || Z.y != 0.f) ? atan2f(Z.y, Z.x) : 0.f;
+            if (pass == 0) tr.y = 0.25f * ang; else tr.x = ang;
+        }
+    }
+    if (tid == 0) p.track[pkt] = tr;
+    if (tr.x == 0.f && tr.y == 0.f) return;
+    // the pilots back to the phase reference of the first DRS symbol (streams 4..7 sit one symbol later)
+    for (uint32_t a = 0; a < d.N_RX; ++a)
+        for (uint32_t ts = 0; ts < d.N_eff_TX; ++ts)
+            for (uint32_t n = 0; n < d.n_drs; ++n) {
+                const uint32_t pc = ((ts & 3) + 2 * (n & 1)) & 3, l = 1 + n * d.N_step + (ts >= 4 ? 1u : 0u);
+                float2* h = hz_pkt + a * stride_a + (ts * d.n_drs + n) * d.NP;
+                for (uint32_t i = tid; i < d.NP; i += blockDim.x) {
+                    const uint32_t q = 4 * i + pc, k = q < d.N_OCC / 2 ? q : q + 1;
+                    h[i] = cmul(h[i], track_phasor(d, tr, l, k));
+                }
+            }
+}
+
+cudaError_t launch_rx_track(const rx_params_t& p, uint32_t n_packets, cudaStream_t st) {
+    k_rx_track<<<n_packets, 128, 0, st>>>(p);
+    return cudaGetLastError();
+}
+
 // ---- channel estimate of transmit stream ts at (symbol l, subcarrier k) seen by RX antenna a: the value
 // rx_synced_t::run_drs_ch_interpolation (rx_synced.cpp:893-960) holds in chestim[ts][k] at the moment
 // the reference collects the cells of symbol l.  Closed form of the processing stage bookkeeping of
@@ -711,10 +796,13 @@ __global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_dema
             float den = 0.f;
             float2 h[NRX];
             chan_est_rx<NRX>(p, pkt, plan[2 * u], k, h);
+            const bool trk = p.track != nullptr;
+            const float2 c0 = trk ? track_phasor(d, p.track[pkt], l, k) : make_float2(1.f, 0.f);
 #pragma unroll
             for (int a = 0; a < NRX; ++a) {
                 // streaming loads / stores (evict first): Y and the LLRs pass through once, the pilots stay in L1
-                const float2 y = __ldcs(&p.Y[(((size_t)pkt * NRX + a) * d.N_DF + (l - 1)) * d.Nk + k]);
+                float2 y = __ldcs(&p.Y[(((size_t)pkt * NRX + a) * d.N_DF + (l - 1)) * d.Nk + k]);
+                if (trk) y = cmul(y, c0);
                 num = cadd(num, cmulc(y, h[a]));
                 den += h[a].x * h[a].x + h[a].y * h[a].y;
             }
@@ -730,10 +818,18 @@ __global__ void __launch_bounds__(128, TXDIV ? (NRX > 2 ? 6 : 8) : 10) k_rx_dema
             const phy_dims_t::pair_lut_t* pl = pcc ? d.pcc_pair : d.pdc_pair;
             chan_est_rx_pair<NRX>(p, pkt, planA, k0, k1, h0, pl, u, 0);
             chan_est_rx_pair<NRX>(p, pkt, planB, k0, k1, h1, pl, u, 1);
+            const bool trk = p.track != nullptr;
+            float2 c0 = make_float2(1.f, 0.f), c1 = c0;
+            if (trk) {
+                const float2 tr = p.track[pkt];
+                c0 = track_phasor(d, tr, l, k0);
+                c1 = track_phasor(d, tr, l, k1);
+            }
 #pragma unroll
             for (int a = 0; a < NRX; ++a) {
                 const float2* Y = p.Y + (((size_t)pkt * NRX + a) * d.N_DF + (l - 1)) * d.Nk;
-                const float2 r0 = __ldcs(&Y[k0]), r1 = __ldcs(&Y[k1]);
+                float2 r0 = __ldcs(&Y[k0]), r1 = __ldcs(&Y[k1]);
+                if (trk) { r0 = cmul(r0, c0); r1 = cmul(r1, c1); }
                 // conj(h0) r0 + h1 conj(r1)   and   -h1 conj(r0) + conj(h0) r1   (rx_synced.cpp:1372-1373)
                 n0 = cadd(n0, cadd(cmulc(r0, h0[a]), cmulc(h1[a], r1)));
                 n1 = cadd(n1, csub(cmulc(r1, h0[a]), cmulc(h1[a], r0)));
@@ -786,6 +882,11 @@ __device__ __forceinline__ void sm_solve(const rx_params_t& p, uint32_t pkt, uin
     float2 y[NRX];
 #pragma unroll
     for (int a = 0; a < NRX; ++a) y[a] = __ldcs(&p.Y[(((size_t)pkt * NRX + a) * d.N_DF + (l - 1)) * d.Nk + k]);
+    if (p.track) {
+        const float2 c0 = track_phasor(d, p.track[pkt], l, k);
+#pragma unroll
+        for (int a = 0; a < NRX; ++a) y[a] = cmul(y[a], c0);
+    }
     float2 L[NSS][NSS], b[NSS];   // lower triangle; after the factorisation the diagonal holds 1 / L_jj in .x
     float g[NSS];
 #pragma unroll
@@ -1013,6 +1114,11 @@ __global__ void __launch_bounds__(128) k_rx_chestim_tap(const rx_params_t p, flo
     if (k >= d.Nk) return;
     float2 h[NRX];
     chan_est_rx<NRX>(p, pkt, d.last_plan[ts], k, h);
+    if (p.track) {   // the estimate as it stands at the last symbol: the tracked rotation put back
+        const float2 c0 = track_phasor(d, p.track[pkt], d.N_DF, k);
+#pragma unroll
+        for (int a = 0; a < NRX; ++a) h[a] = cmulc(h[a], c0);
+    }
 #pragma unroll
     for (int a = 0; a < NRX; ++a) out[(((size_t)pkt * NRX + a) * d.N_eff_TX + ts) * d.Nk + k] = h[a];
 }

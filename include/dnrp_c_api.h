@@ -422,6 +422,20 @@ typedef enum {
 int dnrp_sync_set_fdomain(dnrp_ctx_t* ctx, float beta_threshold_dB, uint32_t cfo_search_range_subc);
 int dnrp_sync_fdomain_read(dnrp_ctx_t* ctx, uint32_t n, uint32_t* beta_out, int32_t* cfo_subc_out);
 
+/* ---- residual CFO / STO tracking on the DRS ---------------------------------------------------------------------
+ * RX_SYNCED_PARAM_CFO_RESIDUAL_BASED_ON_DRS / RX_SYNCED_PARAM_STO_RESIDUAL_BASED_ON_DRS of the reference
+ * (lib/include/dectnrp/phy/rx/rx_synced/rx_synced_param.hpp:156-181, both commented out there: "not functional yet";
+ * estimator_cfo_t::process_drs lib/src/phy/rx/rx_synced/offsets/estimator_cfo.cpp:31-70, call sites rx_synced.cpp:839-851,
+ * the post-correction rx_synced.cpp:1165-1169 is an empty todo).  Here per context at run time, off by default.  Own
+ * specification: per packet ONE estimate over all DRS symbols of the phase advance per N_step OFDM symbols
+ * -- common to all subcarriers (residual CFO) and per subcarrier (drift of the symbol timing, i.e. a sampling clock
+ * offset) --, the DRS pilots and every cell taken back to the phase reference of the first DRS symbol before channel
+ * interpolation and detection (PCC and PDC).  Packets with one DRS occurrence per stream are left as they are.
+ * dnrp_rx_tracking_read: out [n][2] = (dphi, dpsi) in rad of the last dnrp_rx_pcc_batch / dnrp_rx_batch on this context;
+ * residual CFO = dphi / (2 pi N_step (1 + CP/N)) subcarrier spacings. */
+int dnrp_rx_set_tracking(dnrp_ctx_t* ctx, int residual_cfo, int residual_sto);
+int dnrp_rx_tracking_read(dnrp_ctx_t* ctx, uint32_t n, float* out);
+
 /* the synchronisation stages run with the search_length of the last dnrp_sync_batch / dnrp_rx_batch call on this context */
 int dnrp_time_stage(dnrp_ctx_t* ctx, int stage, uint32_t n, uint32_t reps, float* ms_per_rep);
 

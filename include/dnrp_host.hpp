@@ -426,16 +426,21 @@ class batch_phy_t {
         uint32_t get_N_RX() const { return config.N_RX ? config.N_RX : 1; }
         const stats_t& get_stats() const { return stats; }
 
-        /// coarse_peak_f_domain_t of the packet search (sync_param.hpp:238-252, compiled out in the reference): beta search
-        /// with the given threshold (< 0 dB switches it on, the reference suggests -10) and integer CFO search over
-        /// +- cfo_search_range_subc subcarriers (>= 4 switches it on, the reference suggests 4) for every following search
         /// samples of a window the packet search may consume (sync_chunk_t's search range); 0 = the whole window.  The
         /// device only sums the detection steps inside it: with windows of one packet plus slack,
         /// window - packet + STF + 2 patterns covers every packet that still fits
         void set_search_length(uint32_t n_samples) { search_length = n_samples; }
 
+        /// coarse_peak_f_domain_t of the packet search (sync_param.hpp:238-252, compiled out in the reference): beta search
+        /// with the given threshold (< 0 dB switches it on, the reference suggests -10) and integer CFO search over
+        /// +- cfo_search_range_subc subcarriers (>= 4 switches it on, the reference suggests 4) for every following search
         void set_sync_fdomain(float beta_threshold_dB, uint32_t cfo_search_range_subc) {
             check(dnrp_sync_set_fdomain(ctx, beta_threshold_dB, cfo_search_range_subc), "dnrp_sync_set_fdomain");
+        }
+        /// residual CFO / STO tracking on the DRS (rx_synced_param.hpp:156-181, compiled out in the reference) for every
+        /// following reception
+        void set_tracking(bool residual_cfo, bool residual_sto) {
+            check(dnrp_rx_set_tracking(ctx, residual_cfo, residual_sto), "dnrp_rx_set_tracking");
         }
         /// beta estimates and integer CFOs (subcarriers) of the windows of the last search (set_sync_fdomain switched on)
         void read_sync_fdomain(uint32_t n, std::vector<uint32_t>& beta, std::vector<int32_t>& cfo_subc) {
