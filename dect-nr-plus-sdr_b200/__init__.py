@@ -46,7 +46,7 @@ class PacketSizes(C.Structure):
 class Config(C.Structure):
     _fields_ = [("psdef", Psdef)] + [(n, C.c_uint32) for n in (
         "N_RX", "oversampling", "resample_L", "resample_M", "max_batch", "network_id", "plcf_type",
-        "chestim_mode_lr", "chestim_mode_lr_t_stride", "tdec_min_iter", "tdec_max_iter")]
+        "chestim_mode_lr", "chestim_mode_lr_t_stride", "tdec_min_iter", "tdec_max_iter", "N_soft", "M_DL_HARQ")]
 
 
 class TxDesc(C.Structure):
@@ -198,10 +198,10 @@ class Phy:
     """One context = one GPU + one packet geometry + a maximum batch size."""
 
     def __init__(self, psdef, max_batch, N_RX=1, network_id=123456789, plcf_type=1, device=0, oversampling=1,
-                 resample=(1, 1), chestim_mode_lr=True, chestim_stride=2, tdec_iters=(2, 10)):
+                 resample=(1, 1), chestim_mode_lr=True, chestim_stride=2, tdec_iters=(2, 10), N_soft=0, M_DL_HARQ=1):
         self._ctx = C.c_void_p()
         cfg = Config(Psdef(*psdef), N_RX, oversampling, resample[0], resample[1], max_batch, network_id, plcf_type,
-                     int(chestim_mode_lr), chestim_stride, tdec_iters[0], tdec_iters[1])
+                     int(chestim_mode_lr), chestim_stride, tdec_iters[0], tdec_iters[1], N_soft, M_DL_HARQ)
         _check(lib().dnrp_ctx_create(C.byref(cfg), device, C.byref(self._ctx)))
         ps = PacketSizes()
         _check(lib().dnrp_ctx_get_packet_sizes(self._ctx, C.byref(ps)))

@@ -100,7 +100,15 @@ int dnrp_ctx_create(const dnrp_config_t* cfg, int device, dnrp_ctx_t** out) {
         return code;
     };
     if (!spec::get_packet_sizes(d, c->ps)) return fail(DNRP_ERR_INVALID, "packet configuration not possible");
-    if ((rc = build_fec_plan(c->ps, c->fec)) != DNRP_OK) return fail(rc, "FEC plan failed");
+    uint32_t N_IR = 0;
+    if (c->cfg.N_soft) {
+        // TS 36.212 5.1.4.1.2 with K_C = K_MIMO = 1; every code block must keep at least its systematic part
+        N_IR = c->cfg.N_soft / (c->cfg.M_DL_HARQ ? c->cfg.M_DL_HARQ : 1u);
+        const uint32_t Kp = 32 * ((c->ps.seg.K1 + 4 + 31) / 32);
+        if (N_IR / c->ps.seg.C < Kp)
+            return fail(DNRP_ERR_INVALID, "N_soft / M_DL_HARQ / C is smaller than the systematic part of a code block");
+    }
+    if ((rc = build_fec_plan(c->ps, c->fec, N_IR)) != DNRP_OK) return fail(rc, "FEC plan failed");
     if (cudaStreamCreateWithFlags(&c->stream, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->stream_copy, cudaStreamNonBlocking) != cudaSuccess ||
         cudaStreamCreateWithFlags(&c->stream_d2h, cudaStreamNonBlocking) != cudaSuccess)

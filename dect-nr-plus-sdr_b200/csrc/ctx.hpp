@@ -74,7 +74,8 @@ struct fec_plan_t {
     size_t tdec_smem = 0;
 };
 
-int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f);
+// N_IR: soft bits one transport block may use (N_soft / M_DL_HARQ, TS 36.212 5.1.4.1.2); 0 = no limitation
+int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f, uint32_t N_IR = 0);
 
 }  // namespace dnrp
 

@@ -54,7 +54,7 @@ __global__ void __launch_bounds__(256) k_derm(const tdec_params_t p, uint32_t ca
     const bool staged = cb.n_e <= cap;
     // rate >= 1/3 (n_e <= N) and room for N entries: zero pad the staged LLRs up to N, every circular-buffer
     // position then reads exactly one entry (punctured positions read a zero) -- no loop, no bounds test
-    const bool single = staged && cb.n_e <= N && N <= cap;
+    const bool single = staged && cb.n_e <= cb.Nc && N <= cap;
     auto descr = [&](uint32_t e, int v) -> int {   // srsran_scrambling_s_offset: sign flip where the Gold bit is 1
         const uint32_t g = cb.rp + e + p.gold_bit_off;
         return ((gold[g >> 3] >> (7 - (g & 7))) & 1) ? -v : v;
@@ -141,12 +141,13 @@ __global__ void __launch_bounds__(256) k_derm(const tdec_params_t p, uint32_t ca
         for (int u = 0; u < 4; ++u) {
             const uint32_t v = pos[u];
             acc[u] = prev[u];
+            if (v == 0xffffu) continue;   // outside a limited circular buffer: never sent
             if (single) {
                 acc[u] += DSC[v];
             } else if (staged) {
-                for (uint32_t ee = v; ee < cb.n_e; ee += N) acc[u] += DSC[ee];
+                for (uint32_t ee = v; ee < cb.n_e; ee += cb.Nc) acc[u] += DSC[ee];
             } else {
-                for (uint32_t ee = v; ee < cb.n_e; ee += N) acc[u] += descr(ee, llr[ee]);
+                for (uint32_t ee = v; ee < cb.n_e; ee += cb.Nc) acc[u] += descr(ee, llr[ee]);
             }
         }
         soft4[q] = make_uint2(((uint32_t)acc[0] & 0xffffu) | ((uint32_t)acc[1] << 16),

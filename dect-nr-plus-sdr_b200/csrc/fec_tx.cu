@@ -255,8 +255,9 @@ __global__ void __launch_bounds__(256) k_tx_fec(const txfec_params_t p) {
             if (g >= wp && g < we) {
                 const uint32_t e = g - wp;
                 if (e < cb.n_e) {
-                    uint32_t pos = start + (e < N ? e : e % N);   // repetition (e >= N) only below rate 1/3
-                    if (pos >= N) pos -= N;
+                    const uint32_t Nc = cb.Nc;
+                    uint32_t pos = start + (e < Nc ? e : e % Nc);   // repetition (e >= Nc): below rate 1/3 or a limited buffer
+                    if (pos >= Nc) pos -= Nc;
                     bit = d[src[pos]];
                 }
                 const uint32_t gg = g + p.gold_bit_off;

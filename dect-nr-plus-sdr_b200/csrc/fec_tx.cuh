@@ -14,6 +14,7 @@ struct txcb_desc_t {
     uint32_t wp, n_e, n_pad;   // output bit offset, rate matched bits, extra scrambled zero bits
     uint32_t rm_src_off;       // offset of this K's src[] table in the rate-matching arena
     uint32_t rm_start[4];
+    uint32_t Nc;               // usable entries of src[] (3K + 12 unless the soft buffer is limited)
     // CRC chunk combination: x^(bits behind thread t's chunk + order) mod g for the TX_FEC_THREADS chunks of the
     // whole-message CRC (xp_tb_off) and of the code block CRC (xp_cb_off), offsets into the x^n arena
     uint32_t xp_tb_off, xp_cb_off;

@@ -44,18 +44,22 @@ uint32_t gf2_xpow_host(uint32_t n, uint32_t poly, uint32_t order) {
     return result;
 }
 
-int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
+int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f, uint32_t N_IR) {
     const spec::cbsegm_t& s = ps.seg;
     // K -> offset of src[] (transmitter: circular buffer position -> source bit); the receiver's tables follow at +N
     // (four, one per redundancy version): pos[] in the order of the DECODER's soft-buffer layout (soft_layout_index below), so that k_derm, which walks
     // table and soft buffer in lockstep, writes the streams exactly as k_turbo_decode stages them
     std::map<uint32_t, uint32_t> rm_off;
     std::map<uint32_t, spec::rm_table_t> rm_tab;
-    auto add_rm = [&](uint32_t K) {
-        if (rm_off.count(K)) return;
+    // limit = N_cb of this K (0: none).  One plan uses a K with one limit only (the transport block's, or none: PLCF)
+    // key: K for the transport block's tables, K + PLCF_KEY for the PLCF's (never limited, even where a tiny transport
+    // block shares its K)
+    constexpr uint32_t PLCF_KEY = 100000u;
+    auto add_rm = [&](uint32_t K, uint32_t limit = 0, uint32_t key_off = 0) {
+        if (rm_off.count(K + key_off)) return;
         spec::rm_table_t t;
-        spec::build_rm_table(K, t);
-        rm_off[K] = (uint32_t)f.rm_arena.size();
+        spec::build_rm_table(K, t, limit);
+        rm_off[K + key_off] = (uint32_t)f.rm_arena.size();
         f.rm_arena.insert(f.rm_arena.end(), t.src.begin(), t.src.end());
         // soft buffer of a code block (3K + 12 int16): three streams d0 d1 d2 of K/2 words, word a = k * T + t =
         // (element t*L + k | element K/2 + t*L + k << 16) -- the window-transposed pair packing of the decoder's shared
@@ -72,18 +76,22 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         }
         // one copy per redundancy version with the start offset folded in: entry = index of the received LLR (mod N,
         // first pass over the circular buffer) that lands on this soft-buffer position
-        const uint32_t N = 3 * D;
+        // A soft-buffer position outside a limited circular buffer (posT >= Nc) is never sent: entry 0xffff, which the
+        // gather of k_derm skips
+        const uint32_t N = 3 * D, Nc = t.Nc;
         for (int rv = 0; rv < 4; ++rv)
-            for (uint32_t n = 0; n < N; ++n) f.rm_arena.push_back((uint16_t)((posT[n] + N - t.start[rv]) % N));
+            for (uint32_t n = 0; n < N; ++n)
+                f.rm_arena.push_back(posT[n] < Nc ? (uint16_t)((posT[n] + Nc - t.start[rv]) % Nc) : (uint16_t)0xffffu);
         // and the inverse per redundancy version: received LLR e (first pass over the circular buffer) -> soft-buffer
         // position; k_derm scatters the n_e <= N LLRs of a code block through it into a zeroed shared image of the soft
         // buffer (fewer random accesses than gathering all N positions at the usual code rates)
         for (int rv = 0; rv < 4; ++rv) {
-            std::vector<uint16_t> inv(N);
-            for (uint32_t n = 0; n < N; ++n) inv[(posT[n] + N - t.start[rv]) % N] = (uint16_t)n;
+            std::vector<uint16_t> inv(N, 0);
+            for (uint32_t n = 0; n < N; ++n)
+                if (posT[n] < Nc) inv[(posT[n] + Nc - t.start[rv]) % Nc] = (uint16_t)n;
             f.rm_arena.insert(f.rm_arena.end(), inv.begin(), inv.end());
         }
-        rm_tab[K] = t;
+        rm_tab[K + key_off] = t;
     };
     auto add_xp = [&](uint32_t K, uint32_t L, uint32_t poly, uint32_t order) -> uint32_t {
         const uint32_t off = (uint32_t)f.xp_arena.size();
@@ -124,7 +132,7 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         const bool last = cb + 1 == s.C;
         uint32_t f1, f2;
         spec::qpp_params(Kidx, f1, f2);
-        add_rm(K);
+        add_rm(K, N_IR ? std::max(N_IR / s.C, 1u) : 0u);   // N_cb = min(floor(N_IR / C), K_w)
         const uint32_t L = tdec_window(K);
         track(K, L);
         const uint32_t poly = s.C > 1 ? spec::CRC24B_POLY : spec::CRC24A_POLY;
@@ -142,6 +150,7 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         t.n_pad = 0;
         t.rm_src_off = rm_off[K];
         for (int rv = 0; rv < 4; ++rv) t.rm_start[rv] = rm_tab[K].start[rv];
+        t.Nc = rm_tab[K].Nc;
         t.xp_tb_off = t.tb_crc_bits ? add_xp_tx(t.tb_crc_len, t.tb_crc_poly, t.tb_crc_bits, 8) : 0;
         t.xp_cb_off = t.cb_crc ? add_xp_tx(t.n_data + t.tb_crc_bits, spec::CRC24B_POLY, 24, 1) : 0;
         f.tx_cbs.push_back(t);
@@ -165,6 +174,7 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         r.rm_off = rm_off[K] + 3 * (K + 4);  // pos[]
         r.rm_inv_off = r.rm_off + 4 * 3 * (K + 4);
         for (int rv = 0; rv < 4; ++rv) r.rm_start[rv] = rm_tab[K].start[rv];
+        r.Nc = rm_tab[K].Nc;
         r.crc_poly = poly;
         r.crc_order = 24;
         r.xp_off = xp_off[K];
@@ -196,7 +206,7 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         const int Kidx = spec::tc_cb_index(K);
         uint32_t f1, f2;
         spec::qpp_params(Kidx, f1, f2);
-        add_rm(K);
+        add_rm(K, 0, PLCF_KEY);
         const uint32_t L = tdec_window(K);
         track(K, L);
         txcb_desc_t t{};
@@ -205,8 +215,9 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         t.tb_crc_bits = 16; t.tb_crc_poly = spec::CRC16_POLY; t.tb_crc_len = nb;
         t.cb_crc = 0;
         t.wp = 0; t.n_e = spec::PCC_BITS; t.n_pad = 4;  // the reference scrambles 200 bits (pcc_enc.cpp:212)
-        t.rm_src_off = rm_off[K];
-        for (int rv = 0; rv < 4; ++rv) t.rm_start[rv] = rm_tab[K].start[rv];
+        t.rm_src_off = rm_off[K + PLCF_KEY];
+        for (int rv = 0; rv < 4; ++rv) t.rm_start[rv] = rm_tab[K + PLCF_KEY].start[rv];
+        t.Nc = rm_tab[K + PLCF_KEY].Nc;
         t.xp_tb_off = add_xp_tx(t.tb_crc_len, t.tb_crc_poly, t.tb_crc_bits, 8);
         t.xp_cb_off = 0;
         f.tx_pcc[ty] = t;
@@ -217,9 +228,10 @@ int build_fec_plan(const spec::packet_sizes_t& ps, fec_plan_t& f) {
         r.out_byte = ty * 16;      // plcf_out [packet][2][16]
         r.rlen_byte = nb / 8;
         r.soft_off = ty * 320;     // soft_pcc [packet][2][320]
-        r.rm_off = rm_off[K] + 3 * (K + 4);
+        r.rm_off = rm_off[K + PLCF_KEY] + 3 * (K + 4);
         r.rm_inv_off = r.rm_off + 4 * 3 * (K + 4);
-        for (int rv = 0; rv < 4; ++rv) r.rm_start[rv] = rm_tab[K].start[rv];
+        for (int rv = 0; rv < 4; ++rv) r.rm_start[rv] = rm_tab[K + PLCF_KEY].start[rv];
+        r.Nc = rm_tab[K + PLCF_KEY].Nc;
         r.crc_poly = spec::CRC16_POLY;
         r.crc_order = 16;
         r.xp_off = add_xp(K, L, spec::CRC16_POLY, 16);

@@ -35,14 +35,18 @@ inline uint32_t crc_bits(const uint8_t* data, uint32_t nbits, uint32_t poly, uin
 // `src[p]` lists the d-stream address of the p-th NON-NULL entry of the circular buffer w (in buffer
 // order), `start[rv]` is the position in that list of the first non-NULL entry at or after k0(rv).
 // Transmitted bit e of a code block is d[src[(start[rv] + e) % (3K+12)]].
+// Limited soft buffer (TS 36.212 5.1.4.1.2, which ETSI TS 103 636-3 6.1.5.3 follows; the reference leaves it as a ToDo,
+// pdc_enc.cpp:122-123, README.md:180): the circular buffer ends at N_cb = min(floor(N_IR / C), K_w) instead of K_w.  The
+// first Nc entries of src[] are then the usable ones, k0 and the wrap-around follow N_cb.
 struct rm_table_t {
     uint32_t K, N;  // N = 3K+12
+    uint32_t Nc;    // non-NULL entries inside the first N_cb positions of the circular buffer (= N without limitation)
     std::vector<uint16_t> src;
     std::vector<uint16_t> pos;  // inverse of src: d-stream address -> position in the non-NULL list
     uint32_t start[4];
 };
 
-inline void build_rm_table(uint32_t K, rm_table_t& t) {
+inline void build_rm_table(uint32_t K, rm_table_t& t, uint32_t N_cb_limit = 0) {
     static const uint8_t P[32] = {0, 16, 8, 24, 4, 20, 12, 28, 2, 18, 10, 26, 6, 22, 14, 30,
                                   1, 17, 9, 25, 5, 21, 13, 29, 3, 19, 11, 27, 7, 23, 15, 31};
     const uint32_t D = K + 4, R = (D + 31) / 32, Kp = 32 * R, ND = Kp - D, Kw = 3 * Kp;
@@ -70,10 +74,12 @@ inline void build_rm_table(uint32_t K, rm_table_t& t) {
     nn_before[Kw] = (uint32_t)t.src.size();
     t.pos.assign(t.N, 0);
     for (uint32_t p = 0; p < t.N; ++p) t.pos[t.src[p]] = (uint16_t)p;
+    // N_cb = K_w unless the soft buffer is limited (the reference: always K_w, README.md:180)
+    const uint32_t N_cb = (N_cb_limit && N_cb_limit < Kw) ? N_cb_limit : Kw;
+    t.Nc = nn_before[N_cb];
     for (uint32_t rv = 0; rv < 4; ++rv) {
-        // N_cb = K_w (no soft buffer limitation, reference README.md:180)
-        const uint32_t k0 = R * (2 * ((Kw + 8 * R - 1) / (8 * R)) * rv + 2);
-        t.start[rv] = nn_before[k0 % Kw] % t.N;
+        const uint32_t k0 = R * (2 * ((N_cb + 8 * R - 1) / (8 * R)) * rv + 2);
+        t.start[rv] = nn_before[k0 % N_cb] % t.Nc;
     }
 }
 

@@ -36,6 +36,7 @@ struct cb_desc_t {
     uint32_t xp_off;           // offset of the per-window x^n mod g table in the table arena
     uint32_t saved_off;        // byte offset inside the packet's saved-bytes area
     uint32_t Linv;             // ceil(2^32 / L): i / L == __umulhi(i, Linv) for every i < 2^32 / L
+    uint32_t Nc;               // circular-buffer entries in use (3K + 12 unless the soft buffer is limited): wrap-around length
 };
 
 namespace tdec {

@@ -64,6 +64,15 @@ typedef struct {
     uint32_t chestim_mode_lr;  /* phy.json chestim_mode_lr_default */
     uint32_t chestim_mode_lr_t_stride; /* phy.json chestim_mode_lr_t_stride_default */
     uint32_t tdec_min_iter, tdec_max_iter; /* 0 = reference defaults 2 / 10 (pdc_enc.cpp:35-36) */
+    /* Limited soft buffer ("channel coding with a limited number of soft bits is not implemented yet", reference
+     * README.md:180; ToDo at lib/src/phy/fec/pdc_enc.cpp:122-123 pointing to ETSI TS 103 636-3 6.1.5.3, which follows
+     * TS 36.212 5.1.4.1.2).  N_soft = soft bits of the receiving radio device (radio_device_class_t::N_soft_min,
+     * radio_device_class.cpp:37-141, or the RD capability IE), M_DL_HARQ = HARQ processes sharing them: a transport
+     * block may use N_IR = N_soft / M_DL_HARQ soft bits, each of its C code blocks a circular buffer of
+     * N_cb = min(floor(N_IR / C), K_w); transmitter (bit selection) and receiver (soft combining) both honour it, and
+     * every redundancy version starts at k0(N_cb).  N_soft = 0: no limitation (N_cb = K_w), the reference's behaviour.
+     * Own activation of a planned feature: DESIGN.md 4b. */
+    uint32_t N_soft, M_DL_HARQ;
 } dnrp_config_t;
 
 /* sp3::get_packet_sizes, lib/src/sections_part3/derivative/packet_sizes.cpp:97-227.

@@ -100,10 +100,18 @@ static uint32_t build_w(uint32_t K, int32_t* w, uint32_t* Rout) {
     return 3 * Kp;
 }
 
+/* Limited soft buffer (TS 36.212 5.1.4.1.2; ETSI TS 103 636-3 6.1.5.3; the reference: ToDo at pdc_enc.cpp:122-123, always
+ * N_cb = K_w): orc_N_cb > 0 ends the circular buffer of the NEXT orc_rm_tx / orc_rm_rx calls at min(orc_N_cb, K_w).  The
+ * PDC chain (fec_chain.c) sets it per transport block from orc_N_IR (= N_soft / M_DL_HARQ, 0 = no limitation) and clears
+ * it again; the PCC never limits. */
+uint32_t orc_N_IR = 0;
+__thread uint32_t orc_N_cb = 0;
+
 /* e[0..E) <- bits selected from d (one bit per byte) with redundancy version rv */
 void orc_rm_tx(const uint8_t* d, uint32_t K, uint32_t E, uint32_t rv, uint8_t* e) {
     static __thread int32_t w[3 * (MAXK + 36)];
     uint32_t R, Kw = build_w(K, w, &R);
+    if (orc_N_cb && orc_N_cb < Kw) Kw = orc_N_cb;
     uint32_t k0 = R * (2 * ((Kw + 8 * R - 1) / (8 * R)) * rv + 2);
     uint32_t k = 0, j = 0;
     while (k < E) {
@@ -117,6 +125,7 @@ void orc_rm_tx(const uint8_t* d, uint32_t K, uint32_t E, uint32_t rv, uint8_t* e
 void orc_rm_rx(const int16_t* e, uint32_t K, uint32_t E, uint32_t rv, int16_t* soft) {
     static __thread int32_t w[3 * (MAXK + 36)];
     uint32_t R, Kw = build_w(K, w, &R);
+    if (orc_N_cb && orc_N_cb < Kw) Kw = orc_N_cb;
     uint32_t k0 = R * (2 * ((Kw + 8 * R - 1) / (8 * R)) * rv + 2);
     uint32_t k = 0, j = 0;
     while (k < E) {

@@ -147,5 +147,10 @@ def unpack_bits(b, n):
     return np.unpackbits(np.asarray(b, dtype=np.uint8))[:n]
 
 
+def set_soft_limit(N_soft, M_DL_HARQ=1):
+    """limited soft buffer of the PDC chain (N_IR = N_soft / M_DL_HARQ per transport block; 0 = none, the reference's behaviour)"""
+    C.c_uint32.in_dll(_L(), "orc_N_IR").value = (N_soft // max(M_DL_HARQ, 1)) if N_soft else 0
+
+
 def set_window_override(L):
     C.c_uint32.in_dll(_L(), "orc_window_override").value = L

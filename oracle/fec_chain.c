@@ -13,6 +13,8 @@ void orc_pack(const uint8_t* bits, uint8_t* bytes, uint32_t nbits);
 void orc_turbo_encode(const uint8_t* c, uint32_t K, uint32_t f1, uint32_t f2, uint8_t* d);
 void orc_rm_tx(const uint8_t* d, uint32_t K, uint32_t E, uint32_t rv, uint8_t* e);
 void orc_rm_rx(const int16_t* e, uint32_t K, uint32_t E, uint32_t rv, int16_t* soft);
+extern uint32_t orc_N_IR;
+extern __thread uint32_t orc_N_cb;
 tdec_t* orc_tdec_alloc(void);
 void orc_tdec_free(tdec_t* t);
 void orc_tdec_new_cb(tdec_t* t, const int16_t* soft, uint32_t K, uint32_t f1, uint32_t f2);
@@ -54,7 +56,9 @@ void orc_pdc_encode(const uint8_t* tb, const orc_seg_t* s, uint32_t Qm, uint32_t
         if (s->C > 1) put_crc(c + rlen, orc_crc(c, rlen, CRC24B, 24), 24);
         orc_turbo_encode(c, K, f1, f2, d);
         uint8_t* ee = n_e <= sizeof(e) ? e : (uint8_t*)malloc(n_e);
+        orc_N_cb = orc_N_IR ? orc_N_IR / s->C : 0;
         orc_rm_tx(d, K, n_e, rv, ee);
+        orc_N_cb = 0;
         for (uint32_t i = 0; i < n_e; ++i) dbits[wp + i] = ee[i] ^ gold[wp + i];
         if (ee != e) free(ee);
         rp += rlen;
@@ -91,7 +95,9 @@ int orc_pdc_decode(int16_t* e, const orc_seg_t* s, uint32_t Qm, uint32_t rv, uin
             if (gold[rp + i]) e[rp + i] = (int16_t)-e[rp + i];
         n_iter[cb] = 0;
         if (!cb_crc[cb]) {
+            orc_N_cb = orc_N_IR ? orc_N_IR / s->C : 0;
             orc_rm_rx(e + rp, K, n_e2, rv, soft + cb * stride);
+            orc_N_cb = 0;
             orc_tdec_new_cb(t, soft + cb * stride, K, f1, f2);
             uint32_t noi = 0;
             int stop = 0;
