@@ -551,9 +551,13 @@ class batch_phy_t {
             std::vector<dnrp_pcc_report_t> pcc(n);
             check(dnrp_rx_pcc_batch(ctx, n, nullptr, nullptr, pcc.data()), "dnrp_rx_pcc_batch");
             stats.windows += n;
+            last_claimed.assign(n, 0);
+            for (uint32_t i = 0; i < n; ++i) last_claimed[i] = sres[i].detected && (pcc[i].plcf_ok[0] || pcc[i].plcf_ok[1]);
             deliver(n, sres, pcc, window_start_64, tpoint, tx_out);
             return tx_out;
         }
+        /// per window of the last process_windows call: a packet was found AND one of its PLCF CRCs passed
+        const std::vector<uint8_t>& get_last_claimed() const { return last_claimed; }
 
         /// The streaming front door: one continuous stream [N_RX][n_samples] at the hardware rate (first sample at
         /// global time stream_start_64) instead of pre-cut windows -- worker_sync_t / sync_chunk_t / baton_t
@@ -814,6 +818,7 @@ class batch_phy_t {
         stats_t stats;
         bool comm_ready{false};
         uint32_t search_length{0};
+        std::vector<uint8_t> last_claimed;
         static void check(int rc, const char* what) {
             if (rc != DNRP_OK) throw std::runtime_error(std::string(what) + ": " + dnrp_last_error_string());
         }
@@ -849,11 +854,32 @@ class multi_beta_phy_t {
             }
             return *phys.back();
         }
-        batch_phy_t& get(uint32_t b) {
-            for (auto& p : phys) if (p->get_packet_sizes().psdef.b == b) return *p;
-            throw std::invalid_argument("no PHY for this beta");
+        /// Another subcarrier scaling factor mu ("mu detection" is future work in the reference: README.md:198, the
+        /// synchronisation assumes the radio device class' mu, sync_chunk.cpp:168-172).  A packet of another mu has another
+        /// STF pattern length at the receiver's sample rate, so the receiver's detector does not fire on it (the lag-L
+        /// autocorrelation of a signal on every 4th subcarrier of a 2L / 4L grid sums to zero) and the beta search cannot
+        /// name it: the windows no PHY has claimed so far (no packet found, or no PLCF CRC passed) are searched again by
+        /// the PHY of that mu.  psdef = the largest geometry of that mu; mu x beta x oversampling = the receiver's.
+        batch_phy_t& add_mu(const sp3::packet_sizes_def_t& psdef_largest_of_mu) {
+            const uint32_t ub = psdef_largest_of_mu.u * psdef_largest_of_mu.b, rate = base.psdef.u * base.psdef.b * base.oversampling;
+            if (psdef_largest_of_mu.u == base.psdef.u || ub == 0 || rate % ub != 0)
+                throw std::invalid_argument("add_mu: another mu with mu x beta dividing mu x beta x oversampling of the receiver");
+            dnrp_config_t c = base;
+            c.psdef = psdef_largest_of_mu;
+            c.oversampling = rate / ub;
+            phys.emplace_back(std::make_unique<batch_phy_t>(c, device, nof_process_rx));
+            if (phys.back()->get_rx_stride() > phys[0]->get_rx_stride()) {
+                phys.pop_back();
+                throw std::invalid_argument("add_mu: the packet must fit the windows of the receiver");
+            }
+            return *phys.back();
         }
-        /// n host windows [n][N_RX][rx_stride of the largest beta]; returns all TX descriptors handed back
+        batch_phy_t& get(uint32_t b) { return get(base.psdef.u, b); }
+        batch_phy_t& get(uint32_t u, uint32_t b) {
+            for (auto& p : phys) if (p->get_packet_sizes().psdef.u == u && p->get_packet_sizes().psdef.b == b) return *p;
+            throw std::invalid_argument("no PHY for this mu / beta");
+        }
+        /// n host windows [n][N_RX][rx_stride of the receiver]; returns all TX descriptors handed back
         machigh_phy_t::tx_descriptor_vec_t process_windows(uint32_t n, const cf_t* windows, const int64_t* window_start_64,
                                                            upper::tpoint_t& tpoint) {
             if (!windows) throw std::invalid_argument("multi_beta_phy_t needs the windows in host memory");
@@ -862,37 +888,48 @@ class multi_beta_phy_t {
             std::vector<int32_t> cfo;
             phys[0]->read_sync_fdomain(n, beta, cfo);
             last_beta = beta;
+            last_mu.assign(n, 0);
+            std::vector<uint8_t> claimed = phys[0]->get_last_claimed();
+            for (uint32_t i = 0; i < n; ++i) if (claimed[i]) last_mu[i] = base.psdef.u;
             const size_t wlen = (size_t)phys[0]->get_N_RX() * phys[0]->get_rx_stride();
             for (size_t k = 1; k < phys.size(); ++k) {
                 batch_phy_t& P = *phys[k];
-                const uint32_t b = P.get_packet_sizes().psdef.b;
+                const uint32_t u = P.get_packet_sizes().psdef.u, b = P.get_packet_sizes().psdef.b;
+                const bool same_mu = u == base.psdef.u;
                 const size_t plen = (size_t)P.get_N_RX() * P.get_rx_stride();
                 std::vector<cf_t> sub;
                 std::vector<int64_t> start;
+                std::vector<uint32_t> from;
                 for (uint32_t i = 0; i < n; ++i) {
-                    if (beta[i] != b) continue;
-                    // antenna by antenna: the smaller beta's window may be shorter than the receiver's
+                    if (same_mu ? beta[i] != b : claimed[i] != 0) continue;
+                    // antenna by antenna: this PHY's window may be shorter than the receiver's
                     for (uint32_t a = 0; a < P.get_N_RX(); ++a) {
                         const cf_t* src = windows + (size_t)i * wlen + (size_t)a * phys[0]->get_rx_stride();
                         sub.insert(sub.end(), src, src + P.get_rx_stride());
                     }
                     start.push_back(window_start_64 ? window_start_64[i] : 0);
+                    from.push_back(i);
                 }
                 const uint32_t m = (uint32_t)(sub.size() / std::max<size_t>(plen, 1));
                 if (m == 0) continue;
                 machigh_phy_t::tx_descriptor_vec_t t = P.process_windows(m, sub.data(), start.data(), tpoint);
                 for (const auto& d : t) tx.push_back(d);
+                const std::vector<uint8_t>& c = P.get_last_claimed();
+                for (uint32_t z = 0; z < m; ++z)
+                    if (c[z]) { claimed[from[z]] = 1; last_mu[from[z]] = u; if (!same_mu) last_beta[from[z]] = b; }
             }
             return tx;
         }
         const std::vector<uint32_t>& get_last_beta() const { return last_beta; }
+        /// mu of the PHY that claimed the window (0: none did)
+        const std::vector<uint32_t>& get_last_mu() const { return last_mu; }
 
     private:
         int device;
         uint32_t nof_process_rx;
         dnrp_config_t base;
         std::vector<std::unique_ptr<batch_phy_t>> phys;
-        std::vector<uint32_t> last_beta;
+        std::vector<uint32_t> last_beta, last_mu;
 };
 
 }  // namespace phy

@@ -10,6 +10,7 @@
 #include <cstdlib>
 #include <map>
 #include <random>
+#include <string>
 
 #include "dnrp_host.hpp"
 
@@ -27,8 +28,9 @@ struct firmware_t final : public upper::tpoint_t {
         const uint32_t tag = ((uint32_t)plcf[2] << 8) | plcf[3];
         auto it = sent.find(tag);
         if (it == sent.end()) return phy::maclow_phy_t();
-        // the geometry: beta from the synchronisation, MCS from the PLCF
+        // the geometry: mu and beta from the synchronisation, MCS from the PLCF
         sp3::packet_sizes_def_t psdef = it->second.psdef;
+        psdef.u = in.sync_report.u;
         psdef.b = in.sync_report.b;
         psdef.mcs_index = (uint32_t)(plcf[4] & 0x07);
         if (std::memcmp(&psdef, &it->second.psdef, sizeof(psdef)) != 0) { ++n_mismatch; return phy::maclow_phy_t(); }
@@ -54,6 +56,9 @@ struct firmware_t final : public upper::tpoint_t {
 
 int main(int argc, char** argv) {
     const uint32_t n = argc > 1 ? (uint32_t)std::atoi(argv[1]) : 24;
+    // "beta": a mu 1 / beta 4 receiver and packets of beta 4, 2, 1;  "mu": a mu 2 / beta 2 receiver and packets of
+    // (mu, beta) = (2, 2), (2, 1), (1, 4), (1, 2) -- mu detection is future work in the reference (README.md:198)
+    const bool with_mu = argc > 2 && std::string(argv[2]) == "mu";
     int ndev = 0;
     if (cudaGetDeviceCount(&ndev) != cudaSuccess || ndev == 0) {
         std::fprintf(stderr, "multi_beta_firmware: no CUDA device (this library has no CPU fallback)\n");
@@ -61,33 +66,40 @@ int main(int argc, char** argv) {
     }
     int fails = 0;
     try {
-        const uint32_t betas[3] = {4, 2, 1};
+        struct num_t { uint32_t u, b; };
+        const std::vector<num_t> nums = with_mu ? std::vector<num_t>{{2, 2}, {2, 1}, {1, 4}, {1, 2}}
+                                                : std::vector<num_t>{{1, 4}, {1, 2}, {1, 1}};
+        const uint32_t NN = (uint32_t)nums.size(), rate = nums[0].u * nums[0].b;
         dnrp_config_t cfg{};
-        cfg.psdef = {1, 4, 1, 1, 0, 3, 2048};   // the receiver: mu 1, beta 4, one slot, 16-QAM 1/2
+        // the receiver: windows for two slots (the other numerologies' search margins are longer than its own), 16-QAM 1/2
+        cfg.psdef = {nums[0].u, nums[0].b, 1, 2, 0, 3, 2048};
         cfg.N_RX = 1; cfg.oversampling = 1; cfg.resample_L = 1; cfg.resample_M = 1;
         cfg.max_batch = n; cfg.network_id = NET; cfg.plcf_type = 1;
         cfg.chestim_mode_lr = 1; cfg.chestim_mode_lr_t_stride = 2;
         phy::multi_beta_phy_t rx(cfg, 0, n);
-        rx.add_beta({1, 2, 1, 1, 0, 3, 2048});
-        rx.add_beta({1, 1, 1, 1, 0, 3, 2048});
-        const uint32_t rx_stride = rx.get(4).get_rx_stride();
-        firmware_t fw(rx.get(4).get_packet_sizes(), n);
+        for (uint32_t k = 1; k < NN; ++k) {
+            const sp3::packet_sizes_def_t d{nums[k].u, nums[k].b, 1, 1, 0, 3, 2048};
+            if (nums[k].u == nums[0].u) rx.add_beta(d); else rx.add_mu(d);
+        }
+        const uint32_t rx_stride = rx.get(nums[0].u, nums[0].b).get_rx_stride();
+        firmware_t fw(rx.get(nums[0].u, nums[0].b).get_packet_sizes(), n);
         std::mt19937 rng(17);
         std::vector<cf_t> win((size_t)n * rx_stride);
         std::normal_distribution<float> g(0.f, 0.03f);
         for (auto& v : win) { v.re = g(rng); v.im = g(rng); }
         std::vector<int64_t> start(n);
-        std::vector<uint32_t> beta_sent(n);
-        // transmitters: one PHY per beta at the common rate (beta x oversampling = 4)
-        for (uint32_t k = 0; k < 3; ++k) {
-            const uint32_t b = betas[k];
+        std::vector<uint32_t> beta_sent(n), mu_sent(n);
+        // transmitters: one PHY per numerology at the common rate (mu x beta x oversampling constant)
+        for (uint32_t k = 0; k < NN; ++k) {
+            const uint32_t b = nums[k].b;
             dnrp_config_t tc = cfg;
-            tc.psdef.b = b; tc.oversampling = 4 / b;
+            tc.psdef = {nums[k].u, b, 1, 1, 0, 3, 2048};   // packets of one slot
+            tc.oversampling = rate / (nums[k].u * b);
             phy::batch_phy_t txp(tc, 0, n);
             std::vector<phy::tx_descriptor_t> descs;
             std::vector<uint32_t> where;
             const phy::tx_meta_t tx_meta{false, 1.0f, 0.0f, 0.0f, 5};
-            for (uint32_t i = k; i < n; i += 3) {          // windows i = k, k + 3, ... carry beta b
+            for (uint32_t i = k; i < n; i += NN) {         // windows i = k, k + NN, ... carry this numerology
                 firmware_t::sent_t s{};
                 s.psdef = tc.psdef;
                 s.psdef.mcs_index = 1 + (i % 3);
@@ -108,6 +120,7 @@ int main(int argc, char** argv) {
                 descs.emplace_back(*hp, 0, tx_meta, radio::buffer_tx_meta_t{});
                 where.push_back(i);
                 beta_sent[i] = b;
+                mu_sent[i] = nums[k].u;
             }
             const uint32_t tx_stride = txp.get_tx_stride();
             std::vector<cf_t> iq((size_t)descs.size() * tx_stride);
@@ -120,15 +133,16 @@ int main(int argc, char** argv) {
                 start[where[z]] = 1000000 * (int64_t)(where[z] + 1);
             }
         }
-        // add the smaller betas' geometries (three MCS each) to the receiving PHYs
-        for (uint32_t k = 0; k < 3; ++k)
-            for (uint32_t mcs = 1; mcs <= 3; ++mcs) rx.get(betas[k]).add_plan({1, betas[k], 1, 1, 0, mcs, 2048});
+        // add the other geometries (three MCS each) to the receiving PHYs
+        for (uint32_t k = 0; k < NN; ++k)
+            for (uint32_t mcs = 1; mcs <= 3; ++mcs) rx.get(nums[k].u, nums[k].b).add_plan({nums[k].u, nums[k].b, 1, 1, 0, mcs, 2048});
         rx.process_windows(n, win.data(), start.data(), fw);
-        uint32_t beta_wrong = 0;
+        uint32_t beta_wrong = 0, mu_wrong = 0;
         for (uint32_t i = 0; i < n; ++i) beta_wrong += rx.get_last_beta()[i] != beta_sent[i];
-        if (beta_wrong || fw.n_work_pdc != n || fw.n_work_pdc_error || fw.n_mismatch) ++fails;
-        std::printf("{\"n\": %u, \"beta_wrong\": %u, \"work_pcc\": %u, \"work_pdc\": %u, \"work_pdc_error\": %u, \"mismatch\": %u, "
-                    "\"fails\": %d}\n", n, beta_wrong, fw.n_work_pcc, fw.n_work_pdc, fw.n_work_pdc_error, fw.n_mismatch, fails);
+        for (uint32_t i = 0; i < n; ++i) mu_wrong += rx.get_last_mu()[i] != mu_sent[i];
+        if (beta_wrong || mu_wrong || fw.n_work_pdc != n || fw.n_work_pdc_error || fw.n_mismatch) ++fails;
+        std::printf("{\"n\": %u, \"beta_wrong\": %u, \"mu_wrong\": %u, \"work_pcc\": %u, \"work_pdc\": %u, \"work_pdc_error\": %u, \"mismatch\": %u, "
+                    "\"fails\": %d}\n", n, beta_wrong, mu_wrong, fw.n_work_pcc, fw.n_work_pdc, fw.n_work_pdc_error, fw.n_mismatch, fails);
     } catch (const std::exception& e) {
         std::fprintf(stderr, "multi_beta_firmware: %s\n", e.what());
         return 2;

@@ -136,3 +136,16 @@ def test_one_receiver_for_packets_of_beta_4_2_and_1(tmp_path):
     assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
     out = json.loads(r.stdout.strip().splitlines()[-1])
     assert out["fails"] == 0 and out["beta_wrong"] == 0 and out["work_pdc"] == 24 and out["mismatch"] == 0
+
+
+@pytest.mark.gpu
+def test_one_receiver_for_packets_of_two_mu(tmp_path):
+    """multi_beta_phy_t::add_mu: a receiver configured for mu = 2 / beta = 2 gets packets of (mu, beta) = (2, 2), (2, 1),
+    (1, 4) and (1, 2) at its sample rate ("mu detection" is future work in the reference, README.md:198): the windows its
+    own detector and beta search do not claim are searched by the PHYs of the other mu; the firmware reads mu and beta
+    from sync_report and every transport block arrives"""
+    exe = build_program(tmp_path, "multi_beta_firmware")
+    r = subprocess.run([exe, "24", "mu"], capture_output=True, text=True, timeout=600)
+    assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
+    out = json.loads(r.stdout.strip().splitlines()[-1])
+    assert out["fails"] == 0 and out["mu_wrong"] == 0 and out["beta_wrong"] == 0 and out["work_pdc"] == 24
