@@ -126,6 +126,23 @@ def run_cell(product, phy, cell, n_packets, seed, plcf_type=1):
     return row
 
 
+def mmie_result_files(cells, mat, n_packets, mmie_list):
+    """tfw_loopback_mmie::save_all_results_to_file (tfw_loopback_mmie.cpp:148-171): one file per MMIE index of the
+    reference's mmie_pool_tx_t that derives from serdes::testing_t"""
+    files = {}
+    for m in mmie_list:
+        rows = [i for i, c in enumerate(cells) if c[0] == m]
+        per = lambda k: [float(1.0 - mat[i, COUNTERS.index(k)] / max(mat[i, 0], 1)) for i in rows]
+        files["rx_loopback_mmie_%04d" % m] = {
+            "experiment_range": {"snr_vec": [float(cells[i][1]) for i in rows], "nof_experiment_per_snr": int(n_packets)},
+            "parameter": {"mmie_idx": int(m)},
+            "result": {
+                "snr_max_vec": [mat[i, SUMMED + 1] / 1000.0 if mat[i, SUMMED + 1] > -BIG else -100.0e6 for i in rows],
+                "snr_min_vec": [mat[i, SUMMED] / 1000.0 if mat[i, SUMMED] < BIG else 100.0e6 for i in rows],
+                "PER_pcc_crc": per("pcc_crc"), "PER_pcc_crc_and_plcf": per("pcc_crc_and_plcf"), "PER_pdc_crc": per("pdc_crc")}}
+    return files
+
+
 def ratio_cells(ratio_list, snr_list):
     """tfw_loopback_ratio: parameter = power ratio of the interferer in dB (outside), SNR inside"""
     return [(ratio, snr) for ratio in ratio_list for snr in snr_list]
@@ -222,9 +239,14 @@ def main():
     ap.add_argument("--packets", type=int, default=1000, help="packets per (mode, MCS, SNR) cell")
     ap.add_argument("--n-rx", type=int, default=1)
     ap.add_argument("--out", default="", help="directory for the rx_loopback_MCS_xxxx JSON files (rank 0)")
-    ap.add_argument("--experiment", choices=("snr", "ratio"), default="snr",
+    ap.add_argument("--experiment", choices=("snr", "ratio", "mmie"), default="snr",
                     help="snr: tfw_loopback_snr (PER over MCS and SNR); ratio: tfw_loopback_ratio (a strong packet right in "
-                         "front of the wanted one, PER over power ratio and SNR)")
+                         "front of the wanted one, PER over power ratio and SNR); mmie: tfw_loopback_mmie (PER over SNR per "
+                         "MMIE index -- the reference fills the MAC PDU with random bytes whatever the MMIE, "
+                         "tfw_loopback_mmie.cpp:104-113, so a cell is an SNR cell at the first MCS)")
+    ap.add_argument("--mmie", type=int, nargs="+", default=[3],
+                    help="--experiment mmie: indices into the reference's mmie_pool_tx_t (3 = cluster beacon message, the "
+                         "only entry that derives from serdes::testing_t, mmie_pool_tx.cpp:47-70)")
     ap.add_argument("--ratio", type=int, nargs="+", default=[30, 40, 50, 60, 70, 80], help="--experiment ratio: dB")
     args = ap.parse_args()
 
@@ -245,7 +267,10 @@ def main():
     product = load_product()
     snr_list = [float(v) for v in np.arange(args.snr[0], args.snr[1] + 0.5 * args.snr[2], args.snr[2])]
     ratio = args.experiment == "ratio"
+    mmie = args.experiment == "mmie"
     cells = ratio_cells(args.ratio, snr_list) if ratio else sweep_cells(args.tm, args.mcs, snr_list)
+    if mmie:
+        cells = [(m, snr) for m in args.mmie for snr in snr_list]
     mine = cells_of_rank(len(cells), rank, world)
     mat = neutral_matrix(len(cells))
     t_start = time.perf_counter()
@@ -258,7 +283,7 @@ def main():
         phy.close()
         mine = []
     for ci in mine:
-        tm, mcs, _ = cells[ci]
+        tm, mcs, snr_c = (args.tm[0], args.mcs[0], cells[ci][1]) if mmie else cells[ci]
         if (tm, mcs) not in phys:      # one context per packet geometry, reused over the SNR points
             for p in phys.values():
                 p.close()
@@ -266,7 +291,7 @@ def main():
             psdef = (args.mu, args.beta, 1, args.packet_length, tm, mcs, 2048 if args.beta < 4 else 6144)
             phys[(tm, mcs)] = product.Phy(psdef, max_batch=args.packets, N_RX=args.n_rx, network_id=123456789,
                                           plcf_type=1, device=local)
-        mat[ci] = run_cell(product, phys[(tm, mcs)], cells[ci], args.packets, seed=0x5EED0000 + ci)
+        mat[ci] = run_cell(product, phys[(tm, mcs)], (tm, mcs, snr_c), args.packets, seed=0x5EED0000 + ci)
     for p in phys.values():
         p.close()
     torch.cuda.synchronize()
@@ -276,6 +301,7 @@ def main():
     dt = time.perf_counter() - t_start
     if rank == 0:
         files = (ratio_result_files(cells, mat, args.packets, args.ratio, snr_list) if ratio else
+                 mmie_result_files(cells, mat, args.packets, args.mmie) if mmie else
                  result_files(cells, mat, args.packets, args.tm, args.mcs, snr_list))
         if args.out:
             os.makedirs(args.out, exist_ok=True)

@@ -128,3 +128,29 @@ def test_ratio_experiment_on_one_gpu(tmp_path):
     assert j0["experiment_range"]["snr_vec"] == [5.0, 15.0] and j0["parameter"]["ratio"] == 0
     assert j0["result"]["PER_pdc_crc"][1] <= 0.05 and j0["result"]["PER_pcc_crc"][1] <= -0.9
     assert j40["result"]["PER_pdc_crc"][1] >= j0["result"]["PER_pdc_crc"][1] - 1e-9
+
+
+def test_mmie_result_files_follow_the_reference_layout():
+    import per_sweep as ps
+    snr = [0.0, 5.0, 10.0]
+    cells = [(m, s) for m in (3, 7) for s in snr]
+    mat = np.stack([_fake_row(ps, ci, 100) for ci in range(len(cells))])
+    files = ps.mmie_result_files(cells, mat, 100, [3, 7])
+    assert sorted(files) == ["rx_loopback_mmie_0003", "rx_loopback_mmie_0007"]          # tfw_loopback_mmie.cpp:152-153
+    j = files["rx_loopback_mmie_0003"]
+    assert j["experiment_range"] == {"snr_vec": snr, "nof_experiment_per_snr": 100} and j["parameter"] == {"mmie_idx": 3}
+    assert list(j["result"]) == ["snr_max_vec", "snr_min_vec", "PER_pcc_crc", "PER_pcc_crc_and_plcf", "PER_pdc_crc"]
+    json.dumps(files)
+
+
+@pytest.mark.gpu
+def test_mmie_experiment_on_one_gpu(tmp_path):
+    """tfw_loopback_mmie: PER over SNR per MMIE index (random MAC PDU bytes, like the reference's set_mac_pdu)"""
+    r = subprocess.run([sys.executable, os.path.join(ROOT, "per_sweep.py"), "--experiment", "mmie", "--beta", "1", "--mcs", "2",
+                        "--snr", "-4", "16", "10", "--packets", "60", "--out", str(tmp_path)],
+                       capture_output=True, text=True, timeout=900)
+    assert r.returncode == 0, r.stderr[-2000:]
+    s = json.loads(r.stdout.strip().splitlines()[-1])
+    assert s["cells"] == 3 and s["tb_mismatch_after_crc_ok"] == 0 and s["files"] == ["rx_loopback_mmie_0003"]
+    j = json.load(open(tmp_path / "rx_loopback_mmie_0003.json"))
+    assert j["result"]["PER_pdc_crc"][0] > 0.5 and j["result"]["PER_pdc_crc"][-1] < 0.05
