@@ -2,6 +2,7 @@
 # test suite, bench both arms and the other workloads, ncu launch list, ncu --set full of the receive chain (10 000 packets,
 # warm repetition; the detection kernels carry the tracking branch now)
 set -x
+python -c "import __graft_entry__ as g; g.smoke(); print(\"smoke ok\")" > gpurun_out/r02w_smoke.log 2>&1; tail -1 gpurun_out/r02w_smoke.log
 python -m pytest tests -m gpu -x -q > gpurun_out/r02w_gputests.log 2>&1; tail -2 gpurun_out/r02w_gputests.log
 python bench.py > gpurun_out/r02w_bench_c3_tdl_n1.json 2> gpurun_out/r02w_bench_c3.err; tail -2 gpurun_out/r02w_bench_c3.err
 python bench.py --impl reference --steps 3 --warmup 1 > gpurun_out/r02w_bench_reference_arm.json 2> gpurun_out/r02w_ref.err; tail -2 gpurun_out/r02w_ref.err
