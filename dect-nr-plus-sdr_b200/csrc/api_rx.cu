@@ -410,8 +410,15 @@ static int rx_batch_impl(dnrp_ctx_t* c, uint32_t n, const void* iq_in, float sc1
         // 15.7 -> 14.6 ms per 10 000 C2 windows.)
         static const uint32_t wc[] = {2, 2, 3, 3, 4, 4, 4, 4, 4, 4, 4, 4, 3, 3, 2, 2}, ws[] = {2, 3, 4, 4, 4, 3, 2},
                               w6[] = {2, 3, 4, 4, 3, 2}, w3[] = {1, 1, 1}, w1[] = {1};
-        const uint32_t* w = n >= 8192 ? (sc16 ? ws : wc) : (n >= 2048 ? w6 : (n >= 256 ? w3 : w1));
-        uint32_t nw = n >= 8192 ? (sc16 ? 7 : 16) : (n >= 2048 ? 6 : (n >= 256 ? 3 : 1));
+        // (r02w: a call that is bound by its copy -- long windows of several antennas, the north-star workload moves
+        // 1.7 GB per 4000 windows -- ends with the computation of its last chunk: ten chunks with a long taper took
+        // 32.72 -> 31.86 ms there; with short windows (C2, 0.24 GB) the 0.19 ms per chunk weigh more: 6.28 -> 6.76 ms,
+        // so the taper is for calls of 768 MiB and more only.  profiles/tools/e2e_chunks.sh)
+        static const uint32_t w10[] = {1, 2, 3, 4, 4, 4, 3, 2, 1, 1};
+        const uint64_t call_bytes = (uint64_t)n * c->dims.N_RX * c->rx_stride * (sc16 ? 4u : 8u);
+        const bool long_copy = n >= 2048 && n < 8192 && call_bytes >= (768ull << 20);
+        const uint32_t* w = long_copy ? w10 : n >= 8192 ? (sc16 ? ws : wc) : (n >= 2048 ? w6 : (n >= 256 ? w3 : w1));
+        uint32_t nw = long_copy ? 10 : n >= 8192 ? (sc16 ? 7 : 16) : (n >= 2048 ? 6 : (n >= 256 ? 3 : 1));
         const char* env_chunks = std::getenv("DNRP_RX_CHUNKS");   // tuning knobs: that many equal chunks, or weights
         const char* env_w = std::getenv("DNRP_RX_WEIGHTS");       // "3,4,5,..."
         std::vector<uint32_t> eq;

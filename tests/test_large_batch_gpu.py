@@ -58,3 +58,45 @@ def test_10k_packets_at_the_waterfall(product, fmt):
         if o_ok:
             assert np.array_equal(tb_out[i], o_tb)
     phy.close()
+
+
+def test_chunk_schedules_give_identical_results(product, monkeypatch):
+    """the pipelined chunk schedules of dnrp_rx_batch_sc16 change when a stage runs, not what it computes: 2100 windows of
+    the north-star geometry (four antennas, 0.9 GB: the ten-chunk schedule with the long taper) against the same call in
+    one chunk and in six -- sync results, PCC reports, CRC flags, transport blocks and LLRs bit for bit"""
+    cfg, N_RX = CONFIGS["C3_b16_txdiv4_mcs7"], 4
+    ps = spec.get_packet_sizes(*cfg)
+    n = 2100
+    phy = product.Phy(cfg, max_batch=n, N_RX=N_RX, network_id=NET, plcf_type=1)
+    assert n * N_RX * phy.rx_stride() * 4 >= (768 << 20)
+    rng = np.random.default_rng(5)
+    tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
+    plcf = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    stf = ps["N_samples_STF"]
+    t0 = rng.integers(2 * 16 * cfg[1], 2 * stf - 4, n).astype(np.uint32)
+    snr = rng.uniform(14.0, 24.0, n).astype(np.float32)
+    phy.tx(plcf, tb, fetch=False)
+    win = phy.channel(n, snr_dB=snr, t0=t0, mode=1, seed=99, fetch=True)   # flat Rayleigh per antenna pair
+    gain = np.float32(0.1 / np.sqrt(np.mean(np.abs(win[:16]) ** 2)) * 32768.0)
+    w16 = np.empty(win.shape + (2,), dtype=np.int16)
+    for i0 in range(0, n, 100):
+        v = win[i0:i0 + 100].view(np.float32).reshape(-1, N_RX, win.shape[2], 2) * gain
+        w16[i0:i0 + 100] = np.clip(np.rint(v), -32768, 32767).astype(np.int16)
+    del win
+    out = {}
+    for name, env in (("taper10", None), ("one", "1"), ("six", "6")):
+        if env is None:
+            monkeypatch.delenv("DNRP_RX_CHUNKS", raising=False)
+        else:
+            monkeypatch.setenv("DNRP_RX_CHUNKS", env)
+        sres, pcc, ok, tb_out, pdc = phy.rx(w16, sc16_scale=float(1.0 / gain))
+        out[name] = (sres.copy(), pcc.copy(), ok.copy(), tb_out.copy(), phy.tap(product.TAP_LLR_PDC, n).copy())
+    ref = out["one"]
+    assert 0.05 < 1.0 - ref[2].mean() < 0.95 and np.array_equal(ref[3][ref[2]], tb[ref[2]])
+    for name in ("taper10", "six"):
+        o = out[name]
+        for k in (0, 1):     # field by field: the records carry padding bytes
+            for f in ref[k].dtype.names:
+                assert np.array_equal(o[k][f], ref[k][f]), (name, k, f)
+        assert np.array_equal(o[2], ref[2]) and np.array_equal(o[3][o[2]], ref[3][ref[2]]) and np.array_equal(o[4], ref[4]), name
+    phy.close()
