@@ -115,16 +115,17 @@ def _decode(phy, win, t0, n):
     return pcc, ok, tb
 
 
-@pytest.mark.parametrize("name,cfg,N_RX,step_turns", [
-    ("txdiv4_64qam_mode_lr", (1, 2, 1, 4, 5, 6, 2048), 2, 0.2),
-    ("siso_64qam_mode_lr", (1, 4, 1, 2, 0, 6, 2048), 1, 0.22),
-    ("sm_2x2_16qam", (1, 2, 1, 4, 2, 4, 2048), 2, 0.2),
+@pytest.mark.parametrize("name,cfg,N_RX,step_turns,lr", [
+    ("txdiv4_64qam_mode_lr", (1, 2, 1, 4, 5, 6, 2048), 2, 0.2, True),
+    ("siso_64qam_mode_lr", (1, 4, 1, 2, 0, 6, 2048), 1, 0.22, True),
+    ("sm_2x2_16qam", (1, 2, 1, 4, 2, 4, 2048), 2, 0.2, True),
+    ("txdiv2_16qam_mode_l", (1, 2, 1, 3, 1, 4, 2048), 2, 0.12, False),     # mode l holds the last DRS estimate: nothing follows the drift
 ])
-def test_frequency_step_decodes_only_with_tracking(product, name, cfg, N_RX, step_turns):
+def test_frequency_step_decodes_only_with_tracking(product, name, cfg, N_RX, step_turns, lr):
     ps = spec.get_packet_sizes(*cfg)
     n, t0 = 8, 5
     case = dict(cfg=cfg, N_RX=N_RX, snr_db=33.0, t0=t0)
-    phy = product.Phy(cfg, max_batch=n, N_RX=N_RX, network_id=NET, plcf_type=1)
+    phy = product.Phy(cfg, max_batch=n, N_RX=N_RX, network_id=NET, plcf_type=1, chestim_mode_lr=lr)
     rng = np.random.default_rng(sum(map(ord, name)))
     win, tbs, plcfs = make_windows(ps, case, n, phy.rx_stride(), rng, 1)
     N, cp, stf = dims_of(ps)
@@ -140,7 +141,7 @@ def test_frequency_step_decodes_only_with_tracking(product, name, cfg, N_RX, ste
     phy.rx_set_tracking(False, False)
     _, ok_off, _ = _decode(phy, w, t0, n)
     assert ok_on.all() and np.array_equal(tb_on, tbs), (name, ok_on)
-    assert not ok_off.any(), (name, ok_off)
+    assert ok_off.sum() <= 1, (name, ok_off)
     phy.close()
 
 
@@ -161,4 +162,21 @@ def test_clock_offset_decodes_only_with_tracking(product):
     _, ok_off, _ = _decode(phy, w, t0, n)
     assert ok_on.all() and np.array_equal(tb_on, tbs), (ok_on, est)
     assert ok_off.sum() <= 1, ok_off
+    phy.close()
+
+
+def test_one_drs_occurrence_leaves_the_packet_alone(product):
+    """a packet of one subslot has a single DRS symbol: nothing to compare, the stage reports (0, 0) and changes nothing"""
+    cfg, N_RX = (1, 2, 0, 1, 0, 2, 2048), 1
+    ps = spec.get_packet_sizes(*cfg)
+    n, t0 = 4, 3
+    phy = product.Phy(cfg, max_batch=n, N_RX=N_RX, network_id=NET, plcf_type=1)
+    rng = np.random.default_rng(9)
+    win, tbs, plcfs = make_windows(ps, dict(cfg=cfg, N_RX=N_RX, snr_db=25.0, t0=t0), n, phy.rx_stride(), rng, 1)
+    _, ok0, tb0 = _decode(phy, win, t0, n)
+    llr0 = phy.tap(product.TAP_LLR_PDC, n).copy()
+    phy.rx_set_tracking(True, True)
+    _, ok1, tb1 = _decode(phy, win, t0, n)
+    assert np.array_equal(phy.rx_tracking_read(n), np.zeros((n, 2), dtype=np.float32))
+    assert ok0.all() and ok1.all() and np.array_equal(tb1, tbs) and np.array_equal(phy.tap(product.TAP_LLR_PDC, n), llr0)
     phy.close()
