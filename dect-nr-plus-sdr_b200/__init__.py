@@ -476,7 +476,8 @@ class Phy:
         pipelined against the kernels"""
         n = iq.shape[0]
         sc16 = iq.dtype == np.int16   # [n][N_RX][rx_stride][2] int16 I/Q: dnrp_rx_batch_sc16
-        if sc16:
+        sc8 = iq.dtype == np.int8     # the same as int8: dnrp_rx_batch_sc8 (pass sc16_scale = 1 / 128 or the gain used)
+        if sc16 or sc8:
             assert iq.flags["C_CONTIGUOUS"] and iq.shape[1:] == (self.N_RX, self.rx_stride(), 2)
         else:
             assert iq.dtype == np.complex64 and iq.flags["C_CONTIGUOUS"] and iq.shape[1:] == (self.N_RX, self.rx_stride())
@@ -491,7 +492,9 @@ class Phy:
                 None if sres is None else sres.ctypes.data_as(C.c_void_p),
                 None if pcc is None else pcc.ctypes.data_as(C.c_void_p), _ptr(tb, np.uint8),
                 pdc.ctypes.data_as(C.c_void_p), None)
-        if sc16:
+        if sc8:
+            _check(lib().dnrp_rx_batch_sc8(self._ctx, n, iq.ctypes.data_as(C.c_void_p), C.c_float(sc16_scale), *tail))
+        elif sc16:
             _check(lib().dnrp_rx_batch_sc16(self._ctx, n, iq.ctypes.data_as(C.c_void_p), C.c_float(sc16_scale), *tail))
         else:
             _check(lib().dnrp_rx_batch(self._ctx, n, _ptr(iq, np.complex64), *tail))

@@ -360,8 +360,9 @@ int dnrp_rx_pdc_batch(dnrp_ctx_t* c, uint32_t n, const uint32_t* harq_slot, cons
     return fetch_pdc_reports(c, n, tb_out, out, n_iter);
 }
 
-// iq_in: float2 windows, or (sc16_scale != 0) int16 I/Q pairs that are converted on the device chunk by chunk
-static int rx_batch_impl(dnrp_ctx_t* c, uint32_t n, const void* iq_in, float sc16_scale, uint32_t search_length,
+// iq_in: float2 windows, or (sc16_scale != 0) int16 (sc_bytes = 2) / int8 (sc_bytes = 1) I/Q pairs that are converted on the
+// device chunk by chunk
+static int rx_batch_impl(dnrp_ctx_t* c, uint32_t n, const void* iq_in, float sc16_scale, uint32_t sc_bytes, uint32_t search_length,
                          const uint32_t* harq_slot, const uint8_t* rv, const uint8_t* harq_reset,
                          dnrp_sync_result_t* sync_out, dnrp_pcc_report_t* pcc_out, uint8_t* tb_out,
                          dnrp_pdc_report_t* pdc_out, uint8_t* n_iter) {
@@ -372,8 +373,9 @@ static int rx_batch_impl(dnrp_ctx_t* c, uint32_t n, const void* iq_in, float sc1
     DNRP_CUDA(cudaSetDevice(c->device));
     const phy_dims_t& d = c->dims;
     const bool sc16 = sc16_scale != 0.f;
+    DNRP_REQUIRE(!(sc16 && sc_bytes == 1) || c->rx_stride % 8 == 0, "sc8 ingest needs a window stride that is a multiple of 8");
     if (sc16 && !c->d_iq_sc16.p) {
-        DNRP_REQUIRE(c->rx_stride % 4 == 0, "sc16 ingest needs a window stride that is a multiple of 4");
+        DNRP_REQUIRE(c->rx_stride % 4 == 0, "sc16 / sc8 ingest needs a window stride that is a multiple of 4");
         DNRP_CUDA(c->d_iq_sc16.alloc((size_t)c->B * d.N_RX * c->rx_stride * 2));
     }
     {
@@ -415,7 +417,7 @@ static int rx_batch_impl(dnrp_ctx_t* c, uint32_t n, const void* iq_in, float sc1
         // 32.72 -> 31.86 ms there; with short windows (C2, 0.24 GB) the 0.19 ms per chunk weigh more: 6.28 -> 6.76 ms,
         // so the taper is for calls of 768 MiB and more only.  profiles/tools/e2e_chunks.sh)
         static const uint32_t w10[] = {1, 2, 3, 4, 4, 4, 3, 2, 1, 1};
-        const uint64_t call_bytes = (uint64_t)n * c->dims.N_RX * c->rx_stride * (sc16 ? 4u : 8u);
+        const uint64_t call_bytes = (uint64_t)n * c->dims.N_RX * c->rx_stride * (sc16 ? 2u * sc_bytes : 8u);
         const bool long_copy = n >= 2048 && n < 8192 && call_bytes >= (768ull << 20);
         const uint32_t* w = long_copy ? w10 : n >= 8192 ? (sc16 ? ws : wc) : (n >= 2048 ? w6 : (n >= 256 ? w3 : w1));
         uint32_t nw = long_copy ? 10 : n >= 8192 ? (sc16 ? 7 : 16) : (n >= 2048 ? 6 : (n >= 256 ? 3 : 1));
@@ -465,9 +467,10 @@ static int rx_batch_impl(dnrp_ctx_t* c, uint32_t n, const void* iq_in, float sc1
     const size_t win = (size_t)d.N_RX * c->rx_stride;
     for (uint32_t k = 0; k < n_chunks; ++k) {
         const size_t o = bounds[k], m = bounds[k + 1] - bounds[k];
-        if (sc16)
-            DNRP_CUDA(cudaMemcpyAsync(c->d_iq_sc16.p + o * win * 2, reinterpret_cast<const int16_t*>(iq_in) + o * win * 2,
-                                      m * win * 2 * sizeof(int16_t), cudaMemcpyHostToDevice, c->stream_copy));
+        if (sc16)   // staged at byte offset o * win * 2 * sc_bytes of the int16 staging buffer
+            DNRP_CUDA(cudaMemcpyAsync(reinterpret_cast<uint8_t*>(c->d_iq_sc16.p) + o * win * 2 * sc_bytes,
+                                      reinterpret_cast<const uint8_t*>(iq_in) + o * win * 2 * sc_bytes,
+                                      m * win * 2 * sc_bytes, cudaMemcpyHostToDevice, c->stream_copy));
         else
             DNRP_CUDA(cudaMemcpyAsync(c->d_iq_rx.p + o * win, reinterpret_cast<const float2*>(iq_in) + o * win,
                                       m * win * sizeof(float2), cudaMemcpyHostToDevice, c->stream_copy));
@@ -479,9 +482,12 @@ static int rx_batch_impl(dnrp_ctx_t* c, uint32_t n, const void* iq_in, float sc1
         const uint32_t m = bounds[k + 1] - bounds[k];
         DNRP_CUDA(cudaStreamWaitEvent(c->stream, c->chunk_events[k], 0));
         c->off = (uint32_t)o;
-        if (sc16)
+        if (sc16 && sc_bytes == 2)
             DNRP_LAUNCH(c, -1, launch_sc16_to_cf32(c->d_iq_sc16.p + o * win * 2, c->d_iq_rx.p + o * win, m * win, sc16_scale,
                                                    c->stream));
+        if (sc16 && sc_bytes == 1)
+            DNRP_LAUNCH(c, -1, launch_sc8_to_cf32(reinterpret_cast<const int8_t*>(c->d_iq_sc16.p) + o * win * 2,
+                                                  c->d_iq_rx.p + o * win, m * win, sc16_scale, c->stream));
         rc = run_sync(c, m, search_length, true);
         if (rc == DNRP_OK) rc = run_rx_front(c, m);
         if (rc == DNRP_OK) rc = run_rx_pcc(c, m);
@@ -547,7 +553,7 @@ static int rx_batch_impl(dnrp_ctx_t* c, uint32_t n, const void* iq_in, float sc1
 int dnrp_rx_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, uint32_t search_length, const uint32_t* harq_slot,
                   const uint8_t* rv, const uint8_t* harq_reset, dnrp_sync_result_t* sync_out, dnrp_pcc_report_t* pcc_out,
                   uint8_t* tb_out, dnrp_pdc_report_t* pdc_out, uint8_t* n_iter) {
-    return rx_batch_impl(c, n, iq_in, 0.f, search_length, harq_slot, rv, harq_reset, sync_out, pcc_out, tb_out, pdc_out,
+    return rx_batch_impl(c, n, iq_in, 0.f, 0, search_length, harq_slot, rv, harq_reset, sync_out, pcc_out, tb_out, pdc_out,
                          n_iter);
 }
 
@@ -556,7 +562,16 @@ int dnrp_rx_batch_sc16(dnrp_ctx_t* c, uint32_t n, const int16_t* iq_in, float sc
                        dnrp_sync_result_t* sync_out, dnrp_pcc_report_t* pcc_out, uint8_t* tb_out,
                        dnrp_pdc_report_t* pdc_out, uint8_t* n_iter) {
     DNRP_REQUIRE(scale > 0.f, "scale must be > 0");
-    return rx_batch_impl(c, n, iq_in, scale, search_length, harq_slot, rv, harq_reset, sync_out, pcc_out, tb_out,
+    return rx_batch_impl(c, n, iq_in, scale, 2, search_length, harq_slot, rv, harq_reset, sync_out, pcc_out, tb_out,
+                         pdc_out, n_iter);
+}
+
+int dnrp_rx_batch_sc8(dnrp_ctx_t* c, uint32_t n, const int8_t* iq_in, float scale, uint32_t search_length,
+                      const uint32_t* harq_slot, const uint8_t* rv, const uint8_t* harq_reset,
+                      dnrp_sync_result_t* sync_out, dnrp_pcc_report_t* pcc_out, uint8_t* tb_out,
+                      dnrp_pdc_report_t* pdc_out, uint8_t* n_iter) {
+    DNRP_REQUIRE(scale > 0.f, "scale must be > 0");
+    return rx_batch_impl(c, n, iq_in, scale, 1, search_length, harq_slot, rv, harq_reset, sync_out, pcc_out, tb_out,
                          pdc_out, n_iter);
 }
 

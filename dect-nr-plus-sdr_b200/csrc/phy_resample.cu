@@ -192,6 +192,29 @@ __global__ void __launch_bounds__(256) k_sc16_to_cf32(const int4* __restrict__ i
     }
 }
 
+// ---- sc8 -> cf32 (UHD's 8-bit wire format, otw_format "sc8": half the bytes of sc16 on the radio link and on the host
+// link; the reference's radio layer asks for sc16, hw_usrp.cpp:424,438): 8 complex samples per thread, 16 B in, 64 B out
+__global__ void __launch_bounds__(256) k_sc8_to_cf32(const int4* __restrict__ in, float4* __restrict__ out, size_t n8,
+                                                      float scale) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n8; i += (size_t)gridDim.x * blockDim.x) {
+        const int4 v = __ldg(in + i);
+        const int w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k)
+            out[4 * i + k] = make_float4((float)(int8_t)(w[k] & 0xff) * scale, (float)(int8_t)((w[k] >> 8) & 0xff) * scale,
+                                         (float)(int8_t)((w[k] >> 16) & 0xff) * scale, (float)(int8_t)(w[k] >> 24) * scale);
+    }
+}
+
+cudaError_t launch_sc8_to_cf32(const int8_t* in, float2* out, size_t n_samples, float scale, cudaStream_t st) {
+    if (n_samples == 0) return cudaSuccess;
+    if (n_samples % 8) return cudaErrorInvalidValue;
+    const size_t n8 = n_samples / 8;
+    const unsigned grid = (unsigned)std::min<size_t>((n8 + 255) / 256, 148 * 16);
+    k_sc8_to_cf32<<<grid, 256, 0, st>>>(reinterpret_cast<const int4*>(in), reinterpret_cast<float4*>(out), n8, scale);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_sc16_to_cf32(const int16_t* in, float2* out, size_t n_samples, float scale, cudaStream_t st) {
     if (n_samples == 0) return cudaSuccess;
     if (n_samples % 4) return cudaErrorInvalidValue;

@@ -339,6 +339,15 @@ int dnrp_rx_batch_sc16(dnrp_ctx_t* ctx, uint32_t n, const int16_t* iq_in, float 
                        dnrp_sync_result_t* sync_out, dnrp_pcc_report_t* pcc_out, uint8_t* tb_out,
                        dnrp_pdc_report_t* pdc_out, uint8_t* n_iter);
 
+/* The same for UHD's 8-bit wire format (stream args otw_format "sc8"): iq_in [n][N_RX][dnrp_rx_stride()][2] int8.  NOT what
+ * the reference's radio layer asks its USRP for (hw_usrp.cpp:424,438 set "sc16"): an option for a host link that is the
+ * bottleneck at the price of the 8-bit quantisation (about 38 dB below the signal at 12 dB back-off).
+ * scale = 1/128 corresponds to UHD's conversion.  dnrp_rx_stride() must be a multiple of 8. */
+int dnrp_rx_batch_sc8(dnrp_ctx_t* ctx, uint32_t n, const int8_t* iq_in, float scale, uint32_t search_length,
+                      const uint32_t* harq_slot, const uint8_t* rv, const uint8_t* harq_reset,
+                      dnrp_sync_result_t* sync_out, dnrp_pcc_report_t* pcc_out, uint8_t* tb_out,
+                      dnrp_pdc_report_t* pdc_out, uint8_t* n_iter);
+
 /* test / scope taps (the reference exposes the same data through its JSON export and TCP scope,
  * rx_synced.cpp:363-443): copies an intermediate device buffer of the last call to the host.
  * Returns DNRP_ERR_INVALID if dst_bytes is smaller than the buffer for n packets. */

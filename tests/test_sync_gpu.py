@@ -164,6 +164,40 @@ def test_rx_batch_sc16_equals_cf32_on_dequantised_windows(product):
     phy.close()
 
 
+def test_rx_batch_sc8_equals_cf32_on_dequantised_windows(product):
+    """dnrp_rx_batch_sc8 (UHD's 8-bit wire format, an option beyond the reference's sc16) returns bit for bit what
+    dnrp_rx_batch returns for the float windows int8 * scale; at 14 dB the 8-bit quantisation (12 dB back-off) still leaves
+    the packets decodable"""
+    cfg = CONFIGS["C1_loopback"]
+    ps = spec.get_packet_sizes(*cfg)
+    n = 300
+    phy = product.Phy(cfg, max_batch=n, N_RX=2, network_id=NET)
+    if phy.rx_stride() % 8:
+        pytest.skip("window stride not a multiple of 8")
+    rng = np.random.default_rng(23)
+    tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
+    plcf = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    phy.tx(plcf, tb, fetch=False)
+    stf = ps["N_samples_STF"]
+    t0 = rng.integers(stf // 2, 2 * stf - 8, n)
+    win = phy.channel(n, snr_dB=14.0, t0=t0, mode=0, seed=5, fetch=True)
+    gain = np.float32(0.25 / np.sqrt(np.mean(np.abs(win) ** 2)) * 128.0)       # rms at -12 dBFS of the int8 range
+    w8 = np.clip(np.rint(win.view(np.float32).reshape(n, 2, -1, 2) * gain), -128, 127).astype(np.int8)
+    scale = np.float32(1.0) / gain
+    deq = np.ascontiguousarray((w8.astype(np.float32) * scale).reshape(n, 2, -1)).view(np.complex64)
+    s1, p1, ok1, tb1, rep1 = phy.rx(deq)
+    rep1 = rep1.copy()
+    phy.channel(n, snr_dB=-20.0, t0=0, mode=0, seed=6)   # scramble the device state in between
+    phy.sync(n=n)
+    s2, p2, ok2, tb2, rep2 = phy.rx(w8, sc16_scale=float(scale))
+    for a, b in ((s1, s2), (p1, p2), (rep1, rep2)):
+        for f in a.dtype.names:
+            assert np.array_equal(a[f], b[f]), f
+    assert np.array_equal(ok1, ok2) and np.array_equal(tb1, tb2)
+    assert ok2.mean() > 0.9 and (tb2[ok2] == tb[ok2]).all()
+    phy.close()
+
+
 def test_sync_refused_with_a_reason_at_very_high_oversampling(product):
     """FFT sizes above 4096 are supported by the transmitter and the synchronised receiver; the packet search keeps two
     STFs of prefix sums in shared memory and says so instead of failing at launch"""
