@@ -394,6 +394,16 @@ class Phy:
                                      None if out is None else out.ctypes.data_as(C.c_void_p)))
         return out
 
+    def sync_sc16(self, iq16, scale=1.0 / 32768.0, search_length=0):
+        """dnrp_sync_batch_sc16: iq16 [n][N_RX][rx_stride][2] int16 host windows; rx_pcc(None, n=n, sync="device") continues"""
+        n = iq16.shape[0]
+        assert iq16.dtype == np.int16 and iq16.flags["C_CONTIGUOUS"] and iq16.shape[1:] == (self.N_RX, self.rx_stride(), 2)
+        out = np.zeros(n, dtype=SYNC_RESULT_DTYPE).view(np.recarray)
+        f = lib().dnrp_sync_batch_sc16
+        f.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_float, C.c_uint32, C.c_void_p]
+        _check(f(self._ctx, n, iq16.ctypes.data_as(C.c_void_p), float(scale), int(search_length), out.ctypes.data_as(C.c_void_p)))
+        return out
+
     # ---- coarse_peak_f_domain_t between coarse and fine peak: beta search and integer CFO (off by default)
     def sync_set_fdomain(self, beta_threshold_dB=0.0, cfo_search_range_subc=0):
         """dnrp_sync_set_fdomain: beta_threshold_dB < 0 switches the beta search on (reference: -10 dB),

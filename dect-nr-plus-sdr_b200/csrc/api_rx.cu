@@ -317,6 +317,30 @@ int dnrp_sync_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, uint32_
 
 uint32_t dnrp_rx_stride(const dnrp_ctx_t* c) { return c ? c->rx_stride : 0; }
 
+// dnrp_sync_batch for windows in the radio's wire format (int16 I/Q): the windows cross the host link at half the size and
+// are converted on the device, where dnrp_rx_pcc_batch / dnrp_rx_pdc_batch continue on them (iq_in = NULL)
+int dnrp_sync_batch_sc16(dnrp_ctx_t* c, uint32_t n, const int16_t* iq_in, float scale, uint32_t search_length,
+                         dnrp_sync_result_t* out) {
+    DNRP_REQUIRE(c && iq_in, "null argument");
+    DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
+    DNRP_REQUIRE(scale > 0.f, "scale must be > 0");
+    DNRP_REQUIRE(search_length <= c->sync_len, "search_length exceeds the (resampled) IQ window");
+    DNRP_REQUIRE(c->rx_stride % 4 == 0, "sc16 ingest needs a window stride that is a multiple of 4");
+    DNRP_CUDA(cudaSetDevice(c->device));
+    const size_t win = (size_t)c->dims.N_RX * c->rx_stride;
+    if (!c->d_iq_sc16.p) DNRP_CUDA(c->d_iq_sc16.alloc((size_t)c->B * win * 2));
+    DNRP_CUDA(cudaMemcpyAsync(c->d_iq_sc16.p, iq_in, (size_t)n * win * 2 * sizeof(int16_t), cudaMemcpyHostToDevice, c->stream));
+    DNRP_LAUNCH(c, -1, launch_sc16_to_cf32(c->d_iq_sc16.p, c->d_iq_rx.p, (size_t)n * win, scale, c->stream));
+    c->last_search_length = search_length;
+    const int rc = run_sync(c, n, search_length, true);
+    if (rc) return rc;
+    if (out)
+        DNRP_CUDA(cudaMemcpyAsync(out, c->d_sync_result.p, n * sizeof(dnrp_sync_result_t), cudaMemcpyDeviceToHost,
+                                  c->stream));
+    DNRP_CUDA(cudaStreamSynchronize(c->stream));
+    return DNRP_OK;
+}
+
 int dnrp_rx_pcc_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_cf32_t* iq_in, const dnrp_sync_report_t* sync,
                       dnrp_pcc_report_t* out) {
     DNRP_REQUIRE(c && out, "null argument");

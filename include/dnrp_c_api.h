@@ -224,6 +224,14 @@ typedef struct {
 int dnrp_sync_batch(dnrp_ctx_t* ctx, uint32_t n, const dnrp_cf32_t* iq_in, uint32_t search_length,
                     dnrp_sync_result_t* out);
 
+/* dnrp_sync_batch for host windows in the radio's wire format, [n][N_RX][dnrp_rx_stride()][2] int16 (I, Q), converted on
+ * the device (sample = (I, Q) * scale; 1/32768 reproduces UHD's sc16 -> fc32 conversion, hw_usrp.cpp:436-438): half the
+ * host-link bytes for a caller that keeps the reference's flow sync -> PCC -> work_pcc -> PDC (dnrp_rx_pcc_batch and
+ * dnrp_rx_pdc_batch continue on the converted windows with iq_in = NULL).  dnrp_rx_stride() must be a multiple of 4. */
+int dnrp_sync_batch_sc16(dnrp_ctx_t* ctx, uint32_t n, const int16_t* iq_in, float scale, uint32_t search_length,
+                         dnrp_sync_result_t* out);
+
+
 /* Streaming front door: packet search over ONE continuous IQ stream instead of pre-cut windows -- the job of
  * worker_sync_t / sync_chunk_t / baton_t (lib/src/phy/pool/worker_sync.cpp:112-221, src/phy/rx/sync/sync_chunk.cpp:
  * 146-283, src/phy/pool/baton.cpp:157-169).  The stream is cut into chunks of chunk_hop samples (0: four packet

@@ -556,6 +556,23 @@ class batch_phy_t {
             deliver(n, sres, pcc, window_start_64, tpoint, tx_out);
             return tx_out;
         }
+        /// process_windows for windows in the radio's wire format: [n][N_RX][rx_stride][2] int16 (I, Q), sample = (I, Q) x
+        /// scale (1 / 32768 = UHD's sc16 -> fc32); half the bytes over the host link, converted on the device
+        machigh_phy_t::tx_descriptor_vec_t process_windows_sc16(uint32_t n, const int16_t* windows, float scale,
+                                                                const int64_t* window_start_64, upper::tpoint_t& tpoint) {
+            machigh_phy_t::tx_descriptor_vec_t tx_out;
+            if (n == 0) return tx_out;
+            if (n > max_windows) throw std::invalid_argument("more windows than the context was created for");
+            std::vector<dnrp_sync_result_t> sres(n);
+            check(dnrp_sync_batch_sc16(ctx, n, windows, scale, search_length, sres.data()), "dnrp_sync_batch_sc16");
+            std::vector<dnrp_pcc_report_t> pcc(n);
+            check(dnrp_rx_pcc_batch(ctx, n, nullptr, nullptr, pcc.data()), "dnrp_rx_pcc_batch");
+            stats.windows += n;
+            last_claimed.assign(n, 0);
+            for (uint32_t i = 0; i < n; ++i) last_claimed[i] = sres[i].detected && (pcc[i].plcf_ok[0] || pcc[i].plcf_ok[1]);
+            deliver(n, sres, pcc, window_start_64, tpoint, tx_out);
+            return tx_out;
+        }
         /// per window of the last process_windows call: a packet was found AND one of its PLCF CRCs passed
         const std::vector<uint8_t>& get_last_claimed() const { return last_claimed; }
 

@@ -5,6 +5,7 @@
 // Prints one JSON line; exit code 0 = all checks passed, 3 = no usable GPU (the library has no CPU fallback).
 #include <cuda_runtime_api.h>
 
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <map>
@@ -114,6 +115,16 @@ static int run(int device, uint32_t n, firmware_t*& fw_out, std::unique_ptr<phy:
     }
     bp.process_windows(n, win.data(), start.data(), fw);
     if (fw.n_work_pcc != n || fw.n_work_pdc != n || fw.n_work_pdc_error || fw.n_plcf_mismatch || fw.n_tb_mismatch) ++fails;
+    // the same windows in the radio's wire format (int16 I/Q at -20 dBFS rms): half the bytes over the host link, the same
+    // callbacks with the same transport blocks
+    std::vector<int16_t> w16((size_t)n * rx_stride * 2);
+    double pw = 0.0;
+    for (size_t q = 0; q < win.size(); ++q) pw += (double)win[q].re * win[q].re + (double)win[q].im * win[q].im;
+    const float gain = (float)(0.1 * 32768.0 / std::sqrt(pw / (double)win.size()));
+    auto q16 = [&](float v) { const float r = std::nearbyint(v * gain); return (int16_t)(r > 32767.f ? 32767.f : (r < -32768.f ? -32768.f : r)); };
+    for (size_t q = 0; q < win.size(); ++q) { w16[2 * q] = q16(win[q].re); w16[2 * q + 1] = q16(win[q].im); }
+    bp.process_windows_sc16(n, w16.data(), 1.0f / gain, start.data(), fw);
+    if (fw.n_work_pcc != 2 * n || fw.n_work_pdc != 2 * n || fw.n_work_pdc_error || fw.n_plcf_mismatch || fw.n_tb_mismatch) ++fails;
     return fails;
 }
 

@@ -113,7 +113,7 @@ def test_several_geometries_networks_and_plcf_types_in_one_call(tmp_path):
     r = subprocess.run([exe, "32"], capture_output=True, text=True, timeout=600)
     assert r.returncode == 0, (r.returncode, r.stdout, r.stderr)
     out = json.loads(r.stdout.strip().splitlines()[-1])
-    assert out["fails"] == 0 and out["work_pcc"] == 32 and out["work_pdc"] == 32 and out["tb_mismatch"] == 0
+    assert out["fails"] == 0 and out["work_pcc"] == 64 and out["work_pdc"] == 64 and out["tb_mismatch"] == 0
 
 
 def test_multi_beta_firmware_builds_and_refuses_to_run_without_gpu(tmp_path):
