@@ -408,6 +408,7 @@ class batch_phy_t {
                                             "must not be longer than it");
             }
             for (uint32_t id : network_ids) check(dnrp_add_network_id(pl.ctx, id), "dnrp_add_network_id");
+            if (track_cfo || track_sto) check(dnrp_rx_set_tracking(pl.ctx, track_cfo, track_sto), "dnrp_rx_set_tracking");
             plans.push_back(pl);
         }
 
@@ -440,7 +441,8 @@ class batch_phy_t {
         /// residual CFO / STO tracking on the DRS (rx_synced_param.hpp:156-181, compiled out in the reference) for every
         /// following reception
         void set_tracking(bool residual_cfo, bool residual_sto) {
-            check(dnrp_rx_set_tracking(ctx, residual_cfo, residual_sto), "dnrp_rx_set_tracking");
+            track_cfo = residual_cfo; track_sto = residual_sto;
+            for (auto& pl : plans) check(dnrp_rx_set_tracking(pl.ctx, residual_cfo, residual_sto), "dnrp_rx_set_tracking");
         }
         /// beta estimates and integer CFOs (subcarriers) of the windows of the last search (set_sync_fdomain switched on)
         void read_sync_fdomain(uint32_t n, std::vector<uint32_t>& beta, std::vector<int32_t>& cfo_subc) {
@@ -836,6 +838,7 @@ class batch_phy_t {
         bool comm_ready{false};
         uint32_t search_length{0};
         std::vector<uint8_t> last_claimed;
+        bool track_cfo{false}, track_sto{false};
         static void check(int rc, const char* what) {
             if (rc != DNRP_OK) throw std::runtime_error(std::string(what) + ": " + dnrp_last_error_string());
         }

@@ -123,6 +123,7 @@ static int run(int device, uint32_t n, firmware_t*& fw_out, std::unique_ptr<phy:
     const float gain = (float)(0.1 * 32768.0 / std::sqrt(pw / (double)win.size()));
     auto q16 = [&](float v) { const float r = std::nearbyint(v * gain); return (int16_t)(r > 32767.f ? 32767.f : (r < -32768.f ? -32768.f : r)); };
     for (size_t q = 0; q < win.size(); ++q) { w16[2 * q] = q16(win[q].re); w16[2 * q + 1] = q16(win[q].im); }
+    bp.set_tracking(true, true);   // residual CFO / STO stage on in every plan's context: no impairment, no change
     bp.process_windows_sc16(n, w16.data(), 1.0f / gain, start.data(), fw);
     if (fw.n_work_pcc != 2 * n || fw.n_work_pdc != 2 * n || fw.n_work_pdc_error || fw.n_plcf_mismatch || fw.n_tb_mismatch) ++fails;
     return fails;
