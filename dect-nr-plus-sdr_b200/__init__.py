@@ -460,6 +460,17 @@ class Phy:
                                       out.ctypes.data_as(C.c_void_p), C.byref(n_out)))
         return out[:n_out.value].view(np.recarray)
 
+    def stream_push_sc16(self, iq16, scale=1.0 / 32768.0, max_out=256):
+        """iq16 [N_RX][n][2] int16 hardware-rate samples in the radio's wire format -> the packets complete after this push"""
+        iq16 = np.ascontiguousarray(iq16, dtype=np.int16).reshape(self.N_RX, -1, 2)
+        out = np.zeros(max_out, dtype=STREAM_PACKET_DTYPE)
+        n_out = C.c_uint32(0)
+        f = lib().dnrp_stream_push_sc16
+        f.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_float, C.c_uint32, C.c_void_p, C.c_void_p]
+        _check(f(self._ctx, iq16.shape[1], iq16.ctypes.data_as(C.c_void_p) if iq16.shape[1] else None, float(scale), int(max_out),
+                 out.ctypes.data_as(C.c_void_p), C.byref(n_out)))
+        return out[:n_out.value].view(np.recarray)
+
     def stream_close(self):
         _check(lib().dnrp_stream_close(self._ctx))
 

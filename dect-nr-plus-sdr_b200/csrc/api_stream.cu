@@ -360,8 +360,23 @@ int dnrp_stream_close(dnrp_ctx_t* c) {
     return DNRP_OK;
 }
 
+// sc16_scale != 0: iq holds int16 I/Q pairs [N_RX][n_samples][2] (the radio's wire format), converted on the device
+static int stream_push_impl(dnrp_ctx_t* c, uint32_t n_samples, const void* iq, float sc16_scale, uint32_t max_out,
+                            dnrp_stream_packet_t* out, uint32_t* n_out);
+
 int dnrp_stream_push(dnrp_ctx_t* c, uint32_t n_samples, const dnrp_cf32_t* iq, uint32_t max_out, dnrp_stream_packet_t* out,
                      uint32_t* n_out) {
+    return stream_push_impl(c, n_samples, iq, 0.f, max_out, out, n_out);
+}
+
+int dnrp_stream_push_sc16(dnrp_ctx_t* c, uint32_t n_samples, const int16_t* iq, float scale, uint32_t max_out,
+                          dnrp_stream_packet_t* out, uint32_t* n_out) {
+    DNRP_REQUIRE(scale > 0.f, "scale must be > 0");
+    return stream_push_impl(c, n_samples, iq, scale, max_out, out, n_out);
+}
+
+static int stream_push_impl(dnrp_ctx_t* c, uint32_t n_samples, const void* iq, float sc16_scale, uint32_t max_out,
+                            dnrp_stream_packet_t* out, uint32_t* n_out) {
     DNRP_REQUIRE(c && out && n_out, "null argument");
     DNRP_REQUIRE(n_samples == 0 || iq, "null argument");
     auto& ss = c->ss;
@@ -409,7 +424,12 @@ int dnrp_stream_push(dnrp_ctx_t* c, uint32_t n_samples, const dnrp_cf32_t* iq, u
     DNRP_REQUIRE(ss.hw_len + n_samples + ((size_t)ss.len * L) / M + 8 <= ss.cap_hw, "stream ring overflow (hardware rate)");
 
     // ---- 2. append the new samples, zeros behind them (the last chunk window reads past the data)
-    if (n_samples)
+    if (n_samples && sc16_scale != 0.f) {
+        if (c->d_stream_sc16.n < (size_t)d.N_RX * ss.max_push * 2) DNRP_CUDA(c->d_stream_sc16.alloc((size_t)d.N_RX * ss.max_push * 2));
+        DNRP_CUDA(cudaMemcpyAsync(c->d_stream_sc16.p, iq, (size_t)d.N_RX * n_samples * 2 * sizeof(int16_t), cudaMemcpyHostToDevice, c->stream));
+        DNRP_LAUNCH(c, -1, launch_sc16_rows_to_cf32(c->d_stream_sc16.p, n_samples, hw + ss.hw_len, ss.cap_hw, n_samples, d.N_RX,
+                                                    sc16_scale, c->stream));
+    } else if (n_samples)
         DNRP_CUDA(cudaMemcpy2DAsync(hw + ss.hw_len, ss.cap_hw * sizeof(float2), iq, (size_t)n_samples * sizeof(float2),
                                     (size_t)n_samples * sizeof(float2), d.N_RX, cudaMemcpyHostToDevice, c->stream));
     ss.hw_len += n_samples;

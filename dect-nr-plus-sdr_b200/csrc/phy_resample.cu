@@ -215,6 +215,26 @@ cudaError_t launch_sc8_to_cf32(const int8_t* in, float2* out, size_t n_samples, 
     return cudaGetLastError();
 }
 
+// rows of int16 I/Q pairs -> rows of float2 at any offset (the stream ring is appended at arbitrary sample positions):
+// one sample per thread, 4 B in, 8 B out
+__global__ void __launch_bounds__(256) k_sc16_rows_to_cf32(const uint32_t* __restrict__ in, size_t in_stride, float2* __restrict__ out,
+                                                            size_t out_stride, uint32_t n, float scale) {
+    const uint32_t a = blockIdx.y;
+    for (uint32_t i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const uint32_t w = __ldg(in + a * in_stride + i);
+        out[a * out_stride + i] = make_float2((float)(int16_t)(w & 0xffff) * scale, (float)(int16_t)(w >> 16) * scale);
+    }
+}
+
+cudaError_t launch_sc16_rows_to_cf32(const int16_t* in, size_t in_stride_samples, float2* out, size_t out_stride_samples,
+                                     uint32_t n_samples, uint32_t n_rows, float scale, cudaStream_t st) {
+    if (n_samples == 0 || n_rows == 0) return cudaSuccess;
+    const unsigned gx = (unsigned)std::min<size_t>(((size_t)n_samples + 255) / 256, 148 * 8);
+    k_sc16_rows_to_cf32<<<dim3(gx, n_rows), 256, 0, st>>>(reinterpret_cast<const uint32_t*>(in), in_stride_samples, out,
+                                                          out_stride_samples, n_samples, scale);
+    return cudaGetLastError();
+}
+
 cudaError_t launch_sc16_to_cf32(const int16_t* in, float2* out, size_t n_samples, float scale, cudaStream_t st) {
     if (n_samples == 0) return cudaSuccess;
     if (n_samples % 4) return cudaErrorInvalidValue;

@@ -266,6 +266,10 @@ int dnrp_stream_sync(dnrp_ctx_t* ctx, uint64_t n_samples, const dnrp_cf32_t* iq,
  * the packets of one push before the next push.  Results do not depend on how the stream is cut into pushes, except
  * for double detections within one STF pattern, which are dropped in either case. */
 int dnrp_stream_open(dnrp_ctx_t* ctx, uint32_t max_push_samples, uint32_t chunk_hop);
+/* dnrp_stream_push_sc16: the same for samples in the radio's wire format, iq [N_RX][n_samples][2] int16 (I, Q), sample =
+ * (I, Q) * scale on the device (1/32768 = UHD's sc16 -> fc32, hw_usrp.cpp:436-438): half the host-link bytes */
+int dnrp_stream_push_sc16(dnrp_ctx_t* ctx, uint32_t n_samples, const int16_t* iq, float scale, uint32_t max_out,
+                          dnrp_stream_packet_t* out, uint32_t* n_out);
 int dnrp_stream_push(dnrp_ctx_t* ctx, uint32_t n_samples, const dnrp_cf32_t* iq, uint32_t max_out, dnrp_stream_packet_t* out,
                      uint32_t* n_out);
 int dnrp_stream_close(dnrp_ctx_t* ctx);

@@ -614,6 +614,20 @@ class batch_phy_t {
             }
             return tx_out;
         }
+        /// push_stream for samples in the radio's wire format: [N_RX][n_samples][2] int16 (I, Q), sample = (I, Q) x scale
+        machigh_phy_t::tx_descriptor_vec_t push_stream_sc16(uint32_t n_samples, const int16_t* samples, float scale,
+                                                            upper::tpoint_t& tpoint) {
+            machigh_phy_t::tx_descriptor_vec_t tx_out;
+            std::vector<dnrp_stream_packet_t> found(max_windows);
+            const int16_t* src = samples;
+            for (uint32_t n = n_samples;; n = 0, src = nullptr) {
+                uint32_t n_found = 0;
+                check(dnrp_stream_push_sc16(ctx, n, src, scale, max_windows, found.data(), &n_found), "dnrp_stream_push_sc16");
+                deliver_found(found.data(), n_found, stream_clock_64, tpoint, tx_out);
+                if (n_found < max_windows) break;
+            }
+            return tx_out;
+        }
         void close_stream() { check(dnrp_stream_close(ctx), "dnrp_stream_close"); }
 
         /// PHY_JSON_SWITCH_IMPLEMENT_ANY_JSON_FUNCTIONALITY of the reference (worker_tx_rx.cpp:356-414): from now on every

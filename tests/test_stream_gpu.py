@@ -220,3 +220,32 @@ def test_stream_push_limits(product):
     with pytest.raises(product.DnrpError, match="shared memory"):
         phy.stream_sync(np.zeros((1, 4000), dtype=np.complex64), chunk_hop=10_000_000)
     phy.close()
+
+
+@pytest.mark.parametrize("cfg,os_,resample", [((1, 2, 1, 1, 0, 3, 2048), 1, (1, 1)), ((1, 1, 1, 1, 0, 2, 2048), 2, (10, 9))])
+def test_stream_push_sc16_equals_push_of_the_dequantised_stream(product, cfg, os_, resample):
+    """dnrp_stream_push_sc16 (the radio's wire format, converted on the device at whatever ring offset the push lands)
+    hands out record for record what dnrp_stream_push hands out for the float stream int16 * scale, cut at odd positions"""
+    phy, stream, starts, tb, plcf, S = _make_stream_hw(product, cfg, 16, snr_db=20.0, seed=11, os_=os_, resample=resample)
+    n = stream.shape[1]
+    gain = np.float32(0.1 / np.sqrt(np.mean(np.abs(stream) ** 2)) * 32768.0)
+    s16 = np.clip(np.rint(stream.view(np.float32).reshape(stream.shape[0], n, 2) * gain), -32768, 32767).astype(np.int16)
+    scale = np.float32(1.0) / gain
+    deq = np.ascontiguousarray(s16.astype(np.float32) * scale).view(np.complex64).reshape(stream.shape[0], n)
+    cuts = np.array([0, starts[1] + 37, starts[4] + S // 2 + 1, starts[4] + S // 2 + 66, starts[9] - 3, starts[13] + 7, n])
+    max_push = int(np.diff(cuts).max())
+    ref = _push_all(phy, deq, cuts, max_push, 0)
+    phy.stream_open(max_push, chunk_hop=0)
+    got = []
+    for a, b in zip(cuts[:-1], cuts[1:]):
+        r = phy.stream_push_sc16(np.ascontiguousarray(s16[:, a:b]), scale=float(scale))
+        if len(r):
+            got.append(r.copy())
+    phy.stream_close()
+    got = np.concatenate(got).view(np.recarray)
+    assert len(got) == len(ref) and np.isin(starts, got.fine_peak_time_64).all()
+    assert np.array_equal(got.fine_peak_time_64, ref.fine_peak_time_64)
+    assert np.array_equal(got.coarse_peak_time_64, ref.coarse_peak_time_64)
+    assert np.array_equal(got.sync.cfo_fractional_rad, ref.sync.cfo_fractional_rad)
+    assert np.array_equal(got.sync.rms_array, ref.sync.rms_array)
+    phy.close()
