@@ -286,7 +286,8 @@ class Phy:
 
     # ---- tx_t::generate_tx_packet (reference lib/src/phy/tx/tx.cpp:165-314)
     def tx(self, plcf, tb, codebook_index=0, DAC_scale=1.0, iq_phase_rad=0.0, iq_phase_increment=0.0,
-           GI_percentage=5, rv=0, optimal_scaling_DAC=False, fetch=True):
+           GI_percentage=5, rv=0, optimal_scaling_DAC=False, fetch=True, sc16_scale=None):
+        """dnrp_tx_batch; sc16_scale: dnrp_tx_batch_sc16, the IQ comes back as int16 [n][N_TX][stride][2] = round(sample x scale)"""
         n = tb.shape[0]
         plcf = np.ascontiguousarray(plcf, dtype=np.uint8).reshape(n, 10)
         tb = np.ascontiguousarray(tb, dtype=np.uint8).reshape(n, self.ps["N_TB_byte"])
@@ -304,6 +305,13 @@ class Phy:
         stride = lib().dnrp_tx_stride(self._ctx)
         iq = np.zeros((n, self.ps["N_TX"], stride), dtype=np.complex64) if fetch else None
         ns = np.zeros(n, dtype=np.uint32)
+        if sc16_scale is not None:
+            iq16 = np.zeros((n, self.ps["N_TX"], stride, 2), dtype=np.int16)
+            f = lib().dnrp_tx_batch_sc16
+            f.argtypes = [C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_float, C.c_void_p]
+            _check(f(self._ctx, n, C.cast(descs, C.c_void_p), plcf.ctypes.data_as(C.c_void_p), tb.ctypes.data_as(C.c_void_p),
+                     iq16.ctypes.data_as(C.c_void_p), float(sc16_scale), ns.ctypes.data_as(C.c_void_p)))
+            return iq16, ns
         _check(lib().dnrp_tx_batch(self._ctx, n, descs, _ptr(plcf, np.uint8), _ptr(tb, np.uint8),
                                    _ptr(iq, np.complex64), _ptr(ns, np.uint32)))
         return iq, ns

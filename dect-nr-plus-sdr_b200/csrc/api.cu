@@ -472,8 +472,22 @@ extern "C" {
 
 uint32_t dnrp_tx_stride(const dnrp_ctx_t* c) { return c ? c->tx_stride : 0; }
 
+static int tx_batch_impl(dnrp_ctx_t* c, uint32_t n, const dnrp_tx_desc_t* descs, const uint8_t* plcf, const uint8_t* tb,
+                         void* iq_out, float sc16_scale, uint32_t* n_samples_out);
+
 int dnrp_tx_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_tx_desc_t* descs, const uint8_t* plcf, const uint8_t* tb,
                   dnrp_cf32_t* iq_out, uint32_t* n_samples_out) {
+    return tx_batch_impl(c, n, descs, plcf, tb, iq_out, 0.f, n_samples_out);
+}
+
+int dnrp_tx_batch_sc16(dnrp_ctx_t* c, uint32_t n, const dnrp_tx_desc_t* descs, const uint8_t* plcf, const uint8_t* tb,
+                       int16_t* iq_out, float scale, uint32_t* n_samples_out) {
+    DNRP_REQUIRE(iq_out && scale > 0.f, "dnrp_tx_batch_sc16 needs an output buffer and a scale > 0");
+    return tx_batch_impl(c, n, descs, plcf, tb, iq_out, scale, n_samples_out);
+}
+
+static int tx_batch_impl(dnrp_ctx_t* c, uint32_t n, const dnrp_tx_desc_t* descs, const uint8_t* plcf, const uint8_t* tb,
+                         void* iq_out, float sc16_scale, uint32_t* n_samples_out) {
     DNRP_REQUIRE(c && descs && plcf && tb, "null argument");
     DNRP_REQUIRE(n > 0 && n <= c->B, "batch size out of range");
     DNRP_CUDA(cudaSetDevice(c->device));
@@ -505,9 +519,14 @@ int dnrp_tx_batch(dnrp_ctx_t* c, uint32_t n, const dnrp_tx_desc_t* descs, const 
     int rc = run_fec_encode(c, n, true, true);
     if (rc) return rc;
     if ((rc = run_tx_ofdm(c, n)) != DNRP_OK) return rc;
-    if (iq_out)
-        DNRP_CUDA(cudaMemcpyAsync(iq_out, c->d_iq_tx.p, (size_t)n * d.N_TX * c->tx_stride * sizeof(float2),
-                                  cudaMemcpyDeviceToHost, c->stream));
+    const size_t n_iq = (size_t)n * d.N_TX * c->tx_stride;
+    if (iq_out && sc16_scale != 0.f) {
+        DNRP_REQUIRE(c->tx_stride % 4 == 0, "sc16 output needs a transmit stride that is a multiple of 4");
+        if (!c->d_iq_tx_sc16.p) DNRP_CUDA(c->d_iq_tx_sc16.alloc((size_t)c->B * d.N_TX * c->tx_stride * 2));
+        DNRP_LAUNCH(c, -1, launch_cf32_to_sc16(c->d_iq_tx.p, c->d_iq_tx_sc16.p, n_iq, sc16_scale, c->stream));
+        DNRP_CUDA(cudaMemcpyAsync(iq_out, c->d_iq_tx_sc16.p, n_iq * 2 * sizeof(int16_t), cudaMemcpyDeviceToHost, c->stream));
+    } else if (iq_out)
+        DNRP_CUDA(cudaMemcpyAsync(iq_out, c->d_iq_tx.p, n_iq * sizeof(float2), cudaMemcpyDeviceToHost, c->stream));
     DNRP_CUDA(cudaStreamSynchronize(c->stream));
     return DNRP_OK;
 }

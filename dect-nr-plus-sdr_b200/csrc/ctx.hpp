@@ -172,6 +172,7 @@ struct dnrp_ctx {
     uint32_t tx_os_stride = 0, sync_stride = 0, sync_len = 0, rs_stride = 0;
     dnrp::dbuf<float2> d_iq_tx_os;              // [B][N_TX][tx_os_stride] TX IQ before resampling
     dnrp::dbuf<float2> d_iq_sync;               // [B][N_RX][sync_stride] window resampled for detection / coarse peak
+    dnrp::dbuf<int16_t> d_iq_tx_sc16;           // [B][N_TX][tx_stride][2] staging of dnrp_tx_batch_sc16 (allocated on first use)
     dnrp::dbuf<int16_t> d_stream_sc16;          // [N_RX][max_push][2] staging of dnrp_stream_push_sc16 (allocated on first use)
     dnrp::dbuf<int16_t> d_iq_sc16;              // [B][N_RX][rx_stride][2] staging of dnrp_rx_batch_sc16 (allocated on first use)
     dnrp::dbuf<float2> d_iq_rs;                 // [B][N_RX][rs_stride] packet resampled from the fine peak

@@ -174,6 +174,7 @@ cudaError_t launch_resample(const resample_params_t& p, uint32_t n_packets, cuda
 cudaError_t launch_sc16_to_cf32(const int16_t* in, float2* out, size_t n_samples, float scale, cudaStream_t st);
 cudaError_t launch_sc16_rows_to_cf32(const int16_t* in, size_t in_stride_samples, float2* out, size_t out_stride_samples,
                                      uint32_t n_samples, uint32_t n_rows, float scale, cudaStream_t st);
+cudaError_t launch_cf32_to_sc16(const float2* in, int16_t* out, size_t n_samples, float scale, cudaStream_t st);
 cudaError_t launch_sc8_to_cf32(const int8_t* in, float2* out, size_t n_samples, float scale, cudaStream_t st);
 
 // packet synchronisation (phy_sync.cu): detection, coarse peak, fine peak of the first packet in each window

@@ -215,6 +215,26 @@ cudaError_t launch_sc8_to_cf32(const int8_t* in, float2* out, size_t n_samples, 
     return cudaGetLastError();
 }
 
+// ---- cf32 -> sc16 (the transmit direction of the wire format: UHD converts fc32 -> sc16 on the host CPU, hw_usrp.cpp:422-424):
+// round to nearest, saturate; 4 complex samples per thread, 32 B in, 16 B out
+__global__ void __launch_bounds__(256) k_cf32_to_sc16(const float4* __restrict__ in, int4* __restrict__ out, size_t n4, float scale) {
+    for (size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += (size_t)gridDim.x * blockDim.x) {
+        const float4 a = __ldg(in + 2 * i), b = __ldg(in + 2 * i + 1);
+        auto q = [scale](float v) { return (uint32_t)(uint16_t)(int16_t)max(-32768, min(32767, __float2int_rn(v * scale))); };
+        out[i] = make_int4((int)(q(a.x) | (q(a.y) << 16)), (int)(q(a.z) | (q(a.w) << 16)), (int)(q(b.x) | (q(b.y) << 16)),
+                           (int)(q(b.z) | (q(b.w) << 16)));
+    }
+}
+
+cudaError_t launch_cf32_to_sc16(const float2* in, int16_t* out, size_t n_samples, float scale, cudaStream_t st) {
+    if (n_samples == 0) return cudaSuccess;
+    if (n_samples % 4) return cudaErrorInvalidValue;
+    const size_t n4 = n_samples / 4;
+    const unsigned grid = (unsigned)std::min<size_t>((n4 + 255) / 256, 148 * 16);
+    k_cf32_to_sc16<<<grid, 256, 0, st>>>(reinterpret_cast<const float4*>(in), reinterpret_cast<int4*>(out), n4, scale);
+    return cudaGetLastError();
+}
+
 // rows of int16 I/Q pairs -> rows of float2 at any offset (the stream ring is appended at arbitrary sample positions):
 // one sample per thread, 4 B in, 8 B out
 __global__ void __launch_bounds__(256) k_sc16_rows_to_cf32(const uint32_t* __restrict__ in, size_t in_stride, float2* __restrict__ out,

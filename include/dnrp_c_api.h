@@ -155,6 +155,14 @@ uint32_t dnrp_tx_stride(const dnrp_ctx_t* ctx);
 int dnrp_tx_batch(dnrp_ctx_t* ctx, uint32_t n, const dnrp_tx_desc_t* descs, const uint8_t* plcf,
                   const uint8_t* tb, dnrp_cf32_t* iq_out, uint32_t* n_samples_out);
 
+/* dnrp_tx_batch with the IQ in the radio's wire format: iq_out [n][N_TX][dnrp_tx_stride()][2] int16 (I, Q) =
+ * round-to-nearest(sample * scale), saturated (scale = 32767 corresponds to UHD's fc32 -> sc16 conversion, which the
+ * reference leaves to UHD on the host CPU: lib/src/radio/hw_usrp.cpp:422-424, cpu_format "fc32", otw_format "sc16").
+ * Halves the device-to-host bytes; the float IQ stays on the device as after dnrp_tx_batch.  dnrp_tx_stride() must be a
+ * multiple of 4. */
+int dnrp_tx_batch_sc16(dnrp_ctx_t* ctx, uint32_t n, const dnrp_tx_desc_t* descs, const uint8_t* plcf,
+                       const uint8_t* tb, int16_t* iq_out, float scale, uint32_t* n_samples_out);
+
 /* ---- synchronised receiver ----------------------------------------------------------------------
  * dnrp_sync_report_t = the fields of sync_report_t the synchronised receiver consumes
  * (lib/include/dectnrp/phy/rx/sync/sync_report.hpp:41-111).  fine_peak_time_local is the index of the

@@ -60,3 +60,24 @@ def test_tx_iq_matches_oracle(product, name):
         assert evm_db(got, ref) < -80.0, (name, i, evm_db(got, ref))
         assert not iq[i, :, ns[i]:].any()
     phy.close()
+
+
+def test_tx_batch_sc16_is_the_rounded_float_output(product):
+    """dnrp_tx_batch_sc16: the same packets as dnrp_tx_batch, every sample round-to-nearest(sample x scale) saturated to
+    int16 (what UHD's fc32 -> sc16 conversion does on the host in the reference, hw_usrp.cpp:422-424)"""
+    cfg = (1, 4, 1, 2, 5, 3, 2048)       # four transmit antennas
+    ps = spec.get_packet_sizes(*cfg)
+    n = 5
+    phy = product.Phy(cfg, max_batch=n, network_id=123456789, plcf_type=1)
+    rng = np.random.default_rng(3)
+    tb = rng.integers(0, 256, (n, ps["N_TB_byte"]), dtype=np.uint8)
+    plcf = rng.integers(0, 256, (n, 10), dtype=np.uint8)
+    iq, ns = phy.tx(plcf, tb)
+    for scale in (32767.0, 2.0e5):     # the second one saturates the peaks
+        iq16, ns16 = phy.tx(plcf, tb, sc16_scale=scale)
+        assert np.array_equal(ns, ns16)
+        want = np.clip(np.rint(iq.view(np.float32).reshape(iq16.shape).astype(np.float32) * np.float32(scale)), -32768, 32767)
+        d = np.abs(iq16.astype(np.int32) - want.astype(np.int32))
+        assert d.max() <= 1 and (d > 0).mean() < 1e-3      # ties and the product's rounding in float32
+        assert scale < 1e5 or (np.abs(iq16) == 32767).any() or (iq16 == -32768).any()
+    phy.close()
