@@ -298,6 +298,28 @@ int main(int argc, char** argv) {
         if (fw.n_work_pcc - pcc0 != p4.size() || push_found != p4.size() || fw.n_tb_mismatch || fw.n_plcf_mismatch) ++fails;
         for (size_t i = 0; i < p4.size() && fw.order.size() >= p4.size(); ++i)
             if (fw.order[fw.order.size() - p4.size() + i] != (int64_t)(7000000 + at[i])) { ++fails; break; }
+        // the same stream in the radio's wire format (int16 I/Q, push_stream_sc16): the same packets at the same times
+        const uint32_t pdc1 = fw.n_work_pdc;
+        const float gain16 = 0.1f * 32768.0f / 0.5f;     // the packets have an rms of about 0.5 here
+        bp->open_stream(max_push, 9000000);
+        std::vector<int16_t> piece16;
+        for (size_t pos = 0; pos < total;) {
+            const size_t len = std::min<size_t>(total - pos, 1 + rng() % max_push);
+            piece16.resize(4 * len);
+            for (uint32_t a = 0; a < 2; ++a)
+                for (size_t q = 0; q < len; ++q) {
+                    const cf_t v = stream[a * total + pos + q];
+                    auto q16 = [&](float x) { const float r = std::nearbyint(x * gain16); return (int16_t)(r > 32767.f ? 32767.f : (r < -32768.f ? -32768.f : r)); };
+                    piece16[2 * (a * len + q)] = q16(v.re);
+                    piece16[2 * (a * len + q) + 1] = q16(v.im);
+                }
+            bp->push_stream_sc16((uint32_t)len, piece16.data(), 1.0f / gain16, fw);
+            pos += len;
+        }
+        bp->close_stream();
+        if (fw.n_work_pdc - pdc1 != p4.size() || fw.n_tb_mismatch || fw.n_plcf_mismatch) ++fails;
+        for (size_t i = 0; i < p4.size() && fw.order.size() >= p4.size(); ++i)
+            if (fw.order[fw.order.size() - p4.size() + i] != (int64_t)(9000000 + at[i])) { ++fails; break; }
     }
 
     const size_t json_files = bp->flush_json_export().size();
