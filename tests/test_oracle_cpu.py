@@ -1,5 +1,6 @@
 """CPU tests (no GPU): oracle pinned against published known answers, product host tables against the
 oracle, and the C ABI export list against include/dnrp_c_api.h."""
+import os
 import re
 import subprocess
 
@@ -7,7 +8,7 @@ import numpy as np
 import pytest
 
 from oracle import fec, spec
-from conftest import CONFIGS
+from conftest import CONFIGS, ROOT
 
 
 def test_crc_known_answers():
@@ -198,3 +199,29 @@ def test_tdl_profiles_rms_delay_spread():
     # equal sample delays are merged (link.cpp:103-121)
     d2, p2 = ochan.tdl_pdp(1.728e6, 0, 43.13)
     assert len(d2) < 7 and len(set(d2.tolist())) == len(d2) and abs(p2.sum() - 1.0) < 1e-12
+
+
+def test_binding_structs_have_the_layout_of_the_header(product, tmp_path):
+    """the ctypes / numpy mirrors of the C ABI's structs (dect-nr-plus-sdr_b200/__init__.py) against sizeof / offsetof of
+    include/dnrp_c_api.h compiled by gcc: a field added to the header and not to the binding shows up here, without a GPU"""
+    import ctypes as C
+    import subprocess
+    src = tmp_path / "layout.c"
+    src.write_text('''#include <stdio.h>
+#include <stddef.h>
+#include "dnrp_c_api.h"
+int main(void) {
+    printf("%zu %zu %zu %zu %zu %zu %zu %zu %zu %zu %zu\\n", sizeof(dnrp_psdef_t), sizeof(dnrp_packet_sizes_t), sizeof(dnrp_config_t),
+           offsetof(dnrp_config_t, N_soft), offsetof(dnrp_config_t, M_DL_HARQ), sizeof(dnrp_tx_desc_t), sizeof(dnrp_sync_report_t),
+           sizeof(dnrp_pcc_report_t), sizeof(dnrp_pdc_report_t), sizeof(dnrp_sync_result_t), sizeof(dnrp_stream_packet_t));
+    return 0;
+}
+''')
+    exe = tmp_path / "layout"
+    subprocess.check_call(["gcc", "-std=c11", "-I" + os.path.join(ROOT, "include"), str(src), "-o", str(exe)])
+    got = [int(v) for v in subprocess.check_output([str(exe)], text=True).split()]
+    p = product
+    want = [C.sizeof(p.Psdef), C.sizeof(p.PacketSizes), C.sizeof(p.Config), p.Config.N_soft.offset, p.Config.M_DL_HARQ.offset,
+            C.sizeof(p.TxDesc), C.sizeof(p.SyncReport), C.sizeof(p.PccReport), C.sizeof(p.PdcReport), p.SYNC_RESULT_DTYPE.itemsize,
+            p.STREAM_PACKET_DTYPE.itemsize]
+    assert got == want, (got, want)
