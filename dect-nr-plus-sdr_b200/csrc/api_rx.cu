@@ -440,11 +440,14 @@ static int rx_batch_impl(dnrp_ctx_t* c, uint32_t n, const void* iq_in, float sc1
         // 1.7 GB per 4000 windows -- ends with the computation of its last chunk: ten chunks with a long taper took
         // 32.72 -> 31.86 ms there; with short windows (C2, 0.24 GB) the 0.19 ms per chunk weigh more: 6.28 -> 6.76 ms,
         // so the taper is for calls of 768 MiB and more only.  profiles/tools/e2e_chunks.sh)
-        static const uint32_t w10[] = {1, 2, 3, 4, 4, 4, 3, 2, 1, 1};
+        // 8192 windows and more in a packed format: fifteen chunks with the same taper, 72.49 -> 70.63 ms per 9000 north-star
+        // windows (profiles/tools/e2e_chunks_large.sh); complex64 windows already go in sixteen chunks
+        static const uint32_t w10[] = {1, 2, 3, 4, 4, 4, 3, 2, 1, 1}, w15[] = {1, 2, 3, 4, 4, 4, 4, 4, 4, 4, 4, 3, 2, 1, 1};
         const uint64_t call_bytes = (uint64_t)n * c->dims.N_RX * c->rx_stride * (sc16 ? 2u * sc_bytes : 8u);
         const bool long_copy = n >= 2048 && n < 8192 && call_bytes >= (768ull << 20);
-        const uint32_t* w = long_copy ? w10 : n >= 8192 ? (sc16 ? ws : wc) : (n >= 2048 ? w6 : (n >= 256 ? w3 : w1));
-        uint32_t nw = long_copy ? 10 : n >= 8192 ? (sc16 ? 7 : 16) : (n >= 2048 ? 6 : (n >= 256 ? 3 : 1));
+        const bool long_copy15 = n >= 8192 && sc16 && call_bytes >= (768ull << 20);
+        const uint32_t* w = long_copy ? w10 : long_copy15 ? w15 : n >= 8192 ? (sc16 ? ws : wc) : (n >= 2048 ? w6 : (n >= 256 ? w3 : w1));
+        uint32_t nw = long_copy ? 10 : long_copy15 ? 15 : n >= 8192 ? (sc16 ? 7 : 16) : (n >= 2048 ? 6 : (n >= 256 ? 3 : 1));
         const char* env_chunks = std::getenv("DNRP_RX_CHUNKS");   // tuning knobs: that many equal chunks, or weights
         const char* env_w = std::getenv("DNRP_RX_WEIGHTS");       // "3,4,5,..."
         std::vector<uint32_t> eq;
